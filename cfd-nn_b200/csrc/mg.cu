@@ -1,0 +1,438 @@
+// mg.cu — host orchestration of the multigrid V-cycle (see mg.cuh for the layout).
+#include "mg_kernels.cuh"
+#include "comm.cuh"
+#include <cmath>
+#include <algorithm>
+#include <cstring>
+
+namespace cfdnn {
+
+static inline dim3 grid2(int nx, int ny, int nz, dim3 b) {
+    return dim3((nx + b.x - 1) / b.x, (ny + b.y - 1) / b.y, nz);
+}
+static const dim3 kBlk(64, 4, 1);
+constexpr int KZ = 8;
+
+// ---------------------------------------------------------------- construction
+// create_hierarchy (:155-230) + compute_gershgorin_bounds (:232-305)
+Multigrid::Multigrid(const cfdnn_mesh_desc& m) : mesh_(m) {
+    require_device();
+    if (m.Nz <= 1) throw std::invalid_argument("Multigrid: 2-D meshes are handled by Multigrid2D");
+    if (m.Ng != 1) throw std::invalid_argument("Multigrid: only Nghost == 1 (O2 stencils) is supported");
+    ystretched_ = m.y_stretched != 0;
+    semi_ = ystretched_;
+    if (ystretched_) throw std::invalid_argument("Multigrid: y-stretched semi-coarsening not built yet");
+    const int NzG = m.Nz_global > 0 ? m.Nz_global : m.Nz;
+
+    int Nx = m.Nx, Ny = m.Ny, Nz = m.Nz, NzGlob = NzG;
+    double dx = m.dx, dy = m.dy, dz = m.dz;
+    auto add = [&](int nx, int ny, int nz, int nzg, double hx, double hy, double hz) {
+        auto L = std::make_unique<Level>();
+        L->g.Nx = nx; L->g.Ny = ny; L->g.Nz = nz;
+        L->g.Px = (nx + 15) / 16 * 16;
+        L->g.plane = (long long)L->g.Px * ny;
+        L->dx = hx; L->dy = hy; L->dz = hz; L->NzGlobal = nzg;
+        const double dx2 = hx * hx, dy2 = hy * hy, dz2 = hz * hz;
+        L->g.dx2 = make_div_host(dx2);
+        L->g.dy2 = make_div_host(dy2);
+        L->g.dz2 = make_div_host(dz2);
+        L->g.coeff = make_div_host(2.0 / dx2 + 2.0 / dy2 + 2.0 / dz2);   // :845-846
+        L->g.inv_dx2_2 = 2.0 / dx2;
+        L->g.inv_dz2_2 = 2.0 / dz2;
+        L->g.nonuniform_y = 0; L->g.joff = 0;
+        L->g.aS = L->g.aN = L->g.aP = nullptr;
+        L->size = (size_t)(nz + 2) * L->g.plane;
+        L->u.alloc(L->size); L->f.alloc(L->size); L->r.alloc(L->size); L->tmp.alloc(L->size);
+        L->lambda_max = std::max(1.8, (1.0 + 1.0) * 1.10);               // :283-294 uniform
+        levels_.push_back(std::move(L));
+    };
+    add(Nx, Ny, Nz, NzGlob, dx, dy, dz);
+    constexpr int MIN_COARSE = 8;
+    while (Nx > MIN_COARSE && Ny > MIN_COARSE && NzGlob > MIN_COARSE) {
+        if ((Nx | Ny | Nz | NzGlob) & 1)
+            throw std::invalid_argument("Multigrid: grid sizes must stay even while coarsening");
+        Nx /= 2; Ny /= 2; Nz /= 2; NzGlob /= 2;
+        dx *= 2.0; dy *= 2.0; dz *= 2.0;
+        add(Nx, Ny, Nz, NzGlob, dx, dy, dz);
+    }
+    size_t maxblocks = 0;
+    for (auto& L : levels_) {
+        dim3 g1 = grid2(L->g.Nx, L->g.Ny, L->g.Nz, kBlk);
+        maxblocks = std::max(maxblocks, (size_t)g1.x * g1.y * g1.z);
+    }
+    partial_.alloc(2 * maxblocks + 16);
+    scalars_.alloc(16);
+    CFDNN_CUDA(cudaMallocHost(&h_scalars_, 16 * sizeof(double)));
+    CFDNN_CUDA(cudaEventCreate(&ev0_));
+    CFDNN_CUDA(cudaEventCreate(&ev1_));
+    apply_bc_codes();
+}
+
+Multigrid::~Multigrid() {
+    if (graph_) cudaGraphExecDestroy(graph_);
+    if (h_scalars_) cudaFreeHost(h_scalars_);
+    if (ev0_) cudaEventDestroy(ev0_);
+    if (ev1_) cudaEventDestroy(ev1_);
+}
+
+void Multigrid::set_bc(const int bc[6]) {
+    for (int d = 0; d < 6; ++d) {
+        if (bc[d] < 0 || bc[d] > 2) throw std::invalid_argument("set_bc: bad PoissonBC value");
+        bc_[d] = bc[d];
+    }
+    apply_bc_codes();
+}
+
+void Multigrid::apply_bc_codes() {
+    for (auto& L : levels_) {
+        for (int d = 0; d < 6; ++d) L->g.bc[d] = bc_[d];
+        if (comm_ && comm_->nranks > 1 && L->g.Nz != L->NzGlobal) {
+            // slab interfaces: interior ranks always; end ranks only when z is periodic
+            const bool per = bc_[4] == CFDNN_PBC_PERIODIC && bc_[5] == CFDNN_PBC_PERIODIC;
+            if (comm_->rank > 0 || per) L->g.bc[4] = CFDNN_PBC_HALO;
+            if (comm_->rank < comm_->nranks - 1 || per) L->g.bc[5] = CFDNN_PBC_HALO;
+        }
+    }
+    invalidate_graph();
+}
+
+void Multigrid::invalidate_graph() {
+    if (graph_) { cudaGraphExecDestroy(graph_); graph_ = nullptr; }
+    graph_key_[0] = graph_key_[1] = graph_key_[2] = -1;
+}
+
+bool Multigrid::has_nullspace() const {   // :3393-3402
+    for (int d = 0; d < 6; ++d) if (bc_[d] == CFDNN_PBC_DIRICHLET) return false;
+    return true;
+}
+
+void Multigrid::halo(int level, double* field) {
+    if (!comm_ || comm_->nranks <= 1) return;
+    Level& L = *levels_[level];
+    if (L.g.Nz == L.NzGlobal) return;   // agglomerated level: whole domain on every rank
+    comm_->exchange_planes(field, (size_t)L.g.plane, L.g.Nz, 1,
+                           L.g.bc[4] == CFDNN_PBC_HALO, L.g.bc[5] == CFDNN_PBC_HALO, st_);
+}
+
+// ---------------------------------------------------------------- kernels' launchers
+void Multigrid::sweep(int level, const double* uin, double* uout, double omega) {
+    Level& L = *levels_[level];
+    dim3 g = grid2(L.g.Nx, L.g.Ny, (L.g.Nz + KZ - 1) / KZ, kBlk);
+    CFDNN_LAUNCH((k_sweep<KZ, false>), g, kBlk, 0, st_, L.g, uin, L.f.p, uout, omega, 1.0 - omega);
+}
+
+// smooth_chebyshev (:825-1001): degree sweeps with Chebyshev weights; BCs are implicit.
+void Multigrid::smooth_chebyshev(int level, int degree) {
+    Level& L = *levels_[level];
+    const double lambda_max = L.lambda_max;
+    const double lambda_min = 0.1 * lambda_max;
+    const double d = (lambda_max + lambda_min) / 2.0;
+    const double c = (lambda_max - lambda_min) / 2.0;
+    double* a = L.u.p;
+    double* b = L.tmp.p;
+    for (int k = 0; k < degree; ++k) {
+        const double theta = M_PI * (2.0 * k + 1.0) / (2.0 * degree);
+        double omega = 1.0 / (d - c * std::cos(theta));
+        omega = std::min(omega, 2.0);
+        halo(level, a);
+        sweep(level, a, b, omega);
+        std::swap(a, b);
+    }
+    if (a != L.u.p) std::swap(L.u.p, L.tmp.p);   // result lives in L.u
+}
+
+void Multigrid::smooth_jacobi(int level, int iters, double omega) {
+    Level& L = *levels_[level];
+    const int n = L.g.Nx * L.g.Ny * L.g.Nz;
+    const bool local = !(comm_ && comm_->nranks > 1 && L.g.Nz != L.NzGlobal);
+    if (local && n <= 4096) {
+        const size_t smem = 2 * (size_t)n * sizeof(double);
+        const int threads = std::min(1024, (n + 31) / 32 * 32);
+        if (n <= 1024) {
+            CFDNN_LAUNCH((k_coarse_jacobi<1>), 1, threads, smem, st_, L.g, L.u.p, L.f.p, iters, omega, 1.0 - omega);
+        } else {
+            CFDNN_LAUNCH((k_coarse_jacobi<4>), 1, 1024, smem, st_, L.g, L.u.p, L.f.p, iters, omega, 1.0 - omega);
+        }
+        return;
+    }
+    double* a = L.u.p;
+    double* b = L.tmp.p;
+    for (int it = 0; it < iters; ++it) {
+        halo(level, a);
+        sweep(level, a, b, omega);
+        std::swap(a, b);
+    }
+    if (a != L.u.p) std::swap(L.u.p, L.tmp.p);
+}
+
+void Multigrid::residual(int level) {
+    Level& L = *levels_[level];
+    halo(level, L.u.p);
+    dim3 g = grid2(L.g.Nx, L.g.Ny, (L.g.Nz + KZ - 1) / KZ, kBlk);
+    CFDNN_LAUNCH((k_residual<KZ, false, false>), g, kBlk, 0, st_, L.g, L.u.p, L.f.p, L.r.p, nullptr, nullptr);
+}
+
+void Multigrid::residual_norms(int level, double* d_max, double* d_sumsq) {
+    Level& L = *levels_[level];
+    halo(level, L.u.p);
+    dim3 g = grid2(L.g.Nx, L.g.Ny, (L.g.Nz + KZ - 1) / KZ, kBlk);
+    const int nb = g.x * g.y * g.z;
+    double* pm = partial_.p;
+    double* ps = partial_.p + nb;
+    CFDNN_LAUNCH((k_residual<KZ, false, true>), g, kBlk, 0, st_, L.g, L.u.p, L.f.p, L.r.p, pm, ps);
+    CFDNN_LAUNCH(k_final_max, 1, 1024, 0, st_, pm, nb, d_max);
+    CFDNN_LAUNCH(k_final_sum, 1, 1024, 0, st_, ps, nb, d_sumsq, 0.0);
+    if (comm_ && comm_->nranks > 1) {
+        comm_->allreduce_max(d_max, 1, st_);
+        comm_->allreduce_sum(d_sumsq, 1, st_);
+    }
+}
+
+void Multigrid::mean_free(int level, double* field) {
+    Level& L = *levels_[level];
+    dim3 g = grid2(L.g.Nx, L.g.Ny, L.g.Nz, kBlk);
+    const int nb = g.x * g.y * g.z;
+    const bool dist = comm_ && comm_->nranks > 1 && L.g.Nz != L.NzGlobal;
+    const double count = (double)L.g.Nx * L.g.Ny * L.NzGlobal;
+    CFDNN_LAUNCH(k_sum_interior, g, kBlk, 0, st_, L.g, field, partial_.p);
+    CFDNN_LAUNCH(k_final_sum, 1, 1024, 0, st_, partial_.p, nb, scalars_.p + 8, dist ? 0.0 : count);
+    if (dist) {
+        comm_->allreduce_sum(scalars_.p + 8, 1, st_);
+        CFDNN_LAUNCH(k_final_sum, 1, 32, 0, st_, scalars_.p + 8, 1, scalars_.p + 8, count);
+    }
+    CFDNN_LAUNCH(k_sub_scalar, g, kBlk, 0, st_, L.g, field, scalars_.p + 9);
+}
+
+void Multigrid::restrict_to(int fine) {
+    Level& F = *levels_[fine];
+    Level& C = *levels_[fine + 1];
+    halo(fine, F.r.p);
+    const int nzc_local = F.g.Nz / 2;
+    dim3 g = grid2(C.g.Nx, C.g.Ny, nzc_local, kBlk);
+    const int nb = g.x * g.y * g.z;
+    int kc_off = 0;
+    const bool agglomerate = comm_ && comm_->nranks > 1 && F.g.Nz != F.NzGlobal && C.g.Nz == C.NzGlobal;
+    if (agglomerate) kc_off = comm_->rank * nzc_local;
+    const bool nullsp = has_nullspace();
+    CFDNN_LAUNCH(k_restrict, g, kBlk, 0, st_, F.g, C.g, F.r.p, C.f.p, kc_off,
+                 (nullsp && !agglomerate) ? partial_.p : nullptr);
+    if (agglomerate)
+        comm_->allgather_planes(C.f.p + C.g.plane, (size_t)C.g.plane * nzc_local, st_);
+    if (nullsp) {   // make_rhs_mean_free(level+1) :3274-3276
+        const bool dist = comm_ && comm_->nranks > 1 && C.g.Nz != C.NzGlobal;
+        if (agglomerate) {
+            mean_free(fine + 1, C.f.p);
+        } else {
+            const double count = (double)C.g.Nx * C.g.Ny * C.NzGlobal;
+            CFDNN_LAUNCH(k_final_sum, 1, 1024, 0, st_, partial_.p, nb, scalars_.p + 8, dist ? 0.0 : count);
+            if (dist) {
+                comm_->allreduce_sum(scalars_.p + 8, 1, st_);
+                CFDNN_LAUNCH(k_final_sum, 1, 32, 0, st_, scalars_.p + 8, 1, scalars_.p + 8, count);
+            }
+            dim3 gs = grid2(C.g.Nx, C.g.Ny, C.g.Nz, kBlk);
+            CFDNN_LAUNCH(k_sub_scalar, gs, kBlk, 0, st_, C.g, C.f.p, scalars_.p + 9);
+        }
+    }
+}
+
+void Multigrid::prolong_from(int coarse) {
+    Level& C = *levels_[coarse];
+    Level& F = *levels_[coarse - 1];
+    int kc_off = 0;
+    const bool agglomerated = comm_ && comm_->nranks > 1 && F.g.Nz != F.NzGlobal && C.g.Nz == C.NzGlobal;
+    if (agglomerated) kc_off = comm_->rank * (F.g.Nz / 2);
+    else halo(coarse, C.u.p);
+    LevelGeom gc = C.g;
+    dim3 g = grid2(F.g.Nx, F.g.Ny, F.g.Nz, kBlk);
+    CFDNN_LAUNCH(k_prolong, g, kBlk, 0, st_, F.g, gc, C.u.p, F.u.p, kc_off);
+}
+
+// ---------------------------------------------------------------- V-cycle (:3121-3322)
+void Multigrid::vcycle(int level, int nu1, int nu2, int degree) {
+    const int nl = (int)levels_.size();
+    if (level == nl - 1) {
+        smooth_jacobi(level, has_nullspace() ? 100 : 50, 0.67);   // :3193-3195
+        return;
+    }
+    for (int p = 0; p < nu1; ++p) smooth_chebyshev(level, degree);
+    residual(level);
+    restrict_to(level);
+    Level& C = *levels_[level + 1];
+    CFDNN_CUDA(cudaMemsetAsync(C.u.p, 0, C.size * sizeof(double), st_));   // :3279-3304
+    vcycle(level + 1, nu1, nu2, degree);
+    prolong_from(level + 1);
+    for (int p = 0; p < nu2; ++p) smooth_chebyshev(level, degree);
+}
+
+void Multigrid::run_vcycle(int nu1, int nu2, int degree) {
+    const bool multi = comm_ && comm_->nranks > 1;
+    if (!use_graph_ || multi) { vcycle(0, nu1, nu2, degree); return; }
+    if (!graph_ || graph_key_[0] != nu1 || graph_key_[1] != nu2 || graph_key_[2] != degree) {
+        invalidate_graph();
+        // The smoothers ping-pong u<->tmp by swapping the Level's pointers; a graph replays fixed
+        // addresses, so capture requires every level to end a V-cycle with u where it began.
+        // 16 = (nu1+nu2)*degree sweeps at each level: verify by pointer identity after capture.
+        std::vector<double*> before;
+        for (auto& L : levels_) before.push_back(L->u.p);
+        cudaGraph_t gr = nullptr;
+        CFDNN_CUDA(cudaStreamBeginCapture(st_, cudaStreamCaptureModeThreadLocal));
+        const unsigned long long l0 = g_launches.load();
+        try {
+            vcycle(0, nu1, nu2, degree);
+        } catch (...) {
+            cudaStreamEndCapture(st_, &gr);
+            if (gr) cudaGraphDestroy(gr);
+            throw;
+        }
+        graph_launches_ = g_launches.load() - l0;
+        g_launches.store(l0);
+        CFDNN_CUDA(cudaStreamEndCapture(st_, &gr));
+        bool same = true;
+        for (size_t l = 0; l < levels_.size(); ++l) same = same && before[l] == levels_[l]->u.p;
+        if (!same) {
+            // odd sweep count at some level: restore pointers, run without a graph
+            for (size_t l = 0; l < levels_.size(); ++l)
+                if (before[l] != levels_[l]->u.p) std::swap(levels_[l]->u.p, levels_[l]->tmp.p);
+            cudaGraphDestroy(gr);
+            use_graph_ = false;
+            vcycle(0, nu1, nu2, degree);
+            return;
+        }
+        CFDNN_CUDA(cudaGraphInstantiate(&graph_, gr, 0));
+        cudaGraphDestroy(gr);
+        graph_key_[0] = nu1; graph_key_[1] = nu2; graph_key_[2] = degree;
+    }
+    CFDNN_CUDA(cudaGraphLaunch(graph_, st_));
+    g_launches.fetch_add(graph_launches_, std::memory_order_relaxed);
+}
+
+// ---------------------------------------------------------------- solve (:3550-3786)
+int Multigrid::solve_dev(const double* rhs, double* p, const cfdnn_poisson_cfg& cfg, cudaStream_t st) {
+    st_ = st;
+    Level& L0 = *levels_[0];
+    const int Ng = mesh_.Ng;
+    {
+        dim3 g = grid2(L0.g.Nx, L0.g.Ny, L0.g.Nz, kBlk);
+        CFDNN_LAUNCH(k_copy_in, g, kBlk, 0, st_, L0.g, Ng, rhs, p, L0.f.p, L0.u.p);
+    }
+    int cycles_used = 0;
+    stats = cfdnn_poisson_stats{};
+    const int degree = cfg.chebyshev_degree;
+    if (time_vcycles) CFDNN_CUDA(cudaEventRecord(ev0_, st_));
+
+    if (cfg.fixed_cycles > 0) {
+        const int nu1 = cfg.nu1 > 0 ? cfg.nu1 : 3;
+        const int nu2 = cfg.nu2 > 0 ? cfg.nu2 : 1;
+        for (int c = 0; c < cfg.fixed_cycles; ++c) run_vcycle(nu1, nu2, degree);
+        cycles_used = cfg.fixed_cycles;
+        stats.fixed_cycle_mode = 1;
+        stats.converged = 0;
+        stats.status = CFDNN_PSTAT_FIXED;
+        if (time_vcycles) CFDNN_CUDA(cudaEventRecord(ev1_, st_));
+    } else {
+        if (cfg.max_vcycles <= 0) throw std::invalid_argument("PoissonConfig.max_vcycles must be positive");
+        const int max_cycles = cfg.max_vcycles;
+        const bool accurate = max_cycles > 5;                                  // :3647-3650
+        const int nu1 = cfg.nu1 > 0 ? cfg.nu1 : (accurate ? 3 : 2);
+        const int nu2 = cfg.nu2 > 0 ? cfg.nu2 : 1;
+        const int check_interval = std::max(1, semi_ ? std::max(4, cfg.check_interval) : cfg.check_interval);
+
+        // ||b||_inf, ||b||_2 over the interior of f (:3660-3682) — residual kernel with u := 0 is
+        // not the same thing, so use dedicated reductions through the r scratch.
+        double* S = scalars_.p;
+        {
+            dim3 g = grid2(L0.g.Nx, L0.g.Ny, (L0.g.Nz + KZ - 1) / KZ, kBlk);
+            const int nb = g.x * g.y * g.z;
+            // r0 = f - L u  and its norms
+            residual_norms(0, S + 2, S + 3);
+            // b norms: reuse k_residual with u = zero array? cheaper: norm kernel on f
+            CFDNN_LAUNCH(k_norms_interior, g, kBlk, 0, st_, L0.g, L0.f.p, KZ, partial_.p, partial_.p + nb);
+            CFDNN_LAUNCH(k_final_max, 1, 1024, 0, st_, partial_.p, nb, S + 0);
+            CFDNN_LAUNCH(k_final_sum, 1, 1024, 0, st_, partial_.p + nb, nb, S + 1, 0.0);
+            if (comm_ && comm_->nranks > 1) {
+                comm_->allreduce_max(S + 0, 1, st_);
+                comm_->allreduce_sum(S + 1, 1, st_);
+            }
+        }
+        CFDNN_CUDA(cudaMemcpyAsync(h_scalars_, S, 4 * sizeof(double), cudaMemcpyDeviceToHost, st_));
+        CFDNN_CUDA(cudaStreamSynchronize(st_));
+        stats.b_inf = h_scalars_[0];
+        stats.b_l2 = std::sqrt(h_scalars_[1]);
+        stats.r0 = h_scalars_[2];
+        stats.r0_l2 = std::sqrt(h_scalars_[3]);
+        stats.residual = stats.r0;
+        stats.residual_l2 = stats.r0_l2;
+        stats.converged = 0;
+        stats.fixed_cycle_mode = 0;
+
+        for (int cycle = 0; cycle < max_cycles; ++cycle) {
+            run_vcycle(nu1, nu2, degree);
+            cycles_used = cycle + 1;
+            if ((cycle % check_interval) == (check_interval - 1) || cycle == max_cycles - 1) {
+                residual_norms(0, S + 2, S + 3);
+                CFDNN_CUDA(cudaMemcpyAsync(h_scalars_ + 2, S + 2, 2 * sizeof(double), cudaMemcpyDeviceToHost, st_));
+                CFDNN_CUDA(cudaStreamSynchronize(st_));
+                stats.residual = h_scalars_[2];
+                stats.residual_l2 = std::sqrt(h_scalars_[3]);
+                const double r_norm = cfg.use_l2_norm ? stats.residual_l2 : stats.residual;
+                const double b_norm = cfg.use_l2_norm ? stats.b_l2 : stats.b_inf;
+                const double r0_norm = cfg.use_l2_norm ? stats.r0_l2 : stats.r0;
+                bool conv = false;                                                  // :3728-3747
+                if (cfg.tol_abs > 0.0 && r_norm <= cfg.tol_abs) conv = true;
+                if (cfg.tol_rhs > 0.0 && r_norm <= cfg.tol_rhs * (b_norm + 1e-30)) conv = true;
+                if (cfg.tol_rel > 0.0 && r_norm <= cfg.tol_rel * (r0_norm + 1e-30)) conv = true;
+                if (cfg.tol > 0.0 && r_norm <= cfg.tol) conv = true;
+                if (conv && cfg.use_l2_norm && cfg.linf_safety_factor > 0.0 && cfg.tol_rhs > 0.0) {
+                    const double linf_ratio = stats.residual / (stats.b_inf + 1e-30);
+                    if (linf_ratio > cfg.tol_rhs * cfg.linf_safety_factor) conv = false;
+                }
+                if (conv) { stats.converged = 1; break; }
+            }
+        }
+        stats.status = stats.converged ? CFDNN_PSTAT_CONVERGED : CFDNN_PSTAT_HIT_MAX;
+        if (time_vcycles) CFDNN_CUDA(cudaEventRecord(ev1_, st_));
+    }
+    stats.cycles = cycles_used;
+
+    if (has_nullspace()) mean_free(0, L0.u.p);   // fix_nullspace(0) :3404-3409
+    halo(0, L0.u.p);
+    {
+        dim3 g = grid2(L0.g.Nx + 2 * Ng, L0.g.Ny + 2 * Ng, L0.g.Nz + 2 * Ng, kBlk);
+        CFDNN_LAUNCH(k_copy_out, g, kBlk, 0, st_, L0.g, Ng, L0.u.p, p);
+    }
+    vcycle_count = cycles_used;
+    timing_pending_ = time_vcycles;
+    return cycles_used;
+}
+
+void Multigrid::collect_timing() {
+    if (!timing_pending_) return;
+    timing_pending_ = false;
+    float ms = 0.f;
+    if (cudaEventSynchronize(ev1_) == cudaSuccess && cudaEventElapsedTime(&ms, ev0_, ev1_) == cudaSuccess) {
+        vcycle_ms_total = ms;
+        acc_vcycle_ms += ms;
+        acc_vcycles += vcycle_count;
+    }
+}
+
+int Multigrid::solve_host(const double* rhs, double* p, const cfdnn_poisson_cfg& cfg) {
+    const size_t n = (size_t)(mesh_.Nx + 2 * mesh_.Ng) * (mesh_.Ny + 2 * mesh_.Ng) * (mesh_.Nz + 2 * mesh_.Ng);
+    if (h_rhs_.n != n) { h_rhs_.alloc(n); h_p_.alloc(n); }
+    cudaStream_t st = own_stream();
+    CFDNN_CUDA(cudaMemcpyAsync(h_rhs_.p, rhs, n * sizeof(double), cudaMemcpyHostToDevice, st));
+    CFDNN_CUDA(cudaMemcpyAsync(h_p_.p, p, n * sizeof(double), cudaMemcpyHostToDevice, st));
+    const int cyc = solve_dev(h_rhs_.p, h_p_.p, cfg, st);
+    CFDNN_CUDA(cudaMemcpyAsync(p, h_p_.p, n * sizeof(double), cudaMemcpyDeviceToHost, st));
+    CFDNN_CUDA(cudaStreamSynchronize(st));
+    check_launch("mg solve");
+    collect_timing();
+    return cyc;
+}
+
+cudaStream_t Multigrid::own_stream() {
+    if (!own_st_) CFDNN_CUDA(cudaStreamCreateWithFlags(&own_st_, cudaStreamNonBlocking));
+    return own_st_;
+}
+
+}  // namespace cfdnn

@@ -1,0 +1,109 @@
+// mg.cuh — geometric-multigrid pressure-Poisson solver, device-resident.
+//
+// Stands in for MultigridPoissonSolver (reference include/poisson_solver_multigrid.hpp:26-102,
+// src/poisson_solver_multigrid.cpp) — CPU-path numerics, not the reference's
+// mg_cuda_kernels path.
+//
+// HBM layout of one level array (u, f, r, tmp):
+//   * NO x/y ghost cells: ghost values are a pure function of interior values
+//     (apply_bc, :307-554), so every stencil resolves them on the fly from the BC type.
+//   * one halo plane on each z side (k = -1 and k = Nz) — used only when the z side is a
+//     slab interface (BC code CFDNN_PBC_HALO); physical z BCs are resolved on the fly too.
+//   * row pitch Px = Nx rounded up to 16 doubles (128 B) so rows start on a line boundary.
+//   index(i,j,k) = (k+1)*Px*Ny + j*Px + i
+#pragma once
+#include "common.cuh"
+#include <vector>
+#include <memory>
+
+namespace cfdnn {
+
+enum { CFDNN_PBC_HALO = 3 };  // z side is a slab interface: read the halo plane as is
+
+struct LevelGeom {            // by-value kernel argument
+    int Nx, Ny, Nz;           // interior size of the local slab
+    int Px;                   // row pitch
+    long long plane;          // Px * Ny
+    int bc[6];                // xlo,xhi,ylo,yhi,zlo,zhi
+    Div dx2, dy2, dz2, coeff; // dx^2 ..., coeff = 2/dx2 + 2/dy2 + 2/dz2
+    int nonuniform_y;         // 1: use aS/aN/aP[j + joff] (stretched y)
+    int joff;
+    const double *aS, *aN, *aP;
+    double inv_dx2_2, inv_dz2_2;   // 2.0/dx2, 2.0/dz2 (nonuniform diag)
+};
+
+struct Level {
+    LevelGeom g{};
+    double dx, dy, dz;
+    int NzGlobal;
+    size_t size = 0;          // (Nz+2)*plane
+    DevBuf<double> u, f, r, tmp;
+    double lambda_max = 2.2;
+    long long cells() const { return (long long)g.Nx * g.Ny * g.Nz; }
+};
+
+struct Comm;  // slab communicator (comm.cuh)
+
+class Multigrid {
+public:
+    explicit Multigrid(const cfdnn_mesh_desc& m);
+    ~Multigrid();
+    void set_bc(const int bc[6]);
+    int num_levels() const { return (int)levels_.size(); }
+
+    // rhs/p: device pointers, reference ghosted cell layout. Returns V-cycles used.
+    int solve_dev(const double* rhs, double* p, const cfdnn_poisson_cfg& cfg, cudaStream_t st);
+    int solve_host(const double* rhs, double* p, const cfdnn_poisson_cfg& cfg);
+
+    cfdnn_poisson_stats stats{};
+    double vcycle_ms_total = 0.0;   // device time of the V-cycles of the last solve
+    int vcycle_count = 0;
+    // accumulated over solves since reset (solver step timing)
+    double acc_vcycle_ms = 0.0;
+    int acc_vcycles = 0;
+    bool time_vcycles = true;
+
+    void set_comm(Comm* c) { comm_ = c; apply_bc_codes(); }
+    void collect_timing();          // read the V-cycle events of the last solve (syncs on them)
+    cudaStream_t own_stream();
+    const cfdnn_mesh_desc& mesh() const { return mesh_; }
+
+private:
+    cfdnn_mesh_desc mesh_;
+    std::vector<std::unique_ptr<Level>> levels_;
+    int bc_[6] = {2, 2, 1, 1, 2, 2};   // reference defaults (header :185-190)
+    bool semi_ = false, ystretched_ = false;
+    DevBuf<double> aS_, aN_, aP_;
+    DevBuf<double> partial_;        // per-block partials for reductions
+    DevBuf<double> scalars_;        // device scalars: [0]=sum/mean [1]=max [2]=sumsq ...
+    double* h_scalars_ = nullptr;   // pinned
+    cudaEvent_t ev0_ = nullptr, ev1_ = nullptr;
+    Comm* comm_ = nullptr;
+    cudaStream_t st_ = nullptr;
+
+    // CUDA graph of one V-cycle, keyed by (nu1, nu2, degree)
+    cudaGraphExec_t graph_ = nullptr;
+    int graph_key_[3] = {-1, -1, -1};
+    bool use_graph_ = true;
+    unsigned long long graph_launches_ = 0;
+    bool timing_pending_ = false;
+    DevBuf<double> h_rhs_, h_p_;    // device staging for solve_host
+    cudaStream_t own_st_ = nullptr;
+
+    void apply_bc_codes();
+    bool has_nullspace() const;
+    void vcycle(int level, int nu1, int nu2, int degree);
+    void run_vcycle(int nu1, int nu2, int degree);
+    void smooth_chebyshev(int level, int degree);
+    void smooth_jacobi(int level, int iters, double omega);
+    void sweep(int level, const double* uin, double* uout, double omega);
+    void residual(int level);
+    void residual_norms(int level, double* d_max, double* d_sumsq);
+    void restrict_to(int fine);
+    void prolong_from(int coarse);
+    void mean_free(int level, double* field);
+    void halo(int level, double* field);   // slab interface exchange (no-op single GPU)
+    void invalidate_graph();
+};
+
+}  // namespace cfdnn

@@ -1,0 +1,183 @@
+/* cfdnn_b200.h — C ABI of libcfdnn_b200.so
+ *
+ * B200-native (sm_100a) backend for the per-timestep fractional-step hot path of
+ * comp-physics/cfd-nn.  Plain pointers and sizes only; no torch / C++ types.
+ * Every entry point names the reference interface it stands in for
+ * (paths relative to the reference tree, commit c73310a).
+ *
+ * All `const double*` / `double*` field arguments are HOST pointers in the
+ * reference's own ghost-inclusive layouts (include/fields.hpp:118-136):
+ *   cell fields : (Nx+2Ng)(Ny+2Ng)(Nz+2Ng), i fastest
+ *   u faces     : row length Nx+1+2Ng ; v faces: Ny+1+2Ng rows ; w faces: Nz+1+2Ng planes
+ * unless the function name ends in `_dev`, in which case they are device pointers.
+ *
+ * Return value: 0 on success, non-zero on error; cfdnn_last_error() gives the text.
+ * The library has NO CPU fallback: every compute entry fails with CFDNN_ERR_NO_DEVICE
+ * when no CUDA device is usable.
+ */
+#ifndef CFDNN_B200_H
+#define CFDNN_B200_H
+
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CFDNN_OK 0
+#define CFDNN_ERR_INVALID 1    /* std::invalid_argument in the reference            */
+#define CFDNN_ERR_RUNTIME 2    /* std::runtime_error (NaN guard, unsupported BC...) */
+#define CFDNN_ERR_NO_DEVICE 3  /* no CUDA device / kernel image not loadable        */
+#define CFDNN_ERR_CUDA 4
+
+/* PoissonBC — include/poisson_solver.hpp:9-13 (same numeric values) */
+enum { CFDNN_PBC_DIRICHLET = 0, CFDNN_PBC_NEUMANN = 1, CFDNN_PBC_PERIODIC = 2 };
+/* VelocityBC::Type — include/solver.hpp (Periodic, NoSlip, Inflow, Outflow) */
+enum { CFDNN_VBC_NOSLIP = 0, CFDNN_VBC_PERIODIC = 1, CFDNN_VBC_INFLOW = 2, CFDNN_VBC_OUTFLOW = 3 };
+/* TimeIntegrator / ConvectiveScheme — include/config.hpp */
+enum { CFDNN_TI_EULER = 0, CFDNN_TI_RK2 = 1, CFDNN_TI_RK3 = 2 };
+enum { CFDNN_CONV_CENTRAL = 0, CFDNN_CONV_SKEW = 2 };  /* Upwind(1)/Upwind2(3): out of scope */
+/* closure kinds — TurbulenceModelType::{None,NNMLP,NNTBNN} */
+enum { CFDNN_TURB_NONE = 0, CFDNN_TURB_NN_MLP = 1, CFDNN_TURB_NN_TBNN = 2 };
+/* PoissonSolveStatus — include/solver.hpp:130-140 */
+enum { CFDNN_PSTAT_CONVERGED = 0, CFDNN_PSTAT_HIT_MAX = 1, CFDNN_PSTAT_FIXED = 2 };
+
+/* field ids for upload/download (RANSSolver accessors, include/solver.hpp:230-300) */
+enum {
+    CFDNN_F_U = 0, CFDNN_F_V = 1, CFDNN_F_W = 2,      /* velocity()            */
+    CFDNN_F_P = 3,                                      /* pressure()            */
+    CFDNN_F_PCORR = 4,                                  /* pressure_correction() */
+    CFDNN_F_DIV = 5,                                    /* div_velocity()        */
+    CFDNN_F_RHS = 6,                                    /* rhs_poisson()         */
+    CFDNN_F_NUT = 7,                                    /* nu_t()                */
+    CFDNN_F_K = 8, CFDNN_F_OMEGA = 9,                   /* k(), omega()          */
+    CFDNN_F_NUEFF = 10,
+    CFDNN_F_TAU_XX = 11, CFDNN_F_TAU_XY = 12, CFDNN_F_TAU_YY = 13,
+    CFDNN_F_COUNT = 14
+};
+
+/* Mesh — include/mesh.hpp:16-182 (only what the hot path reads).
+ * y-metric arrays have Ny+2Ng entries (dyv, yLap_*) / Ny+2Ng+1 (dyc, yf) and may be NULL
+ * when y_stretched == 0.  Nz == 1 means a 2-D mesh (reference Mesh::is2D()). */
+typedef struct cfdnn_mesh_desc {
+    int Nx, Ny, Nz, Ng;
+    double dx, dy, dz;
+    int y_stretched;
+    const double* dyv;
+    const double* dyc;
+    const double* yLap_aS;
+    const double* yLap_aN;
+    const double* yLap_aP;
+    const double* yc;       /* cell-centre y, Ny+2Ng                                   */
+    double y_lo, y_hi;      /* wall positions (Mesh::y_min/y_max) for wall distance      */
+    /* z-slab decomposition (replaces include/decomposition.hpp): this rank owns global
+     * planes [k_offset, k_offset+Nz) of Nz_global; single rank: k_offset=0, Nz_global=Nz */
+    int Nz_global, k_offset;
+} cfdnn_mesh_desc;
+
+/* PoissonConfig — include/poisson_solver.hpp:16-53 (same defaults via cfdnn_poisson_cfg_default) */
+typedef struct cfdnn_poisson_cfg {
+    double tol, tol_abs, tol_rhs, tol_rel;
+    int max_vcycles, check_interval, use_l2_norm;
+    double linf_safety_factor;
+    int fixed_cycles, nu1, nu2, chebyshev_degree;
+} cfdnn_poisson_cfg;
+
+/* MultigridPoissonSolver accessors residual()/residual_l2()/rhs_norm()/... —
+ * include/poisson_solver_multigrid.hpp:61-96 */
+typedef struct cfdnn_poisson_stats {
+    int cycles, converged, fixed_cycle_mode, status;
+    double residual, residual_l2, b_inf, b_l2, r0, r0_l2;
+} cfdnn_poisson_stats;
+
+/* Hot-path keys of Config — include/config.hpp:65-234 */
+typedef struct cfdnn_config {
+    double nu, dt;
+    int time_integrator, convective_scheme;
+    int adaptive_dt;
+    double CFL_max, CFL_xz, dt_safety;
+    int poisson_fixed_cycles, poisson_max_vcycles;
+    double poisson_tol_rhs;
+    int turb_guard_enabled, turb_guard_interval;
+    int turb_model;
+    double nu_t_max;
+} cfdnn_config;
+
+typedef struct cfdnn_solver cfdnn_solver;   /* stands in for RANSSolver              */
+typedef struct cfdnn_mg cfdnn_mg;           /* stands in for MultigridPoissonSolver  */
+typedef struct cfdnn_nn cfdnn_nn;           /* stands in for TurbulenceNNTBNN / NNMLP */
+
+const char* cfdnn_last_error(void);
+int cfdnn_version(void);
+/* number of CUDA kernels this library has launched in this process (bench.py: gpu_launches) */
+unsigned long long cfdnn_kernel_launches(void);
+int cfdnn_device_count(void);
+int cfdnn_set_device(int device);
+int cfdnn_device_synchronize(void);
+
+void cfdnn_poisson_cfg_default(cfdnn_poisson_cfg* cfg);
+void cfdnn_config_default(cfdnn_config* cfg);
+
+/* ---- MultigridPoissonSolver (include/poisson_solver_multigrid.hpp:26-102) ---- */
+int cfdnn_mg_create(const cfdnn_mesh_desc* mesh, cfdnn_mg** out);      /* ctor :29            */
+void cfdnn_mg_destroy(cfdnn_mg* mg);                                    /* dtor :32            */
+int cfdnn_mg_set_bc(cfdnn_mg* mg, const int bc[6]);                     /* set_bc :35-42       */
+int cfdnn_mg_num_levels(const cfdnn_mg* mg);
+/* solve(const ScalarField& rhs, ScalarField& p, cfg) :46 — host arrays, copies inside */
+int cfdnn_mg_solve(cfdnn_mg* mg, const double* rhs, double* p, const cfdnn_poisson_cfg* cfg,
+                   cfdnn_poisson_stats* stats);
+/* solve_device(double* rhs, double* p, cfg) :59 — device-resident twin */
+int cfdnn_mg_solve_dev(cfdnn_mg* mg, const double* rhs_dev, double* p_dev,
+                       const cfdnn_poisson_cfg* cfg, cfdnn_poisson_stats* stats);
+/* device timing of the last solve's V-cycles (CUDA events), for bench.py's roofline object */
+int cfdnn_mg_last_timing(const cfdnn_mg* mg, double* vcycle_ms_total, int* n_vcycles);
+
+/* ---- RANSSolver (include/solver.hpp:86-311) ---- */
+int cfdnn_solver_create(const cfdnn_mesh_desc* mesh, const cfdnn_config* cfg, cfdnn_solver** out); /* ctor :88 */
+void cfdnn_solver_destroy(cfdnn_solver* s);
+int cfdnn_solver_set_velocity_bc(cfdnn_solver* s, const int bc[6]);     /* set_velocity_bc :101 */
+int cfdnn_solver_set_body_force(cfdnn_solver* s, double fx, double fy, double fz); /* :104 */
+int cfdnn_solver_set_dt(cfdnn_solver* s, double dt);                    /* set_dt             */
+int cfdnn_solver_get_dt(const cfdnn_solver* s, double* dt);             /* current_dt         */
+int cfdnn_solver_upload(cfdnn_solver* s, int field, const double* host, size_t n);   /* sync_to_gpu   */
+int cfdnn_solver_download(cfdnn_solver* s, int field, double* host, size_t n);       /* sync_from_gpu */
+size_t cfdnn_solver_field_size(const cfdnn_solver* s, int field);
+int cfdnn_solver_step(cfdnn_solver* s, double* residual_out);           /* double step() :208 */
+/* run n steps without reading the residual back between them (app time loops) */
+int cfdnn_solver_run(cfdnn_solver* s, int nsteps, double* last_residual_out);
+int cfdnn_solver_compute_adaptive_dt(cfdnn_solver* s, double* dt_out);  /* compute_adaptive_dt :214 */
+int cfdnn_solver_poisson_stats(const cfdnn_solver* s, cfdnn_poisson_stats* out); /* poisson_stats() */
+/* V-cycles of every Poisson solve since the last call (oracle: POISSON_STATS lines) */
+int cfdnn_solver_cycle_log(cfdnn_solver* s, int* cycles, int cap, int* n_out);
+/* set_turbulence_model(unique_ptr<TurbulenceModel>) :98 — solver borrows the closure */
+int cfdnn_solver_set_turbulence_model(cfdnn_solver* s, cfdnn_nn* nn);
+/* device timing of the last step()/run(): total ms and ms spent inside V-cycles */
+int cfdnn_solver_last_timing(const cfdnn_solver* s, double* step_ms, double* vcycle_ms, int* n_vcycles);
+/* z-slab multi-GPU (replaces Decomposition + HaloExchange, src/decomposition.cpp, src/halo_exchange.cpp):
+ * nccl_unique_id is the 128-byte ncclUniqueId produced by rank 0 and broadcast by the caller */
+int cfdnn_comm_unique_id(void* id128);
+int cfdnn_solver_comm_init(cfdnn_solver* s, int rank, int nranks, const void* id128);
+
+/* ---- NN closures (include/turbulence_model.hpp:81-165, include/turbulence_nn_tbnn.hpp:35-56) ---- */
+/* weights: row-major (out,in) per layer as in layerN_W.txt (src/nn_core.cpp:501-611);
+ * act[l]: 0 linear, 1 tanh, 2 relu ; means/stds may be NULL (no input scaling) */
+int cfdnn_nn_create(int kind, int n_layers, const int* dims /* n_layers+1 */, const int* act,
+                    const double* const* W, const double* const* b,
+                    const double* means, const double* stds, cfdnn_nn** out);
+void cfdnn_nn_destroy(cfdnn_nn* nn);
+int cfdnn_nn_set_params(cfdnn_nn* nn, double nu, double delta, double u_ref, double k_min,
+                        double nu_t_max);
+/* TurbulenceModel::update(mesh, velocity, k, omega, nu_t, tau_ij, view) on host arrays of a
+ * 2-D mesh (reference semantics) or on every interior z-plane of a 3-D mesh.
+ * k/omega may be NULL (== all zero); tau_* may be NULL. */
+int cfdnn_nn_update(cfdnn_nn* nn, const cfdnn_mesh_desc* mesh, const double* u, const double* v,
+                    const double* k, const double* omega, double* nu_t,
+                    double* tau_xx, double* tau_xy, double* tau_yy);
+/* batched MLP forward (MLP::forward, src/nn_core.cpp:144-204): x[n][in] -> y[n][out] */
+int cfdnn_nn_forward(cfdnn_nn* nn, const double* x, double* y, size_t n);
+int cfdnn_nn_last_timing(const cfdnn_nn* nn, double* ms);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CFDNN_B200_H */
