@@ -1,0 +1,140 @@
+// comm.cu — NCCL-backed slab communicator (see comm.cuh).
+#include "comm.cuh"
+#include <dlfcn.h>
+#include <cstring>
+#include <mutex>
+
+namespace cfdnn {
+
+#ifndef CFDNN_DEVSIM
+namespace {
+// Minimal NCCL surface, bound at run time (ABI of nccl.h 2.x).
+typedef struct ncclComm* ncclComm_t;
+struct ncclUniqueId { char internal[128]; };
+enum { ncclSuccess = 0 };
+enum { ncclFloat64 = 8 };
+enum { ncclSum = 0, ncclProd = 1, ncclMax = 2, ncclMin = 3 };
+
+struct Nccl {
+    void* lib = nullptr;
+    int (*GetUniqueId)(ncclUniqueId*) = nullptr;
+    int (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
+    int (*CommDestroy)(ncclComm_t) = nullptr;
+    int (*GroupStart)() = nullptr;
+    int (*GroupEnd)() = nullptr;
+    int (*Send)(const void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+    int (*Recv)(void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+    int (*AllReduce)(const void*, void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+    int (*AllGather)(const void*, void*, size_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    const char* (*GetErrorString)(int) = nullptr;
+};
+Nccl& nccl() {
+    static Nccl n;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        const char* names[] = {"libnccl.so.2", "libnccl.so"};
+        for (const char* nm : names) {
+            n.lib = dlopen(nm, RTLD_NOW | RTLD_GLOBAL);
+            if (n.lib) break;
+        }
+        if (!n.lib) return;
+#define BIND(f) n.f = reinterpret_cast<decltype(n.f)>(dlsym(n.lib, "nccl" #f))
+        BIND(GetUniqueId); BIND(CommInitRank); BIND(CommDestroy); BIND(GroupStart); BIND(GroupEnd);
+        BIND(Send); BIND(Recv); BIND(AllReduce); BIND(AllGather); BIND(GetErrorString);
+#undef BIND
+    });
+    if (!n.lib || !n.CommInitRank || !n.Send || !n.AllReduce)
+        throw Error(CFDNN_ERR_RUNTIME, "libnccl.so.2 could not be loaded: multi-GPU slabs need NCCL");
+    return n;
+}
+#define NCCL_OK(call)                                                                          \
+    do {                                                                                       \
+        int r__ = (call);                                                                      \
+        if (r__ != ncclSuccess)                                                                \
+            throw Error(CFDNN_ERR_RUNTIME, std::string(#call) + ": " +                         \
+                        (nccl().GetErrorString ? nccl().GetErrorString(r__) : "nccl error")); \
+    } while (0)
+
+struct NcclComm final : Comm {
+    ncclComm_t comm = nullptr;
+    ~NcclComm() override { if (comm) nccl().CommDestroy(comm); }
+    void exchange_planes(double* f, size_t plane, int nz, int ng, bool lo, bool hi,
+                         cudaStream_t st) override {
+        if (!lo && !hi) return;
+        Nccl& n = nccl();
+        const int dn = (rank + nranks - 1) % nranks, up = (rank + 1) % nranks;
+        const size_t cnt = plane * (size_t)ng;
+        NCCL_OK(n.GroupStart());
+        if (lo) {
+            NCCL_OK(n.Send(f + cnt, cnt, ncclFloat64, dn, comm, st));                // first interior planes
+            NCCL_OK(n.Recv(f, cnt, ncclFloat64, dn, comm, st));                      // low ghosts
+        }
+        if (hi) {
+            NCCL_OK(n.Send(f + (size_t)nz * plane, cnt, ncclFloat64, up, comm, st)); // last interior planes
+            NCCL_OK(n.Recv(f + (size_t)(nz + ng) * plane, cnt, ncclFloat64, up, comm, st));
+        }
+        NCCL_OK(n.GroupEnd());
+    }
+    void allreduce(double* d, int cnt, int op, cudaStream_t st) {
+        NCCL_OK(nccl().AllReduce(d, d, (size_t)cnt, ncclFloat64, op, comm, st));
+    }
+    void allreduce_sum(double* d, int n, cudaStream_t st) override { allreduce(d, n, ncclSum, st); }
+    void allreduce_max(double* d, int n, cudaStream_t st) override { allreduce(d, n, ncclMax, st); }
+    void allreduce_min(double* d, int n, cudaStream_t st) override { allreduce(d, n, ncclMin, st); }
+    void allgather_planes(double* base, size_t count, cudaStream_t st) override {
+        NCCL_OK(nccl().AllGather(base + (size_t)rank * count, base, count, ncclFloat64, comm, st));
+    }
+};
+}  // namespace
+
+void nccl_unique_id(void* id128) {
+    ncclUniqueId id;
+    NCCL_OK(nccl().GetUniqueId(&id));
+    std::memcpy(id128, &id, sizeof(id));
+}
+
+Comm* make_nccl_comm(int rank, int nranks, const void* id128) {
+    if (nranks < 1 || rank < 0 || rank >= nranks) throw std::invalid_argument("comm_init: bad rank/nranks");
+    auto* c = new NcclComm();
+    c->rank = rank; c->nranks = nranks;
+    if (nranks > 1) {
+        ncclUniqueId id;
+        std::memcpy(&id, id128, sizeof(id));
+        int r = nccl().CommInitRank(&c->comm, nranks, id, rank);
+        if (r != ncclSuccess) { delete c; throw Error(CFDNN_ERR_RUNTIME, "ncclCommInitRank failed"); }
+    }
+    return c;
+}
+#else   // ---- CFDNN_DEVSIM: no NCCL in the CPU test double
+void nccl_unique_id(void* id128) { std::memset(id128, 0, 128); }
+Comm* make_nccl_comm(int, int, const void*) {
+    throw Error(CFDNN_ERR_RUNTIME, "devsim build has no NCCL transport");
+}
+#endif
+
+#ifdef CFDNN_DEVSIM
+// Host-callback transport: exists in the CPU test double only.
+namespace {
+struct CallbackComm final : Comm {
+    cfdnn_comm_callbacks_t cb;
+    void exchange_planes(double* f, size_t plane, int nz, int ng, bool lo, bool hi, cudaStream_t) override {
+        if (!lo && !hi) return;
+        const int dn = (rank + nranks - 1) % nranks, up = (rank + 1) % nranks;
+        const size_t cnt = plane * (size_t)ng;
+        cb.sendrecv(cb.ctx, f + cnt, lo ? dn : -1, f, f + (size_t)nz * plane, hi ? up : -1,
+                    f + (size_t)(nz + ng) * plane, cnt);
+    }
+    void allreduce_sum(double* d, int n, cudaStream_t) override { cb.allreduce(cb.ctx, d, n, 0); }
+    void allreduce_max(double* d, int n, cudaStream_t) override { cb.allreduce(cb.ctx, d, n, 1); }
+    void allreduce_min(double* d, int n, cudaStream_t) override { cb.allreduce(cb.ctx, d, n, 2); }
+    void allgather_planes(double* base, size_t count, cudaStream_t) override { cb.allgather(cb.ctx, base, count); }
+};
+}  // namespace
+Comm* make_callback_comm(int rank, int nranks, const cfdnn_comm_callbacks_t& cb) {
+    auto* c = new CallbackComm();
+    c->rank = rank; c->nranks = nranks; c->cb = cb;
+    return c;
+}
+#endif
+
+}  // namespace cfdnn

@@ -33,11 +33,29 @@ extern std::atomic<unsigned long long> g_launches;
     } while (0)
 
 // Count every kernel we launch (bench.py reports it as gpu_launches).
+// CFDNN_LAUNCH_COOP marks kernels whose threads cooperate (__syncthreads / warp shuffles); on
+// the GPU the two are the same launch, the distinction only matters to the host-side test
+// double in tests/devsim (which is never part of this library).
+#ifndef CFDNN_DEVSIM
 #define CFDNN_LAUNCH(kernel, grid, block, smem, stream, ...)                                 \
     do {                                                                                     \
         kernel<<<(grid), (block), (smem), (stream)>>>(__VA_ARGS__);                          \
         ::cfdnn::g_launches.fetch_add(1, std::memory_order_relaxed);                         \
     } while (0)
+#define CFDNN_LAUNCH_COOP CFDNN_LAUNCH
+#define CFDNN_DYN_SMEM(T, name) extern __shared__ T name[]
+#else
+#define CFDNN_LAUNCH(kernel, grid, block, smem, stream, ...)                                 \
+    do {                                                                                     \
+        ::devsim::launch_plain(dim3(grid), dim3(block), (smem), [&] { kernel(__VA_ARGS__); }); \
+        ::cfdnn::g_launches.fetch_add(1, std::memory_order_relaxed);                         \
+    } while (0)
+#define CFDNN_LAUNCH_COOP(kernel, grid, block, smem, stream, ...)                            \
+    do {                                                                                     \
+        ::devsim::launch_coop(dim3(grid), dim3(block), (smem), [&] { kernel(__VA_ARGS__); }); \
+        ::cfdnn::g_launches.fetch_add(1, std::memory_order_relaxed);                         \
+    } while (0)
+#endif
 
 inline void check_launch(const char* what) {
     cudaError_t e = cudaGetLastError();
@@ -93,7 +111,7 @@ struct DevBuf {
 struct Div {       // a divisor and its reciprocal, passed by value to kernels
     double d, r;
 };
-#ifdef __CUDACC__
+#if defined(__CUDACC__) || defined(CFDNN_DEVSIM)
 // Correctly rounded x/d from a precomputed rd = RN(1/d) (Markstein correction step).
 // The FP64 stencils of the reference are written with true divisions (e.g.
 // src/poisson_solver_multigrid.cpp:976-979); this reproduces them with 3 FMA-pipe

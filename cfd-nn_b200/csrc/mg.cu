@@ -65,6 +65,9 @@ Multigrid::Multigrid(const cfdnn_mesh_desc& m) : mesh_(m) {
     CFDNN_CUDA(cudaMallocHost(&h_scalars_, 16 * sizeof(double)));
     CFDNN_CUDA(cudaEventCreate(&ev0_));
     CFDNN_CUDA(cudaEventCreate(&ev1_));
+#ifdef CFDNN_DEVSIM
+    use_graph_ = false;   // the CPU test double does not model CUDA graphs
+#endif
     apply_bc_codes();
 }
 
@@ -149,9 +152,9 @@ void Multigrid::smooth_jacobi(int level, int iters, double omega) {
         const size_t smem = 2 * (size_t)n * sizeof(double);
         const int threads = std::min(1024, (n + 31) / 32 * 32);
         if (n <= 1024) {
-            CFDNN_LAUNCH((k_coarse_jacobi<1>), 1, threads, smem, st_, L.g, L.u.p, L.f.p, iters, omega, 1.0 - omega);
+            CFDNN_LAUNCH_COOP((k_coarse_jacobi<1>), 1, threads, smem, st_, L.g, L.u.p, L.f.p, iters, omega, 1.0 - omega);
         } else {
-            CFDNN_LAUNCH((k_coarse_jacobi<4>), 1, 1024, smem, st_, L.g, L.u.p, L.f.p, iters, omega, 1.0 - omega);
+            CFDNN_LAUNCH_COOP((k_coarse_jacobi<4>), 1, 1024, smem, st_, L.g, L.u.p, L.f.p, iters, omega, 1.0 - omega);
         }
         return;
     }
@@ -179,9 +182,9 @@ void Multigrid::residual_norms(int level, double* d_max, double* d_sumsq) {
     const int nb = g.x * g.y * g.z;
     double* pm = partial_.p;
     double* ps = partial_.p + nb;
-    CFDNN_LAUNCH((k_residual<KZ, false, true>), g, kBlk, 0, st_, L.g, L.u.p, L.f.p, L.r.p, pm, ps);
-    CFDNN_LAUNCH(k_final_max, 1, 1024, 0, st_, pm, nb, d_max);
-    CFDNN_LAUNCH(k_final_sum, 1, 1024, 0, st_, ps, nb, d_sumsq, 0.0);
+    CFDNN_LAUNCH_COOP((k_residual<KZ, false, true>), g, kBlk, 0, st_, L.g, L.u.p, L.f.p, L.r.p, pm, ps);
+    CFDNN_LAUNCH_COOP(k_final_max, 1, 1024, 0, st_, pm, nb, d_max);
+    CFDNN_LAUNCH_COOP(k_final_sum, 1, 1024, 0, st_, ps, nb, d_sumsq, 0.0);
     if (comm_ && comm_->nranks > 1) {
         comm_->allreduce_max(d_max, 1, st_);
         comm_->allreduce_sum(d_sumsq, 1, st_);
@@ -194,11 +197,11 @@ void Multigrid::mean_free(int level, double* field) {
     const int nb = g.x * g.y * g.z;
     const bool dist = comm_ && comm_->nranks > 1 && L.g.Nz != L.NzGlobal;
     const double count = (double)L.g.Nx * L.g.Ny * L.NzGlobal;
-    CFDNN_LAUNCH(k_sum_interior, g, kBlk, 0, st_, L.g, field, partial_.p);
-    CFDNN_LAUNCH(k_final_sum, 1, 1024, 0, st_, partial_.p, nb, scalars_.p + 8, dist ? 0.0 : count);
+    CFDNN_LAUNCH_COOP(k_sum_interior, g, kBlk, 0, st_, L.g, field, partial_.p);
+    CFDNN_LAUNCH_COOP(k_final_sum, 1, 1024, 0, st_, partial_.p, nb, scalars_.p + 8, dist ? 0.0 : count);
     if (dist) {
         comm_->allreduce_sum(scalars_.p + 8, 1, st_);
-        CFDNN_LAUNCH(k_final_sum, 1, 32, 0, st_, scalars_.p + 8, 1, scalars_.p + 8, count);
+        CFDNN_LAUNCH_COOP(k_final_sum, 1, 32, 0, st_, scalars_.p + 8, 1, scalars_.p + 8, count);
     }
     CFDNN_LAUNCH(k_sub_scalar, g, kBlk, 0, st_, L.g, field, scalars_.p + 9);
 }
@@ -214,7 +217,7 @@ void Multigrid::restrict_to(int fine) {
     const bool agglomerate = comm_ && comm_->nranks > 1 && F.g.Nz != F.NzGlobal && C.g.Nz == C.NzGlobal;
     if (agglomerate) kc_off = comm_->rank * nzc_local;
     const bool nullsp = has_nullspace();
-    CFDNN_LAUNCH(k_restrict, g, kBlk, 0, st_, F.g, C.g, F.r.p, C.f.p, kc_off,
+    CFDNN_LAUNCH_COOP(k_restrict, g, kBlk, 0, st_, F.g, C.g, F.r.p, C.f.p, kc_off,
                  (nullsp && !agglomerate) ? partial_.p : nullptr);
     if (agglomerate)
         comm_->allgather_planes(C.f.p + C.g.plane, (size_t)C.g.plane * nzc_local, st_);
@@ -224,10 +227,10 @@ void Multigrid::restrict_to(int fine) {
             mean_free(fine + 1, C.f.p);
         } else {
             const double count = (double)C.g.Nx * C.g.Ny * C.NzGlobal;
-            CFDNN_LAUNCH(k_final_sum, 1, 1024, 0, st_, partial_.p, nb, scalars_.p + 8, dist ? 0.0 : count);
+            CFDNN_LAUNCH_COOP(k_final_sum, 1, 1024, 0, st_, partial_.p, nb, scalars_.p + 8, dist ? 0.0 : count);
             if (dist) {
                 comm_->allreduce_sum(scalars_.p + 8, 1, st_);
-                CFDNN_LAUNCH(k_final_sum, 1, 32, 0, st_, scalars_.p + 8, 1, scalars_.p + 8, count);
+                CFDNN_LAUNCH_COOP(k_final_sum, 1, 32, 0, st_, scalars_.p + 8, 1, scalars_.p + 8, count);
             }
             dim3 gs = grid2(C.g.Nx, C.g.Ny, C.g.Nz, kBlk);
             CFDNN_LAUNCH(k_sub_scalar, gs, kBlk, 0, st_, C.g, C.f.p, scalars_.p + 9);
@@ -346,9 +349,9 @@ int Multigrid::solve_dev(const double* rhs, double* p, const cfdnn_poisson_cfg& 
             // r0 = f - L u  and its norms
             residual_norms(0, S + 2, S + 3);
             // b norms: reuse k_residual with u = zero array? cheaper: norm kernel on f
-            CFDNN_LAUNCH(k_norms_interior, g, kBlk, 0, st_, L0.g, L0.f.p, KZ, partial_.p, partial_.p + nb);
-            CFDNN_LAUNCH(k_final_max, 1, 1024, 0, st_, partial_.p, nb, S + 0);
-            CFDNN_LAUNCH(k_final_sum, 1, 1024, 0, st_, partial_.p + nb, nb, S + 1, 0.0);
+            CFDNN_LAUNCH_COOP(k_norms_interior, g, kBlk, 0, st_, L0.g, L0.f.p, KZ, partial_.p, partial_.p + nb);
+            CFDNN_LAUNCH_COOP(k_final_max, 1, 1024, 0, st_, partial_.p, nb, S + 0);
+            CFDNN_LAUNCH_COOP(k_final_sum, 1, 1024, 0, st_, partial_.p + nb, nb, S + 1, 0.0);
             if (comm_ && comm_->nranks > 1) {
                 comm_->allreduce_max(S + 0, 1, st_);
                 comm_->allreduce_sum(S + 1, 1, st_);

@@ -384,7 +384,7 @@ template <int CPT>
 __global__ void __launch_bounds__(1024)
 k_coarse_jacobi(LevelGeom g, double* __restrict__ u, const double* __restrict__ f, int iters,
                 double omega, double om1) {
-    extern __shared__ double smem[];
+    CFDNN_DYN_SMEM(double, smem);
     const int n = g.Nx * g.Ny * g.Nz;
     double* a = smem;
     double* b = smem + n;
