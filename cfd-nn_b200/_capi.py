@@ -50,7 +50,12 @@ class Config(C.Structure):
                 ("adaptive_dt", C.c_int),
                 ("CFL_max", C.c_double), ("CFL_xz", C.c_double), ("dt_safety", C.c_double),
                 ("poisson_fixed_cycles", C.c_int), ("poisson_max_vcycles", C.c_int),
-                ("poisson_tol_rhs", C.c_double),
+                ("poisson_tol_rhs", C.c_double), ("poisson_tol", C.c_double),
+                ("poisson_abs_tol_floor", C.c_double), ("poisson_tol_abs", C.c_double),
+                ("poisson_tol_rel", C.c_double),
+                ("poisson_check_interval", C.c_int), ("poisson_use_l2_norm", C.c_int),
+                ("poisson_linf_safety", C.c_double),
+                ("poisson_nu1", C.c_int), ("poisson_nu2", C.c_int), ("poisson_chebyshev_degree", C.c_int),
                 ("turb_guard_enabled", C.c_int), ("turb_guard_interval", C.c_int),
                 ("turb_model", C.c_int), ("nu_t_max", C.c_double)]
 
@@ -86,6 +91,7 @@ _SIGS = {
     "cfdnn_solver_upload": (C.c_int, [C.c_void_p, C.c_int, c_double_p, C.c_size_t]),
     "cfdnn_solver_download": (C.c_int, [C.c_void_p, C.c_int, c_double_p, C.c_size_t]),
     "cfdnn_solver_field_size": (C.c_size_t, [C.c_void_p, C.c_int]),
+    "cfdnn_solver_initialize": (C.c_int, [C.c_void_p]),
     "cfdnn_solver_step": (C.c_int, [C.c_void_p, c_double_p]),
     "cfdnn_solver_run": (C.c_int, [C.c_void_p, C.c_int, c_double_p]),
     "cfdnn_solver_compute_adaptive_dt": (C.c_int, [C.c_void_p, c_double_p]),

@@ -7,6 +7,8 @@
 #endif
 #include <mutex>
 #include <cstring>
+#include <memory>
+#include <algorithm>
 
 namespace cfdnn {
 std::atomic<unsigned long long> g_launches{0};
@@ -26,8 +28,16 @@ using namespace cfdnn;
 
 struct cfdnn_mg { Multigrid impl; explicit cfdnn_mg(const cfdnn_mesh_desc& m) : impl(m) {} };
 #ifndef CFDNN_MG_ONLY
-struct cfdnn_nn { NNClosure impl; };
-struct cfdnn_solver { Solver impl; cfdnn_solver(const cfdnn_mesh_desc& m, const cfdnn_config& c) : impl(m, c) {} };
+struct cfdnn_nn {
+    NNClosure impl;
+    cfdnn_nn(int kind, int nl, const int* dims, const int* act, const double* const* W, const double* const* b,
+             const double* means, const double* stds) : impl(kind, nl, dims, act, W, b, means, stds) {}
+};
+struct cfdnn_solver {
+    Solver impl;
+    std::unique_ptr<Comm> comm;
+    cfdnn_solver(const cfdnn_mesh_desc& m, const cfdnn_config& c) : impl(m, c) {}
+};
 #endif
 
 extern "C" {
@@ -53,7 +63,10 @@ void cfdnn_config_default(cfdnn_config* c) {             // include/config.hpp:6
     c->nu = 0.001; c->dt = 0.001;
     c->time_integrator = CFDNN_TI_EULER; c->convective_scheme = CFDNN_CONV_CENTRAL;
     c->adaptive_dt = 1; c->CFL_max = 0.5; c->CFL_xz = -1.0; c->dt_safety = 1.0;
-    c->poisson_fixed_cycles = 8; c->poisson_max_vcycles = 20; c->poisson_tol_rhs = 1e-3;
+    c->poisson_fixed_cycles = 8; c->poisson_max_vcycles = 20; c->poisson_tol_rhs = 1e-6;
+    c->poisson_tol = 1e-6; c->poisson_abs_tol_floor = 1e-8; c->poisson_tol_abs = 0.0; c->poisson_tol_rel = 1e-3;
+    c->poisson_check_interval = 3; c->poisson_use_l2_norm = 1; c->poisson_linf_safety = 10.0;
+    c->poisson_nu1 = 0; c->poisson_nu2 = 0; c->poisson_chebyshev_degree = 4;
     c->turb_guard_enabled = 1; c->turb_guard_interval = 5;
     c->turb_model = CFDNN_TURB_NONE; c->nu_t_max = 1.0;
 }
@@ -91,5 +104,102 @@ int cfdnn_mg_last_timing(const cfdnn_mg* mg, double* ms, int* n) {
     if (n) *n = mg->impl.vcycle_count;
     return CFDNN_OK;
 }
+
+
+#ifndef CFDNN_MG_ONLY
+// ---------------------------------------------------------------- solver
+int cfdnn_solver_create(const cfdnn_mesh_desc* mesh, const cfdnn_config* cfg, cfdnn_solver** out) {
+    return guarded([&] {
+        if (!mesh || !cfg || !out) throw std::invalid_argument("cfdnn_solver_create: null argument");
+        *out = new cfdnn_solver(*mesh, *cfg);
+    });
+}
+void cfdnn_solver_destroy(cfdnn_solver* s) { delete s; }
+int cfdnn_solver_set_velocity_bc(cfdnn_solver* s, const int bc[6]) { return guarded([&] { s->impl.set_velocity_bc(bc); }); }
+int cfdnn_solver_set_body_force(cfdnn_solver* s, double fx, double fy, double fz) {
+    return guarded([&] { s->impl.set_body_force(fx, fy, fz); });
+}
+int cfdnn_solver_set_dt(cfdnn_solver* s, double dt) { return guarded([&] { s->impl.set_dt(dt); }); }
+int cfdnn_solver_get_dt(const cfdnn_solver* s, double* dt) { *dt = s->impl.dt(); return CFDNN_OK; }
+int cfdnn_solver_upload(cfdnn_solver* s, int field, const double* host, size_t n) {
+    return guarded([&] { s->impl.upload(field, host, n); });
+}
+int cfdnn_solver_download(cfdnn_solver* s, int field, double* host, size_t n) {
+    return guarded([&] { s->impl.download(field, host, n); });
+}
+size_t cfdnn_solver_field_size(const cfdnn_solver* s, int field) {
+    size_t n = 0;
+    guarded([&] { n = s->impl.field_size(field); });
+    return n;
+}
+int cfdnn_solver_initialize(cfdnn_solver* s) { return guarded([&] { s->impl.initialize(); }); }
+int cfdnn_solver_step(cfdnn_solver* s, double* residual_out) {
+    return guarded([&] { double r = s->impl.step(); if (residual_out) *residual_out = r; });
+}
+int cfdnn_solver_run(cfdnn_solver* s, int nsteps, double* last_residual_out) {
+    return guarded([&] { s->impl.run(nsteps, last_residual_out); });
+}
+int cfdnn_solver_compute_adaptive_dt(cfdnn_solver* s, double* dt_out) {
+    return guarded([&] { *dt_out = s->impl.compute_adaptive_dt(); });
+}
+int cfdnn_solver_poisson_stats(const cfdnn_solver* s, cfdnn_poisson_stats* out) {
+    *out = s->impl.poisson_stats();
+    return CFDNN_OK;
+}
+int cfdnn_solver_cycle_log(cfdnn_solver* s, int* cycles, int cap, int* n_out) {
+    auto& log = s->impl.cycle_log;
+    const int n = (int)std::min<size_t>(log.size(), (size_t)std::max(cap, 0));
+    for (int i = 0; i < n; ++i) cycles[i] = log[log.size() - n + i];
+    if (n_out) *n_out = (int)log.size();
+    log.clear();
+    return CFDNN_OK;
+}
+int cfdnn_solver_set_turbulence_model(cfdnn_solver* s, cfdnn_nn* nn) {
+    return guarded([&] { s->impl.set_turbulence_model(nn ? &nn->impl : nullptr); });
+}
+int cfdnn_solver_last_timing(const cfdnn_solver* s, double* step_ms, double* vcycle_ms, int* n_vcycles) {
+    if (step_ms) *step_ms = s->impl.last_step_ms;
+    if (vcycle_ms) *vcycle_ms = s->impl.last_vcycle_ms;
+    if (n_vcycles) *n_vcycles = s->impl.last_vcycles;
+    return CFDNN_OK;
+}
+int cfdnn_comm_unique_id(void* id128) { return guarded([&] { nccl_unique_id(id128); }); }
+int cfdnn_solver_comm_init(cfdnn_solver* s, int rank, int nranks, const void* id128) {
+    return guarded([&] {
+        s->comm.reset(make_nccl_comm(rank, nranks, id128));
+        s->impl.comm_init(s->comm.get());
+    });
+}
+#ifdef CFDNN_DEVSIM
+// test double only: slab communicator over host callbacks (gloo in tests/)
+int cfdnn_devsim_solver_comm_init(cfdnn_solver* s, int rank, int nranks, const cfdnn_comm_callbacks_t* cb) {
+    return guarded([&] {
+        s->comm.reset(make_callback_comm(rank, nranks, *cb));
+        s->impl.comm_init(s->comm.get());
+    });
+}
+#endif
+
+// ---------------------------------------------------------------- NN closures
+int cfdnn_nn_create(int kind, int n_layers, const int* dims, const int* act, const double* const* W,
+                    const double* const* b, const double* means, const double* stds, cfdnn_nn** out) {
+    return guarded([&] {
+        if (!dims || !W || !b || !out) throw std::invalid_argument("cfdnn_nn_create: null argument");
+        *out = new cfdnn_nn(kind, n_layers, dims, act, W, b, means, stds);
+    });
+}
+void cfdnn_nn_destroy(cfdnn_nn* nn) { delete nn; }
+int cfdnn_nn_set_params(cfdnn_nn* nn, double nu, double delta, double u_ref, double k_min, double nu_t_max) {
+    return guarded([&] { nn->impl.set_params(nu, delta, u_ref, k_min, nu_t_max); });
+}
+int cfdnn_nn_update(cfdnn_nn* nn, const cfdnn_mesh_desc* mesh, const double* u, const double* v, const double* k,
+                    const double* omega, double* nu_t, double* tau_xx, double* tau_xy, double* tau_yy) {
+    return guarded([&] { nn->impl.update_host(*mesh, u, v, k, omega, nu_t, tau_xx, tau_xy, tau_yy); });
+}
+int cfdnn_nn_forward(cfdnn_nn* nn, const double* x, double* y, size_t n) {
+    return guarded([&] { nn->impl.forward_host(x, y, n); });
+}
+int cfdnn_nn_last_timing(const cfdnn_nn* nn, double* ms) { if (ms) *ms = nn->impl.last_ms; return CFDNN_OK; }
+#endif  // CFDNN_MG_ONLY
 
 }  // extern "C"

@@ -63,8 +63,8 @@ Multigrid::Multigrid(const cfdnn_mesh_desc& m) : mesh_(m) {
     partial_.alloc(2 * maxblocks + 16);
     scalars_.alloc(16);
     CFDNN_CUDA(cudaMallocHost(&h_scalars_, 16 * sizeof(double)));
-    CFDNN_CUDA(cudaEventCreate(&ev0_));
-    CFDNN_CUDA(cudaEventCreate(&ev1_));
+    // coarsest-level Jacobi keeps the whole level (two copies) in shared memory: up to 64 KB
+    CFDNN_CUDA(cudaFuncSetAttribute(k_coarse_jacobi<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 65536));
 #ifdef CFDNN_DEVSIM
     use_graph_ = false;   // the CPU test double does not model CUDA graphs
 #endif
@@ -74,8 +74,7 @@ Multigrid::Multigrid(const cfdnn_mesh_desc& m) : mesh_(m) {
 Multigrid::~Multigrid() {
     if (graph_) cudaGraphExecDestroy(graph_);
     if (h_scalars_) cudaFreeHost(h_scalars_);
-    if (ev0_) cudaEventDestroy(ev0_);
-    if (ev1_) cudaEventDestroy(ev1_);
+    for (auto& e : evpool_) { if (e.a) cudaEventDestroy(e.a); if (e.b) cudaEventDestroy(e.b); }
 }
 
 void Multigrid::set_bc(const int bc[6]) {
@@ -321,7 +320,17 @@ int Multigrid::solve_dev(const double* rhs, double* p, const cfdnn_poisson_cfg& 
     int cycles_used = 0;
     stats = cfdnn_poisson_stats{};
     const int degree = cfg.chebyshev_degree;
-    if (time_vcycles) CFDNN_CUDA(cudaEventRecord(ev0_, st_));
+    cur_ev_ = nullptr;
+    if (time_vcycles && evused_ < 4096) {
+        if (evused_ == evpool_.size()) {
+            EvPair e;
+            CFDNN_CUDA(cudaEventCreate(&e.a));
+            CFDNN_CUDA(cudaEventCreate(&e.b));
+            evpool_.push_back(e);
+        }
+        cur_ev_ = &evpool_[evused_++];
+        CFDNN_CUDA(cudaEventRecord(cur_ev_->a, st_));
+    }
 
     if (cfg.fixed_cycles > 0) {
         const int nu1 = cfg.nu1 > 0 ? cfg.nu1 : 3;
@@ -331,7 +340,7 @@ int Multigrid::solve_dev(const double* rhs, double* p, const cfdnn_poisson_cfg& 
         stats.fixed_cycle_mode = 1;
         stats.converged = 0;
         stats.status = CFDNN_PSTAT_FIXED;
-        if (time_vcycles) CFDNN_CUDA(cudaEventRecord(ev1_, st_));
+        if (cur_ev_) CFDNN_CUDA(cudaEventRecord(cur_ev_->b, st_));
     } else {
         if (cfg.max_vcycles <= 0) throw std::invalid_argument("PoissonConfig.max_vcycles must be positive");
         const int max_cycles = cfg.max_vcycles;
@@ -393,7 +402,7 @@ int Multigrid::solve_dev(const double* rhs, double* p, const cfdnn_poisson_cfg& 
             }
         }
         stats.status = stats.converged ? CFDNN_PSTAT_CONVERGED : CFDNN_PSTAT_HIT_MAX;
-        if (time_vcycles) CFDNN_CUDA(cudaEventRecord(ev1_, st_));
+        if (cur_ev_) CFDNN_CUDA(cudaEventRecord(cur_ev_->b, st_));
     }
     stats.cycles = cycles_used;
 
@@ -404,19 +413,23 @@ int Multigrid::solve_dev(const double* rhs, double* p, const cfdnn_poisson_cfg& 
         CFDNN_LAUNCH(k_copy_out, g, kBlk, 0, st_, L0.g, Ng, L0.u.p, p);
     }
     vcycle_count = cycles_used;
-    timing_pending_ = time_vcycles;
+    if (cur_ev_) cur_ev_->cycles = cycles_used;
     return cycles_used;
 }
 
 void Multigrid::collect_timing() {
-    if (!timing_pending_) return;
-    timing_pending_ = false;
-    float ms = 0.f;
-    if (cudaEventSynchronize(ev1_) == cudaSuccess && cudaEventElapsedTime(&ms, ev0_, ev1_) == cudaSuccess) {
-        vcycle_ms_total = ms;
-        acc_vcycle_ms += ms;
-        acc_vcycles += vcycle_count;
+    double last = 0.0;
+    for (size_t e = 0; e < evused_; ++e) {
+        float ms = 0.f;
+        if (cudaEventSynchronize(evpool_[e].b) == cudaSuccess &&
+            cudaEventElapsedTime(&ms, evpool_[e].a, evpool_[e].b) == cudaSuccess) {
+            acc_vcycle_ms += ms;
+            acc_vcycles += evpool_[e].cycles;
+            last = ms;
+        }
     }
+    if (evused_ > 0) vcycle_ms_total = last;
+    evused_ = 0;
 }
 
 int Multigrid::solve_host(const double* rhs, double* p, const cfdnn_poisson_cfg& cfg) {

@@ -64,7 +64,7 @@ public:
     bool time_vcycles = true;
 
     void set_comm(Comm* c) { comm_ = c; apply_bc_codes(); }
-    void collect_timing();          // read the V-cycle events of the last solve (syncs on them)
+    void collect_timing();          // read the V-cycle events of the solves since the last call (syncs)
     cudaStream_t own_stream();
     const cfdnn_mesh_desc& mesh() const { return mesh_; }
 
@@ -77,7 +77,10 @@ private:
     DevBuf<double> partial_;        // per-block partials for reductions
     DevBuf<double> scalars_;        // device scalars: [0]=sum/mean [1]=max [2]=sumsq ...
     double* h_scalars_ = nullptr;   // pinned
-    cudaEvent_t ev0_ = nullptr, ev1_ = nullptr;
+    struct EvPair { cudaEvent_t a = nullptr, b = nullptr; int cycles = 0; };
+    std::vector<EvPair> evpool_;    // one pair per solve since the last collect_timing()
+    size_t evused_ = 0;
+    EvPair* cur_ev_ = nullptr;
     Comm* comm_ = nullptr;
     cudaStream_t st_ = nullptr;
 
@@ -86,7 +89,6 @@ private:
     int graph_key_[3] = {-1, -1, -1};
     bool use_graph_ = true;
     unsigned long long graph_launches_ = 0;
-    bool timing_pending_ = false;
     DevBuf<double> h_rhs_, h_p_;    // device staging for solve_host
     cudaStream_t own_st_ = nullptr;
 

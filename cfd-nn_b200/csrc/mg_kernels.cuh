@@ -178,7 +178,7 @@ k_residual(LevelGeom g, const double* __restrict__ u, const double* __restrict__
 // 27-point full weighting centred on fine cell 2*ic (restrict_residual :2035-2062); residual
 // ghosts: periodic wrap else 0.  One thread per coarse cell; also emits per-block partial sums
 // of f_c for make_rhs_mean_free (:3479-3548).
-__global__ void __launch_bounds__(256)
+static __global__ void __launch_bounds__(256)
 k_restrict(LevelGeom gf, LevelGeom gc, const double* __restrict__ r, double* __restrict__ fc,
            int kc_off, double* __restrict__ part_sum) {
     __shared__ double sh[32];
@@ -233,7 +233,7 @@ k_restrict(LevelGeom gf, LevelGeom gc, const double* __restrict__ r, double* __r
 // ------------------------------------------------------------------ prolongation
 // u_f += trilinear(u_c) with the reference's one-sided owner-computes weights
 // (prolongate_correction :2230-2260): ic = i_f/2, weight 1 (even) or 1/2,1/2 toward ic+1 (odd).
-__global__ void __launch_bounds__(256)
+static __global__ void __launch_bounds__(256)
 k_prolong(LevelGeom gf, LevelGeom gc, const double* __restrict__ uc, double* __restrict__ uf,
           int kc_off) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -270,7 +270,7 @@ k_prolong(LevelGeom gf, LevelGeom gc, const double* __restrict__ uc, double* __r
 
 // ------------------------------------------------------------------ small helpers
 // out[0] = sum(part[0..n)) (fixed order); if count>0 also out[1] = out[0]/count (the mean).
-__global__ void k_final_sum(const double* __restrict__ part, int n, double* __restrict__ out,
+static __global__ void k_final_sum(const double* __restrict__ part, int n, double* __restrict__ out,
                             double count) {
     __shared__ double sh[32];
     double s = 0.0;
@@ -281,7 +281,7 @@ __global__ void k_final_sum(const double* __restrict__ part, int n, double* __re
         if (count > 0.0) out[1] = s / count;
     }
 }
-__global__ void k_final_max(const double* __restrict__ part, int n, double* __restrict__ out) {
+static __global__ void k_final_max(const double* __restrict__ part, int n, double* __restrict__ out) {
     __shared__ double sh[32];
     double s = 0.0;
     for (int t = threadIdx.x; t < n; t += blockDim.x) s = fmax(s, part[t]);
@@ -289,7 +289,7 @@ __global__ void k_final_max(const double* __restrict__ part, int n, double* __re
     if (threadIdx.x == 0) out[0] = s;
 }
 // interior sum of a level array -> per-block partials
-__global__ void __launch_bounds__(256)
+static __global__ void __launch_bounds__(256)
 k_sum_interior(LevelGeom g, const double* __restrict__ a, double* __restrict__ part) {
     __shared__ double sh[32];
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -306,7 +306,7 @@ k_sum_interior(LevelGeom g, const double* __restrict__ a, double* __restrict__ p
     if (w == 0) { s2 = lane < nw ? sh[lane] : 0.0; s2 = warp_sum(s2); if (lane == 0) part[bid] = s2; }
 }
 // a -= *mean on interior cells (subtract_mean / make_rhs_mean_free second loops)
-__global__ void __launch_bounds__(256)
+static __global__ void __launch_bounds__(256)
 k_sub_scalar(LevelGeom g, double* __restrict__ a, const double* __restrict__ mean) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     const int j = blockIdx.y * blockDim.y + threadIdx.y;
@@ -315,7 +315,7 @@ k_sub_scalar(LevelGeom g, double* __restrict__ a, const double* __restrict__ mea
 }
 
 // max|a| and sum a^2 over interior cells -> per-block partials (||b||_inf, ||b||_2 :3660-3682)
-__global__ void __launch_bounds__(256)
+static __global__ void __launch_bounds__(256)
 k_norms_interior(LevelGeom g, const double* __restrict__ a, int kz, double* __restrict__ part_max,
                  double* __restrict__ part_sq) {
     __shared__ double sh[32];
@@ -347,7 +347,7 @@ k_norms_interior(LevelGeom g, const double* __restrict__ a, int kz, double* __re
 
 // level-0 transfer between the reference's ghosted cell layout and the level layout.
 // in : f <- rhs interior, u <- p interior                           (solve :3558-3574)
-__global__ void __launch_bounds__(256)
+static __global__ void __launch_bounds__(256)
 k_copy_in(LevelGeom g, int Ng, const double* __restrict__ rhs, const double* __restrict__ p,
           double* __restrict__ f, double* __restrict__ u) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -361,7 +361,7 @@ k_copy_in(LevelGeom g, int Ng, const double* __restrict__ rhs, const double* __r
     u[o] = p[src];
 }
 // out: p <- u on ALL cells, ghosts from the BCs in x,y,z pass order    (solve :3769-3783)
-__global__ void __launch_bounds__(256)
+static __global__ void __launch_bounds__(256)
 k_copy_out(LevelGeom g, int Ng, const double* __restrict__ u, double* __restrict__ p) {
     const int I = blockIdx.x * blockDim.x + threadIdx.x;   // ghosted indices
     const int J = blockIdx.y * blockDim.y + threadIdx.y;

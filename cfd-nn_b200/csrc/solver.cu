@@ -1,0 +1,484 @@
+// solver.cu — host orchestration of the fractional-step path (see solver.cuh).
+#include "solver_kernels.cuh"
+#include "mg_kernels.cuh"
+#include "comm.cuh"
+#include "nn.cuh"
+#include <cmath>
+#include <algorithm>
+#include <cstring>
+
+namespace cfdnn {
+
+static const dim3 kB(64, 4, 1);
+static inline dim3 grid3(int nx, int ny, int nz) {
+    return dim3((nx + kB.x - 1) / kB.x, (ny + kB.y - 1) / kB.y, nz);
+}
+
+// ---------------------------------------------------------------- construction
+Solver::Solver(const cfdnn_mesh_desc& m, const cfdnn_config& c) : mesh_(m), cfg_(c) {
+    require_device();
+    if (m.Nx < 1 || m.Ny < 1 || m.Nz < 1) throw std::invalid_argument("Solver: bad mesh size");
+    if (m.Ng != 1) throw std::invalid_argument("Solver: only Nghost == 1 (O2 schemes) is supported");
+    if (m.Nz == 1) throw std::invalid_argument("Solver: 2-D meshes (Nz == 1) are not built yet");
+    if (c.convective_scheme != CFDNN_CONV_CENTRAL && c.convective_scheme != CFDNN_CONV_SKEW)
+        throw std::invalid_argument("Solver: convective_scheme must be central or skew");
+    if (c.time_integrator < CFDNN_TI_EULER || c.time_integrator > CFDNN_TI_RK3)
+        throw std::invalid_argument("Solver: bad time_integrator");
+    is2d_ = false;
+    const int Ng = m.Ng, Nx = m.Nx, Ny = m.Ny, Nz = m.Nz;
+    g_.Nx = Nx; g_.Ny = Ny; g_.Nz = Nz; g_.Ng = Ng;
+    g_.us = Nx + 1 + 2 * Ng; g_.vs = Nx + 2 * Ng; g_.ws = Nx + 2 * Ng; g_.cs = Nx + 2 * Ng;
+    g_.up = (long long)g_.us * (Ny + 2 * Ng);
+    g_.vp = (long long)g_.vs * (Ny + 1 + 2 * Ng);
+    g_.wp = (long long)g_.ws * (Ny + 2 * Ng);
+    g_.cp = (long long)g_.cs * (Ny + 2 * Ng);
+    su_ = (size_t)g_.up * (Nz + 2 * Ng);
+    sv_ = (size_t)g_.vp * (Nz + 2 * Ng);
+    sw_ = (size_t)g_.wp * (Nz + 1 + 2 * Ng);
+    sc_ = (size_t)g_.cp * (Nz + 2 * Ng);
+    g_.dx = make_div_host(m.dx); g_.dy = make_div_host(m.dy); g_.dz = make_div_host(m.dz);
+    g_.dx_2 = make_div_host(2.0 * m.dx); g_.dy_2 = make_div_host(2.0 * m.dy); g_.dz_2 = make_div_host(2.0 * m.dz);
+    g_.dx2 = make_div_host(m.dx * m.dx); g_.dy2 = make_div_host(m.dy * m.dy); g_.dz2 = make_div_host(m.dz * m.dz);
+    g_.y_stretched = m.y_stretched;
+    dy_min_ = m.dy;
+    if (m.y_stretched) {
+        if (!m.dyv || !m.dyc) throw std::invalid_argument("Solver: stretched mesh needs dyv/dyc");
+        const int nv = Ny + 2 * Ng, nc = Ny + 2 * Ng + 1;
+        h_dyv_.assign(m.dyv, m.dyv + nv);
+        std::vector<double> r(nv), rc(nc);
+        for (int j = 0; j < nv; ++j) r[j] = 1.0 / m.dyv[j];
+        for (int j = 0; j < nc; ++j) rc[j] = 1.0 / m.dyc[j];
+        dyv_.alloc(nv); rdyv_.alloc(nv); dyc_.alloc(nc); rdyc_.alloc(nc);
+        CFDNN_CUDA(cudaMemcpy(dyv_.p, m.dyv, nv * sizeof(double), cudaMemcpyHostToDevice));
+        CFDNN_CUDA(cudaMemcpy(rdyv_.p, r.data(), nv * sizeof(double), cudaMemcpyHostToDevice));
+        CFDNN_CUDA(cudaMemcpy(dyc_.p, m.dyc, nc * sizeof(double), cudaMemcpyHostToDevice));
+        CFDNN_CUDA(cudaMemcpy(rdyc_.p, rc.data(), nc * sizeof(double), cudaMemcpyHostToDevice));
+        g_.dyv = dyv_.p; g_.rdyv = rdyv_.p; g_.dyc = dyc_.p; g_.rdyc = rdyc_.p;
+        dy_min_ = *std::min_element(h_dyv_.begin(), h_dyv_.end());   // src/solver.cpp:3672-3675
+    }
+    mesh_.dyv = mesh_.dyc = mesh_.yLap_aS = mesh_.yLap_aN = mesh_.yLap_aP = mesh_.yc = nullptr;  // host pointers not kept
+
+    vel_ = alloc_vel(); star_ = alloc_vel(); old_ = alloc_vel(); rk_ = alloc_vel();
+    conv_ = alloc_vel(); diff_ = alloc_vel();
+    p_ = alloc_cell(); pcorr_ = alloc_cell(); div_ = alloc_cell(); rhs_ = alloc_cell();
+    nut_ = alloc_cell(); nueff_ = alloc_cell(); k_ = alloc_cell(); omega_ = alloc_cell();
+    for (int t = 0; t < 3; ++t) tau_[t] = alloc_cell();
+
+    const dim3 gmax = grid3(Nx + 1, Ny + 1, Nz + 1);
+    npartial_ = (size_t)gmax.x * gmax.y * gmax.z;
+    partial_.alloc(5 * npartial_ + 16);
+    scalars_.alloc(32);
+    CFDNN_CUDA(cudaMallocHost(&h_scalars_, 32 * sizeof(double)));
+    CFDNN_CUDA(cudaStreamCreateWithFlags(&st_, cudaStreamNonBlocking));
+    CFDNN_CUDA(cudaEventCreate(&ev0_));
+    CFDNN_CUDA(cudaEventCreate(&ev1_));
+
+    mg_ = std::make_unique<Multigrid>(m);
+    dt_ = c.dt;
+    set_velocity_bc(vbc_);
+}
+
+Solver::~Solver() {
+    if (h_scalars_) cudaFreeHost(h_scalars_);
+    if (ev0_) cudaEventDestroy(ev0_);
+    if (ev1_) cudaEventDestroy(ev1_);
+    if (st_) cudaStreamDestroy(st_);
+}
+
+Vel Solver::alloc_vel() {
+    Vel v;
+    store_.emplace_back(); store_.back().alloc(su_); v.u = store_.back().p;
+    store_.emplace_back(); store_.back().alloc(sv_); v.v = store_.back().p;
+    store_.emplace_back(); store_.back().alloc(sw_); v.w = store_.back().p;
+    return v;
+}
+double* Solver::alloc_cell() {
+    store_.emplace_back(); store_.back().alloc(sc_);
+    return store_.back().p;
+}
+
+// set_velocity_bc (src/solver.cpp:650-697): validates periodic pairs and maps to Poisson BCs
+void Solver::set_velocity_bc(const int bc[6]) {
+    for (int d = 0; d < 6; ++d)
+        if (bc[d] < 0 || bc[d] > 3) throw std::invalid_argument("set_velocity_bc: bad VelocityBC type");
+    const char* axis[3] = {"x", "y", "z"};
+    for (int a = 0; a < 3; ++a)
+        if ((bc[2 * a] == CFDNN_VBC_PERIODIC) != (bc[2 * a + 1] == CFDNN_VBC_PERIODIC))
+            throw std::invalid_argument(std::string("Periodic BC in ") + axis[a] + " requires both " + axis[a] +
+                                        "_lo and " + axis[a] + "_hi to be Periodic");
+    for (int d = 0; d < 6; ++d) vbc_[d] = bc[d];
+    int pbc[6];
+    for (int d = 0; d < 6; ++d) pbc[d] = bc[d] == CFDNN_VBC_PERIODIC ? CFDNN_PBC_PERIODIC : CFDNN_PBC_NEUMANN;
+    mg_->set_bc(pbc);
+}
+
+void Solver::comm_init(Comm* c) {
+    comm_ = c;
+    mg_->set_comm(c);
+}
+
+// ---------------------------------------------------------------- field transfer
+double* Solver::field_ptr(int field, size_t* n) const {
+    switch (field) {
+        case CFDNN_F_U: *n = su_; return vel_.u;
+        case CFDNN_F_V: *n = sv_; return vel_.v;
+        case CFDNN_F_W: *n = sw_; return vel_.w;
+        case CFDNN_F_P: *n = sc_; return p_;
+        case CFDNN_F_PCORR: *n = sc_; return pcorr_;
+        case CFDNN_F_DIV: *n = sc_; return div_;
+        case CFDNN_F_RHS: *n = sc_; return rhs_;
+        case CFDNN_F_NUT: *n = sc_; return nut_;
+        case CFDNN_F_K: *n = sc_; return k_;
+        case CFDNN_F_OMEGA: *n = sc_; return omega_;
+        case CFDNN_F_NUEFF: *n = sc_; return nueff_;
+        case CFDNN_F_TAU_XX: *n = sc_; return tau_[0];
+        case CFDNN_F_TAU_XY: *n = sc_; return tau_[1];
+        case CFDNN_F_TAU_YY: *n = sc_; return tau_[2];
+    }
+    throw std::invalid_argument("unknown field id");
+}
+size_t Solver::field_size(int field) const { size_t n; field_ptr(field, &n); return n; }
+void Solver::upload(int field, const double* host, size_t n) {
+    size_t want; double* d = field_ptr(field, &want);
+    if (n != want) throw std::invalid_argument("upload: size mismatch for field " + std::to_string(field));
+    CFDNN_CUDA(cudaMemcpyAsync(d, host, n * sizeof(double), cudaMemcpyHostToDevice, st_));
+    CFDNN_CUDA(cudaStreamSynchronize(st_));
+}
+void Solver::download(int field, double* host, size_t n) {
+    size_t want; double* d = field_ptr(field, &want);
+    if (n != want) throw std::invalid_argument("download: size mismatch for field " + std::to_string(field));
+    CFDNN_CUDA(cudaMemcpyAsync(host, d, n * sizeof(double), cudaMemcpyDeviceToHost, st_));
+    CFDNN_CUDA(cudaStreamSynchronize(st_));
+    check_launch("download");
+}
+void Solver::initialize() {
+    apply_velocity_bc();
+    CFDNN_CUDA(cudaStreamSynchronize(st_));
+    check_launch("initialize");
+}
+
+// ---------------------------------------------------------------- operators
+void Solver::apply_velocity_bc() {
+    const int Nx = g_.Nx, Ny = g_.Ny, Nz = g_.Nz, Ng = g_.Ng;
+    const int xlo = vbc_[0], xhi = vbc_[1], ylo = vbc_[2], yhi = vbc_[3], zlo = vbc_[4], zhi = vbc_[5];
+    // src/solver_operators.cpp:70-81, 283-288
+    if (xlo != CFDNN_VBC_PERIODIC && xlo != CFDNN_VBC_NOSLIP && xlo != CFDNN_VBC_INFLOW)
+        throw Error(CFDNN_ERR_RUNTIME, "Unsupported velocity BC type for x_lo");
+    if (xhi != CFDNN_VBC_PERIODIC && xhi != CFDNN_VBC_NOSLIP && xhi != CFDNN_VBC_OUTFLOW)
+        throw Error(CFDNN_ERR_RUNTIME, "Unsupported velocity BC type for x_hi");
+    if (ylo != CFDNN_VBC_PERIODIC && ylo != CFDNN_VBC_NOSLIP)
+        throw Error(CFDNN_ERR_RUNTIME, "Unsupported velocity BC type for y_lo (only Periodic and NoSlip are implemented)");
+    if (yhi != CFDNN_VBC_PERIODIC && yhi != CFDNN_VBC_NOSLIP)
+        throw Error(CFDNN_ERR_RUNTIME, "Unsupported velocity BC type for y_hi (only Periodic and NoSlip are implemented)");
+    const bool z_local = !(comm_ && comm_->nranks > 1);
+    if (z_local) {
+        if (zlo != CFDNN_VBC_PERIODIC && zlo != CFDNN_VBC_NOSLIP)
+            throw Error(CFDNN_ERR_RUNTIME, "Unsupported velocity BC type for z_lo (only Periodic and NoSlip are implemented)");
+        if (zhi != CFDNN_VBC_PERIODIC && zhi != CFDNN_VBC_NOSLIP)
+            throw Error(CFDNN_ERR_RUNTIME, "Unsupported velocity BC type for z_hi (only Periodic and NoSlip are implemented)");
+    }
+    BcFlags bc{xlo, xhi, ylo, yhi, zlo, zhi};
+    const int Pz = Nz + 2 * Ng;   // all planes of u, v
+    auto pass = [&](int id, int na, int nb) {
+        dim3 gr((na + kB.x - 1) / kB.x, (nb + kB.y - 1) / kB.y, 1);
+        CFDNN_LAUNCH(k_velocity_bc, gr, kB, 0, st_, g_, vel_, bc, id, na, nb);
+    };
+    pass(BC_U_X, Ny + 2 * Ng, Pz);
+    pass(BC_U_Y, Nx + 1 + 2 * Ng, Pz);
+    pass(BC_V_X, Ny + 1 + 2 * Ng, Pz);
+    pass(BC_V_Y, Nx + 2 * Ng, Pz);
+    if (xlo == CFDNN_VBC_PERIODIC && xhi == CFDNN_VBC_PERIODIC) pass(BC_U_X2, Ny + 2 * Ng, Pz);
+    if (ylo == CFDNN_VBC_PERIODIC && yhi == CFDNN_VBC_PERIODIC) pass(BC_V_Y2, Nx + 2 * Ng, Pz);
+    if (xhi == CFDNN_VBC_OUTFLOW) pass(BC_OUTFLOW_UV, Ny + 1 + 2 * Ng, Pz);
+    if (xlo == CFDNN_VBC_INFLOW) pass(BC_INFLOW_UV, Ny + 1 + 2 * Ng, Pz);
+    if (z_local) {
+        pass(BC_U_Z, Nx + 1 + 2 * Ng, Ny + 2 * Ng);
+        pass(BC_V_Z, Nx + 2 * Ng, Ny + 1 + 2 * Ng);
+        pass(BC_W_Z, Nx + 2 * Ng, Ny + 2 * Ng);
+    }
+    const int Pw = Nz + 1 + 2 * Ng;
+    pass(BC_W_X, Ny + 2 * Ng, Pw);
+    if (xlo == CFDNN_VBC_INFLOW) pass(BC_W_X_INFLOW, Ny + 2 * Ng, Pw);
+    if (xhi == CFDNN_VBC_OUTFLOW) pass(BC_W_X_OUTFLOW, Ny + 2 * Ng, Pw);
+    pass(BC_W_Y, Nx + 2 * Ng, Pw);
+}
+
+void Solver::compute_convective_term() {
+    const dim3 gr = grid3(g_.Nx + 1, g_.Ny + 1, g_.Nz + 1);
+    if (cfg_.convective_scheme == CFDNN_CONV_SKEW)
+        CFDNN_LAUNCH((k_convective<true>), gr, kB, 0, st_, g_, vel_.u, vel_.v, vel_.w, conv_.u, conv_.v, conv_.w);
+    else
+        CFDNN_LAUNCH((k_convective<false>), gr, kB, 0, st_, g_, vel_.u, vel_.v, vel_.w, conv_.u, conv_.v, conv_.w);
+}
+void Solver::compute_diffusive_term() {
+    const dim3 gr = grid3(g_.Nx + 1, g_.Ny + 1, g_.Nz + 1);
+    CFDNN_LAUNCH(k_diffusive, gr, kB, 0, st_, g_, vel_.u, vel_.v, vel_.w, nueff_, diff_.u, diff_.v, diff_.w);
+}
+void Solver::advance(const Vel& in, const Vel& out, double dt, bool seam_average) {
+    const dim3 gr = grid3(g_.Nx + 1, g_.Ny + 1, g_.Nz + 1);
+    CFDNN_LAUNCH(k_advance, gr, kB, 0, st_, g_, in, out, conv_, diff_, dt, fx_, fy_, fz_);
+    const int px = vbc_[0] == CFDNN_VBC_PERIODIC && vbc_[1] == CFDNN_VBC_PERIODIC;
+    const int py = vbc_[2] == CFDNN_VBC_PERIODIC && vbc_[3] == CFDNN_VBC_PERIODIC;
+    const int pz = vbc_[4] == CFDNN_VBC_PERIODIC && vbc_[5] == CFDNN_VBC_PERIODIC;
+    if (px || py || pz) {
+        const int na = std::max(g_.Nx, g_.Ny), nb = std::max(g_.Ny, g_.Nz);
+        dim3 gs((na + kB.x - 1) / kB.x, (nb + kB.y - 1) / kB.y, 3);
+        if (seam_average) CFDNN_LAUNCH((k_seam<true>), gs, kB, 0, st_, g_, out, px, py, pz);
+        else CFDNN_LAUNCH((k_seam<false>), gs, kB, 0, st_, g_, out, px, py, pz);
+    }
+}
+void Solver::blend(const Vel& a, const Vel& b, const Vel& c, double a1, double a2) {
+    const dim3 gr = grid3(g_.Nx + 1, g_.Ny + 1, g_.Nz + 1);
+    CFDNN_LAUNCH(k_blend, gr, kB, 0, st_, g_, a, b, c, a1, a2);
+}
+void Solver::compute_divergence(const Vel& v) {
+    const dim3 gr = grid3(g_.Nx, g_.Ny, g_.Nz);
+    CFDNN_LAUNCH_COOP(k_divergence, gr, kB, 0, st_, g_, v, div_, partial_.p);
+}
+// mean divergence + rhs (src/solver_time.cpp:812-866; src/solver.cpp:1920-2078)
+void Solver::build_rhs(double dt) {
+    const dim3 gr = grid3(g_.Nx, g_.Ny, g_.Nz);
+    const int nb = gr.x * gr.y * gr.z;
+    const bool dist = comm_ && comm_->nranks > 1;
+    const int NzG = mesh_.Nz_global > 0 ? mesh_.Nz_global : g_.Nz;
+    const double count = (double)g_.Nx * g_.Ny * NzG;
+    CFDNN_LAUNCH_COOP(k_final_sum, 1, 1024, 0, st_, partial_.p, nb, scalars_.p + 0, dist ? 0.0 : count);
+    if (dist) {
+        comm_->allreduce_sum(scalars_.p + 0, 1, st_);
+        CFDNN_LAUNCH_COOP(k_final_sum, 1, 32, 0, st_, scalars_.p + 0, 1, scalars_.p + 0, count);
+    }
+    CFDNN_LAUNCH(k_build_rhs, gr, kB, 0, st_, g_, div_, scalars_.p + 1, 1.0 / dt, rhs_);
+}
+void Solver::correct_velocity() {
+    const dim3 gr = grid3(g_.Nx + 1, g_.Ny + 1, g_.Nz + 1);
+    CFDNN_LAUNCH(k_correct, gr, kB, 0, st_, g_, star_, vel_, pcorr_, p_, dt_);
+    const int px = vbc_[0] == CFDNN_VBC_PERIODIC && vbc_[1] == CFDNN_VBC_PERIODIC;
+    const int py = vbc_[2] == CFDNN_VBC_PERIODIC && vbc_[3] == CFDNN_VBC_PERIODIC;
+    const int pz = vbc_[4] == CFDNN_VBC_PERIODIC && vbc_[5] == CFDNN_VBC_PERIODIC;
+    if (px || py || pz) {
+        const int na = std::max(g_.Nx, g_.Ny), nb = std::max(g_.Ny, g_.Nz);
+        dim3 gs((na + kB.x - 1) / kB.x, (nb + kB.y - 1) / kB.y, 3);
+        CFDNN_LAUNCH((k_seam<true>), gs, kB, 0, st_, g_, vel_, px, py, pz);
+    }
+}
+
+int Solver::poisson_solve(const cfdnn_poisson_cfg& pc) {
+    const int cyc = mg_->solve_dev(rhs_, pcorr_, pc, st_);
+    cycle_log.push_back(cyc);
+    return cyc;
+}
+
+void Solver::halo_vel(const Vel&) {}
+void Solver::halo_cell(double*) {}
+
+// ---------------------------------------------------------------- integrators
+// euler_substep (src/solver_time.cpp:269-661): operators always read velocity_
+void Solver::euler_substep(const Vel& in, const Vel& out, double dt) {
+    compute_convective_term();
+    compute_diffusive_term();
+    advance(in, out, dt, /*seam_average=*/false);
+}
+
+// project_velocity (src/solver_time.cpp:736-1211); which == &vel_ means "no swap"
+void Solver::project_velocity(Vel* which, double dt) {
+    const bool need_swap = which != &vel_;
+    if (need_swap) std::swap(vel_, *which);
+    apply_velocity_bc();
+    compute_divergence(vel_);
+    build_rhs(dt);
+    cfdnn_poisson_cfg pc;
+    cfdnn_poisson_cfg_default(&pc);
+    pc.max_vcycles = cfg_.poisson_max_vcycles;     // :868-871 — everything else stays at defaults
+    pc.tol_rhs = cfg_.poisson_tol_rhs;
+    pc.fixed_cycles = cfg_.poisson_fixed_cycles;
+    poisson_solve(pc);
+    blend(vel_, star_, star_, 1.0, 0.0);           // copy velocity_ -> velocity_star_ (interior) :972-995
+    correct_velocity();
+    apply_velocity_bc();
+    if (need_swap) std::swap(vel_, *which);
+}
+
+void Solver::ssprk3_step(double dt) {              // src/solver_time.cpp:1303-1513
+    blend(vel_, rk_, rk_, 1.0, 0.0);               // u^n -> velocity_rk_
+    euler_substep(vel_, star_, dt);
+    project_velocity(&star_, dt);
+    euler_substep(star_, vel_, dt);
+    blend(rk_, vel_, star_, 0.75, 0.25);           // blend_to: star = 0.75 rk + 0.25 velocity_
+    project_velocity(&star_, dt);
+    euler_substep(star_, vel_, dt);
+    blend(rk_, vel_, vel_, 1.0 / 3.0, 2.0 / 3.0);
+    project_velocity(&vel_, dt);
+    apply_velocity_bc();
+}
+void Solver::ssprk2_step(double dt) {              // :1213-1301
+    blend(vel_, rk_, rk_, 1.0, 0.0);
+    euler_substep(vel_, star_, dt);
+    project_velocity(&star_, dt);
+    euler_substep(star_, vel_, dt);
+    blend(rk_, vel_, vel_, 0.5, 0.5);
+    project_velocity(&vel_, dt);
+}
+
+// Euler path of step() (src/solver.cpp:1505-2507)
+void Solver::euler_step() {
+    compute_convective_term();
+    compute_diffusive_term();
+    advance(vel_, star_, dt_, /*seam_average=*/true);          // predictor :1558-1722
+    const bool px = vbc_[0] == CFDNN_VBC_PERIODIC && vbc_[1] == CFDNN_VBC_PERIODIC;
+    const bool py = vbc_[2] == CFDNN_VBC_PERIODIC && vbc_[3] == CFDNN_VBC_PERIODIC;
+    const bool pz = vbc_[4] == CFDNN_VBC_PERIODIC && vbc_[5] == CFDNN_VBC_PERIODIC;
+    if (!px || !py || !pz) {                                    // :1814-1845
+        std::swap(vel_, star_);
+        apply_velocity_bc();
+        std::swap(vel_, star_);
+    }
+    compute_divergence(star_);
+    build_rhs(dt_);
+    // iter_ is only advanced by solve_steady*, so a step()-driven run zeroes p' every step
+    // (:2006-2012, 2081-2090)
+    CFDNN_CUDA(cudaMemsetAsync(pcorr_, 0, sc_ * sizeof(double), st_));
+    cfdnn_poisson_cfg pc;                                       // :2179-2205
+    cfdnn_poisson_cfg_default(&pc);
+    pc.max_vcycles = cfg_.poisson_max_vcycles;
+    pc.tol_abs = cfg_.poisson_tol_abs;
+    pc.tol_rhs = cfg_.poisson_tol_rhs;
+    pc.tol_rel = cfg_.poisson_tol_rel;
+    pc.check_interval = cfg_.poisson_check_interval;
+    pc.use_l2_norm = cfg_.poisson_use_l2_norm;
+    pc.linf_safety_factor = cfg_.poisson_linf_safety;
+    pc.fixed_cycles = cfg_.poisson_fixed_cycles;
+    pc.nu1 = cfg_.poisson_nu1;
+    pc.nu2 = cfg_.poisson_nu2;
+    pc.chebyshev_degree = cfg_.poisson_chebyshev_degree;
+    if (pc.fixed_cycles <= 0) {
+        // effective legacy tolerance needs rms(rhs) (:2135-2176, 2207-2209)
+        const dim3 gr = grid3(g_.Nx, g_.Ny, g_.Nz);
+        const int nb = gr.x * gr.y * gr.z;
+        CFDNN_LAUNCH_COOP(k_sumsq_cells, gr, kB, 0, st_, g_, rhs_, partial_.p);
+        CFDNN_LAUNCH_COOP(k_final_sum, 1, 1024, 0, st_, partial_.p, nb, scalars_.p + 2, 0.0);
+        if (comm_ && comm_->nranks > 1) comm_->allreduce_sum(scalars_.p + 2, 1, st_);
+        CFDNN_CUDA(cudaMemcpyAsync(h_scalars_ + 2, scalars_.p + 2, sizeof(double), cudaMemcpyDeviceToHost, st_));
+        CFDNN_CUDA(cudaStreamSynchronize(st_));
+        const int NzG = mesh_.Nz_global > 0 ? mesh_.Nz_global : g_.Nz;
+        const double cnt = std::max((double)g_.Nx * g_.Ny * NzG, 1.0);
+        const double rhs_rms = std::sqrt(h_scalars_[2] / cnt);
+        pc.tol = std::max(cfg_.poisson_tol * std::max(rhs_rms, 1e-12), cfg_.poisson_abs_tol_floor);
+    }
+    poisson_solve(pc);
+    correct_velocity();                                         // u = u* - dt grad p' :2443
+    apply_velocity_bc();                                        // :2503-2507
+}
+
+void Solver::build_nu_eff() {
+    const dim3 gr = grid3(g_.Nx + 2 * g_.Ng, g_.Ny + 2 * g_.Ng, g_.Nz + 2 * g_.Ng);
+    CFDNN_LAUNCH(k_nu_eff, gr, kB, 0, st_, g_, cfg_.nu, nut_, nn_ ? 1 : 0, nueff_);
+}
+
+void Solver::update_turbulence() {
+    if (!nn_) return;
+    nn_->update_device(g_, mesh_, vel_, k_, omega_, nut_, tau_[0], tau_[1], tau_[2], st_);
+}
+
+void Solver::check_nan(int step) {                              // check_for_nan_inf :3195-3350
+    if (!cfg_.turb_guard_enabled) return;
+    if (cfg_.turb_guard_interval <= 0 || step % cfg_.turb_guard_interval != 0) return;
+    int* flag = reinterpret_cast<int*>(scalars_.p + 16);
+    CFDNN_CUDA(cudaMemsetAsync(flag, 0, sizeof(int), st_));
+    const int blocks = 148 * 8;
+    CFDNN_LAUNCH(k_nonfinite, blocks, 256, 0, st_, vel_.u, su_, flag);
+    CFDNN_LAUNCH(k_nonfinite, blocks, 256, 0, st_, vel_.v, sv_, flag);
+    CFDNN_LAUNCH(k_nonfinite, blocks, 256, 0, st_, vel_.w, sw_, flag);
+    CFDNN_LAUNCH(k_nonfinite, blocks, 256, 0, st_, p_, sc_, flag);
+    if (nn_) CFDNN_LAUNCH(k_nonfinite, blocks, 256, 0, st_, nut_, sc_, flag);
+    CFDNN_CUDA(cudaMemcpyAsync(h_scalars_ + 16, flag, sizeof(int), cudaMemcpyDeviceToHost, st_));
+    CFDNN_CUDA(cudaStreamSynchronize(st_));
+    if (*reinterpret_cast<int*>(h_scalars_ + 16) != 0)
+        throw Error(CFDNN_ERR_RUNTIME, "NaN/Inf detected in solution fields");
+}
+
+// step() (src/solver.cpp:1200-2786)
+void Solver::step_device(bool want_residual) {
+    blend(vel_, old_, old_, 1.0, 0.0);                          // velocity_old_ <- velocity_ :1210-1237
+    update_turbulence();                                        // :1284-1324
+    build_nu_eff();                                             // :1326-1410
+    if (cfg_.adaptive_dt && nn_) {                              // diffusion-CFL re-check :1416-1491
+        const dim3 gr = grid3(g_.Nx, g_.Ny, g_.Nz);
+        const int nb = gr.x * gr.y * gr.z;
+        CFDNN_LAUNCH_COOP(k_cfl_maxima, gr, kB, 0, st_, g_, vel_, nut_, cfg_.nu, 1, partial_.p, nb);
+        CFDNN_LAUNCH_COOP(k_final_max_rows, 1, 1024, 0, st_, partial_.p, nb, 5, scalars_.p + 4);
+        if (comm_ && comm_->nranks > 1) comm_->allreduce_max(scalars_.p + 4, 5, st_);
+        CFDNN_CUDA(cudaMemcpyAsync(h_scalars_ + 4, scalars_.p + 4, 5 * sizeof(double), cudaMemcpyDeviceToHost, st_));
+        CFDNN_CUDA(cudaStreamSynchronize(st_));
+        const double nu_eff_max = std::max(cfg_.nu, h_scalars_[8]);
+        const double dx_min = std::min({mesh_.dx, dy_min_, mesh_.dz});
+        const double dt_diff_limit = 0.25 * dx_min * dx_min / nu_eff_max;
+        if (dt_ > dt_diff_limit) dt_ = std::max(cfg_.dt_safety * dt_diff_limit, 1e-15);
+    }
+    if (cfg_.time_integrator == CFDNN_TI_RK3) ssprk3_step(dt_);
+    else if (cfg_.time_integrator == CFDNN_TI_RK2) ssprk2_step(dt_);
+    else euler_step();
+    if (want_residual) {                                        // :2659-2775
+        const dim3 gr = grid3(g_.Nx + 1, g_.Ny + 1, g_.Nz + 1);
+        const int nb = gr.x * gr.y * gr.z;
+        CFDNN_LAUNCH_COOP(k_max_change, gr, kB, 0, st_, g_, vel_, old_, partial_.p);
+        CFDNN_LAUNCH_COOP(k_final_max, 1, 1024, 0, st_, partial_.p, nb, scalars_.p + 3);
+        if (comm_ && comm_->nranks > 1) comm_->allreduce_max(scalars_.p + 3, 1, st_);
+        CFDNN_CUDA(cudaMemcpyAsync(h_scalars_ + 3, scalars_.p + 3, sizeof(double), cudaMemcpyDeviceToHost, st_));
+    }
+    check_nan(step_count_);
+    ++step_count_;
+    time_ += dt_;
+}
+
+double Solver::step() {
+    double r = 0.0;
+    run(1, &r);
+    return r;
+}
+
+void Solver::run(int nsteps, double* last_residual) {
+    if (nsteps <= 0) return;
+    mg_->acc_vcycle_ms = 0.0; mg_->acc_vcycles = 0;
+    CFDNN_CUDA(cudaEventRecord(ev0_, st_));
+    for (int s = 0; s < nsteps; ++s) step_device(s == nsteps - 1);
+    CFDNN_CUDA(cudaEventRecord(ev1_, st_));
+    CFDNN_CUDA(cudaStreamSynchronize(st_));
+    check_launch("step");
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, ev0_, ev1_);
+    last_step_ms = ms;
+    mg_->collect_timing();
+    last_vcycle_ms = mg_->acc_vcycle_ms;
+    last_vcycles = mg_->acc_vcycles;
+    if (last_residual) *last_residual = h_scalars_[3];
+}
+
+double Solver::compute_adaptive_dt() {                          // src/solver.cpp:3369-3729
+    const dim3 gr = grid3(g_.Nx, g_.Ny, g_.Nz);
+    const int nb = gr.x * gr.y * gr.z;
+    CFDNN_LAUNCH_COOP(k_cfl_maxima, gr, kB, 0, st_, g_, vel_, nut_, cfg_.nu, nn_ ? 1 : 0, partial_.p, nb);
+    CFDNN_LAUNCH_COOP(k_final_max_rows, 1, 1024, 0, st_, partial_.p, nb, 5, scalars_.p + 4);
+    CFDNN_CUDA(cudaMemcpyAsync(h_scalars_ + 4, scalars_.p + 4, 5 * sizeof(double), cudaMemcpyDeviceToHost, st_));
+    CFDNN_CUDA(cudaStreamSynchronize(st_));
+    check_launch("compute_adaptive_dt");
+    const double u_abs_max = std::max(1e-10, h_scalars_[4]);
+    const double w_abs_max = std::max(1e-10, h_scalars_[6]);
+    const double v_dy_ratio_max = std::max(1e-10, h_scalars_[7]);
+    const double nu_eff_max = std::max(cfg_.nu, h_scalars_[8]);
+    const double cfl_xz = cfg_.CFL_xz > 0 ? cfg_.CFL_xz : cfg_.CFL_max;
+    const double dt_cfl_x = cfl_xz * mesh_.dx / u_abs_max;
+    const double dt_cfl_y = cfg_.CFL_max / v_dy_ratio_max;
+    const double dt_cfl_z = cfl_xz * mesh_.dz / w_abs_max;
+    const double dx_min = std::min({mesh_.dx, dy_min_, mesh_.dz});
+    const double dt_diff = 0.25 * dx_min * dx_min / nu_eff_max;
+    double dt_new = cfg_.dt_safety * std::min({dt_cfl_x, dt_cfl_y, dt_cfl_z, dt_diff});
+    if (comm_ && comm_->nranks > 1) {
+        CFDNN_CUDA(cudaMemcpyAsync(scalars_.p + 10, &dt_new, sizeof(double), cudaMemcpyHostToDevice, st_));
+        comm_->allreduce_min(scalars_.p + 10, 1, st_);
+        CFDNN_CUDA(cudaMemcpyAsync(&dt_new, scalars_.p + 10, sizeof(double), cudaMemcpyDeviceToHost, st_));
+        CFDNN_CUDA(cudaStreamSynchronize(st_));
+    }
+    return dt_new;
+}
+
+}  // namespace cfdnn

@@ -1,0 +1,123 @@
+// solver.cuh — device-resident fractional-step solver on the staggered MAC grid.
+//
+// Stands in for RANSSolver (reference include/solver.hpp:86-311): step() with the Euler,
+// SSP-RK2 and SSP-RK3 integrators (src/solver.cpp:1200-2786, src/solver_time.cpp:269-1513),
+// velocity BCs, convection (central / skew), variable-viscosity diffusion, divergence,
+// Poisson RHS, multigrid projection, velocity correction, CFL / residual / NaN reductions.
+//
+// HBM layout: every solver field keeps the reference's ghost-inclusive layout
+// (include/fields.hpp:118-136), i fastest, so upload/download are flat copies and the
+// stale-ghost semantics of the RK stages are reproduced by construction:
+//   cell : (Nx+2Ng)(Ny+2Ng)(Nz+2Ng)         u : row length Nx+1+2Ng
+//   v    : Ny+1+2Ng rows                      w : Nz+1+2Ng planes
+// The multigrid levels use their own ghost-free layout (mg.cuh).
+#pragma once
+#include "common.cuh"
+#include "mg.cuh"
+#include <vector>
+#include <memory>
+
+namespace cfdnn {
+
+struct Comm;
+class NNClosure;
+
+struct Geom {                 // by-value kernel argument
+    int Nx, Ny, Nz, Ng;
+    int us, vs, ws, cs;       // row strides of u, v, w, cell arrays
+    long long up, vp, wp, cp; // plane strides
+    Div dx, dy, dz;           // spacings
+    Div dx_2, dy_2, dz_2;     // 2*dx ...   (central differences)
+    Div dx2, dy2, dz2;        // dx*dx ...  (diffusion)
+    int y_stretched;
+    const double* dyv;        // Ny+2Ng   (divergence, stretched y)
+    const double* dyc;        // Ny+2Ng+1 (pressure gradient, stretched y)
+    const double* rdyv;       // reciprocals of the above (for the corrected division)
+    const double* rdyc;
+};
+
+struct Vel { double *u = nullptr, *v = nullptr, *w = nullptr; };
+
+class Solver {
+public:
+    Solver(const cfdnn_mesh_desc& m, const cfdnn_config& c);
+    ~Solver();
+
+    void set_velocity_bc(const int bc[6]);
+    void set_body_force(double fx, double fy, double fz) { fx_ = fx; fy_ = fy; fz_ = fz; }
+    void set_dt(double dt) { dt_ = dt; }
+    double dt() const { return dt_; }
+    void set_turbulence_model(NNClosure* nn) { nn_ = nn; }
+    void comm_init(Comm* c);
+
+    size_t field_size(int field) const;
+    void upload(int field, const double* host, size_t n);
+    void download(int field, double* host, size_t n);
+    void initialize();                    // apply_velocity_bc on the uploaded velocity (:1060-1062)
+
+    double step();                        // double RANSSolver::step()
+    void run(int nsteps, double* last_residual);
+    double compute_adaptive_dt();
+
+    cfdnn_poisson_stats poisson_stats() const { return mg_->stats; }
+    std::vector<int> cycle_log;           // V-cycles of every Poisson solve since last read
+    double last_step_ms = 0.0, last_vcycle_ms = 0.0;
+    int last_vcycles = 0;
+    Multigrid& mg() { return *mg_; }
+
+private:
+    cfdnn_mesh_desc mesh_;
+    cfdnn_config cfg_;
+    Geom g_{};
+    size_t su_ = 0, sv_ = 0, sw_ = 0, sc_ = 0;
+    int vbc_[6] = {1, 1, 0, 0, 1, 1};     // VelocityBC defaults (include/solver.hpp:63-70)
+    double fx_ = 0, fy_ = 0, fz_ = 0, dt_ = 0, time_ = 0;
+    int step_count_ = 0;
+    bool is2d_ = false;
+
+    std::vector<DevBuf<double>> store_;
+    Vel vel_, star_, old_, rk_, conv_, diff_;
+    double *p_ = nullptr, *pcorr_ = nullptr, *div_ = nullptr, *rhs_ = nullptr, *nut_ = nullptr,
+           *nueff_ = nullptr, *k_ = nullptr, *omega_ = nullptr, *tau_[3] = {nullptr, nullptr, nullptr};
+    DevBuf<double> dyv_, dyc_, rdyv_, rdyc_;
+    double dy_min_ = 0.0;
+    std::vector<double> h_dyv_;
+    DevBuf<double> partial_, scalars_;
+    double* h_scalars_ = nullptr;          // pinned
+    size_t npartial_ = 0;
+
+    std::unique_ptr<Multigrid> mg_;
+    NNClosure* nn_ = nullptr;
+    Comm* comm_ = nullptr;
+    cudaStream_t st_ = nullptr;
+    cudaEvent_t ev0_ = nullptr, ev1_ = nullptr;
+
+    Vel alloc_vel();
+    double* alloc_cell();
+    double* field_ptr(int field, size_t* n) const;
+
+    // operators (all act on vel_ like the reference's, which ignore their arguments)
+    void apply_velocity_bc();                                   // solver_operators.cpp:43-491
+    void compute_convective_term();                             // :493-867
+    void compute_diffusive_term();                              // :869-1070
+    void compute_divergence(const Vel& v);                      // :1072-1245
+    void correct_velocity();                                    // :1259-1604
+    void blend(const Vel& a, const Vel& b, const Vel& c, double a1, double a2);  // c = a1 a + a2 b
+    void advance(const Vel& in, const Vel& out, double dt, bool seam_average);
+    void build_rhs(double dt);
+    int poisson_solve(const cfdnn_poisson_cfg& pc);
+    void euler_substep(const Vel& in, const Vel& out, double dt);   // solver_time.cpp:269-661
+    void project_velocity(Vel* which, double dt);                    // :736-1211
+    void ssprk3_step(double dt);                                     // :1303-1513
+    void ssprk2_step(double dt);                                     // :1213-1301
+    void euler_step();                                               // solver.cpp:1505-2507
+    void update_turbulence();
+    void build_nu_eff();
+    void step_device(bool want_residual);
+    void halo_vel(const Vel& v);
+    void halo_cell(double* c);
+    void check_nan(int step);
+    double max_change_host();
+};
+
+}  // namespace cfdnn

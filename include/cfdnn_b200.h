@@ -90,14 +90,20 @@ typedef struct cfdnn_poisson_stats {
     double residual, residual_l2, b_inf, b_l2, r0, r0_l2;
 } cfdnn_poisson_stats;
 
-/* Hot-path keys of Config — include/config.hpp:65-234 */
+/* Hot-path keys of Config — include/config.hpp:65-234 (same names, same defaults via
+ * cfdnn_config_default) */
 typedef struct cfdnn_config {
     double nu, dt;
     int time_integrator, convective_scheme;
     int adaptive_dt;
     double CFL_max, CFL_xz, dt_safety;
+    /* Poisson keys; the RK path uses only max_vcycles, tol_rhs, fixed_cycles
+     * (src/solver_time.cpp:868-871), the Euler path all of them (src/solver.cpp:2181-2205) */
     int poisson_fixed_cycles, poisson_max_vcycles;
-    double poisson_tol_rhs;
+    double poisson_tol_rhs, poisson_tol, poisson_abs_tol_floor, poisson_tol_abs, poisson_tol_rel;
+    int poisson_check_interval, poisson_use_l2_norm;
+    double poisson_linf_safety;
+    int poisson_nu1, poisson_nu2, poisson_chebyshev_degree;
     int turb_guard_enabled, turb_guard_interval;
     int turb_model;
     double nu_t_max;
@@ -142,6 +148,8 @@ int cfdnn_solver_get_dt(const cfdnn_solver* s, double* dt);             /* curre
 int cfdnn_solver_upload(cfdnn_solver* s, int field, const double* host, size_t n);   /* sync_to_gpu   */
 int cfdnn_solver_download(cfdnn_solver* s, int field, double* host, size_t n);       /* sync_from_gpu */
 size_t cfdnn_solver_field_size(const cfdnn_solver* s, int field);
+/* initialize(const VectorField&) :1060-1062 — apply_velocity_bc on the uploaded velocity */
+int cfdnn_solver_initialize(cfdnn_solver* s);
 int cfdnn_solver_step(cfdnn_solver* s, double* residual_out);           /* double step() :208 */
 /* run n steps without reading the residual back between them (app time loops) */
 int cfdnn_solver_run(cfdnn_solver* s, int nsteps, double* last_residual_out);

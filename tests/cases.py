@@ -1,0 +1,159 @@
+"""Shared parity cases (inputs are seeded; the oracle and the backend get identical arrays)."""
+import os
+import tempfile
+
+import numpy as np
+
+import refharness as R
+
+# (name, (Nx,Ny,Nz), poisson bc, fixed_cycles, extra harness args)
+MG_CASES = [
+    ("per16_fixed2", (16, 16, 16), "PPPPPP", 2, {}),
+    ("per32_conv1e8", (32, 32, 32), "PPPPPP", 0, dict(tol_rhs=1e-8, maxv=50, tol_rel=0, tol=0)),
+    ("chan_32x16x32_fixed3", (32, 16, 32), "PPNNPP", 3, {}),
+    ("neumann_16x32x16_conv", (16, 32, 16), "NNNNNN", 0, dict(tol_rhs=1e-6, maxv=30)),
+    ("mixed_dirichlet_fixed4", (32, 32, 32), "DDNNPP", 4, {}),
+    ("mixed2_conv_hitmax", (32, 32, 16), "DNNDND", 0, dict(tol_rhs=1e-10, maxv=12, tol_rel=0, tol=0)),
+    ("ragged_24x16x40_fixed2", (24, 16, 40), "PPNNPP", 2, {}),
+    ("tiny_8cube_single_level", (8, 8, 8), "PPPPPP", 2, {}),
+]
+
+# (name, N, velocity bc, integrator, scheme, fixed, nsteps, init, force, extra)
+STEP_CASES = [
+    ("tgv16_rk3_skew_fixed8", (16, 16, 16), "PPPPPP", "rk3", "skew", 8, 2, "tgv", (0, 0, 0), {}),
+    ("tgv16_rk3_skew_conv", (16, 16, 16), "PPPPPP", "rk3", "skew", 0, 3, "tgv", (0, 0, 0), dict(tol_rhs=1e-8, maxv=50)),
+    ("tgv16_rk3_central", (16, 16, 16), "PPPPPP", "rk3", "central", 8, 2, "tgv", (0, 0, 0), {}),
+    ("tgv16_euler_central", (16, 16, 16), "PPPPPP", "euler", "central", 8, 2, "tgv", (0, 0, 0), {}),
+    ("tgv16_euler_conv", (16, 16, 16), "PPPPPP", "euler", "skew", 0, 2, "tgv", (0, 0, 0), dict(tol_rhs=1e-6, maxv=20)),
+    ("channel16_rk3_walls_y", (16, 16, 16), "PPWWPP", "rk3", "skew", 8, 2, "shear", (1.0, 0, 0), {}),
+    ("duct16_rk2_walls_xy", (16, 16, 16), "WWWWPP", "rk2", "central", 4, 2, "shear", (1.0, 0, 0), {}),
+    ("box16_euler_walls_all", (16, 16, 16), "WWWWWW", "euler", "skew", 6, 2, "shear", (0.5, 0, 0), {}),
+    ("ragged_24x16x32_rk3", (24, 16, 32), "PPWWPP", "rk3", "skew", 4, 1, "shear", (1.0, 0, 0), {}),
+]
+
+
+def mg_inputs(N, seed=0):
+    Nx, Ny, Nz = N
+    rng = np.random.default_rng(seed)
+    shp = (Nz + 2, Ny + 2, Nx + 2)
+    rhs = np.zeros(shp)
+    r = rng.standard_normal((Nz, Ny, Nx))
+    r -= r.mean()
+    rhs[1:-1, 1:-1, 1:-1] = r
+    p0 = np.zeros(shp)
+    p0[1:-1, 1:-1, 1:-1] = 0.1 * rng.standard_normal((Nz, Ny, Nx))
+    return rhs, p0
+
+
+def run_mg_ref(case, td):
+    name, N, bc, fixed, extra = case
+    rhs, p0 = mg_inputs(N)
+    rhs.tofile(os.path.join(td, "rhs.f64"))
+    p0.tofile(os.path.join(td, "p0.f64"))
+    meta = R.run_ref("mg", Nx=N[0], Ny=N[1], Nz=N[2], bc=bc, fixed=fixed, rhs=os.path.join(td, "rhs.f64"),
+                     p0=os.path.join(td, "p0.f64"), out=os.path.join(td, "ref"), **extra)
+    p = np.fromfile(os.path.join(td, "ref_p.f64")).reshape(rhs.shape)
+    return meta, p
+
+
+def run_mg_backend(B, case):
+    import ctypes as C
+    name, N, bc, fixed, extra = case
+    rhs, p0 = mg_inputs(N)
+    capi = R.capi
+    md = B.mesh(*N)
+    h = C.c_void_p()
+    B.check(B.lib.cfdnn_mg_create(C.byref(md), C.byref(h)))
+    try:
+        arr = (C.c_int * 6)(*[R.PBC[c] for c in bc])
+        B.check(B.lib.cfdnn_mg_set_bc(h, arr))
+        cfg = capi.PoissonCfg()
+        B.lib.cfdnn_poisson_cfg_default(C.byref(cfg))
+        cfg.fixed_cycles = fixed
+        cfg.max_vcycles = int(extra.get("maxv", 20))
+        for k in ("tol_rhs", "tol_rel", "tol", "tol_abs"):
+            if k in extra:
+                setattr(cfg, k, float(extra[k]))
+        st = capi.PoissonStats()
+        p = p0.copy()
+        B.check(B.lib.cfdnn_mg_solve(h, capi.dptr(rhs), capi.dptr(p), C.byref(cfg), C.byref(st)))
+        return st.as_dict(), p
+    finally:
+        B.lib.cfdnn_mg_destroy(h)
+
+
+def step_init(N, init):
+    """Initial velocity exactly as oracle/ref_harness.cpp builds it (so goldens need no oracle run)."""
+    Nx, Ny, Nz = N
+    if init == "tgv":
+        return R.tgv_init(Nx, Ny, Nz)
+    sh = R.shapes(Nx, Ny, Nz)
+    u = np.zeros(sh["u"]); v = np.zeros(sh["v"]); w = np.zeros(sh["w"])
+    j = np.arange(Ny + 1)
+    u[0:Nz + 1, 0:Ny + 1, 0:Nx + 2] = (0.01 * np.sin(j * 3.14159 / Ny))[None, :, None]
+    return u, v, w
+
+
+def run_step_ref(case, td, dump_at=""):
+    name, N, bc, ti, scheme, fixed, nsteps, init, force, extra = case
+    u, v, w = step_init(N, init)
+    pre = os.path.join(td, "in")
+    u.tofile(pre + "_u.f64"); v.tofile(pre + "_v.f64"); w.tofile(pre + "_w.f64")
+    meta = R.run_ref("step", Nx=N[0], Ny=N[1], Nz=N[2], bc=bc, ti=ti, scheme=scheme, fixed=fixed, nsteps=nsteps,
+                     dt=0.01, nu=0.01, init="file:" + pre, fx=force[0], fy=force[1], fz=force[2],
+                     out=os.path.join(td, "ref"), dump_at=dump_at, **extra)
+    return meta, R.load_state(os.path.join(td, "ref_final"), *N)
+
+
+def make_solver(B, case, **cfg_over):
+    name, N, bc, ti, scheme, fixed, nsteps, init, force, extra = case
+    kw = dict(nu=0.01, dt=0.01, time_integrator=R.TI[ti], convective_scheme=R.SCHEME[scheme], adaptive_dt=0,
+              poisson_fixed_cycles=fixed)
+    if "tol_rhs" in extra:
+        kw["poisson_tol_rhs"] = float(extra["tol_rhs"])
+    if "maxv" in extra:
+        kw["poisson_max_vcycles"] = int(extra["maxv"])
+    kw.update(cfg_over)
+    cfg = B.config(**kw)
+    h = B.solver(B.mesh(*N), cfg, bc, tuple(float(f) for f in force))
+    u, v, w = step_init(N, init)
+    B.upload(h, "u", u); B.upload(h, "v", v); B.upload(h, "w", w)
+    return h
+
+
+def run_step_backend(B, case):
+    name, N, bc, ti, scheme, fixed, nsteps, init, force, extra = case
+    h = make_solver(B, case)
+    try:
+        res = [B.step(h) for _ in range(nsteps)]
+        return dict(residuals=res, cycles=B.cycles(h)), B.state(h, *N)
+    finally:
+        B.lib.cfdnn_solver_destroy(h)
+
+
+FIELDS = ("u", "v", "w", "p", "pcorr", "div", "rhs")
+
+
+def compare_states(got, ref, tol, label):
+    """per-field relative L2 over interior faces/cells (BASELINE.json gate); fields that are
+    ~0 (e.g. w of a 2-D-like flow) are compared by absolute max instead."""
+    worst = {}
+    for n in FIELDS:
+        a, b = R.interior(n, got[n]), R.interior(n, ref[n])
+        scale = np.abs(b).max()
+        if n in ("div",):
+            # divergence is a difference of O(1) numbers: compare against the velocity-gradient scale
+            err = np.abs(a - b).max()
+            worst[n] = err
+            assert err <= 1e-9, f"{label}: {n} abs err {err:.3e}"
+        elif scale < 1e-9:
+            err = np.abs(a - b).max()
+            worst[n] = err
+            assert err <= 1e-12, f"{label}: {n} abs err {err:.3e} (field ~ 0)"
+        else:
+            err = R.rel_l2(a, b)
+            worst[n] = err
+            # rhs = div/dt inherits the cancellation noise of div
+            lim = tol if n != "rhs" else max(tol, 1e-9)
+            assert err <= lim, f"{label}: {n} rel L2 {err:.3e} > {lim:.1e}"
+    return worst

@@ -1,0 +1,78 @@
+"""`-m "not gpu"`: host logic of the backend (V-cycle recursion, convergence checks, RK buffer
+choreography, BC pass order) run on the CPU test double (tests/devsim) against the oracle
+(the unmodified reference CPU build).  The GPU parity tests proper are in test_gpu_parity.py."""
+import tempfile
+
+import numpy as np
+import pytest
+
+import cases
+
+
+@pytest.mark.parametrize("case", cases.MG_CASES, ids=[c[0] for c in cases.MG_CASES])
+def test_mg_solve_matches_reference(sim, oracle, case):
+    with tempfile.TemporaryDirectory() as td:
+        meta, pref = cases.run_mg_ref(case, td)
+    st, p = cases.run_mg_backend(sim, case)
+    assert st["cycles"] == meta["cycles"]                      # BASELINE gate: same MG iteration count
+    assert st["converged"] == meta["converged"] and st["fixed_cycle_mode"] == meta["fixed_mode"]
+    assert oracle.rel_l2(p, pref) <= 1e-12                     # all cells incl. ghosts (solve :3769-3783)
+    for k in ("b_inf", "b_l2", "r0", "r0_l2"):
+        assert st[k] == pytest.approx(meta[k], rel=1e-9, abs=1e-300)
+    for k in ("residual", "residual_l2"):      # converged residuals are cancellation noise: looser
+        assert st[k] == pytest.approx(meta[k], rel=1e-4, abs=1e-300)
+
+
+@pytest.mark.parametrize("case", cases.STEP_CASES, ids=[c[0] for c in cases.STEP_CASES])
+def test_step_matches_reference(sim, oracle, case):
+    with tempfile.TemporaryDirectory() as td:
+        meta, ref = cases.run_step_ref(case, td)
+    got_meta, got = cases.run_step_backend(sim, case)
+    if meta["cycles"]:                                         # POISSON_STATS lines exist on the RK path only
+        assert got_meta["cycles"] == meta["cycles"]
+    assert got_meta["residuals"] == pytest.approx(meta["residuals"], rel=1e-9)
+    cases.compare_states(got, ref, 1e-10, case[0])
+
+
+def test_invalid_periodic_pair_is_invalid_argument(sim, R):
+    import ctypes as C
+    cfg = sim.config()
+    h = C.c_void_p()
+    m = sim.mesh(16, 16, 16)
+    sim.check(sim.lib.cfdnn_solver_create(C.byref(m), C.byref(cfg), C.byref(h)))
+    arr = (C.c_int * 6)(1, 0, 0, 0, 1, 1)                    # x_lo periodic, x_hi wall
+    rc = sim.lib.cfdnn_solver_set_velocity_bc(h, arr)
+    assert rc == 1 and b"Periodic BC in x" in sim.lib.cfdnn_last_error()   # std::invalid_argument (solver.cpp:653-661)
+    sim.lib.cfdnn_solver_destroy(h)
+
+
+def test_nan_guard_raises_runtime_error(sim, R):
+    case = cases.STEP_CASES[0]
+    h = cases.make_solver(sim, case, turb_guard_interval=1)
+    sh = R.shapes(16, 16, 16)
+    u = np.zeros(sh["u"]); u[5, 5, 5] = np.nan
+    sim.upload(h, "u", u)
+    with pytest.raises(R.capi.CfdnnError) as e:
+        sim.step(h)
+    assert e.value.code == 2 and "NaN/Inf" in str(e.value)    # std::runtime_error (solver.cpp:3195-3350)
+    sim.lib.cfdnn_solver_destroy(h)
+
+
+def test_adaptive_dt_matches_reference(sim, oracle):
+    import os
+    N = (16, 16, 16)
+    with tempfile.TemporaryDirectory() as td:
+        meta = oracle.run_ref("step", Nx=16, Ny=16, Nz=16, bc="PPPPPP", ti="rk3", scheme="skew", fixed=8, nsteps=3,
+                              dt=0.01, nu=0.01, init="tgv", adaptive_dt=1, CFL_max=0.4, out=os.path.join(td, "r"))
+    case = ("a", N, "PPPPPP", "rk3", "skew", 8, 3, "tgv", (0, 0, 0), {})
+    h = cases.make_solver(sim, case, adaptive_dt=1, CFL_max=0.4)
+    import ctypes as C
+    dts = []
+    for _ in range(3):
+        dt = C.c_double()
+        sim.check(sim.lib.cfdnn_solver_compute_adaptive_dt(h, C.byref(dt)))
+        sim.check(sim.lib.cfdnn_solver_set_dt(h, dt.value))
+        dts.append(dt.value)
+        sim.step(h)
+    sim.lib.cfdnn_solver_destroy(h)
+    assert dts == pytest.approx(meta["dts"], rel=1e-12)
