@@ -217,7 +217,7 @@ def main():
         roof = {"bound": "hbm", "kernel": "multigrid V-cycle (all levels; smoother sweeps dominate)",
                 "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak if achieved else None,
                 "traffic": None, "peak_source": which, "algorithmic_bytes_per_launch": VCYCLE_BYTES_PER_CELL * N ** 3,
-                "vcycle_ms": vc_avg_ms, "vcycles_timed": n_vc, "vcycle_share_of_step": vc_ms / (step_ms * args.steps)}
+                "vcycle_ms": vc_avg_ms, "vcycles_timed": n_vc, "vcycle_share_of_step": vc_ms / step_ms}
         cpu = None
         if not args.no_cpu_baseline and R.have_oracle():
             ns = 4

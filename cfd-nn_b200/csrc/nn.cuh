@@ -3,12 +3,30 @@
 // Stands in for TurbulenceNNTBNN / TurbulenceNNMLP (reference include/turbulence_nn_tbnn.hpp:35-56,
 // include/turbulence_nn_mlp.hpp, src/turbulence_nn_tbnn.cpp:640-871, src/turbulence_nn_mlp.cpp:140-292),
 // the FP64 MLP of src/nn_core.cpp:36-204 and the features / tensor basis of src/features.cpp:67-326.
+// CPU-path semantics: k/omega estimated algebraically when k is not provided,
+// uniform-spacing gradients for the features, stretched-aware gradients for the tensor basis.
+// 3-D meshes: the 2-D update is applied to every interior z-plane.
 #pragma once
 #include "common.cuh"
 #include "solver.cuh"
 #include <vector>
 
 namespace cfdnn {
+
+constexpr int NN_MAX_LAYERS = 8;
+constexpr int NN_MAX_WIDTH = 64;
+
+struct NNDev {                       // by-value kernel argument
+    int n_layers;
+    int dims[NN_MAX_LAYERS + 1];
+    int act[NN_MAX_LAYERS];          // 0 linear, 1 tanh, 2 relu
+    int woff[NN_MAX_LAYERS], boff[NN_MAX_LAYERS];
+    const double *W, *b;             // row-major (out,in) per layer, concatenated
+    const double *means, *stds;      // null when the model has no input scaling
+    int n_scale;
+};
+
+struct NNParams { double nu, delta, u_ref, k_min, nu_t_max; };
 
 class NNClosure {
 public:
@@ -20,26 +38,25 @@ public:
     // TurbulenceModel::update on host arrays (2-D mesh: reference semantics; 3-D: every interior plane)
     void update_host(const cfdnn_mesh_desc& m, const double* u, const double* v, const double* k,
                      const double* omega, double* nu_t, double* txx, double* txy, double* tyy);
-    // device-resident twin used by Solver::step
-    void update_device(const Geom& g, const cfdnn_mesh_desc& m, const Vel& vel, const double* k,
-                       const double* omega, double* nu_t, double* txx, double* txy, double* tyy,
-                       cudaStream_t st);
+    // device-resident twin used by Solver::step.  yc: device array of Ny+2Ng cell-centre y.
+    void update_device(const Geom& g, const double* yc, double y_lo, double y_hi, const Vel& vel,
+                       const double* k, const double* omega, double* nu_t, double* txx, double* txy,
+                       double* tyy, cudaStream_t st);
     // MLP::forward on a batch: x[n][in] -> y[n][out]
     void forward_host(const double* x, double* y, size_t n);
     double last_ms = 0.0;
     int kind() const { return kind_; }
+    int in_dim() const { return net_.dims[0]; }
+    int out_dim() const { return net_.dims[net_.n_layers]; }
 
 private:
     int kind_;
-    std::vector<int> dims_, act_;
+    NNDev net_{};
+    NNParams prm_{0.001, 1.0, 1.0, 1e-10, 1.0};
     DevBuf<double> W_, b_, means_, stds_;
-    std::vector<size_t> woff_, boff_;
-    bool has_scaling_ = false;
-    double nu_ = 0.001, delta_ = 1.0, u_ref_ = 1.0, k_min_ = 1e-10, nu_t_max_ = 1.0;
+    DevBuf<int> kflag_;
     cudaStream_t st_ = nullptr;
     cudaEvent_t ev0_ = nullptr, ev1_ = nullptr;
-    DevBuf<double> scratch_[12];
-    DevBuf<double> yc_, dyc_;
 };
 
 }  // namespace cfdnn

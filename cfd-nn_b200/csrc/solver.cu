@@ -14,6 +14,22 @@ static inline dim3 grid3(int nx, int ny, int nz) {
     return dim3((nx + kB.x - 1) / kB.x, (ny + kB.y - 1) / kB.y, nz);
 }
 
+Geom make_geom(const cfdnn_mesh_desc& m) {
+    Geom g{};
+    const int Ng = m.Ng, Nx = m.Nx, Ny = m.Ny;
+    g.Nx = Nx; g.Ny = Ny; g.Nz = m.Nz; g.Ng = Ng;
+    g.us = Nx + 1 + 2 * Ng; g.vs = Nx + 2 * Ng; g.ws = Nx + 2 * Ng; g.cs = Nx + 2 * Ng;
+    g.up = (long long)g.us * (Ny + 2 * Ng);
+    g.vp = (long long)g.vs * (Ny + 1 + 2 * Ng);
+    g.wp = (long long)g.ws * (Ny + 2 * Ng);
+    g.cp = (long long)g.cs * (Ny + 2 * Ng);
+    g.dx = make_div_host(m.dx); g.dy = make_div_host(m.dy); g.dz = make_div_host(m.dz);
+    g.dx_2 = make_div_host(2.0 * m.dx); g.dy_2 = make_div_host(2.0 * m.dy); g.dz_2 = make_div_host(2.0 * m.dz);
+    g.dx2 = make_div_host(m.dx * m.dx); g.dy2 = make_div_host(m.dy * m.dy); g.dz2 = make_div_host(m.dz * m.dz);
+    g.y_stretched = m.y_stretched;
+    return g;
+}
+
 // ---------------------------------------------------------------- construction
 Solver::Solver(const cfdnn_mesh_desc& m, const cfdnn_config& c) : mesh_(m), cfg_(c) {
     require_device();
@@ -26,19 +42,11 @@ Solver::Solver(const cfdnn_mesh_desc& m, const cfdnn_config& c) : mesh_(m), cfg_
         throw std::invalid_argument("Solver: bad time_integrator");
     is2d_ = false;
     const int Ng = m.Ng, Nx = m.Nx, Ny = m.Ny, Nz = m.Nz;
-    g_.Nx = Nx; g_.Ny = Ny; g_.Nz = Nz; g_.Ng = Ng;
-    g_.us = Nx + 1 + 2 * Ng; g_.vs = Nx + 2 * Ng; g_.ws = Nx + 2 * Ng; g_.cs = Nx + 2 * Ng;
-    g_.up = (long long)g_.us * (Ny + 2 * Ng);
-    g_.vp = (long long)g_.vs * (Ny + 1 + 2 * Ng);
-    g_.wp = (long long)g_.ws * (Ny + 2 * Ng);
-    g_.cp = (long long)g_.cs * (Ny + 2 * Ng);
+    g_ = make_geom(m);
     su_ = (size_t)g_.up * (Nz + 2 * Ng);
     sv_ = (size_t)g_.vp * (Nz + 2 * Ng);
     sw_ = (size_t)g_.wp * (Nz + 1 + 2 * Ng);
     sc_ = (size_t)g_.cp * (Nz + 2 * Ng);
-    g_.dx = make_div_host(m.dx); g_.dy = make_div_host(m.dy); g_.dz = make_div_host(m.dz);
-    g_.dx_2 = make_div_host(2.0 * m.dx); g_.dy_2 = make_div_host(2.0 * m.dy); g_.dz_2 = make_div_host(2.0 * m.dz);
-    g_.dx2 = make_div_host(m.dx * m.dx); g_.dy2 = make_div_host(m.dy * m.dy); g_.dz2 = make_div_host(m.dz * m.dz);
     g_.y_stretched = m.y_stretched;
     dy_min_ = m.dy;
     if (m.y_stretched) {
@@ -55,6 +63,12 @@ Solver::Solver(const cfdnn_mesh_desc& m, const cfdnn_config& c) : mesh_(m), cfg_
         CFDNN_CUDA(cudaMemcpy(rdyc_.p, rc.data(), nc * sizeof(double), cudaMemcpyHostToDevice));
         g_.dyv = dyv_.p; g_.rdyv = rdyv_.p; g_.dyc = dyc_.p; g_.rdyc = rdyc_.p;
         dy_min_ = *std::min_element(h_dyv_.begin(), h_dyv_.end());   // src/solver.cpp:3672-3675
+    }
+    {
+        std::vector<double> yc(Ny + 2 * Ng);
+        for (int j = 0; j < Ny + 2 * Ng; ++j) yc[j] = m.yc ? m.yc[j] : m.y_lo + (j - Ng + 0.5) * m.dy;   // src/mesh.cpp:66-68
+        yc_.alloc(yc.size(), false);
+        CFDNN_CUDA(cudaMemcpy(yc_.p, yc.data(), yc.size() * sizeof(double), cudaMemcpyHostToDevice));
     }
     mesh_.dyv = mesh_.dyc = mesh_.yLap_aS = mesh_.yLap_aN = mesh_.yLap_aP = mesh_.yc = nullptr;  // host pointers not kept
 
@@ -376,7 +390,7 @@ void Solver::build_nu_eff() {
 
 void Solver::update_turbulence() {
     if (!nn_) return;
-    nn_->update_device(g_, mesh_, vel_, k_, omega_, nut_, tau_[0], tau_[1], tau_[2], st_);
+    nn_->update_device(g_, yc_.p, mesh_.y_lo, mesh_.y_hi, vel_, k_, omega_, nut_, tau_[0], tau_[1], tau_[2], st_);
 }
 
 void Solver::check_nan(int step) {                              // check_for_nan_inf :3195-3350

@@ -38,6 +38,9 @@ struct Geom {                 // by-value kernel argument
 
 struct Vel { double *u = nullptr, *v = nullptr, *w = nullptr; };
 
+// strides / spacings of a mesh in the reference layout (y-metric pointers are left null)
+Geom make_geom(const cfdnn_mesh_desc& m);
+
 class Solver {
 public:
     Solver(const cfdnn_mesh_desc& m, const cfdnn_config& c);
@@ -79,7 +82,7 @@ private:
     Vel vel_, star_, old_, rk_, conv_, diff_;
     double *p_ = nullptr, *pcorr_ = nullptr, *div_ = nullptr, *rhs_ = nullptr, *nut_ = nullptr,
            *nueff_ = nullptr, *k_ = nullptr, *omega_ = nullptr, *tau_[3] = {nullptr, nullptr, nullptr};
-    DevBuf<double> dyv_, dyc_, rdyv_, rdyc_;
+    DevBuf<double> dyv_, dyc_, rdyv_, rdyc_, yc_;
     double dy_min_ = 0.0;
     std::vector<double> h_dyv_;
     DevBuf<double> partial_, scalars_;
