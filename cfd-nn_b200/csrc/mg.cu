@@ -1,6 +1,8 @@
 // mg.cu — host orchestration of the multigrid V-cycle (see mg.cuh for the layout).
 #include "mg_kernels.cuh"
+#include "mg_tb_kernels.cuh"
 #include "comm.cuh"
+#include <cstdlib>
 #include <cmath>
 #include <algorithm>
 #include <cstring>
@@ -68,6 +70,7 @@ Multigrid::Multigrid(const cfdnn_mesh_desc& m) : mesh_(m) {
 #ifdef CFDNN_DEVSIM
     use_graph_ = false;   // the CPU test double does not model CUDA graphs
 #endif
+    tb_setup();
     apply_bc_codes();
 }
 
@@ -123,6 +126,59 @@ void Multigrid::sweep(int level, const double* uin, double* uout, double omega) 
     CFDNN_LAUNCH((k_sweep<KZ, false>), g, kBlk, 0, st_, L.g, uin, L.f.p, uout, omega, 1.0 - omega);
 }
 
+// ---- temporally blocked sweeps (mg_tb_kernels.cuh)
+namespace {
+// tile shapes: BIG for levels that fill the chip with 64-wide tiles, SMALL for the rest
+constexpr int TB_BX_BIG = 64, TB_BY_BIG = 28, TB_BX_SMALL = 32, TB_BY_SMALL = 12;
+
+template <int T, int BX, int BY>
+void tb_attr() {
+    using S = TbShape<T, BX, BY>;
+    CFDNN_CUDA(cudaFuncSetAttribute(k_sweep_tb<T, BX, BY>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::SMEM));
+}
+template <int T, int BX, int BY>
+void tb_launch(const LevelGeom& g, const double* in, const double* f, double* out, const double* w,
+               cudaStream_t st) {
+    using S = TbShape<T, BX, BY>;
+    TbOmega<T> om;
+    for (int s = 0; s < T; ++s) om.w[s] = w[s];
+    const int tx = (g.Nx + BX - 1) / BX, ty = (g.Ny + BY - 1) / BY;
+    // z chunks: enough CTAs for >= ~8 waves of 148 SMs, but chunks no thinner than 8*T planes
+    const int zc_min = 8 * T;
+    const int nch_max = std::max(1, g.Nz / zc_min);
+    const int want = 148 * 8;
+    int nch = std::min(nch_max, std::max(1, (want + tx * ty - 1) / (tx * ty)));
+    const int ZC = (g.Nz + nch - 1) / nch;
+    nch = (g.Nz + ZC - 1) / ZC;
+    dim3 grid(tx, ty, nch);
+    CFDNN_LAUNCH_COOP((k_sweep_tb<T, BX, BY>), grid, S::NTHREADS, S::SMEM, st, g, in, f, out, om, ZC);
+}
+}  // namespace
+
+void Multigrid::tb_setup() {
+    tb_attr<1, TB_BX_BIG, TB_BY_BIG>(); tb_attr<2, TB_BX_BIG, TB_BY_BIG>();
+    tb_attr<1, TB_BX_SMALL, TB_BY_SMALL>(); tb_attr<2, TB_BX_SMALL, TB_BY_SMALL>();
+    if (const char* e = std::getenv("CFDNN_MG_TB")) tb_max_ = std::max(0, std::min(2, std::atoi(e)));
+}
+
+// n (<= 2) sweeps in one pass; false when this level is not eligible
+bool Multigrid::sweeps_tb(int level, const double* in, double* out, const double* w, int n) {
+    Level& L = *levels_[level];
+    const LevelGeom& g = L.g;
+    if (tb_max_ <= 0 || n > tb_max_) return false;
+    if (g.nonuniform_y || (g.Nx & 1) || g.Nx < 16 || g.Ny < 8 || g.Nz < 4) return false;
+    if (g.bc[4] == CFDNN_PBC_HALO || g.bc[5] == CFDNN_PBC_HALO) return false;
+    const bool big = g.Nx >= 128 && g.Ny >= 56 && g.Nz >= 32;
+    if (big) {
+        if (n == 2) tb_launch<2, TB_BX_BIG, TB_BY_BIG>(g, in, L.f.p, out, w, st_);
+        else tb_launch<1, TB_BX_BIG, TB_BY_BIG>(g, in, L.f.p, out, w, st_);
+    } else {
+        if (n == 2) tb_launch<2, TB_BX_SMALL, TB_BY_SMALL>(g, in, L.f.p, out, w, st_);
+        else tb_launch<1, TB_BX_SMALL, TB_BY_SMALL>(g, in, L.f.p, out, w, st_);
+    }
+    return true;
+}
+
 // smooth_chebyshev (:825-1001): degree sweeps with Chebyshev weights; BCs are implicit.
 void Multigrid::smooth_chebyshev(int level, int degree) {
     Level& L = *levels_[level];
@@ -132,13 +188,20 @@ void Multigrid::smooth_chebyshev(int level, int degree) {
     const double c = (lambda_max - lambda_min) / 2.0;
     double* a = L.u.p;
     double* b = L.tmp.p;
-    for (int k = 0; k < degree; ++k) {
+    auto omega_of = [&](int k) {
         const double theta = M_PI * (2.0 * k + 1.0) / (2.0 * degree);
-        double omega = 1.0 / (d - c * std::cos(theta));
-        omega = std::min(omega, 2.0);
-        halo(level, a);
-        sweep(level, a, b, omega);
+        return std::min(1.0 / (d - c * std::cos(theta)), 2.0);
+    };
+    for (int k = 0; k < degree;) {
+        const int n = std::min(2, degree - k);
+        const double w[2] = {omega_of(k), omega_of(k + 1)};
+        if (n == 2 && sweeps_tb(level, a, b, w, 2)) { k += 2; std::swap(a, b); continue; }
+        if (!sweeps_tb(level, a, b, w, 1)) {
+            halo(level, a);
+            sweep(level, a, b, w[0]);
+        }
         std::swap(a, b);
+        ++k;
     }
     if (a != L.u.p) std::swap(L.u.p, L.tmp.p);   // result lives in L.u
 }

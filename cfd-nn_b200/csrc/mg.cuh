@@ -99,6 +99,9 @@ private:
     void smooth_chebyshev(int level, int degree);
     void smooth_jacobi(int level, int iters, double omega);
     void sweep(int level, const double* uin, double* uout, double omega);
+    void tb_setup();
+    bool sweeps_tb(int level, const double* in, double* out, const double* w, int n);
+    int tb_max_ = 2;                // sweeps fused per pass (env CFDNN_MG_TB: 0 = plain k_sweep only)
     void residual(int level);
     void residual_norms(int level, double* d_max, double* d_sumsq);
     void restrict_to(int fine);

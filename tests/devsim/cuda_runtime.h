@@ -112,6 +112,7 @@ inline T devsim_shfl(T v, int src) {
     return r;
 }
 template <typename T> inline T __shfl_down_sync(unsigned, T v, int d) { int s = devsim::lane_id() + d; return devsim_shfl(v, s < 32 ? s : -1); }
+template <typename T> inline T __shfl_up_sync(unsigned, T v, int d) { int s = devsim::lane_id() - d; return devsim_shfl(v, s >= 0 ? s : -1); }
 template <typename T> inline T __shfl_xor_sync(unsigned, T v, int m) { return devsim_shfl(v, devsim::lane_id() ^ m); }
 template <typename T> inline T __shfl_sync(unsigned, T v, int s) { return devsim_shfl(v, s & 31); }
 template <typename T> inline T __ldg(const T* p) { return *p; }
