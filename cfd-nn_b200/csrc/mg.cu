@@ -129,7 +129,7 @@ void Multigrid::sweep(int level, const double* uin, double* uout, double omega) 
 // ---- temporally blocked sweeps (mg_tb_kernels.cuh)
 namespace {
 // tile shapes: BIG for levels that fill the chip with 64-wide tiles, SMALL for the rest
-constexpr int TB_BX_BIG = 64, TB_BY_BIG = 28, TB_BX_SMALL = 32, TB_BY_SMALL = 12;
+constexpr int TB_BX_BIG = 64, TB_BY_BIG = 26, TB_BX_SMALL = 32, TB_BY_SMALL = 12;
 
 template <int T, int BX, int BY>
 void tb_attr() {

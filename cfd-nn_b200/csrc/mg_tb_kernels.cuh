@@ -14,8 +14,11 @@
 //     (level l = field after l sweeps).  Per level it keeps the planes z-1 and z of its quad in
 //     registers; plane z+1 arrives from the level below in the same iteration (registers);
 //   * only the x/y neighbours of the centre plane go through shared memory (N/S rows as
-//     LDS.128) or warp shuffles (E/W), one double-buffered plane per level, one __syncthreads
-//     per z iteration;
+//     conflict-free LDS.128: a plane is stored as [pair][thread] double2) or warp shuffles (E/W),
+//     one double-buffered plane per level, one __syncthreads per z iteration;
+//   * the z loop is unrolled by 3 so the three live planes of a level rotate through fixed
+//     registers (no moves); tiles that touch a non-periodic face take a separate code path so
+//     the interior path carries no boundary selects;
 //   * tile cells whose dependency cone leaves the tile compute garbage that is never consumed
 //     by a stored cell (the valid region shrinks by one cell per level, exactly the halo).
 // Arithmetic of one sweep is expression-for-expression that of k_sweep (mg_kernels.cuh), so the
@@ -40,17 +43,13 @@ struct TbShape {
     static constexpr int NACTIVE = NQ * TY;
     static constexpr int NTHREADS = (NACTIVE + 31) / 32 * 32;
     static constexpr int PLANE = TX * TY;
-    static constexpr size_t SMEM = sizeof(double) * (size_t)PLANE * 2 * T;
+    static constexpr size_t SMEM = sizeof(double) * (size_t)(4 * NTHREADS) * 2 * T;   // [2T planes][2 pairs][NTHREADS] double2
 };
 
 __device__ __forceinline__ int wrap_idx(int i, int N) {
     i %= N;
     return i < 0 ? i + N : i;
 }
-
-struct Quad {
-    double v[4];
-};
 
 __device__ __forceinline__ void ld_pair(const double* __restrict__ p, double& a, double& b) {
     const double2 t = *reinterpret_cast<const double2*>(p);
@@ -74,7 +73,9 @@ __global__ void __launch_bounds__(TbShape<T, BX, BY>::NTHREADS, 1)
 k_sweep_tb(LevelGeom g, const double* __restrict__ u, const double* __restrict__ f,
            double* __restrict__ out, TbOmega<T> om, int ZC) {
     using S = TbShape<T, BX, BY>;
+    static_assert(T >= 1 && T <= 2, "f ring has 3 slots");
     CFDNN_DYN_SMEM(double, sm);
+    constexpr int NT = S::NTHREADS;
     const int t = threadIdx.x;
     const int lane = t & 31;
     const bool active = t < S::NACTIVE;
@@ -97,7 +98,7 @@ k_sweep_tb(LevelGeom g, const double* __restrict__ u, const double* __restrict__
     // ---- per-thread geometry: load offsets, store validity, boundary masks
     const bool rowok = active && (pery || (gy >= 0 && gy < g.Ny));
     const int gyw = pery ? wrap_idx(gy, g.Ny) : gy;
-    long long off[2];
+    int off[2];                         // within-plane element offset (< 2^31)
     bool ldok[2], stok[2];
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
@@ -105,7 +106,7 @@ k_sweep_tb(LevelGeom g, const double* __restrict__ u, const double* __restrict__
         const bool okx = perx || (gxp >= 0 && gxp + 1 < g.Nx);
         const int gxw = perx ? wrap_idx(gxp, g.Nx) : gxp;
         ldok[h] = rowok && okx;
-        off[h] = ldok[h] ? (long long)gyw * g.Px + gxw : 0;
+        off[h] = ldok[h] ? gyw * g.Px + gxw : 0;
         const int tx = lx + 2 * h;
         stok[h] = active && tx >= S::HX && tx < S::HX + BX && row >= T && row < T + BY &&
                   gxp >= 0 && gxp + 1 < g.Nx && gy >= 0 && gy < g.Ny;
@@ -119,27 +120,36 @@ k_sweep_tb(LevelGeom g, const double* __restrict__ u, const double* __restrict__
         }
     }
     const bool selfS = !pery && gy == 0, selfN = !pery && gy == g.Ny - 1;
-    const int si = row * S::TX + lx;                       // my quad in a smem plane
-    const int sS = row > 0 ? si - S::TX : si;
-    const int sN = row < S::TY - 1 ? si + S::TX : si;
+    const bool edge = (bw | be) != 0u || selfS || selfN;
+    // smem plane = [2 pairs][NT threads] double2: every LDS/STS.128 of a warp is contiguous
+    const int tS = row > 0 ? t - S::NQ : t;               // thread holding my S / N neighbours
+    const int tN = (active && row < S::TY - 1) ? t + S::NQ : t;
     const bool wsm = (lane == 0) && q > 0;                 // W neighbour must come from smem
     const bool esm = (lane == 31) && q < S::NQ - 1;
+    constexpr int PL = 4 * NT;                             // doubles per smem plane
 
-    // ---- pipeline state
-    double m[T][4], c[T][4], fr[T][4];
+    // ---- pipeline state: lv[l][slot] = plane of level l that arrived in phase `slot` (mod 3)
+    double lv[T][3][4], fr[3][4], nu_[4];
 #pragma unroll
     for (int l = 0; l < T; ++l)
 #pragma unroll
-        for (int p = 0; p < 4; ++p) { m[l][p] = 0.0; c[l][p] = 0.0; fr[l][p] = 0.0; }
+        for (int k = 0; k < 3; ++k)
+#pragma unroll
+            for (int p = 0; p < 4; ++p) lv[l][k][p] = 0.0;
+#pragma unroll
+    for (int k = 0; k < 3; ++k)
+#pragma unroll
+        for (int p = 0; p < 4; ++p) fr[k][p] = 0.0;
 
     // z range of input planes: virtual planes wrap when periodic, are clipped otherwise
     const int zi_first = perz ? z0 - T : max(z0 - T, 0);
-    const int zi_last = z1 - 1 + T;                        // inclusive; loads stop at Nz-1 unless periodic
-    double nu_[4], nf_[4];                                  // prefetched u[zi], f[zi-1]
+    const int zi_last = z1 - 1 + T;
+    const unsigned uplane = (unsigned)g.plane;
     auto load_plane = [&](const double* __restrict__ a, int z, double* dst) {
-        const bool zok = perz || (z >= 0 && z < g.Nz);
-        const int zw = perz ? wrap_idx(z, g.Nz) : z;
-        const double* base = a + (size_t)(zw + 1) * (size_t)g.plane;
+        int zw = z;                                        // z in [-T, Nz+T): one conditional wrap
+        if (perz) zw = zw < 0 ? zw + g.Nz : (zw >= g.Nz ? zw - g.Nz : zw);
+        const bool zok = zw >= 0 && zw < g.Nz;
+        const double* base = a + (size_t)(unsigned)(zw + 1) * (size_t)uplane;   // one IMAD.WIDE.U32
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
             if (zok && ldok[h]) ld_pair(base + off[h], dst[2 * h], dst[2 * h + 1]);
@@ -147,74 +157,82 @@ k_sweep_tb(LevelGeom g, const double* __restrict__ u, const double* __restrict__
         }
     };
     load_plane(u, zi_first, nu_);
-    load_plane(f, zi_first - 1, nf_);
+    load_plane(f, zi_first - 1, fr[0]);
 
     int par = 0;
-    for (int zi = zi_first; zi <= zi_last; ++zi, par ^= 1) {
-        double p_in[4];
+    for (int zb = zi_first; zb <= zi_last; zb += 3) {
 #pragma unroll
-        for (int p = 0; p < 4; ++p) p_in[p] = nu_[p];
-        // f ring: fr[s] must hold f[zi-1-s] while the stages run
+        for (int ph = 0; ph < 3; ++ph) {
+            const int zi = zb + ph;
+            if (zi > zi_last) break;
+            const int A = ph, C = (ph + 2) % 3, M = (ph + 1) % 3;   // arriving / centre / z-1 slots
 #pragma unroll
-        for (int s = T - 1; s > 0; --s)
-#pragma unroll
-            for (int p = 0; p < 4; ++p) fr[s][p] = fr[s - 1][p];
-#pragma unroll
-        for (int p = 0; p < 4; ++p) fr[0][p] = nf_[p];
-        // prefetch the next iteration's planes
-        if (zi < zi_last) {
-            load_plane(u, zi + 1, nu_);
-            load_plane(f, zi, nf_);
-        }
-#pragma unroll
-        for (int s = 0; s < T; ++s) {
-            // level-s plane (zi - s) arrives in p_in: publish it as next iteration's centre plane
-            double* wbuf = sm + (size_t)(2 * s + par) * S::PLANE;
-            const double* rbuf = sm + (size_t)(2 * s + (par ^ 1)) * S::PLANE;
-            if (active) {
-                st_pair(wbuf + si, p_in[0], p_in[1]);
-                st_pair(wbuf + si + 2, p_in[2], p_in[3]);
+            for (int p = 0; p < 4; ++p) lv[0][A][p] = nu_[p];
+            if (zi < zi_last) {                            // prefetch next iteration's planes
+                load_plane(u, zi + 1, nu_);
+                load_plane(f, zi, fr[(ph + 1) % 3]);
             }
-            const int zo = zi - 1 - s;                     // plane this stage produces (level s+1)
-            const bool zvalid = perz || (zo >= 0 && zo < g.Nz);
-            double o[4] = {0.0, 0.0, 0.0, 0.0};
-            // E/W neighbours of the centre plane: registers of the adjacent lanes
-            double uWq = __shfl_up_sync(0xffffffffu, c[s][3], 1);
-            double uEq = __shfl_down_sync(0xffffffffu, c[s][0], 1);
-            if (zvalid) {
-                if (wsm) uWq = rbuf[si - 1];
-                if (esm) uEq = rbuf[si + 4];
-                double n_[4], s_[4];
-                ld_pair(rbuf + sN, n_[0], n_[1]); ld_pair(rbuf + sN + 2, n_[2], n_[3]);
-                ld_pair(rbuf + sS, s_[0], s_[1]); ld_pair(rbuf + sS + 2, s_[2], s_[3]);
-                const bool zlo = !perz && zo == 0, zhi = !perz && zo == g.Nz - 1;
-                const double omega = om.w[s], om1 = 1.0 - omega;
 #pragma unroll
-                for (int p = 0; p < 4; ++p) {
-                    const double uc = c[s][p];
-                    double uW = p == 0 ? uWq : c[s][p - 1];
-                    double uE = p == 3 ? uEq : c[s][p + 1];
-                    if (bw >> p & 1u) uW = sxlo * uc;
-                    if (be >> p & 1u) uE = sxhi * uc;
-                    const double uS = selfS ? sylo * uc : s_[p];
-                    const double uN = selfN ? syhi * uc : n_[p];
-                    const double ub = zlo ? szlo * uc : m[s][p];
-                    const double uf = zhi ? szhi * uc : p_in[p];
-                    o[p] = jacobi_point(g, uc, uW, uE, uS, uN, ub, uf, fr[s][p], omega, om1);
+            for (int s = 0; s < T; ++s) {
+                // level-s plane (zi - s) has arrived: publish it as next iteration's centre plane
+                double* wbuf = sm + (size_t)(2 * s + par) * PL;
+                const double* rbuf = sm + (size_t)(2 * s + (par ^ 1)) * PL;
+                st_pair(wbuf + 2 * t, lv[s][A][0], lv[s][A][1]);
+                st_pair(wbuf + 2 * NT + 2 * t, lv[s][A][2], lv[s][A][3]);
+                const int zo = zi - 1 - s;                 // plane this stage produces (level s+1)
+                const bool zvalid = perz || (zo >= 0 && zo < g.Nz);
+                double o[4] = {0.0, 0.0, 0.0, 0.0};
+                double uWq = __shfl_up_sync(0xffffffffu, lv[s][C][3], 1);
+                double uEq = __shfl_down_sync(0xffffffffu, lv[s][C][0], 1);
+                if (zvalid) {
+                    if (wsm) uWq = rbuf[2 * NT + 2 * (t - 1) + 1];
+                    if (esm) uEq = rbuf[2 * (t + 1)];
+                    double n_[4], s_[4];
+                    ld_pair(rbuf + 2 * tN, n_[0], n_[1]); ld_pair(rbuf + 2 * NT + 2 * tN, n_[2], n_[3]);
+                    ld_pair(rbuf + 2 * tS, s_[0], s_[1]); ld_pair(rbuf + 2 * NT + 2 * tS, s_[2], s_[3]);
+                    const double omega = om.w[s], om1 = 1.0 - omega;
+                    const double* fv = fr[(ph + 3 - s) % 3];
+                    const bool zlo = !perz && zo == 0, zhi = !perz && zo == g.Nz - 1;
+                    if (!edge && !zlo && !zhi) {           // interior path: no boundary selects
+#pragma unroll
+                        for (int p = 0; p < 4; ++p) {
+                            const double uW = p == 0 ? uWq : lv[s][C][p - 1];
+                            const double uE = p == 3 ? uEq : lv[s][C][p + 1];
+                            o[p] = jacobi_point(g, lv[s][C][p], uW, uE, s_[p], n_[p], lv[s][M][p], lv[s][A][p],
+                                                fv[p], omega, om1);
+                        }
+                    } else {                               // faces: ghost = sign * adjacent interior value
+#pragma unroll
+                        for (int p = 0; p < 4; ++p) {
+                            const double uc = lv[s][C][p];
+                            double uW = p == 0 ? uWq : lv[s][C][p - 1];
+                            double uE = p == 3 ? uEq : lv[s][C][p + 1];
+                            if (bw >> p & 1u) uW = sxlo * uc;
+                            if (be >> p & 1u) uE = sxhi * uc;
+                            const double uS = selfS ? sylo * uc : s_[p];
+                            const double uN = selfN ? syhi * uc : n_[p];
+                            const double ub = zlo ? szlo * uc : lv[s][M][p];
+                            const double uf = zhi ? szhi * uc : lv[s][A][p];
+                            o[p] = jacobi_point(g, uc, uW, uE, uS, uN, ub, uf, fv[p], omega, om1);
+                        }
+                    }
+                }
+                if (s + 1 < T) {
+#pragma unroll
+                    for (int p = 0; p < 4; ++p) lv[(s + 1) % T][A][p] = o[p];
+                } else {
+                    const int zf = zi - T;                 // o = level-T plane zi - T
+                    if (zf >= z0 && zf < z1) {
+                        double* base = out + (size_t)(unsigned)(zf + 1) * (size_t)uplane;
+#pragma unroll
+                        for (int h = 0; h < 2; ++h)
+                            if (stok[h]) st_pair(base + off[h], o[2 * h], o[2 * h + 1]);
+                    }
                 }
             }
-#pragma unroll
-            for (int p = 0; p < 4; ++p) { m[s][p] = c[s][p]; c[s][p] = p_in[p]; p_in[p] = o[p]; }
+            __syncthreads();
+            par ^= 1;
         }
-        // p_in now holds level-T plane zi - T
-        const int zf = zi - T;
-        if (zf >= z0 && zf < z1) {
-            double* base = out + (size_t)(zf + 1) * (size_t)g.plane;
-#pragma unroll
-            for (int h = 0; h < 2; ++h)
-                if (stok[h]) st_pair(base + off[h], p_in[2 * h], p_in[2 * h + 1]);
-        }
-        __syncthreads();
     }
 }
 
