@@ -1,0 +1,333 @@
+// cfdnn_b200_shim.hpp — reference-side C++ binding of libcfdnn_b200.so.
+//
+// Header-only.  Compiled INSIDE the reference tree (it includes the reference's own headers) so
+// that reference host code — apps, tests, bench_mg — can switch to the B200 backend by changing a
+// type name: the classes below present the public signatures of
+//   nncfd::MultigridPoissonSolver   (include/poisson_solver_multigrid.hpp:26-102)
+//   nncfd::RANSSolver               (include/solver.hpp:86-311; hot-path subset)
+//   nncfd::TurbulenceNNTBNN / NNMLP (include/turbulence_nn_tbnn.hpp:35-56, turbulence_nn_mlp.hpp)
+// and forward to the C ABI of include/cfdnn_b200.h.  Errors come back as the exception types
+// the reference throws (std::invalid_argument / std::runtime_error).
+//
+// Nothing here computes: there is no CPU path.  See INTEGRATION.md for the build line.
+#pragma once
+#include <memory>
+#include <stdexcept>
+#include <string>
+#include <utility>
+#include <vector>
+
+#include "cfdnn_b200.h"
+#include "config.hpp"
+#include "fields.hpp"
+#include "mesh.hpp"
+#include "nn_core.hpp"
+#include "poisson_solver.hpp"
+#include "solver.hpp"   // VelocityBC, RANSSolver::PoissonStats
+
+namespace nncfd {
+namespace b200 {
+
+inline void check(int rc) {
+    if (rc == CFDNN_OK) return;
+    const std::string msg = cfdnn_last_error();
+    if (rc == CFDNN_ERR_INVALID) throw std::invalid_argument(msg);
+    throw std::runtime_error(msg);
+}
+
+inline cfdnn_mesh_desc mesh_desc(const Mesh& m) {
+    cfdnn_mesh_desc d{};
+    d.Nx = m.Nx; d.Ny = m.Ny; d.Nz = m.Nz; d.Ng = m.Nghost;
+    d.dx = m.dx; d.dy = m.dy; d.dz = m.dz;
+    d.y_stretched = m.is_y_stretched() ? 1 : 0;
+    if (d.y_stretched) {
+        d.dyv = m.dyv.data(); d.dyc = m.dyc.data();
+        d.yLap_aS = m.yLap_aS.data(); d.yLap_aN = m.yLap_aN.data(); d.yLap_aP = m.yLap_aP.data();
+    }
+    d.yc = m.yc.data();
+    d.y_lo = m.y_min; d.y_hi = m.y_max;
+    d.Nz_global = m.Nz; d.k_offset = 0;
+    return d;
+}
+
+inline cfdnn_poisson_cfg poisson_cfg(const PoissonConfig& c) {
+    cfdnn_poisson_cfg o;
+    cfdnn_poisson_cfg_default(&o);
+    o.tol = c.tol; o.tol_abs = c.tol_abs; o.tol_rhs = c.tol_rhs; o.tol_rel = c.tol_rel;
+    o.max_vcycles = c.max_vcycles; o.check_interval = c.check_interval;
+    o.use_l2_norm = c.use_l2_norm ? 1 : 0; o.linf_safety_factor = c.linf_safety_factor;
+    o.fixed_cycles = c.fixed_cycles; o.nu1 = c.nu1; o.nu2 = c.nu2; o.chebyshev_degree = c.chebyshev_degree;
+    return o;
+}
+
+// ------------------------------------------------------------------ MultigridPoissonSolver
+class MultigridPoissonSolverB200 {
+public:
+    explicit MultigridPoissonSolverB200(const Mesh& mesh) {
+        const cfdnn_mesh_desc d = mesh_desc(mesh);
+        check(cfdnn_mg_create(&d, &h_));
+    }
+    ~MultigridPoissonSolverB200() { cfdnn_mg_destroy(h_); }
+    MultigridPoissonSolverB200(const MultigridPoissonSolverB200&) = delete;
+    MultigridPoissonSolverB200& operator=(const MultigridPoissonSolverB200&) = delete;
+
+    void set_bc(PoissonBC x_lo, PoissonBC x_hi, PoissonBC y_lo, PoissonBC y_hi) {
+        set_bc(x_lo, x_hi, y_lo, y_hi, PoissonBC::Periodic, PoissonBC::Periodic);
+    }
+    void set_bc(PoissonBC x_lo, PoissonBC x_hi, PoissonBC y_lo, PoissonBC y_hi, PoissonBC z_lo, PoissonBC z_hi) {
+        const int bc[6] = {(int)x_lo, (int)x_hi, (int)y_lo, (int)y_hi, (int)z_lo, (int)z_hi};
+        check(cfdnn_mg_set_bc(h_, bc));
+    }
+    /// nabla^2 p = rhs; returns the number of V-cycles (reference :46)
+    int solve(const ScalarField& rhs, ScalarField& p, const PoissonConfig& cfg) {
+        const cfdnn_poisson_cfg c = poisson_cfg(cfg);
+        check(cfdnn_mg_solve(h_, rhs.data().data(), p.data().data(), &c, &st_));
+        return st_.cycles;
+    }
+    /// device twin (reference :59): here the arguments are DEVICE pointers in the ghosted cell layout
+    int solve_device(double* rhs_dev, double* p_dev, const PoissonConfig& cfg) {
+        const cfdnn_poisson_cfg c = poisson_cfg(cfg);
+        check(cfdnn_mg_solve_dev(h_, rhs_dev, p_dev, &c, &st_));
+        return st_.cycles;
+    }
+    double residual() const { return st_.residual; }
+    double residual_l2() const { return st_.residual_l2; }
+    double rhs_norm() const { return st_.b_inf; }
+    double rhs_norm_l2() const { return st_.b_l2; }
+    double initial_residual() const { return st_.r0; }
+    double initial_residual_l2() const { return st_.r0_l2; }
+    bool converged() const { return st_.converged != 0; }
+    bool used_fixed_cycles() const { return st_.fixed_cycle_mode != 0; }
+    void disable_vcycle_graph() {}
+    cfdnn_mg* handle() const { return h_; }
+
+private:
+    cfdnn_mg* h_ = nullptr;
+    cfdnn_poisson_stats st_{};
+};
+
+// ------------------------------------------------------------------ NN closures
+/// Stands in for TurbulenceNNTBNN / TurbulenceNNMLP.  Weights come from the reference's own
+/// nncfd::MLP loader (src/nn_core.cpp:501-611) so the on-disk format stays the reference's.
+class TurbulenceNNB200 {
+public:
+    TurbulenceNNB200(int kind /* CFDNN_TURB_NN_MLP | CFDNN_TURB_NN_TBNN */) : kind_(kind) {}
+    ~TurbulenceNNB200() { cfdnn_nn_destroy(h_); }
+    TurbulenceNNB200(const TurbulenceNNB200&) = delete;
+    TurbulenceNNB200& operator=(const TurbulenceNNB200&) = delete;
+
+    void load(const std::string& weights_dir, const std::string& scaling_dir) {
+        MLP mlp;
+        mlp.load_weights(weights_dir);
+        try {
+            mlp.load_scaling(scaling_dir + "/input_means.txt", scaling_dir + "/input_stds.txt");
+        } catch (...) { /* no scaling files: raw features, as the reference */ }
+        const int nl = mlp.num_layers();
+        std::vector<int> dims(nl + 1), act(nl);
+        std::vector<const double*> W(nl), b(nl);
+        for (int l = 0; l < nl; ++l) {
+            const DenseLayer& L = mlp.layer(l);
+            dims[l] = L.in_dim; dims[l + 1] = L.out_dim;
+            W[l] = L.W.data(); b[l] = L.b.data();
+            const Activation a = mlp.activations()[l];
+            if (a == Activation::Linear) act[l] = 0;
+            else if (a == Activation::Tanh) act[l] = 1;
+            else if (a == Activation::ReLU) act[l] = 2;
+            else throw std::invalid_argument("TurbulenceNNB200: activation not supported by the B200 backend");
+        }
+        cfdnn_nn_destroy(h_); h_ = nullptr;
+        check(cfdnn_nn_create(kind_, nl, dims.data(), act.data(), W.data(), b.data(),
+                              mlp.has_scaling() ? mlp.input_means_ptr() : nullptr,
+                              mlp.has_scaling() ? mlp.input_stds_ptr() : nullptr, &h_));
+        push_params();
+    }
+    void set_nu(double nu) { nu_ = nu; push_params(); }
+    void set_delta(double d) { delta_ = d; push_params(); }
+    void set_u_ref(double u) { u_ref_ = u; push_params(); }
+    void set_k_min(double k) { k_min_ = k; push_params(); }
+    void set_nu_t_max(double v) { nu_t_max_ = v; push_params(); }
+    std::string name() const { return kind_ == CFDNN_TURB_NN_TBNN ? "NNTBNN" : "NNMLP"; }
+    bool provides_reynolds_stresses() const { return kind_ == CFDNN_TURB_NN_TBNN; }
+    bool uses_transport_equations() const { return false; }
+
+    /// TurbulenceModel::update (include/turbulence_model.hpp:100-108), host fields
+    void update(const Mesh& mesh, const VectorField& velocity, const ScalarField& k, const ScalarField& omega,
+                ScalarField& nu_t, TensorField* tau_ij = nullptr) {
+        const cfdnn_mesh_desc d = mesh_desc(mesh);
+        check(cfdnn_nn_update(h_, &d, velocity.u_data().data(), velocity.v_data().data(), k.data().data(),
+                              omega.data().data(), nu_t.data().data(),
+                              tau_ij ? tau_ij->xx_data().data() : nullptr,
+                              tau_ij ? tau_ij->xy_data().data() : nullptr,
+                              tau_ij ? tau_ij->yy_data().data() : nullptr));
+    }
+    cfdnn_nn* handle() const { return h_; }
+
+private:
+    void push_params() {
+        if (h_) check(cfdnn_nn_set_params(h_, nu_, delta_, u_ref_, k_min_, nu_t_max_));
+    }
+    int kind_;
+    cfdnn_nn* h_ = nullptr;
+    double nu_ = 1e-3, delta_ = 1.0, u_ref_ = 1.0, k_min_ = 1e-10, nu_t_max_ = 1.0;
+};
+
+// ------------------------------------------------------------------ RANSSolver (hot-path subset)
+inline cfdnn_config solver_cfg(const Config& c) {
+    cfdnn_config o;
+    cfdnn_config_default(&o);
+    o.nu = c.nu; o.dt = c.dt;
+    o.time_integrator = c.time_integrator == TimeIntegrator::RK3 ? CFDNN_TI_RK3
+                      : c.time_integrator == TimeIntegrator::RK2 ? CFDNN_TI_RK2 : CFDNN_TI_EULER;
+    switch (c.convective_scheme) {
+        case ConvectiveScheme::Central: o.convective_scheme = CFDNN_CONV_CENTRAL; break;
+        case ConvectiveScheme::Skew: o.convective_scheme = CFDNN_CONV_SKEW; break;
+        default: throw std::invalid_argument("B200 backend: convective_scheme must be central or skew");
+    }
+    o.adaptive_dt = c.adaptive_dt ? 1 : 0;
+    o.CFL_max = c.CFL_max; o.CFL_xz = c.CFL_xz; o.dt_safety = c.dt_safety;
+    o.poisson_fixed_cycles = c.poisson_fixed_cycles; o.poisson_max_vcycles = c.poisson_max_vcycles;
+    o.poisson_tol_rhs = c.poisson_tol_rhs; o.poisson_tol = c.poisson_tol;
+    o.poisson_abs_tol_floor = c.poisson_abs_tol_floor; o.poisson_tol_abs = c.poisson_tol_abs;
+    o.poisson_tol_rel = c.poisson_tol_rel; o.poisson_check_interval = c.poisson_check_interval;
+    o.poisson_use_l2_norm = c.poisson_use_l2_norm ? 1 : 0; o.poisson_linf_safety = c.poisson_linf_safety;
+    o.poisson_nu1 = c.poisson_nu1; o.poisson_nu2 = c.poisson_nu2;
+    o.poisson_chebyshev_degree = c.poisson_chebyshev_degree;
+    o.turb_guard_enabled = c.turb_guard_enabled ? 1 : 0; o.turb_guard_interval = c.turb_guard_interval;
+    o.turb_model = c.turb_model == TurbulenceModelType::NNTBNN ? CFDNN_TURB_NN_TBNN
+                 : c.turb_model == TurbulenceModelType::NNMLP ? CFDNN_TURB_NN_MLP : CFDNN_TURB_NONE;
+    o.nu_t_max = c.nu_t_max;
+    return o;
+}
+
+inline int vbc_code(VelocityBC::Type t) {
+    switch (t) {
+        case VelocityBC::NoSlip: return CFDNN_VBC_NOSLIP;
+        case VelocityBC::Periodic: return CFDNN_VBC_PERIODIC;
+        case VelocityBC::Inflow: return CFDNN_VBC_INFLOW;
+        case VelocityBC::Outflow: return CFDNN_VBC_OUTFLOW;
+    }
+    return CFDNN_VBC_NOSLIP;
+}
+
+/// Same construction / stepping / accessor surface as nncfd::RANSSolver for the fractional-step
+/// hot path.  Host fields (std::vector<double>, reference layouts) are authoritative at
+/// initialize()/sync_to_gpu() and refreshed by sync_from_gpu()/sync_solution_from_gpu(); between
+/// those calls the fields live in HBM (the reference's "Model 1" contract, turbulence_model.hpp:24-26).
+class RANSSolverB200 {
+public:
+    using PoissonStats = RANSSolver::PoissonStats;
+    using PoissonSolveStatus = RANSSolver::PoissonSolveStatus;
+
+    RANSSolverB200(const Mesh& mesh, const Config& config)
+        : mesh_(&mesh), velocity_(mesh), pressure_(mesh), pressure_correction_(mesh), div_velocity_(mesh),
+          rhs_poisson_(mesh), nu_t_(mesh), k_(mesh), omega_(mesh), nu_eff_(mesh) {
+        const cfdnn_mesh_desc d = mesh_desc(mesh);
+        const cfdnn_config c = solver_cfg(config);
+        check(cfdnn_solver_create(&d, &c, &h_));
+        current_dt_ = config.dt;
+        nu_ = config.nu;
+        nu_t_max_ = config.nu_t_max;
+    }
+    ~RANSSolverB200() { cfdnn_solver_destroy(h_); }
+    RANSSolverB200(const RANSSolverB200&) = delete;
+    RANSSolverB200& operator=(const RANSSolverB200&) = delete;
+
+    void set_velocity_bc(const VelocityBC& bc) {
+        const int v[6] = {vbc_code(bc.x_lo), vbc_code(bc.x_hi), vbc_code(bc.y_lo), vbc_code(bc.y_hi),
+                          vbc_code(bc.z_lo), vbc_code(bc.z_hi)};
+        check(cfdnn_solver_set_velocity_bc(h_, v));
+    }
+    void set_body_force(double fx, double fy, double fz = 0.0) { check(cfdnn_solver_set_body_force(h_, fx, fy, fz)); }
+    void set_turbulence_model(std::unique_ptr<TurbulenceNNB200> model) {
+        turb_ = std::move(model);
+        if (turb_) {
+            turb_->set_nu(nu_);
+            turb_->set_nu_t_max(nu_t_max_);
+        }
+        check(cfdnn_solver_set_turbulence_model(h_, turb_ ? turb_->handle() : nullptr));
+    }
+    void initialize(const VectorField& initial_velocity) {
+        velocity_ = initial_velocity;
+        sync_to_gpu();
+        check(cfdnn_solver_initialize(h_));
+    }
+    void sync_to_gpu() {
+        up(CFDNN_F_U, velocity_.u_data()); up(CFDNN_F_V, velocity_.v_data());
+        if (!mesh_->is2D()) up(CFDNN_F_W, velocity_.w_data());
+        up(CFDNN_F_P, pressure_.data()); up(CFDNN_F_NUT, nu_t_.data());
+        up(CFDNN_F_K, k_.data()); up(CFDNN_F_OMEGA, omega_.data());
+    }
+    void sync_solution_from_gpu() {
+        down(CFDNN_F_U, velocity_.u_data()); down(CFDNN_F_V, velocity_.v_data());
+        if (!mesh_->is2D()) down(CFDNN_F_W, velocity_.w_data());
+        down(CFDNN_F_P, pressure_.data()); down(CFDNN_F_NUT, nu_t_.data());
+    }
+    void sync_from_gpu() {
+        sync_solution_from_gpu();
+        down(CFDNN_F_PCORR, pressure_correction_.data()); down(CFDNN_F_DIV, div_velocity_.data());
+        down(CFDNN_F_RHS, rhs_poisson_.data()); down(CFDNN_F_NUEFF, nu_eff_.data());
+        down(CFDNN_F_K, k_.data()); down(CFDNN_F_OMEGA, omega_.data());
+    }
+    /// one time step; returns max|u^{n+1} - u^n| like the reference (:208)
+    double step() {
+        double r = 0.0;
+        check(cfdnn_solver_step(h_, &r));
+        refresh_stats();
+        return r;
+    }
+    /// n steps without host round trips (app time loops)
+    double advance(int nsteps) {
+        double r = 0.0;
+        check(cfdnn_solver_run(h_, nsteps, &r));
+        refresh_stats();
+        return r;
+    }
+    double compute_adaptive_dt() const {
+        double dt = 0.0;
+        check(cfdnn_solver_compute_adaptive_dt(h_, &dt));
+        return dt;
+    }
+    double current_dt() const { return current_dt_; }
+    void set_dt(double dt) { current_dt_ = dt; check(cfdnn_solver_set_dt(h_, dt)); }
+
+    // accessors: host mirrors (call sync_*_from_gpu() first, as with the reference's GPU build)
+    const VectorField& velocity() const { return velocity_; }
+    VectorField& velocity() { return velocity_; }
+    const ScalarField& pressure() const { return pressure_; }
+    ScalarField& pressure() { return pressure_; }
+    const ScalarField& nu_t() const { return nu_t_; }
+    const ScalarField& k() const { return k_; }
+    const ScalarField& omega() const { return omega_; }
+    const ScalarField& nu_eff() const { return nu_eff_; }
+    const ScalarField& div_velocity() const { return div_velocity_; }
+    const ScalarField& rhs_poisson() const { return rhs_poisson_; }
+    const ScalarField& pressure_correction() const { return pressure_correction_; }
+    const PoissonStats& poisson_stats() const { return poisson_stats_; }
+    cfdnn_solver* handle() const { return h_; }
+
+private:
+    void up(int f, const std::vector<double>& v) { check(cfdnn_solver_upload(h_, f, v.data(), v.size())); }
+    void down(int f, std::vector<double>& v) { check(cfdnn_solver_download(h_, f, v.data(), v.size())); }
+    void refresh_stats() {
+        cfdnn_poisson_stats s{};
+        check(cfdnn_solver_poisson_stats(h_, &s));
+        poisson_stats_.cycles = s.cycles;
+        poisson_stats_.status = s.status == CFDNN_PSTAT_FIXED ? PoissonSolveStatus::FixedCycles
+                              : s.status == CFDNN_PSTAT_HIT_MAX ? PoissonSolveStatus::HitMaxCycles
+                                                                : PoissonSolveStatus::ConvergedToTol;
+        poisson_stats_.rhs_norm_l2 = s.b_l2; poisson_stats_.rhs_norm_inf = s.b_inf;
+        poisson_stats_.res_norm_l2 = s.residual_l2; poisson_stats_.res_norm_inf = s.residual;
+        poisson_stats_.res_over_rhs = s.b_l2 > 0.0 ? s.residual_l2 / s.b_l2 : 0.0;
+        cfdnn_solver_get_dt(h_, &current_dt_);
+    }
+    const Mesh* mesh_;
+    cfdnn_solver* h_ = nullptr;
+    std::unique_ptr<TurbulenceNNB200> turb_;
+    VectorField velocity_;
+    ScalarField pressure_, pressure_correction_, div_velocity_, rhs_poisson_, nu_t_, k_, omega_, nu_eff_;
+    PoissonStats poisson_stats_;
+    double current_dt_ = 0.0, nu_ = 0.0, nu_t_max_ = 1.0;
+};
+
+}  // namespace b200
+}  // namespace nncfd
