@@ -1,0 +1,43 @@
+"""The C++ drop-in binding (include/cfdnn_b200_shim.hpp): a reference RANSSolver /
+MultigridPoissonSolver and the B200 shim classes side by side in ONE C++ program
+(tests/shim/shim_parity.cpp), same Mesh / Config / VelocityBC / VectorField objects."""
+import json
+import os
+import subprocess
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+BUILD = os.path.join(ROOT, "tests", "shim", "_build")
+
+
+def _ensure_built():
+    exe = os.path.join(BUILD, "shim_parity_sim")
+    if not os.path.exists(exe):
+        if not os.path.isdir("/root/reference/include"):
+            pytest.skip("shim parity program is built where /root/reference exists")
+        subprocess.run(["bash", os.path.join(ROOT, "tests", "shim", "build.sh")], check=True)
+
+
+def _run(exe, *args):
+    r = subprocess.run([os.path.join(BUILD, exe), *map(str, args)], capture_output=True, text=True, timeout=900)
+    line = [l for l in r.stdout.splitlines() if l.startswith("{")][-1]
+    return r.returncode, json.loads(line)
+
+
+def test_shim_matches_reference_classes_on_test_double(oracle, sim):
+    _ensure_built()
+    rc, d = _run("shim_parity_sim", 16, 2)
+    assert rc == 0 and d["ok"], d
+    assert d["cycles_ref"] == d["cycles_b200"] and d["mg_cycles_ref"] == d["mg_cycles_b200"]
+    assert d["u_rel_l2"] <= 1e-10 and d["p_rel_l2"] <= 1e-10 and d["mg_p_rel_l2"] <= 1e-10
+    assert d["invalid_argument"]
+
+
+@pytest.mark.gpu
+def test_shim_matches_reference_classes_on_gpu(gpu):
+    if not os.path.exists(os.path.join(BUILD, "shim_parity_gpu")):
+        pytest.fail("tests/shim/_build/shim_parity_gpu missing (built by __graft_entry__.build())")
+    rc, d = _run("shim_parity_gpu", 32, 3)
+    assert rc == 0 and d["ok"], d
+    assert d["u_rel_l2"] <= 1e-10 and d["p_rel_l2"] <= 1e-10 and d["mg_p_rel_l2"] <= 1e-10
