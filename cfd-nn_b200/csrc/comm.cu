@@ -58,21 +58,17 @@ Nccl& nccl() {
 struct NcclComm final : Comm {
     ncclComm_t comm = nullptr;
     ~NcclComm() override { if (comm) nccl().CommDestroy(comm); }
-    void exchange_planes(double* f, size_t plane, int nz, int ng, bool lo, bool hi,
-                         cudaStream_t st) override {
+    void exchange_ptrs(const double* send_lo, size_t n_send_lo, double* recv_lo, size_t n_recv_lo,
+                       const double* send_hi, size_t n_send_hi, double* recv_hi, size_t n_recv_hi,
+                       bool lo, bool hi, cudaStream_t st) override {
         if (!lo && !hi) return;
         Nccl& n = nccl();
         const int dn = (rank + nranks - 1) % nranks, up = (rank + 1) % nranks;
-        const size_t cnt = plane * (size_t)ng;
         NCCL_OK(n.GroupStart());
-        if (lo) {
-            NCCL_OK(n.Send(f + cnt, cnt, ncclFloat64, dn, comm, st));                // first interior planes
-            NCCL_OK(n.Recv(f, cnt, ncclFloat64, dn, comm, st));                      // low ghosts
-        }
-        if (hi) {
-            NCCL_OK(n.Send(f + (size_t)nz * plane, cnt, ncclFloat64, up, comm, st)); // last interior planes
-            NCCL_OK(n.Recv(f + (size_t)(nz + ng) * plane, cnt, ncclFloat64, up, comm, st));
-        }
+        if (hi && n_send_hi) NCCL_OK(n.Send(send_hi, n_send_hi, ncclFloat64, up, comm, st));
+        if (lo && n_recv_lo) NCCL_OK(n.Recv(recv_lo, n_recv_lo, ncclFloat64, dn, comm, st));
+        if (lo && n_send_lo) NCCL_OK(n.Send(send_lo, n_send_lo, ncclFloat64, dn, comm, st));
+        if (hi && n_recv_hi) NCCL_OK(n.Recv(recv_hi, n_recv_hi, ncclFloat64, up, comm, st));
         NCCL_OK(n.GroupEnd());
     }
     void allreduce(double* d, int cnt, int op, cudaStream_t st) {
@@ -117,12 +113,13 @@ Comm* make_nccl_comm(int, int, const void*) {
 namespace {
 struct CallbackComm final : Comm {
     cfdnn_comm_callbacks_t cb;
-    void exchange_planes(double* f, size_t plane, int nz, int ng, bool lo, bool hi, cudaStream_t) override {
+    void exchange_ptrs(const double* send_lo, size_t n_send_lo, double* recv_lo, size_t n_recv_lo,
+                       const double* send_hi, size_t n_send_hi, double* recv_hi, size_t n_recv_hi,
+                       bool lo, bool hi, cudaStream_t) override {
         if (!lo && !hi) return;
         const int dn = (rank + nranks - 1) % nranks, up = (rank + 1) % nranks;
-        const size_t cnt = plane * (size_t)ng;
-        cb.sendrecv(cb.ctx, f + cnt, lo ? dn : -1, f, f + (size_t)nz * plane, hi ? up : -1,
-                    f + (size_t)(nz + ng) * plane, cnt);
+        cb.sendrecv(cb.ctx, lo ? dn : -1, send_lo, n_send_lo, recv_lo, n_recv_lo,
+                    hi ? up : -1, send_hi, n_send_hi, recv_hi, n_recv_hi);
     }
     void allreduce_sum(double* d, int n, cudaStream_t) override { cb.allreduce(cb.ctx, d, n, 0); }
     void allreduce_max(double* d, int n, cudaStream_t) override { cb.allreduce(cb.ctx, d, n, 1); }

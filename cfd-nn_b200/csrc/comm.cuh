@@ -20,8 +20,18 @@ struct Comm {
     // field: level/field array whose z-planes are `plane` doubles; interior planes live at
     // plane indices [ng, ng+nz).  Sends the first/last ng interior planes to the lower/upper
     // neighbour's opposite ghost planes (ring when the end ranks pass lo/hi = true).
-    virtual void exchange_planes(double* field, size_t plane, int nz, int ng, bool lo, bool hi,
-                                 cudaStream_t st) = 0;
+    void exchange_planes(double* field, size_t plane, int nz, int ng, bool lo, bool hi, cudaStream_t st) {
+        const size_t cnt = plane * (size_t)ng;
+        exchange_ptrs(field + cnt, cnt, field, cnt, field + (size_t)nz * plane, cnt,
+                      field + (size_t)(nz + ng) * plane, cnt, lo, hi, st);
+    }
+    // general form: send `n_send_lo` doubles to the lower neighbour and receive `n_recv_lo` from it
+    // (if lo), same with the upper neighbour (if hi).  A count of 0 skips that transfer; the two
+    // ends of a link must agree on the counts.  Posting order is send-up, recv-lo, send-lo,
+    // recv-up so that the pairs also match when both neighbours are the same rank (P = 2 ring).
+    virtual void exchange_ptrs(const double* send_lo, size_t n_send_lo, double* recv_lo, size_t n_recv_lo,
+                               const double* send_hi, size_t n_send_hi, double* recv_hi, size_t n_recv_hi,
+                               bool lo, bool hi, cudaStream_t st) = 0;
     virtual void allreduce_sum(double* d, int n, cudaStream_t st) = 0;
     virtual void allreduce_max(double* d, int n, cudaStream_t st) = 0;
     virtual void allreduce_min(double* d, int n, cudaStream_t st) = 0;
@@ -37,8 +47,9 @@ void nccl_unique_id(void* id128);
 struct cfdnn_comm_callbacks_t {
     void* ctx;
     // exchange with two peers at once; a peer < 0 means "no transfer on that side"
-    void (*sendrecv)(void* ctx, const double* send_lo, int lo_peer, double* recv_lo,
-                     const double* send_hi, int hi_peer, double* recv_hi, size_t count);
+    void (*sendrecv)(void* ctx, int lo_peer, const double* send_lo, size_t n_send_lo, double* recv_lo,
+                     size_t n_recv_lo, int hi_peer, const double* send_hi, size_t n_send_hi, double* recv_hi,
+                     size_t n_recv_hi);
     void (*allreduce)(void* ctx, double* d, int n, int op /*0 sum 1 max 2 min*/);
     void (*allgather)(void* ctx, double* base, size_t count);
 };

@@ -50,11 +50,18 @@ Multigrid::Multigrid(const cfdnn_mesh_desc& m) : mesh_(m) {
     };
     add(Nx, Ny, Nz, NzGlob, dx, dy, dz);
     constexpr int MIN_COARSE = 8;
+    // z-slab runs: a coarse level is REPLICATED on every rank (the slabs are all-gathered at the
+    // restriction into it, restrict_to) once it is small or its slab would get thinner than 2
+    // planes — no halo exchanges below that level, every rank solves it redundantly.
+    constexpr long long REPLICATE_CELLS = 64LL * 64 * 64;
+    bool replicated = (Nz == NzGlob);
     while (Nx > MIN_COARSE && Ny > MIN_COARSE && NzGlob > MIN_COARSE) {
         if ((Nx | Ny | Nz | NzGlob) & 1)
             throw std::invalid_argument("Multigrid: grid sizes must stay even while coarsening");
         Nx /= 2; Ny /= 2; Nz /= 2; NzGlob /= 2;
         dx *= 2.0; dy *= 2.0; dz *= 2.0;
+        if (!replicated && ((long long)Nx * Ny * NzGlob <= REPLICATE_CELLS || Nz < 2 || (Nz & 1))) replicated = true;
+        if (replicated) Nz = NzGlob;
         add(Nx, Ny, Nz, NzGlob, dx, dy, dz);
     }
     size_t maxblocks = 0;

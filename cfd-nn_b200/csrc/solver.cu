@@ -124,11 +124,24 @@ void Solver::set_velocity_bc(const int bc[6]) {
     int pbc[6];
     for (int d = 0; d < 6; ++d) pbc[d] = bc[d] == CFDNN_VBC_PERIODIC ? CFDNN_PBC_PERIODIC : CFDNN_PBC_NEUMANN;
     mg_->set_bc(pbc);
+    update_links();
 }
 
 void Solver::comm_init(Comm* c) {
     comm_ = c;
     mg_->set_comm(c);
+    update_links();
+}
+bool Solver::multi() const { return comm_ && comm_->nranks > 1; }
+void Solver::update_links() {
+    lo_int_ = hi_int_ = lo_wrap_ = hi_wrap_ = false;
+    if (!multi()) return;
+    const bool pz = vbc_[4] == CFDNN_VBC_PERIODIC && vbc_[5] == CFDNN_VBC_PERIODIC;
+    lo_int_ = comm_->rank > 0;
+    hi_int_ = comm_->rank < comm_->nranks - 1;
+    lo_wrap_ = pz && comm_->rank == 0;
+    hi_wrap_ = pz && comm_->rank == comm_->nranks - 1;
+    if (seam_scratch_.n != (size_t)g_.wp) seam_scratch_.alloc((size_t)g_.wp);
 }
 
 // ---------------------------------------------------------------- field transfer
@@ -184,14 +197,16 @@ void Solver::apply_velocity_bc() {
         throw Error(CFDNN_ERR_RUNTIME, "Unsupported velocity BC type for y_lo (only Periodic and NoSlip are implemented)");
     if (yhi != CFDNN_VBC_PERIODIC && yhi != CFDNN_VBC_NOSLIP)
         throw Error(CFDNN_ERR_RUNTIME, "Unsupported velocity BC type for y_hi (only Periodic and NoSlip are implemented)");
-    const bool z_local = !(comm_ && comm_->nranks > 1);
-    if (z_local) {
-        if (zlo != CFDNN_VBC_PERIODIC && zlo != CFDNN_VBC_NOSLIP)
-            throw Error(CFDNN_ERR_RUNTIME, "Unsupported velocity BC type for z_lo (only Periodic and NoSlip are implemented)");
-        if (zhi != CFDNN_VBC_PERIODIC && zhi != CFDNN_VBC_NOSLIP)
-            throw Error(CFDNN_ERR_RUNTIME, "Unsupported velocity BC type for z_hi (only Periodic and NoSlip are implemented)");
-    }
-    BcFlags bc{xlo, xhi, ylo, yhi, zlo, zhi};
+    // z sides that are slab links carry no physical BC here: the halo exchange below is their z pass
+    const bool lo_link = lo_int_ || lo_wrap_, hi_link = hi_int_ || hi_wrap_;
+    if (!lo_link && zlo != CFDNN_VBC_PERIODIC && zlo != CFDNN_VBC_NOSLIP)
+        throw Error(CFDNN_ERR_RUNTIME, "Unsupported velocity BC type for z_lo (only Periodic and NoSlip are implemented)");
+    if (!hi_link && zhi != CFDNN_VBC_PERIODIC && zhi != CFDNN_VBC_NOSLIP)
+        throw Error(CFDNN_ERR_RUNTIME, "Unsupported velocity BC type for z_hi (only Periodic and NoSlip are implemented)");
+    if (multi() && ((zlo == CFDNN_VBC_PERIODIC) != (zhi == CFDNN_VBC_PERIODIC)))
+        throw std::invalid_argument("Periodic BC in z requires both z_lo and z_hi to be Periodic");
+    BcFlags bc{xlo, xhi, ylo, yhi, lo_link || (multi() && zlo == CFDNN_VBC_PERIODIC) ? -1 : zlo,
+               hi_link || (multi() && zhi == CFDNN_VBC_PERIODIC) ? -1 : zhi};
     const int Pz = Nz + 2 * Ng;   // all planes of u, v
     auto pass = [&](int id, int na, int nb) {
         dim3 gr((na + kB.x - 1) / kB.x, (nb + kB.y - 1) / kB.y, 1);
@@ -205,11 +220,10 @@ void Solver::apply_velocity_bc() {
     if (ylo == CFDNN_VBC_PERIODIC && yhi == CFDNN_VBC_PERIODIC) pass(BC_V_Y2, Nx + 2 * Ng, Pz);
     if (xhi == CFDNN_VBC_OUTFLOW) pass(BC_OUTFLOW_UV, Ny + 1 + 2 * Ng, Pz);
     if (xlo == CFDNN_VBC_INFLOW) pass(BC_INFLOW_UV, Ny + 1 + 2 * Ng, Pz);
-    if (z_local) {
-        pass(BC_U_Z, Nx + 1 + 2 * Ng, Ny + 2 * Ng);
-        pass(BC_V_Z, Nx + 2 * Ng, Ny + 1 + 2 * Ng);
-        pass(BC_W_Z, Nx + 2 * Ng, Ny + 2 * Ng);
-    }
+    pass(BC_U_Z, Nx + 1 + 2 * Ng, Ny + 2 * Ng);
+    pass(BC_V_Z, Nx + 2 * Ng, Ny + 1 + 2 * Ng);
+    pass(BC_W_Z, Nx + 2 * Ng, Ny + 2 * Ng);
+    if (multi()) halo_vel(vel_, /*bc_site=*/true);
     const int Pw = Nz + 1 + 2 * Ng;
     pass(BC_W_X, Ny + 2 * Ng, Pw);
     if (xlo == CFDNN_VBC_INFLOW) pass(BC_W_X_INFLOW, Ny + 2 * Ng, Pw);
@@ -233,13 +247,15 @@ void Solver::advance(const Vel& in, const Vel& out, double dt, bool seam_average
     CFDNN_LAUNCH(k_advance, gr, kB, 0, st_, g_, in, out, conv_, diff_, dt, fx_, fy_, fz_);
     const int px = vbc_[0] == CFDNN_VBC_PERIODIC && vbc_[1] == CFDNN_VBC_PERIODIC;
     const int py = vbc_[2] == CFDNN_VBC_PERIODIC && vbc_[3] == CFDNN_VBC_PERIODIC;
-    const int pz = vbc_[4] == CFDNN_VBC_PERIODIC && vbc_[5] == CFDNN_VBC_PERIODIC;
+    const int pzg = vbc_[4] == CFDNN_VBC_PERIODIC && vbc_[5] == CFDNN_VBC_PERIODIC;
+    const int pz = pzg && !multi();
     if (px || py || pz) {
         const int na = std::max(g_.Nx, g_.Ny), nb = std::max(g_.Ny, g_.Nz);
         dim3 gs((na + kB.x - 1) / kB.x, (nb + kB.y - 1) / kB.y, 3);
         if (seam_average) CFDNN_LAUNCH((k_seam<true>), gs, kB, 0, st_, g_, out, px, py, pz);
         else CFDNN_LAUNCH((k_seam<false>), gs, kB, 0, st_, g_, out, px, py, pz);
     }
+    if (pzg && multi()) seam_z(out, seam_average);
 }
 void Solver::blend(const Vel& a, const Vel& b, const Vel& c, double a1, double a2) {
     const dim3 gr = grid3(g_.Nx + 1, g_.Ny + 1, g_.Nz + 1);
@@ -268,12 +284,14 @@ void Solver::correct_velocity() {
     CFDNN_LAUNCH(k_correct, gr, kB, 0, st_, g_, star_, vel_, pcorr_, p_, dt_);
     const int px = vbc_[0] == CFDNN_VBC_PERIODIC && vbc_[1] == CFDNN_VBC_PERIODIC;
     const int py = vbc_[2] == CFDNN_VBC_PERIODIC && vbc_[3] == CFDNN_VBC_PERIODIC;
-    const int pz = vbc_[4] == CFDNN_VBC_PERIODIC && vbc_[5] == CFDNN_VBC_PERIODIC;
+    const int pzg = vbc_[4] == CFDNN_VBC_PERIODIC && vbc_[5] == CFDNN_VBC_PERIODIC;
+    const int pz = pzg && !multi();
     if (px || py || pz) {
         const int na = std::max(g_.Nx, g_.Ny), nb = std::max(g_.Ny, g_.Nz);
         dim3 gs((na + kB.x - 1) / kB.x, (nb + kB.y - 1) / kB.y, 3);
         CFDNN_LAUNCH((k_seam<true>), gs, kB, 0, st_, g_, vel_, px, py, pz);
     }
+    if (pzg && multi()) seam_z(vel_, true);
 }
 
 int Solver::poisson_solve(const cfdnn_poisson_cfg& pc) {
@@ -282,12 +300,49 @@ int Solver::poisson_solve(const cfdnn_poisson_cfg& pc) {
     return cyc;
 }
 
-void Solver::halo_vel(const Vel&) {}
-void Solver::halo_cell(double*) {}
+// ---------------------------------------------------------------- z-slab exchanges
+void Solver::halo_vel(const Vel& v, bool bc_site) {
+    if (!multi()) return;
+    const bool lo = lo_int_ || (bc_site && lo_wrap_), hi = hi_int_ || (bc_site && hi_wrap_);
+    if (!lo && !hi) return;
+    const int Ng = g_.Ng, Nz = g_.Nz;
+    comm_->exchange_planes(v.u, (size_t)g_.up, Nz, Ng, lo, hi, st_);
+    comm_->exchange_planes(v.v, (size_t)g_.vp, Nz, Ng, lo, hi, st_);
+    // w: my faces Ng..Ng+Nz-1 are owned, face Ng+Nz duplicates the upper neighbour's face Ng.
+    // down: faces Ng, Ng+1 -> the lower rank's Ng+Nz (far <- near, BC_W_Z) and Ng+Nz+1 ghost;
+    // up  : face Ng+Nz-1   -> the upper rank's Ng-1 ghost.
+    const size_t wp = (size_t)g_.wp;
+    comm_->exchange_ptrs(v.w + (size_t)Ng * wp, 2 * wp, v.w + (size_t)(Ng - 1) * wp, wp,
+                         v.w + (size_t)(Ng + Nz - 1) * wp, wp, v.w + (size_t)(Ng + Nz) * wp, 2 * wp, lo, hi, st_);
+}
+void Solver::halo_cell(double* c, bool bc_site) {
+    if (!multi()) return;
+    const bool lo = lo_int_ || (bc_site && lo_wrap_), hi = hi_int_ || (bc_site && hi_wrap_);
+    if (!lo && !hi) return;
+    comm_->exchange_planes(c, (size_t)g_.cp, g_.Nz, g_.Ng, lo, hi, st_);
+}
+// Periodic seam of w between the end ranks: the duplicated faces are rank 0's Ng ("near") and the
+// last rank's Ng+Nz ("far").  average = false: far <- near (euler_substep, src/solver_time.cpp:518-559);
+// true: both <- 0.5*(near + far) (correct_velocity src/solver_operators.cpp:1469-1485, Euler predictor).
+void Solver::seam_z(const Vel& v, bool average) {
+    if (!lo_wrap_ && !hi_wrap_) return;
+    const size_t wp = (size_t)g_.wp;
+    double* near_face = v.w + (size_t)g_.Ng * wp;
+    double* far_face = v.w + (size_t)(g_.Ng + g_.Nz) * wp;
+    if (!average) {
+        comm_->exchange_ptrs(near_face, wp, nullptr, 0, nullptr, 0, far_face, wp, lo_wrap_, hi_wrap_, st_);
+        return;
+    }
+    comm_->exchange_ptrs(near_face, wp, seam_scratch_.p, wp, far_face, wp, seam_scratch_.p, wp, lo_wrap_, hi_wrap_, st_);
+    const int blocks = (int)((wp + 255) / 256);
+    if (lo_wrap_) CFDNN_LAUNCH(k_avg_plane, blocks, 256, 0, st_, near_face, near_face, seam_scratch_.p, wp);
+    if (hi_wrap_) CFDNN_LAUNCH(k_avg_plane, blocks, 256, 0, st_, far_face, seam_scratch_.p, far_face, wp);
+}
 
 // ---------------------------------------------------------------- integrators
 // euler_substep (src/solver_time.cpp:269-661): operators always read velocity_
 void Solver::euler_substep(const Vel& in, const Vel& out, double dt) {
+    halo_vel(vel_, /*bc_site=*/false);
     compute_convective_term();
     compute_diffusive_term();
     advance(in, out, dt, /*seam_average=*/false);
@@ -335,6 +390,7 @@ void Solver::ssprk2_step(double dt) {              // :1213-1301
 
 // Euler path of step() (src/solver.cpp:1505-2507)
 void Solver::euler_step() {
+    halo_vel(vel_, /*bc_site=*/false);
     compute_convective_term();
     compute_diffusive_term();
     advance(vel_, star_, dt_, /*seam_average=*/true);          // predictor :1558-1722
@@ -386,6 +442,7 @@ void Solver::euler_step() {
 void Solver::build_nu_eff() {
     const dim3 gr = grid3(g_.Nx + 2 * g_.Ng, g_.Ny + 2 * g_.Ng, g_.Nz + 2 * g_.Ng);
     CFDNN_LAUNCH(k_nu_eff, gr, kB, 0, st_, g_, cfg_.nu, nut_, nn_ ? 1 : 0, nueff_);
+    if (nn_) halo_cell(nueff_, /*bc_site=*/false);
 }
 
 void Solver::update_turbulence() {

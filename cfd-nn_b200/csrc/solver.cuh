@@ -117,8 +117,18 @@ private:
     void update_turbulence();
     void build_nu_eff();
     void step_device(bool want_residual);
-    void halo_vel(const Vel& v);
-    void halo_cell(double* c);
+    // ---- z-slab links (multi-GPU): internal interfaces and the periodic wrap between the end ranks
+    bool multi() const;
+    bool lo_int_ = false, hi_int_ = false, lo_wrap_ = false, hi_wrap_ = false;
+    DevBuf<double> seam_scratch_;
+    void update_links();
+    // bc_site = true : at apply_velocity_bc call sites (all links, incl. the periodic wrap: this is
+    //                  the z pass of the reference's BC routine, ghosts go stale like the reference's)
+    // bc_site = false: refresh of internal interfaces before a stencil reads across them (an
+    //                  interior plane of the single-domain run is never stale)
+    void halo_vel(const Vel& v, bool bc_site);
+    void halo_cell(double* c, bool bc_site);
+    void seam_z(const Vel& v, bool average);   // periodic seam of w across the end ranks
     void check_nan(int step);
     double max_change_host();
 };

@@ -238,6 +238,13 @@ k_seam(Geom g, Vel vel, int px, int py, int pz) {
     }
 }
 
+// out = 0.5 * (a + b) over one plane (periodic w seam across the end ranks of a slab run)
+static __global__ void __launch_bounds__(256)
+k_avg_plane(double* out, const double* a, const double* b, size_t n) {
+    const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t < n) out[t] = 0.5 * (a[t] + b[t]);
+}
+
 // ------------------------------------------------------------------ divergence / RHS / correction
 // divergence_cell_kernel_staggered_3d (include/solver_kernels.hpp:568-591); stretched y divides
 // by dyv[j] (src/solver_operators.cpp:1157-1175).  Also emits per-block partial sums of div for

@@ -1,0 +1,103 @@
+"""world_size-2 `gloo` run of the z-slab path on the CPU test double: the distributed V-cycle,
+the velocity / pressure halo exchanges and the fused scalar all-reduces must reproduce the
+SINGLE-DOMAIN result (oracle = the unmodified reference CPU build)."""
+import os
+import socket
+import subprocess
+import sys
+import tempfile
+
+import numpy as np
+import pytest
+
+import cases
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+WORKER = os.path.join(ROOT, "tests", "slab_worker.py")
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _run_slabs(world, N, bc, ti, nsteps, fixed, td, gpu=False):
+    port = _free_port()
+    procs = [subprocess.Popen([sys.executable, WORKER, str(r), str(world), str(port), td, str(N[0]), str(N[1]), str(N[2]),
+                               bc, ti, str(nsteps), str(fixed)] + (["gpu"] if gpu else []),
+                              stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+             for r in range(world)]
+    outs = [p.communicate(timeout=1500)[0] for p in procs]
+    for p, o in zip(procs, outs):
+        assert p.returncode == 0, o[-3000:]
+    return [np.load(os.path.join(td, f"slab{r}.npz")) for r in range(world)]
+
+
+def _assemble(slabs, name, Nz):
+    """Global ghost-inclusive array from the slabs' owned planes (ghost z planes from the end ranks)."""
+    parts = []
+    for r, s in enumerate(slabs):
+        a = s[name]
+        lo = 0 if r == 0 else 1
+        hi = a.shape[0] if r == len(slabs) - 1 else 1 + Nz      # owned planes: 1..Nz (w: faces 1..Nz)
+        parts.append(a[lo:hi])
+    return np.concatenate(parts, axis=0)
+
+
+@pytest.mark.parametrize("bc,ti,fixed", [("PPPPPP", "rk3", 4), ("PPWWPP", "rk3", 0), ("PPWWWW", "euler", 3)],
+                         ids=["tgv_periodic_rk3", "channel_rk3_converge", "duct_z_walls_euler"])
+def test_two_slabs_match_single_domain(R, oracle, sim, bc, ti, fixed):
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import slab_worker
+    N = (16, 16, 32)
+    nsteps = 2
+    with tempfile.TemporaryDirectory() as td:
+        slabs = _run_slabs(2, N, bc, ti, nsteps, fixed, td)
+        u, v, w = slab_worker.global_init(*N, bc)
+        pre = os.path.join(td, "in")
+        u.tofile(pre + "_u.f64"); v.tofile(pre + "_v.f64"); w.tofile(pre + "_w.f64")
+        force = (0.5, 0, 0) if "W" in bc else (0, 0, 0)
+        extra = dict(tol_rhs=1e-8, maxv=50) if fixed == 0 else {}
+        meta = R.run_ref("step", Nx=N[0], Ny=N[1], Nz=N[2], bc=bc, ti=ti, scheme="skew", fixed=fixed, nsteps=nsteps,
+                         dt=0.01, nu=0.01, init="file:" + pre, call_initialize=1, fx=force[0], fy=force[1], fz=force[2],
+                         out=os.path.join(td, "ref"), **extra)
+        ref = R.load_state(os.path.join(td, "ref_final"), *N)
+    Nz = N[2] // 2
+    got = {n: _assemble(slabs, n, Nz) for n in ("u", "v", "w", "p", "pcorr", "div", "rhs")}
+    for n in got:
+        assert got[n].shape == ref[n].shape, (n, got[n].shape, ref[n].shape)
+    cases.compare_states(got, ref, 1e-10, f"2 slabs {bc} {ti}")
+    assert list(slabs[0]["cycles"]) == list(slabs[1]["cycles"])
+    if meta["cycles"]:
+        assert list(slabs[0]["cycles"]) == meta["cycles"]
+    assert slabs[0]["residuals"] == pytest.approx(meta["residuals"], rel=1e-9)
+    assert float(slabs[0]["adaptive_dt"]) == float(slabs[1]["adaptive_dt"])
+    assert slabs[0]["stats"][0] > 0 and slabs[0]["stats"][1] > 0     # halos and all-reduces really ran
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_gpu_slabs_match_single_domain(R, oracle, gpu, world):
+    """P B200s over NCCL vs the single-domain oracle (skipped when the box has fewer GPUs)."""
+    if gpu.lib.cfdnn_device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import slab_worker
+    N = (32, 32, 64)
+    bc, ti, fixed, nsteps = "PPWWPP", "rk3", 0, 2
+    with tempfile.TemporaryDirectory() as td:
+        slabs = _run_slabs(world, N, bc, ti, nsteps, fixed, td, gpu=True)
+        u, v, w = slab_worker.global_init(*N, bc)
+        pre = os.path.join(td, "in")
+        u.tofile(pre + "_u.f64"); v.tofile(pre + "_v.f64"); w.tofile(pre + "_w.f64")
+        meta = R.run_ref("step", Nx=N[0], Ny=N[1], Nz=N[2], bc=bc, ti=ti, scheme="skew", fixed=fixed, nsteps=nsteps,
+                         dt=0.01, nu=0.01, init="file:" + pre, call_initialize=1, fx=0.5, fy=0, fz=0,
+                         out=os.path.join(td, "ref"), tol_rhs=1e-8, maxv=50)
+        ref = R.load_state(os.path.join(td, "ref_final"), *N)
+    Nz = N[2] // world
+    got = {n: _assemble(slabs, n, Nz) for n in ("u", "v", "w", "p", "pcorr", "div", "rhs")}
+    cases.compare_states(got, ref, 1e-10, f"{world} GPU slabs")
+    assert list(slabs[0]["cycles"]) == meta["cycles"]
