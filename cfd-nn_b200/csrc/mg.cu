@@ -31,6 +31,7 @@ Multigrid::Multigrid(const cfdnn_mesh_desc& m) : mesh_(m) {
     auto add = [&](int nx, int ny, int nz, int nzg, double hx, double hy, double hz) {
         auto L = std::make_unique<Level>();
         L->g.Nx = nx; L->g.Ny = ny; L->g.Nz = nz;
+        L->g.Hz = (nz != nzg) ? 2 : 1;    // slab levels: room for the 2-deep halo of the blocked smoother
         L->g.Px = (nx + 15) / 16 * 16;
         L->g.plane = (long long)L->g.Px * ny;
         L->dx = hx; L->dy = hy; L->dz = hz; L->NzGlobal = nzg;
@@ -43,7 +44,7 @@ Multigrid::Multigrid(const cfdnn_mesh_desc& m) : mesh_(m) {
         L->g.inv_dz2_2 = 2.0 / dz2;
         L->g.nonuniform_y = 0; L->g.joff = 0;
         L->g.aS = L->g.aN = L->g.aP = nullptr;
-        L->size = (size_t)(nz + 2) * L->g.plane;
+        L->size = (size_t)(nz + 2 * L->g.Hz) * L->g.plane;
         L->u.alloc(L->size); L->f.alloc(L->size); L->r.alloc(L->size); L->tmp.alloc(L->size);
         L->lambda_max = std::max(1.8, (1.0 + 1.0) * 1.10);               // :283-294 uniform
         levels_.push_back(std::move(L));
@@ -118,12 +119,17 @@ bool Multigrid::has_nullspace() const {   // :3393-3402
     return true;
 }
 
-void Multigrid::halo(int level, double* field) {
+void Multigrid::halo(int level, double* field, int depth) {
     if (!comm_ || comm_->nranks <= 1) return;
     Level& L = *levels_[level];
     if (L.g.Nz == L.NzGlobal) return;   // agglomerated level: whole domain on every rank
-    comm_->exchange_planes(field, (size_t)L.g.plane, L.g.Nz, 1,
-                           L.g.bc[4] == CFDNN_PBC_HALO, L.g.bc[5] == CFDNN_PBC_HALO, st_);
+    const size_t pl = (size_t)L.g.plane;
+    const size_t cnt = pl * (size_t)depth;
+    const int Hz = L.g.Hz, Nz = L.g.Nz;
+    // interior planes live at [Hz, Hz+Nz); the `depth` planes next to each interface travel
+    comm_->exchange_ptrs(field + (size_t)Hz * pl, cnt, field + (size_t)(Hz - depth) * pl, cnt,
+                         field + (size_t)(Hz + Nz - depth) * pl, cnt, field + (size_t)(Hz + Nz) * pl, cnt,
+                         L.g.bc[4] == CFDNN_PBC_HALO, L.g.bc[5] == CFDNN_PBC_HALO, st_);
 }
 
 // ---------------------------------------------------------------- kernels' launchers
@@ -174,7 +180,9 @@ bool Multigrid::sweeps_tb(int level, const double* in, double* out, const double
     const LevelGeom& g = L.g;
     if (tb_max_ <= 0 || n > tb_max_) return false;
     if (g.nonuniform_y || (g.Nx & 1) || g.Nx < 16 || g.Ny < 8 || g.Nz < 4) return false;
-    if (g.bc[4] == CFDNN_PBC_HALO || g.bc[5] == CFDNN_PBC_HALO) return false;
+    const bool slab = g.bc[4] == CFDNN_PBC_HALO || g.bc[5] == CFDNN_PBC_HALO;
+    if (slab && (g.Hz < n || g.Nz < n)) return false;
+    if (slab) halo(level, const_cast<double*>(in), n);     // n-deep halo: one exchange per pass
     const bool big = g.Nx >= 128 && g.Ny >= 56 && g.Nz >= 32;
     if (big) {
         if (n == 2) tb_launch<2, TB_BX_BIG, TB_BY_BIG>(g, in, L.f.p, out, w, st_);
@@ -289,7 +297,7 @@ void Multigrid::restrict_to(int fine) {
     CFDNN_LAUNCH_COOP(k_restrict, g, kBlk, 0, st_, F.g, C.g, F.r.p, C.f.p, kc_off,
                  (nullsp && !agglomerate) ? partial_.p : nullptr);
     if (agglomerate)
-        comm_->allgather_planes(C.f.p + C.g.plane, (size_t)C.g.plane * nzc_local, st_);
+        comm_->allgather_planes(C.f.p + (size_t)C.g.Hz * C.g.plane, (size_t)C.g.plane * nzc_local, st_);
     if (nullsp) {   // make_rhs_mean_free(level+1) :3274-3276
         const bool dist = comm_ && comm_->nranks > 1 && C.g.Nz != C.NzGlobal;
         if (agglomerate) {
@@ -305,6 +313,7 @@ void Multigrid::restrict_to(int fine) {
             CFDNN_LAUNCH(k_sub_scalar, gs, kBlk, 0, st_, C.g, C.f.p, scalars_.p + 9);
         }
     }
+    halo(fine + 1, C.f.p, C.g.Hz);   // slab coarse level: deep halo of its (now final) right-hand side
 }
 
 void Multigrid::prolong_from(int coarse) {
@@ -386,6 +395,7 @@ int Multigrid::solve_dev(const double* rhs, double* p, const cfdnn_poisson_cfg& 
     {
         dim3 g = grid2(L0.g.Nx, L0.g.Ny, L0.g.Nz, kBlk);
         CFDNN_LAUNCH(k_copy_in, g, kBlk, 0, st_, L0.g, Ng, rhs, p, L0.f.p, L0.u.p);
+        halo(0, L0.f.p, L0.g.Hz);   // slab runs: f is constant during the solve, its deep halo travels once
     }
     int cycles_used = 0;
     stats = cfdnn_poisson_stats{};

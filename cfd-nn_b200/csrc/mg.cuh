@@ -7,10 +7,11 @@
 // HBM layout of one level array (u, f, r, tmp):
 //   * NO x/y ghost cells: ghost values are a pure function of interior values
 //     (apply_bc, :307-554), so every stencil resolves them on the fly from the BC type.
-//   * one halo plane on each z side (k = -1 and k = Nz) — used only when the z side is a
-//     slab interface (BC code CFDNN_PBC_HALO); physical z BCs are resolved on the fly too.
+//   * Hz halo planes on each z side (k = -Hz..-1 and k = Nz..Nz+Hz-1) — used only when the z side
+//     is a slab interface (BC code CFDNN_PBC_HALO; Hz = 2 there so that two blocked sweeps need one
+//     exchange); physical z BCs are resolved on the fly too.
 //   * row pitch Px = Nx rounded up to 16 doubles (128 B) so rows start on a line boundary.
-//   index(i,j,k) = (k+1)*Px*Ny + j*Px + i
+//   index(i,j,k) = (k+Hz)*Px*Ny + j*Px + i
 #pragma once
 #include "common.cuh"
 #include <vector>
@@ -23,6 +24,7 @@ enum { CFDNN_PBC_HALO = 3 };  // z side is a slab interface: read the halo plane
 struct LevelGeom {            // by-value kernel argument
     int Nx, Ny, Nz;           // interior size of the local slab
     int Px;                   // row pitch
+    int Hz;                   // halo planes on each z side (1; T of the blocked smoother on slab levels)
     long long plane;          // Px * Ny
     int bc[6];                // xlo,xhi,ylo,yhi,zlo,zhi
     Div dx2, dy2, dz2, coeff; // dx^2 ..., coeff = 2/dx2 + 2/dy2 + 2/dz2
@@ -36,7 +38,7 @@ struct Level {
     LevelGeom g{};
     double dx, dy, dz;
     int NzGlobal;
-    size_t size = 0;          // (Nz+2)*plane
+    size_t size = 0;          // (Nz+2*Hz)*plane
     DevBuf<double> u, f, r, tmp;
     double lambda_max = 2.2;
     long long cells() const { return (long long)g.Nx * g.Ny * g.Nz; }
@@ -107,7 +109,7 @@ private:
     void restrict_to(int fine);
     void prolong_from(int coarse);
     void mean_free(int level, double* field);
-    void halo(int level, double* field);   // slab interface exchange (no-op single GPU)
+    void halo(int level, double* field, int depth = 1);   // slab interface exchange of `depth` planes (no-op single GPU)
     void invalidate_graph();
 };
 

@@ -42,7 +42,7 @@ __device__ __forceinline__ int rbc_map(int i, int N, int lo, int hi, bool& ok) {
 }
 
 __device__ __forceinline__ size_t lidx(const LevelGeom& g, int i, int j, int k) {
-    return (size_t)(k + 1) * (size_t)g.plane + (size_t)j * g.Px + i;
+    return (size_t)(k + g.Hz) * (size_t)g.plane + (size_t)j * g.Px + i;
 }
 
 // ------------------------------------------------------------------ smoother sweep
@@ -76,13 +76,13 @@ k_sweep(LevelGeom g, const double* __restrict__ u, const double* __restrict__ f,
     const int kend = min(k0 + KZ, g.Nz);
     double s = 1.0;
     int kb = bc_map(k0 - 1, g.Nz, g.bc[4], g.bc[5], s);
-    double ub = s * u[(size_t)(kb + 1) * g.plane + rc + i];
-    double uc = u[(size_t)(k0 + 1) * g.plane + rc + i];
+    double ub = s * u[(size_t)(kb + g.Hz) * g.plane + rc + i];
+    double uc = u[(size_t)(k0 + g.Hz) * g.plane + rc + i];
     for (int k = k0; k < kend; ++k) {
-        const size_t pc = (size_t)(k + 1) * g.plane;
+        const size_t pc = (size_t)(k + g.Hz) * g.plane;
         double sf = 1.0;
         const int kf = bc_map(k + 1, g.Nz, g.bc[4], g.bc[5], sf);
-        const double uf = sf * u[(size_t)(kf + 1) * g.plane + rc + i];
+        const double uf = sf * u[(size_t)(kf + g.Hz) * g.plane + rc + i];
         const double uE = sxp * u[pc + rc + ip];
         const double uW = sxm * u[pc + rc + im];
         const double uN = syp * u[pc + rp + i];
@@ -127,13 +127,13 @@ k_residual(LevelGeom g, const double* __restrict__ u, const double* __restrict__
         const int kend = min(k0 + KZ, g.Nz);
         double s = 1.0;
         int kb = bc_map(k0 - 1, g.Nz, g.bc[4], g.bc[5], s);
-        double ub = s * u[(size_t)(kb + 1) * g.plane + rc + i];
-        double uc = u[(size_t)(k0 + 1) * g.plane + rc + i];
+        double ub = s * u[(size_t)(kb + g.Hz) * g.plane + rc + i];
+        double uc = u[(size_t)(k0 + g.Hz) * g.plane + rc + i];
         for (int k = k0; k < kend; ++k) {
-            const size_t pc = (size_t)(k + 1) * g.plane;
+            const size_t pc = (size_t)(k + g.Hz) * g.plane;
             double sf = 1.0;
             const int kf = bc_map(k + 1, g.Nz, g.bc[4], g.bc[5], sf);
-            const double uf = sf * u[(size_t)(kf + 1) * g.plane + rc + i];
+            const double uf = sf * u[(size_t)(kf + g.Hz) * g.plane + rc + i];
             const double uE = sxp * u[pc + rc + ip];
             const double uW = sxm * u[pc + rc + im];
             const double uN = syp * u[pc + rp + i];

@@ -142,14 +142,17 @@ k_sweep_tb(LevelGeom g, const double* __restrict__ u, const double* __restrict__
         for (int p = 0; p < 4; ++p) fr[k][p] = 0.0;
 
     // z range of input planes: virtual planes wrap when periodic, are clipped otherwise
-    const int zi_first = perz ? z0 - T : max(z0 - T, 0);
+    // a z side is "open" when planes beyond it exist: periodic wrap, or the halo planes of a slab
+    // interface (exchanged T deep before the launch); a closed side is a physical face.
+    const bool lo_open = perz || g.bc[4] == CFDNN_PBC_HALO, hi_open = perz || g.bc[5] == CFDNN_PBC_HALO;
+    const int zi_first = lo_open ? z0 - T : max(z0 - T, 0);
     const int zi_last = z1 - 1 + T;
     const unsigned uplane = (unsigned)g.plane;
     auto load_plane = [&](const double* __restrict__ a, int z, double* dst) {
         int zw = z;                                        // z in [-T, Nz+T): one conditional wrap
         if (perz) zw = zw < 0 ? zw + g.Nz : (zw >= g.Nz ? zw - g.Nz : zw);
-        const bool zok = zw >= 0 && zw < g.Nz;
-        const double* base = a + (size_t)(unsigned)(zw + 1) * (size_t)uplane;   // one IMAD.WIDE.U32
+        const bool zok = zw >= (lo_open ? -g.Hz : 0) && zw < g.Nz + (hi_open ? g.Hz : 0);   // halo planes are stored planes
+        const double* base = a + (size_t)(unsigned)(zw + g.Hz) * (size_t)uplane;   // one IMAD.WIDE.U32
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
             if (zok && ldok[h]) ld_pair(base + off[h], dst[2 * h], dst[2 * h + 1]);
@@ -180,7 +183,7 @@ k_sweep_tb(LevelGeom g, const double* __restrict__ u, const double* __restrict__
                 st_pair(wbuf + 2 * t, lv[s][A][0], lv[s][A][1]);
                 st_pair(wbuf + 2 * NT + 2 * t, lv[s][A][2], lv[s][A][3]);
                 const int zo = zi - 1 - s;                 // plane this stage produces (level s+1)
-                const bool zvalid = perz || (zo >= 0 && zo < g.Nz);
+                const bool zvalid = (zo >= 0 || lo_open) && (zo < g.Nz || hi_open);
                 double o[4] = {0.0, 0.0, 0.0, 0.0};
                 double uWq = __shfl_up_sync(0xffffffffu, lv[s][C][3], 1);
                 double uEq = __shfl_down_sync(0xffffffffu, lv[s][C][0], 1);
@@ -192,7 +195,7 @@ k_sweep_tb(LevelGeom g, const double* __restrict__ u, const double* __restrict__
                     ld_pair(rbuf + 2 * tS, s_[0], s_[1]); ld_pair(rbuf + 2 * NT + 2 * tS, s_[2], s_[3]);
                     const double omega = om.w[s], om1 = 1.0 - omega;
                     const double* fv = fr[(ph + 3 - s) % 3];
-                    const bool zlo = !perz && zo == 0, zhi = !perz && zo == g.Nz - 1;
+                    const bool zlo = !lo_open && zo == 0, zhi = !hi_open && zo == g.Nz - 1;
                     if (!edge && !zlo && !zhi) {           // interior path: no boundary selects
 #pragma unroll
                         for (int p = 0; p < 4; ++p) {
@@ -223,7 +226,7 @@ k_sweep_tb(LevelGeom g, const double* __restrict__ u, const double* __restrict__
                 } else {
                     const int zf = zi - T;                 // o = level-T plane zi - T
                     if (zf >= z0 && zf < z1) {
-                        double* base = out + (size_t)(unsigned)(zf + 1) * (size_t)uplane;
+                        double* base = out + (size_t)(unsigned)(zf + g.Hz) * (size_t)uplane;
 #pragma unroll
                         for (int h = 0; h < 2; ++h)
                             if (stok[h]) st_pair(base + off[h], o[2 * h], o[2 * h + 1]);
