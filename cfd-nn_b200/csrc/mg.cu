@@ -144,17 +144,17 @@ namespace {
 // tile shapes: BIG for levels that fill the chip with 64-wide tiles, SMALL for the rest
 constexpr int TB_BX_BIG = 64, TB_BY_BIG = 26, TB_BX_SMALL = 32, TB_BY_SMALL = 12;
 
-template <int T, int BX, int BY>
+template <int T, int BX, int BY, bool RES = false>
 void tb_attr() {
     using S = TbShape<T, BX, BY>;
-    CFDNN_CUDA(cudaFuncSetAttribute(k_sweep_tb<T, BX, BY>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::SMEM));
+    CFDNN_CUDA(cudaFuncSetAttribute(k_sweep_tb<T, BX, BY, RES>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::SMEM));
 }
-template <int T, int BX, int BY>
+template <int T, int BX, int BY, bool RES = false>
 void tb_launch(const LevelGeom& g, const double* in, const double* f, double* out, const double* w,
                cudaStream_t st) {
     using S = TbShape<T, BX, BY>;
     TbOmega<T> om;
-    for (int s = 0; s < T; ++s) om.w[s] = w[s];
+    for (int s = 0; s < T; ++s) om.w[s] = w ? w[s] : 0.0;
     const int tx = (g.Nx + BX - 1) / BX, ty = (g.Ny + BY - 1) / BY;
     // z chunks: enough CTAs for >= ~8 waves of 148 SMs, but chunks no thinner than 8*T planes
     const int zc_min = 8 * T;
@@ -164,17 +164,19 @@ void tb_launch(const LevelGeom& g, const double* in, const double* f, double* ou
     const int ZC = (g.Nz + nch - 1) / nch;
     nch = (g.Nz + ZC - 1) / ZC;
     dim3 grid(tx, ty, nch);
-    CFDNN_LAUNCH_COOP((k_sweep_tb<T, BX, BY>), grid, S::NTHREADS, S::SMEM, st, g, in, f, out, om, ZC);
+    CFDNN_LAUNCH_COOP((k_sweep_tb<T, BX, BY, RES>), grid, S::NTHREADS, S::SMEM, st, g, in, f, out, om, ZC);
 }
 }  // namespace
 
 void Multigrid::tb_setup() {
     tb_attr<1, TB_BX_BIG, TB_BY_BIG>(); tb_attr<2, TB_BX_BIG, TB_BY_BIG>();
     tb_attr<1, TB_BX_SMALL, TB_BY_SMALL>(); tb_attr<2, TB_BX_SMALL, TB_BY_SMALL>();
+    tb_attr<1, TB_BX_BIG, TB_BY_BIG, true>(); tb_attr<1, TB_BX_SMALL, TB_BY_SMALL, true>();
     if (const char* e = std::getenv("CFDNN_MG_TB")) tb_max_ = std::max(0, std::min(2, std::atoi(e)));
 }
 
-// n (<= 2) sweeps in one pass; false when this level is not eligible
+// n (<= 2) sweeps in one pass (w != nullptr), or the tiled residual r = f - L u (w == nullptr, n = 1);
+// false when this level is not eligible
 bool Multigrid::sweeps_tb(int level, const double* in, double* out, const double* w, int n) {
     Level& L = *levels_[level];
     const LevelGeom& g = L.g;
@@ -184,6 +186,11 @@ bool Multigrid::sweeps_tb(int level, const double* in, double* out, const double
     if (slab && (g.Hz < n || g.Nz < n)) return false;
     if (slab) halo(level, const_cast<double*>(in), n);     // n-deep halo: one exchange per pass
     const bool big = g.Nx >= 128 && g.Ny >= 56 && g.Nz >= 32;
+    if (!w) {
+        if (big) tb_launch<1, TB_BX_BIG, TB_BY_BIG, true>(g, in, L.f.p, out, nullptr, st_);
+        else tb_launch<1, TB_BX_SMALL, TB_BY_SMALL, true>(g, in, L.f.p, out, nullptr, st_);
+        return true;
+    }
     if (big) {
         if (n == 2) tb_launch<2, TB_BX_BIG, TB_BY_BIG>(g, in, L.f.p, out, w, st_);
         else tb_launch<1, TB_BX_BIG, TB_BY_BIG>(g, in, L.f.p, out, w, st_);
@@ -247,6 +254,7 @@ void Multigrid::smooth_jacobi(int level, int iters, double omega) {
 
 void Multigrid::residual(int level) {
     Level& L = *levels_[level];
+    if (sweeps_tb(level, L.u.p, L.r.p, nullptr, 1)) return;   // tiled residual (exchanges the halo itself)
     halo(level, L.u.p);
     dim3 g = grid2(L.g.Nx, L.g.Ny, (L.g.Nz + KZ - 1) / KZ, kBlk);
     CFDNN_LAUNCH((k_residual<KZ, false, false>), g, kBlk, 0, st_, L.g, L.u.p, L.f.p, L.r.p, nullptr, nullptr);
@@ -325,7 +333,12 @@ void Multigrid::prolong_from(int coarse) {
     else halo(coarse, C.u.p);
     LevelGeom gc = C.g;
     dim3 g = grid2(F.g.Nx, F.g.Ny, F.g.Nz, kBlk);
-    CFDNN_LAUNCH(k_prolong, g, kBlk, 0, st_, F.g, gc, C.u.p, F.u.p, kc_off);
+    if (!((F.g.Nx | F.g.Ny | F.g.Nz) & 1)) {
+        dim3 g8 = grid2(F.g.Nx / 2, F.g.Ny / 2, F.g.Nz / 2, kBlk);
+        CFDNN_LAUNCH(k_prolong8, g8, kBlk, 0, st_, F.g, gc, C.u.p, F.u.p, kc_off);
+    } else {
+        CFDNN_LAUNCH(k_prolong, g, kBlk, 0, st_, F.g, gc, C.u.p, F.u.p, kc_off);
+    }
 }
 
 // ---------------------------------------------------------------- V-cycle (:3121-3322)

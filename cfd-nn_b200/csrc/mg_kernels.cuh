@@ -268,6 +268,57 @@ k_prolong(LevelGeom gf, LevelGeom gc, const double* __restrict__ uc, double* __r
     uf[o] += corr;
 }
 
+// Same operator, one thread per COARSE cell updating its 8 fine children: the 8 coarse values are
+// loaded once per thread instead of once per fine cell, fine rows are read/written as aligned
+// double2.  For child (a,b,c) only the terms with (da<=a, db<=b, dc<=c) have non-zero weight; they
+// are summed in the reference's order (c000,c100,c010,c110,c001,...), so the result is bitwise that
+// of k_prolong (weights are exact powers of two).  Needs even fine sizes.
+static __global__ void __launch_bounds__(256)
+k_prolong8(LevelGeom gf, LevelGeom gc, const double* __restrict__ uc, double* __restrict__ uf, int kc_off) {
+    const int ic = blockIdx.x * blockDim.x + threadIdx.x;
+    const int jc = blockIdx.y * blockDim.y + threadIdx.y;
+    const int kl = blockIdx.z;                       // local coarse plane of this slab
+    if (2 * ic >= gf.Nx || 2 * jc >= gf.Ny || 2 * kl >= gf.Nz) return;
+    const int kc = kl + kc_off;
+    double sx = 1.0, sy = 1.0, sz = 1.0;
+    const int ip = bc_map(ic + 1, gc.Nx, gc.bc[0], gc.bc[1], sx);
+    const int jp = bc_map(jc + 1, gc.Ny, gc.bc[2], gc.bc[3], sy);
+    const int kp = bc_map(kc + 1, gc.Nz, gc.bc[4], gc.bc[5], sz);
+    double cv[2][2][2];                              // [dc][db][da]
+    cv[0][0][0] = uc[lidx(gc, ic, jc, kc)];
+    cv[0][0][1] = sx * uc[lidx(gc, ip, jc, kc)];
+    cv[0][1][0] = sy * uc[lidx(gc, ic, jp, kc)];
+    cv[0][1][1] = (sx * sy) * uc[lidx(gc, ip, jp, kc)];
+    cv[1][0][0] = sz * uc[lidx(gc, ic, jc, kp)];
+    cv[1][0][1] = (sx * sz) * uc[lidx(gc, ip, jc, kp)];
+    cv[1][1][0] = (sy * sz) * uc[lidx(gc, ic, jp, kp)];
+    cv[1][1][1] = (sx * sy * sz) * uc[lidx(gc, ip, jp, kp)];
+#pragma unroll
+    for (int c = 0; c < 2; ++c)
+#pragma unroll
+        for (int b = 0; b < 2; ++b) {
+            double corr[2];
+#pragma unroll
+            for (int a = 0; a < 2; ++a) {
+                const double w = (a ? 0.5 : 1.0) * (b ? 0.5 : 1.0) * (c ? 0.5 : 1.0);
+                double acc = w * cv[0][0][0];
+#pragma unroll
+                for (int dc = 0; dc <= c; ++dc)
+#pragma unroll
+                    for (int db = 0; db <= b; ++db)
+#pragma unroll
+                        for (int da = 0; da <= a; ++da)
+                            if (dc | db | da) acc += w * cv[dc][db][da];
+                corr[a] = acc;
+            }
+            double2* row = reinterpret_cast<double2*>(uf + lidx(gf, 2 * ic, 2 * jc + b, 2 * kl + c));
+            double2 v = *row;
+            v.x += corr[0];
+            v.y += corr[1];
+            *row = v;
+        }
+}
+
 // ------------------------------------------------------------------ small helpers
 // out[0] = sum(part[0..n)) (fixed order); if count>0 also out[1] = out[0]/count (the mean).
 static __global__ void k_final_sum(const double* __restrict__ part, int n, double* __restrict__ out,

@@ -68,7 +68,17 @@ __device__ __forceinline__ double jacobi_point(const LevelGeom& g, double uc, do
     return om1 * uc + omega * uj;
 }
 
-template <int T, int BX, int BY>
+// r = f - L u, same expression as k_residual (compute_residual :1807-1816)
+__device__ __forceinline__ double residual_point(const LevelGeom& g, double uc, double uW, double uE, double uS,
+                                                 double uN, double ub, double uf, double fv) {
+    const double two_c = 2.0 * uc;
+    const double lap = (uE - two_c + uW) / g.dx2 + (uN - two_c + uS) / g.dy2 + (uf - two_c + ub) / g.dz2;
+    return fv - lap;
+}
+
+// RES = true: the LAST stage evaluates the residual of its input level instead of a sweep
+// (T = 1, RES: a tiled residual kernel; `out` is then the r array).
+template <int T, int BX, int BY, bool RES = false>
 __global__ void __launch_bounds__(TbShape<T, BX, BY>::NTHREADS, 1)
 k_sweep_tb(LevelGeom g, const double* __restrict__ u, const double* __restrict__ f,
            double* __restrict__ out, TbOmega<T> om, int ZC) {
@@ -201,8 +211,11 @@ k_sweep_tb(LevelGeom g, const double* __restrict__ u, const double* __restrict__
                         for (int p = 0; p < 4; ++p) {
                             const double uW = p == 0 ? uWq : lv[s][C][p - 1];
                             const double uE = p == 3 ? uEq : lv[s][C][p + 1];
-                            o[p] = jacobi_point(g, lv[s][C][p], uW, uE, s_[p], n_[p], lv[s][M][p], lv[s][A][p],
-                                                fv[p], omega, om1);
+                            if (RES && s == T - 1)
+                                o[p] = residual_point(g, lv[s][C][p], uW, uE, s_[p], n_[p], lv[s][M][p], lv[s][A][p], fv[p]);
+                            else
+                                o[p] = jacobi_point(g, lv[s][C][p], uW, uE, s_[p], n_[p], lv[s][M][p], lv[s][A][p],
+                                                    fv[p], omega, om1);
                         }
                     } else {                               // faces: ghost = sign * adjacent interior value
 #pragma unroll
@@ -216,7 +229,8 @@ k_sweep_tb(LevelGeom g, const double* __restrict__ u, const double* __restrict__
                             const double uN = selfN ? syhi * uc : n_[p];
                             const double ub = zlo ? szlo * uc : lv[s][M][p];
                             const double uf = zhi ? szhi * uc : lv[s][A][p];
-                            o[p] = jacobi_point(g, uc, uW, uE, uS, uN, ub, uf, fv[p], omega, om1);
+                            if (RES && s == T - 1) o[p] = residual_point(g, uc, uW, uE, uS, uN, ub, uf, fv[p]);
+                            else o[p] = jacobi_point(g, uc, uW, uE, uS, uN, ub, uf, fv[p], omega, om1);
                         }
                     }
                 }
