@@ -242,9 +242,8 @@ void Solver::compute_diffusive_term() {
     const dim3 gr = grid3(g_.Nx + 1, g_.Ny + 1, g_.Nz + 1);
     CFDNN_LAUNCH(k_diffusive, gr, kB, 0, st_, g_, vel_.u, vel_.v, vel_.w, nueff_, diff_.u, diff_.v, diff_.w);
 }
-void Solver::advance(const Vel& in, const Vel& out, double dt, bool seam_average) {
-    const dim3 gr = grid3(g_.Nx + 1, g_.Ny + 1, g_.Nz + 1);
-    CFDNN_LAUNCH(k_advance, gr, kB, 0, st_, g_, in, out, conv_, diff_, dt, fx_, fy_, fz_);
+// periodic seam of the duplicated faces of `out` (see k_seam)
+void Solver::seam(const Vel& out, bool seam_average) {
     const int px = vbc_[0] == CFDNN_VBC_PERIODIC && vbc_[1] == CFDNN_VBC_PERIODIC;
     const int py = vbc_[2] == CFDNN_VBC_PERIODIC && vbc_[3] == CFDNN_VBC_PERIODIC;
     const int pzg = vbc_[4] == CFDNN_VBC_PERIODIC && vbc_[5] == CFDNN_VBC_PERIODIC;
@@ -256,6 +255,22 @@ void Solver::advance(const Vel& in, const Vel& out, double dt, bool seam_average
         else CFDNN_LAUNCH((k_seam<false>), gs, kB, 0, st_, g_, out, px, py, pz);
     }
     if (pzg && multi()) seam_z(out, seam_average);
+}
+// out = in + dt * (-conv + diff + f) with conv/diff evaluated on vel_ (the reference's operators
+// always read velocity_), fused into one pass.  When `out` IS vel_ (RK stages 2-3) the
+// result goes to a scratch buffer that also receives vel_'s ghost entries, and the two are swapped.
+void Solver::momentum(const Vel& in, Vel& out, double dt, bool seam_average) {
+    const int Ng = g_.Ng;
+    const dim3 gr = grid3(g_.Nx + 1 + 2 * Ng, g_.Ny + 1 + 2 * Ng, g_.Nz + 1 + 2 * Ng);
+    const bool alias = out.u == vel_.u;
+    const Vel src_in = in;                       // copies of the pointer triples (in may be vel_ itself)
+    const Vel dst = alias ? conv_ : out;
+    if (cfg_.convective_scheme == CFDNN_CONV_SKEW)
+        CFDNN_LAUNCH((k_momentum<true>), gr, kB, 0, st_, g_, vel_, nueff_, src_in, dst, dt, fx_, fy_, fz_, alias ? 1 : 0);
+    else
+        CFDNN_LAUNCH((k_momentum<false>), gr, kB, 0, st_, g_, vel_, nueff_, src_in, dst, dt, fx_, fy_, fz_, alias ? 1 : 0);
+    if (alias) std::swap(vel_, conv_);           // `out` refers to vel_: it now names the new buffer
+    seam(out, seam_average);
 }
 void Solver::blend(const Vel& a, const Vel& b, const Vel& c, double a1, double a2) {
     const dim3 gr = grid3(g_.Nx + 1, g_.Ny + 1, g_.Nz + 1);
@@ -282,16 +297,13 @@ void Solver::build_rhs(double dt) {
 void Solver::correct_velocity() {
     const dim3 gr = grid3(g_.Nx + 1, g_.Ny + 1, g_.Nz + 1);
     CFDNN_LAUNCH(k_correct, gr, kB, 0, st_, g_, star_, vel_, pcorr_, p_, dt_);
-    const int px = vbc_[0] == CFDNN_VBC_PERIODIC && vbc_[1] == CFDNN_VBC_PERIODIC;
-    const int py = vbc_[2] == CFDNN_VBC_PERIODIC && vbc_[3] == CFDNN_VBC_PERIODIC;
-    const int pzg = vbc_[4] == CFDNN_VBC_PERIODIC && vbc_[5] == CFDNN_VBC_PERIODIC;
-    const int pz = pzg && !multi();
-    if (px || py || pz) {
-        const int na = std::max(g_.Nx, g_.Ny), nb = std::max(g_.Ny, g_.Nz);
-        dim3 gs((na + kB.x - 1) / kB.x, (nb + kB.y - 1) / kB.y, 3);
-        CFDNN_LAUNCH((k_seam<true>), gs, kB, 0, st_, g_, vel_, px, py, pz);
-    }
-    if (pzg && multi()) seam_z(vel_, true);
+    seam(vel_, true);
+}
+// RK path: velocity_star_ <- velocity_ (interior) and the correction in one pass
+void Solver::copy_correct_velocity() {
+    const dim3 gr = grid3(g_.Nx + 1, g_.Ny + 1, g_.Nz + 1);
+    CFDNN_LAUNCH(k_copy_correct, gr, kB, 0, st_, g_, star_, vel_, pcorr_, p_, dt_);
+    seam(vel_, true);
 }
 
 int Solver::poisson_solve(const cfdnn_poisson_cfg& pc) {
@@ -341,11 +353,9 @@ void Solver::seam_z(const Vel& v, bool average) {
 
 // ---------------------------------------------------------------- integrators
 // euler_substep (src/solver_time.cpp:269-661): operators always read velocity_
-void Solver::euler_substep(const Vel& in, const Vel& out, double dt) {
+void Solver::euler_substep(const Vel& in, Vel& out, double dt) {
     halo_vel(vel_, /*bc_site=*/false);
-    compute_convective_term();
-    compute_diffusive_term();
-    advance(in, out, dt, /*seam_average=*/false);
+    momentum(in, out, dt, /*seam_average=*/false);
 }
 
 // project_velocity (src/solver_time.cpp:736-1211); which == &vel_ means "no swap"
@@ -361,14 +371,13 @@ void Solver::project_velocity(Vel* which, double dt) {
     pc.tol_rhs = cfg_.poisson_tol_rhs;
     pc.fixed_cycles = cfg_.poisson_fixed_cycles;
     poisson_solve(pc);
-    blend(vel_, star_, star_, 1.0, 0.0);           // copy velocity_ -> velocity_star_ (interior) :972-995
-    correct_velocity();
+    copy_correct_velocity();                       // velocity_ -> velocity_star_ (interior) :972-995, then correct
     apply_velocity_bc();
     if (need_swap) std::swap(vel_, *which);
 }
 
 void Solver::ssprk3_step(double dt) {              // src/solver_time.cpp:1303-1513
-    blend(vel_, rk_, rk_, 1.0, 0.0);               // u^n -> velocity_rk_
+    // u^n -> velocity_rk_ was done together with velocity_old_ <- velocity_ in step_device (k_copy2)
     euler_substep(vel_, star_, dt);
     project_velocity(&star_, dt);
     euler_substep(star_, vel_, dt);
@@ -380,7 +389,6 @@ void Solver::ssprk3_step(double dt) {              // src/solver_time.cpp:1303-1
     apply_velocity_bc();
 }
 void Solver::ssprk2_step(double dt) {              // :1213-1301
-    blend(vel_, rk_, rk_, 1.0, 0.0);
     euler_substep(vel_, star_, dt);
     project_velocity(&star_, dt);
     euler_substep(star_, vel_, dt);
@@ -391,9 +399,7 @@ void Solver::ssprk2_step(double dt) {              // :1213-1301
 // Euler path of step() (src/solver.cpp:1505-2507)
 void Solver::euler_step() {
     halo_vel(vel_, /*bc_site=*/false);
-    compute_convective_term();
-    compute_diffusive_term();
-    advance(vel_, star_, dt_, /*seam_average=*/true);          // predictor :1558-1722
+    momentum(vel_, star_, dt_, /*seam_average=*/true);         // conv + diff + predictor :1505-1722
     const bool px = vbc_[0] == CFDNN_VBC_PERIODIC && vbc_[1] == CFDNN_VBC_PERIODIC;
     const bool py = vbc_[2] == CFDNN_VBC_PERIODIC && vbc_[3] == CFDNN_VBC_PERIODIC;
     const bool pz = vbc_[4] == CFDNN_VBC_PERIODIC && vbc_[5] == CFDNN_VBC_PERIODIC;
@@ -469,7 +475,12 @@ void Solver::check_nan(int step) {                              // check_for_nan
 
 // step() (src/solver.cpp:1200-2786)
 void Solver::step_device(bool want_residual) {
-    blend(vel_, old_, old_, 1.0, 0.0);                          // velocity_old_ <- velocity_ :1210-1237
+    if (cfg_.time_integrator == CFDNN_TI_EULER) {
+        blend(vel_, old_, old_, 1.0, 0.0);                      // velocity_old_ <- velocity_ :1210-1237
+    } else {                                                    // ... and u^n -> velocity_rk_ (solver_time.cpp:1313-1330)
+        const dim3 gr = grid3(g_.Nx + 1, g_.Ny + 1, g_.Nz + 1);
+        CFDNN_LAUNCH(k_copy2, gr, kB, 0, st_, g_, vel_, old_, rk_);
+    }
     update_turbulence();                                        // :1284-1324
     build_nu_eff();                                             // :1326-1410
     if (cfg_.adaptive_dt && nn_) {                              // diffusion-CFL re-check :1416-1491

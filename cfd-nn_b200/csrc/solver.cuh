@@ -106,10 +106,12 @@ private:
     void compute_divergence(const Vel& v);                      // :1072-1245
     void correct_velocity();                                    // :1259-1604
     void blend(const Vel& a, const Vel& b, const Vel& c, double a1, double a2);  // c = a1 a + a2 b
-    void advance(const Vel& in, const Vel& out, double dt, bool seam_average);
+    void momentum(const Vel& in, Vel& out, double dt, bool seam_average);   // fused conv + diff + advance
+    void seam(const Vel& out, bool seam_average);
+    void copy_correct_velocity();
     void build_rhs(double dt);
     int poisson_solve(const cfdnn_poisson_cfg& pc);
-    void euler_substep(const Vel& in, const Vel& out, double dt);   // solver_time.cpp:269-661
+    void euler_substep(const Vel& in, Vel& out, double dt);         // solver_time.cpp:269-661
     void project_velocity(Vel* which, double dt);                    // :736-1211
     void ssprk3_step(double dt);                                     // :1303-1513
     void ssprk2_step(double dt);                                     // :1213-1301

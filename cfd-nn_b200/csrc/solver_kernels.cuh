@@ -29,164 +29,179 @@ namespace cfdnn {
 // SKEW = true : convective_{u,v,w}_face_kernel_skew_3d   (include/solver_kernels.hpp:1377-1569)
 // SKEW = false: convective_{u,v,w}_face_kernel_staggered_3d with use_central (:845-1022)
 template <bool SKEW>
+__device__ __forceinline__ double conv_u(const Geom& g, const double* __restrict__ u, const double* __restrict__ v,
+                                         const double* __restrict__ w, int i, int j, int k) {
+    const double uu = u[UIDX(i, j, k)];
+    const double u_ip1 = u[UIDX(i + 1, j, k)], u_im1 = u[UIDX(i - 1, j, k)];
+    const double u_jp1 = u[UIDX(i, j + 1, k)], u_jm1 = u[UIDX(i, j - 1, k)];
+    const double u_kp1 = u[UIDX(i, j, k + 1)], u_km1 = u[UIDX(i, j, k - 1)];
+    const double v_bl = v[VIDX(i - 1, j, k)], v_br = v[VIDX(i, j, k)];
+    const double v_tl = v[VIDX(i - 1, j + 1, k)], v_tr = v[VIDX(i, j + 1, k)];
+    const double vv = 0.25 * (v_bl + v_br + v_tl + v_tr);
+    const double w_bl = w[WIDX(i - 1, j, k)], w_br = w[WIDX(i, j, k)];
+    const double w_fl = w[WIDX(i - 1, j, k + 1)], w_fr = w[WIDX(i, j, k + 1)];
+    const double ww = 0.25 * (w_bl + w_br + w_fl + w_fr);
+    double r;
+    if (SKEW) {
+        const double adv_x = uu * (u_ip1 - u_im1) / g.dx_2;
+        const double uu_left = 0.5 * (u_im1 + uu), uu_right = 0.5 * (uu + u_ip1);
+        const double cons_x = (uu_right * uu_right - uu_left * uu_left) / g.dx;
+        const double skew_x = 0.5 * (adv_x + cons_x);
+        const double adv_y = vv * (u_jp1 - u_jm1) / g.dy_2;
+        const double vv_bot = 0.5 * (v_bl + v_br), vv_top = 0.5 * (v_tl + v_tr);
+        const double u_bot = 0.5 * (uu + u_jm1), u_top = 0.5 * (uu + u_jp1);
+        const double cons_y = (vv_top * u_top - vv_bot * u_bot) / g.dy;
+        const double skew_y = 0.5 * (adv_y + cons_y);
+        const double adv_z = ww * (u_kp1 - u_km1) / g.dz_2;
+        const double ww_back = 0.5 * (w_bl + w_br), ww_front = 0.5 * (w_fl + w_fr);
+        const double u_back = 0.5 * (uu + u_km1), u_front = 0.5 * (uu + u_kp1);
+        const double cons_z = (ww_front * u_front - ww_back * u_back) / g.dz;
+        const double skew_z = 0.5 * (adv_z + cons_z);
+        r = skew_x + skew_y + skew_z;
+    } else {
+        const double dudx = (u_ip1 - u_im1) / g.dx_2;
+        const double dudy = (u_jp1 - u_jm1) / g.dy_2;
+        const double dudz = (u_kp1 - u_km1) / g.dz_2;
+        r = uu * dudx + vv * dudy + ww * dudz;
+    }
+    return r;
+}
+template <bool SKEW>
+__device__ __forceinline__ double conv_v(const Geom& g, const double* __restrict__ u, const double* __restrict__ v,
+                                         const double* __restrict__ w, int i, int j, int k) {
+    const double vv = v[VIDX(i, j, k)];
+    const double v_ip1 = v[VIDX(i + 1, j, k)], v_im1 = v[VIDX(i - 1, j, k)];
+    const double v_jp1 = v[VIDX(i, j + 1, k)], v_jm1 = v[VIDX(i, j - 1, k)];
+    const double v_kp1 = v[VIDX(i, j, k + 1)], v_km1 = v[VIDX(i, j, k - 1)];
+    const double u_bl = u[UIDX(i, j - 1, k)], u_br = u[UIDX(i + 1, j - 1, k)];
+    const double u_tl = u[UIDX(i, j, k)], u_tr = u[UIDX(i + 1, j, k)];
+    const double uu = 0.25 * (u_bl + u_br + u_tl + u_tr);
+    const double w_bl = w[WIDX(i, j - 1, k)], w_tl = w[WIDX(i, j, k)];
+    const double w_bf = w[WIDX(i, j - 1, k + 1)], w_tf = w[WIDX(i, j, k + 1)];
+    const double ww = 0.25 * (w_bl + w_tl + w_bf + w_tf);
+    double r;
+    if (SKEW) {
+        const double adv_x = uu * (v_ip1 - v_im1) / g.dx_2;
+        const double uu_left = 0.5 * (u_bl + u_tl), uu_right = 0.5 * (u_br + u_tr);
+        const double v_left = 0.5 * (v_im1 + vv), v_right = 0.5 * (vv + v_ip1);
+        const double cons_x = (uu_right * v_right - uu_left * v_left) / g.dx;
+        const double skew_x = 0.5 * (adv_x + cons_x);
+        const double adv_y = vv * (v_jp1 - v_jm1) / g.dy_2;
+        const double vv_bot = 0.5 * (v_jm1 + vv), vv_top = 0.5 * (vv + v_jp1);
+        const double cons_y = (vv_top * vv_top - vv_bot * vv_bot) / g.dy;
+        const double skew_y = 0.5 * (adv_y + cons_y);
+        const double adv_z = ww * (v_kp1 - v_km1) / g.dz_2;
+        const double ww_back = 0.5 * (w_bl + w_tl), ww_front = 0.5 * (w_bf + w_tf);
+        const double v_back = 0.5 * (vv + v_km1), v_front = 0.5 * (vv + v_kp1);
+        const double cons_z = (ww_front * v_front - ww_back * v_back) / g.dz;
+        const double skew_z = 0.5 * (adv_z + cons_z);
+        r = skew_x + skew_y + skew_z;
+    } else {
+        const double dvdx = (v_ip1 - v_im1) / g.dx_2;
+        const double dvdy = (v_jp1 - v_jm1) / g.dy_2;
+        const double dvdz = (v_kp1 - v_km1) / g.dz_2;
+        r = uu * dvdx + vv * dvdy + ww * dvdz;
+    }
+    return r;
+}
+template <bool SKEW>
+__device__ __forceinline__ double conv_w(const Geom& g, const double* __restrict__ u, const double* __restrict__ v,
+                                         const double* __restrict__ w, int i, int j, int k) {
+    const double ww = w[WIDX(i, j, k)];
+    const double w_ip1 = w[WIDX(i + 1, j, k)], w_im1 = w[WIDX(i - 1, j, k)];
+    const double w_jp1 = w[WIDX(i, j + 1, k)], w_jm1 = w[WIDX(i, j - 1, k)];
+    const double w_kp1 = w[WIDX(i, j, k + 1)], w_km1 = w[WIDX(i, j, k - 1)];
+    const double u_bl = u[UIDX(i, j, k - 1)], u_br = u[UIDX(i + 1, j, k - 1)];
+    const double u_fl = u[UIDX(i, j, k)], u_fr = u[UIDX(i + 1, j, k)];
+    const double uu = 0.25 * (u_bl + u_br + u_fl + u_fr);
+    const double v_bl = v[VIDX(i, j, k - 1)], v_tl = v[VIDX(i, j + 1, k - 1)];
+    const double v_bf = v[VIDX(i, j, k)], v_tf = v[VIDX(i, j + 1, k)];
+    const double vv = 0.25 * (v_bl + v_tl + v_bf + v_tf);
+    double r;
+    if (SKEW) {
+        const double adv_x = uu * (w_ip1 - w_im1) / g.dx_2;
+        const double uu_left = 0.5 * (u_bl + u_fl), uu_right = 0.5 * (u_br + u_fr);
+        const double w_left = 0.5 * (w_im1 + ww), w_right = 0.5 * (ww + w_ip1);
+        const double cons_x = (uu_right * w_right - uu_left * w_left) / g.dx;
+        const double skew_x = 0.5 * (adv_x + cons_x);
+        const double adv_y = vv * (w_jp1 - w_jm1) / g.dy_2;
+        const double vv_bot = 0.5 * (v_bl + v_bf), vv_top = 0.5 * (v_tl + v_tf);
+        const double w_bot = 0.5 * (ww + w_jm1), w_top = 0.5 * (ww + w_jp1);
+        const double cons_y = (vv_top * w_top - vv_bot * w_bot) / g.dy;
+        const double skew_y = 0.5 * (adv_y + cons_y);
+        const double adv_z = ww * (w_kp1 - w_km1) / g.dz_2;
+        const double ww_back = 0.5 * (w_km1 + ww), ww_front = 0.5 * (ww + w_kp1);
+        const double cons_z = (ww_front * ww_front - ww_back * ww_back) / g.dz;
+        const double skew_z = 0.5 * (adv_z + cons_z);
+        r = skew_x + skew_y + skew_z;
+    } else {
+        const double dwdx = (w_ip1 - w_im1) / g.dx_2;
+        const double dwdy = (w_jp1 - w_jm1) / g.dy_2;
+        const double dwdz = (w_kp1 - w_km1) / g.dz_2;
+        r = uu * dwdx + vv * dwdy + ww * dwdz;
+    }
+    return r;
+}
+template <bool SKEW>
 __global__ void __launch_bounds__(256)
 k_convective(Geom g, const double* __restrict__ u, const double* __restrict__ v,
              const double* __restrict__ w, double* __restrict__ cu, double* __restrict__ cv,
              double* __restrict__ cw) {
     FACE_THREAD_PROLOGUE
-    if (has_u) {
-        const double uu = u[UIDX(i, j, k)];
-        const double u_ip1 = u[UIDX(i + 1, j, k)], u_im1 = u[UIDX(i - 1, j, k)];
-        const double u_jp1 = u[UIDX(i, j + 1, k)], u_jm1 = u[UIDX(i, j - 1, k)];
-        const double u_kp1 = u[UIDX(i, j, k + 1)], u_km1 = u[UIDX(i, j, k - 1)];
-        const double v_bl = v[VIDX(i - 1, j, k)], v_br = v[VIDX(i, j, k)];
-        const double v_tl = v[VIDX(i - 1, j + 1, k)], v_tr = v[VIDX(i, j + 1, k)];
-        const double vv = 0.25 * (v_bl + v_br + v_tl + v_tr);
-        const double w_bl = w[WIDX(i - 1, j, k)], w_br = w[WIDX(i, j, k)];
-        const double w_fl = w[WIDX(i - 1, j, k + 1)], w_fr = w[WIDX(i, j, k + 1)];
-        const double ww = 0.25 * (w_bl + w_br + w_fl + w_fr);
-        double r;
-        if (SKEW) {
-            const double adv_x = uu * (u_ip1 - u_im1) / g.dx_2;
-            const double uu_left = 0.5 * (u_im1 + uu), uu_right = 0.5 * (uu + u_ip1);
-            const double cons_x = (uu_right * uu_right - uu_left * uu_left) / g.dx;
-            const double skew_x = 0.5 * (adv_x + cons_x);
-            const double adv_y = vv * (u_jp1 - u_jm1) / g.dy_2;
-            const double vv_bot = 0.5 * (v_bl + v_br), vv_top = 0.5 * (v_tl + v_tr);
-            const double u_bot = 0.5 * (uu + u_jm1), u_top = 0.5 * (uu + u_jp1);
-            const double cons_y = (vv_top * u_top - vv_bot * u_bot) / g.dy;
-            const double skew_y = 0.5 * (adv_y + cons_y);
-            const double adv_z = ww * (u_kp1 - u_km1) / g.dz_2;
-            const double ww_back = 0.5 * (w_bl + w_br), ww_front = 0.5 * (w_fl + w_fr);
-            const double u_back = 0.5 * (uu + u_km1), u_front = 0.5 * (uu + u_kp1);
-            const double cons_z = (ww_front * u_front - ww_back * u_back) / g.dz;
-            const double skew_z = 0.5 * (adv_z + cons_z);
-            r = skew_x + skew_y + skew_z;
-        } else {
-            const double dudx = (u_ip1 - u_im1) / g.dx_2;
-            const double dudy = (u_jp1 - u_jm1) / g.dy_2;
-            const double dudz = (u_kp1 - u_km1) / g.dz_2;
-            r = uu * dudx + vv * dudy + ww * dudz;
-        }
-        cu[UIDX(i, j, k)] = r;
-    }
-    if (has_v) {
-        const double vv = v[VIDX(i, j, k)];
-        const double v_ip1 = v[VIDX(i + 1, j, k)], v_im1 = v[VIDX(i - 1, j, k)];
-        const double v_jp1 = v[VIDX(i, j + 1, k)], v_jm1 = v[VIDX(i, j - 1, k)];
-        const double v_kp1 = v[VIDX(i, j, k + 1)], v_km1 = v[VIDX(i, j, k - 1)];
-        const double u_bl = u[UIDX(i, j - 1, k)], u_br = u[UIDX(i + 1, j - 1, k)];
-        const double u_tl = u[UIDX(i, j, k)], u_tr = u[UIDX(i + 1, j, k)];
-        const double uu = 0.25 * (u_bl + u_br + u_tl + u_tr);
-        const double w_bl = w[WIDX(i, j - 1, k)], w_tl = w[WIDX(i, j, k)];
-        const double w_bf = w[WIDX(i, j - 1, k + 1)], w_tf = w[WIDX(i, j, k + 1)];
-        const double ww = 0.25 * (w_bl + w_tl + w_bf + w_tf);
-        double r;
-        if (SKEW) {
-            const double adv_x = uu * (v_ip1 - v_im1) / g.dx_2;
-            const double uu_left = 0.5 * (u_bl + u_tl), uu_right = 0.5 * (u_br + u_tr);
-            const double v_left = 0.5 * (v_im1 + vv), v_right = 0.5 * (vv + v_ip1);
-            const double cons_x = (uu_right * v_right - uu_left * v_left) / g.dx;
-            const double skew_x = 0.5 * (adv_x + cons_x);
-            const double adv_y = vv * (v_jp1 - v_jm1) / g.dy_2;
-            const double vv_bot = 0.5 * (v_jm1 + vv), vv_top = 0.5 * (vv + v_jp1);
-            const double cons_y = (vv_top * vv_top - vv_bot * vv_bot) / g.dy;
-            const double skew_y = 0.5 * (adv_y + cons_y);
-            const double adv_z = ww * (v_kp1 - v_km1) / g.dz_2;
-            const double ww_back = 0.5 * (w_bl + w_tl), ww_front = 0.5 * (w_bf + w_tf);
-            const double v_back = 0.5 * (vv + v_km1), v_front = 0.5 * (vv + v_kp1);
-            const double cons_z = (ww_front * v_front - ww_back * v_back) / g.dz;
-            const double skew_z = 0.5 * (adv_z + cons_z);
-            r = skew_x + skew_y + skew_z;
-        } else {
-            const double dvdx = (v_ip1 - v_im1) / g.dx_2;
-            const double dvdy = (v_jp1 - v_jm1) / g.dy_2;
-            const double dvdz = (v_kp1 - v_km1) / g.dz_2;
-            r = uu * dvdx + vv * dvdy + ww * dvdz;
-        }
-        cv[VIDX(i, j, k)] = r;
-    }
-    if (has_w) {
-        const double ww = w[WIDX(i, j, k)];
-        const double w_ip1 = w[WIDX(i + 1, j, k)], w_im1 = w[WIDX(i - 1, j, k)];
-        const double w_jp1 = w[WIDX(i, j + 1, k)], w_jm1 = w[WIDX(i, j - 1, k)];
-        const double w_kp1 = w[WIDX(i, j, k + 1)], w_km1 = w[WIDX(i, j, k - 1)];
-        const double u_bl = u[UIDX(i, j, k - 1)], u_br = u[UIDX(i + 1, j, k - 1)];
-        const double u_fl = u[UIDX(i, j, k)], u_fr = u[UIDX(i + 1, j, k)];
-        const double uu = 0.25 * (u_bl + u_br + u_fl + u_fr);
-        const double v_bl = v[VIDX(i, j, k - 1)], v_tl = v[VIDX(i, j + 1, k - 1)];
-        const double v_bf = v[VIDX(i, j, k)], v_tf = v[VIDX(i, j + 1, k)];
-        const double vv = 0.25 * (v_bl + v_tl + v_bf + v_tf);
-        double r;
-        if (SKEW) {
-            const double adv_x = uu * (w_ip1 - w_im1) / g.dx_2;
-            const double uu_left = 0.5 * (u_bl + u_fl), uu_right = 0.5 * (u_br + u_fr);
-            const double w_left = 0.5 * (w_im1 + ww), w_right = 0.5 * (ww + w_ip1);
-            const double cons_x = (uu_right * w_right - uu_left * w_left) / g.dx;
-            const double skew_x = 0.5 * (adv_x + cons_x);
-            const double adv_y = vv * (w_jp1 - w_jm1) / g.dy_2;
-            const double vv_bot = 0.5 * (v_bl + v_bf), vv_top = 0.5 * (v_tl + v_tf);
-            const double w_bot = 0.5 * (ww + w_jm1), w_top = 0.5 * (ww + w_jp1);
-            const double cons_y = (vv_top * w_top - vv_bot * w_bot) / g.dy;
-            const double skew_y = 0.5 * (adv_y + cons_y);
-            const double adv_z = ww * (w_kp1 - w_km1) / g.dz_2;
-            const double ww_back = 0.5 * (w_km1 + ww), ww_front = 0.5 * (ww + w_kp1);
-            const double cons_z = (ww_front * ww_front - ww_back * ww_back) / g.dz;
-            const double skew_z = 0.5 * (adv_z + cons_z);
-            r = skew_x + skew_y + skew_z;
-        } else {
-            const double dwdx = (w_ip1 - w_im1) / g.dx_2;
-            const double dwdy = (w_jp1 - w_jm1) / g.dy_2;
-            const double dwdz = (w_kp1 - w_km1) / g.dz_2;
-            r = uu * dwdx + vv * dwdy + ww * dwdz;
-        }
-        cw[WIDX(i, j, k)] = r;
-    }
+    if (has_u) cu[UIDX(i, j, k)] = conv_u<SKEW>(g, u, v, w, i, j, k);
+    if (has_v) cv[VIDX(i, j, k)] = conv_v<SKEW>(g, u, v, w, i, j, k);
+    if (has_w) cw[WIDX(i, j, k)] = conv_w<SKEW>(g, u, v, w, i, j, k);
 }
 
 // ------------------------------------------------------------------ diffusion
 // diffusive_{u,v,w}_face_kernel_staggered_3d (include/solver_kernels.hpp:2199-2337)
+__device__ __forceinline__ double diff_u(const Geom& g, const double* __restrict__ u, const double* __restrict__ v,
+                                         const double* __restrict__ w, const double* __restrict__ nu, int i, int j, int k) {
+    const double uc = u[UIDX(i, j, k)];
+    const double nu_left = nu[CIDX(i - 1, j, k)], nu_right = nu[CIDX(i, j, k)];
+    const double d2x = (nu_right * (u[UIDX(i + 1, j, k)] - uc) - nu_left * (uc - u[UIDX(i - 1, j, k)])) / g.dx2;
+    const double nu_n = 0.25 * (nu_left + nu_right + nu[CIDX(i - 1, j + 1, k)] + nu[CIDX(i, j + 1, k)]);
+    const double nu_s = 0.25 * (nu_left + nu_right + nu[CIDX(i - 1, j - 1, k)] + nu[CIDX(i, j - 1, k)]);
+    const double d2y = (nu_n * (u[UIDX(i, j + 1, k)] - uc) - nu_s * (uc - u[UIDX(i, j - 1, k)])) / g.dy2;
+    const double nu_f = 0.25 * (nu_left + nu_right + nu[CIDX(i - 1, j, k + 1)] + nu[CIDX(i, j, k + 1)]);
+    const double nu_b = 0.25 * (nu_left + nu_right + nu[CIDX(i - 1, j, k - 1)] + nu[CIDX(i, j, k - 1)]);
+    const double d2z = (nu_f * (u[UIDX(i, j, k + 1)] - uc) - nu_b * (uc - u[UIDX(i, j, k - 1)])) / g.dz2;
+    return d2x + d2y + d2z;
+}
+__device__ __forceinline__ double diff_v(const Geom& g, const double* __restrict__ u, const double* __restrict__ v,
+                                         const double* __restrict__ w, const double* __restrict__ nu, int i, int j, int k) {
+    const double vc = v[VIDX(i, j, k)];
+    const double nu_bottom = nu[CIDX(i, j - 1, k)], nu_top = nu[CIDX(i, j, k)];
+    const double nu_e = 0.25 * (nu_bottom + nu_top + nu[CIDX(i + 1, j - 1, k)] + nu[CIDX(i + 1, j, k)]);
+    const double nu_w = 0.25 * (nu_bottom + nu_top + nu[CIDX(i - 1, j - 1, k)] + nu[CIDX(i - 1, j, k)]);
+    const double d2x = (nu_e * (v[VIDX(i + 1, j, k)] - vc) - nu_w * (vc - v[VIDX(i - 1, j, k)])) / g.dx2;
+    const double d2y = (nu_top * (v[VIDX(i, j + 1, k)] - vc) - nu_bottom * (vc - v[VIDX(i, j - 1, k)])) / g.dy2;
+    const double nu_f = 0.25 * (nu_bottom + nu_top + nu[CIDX(i, j - 1, k + 1)] + nu[CIDX(i, j, k + 1)]);
+    const double nu_b = 0.25 * (nu_bottom + nu_top + nu[CIDX(i, j - 1, k - 1)] + nu[CIDX(i, j, k - 1)]);
+    const double d2z = (nu_f * (v[VIDX(i, j, k + 1)] - vc) - nu_b * (vc - v[VIDX(i, j, k - 1)])) / g.dz2;
+    return d2x + d2y + d2z;
+}
+__device__ __forceinline__ double diff_w(const Geom& g, const double* __restrict__ u, const double* __restrict__ v,
+                                         const double* __restrict__ w, const double* __restrict__ nu, int i, int j, int k) {
+    const double wc = w[WIDX(i, j, k)];
+    const double nu_back = nu[CIDX(i, j, k - 1)], nu_front = nu[CIDX(i, j, k)];
+    const double nu_e = 0.25 * (nu_back + nu_front + nu[CIDX(i + 1, j, k - 1)] + nu[CIDX(i + 1, j, k)]);
+    const double nu_w = 0.25 * (nu_back + nu_front + nu[CIDX(i - 1, j, k - 1)] + nu[CIDX(i - 1, j, k)]);
+    const double d2x = (nu_e * (w[WIDX(i + 1, j, k)] - wc) - nu_w * (wc - w[WIDX(i - 1, j, k)])) / g.dx2;
+    const double nu_n = 0.25 * (nu_back + nu_front + nu[CIDX(i, j + 1, k - 1)] + nu[CIDX(i, j + 1, k)]);
+    const double nu_s = 0.25 * (nu_back + nu_front + nu[CIDX(i, j - 1, k - 1)] + nu[CIDX(i, j - 1, k)]);
+    const double d2y = (nu_n * (w[WIDX(i, j + 1, k)] - wc) - nu_s * (wc - w[WIDX(i, j - 1, k)])) / g.dy2;
+    const double d2z = (nu_front * (w[WIDX(i, j, k + 1)] - wc) - nu_back * (wc - w[WIDX(i, j, k - 1)])) / g.dz2;
+    return d2x + d2y + d2z;
+}
 static __global__ void __launch_bounds__(256)
 k_diffusive(Geom g, const double* __restrict__ u, const double* __restrict__ v,
             const double* __restrict__ w, const double* __restrict__ nu,
             double* __restrict__ du, double* __restrict__ dv, double* __restrict__ dw) {
     FACE_THREAD_PROLOGUE
-    if (has_u) {
-        const double uc = u[UIDX(i, j, k)];
-        const double nu_left = nu[CIDX(i - 1, j, k)], nu_right = nu[CIDX(i, j, k)];
-        const double d2x = (nu_right * (u[UIDX(i + 1, j, k)] - uc) - nu_left * (uc - u[UIDX(i - 1, j, k)])) / g.dx2;
-        const double nu_n = 0.25 * (nu_left + nu_right + nu[CIDX(i - 1, j + 1, k)] + nu[CIDX(i, j + 1, k)]);
-        const double nu_s = 0.25 * (nu_left + nu_right + nu[CIDX(i - 1, j - 1, k)] + nu[CIDX(i, j - 1, k)]);
-        const double d2y = (nu_n * (u[UIDX(i, j + 1, k)] - uc) - nu_s * (uc - u[UIDX(i, j - 1, k)])) / g.dy2;
-        const double nu_f = 0.25 * (nu_left + nu_right + nu[CIDX(i - 1, j, k + 1)] + nu[CIDX(i, j, k + 1)]);
-        const double nu_b = 0.25 * (nu_left + nu_right + nu[CIDX(i - 1, j, k - 1)] + nu[CIDX(i, j, k - 1)]);
-        const double d2z = (nu_f * (u[UIDX(i, j, k + 1)] - uc) - nu_b * (uc - u[UIDX(i, j, k - 1)])) / g.dz2;
-        du[UIDX(i, j, k)] = d2x + d2y + d2z;
-    }
-    if (has_v) {
-        const double vc = v[VIDX(i, j, k)];
-        const double nu_bottom = nu[CIDX(i, j - 1, k)], nu_top = nu[CIDX(i, j, k)];
-        const double nu_e = 0.25 * (nu_bottom + nu_top + nu[CIDX(i + 1, j - 1, k)] + nu[CIDX(i + 1, j, k)]);
-        const double nu_w = 0.25 * (nu_bottom + nu_top + nu[CIDX(i - 1, j - 1, k)] + nu[CIDX(i - 1, j, k)]);
-        const double d2x = (nu_e * (v[VIDX(i + 1, j, k)] - vc) - nu_w * (vc - v[VIDX(i - 1, j, k)])) / g.dx2;
-        const double d2y = (nu_top * (v[VIDX(i, j + 1, k)] - vc) - nu_bottom * (vc - v[VIDX(i, j - 1, k)])) / g.dy2;
-        const double nu_f = 0.25 * (nu_bottom + nu_top + nu[CIDX(i, j - 1, k + 1)] + nu[CIDX(i, j, k + 1)]);
-        const double nu_b = 0.25 * (nu_bottom + nu_top + nu[CIDX(i, j - 1, k - 1)] + nu[CIDX(i, j, k - 1)]);
-        const double d2z = (nu_f * (v[VIDX(i, j, k + 1)] - vc) - nu_b * (vc - v[VIDX(i, j, k - 1)])) / g.dz2;
-        dv[VIDX(i, j, k)] = d2x + d2y + d2z;
-    }
-    if (has_w) {
-        const double wc = w[WIDX(i, j, k)];
-        const double nu_back = nu[CIDX(i, j, k - 1)], nu_front = nu[CIDX(i, j, k)];
-        const double nu_e = 0.25 * (nu_back + nu_front + nu[CIDX(i + 1, j, k - 1)] + nu[CIDX(i + 1, j, k)]);
-        const double nu_w = 0.25 * (nu_back + nu_front + nu[CIDX(i - 1, j, k - 1)] + nu[CIDX(i - 1, j, k)]);
-        const double d2x = (nu_e * (w[WIDX(i + 1, j, k)] - wc) - nu_w * (wc - w[WIDX(i - 1, j, k)])) / g.dx2;
-        const double nu_n = 0.25 * (nu_back + nu_front + nu[CIDX(i, j + 1, k - 1)] + nu[CIDX(i, j + 1, k)]);
-        const double nu_s = 0.25 * (nu_back + nu_front + nu[CIDX(i, j - 1, k - 1)] + nu[CIDX(i, j - 1, k)]);
-        const double d2y = (nu_n * (w[WIDX(i, j + 1, k)] - wc) - nu_s * (wc - w[WIDX(i, j - 1, k)])) / g.dy2;
-        const double d2z = (nu_front * (w[WIDX(i, j, k + 1)] - wc) - nu_back * (wc - w[WIDX(i, j, k - 1)])) / g.dz2;
-        dw[WIDX(i, j, k)] = d2x + d2y + d2z;
-    }
+    if (has_u) du[UIDX(i, j, k)] = diff_u(g, u, v, w, nu, i, j, k);
+    if (has_v) dv[VIDX(i, j, k)] = diff_v(g, u, v, w, nu, i, j, k);
+    if (has_w) dw[WIDX(i, j, k)] = diff_w(g, u, v, w, nu, i, j, k);
 }
 
 // ------------------------------------------------------------------ time advance / blends
@@ -198,6 +213,97 @@ k_advance(Geom g, Vel in, Vel out, Vel conv, Vel diff, double dt, double fx, dou
     if (has_u) { const size_t o = UIDX(i, j, k); out.u[o] = in.u[o] + dt * (-conv.u[o] + diff.u[o] + fx); }
     if (has_v) { const size_t o = VIDX(i, j, k); out.v[o] = in.v[o] + dt * (-conv.v[o] + diff.v[o] + fy); }
     if (has_w) { const size_t o = WIDX(i, j, k); out.w[o] = in.w[o] + dt * (-conv.w[o] + diff.w[o] + fz); }
+}
+// Fused momentum update: out = in + dt * (-conv(vel) + diff(vel, nu) + f) on interior faces in ONE pass
+// (compute_convective_term + compute_diffusive_term + the advance loop of euler_substep,
+// src/solver_time.cpp:269-516, same expressions in the same order).  Raw index space (I,J,K) over the
+// ghost-inclusive arrays.  copy_ghosts = 1: every non-interior entry of out is set to vel's, so
+// that a caller whose `out` aliases `vel` in the reference (RK stages 2-3) can pass a scratch
+// buffer and swap it with vel afterwards — bit-identical to the in-place reference semantics.
+template <bool SKEW>
+__global__ void __launch_bounds__(256)
+k_momentum(Geom g, Vel vel, const double* __restrict__ nu, Vel in, Vel out, double dt, double fx, double fy,
+           double fz, int copy_ghosts) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int j = blockIdx.y * blockDim.y + threadIdx.y;
+    const int k = blockIdx.z;
+    const int Ng = g.Ng;
+    const int ex = g.Nx + 2 * Ng, ey = g.Ny + 2 * Ng, ez = g.Nz + 2 * Ng;   // cell-array extents
+    if (i > ex || j > ey || k > ez) return;
+    const bool ix_c = i >= Ng && i < Ng + g.Nx, iy_c = j >= Ng && j < Ng + g.Ny, iz_c = k >= Ng && k < Ng + g.Nz;
+    const bool ix_f = i >= Ng && i <= Ng + g.Nx, iy_f = j >= Ng && j <= Ng + g.Ny, iz_f = k >= Ng && k <= Ng + g.Nz;
+    if (j < ey && k < ez) {                       // u array entry (i <= ex always holds)
+        const size_t o = UIDX(i, j, k);
+        if (ix_f && iy_c && iz_c) {
+            const double c = conv_u<SKEW>(g, vel.u, vel.v, vel.w, i, j, k);
+            const double d = diff_u(g, vel.u, vel.v, vel.w, nu, i, j, k);
+            out.u[o] = in.u[o] + dt * (-c + d + fx);
+        } else if (copy_ghosts) {
+            out.u[o] = vel.u[o];
+        }
+    }
+    if (i < ex && k < ez) {                       // v array entry
+        const size_t o = VIDX(i, j, k);
+        if (ix_c && iy_f && iz_c) {
+            const double c = conv_v<SKEW>(g, vel.u, vel.v, vel.w, i, j, k);
+            const double d = diff_v(g, vel.u, vel.v, vel.w, nu, i, j, k);
+            out.v[o] = in.v[o] + dt * (-c + d + fy);
+        } else if (copy_ghosts) {
+            out.v[o] = vel.v[o];
+        }
+    }
+    if (i < ex && j < ey) {                       // w array entry
+        const size_t o = WIDX(i, j, k);
+        if (ix_c && iy_c && iz_f) {
+            const double c = conv_w<SKEW>(g, vel.u, vel.v, vel.w, i, j, k);
+            const double d = diff_w(g, vel.u, vel.v, vel.w, nu, i, j, k);
+            out.w[o] = in.w[o] + dt * (-c + d + fz);
+        } else if (copy_ghosts) {
+            out.w[o] = vel.w[o];
+        }
+    }
+}
+// star <- vel (interior faces), vel <- vel - dt * grad p', p += p' in one pass
+// (the velocity_ -> velocity_star_ copy of project_velocity, src/solver_time.cpp:972-995, fused with
+// correct_velocity, src/solver_operators.cpp:1259-1604; both are pointwise in the velocity arrays)
+static __global__ void __launch_bounds__(256)
+k_copy_correct(Geom g, Vel star, Vel vel, const double* __restrict__ pc, double* __restrict__ p, double dt) {
+    FACE_THREAD_PROLOGUE
+    if (has_u) {
+        const size_t o = UIDX(i, j, k);
+        const double us = vel.u[o];
+        const double dp = (pc[CIDX(i, j, k)] - pc[CIDX(i - 1, j, k)]) / g.dx;
+        star.u[o] = us;
+        vel.u[o] = us - dt * dp;
+    }
+    if (has_v) {
+        const size_t o = VIDX(i, j, k);
+        const double vs = vel.v[o];
+        const double d = pc[CIDX(i, j, k)] - pc[CIDX(i, j - 1, k)];
+        const double dp = g.y_stretched ? fdiv(d, g.dyc[j], g.rdyc[j]) : d / g.dy;
+        star.v[o] = vs;
+        vel.v[o] = vs - dt * dp;
+    }
+    if (has_w) {
+        const size_t o = WIDX(i, j, k);
+        const double ws = vel.w[o];
+        const double dp = (pc[CIDX(i, j, k)] - pc[CIDX(i, j, k - 1)]) / g.dz;
+        star.w[o] = ws;
+        vel.w[o] = ws - dt * dp;
+    }
+    if (ix < g.Nx && iy < g.Ny && iz < g.Nz) {
+        const size_t o = CIDX(i, j, k);
+        p[o] += pc[o];
+    }
+}
+// b <- a and c <- a on interior faces in one pass (velocity_old_ and velocity_rk_ copies at the top
+// of step() / ssprk3_step: src/solver.cpp:1210-1237, src/solver_time.cpp:1313-1330)
+static __global__ void __launch_bounds__(256)
+k_copy2(Geom g, Vel a, Vel b, Vel c) {
+    FACE_THREAD_PROLOGUE
+    if (has_u) { const size_t o = UIDX(i, j, k); const double x = a.u[o]; b.u[o] = x; c.u[o] = x; }
+    if (has_v) { const size_t o = VIDX(i, j, k); const double x = a.v[o]; b.v[o] = x; c.v[o] = x; }
+    if (has_w) { const size_t o = WIDX(i, j, k); const double x = a.w[o]; b.w[o] = x; c.w[o] = x; }
 }
 // c = a1*a + a2*b on interior faces (blend_3d_uvw / blend_to_3d_uvw / copy_3d_uvw,
 // src/solver_time_kernels_blend.cpp:38-158; the copy is literally 1.0*a + 0.0*b)
