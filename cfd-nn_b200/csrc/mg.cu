@@ -156,11 +156,21 @@ void tb_launch(const LevelGeom& g, const double* in, const double* f, double* ou
     TbOmega<T> om;
     for (int s = 0; s < T; ++s) om.w[s] = w ? w[s] : 0.0;
     const int tx = (g.Nx + BX - 1) / BX, ty = (g.Ny + BY - 1) / BY;
-    // z chunks: enough CTAs for >= ~8 waves of 148 SMs, but chunks no thinner than 8*T planes
-    const int zc_min = 8 * T;
-    const int nch_max = std::max(1, g.Nz / zc_min);
-    const int want = 148 * 8;
-    int nch = std::min(nch_max, std::max(1, (want + tx * ty - 1) / (tx * ty)));
+    // z chunks (one CTA per SM): pick the chunk count that maximises
+    //   (fill of the last wave of 148 SMs) x (useful planes / planes marched incl. the 2T warm-up),
+    // with chunks no thinner than 4*T planes.
+    const int nch_max = std::max(1, g.Nz / (4 * T));
+    int nch = 1;
+    double best = -1.0;
+    for (int c = 1; c <= nch_max; ++c) {
+        const int zc = (g.Nz + c - 1) / c;
+        const int cc = (g.Nz + zc - 1) / zc;
+        const double ctas = (double)tx * ty * cc;
+        const double waves = ctas / 148.0;
+        const double fill = waves / std::ceil(waves);
+        const double score = fill * zc / (zc + 2.0 * T);
+        if (score > best + 1e-9) { best = score; nch = cc; }
+    }
     const int ZC = (g.Nz + nch - 1) / nch;
     nch = (g.Nz + ZC - 1) / ZC;
     dim3 grid(tx, ty, nch);

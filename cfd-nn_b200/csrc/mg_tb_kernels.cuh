@@ -139,7 +139,7 @@ k_sweep_tb(LevelGeom g, const double* __restrict__ u, const double* __restrict__
     constexpr int PL = 4 * NT;                             // doubles per smem plane
 
     // ---- pipeline state: lv[l][slot] = plane of level l that arrived in phase `slot` (mod 3)
-    double lv[T][3][4], fr[3][4], nu_[4];
+    double lv[T][3][4], fr[3][4], nu_[4] = {0.0, 0.0, 0.0, 0.0};
 #pragma unroll
     for (int l = 0; l < T; ++l)
 #pragma unroll
@@ -165,8 +165,7 @@ k_sweep_tb(LevelGeom g, const double* __restrict__ u, const double* __restrict__
         const double* base = a + (size_t)(unsigned)(zw + g.Hz) * (size_t)uplane;   // one IMAD.WIDE.U32
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
-            if (zok && ldok[h]) ld_pair(base + off[h], dst[2 * h], dst[2 * h + 1]);
-            else { dst[2 * h] = 0.0; dst[2 * h + 1] = 0.0; }
+            if (zok && ldok[h]) ld_pair(base + off[h], dst[2 * h], dst[2 * h + 1]);   // else: keep the stale (finite) value
         }
     };
     load_plane(u, zi_first, nu_);
@@ -194,7 +193,7 @@ k_sweep_tb(LevelGeom g, const double* __restrict__ u, const double* __restrict__
                 st_pair(wbuf + 2 * NT + 2 * t, lv[s][A][2], lv[s][A][3]);
                 const int zo = zi - 1 - s;                 // plane this stage produces (level s+1)
                 const bool zvalid = (zo >= 0 || lo_open) && (zo < g.Nz || hi_open);
-                double o[4] = {0.0, 0.0, 0.0, 0.0};
+                double o[4];
                 double uWq = __shfl_up_sync(0xffffffffu, lv[s][C][3], 1);
                 double uEq = __shfl_down_sync(0xffffffffu, lv[s][C][0], 1);
                 if (zvalid) {
@@ -233,6 +232,9 @@ k_sweep_tb(LevelGeom g, const double* __restrict__ u, const double* __restrict__
                             else o[p] = jacobi_point(g, uc, uW, uE, uS, uN, ub, uf, fv[p], omega, om1);
                         }
                     }
+                } else {
+#pragma unroll
+                    for (int p = 0; p < 4; ++p) o[p] = lv[s][C][p];   // plane outside a closed z face: never consumed
                 }
                 if (s + 1 < T) {
 #pragma unroll
