@@ -109,6 +109,7 @@ _SIGS = {
                                   c_double_p, c_double_p, c_double_p, c_double_p]),
     "cfdnn_nn_forward": (C.c_int, [C.c_void_p, c_double_p, c_double_p, C.c_size_t]),
     "cfdnn_nn_last_timing": (C.c_int, [C.c_void_p, c_double_p]),
+    "cfdnn_nn_uses_tensor_cores": (C.c_int, [C.c_void_p]),
 }
 
 EXPORTS = tuple(_SIGS)

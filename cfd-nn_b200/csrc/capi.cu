@@ -200,6 +200,7 @@ int cfdnn_nn_forward(cfdnn_nn* nn, const double* x, double* y, size_t n) {
     return guarded([&] { nn->impl.forward_host(x, y, n); });
 }
 int cfdnn_nn_last_timing(const cfdnn_nn* nn, double* ms) { if (ms) *ms = nn->impl.last_ms; return CFDNN_OK; }
+int cfdnn_nn_uses_tensor_cores(const cfdnn_nn* nn) { return nn && nn->impl.uses_tensor_cores() ? 1 : 0; }
 #endif  // CFDNN_MG_ONLY
 
 }  // extern "C"

@@ -2,6 +2,7 @@
 #include "nn.cuh"
 #include <cmath>
 #include <algorithm>
+#include <cstdlib>
 
 namespace cfdnn {
 
@@ -68,22 +69,20 @@ __device__ __forceinline__ double wall_distance(double y, double y_lo, double y_
     return fmin(fabs(y - y_lo), fabs(y - y_hi));
 }
 
-// One thread per cell of one z-plane.  KIND: CFDNN_TURB_NN_TBNN or CFDNN_TURB_NN_MLP.
+// Per-cell context carried from the feature stage to the nu_t stage.
+struct CellCtx {
+    double T[4][3];
+    double k_val, Sxy_, S_mag;
+};
+
+// Features of one cell (i, j) of plane kk: TBNN 5 invariants (src/features.cpp:121-190) or the 6
+// scalar-nu_t features (:67-119); for TBNN also the tensor basis (:192-292) and k / omega.
 template <int KIND>
-__global__ void __launch_bounds__(128)
-k_nn_update(Geom g, NNDev net, NNParams prm, const double* __restrict__ yc, double y_lo, double y_hi,
-            const double* __restrict__ ub, const double* __restrict__ vb, const double* __restrict__ k_in,
-            const double* __restrict__ omega_in, const int* __restrict__ kflag, int plane0,
-            double* __restrict__ nu_t, double* __restrict__ txx, double* __restrict__ txy,
-            double* __restrict__ tyy) {
-    const int ix = blockIdx.x * blockDim.x + threadIdx.x;
-    const int iy = blockIdx.y * blockDim.y + threadIdx.y;
-    const int pl = blockIdx.z;
-    if (ix >= g.Nx || iy >= g.Ny) return;
-    const int i = ix + g.Ng, j = iy + g.Ng, kk = plane0 + pl;
-    const double* u = ub + (size_t)kk * g.up;
-    const double* v = vb + (size_t)kk * g.vp;
-    const size_t oc = (size_t)kk * g.cp + (size_t)j * g.cs + i;
+__device__ __forceinline__ void cell_features(const Geom& g, const NNParams& prm, const double* __restrict__ yc,
+                                              double y_lo, double y_hi, const double* __restrict__ u,
+                                              const double* __restrict__ v, const double* __restrict__ k_in,
+                                              const double* __restrict__ omega_in, int kprovided, int i, int j,
+                                              size_t oc, double* feat, CellCtx& c) {
 #define U2(I, J) u[(size_t)(J) * g.us + (I)]
 #define V2(I, J) v[(size_t)(J) * g.vs + (I)]
     // uniform-spacing MAC gradients (features.cpp:132-140, turbulence_nn_tbnn.cpp:838-845)
@@ -97,8 +96,7 @@ k_nn_update(Geom g, NNDev net, NNParams prm, const double* __restrict__ yc, doub
     const double S_mag = sqrt(Sxx_ * Sxx_ + Syy_ * Syy_ + 2.0 * Sxy_ * Sxy_);
     const double Omega_mag = sqrt(2.0 * Oxy_ * Oxy_);
     const double y_wall = wall_distance(yc[j], y_lo, y_hi);
-    double feat[8];
-    double out[NN_MAX_WIDTH];
+    c.Sxy_ = Sxy_; c.S_mag = S_mag;
 
     if (KIND == CFDNN_TURB_NN_MLP) {
         // compute_features_scalar_nut (src/features.cpp:67-119)
@@ -112,17 +110,13 @@ k_nn_update(Geom g, NNDev net, NNParams prm, const double* __restrict__ yc, doub
         feat[3] = (S_mag > 1e-10) ? Omega_mag / S_mag : 0.0;
         feat[4] = S_mag * prm.delta * prm.delta / prm.nu;
         feat[5] = u_mag / u_ref;
-        mlp_forward(net, feat, out);
-        double nn = out[0];                                   // turbulence_nn_mlp.cpp:262-278
-        if (nn - nn != 0.0) nn = 0.0;
-        else { nn = fmax(0.0, nn); nn = fmin(nn, prm.nu_t_max); }
-        nu_t[oc] = nn;
+        c.k_val = 0.0;
         return;
     }
 
     // ---- TBNN: k / omega (turbulence_nn_tbnn.cpp:659-684, estimate_k :274-309)
     double k_val, omega_val;
-    if (kflag[pl]) {
+    if (kprovided) {
         k_val = k_in[oc];
         omega_val = omega_in[oc];
     } else {
@@ -133,6 +127,7 @@ k_nn_update(Geom g, NNDev net, NNParams prm, const double* __restrict__ yc, doub
         k_val = fmax(prm.k_min, fmin(k_est, 10.0 * u_tau * u_tau));
         omega_val = sqrt(k_val) / (KAPPA * fmax(y_wall, 1e-10));
     }
+    c.k_val = k_val;
     // compute_features_tbnn (src/features.cpp:121-190)
     const double eps = C_MU * k_val * omega_val;
     const double tau = fmax(k_val, 1e-10) / fmax(eps, 1e-20);
@@ -152,45 +147,251 @@ k_nn_update(Geom g, NNDev net, NNParams prm, const double* __restrict__ yc, doub
         gdudy = (U2(i, j + 1) - U2(i, j - 1)) * inv_dy_local;
         gdvdy = (V2(i, j + 1) - V2(i, j - 1)) * inv_dy_local;
     }
-    double T[4][3];
     {
         const double Sxx = dudx * tau, Syy = gdvdy * tau;
         const double Sxy = (0.5 * (gdudy + dvdx)) * tau, Oxy = (0.5 * (gdudy - dvdx)) * tau;
-        T[0][0] = Sxx; T[0][1] = Sxy; T[0][2] = Syy;
-        T[1][0] = -2.0 * Sxy * Oxy; T[1][1] = (Sxx - Syy) * Oxy; T[1][2] = 2.0 * Sxy * Oxy;
+        c.T[0][0] = Sxx; c.T[0][1] = Sxy; c.T[0][2] = Syy;
+        c.T[1][0] = -2.0 * Sxy * Oxy; c.T[1][1] = (Sxx - Syy) * Oxy; c.T[1][2] = 2.0 * Sxy * Oxy;
         const double S2xx = Sxx * Sxx + Sxy * Sxy, S2yy = Sxy * Sxy + Syy * Syy, S2xy = Sxy * (Sxx + Syy);
         const double trS2 = S2xx + S2yy;
-        T[2][0] = S2xx - 0.5 * trS2; T[2][1] = S2xy; T[2][2] = S2yy - 0.5 * trS2;
-        T[3][0] = 0.0; T[3][1] = 0.0; T[3][2] = 0.0;
+        c.T[2][0] = S2xx - 0.5 * trS2; c.T[2][1] = S2xy; c.T[2][2] = S2yy - 0.5 * trS2;
+        c.T[3][0] = 0.0; c.T[3][1] = 0.0; c.T[3][2] = 0.0;
     }
-    mlp_forward(net, feat, out);
-    const int nout = net.dims[net.n_layers];
+#undef U2
+#undef V2
+}
+
+// MLP output of one cell -> nu_t (and tau_ij for TBNN).
+template <int KIND>
+__device__ __forceinline__ void cell_finish(const NNParams& prm, const CellCtx& c, const double* out, int nout,
+                                            size_t oc, double* __restrict__ nu_t, double* __restrict__ txx,
+                                            double* __restrict__ txy, double* __restrict__ tyy) {
+    if (KIND == CFDNN_TURB_NN_MLP) {
+        double nn = out[0];                                   // turbulence_nn_mlp.cpp:262-278
+        if (nn - nn != 0.0) nn = 0.0;
+        else { nn = fmax(0.0, nn); nn = fmin(nn, prm.nu_t_max); }
+        nu_t[oc] = nn;
+        return;
+    }
     double b_xx = 0.0, b_xy = 0.0, b_yy = 0.0;                // construct_anisotropy :294-306
+#pragma unroll
     for (int n = 0; n < 4; ++n) {
         const double G = n < nout ? out[n] : 0.0;
-        b_xx += G * T[n][0]; b_xy += G * T[n][1]; b_yy += G * T[n][2];
+        b_xx += G * c.T[n][0]; b_xy += G * c.T[n][1]; b_yy += G * c.T[n][2];
     }
     if (txx) {                                                // anisotropy_to_reynolds_stress :308-326
-        const double k_safe = fmax(k_val, 0.0);
+        const double k_safe = fmax(c.k_val, 0.0);
         txx[oc] = 2.0 * k_safe * (b_xx + 1.0 / 3.0);
         txy[oc] = 2.0 * k_safe * b_xy;
         tyy[oc] = 2.0 * k_safe * (b_yy + 1.0 / 3.0);
     }
     double nt;                                                // turbulence_nn_tbnn.cpp:846-864
-    if (fabs(Sxy_) > 1e-10) {
-        nt = fabs(-b_xy * k_val / Sxy_);
-    } else if (S_mag > 1e-10) {
+    if (fabs(c.Sxy_) > 1e-10) {
+        nt = fabs(-b_xy * c.k_val / c.Sxy_);
+    } else if (c.S_mag > 1e-10) {
         const double b_mag = sqrt(b_xx * b_xx + 2.0 * b_xy * b_xy + b_yy * b_yy);
-        nt = k_val * b_mag / S_mag;
+        nt = c.k_val * b_mag / c.S_mag;
     } else {
         nt = 0.0;
     }
     nt = fmax(0.0, fmin(nt, 10.0 * prm.nu));
     if (nt - nt != 0.0) nt = 0.0;
     nu_t[oc] = nt;
-#undef U2
-#undef V2
 }
+
+// ---- scalar (SIMT) path: one thread per cell of one z-plane.  Used for networks whose weight
+// fragments do not fit the tensor-core kernel's shared memory, by CFDNN_NN_SIMT=1 (A/B checks)
+// and by the host-side test double.  KIND: CFDNN_TURB_NN_TBNN or CFDNN_TURB_NN_MLP.
+template <int KIND>
+__global__ void __launch_bounds__(128)
+k_nn_update(Geom g, NNDev net, NNParams prm, const double* __restrict__ yc, double y_lo, double y_hi,
+            const double* __restrict__ ub, const double* __restrict__ vb, const double* __restrict__ k_in,
+            const double* __restrict__ omega_in, const int* __restrict__ kflag, int plane0,
+            double* __restrict__ nu_t, double* __restrict__ txx, double* __restrict__ txy,
+            double* __restrict__ tyy) {
+    const int ix = blockIdx.x * blockDim.x + threadIdx.x;
+    const int iy = blockIdx.y * blockDim.y + threadIdx.y;
+    const int pl = blockIdx.z;
+    if (ix >= g.Nx || iy >= g.Ny) return;
+    const int i = ix + g.Ng, j = iy + g.Ng, kk = plane0 + pl;
+    const size_t oc = (size_t)kk * g.cp + (size_t)j * g.cs + i;
+    double feat[8];
+    double out[NN_MAX_WIDTH];
+    CellCtx c;
+    cell_features<KIND>(g, prm, yc, y_lo, y_hi, ub + (size_t)kk * g.up, vb + (size_t)kk * g.vp, k_in, omega_in,
+                        KIND == CFDNN_TURB_NN_TBNN ? kflag[pl] : 0, i, j, oc, feat, c);
+    mlp_forward(net, feat, out);
+    cell_finish<KIND>(prm, c, out, net.dims[net.n_layers], oc, nu_t, txx, txy, tyy);
+}
+
+#ifndef CFDNN_DEVSIM
+// ---------------------------------------------------------------- tensor-core path (FP64 DMMA)
+// The hidden-layer GEMMs  Y[cells x out] = act(X[cells x in] W^T + b)  run on the FP64 tensor
+// cores with mma.sync.m8n8k4.f64.  One warp owns 32 consecutive cells of a row: each lane builds
+// the features of its own cell, then the warp pushes the cells through the network 16 at a time
+// (two 8-row M tiles share every weight fragment).  The D fragment of layer l (row = lane/4,
+// columns 2q, 2q+1 of each 8-wide N tile, q = lane%4) is used directly as the A fragments of
+// layer l+1 by enumerating K in the order (tile, parity, q) instead of ascending — the weights
+// are stored pre-permuted in that fragment order (NNClosure::build_fragments), so no shuffles or
+// shared-memory round trips sit between layers.  Summation order inside a dot product differs
+// from the reference's ascending-j loop (and DMMA fuses), which moves results by O(1e-16) —
+// the closure's gate is 1e-6.
+__device__ __forceinline__ void dmma(double& d0, double& d1, double a, double b) {
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+                 : "+d"(d0), "+d"(d1) : "d"(a), "d"(b));
+}
+
+// tanh to ~2e-13 absolute: t = exp(-2|x|) (Cody-Waite + degree-10 Taylor on |r| <= ln2/2), then
+// (1-t)/(1+t) with a Newton-refined reciprocal.  ~22 FP64 instructions instead of libdevice's
+// branchy sequence; explicit fma intrinsics (the library is compiled with -fmad=false).
+__device__ __forceinline__ double fast_tanh(double x) {
+    const double ax = fmin(fabs(x), 20.0);
+    const double y = -2.0 * ax;
+    const double MAGIC = 6755399441055744.0;                       // 1.5 * 2^52
+    double fn = __fma_rn(y, 1.4426950408889634, MAGIC);
+    const int n = __double2loint(fn);
+    fn = fn - MAGIC;
+    double r = __fma_rn(fn, -6.93147180369123816490e-01, y);
+    r = __fma_rn(fn, -1.90821492927058770002e-10, r);
+    double p = 2.7557319223985893e-07;                              // 1/10!
+    p = __fma_rn(p, r, 2.7557319223985888e-06);                     // 1/9!
+    p = __fma_rn(p, r, 2.4801587301587302e-05);
+    p = __fma_rn(p, r, 1.9841269841269841e-04);
+    p = __fma_rn(p, r, 1.3888888888888889e-03);
+    p = __fma_rn(p, r, 8.3333333333333332e-03);
+    p = __fma_rn(p, r, 4.1666666666666664e-02);
+    p = __fma_rn(p, r, 1.6666666666666666e-01);
+    p = __fma_rn(p, r, 0.5);
+    p = __fma_rn(p, r, 1.0);
+    p = __fma_rn(p, r, 1.0);
+    const double t = __hiloint2double(__double2hiint(p) + n * 1048576, __double2loint(p));   // p * 2^n, n in [-58, 0]
+    const double num = 1.0 - t, den = 1.0 + t;                     // den in [1, 2]
+    double rc;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(rc) : "d"(den));
+    double e = __fma_rn(-den, rc, 1.0);
+    rc = __fma_rn(rc, e, rc);
+    e = __fma_rn(-den, rc, 1.0);
+    rc = __fma_rn(rc, e, rc);
+    const double q = num * rc;
+    return x != x ? x : copysign(q, x);                            // NaN in -> NaN out
+}
+
+__device__ __forceinline__ double act_mma(double s, int act) {
+    if (act == 1) return fast_tanh(s);
+    if (act == 2) return s > 0.0 ? s : 0.0;
+    return s;
+}
+
+constexpr int MMA_WARPS = 4;
+
+template <int KIND>
+__global__ void __launch_bounds__(MMA_WARPS * 32)
+k_nn_update_mma(Geom g, NNFrag net, NNParams prm, const double* __restrict__ yc, double y_lo, double y_hi,
+                const double* __restrict__ ub, const double* __restrict__ vb, const double* __restrict__ k_in,
+                const double* __restrict__ omega_in, const int* __restrict__ kflag, int plane0,
+                double* __restrict__ nu_t, double* __restrict__ txx, double* __restrict__ txy,
+                double* __restrict__ tyy) {
+    extern __shared__ double2 smem2[];
+    double2* Wsm = smem2;                                               // fragments
+    double* bsm = reinterpret_cast<double*>(Wsm + net.w_total);         // biases
+    double* xsm = bsm + ((net.b_total + 1) & ~1);                       // [warp][32 cells][8] features
+    double* gsm = xsm + MMA_WARPS * 32 * 8;                             // [warp][32 cells][8] outputs
+    for (int t = threadIdx.x; t < net.w_total; t += blockDim.x) Wsm[t] = net.W[t];
+    for (int t = threadIdx.x; t < net.b_total; t += blockDim.x) bsm[t] = net.b[t];
+    __syncthreads();
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int grp = lane >> 2, q = lane & 3;
+    double* xw = xsm + warp * 256;
+    double* gw = gsm + warp * 256;
+    const int pl = blockIdx.z;
+    const int kk = plane0 + pl;
+    const double* u = ub + (size_t)kk * g.up;
+    const double* v = vb + (size_t)kk * g.vp;
+    const int kprov = KIND == CFDNN_TURB_NN_TBNN ? kflag[pl] : 0;
+    const int ix = blockIdx.x * 32 + lane;
+    const int ixc = min(ix, g.Nx - 1);                                  // clamp: tail lanes recompute the last cell
+    const int nrows = (g.Ny + MMA_WARPS - 1) / MMA_WARPS;
+
+    for (int rg = blockIdx.y; rg < nrows; rg += gridDim.y) {
+        const int iy = rg * MMA_WARPS + warp;
+        if (iy >= g.Ny) continue;                                       // warp-uniform
+        const int i = ixc + g.Ng, j = iy + g.Ng;
+        const size_t oc = (size_t)kk * g.cp + (size_t)j * g.cs + i;
+        CellCtx c;
+        {
+            double feat[8];
+#pragma unroll
+            for (int f = 0; f < 8; ++f) feat[f] = 0.0;
+            cell_features<KIND>(g, prm, yc, y_lo, y_hi, u, v, k_in, omega_in, kprov, i, j, oc, feat, c);
+            if (net.means) {
+#pragma unroll
+                for (int f = 0; f < 8; ++f)
+                    if (f < net.n_in) feat[f] = (feat[f] - net.means[f]) / net.stds[f];
+            }
+#pragma unroll
+            for (int f = 0; f < 8; f += 2)
+                *reinterpret_cast<double2*>(xw + lane * 8 + f) = make_double2(feat[f], feat[f + 1]);
+        }
+        __syncwarp();
+
+#pragma unroll 1
+        for (int half = 0; half < 2; ++half) {
+            // A fragments: a[mt][tile] = columns (tile*8 + 2q, +1) of cell row half*16 + mt*8 + grp
+            double2 a[2][8];
+#pragma unroll
+            for (int mt = 0; mt < 2; ++mt) {
+                a[mt][0] = *reinterpret_cast<const double2*>(xw + (half * 16 + mt * 8 + grp) * 8 + 2 * q);
+#pragma unroll
+                for (int t = 1; t < 8; ++t) a[mt][t] = make_double2(0.0, 0.0);
+            }
+#pragma unroll 1
+            for (int l = 0; l < net.n_layers; ++l) {
+                const double2* Wl = Wsm + net.woff[l];
+                const double* bl = bsm + net.boff[l];
+                const int nti = net.nti[l], nto = net.nto[l], act = net.act[l];
+                double2 o[2][8];
+#pragma unroll
+                for (int no = 0; no < 8; ++no) {
+                    if (no < nto) {
+                        const double2 bias = *reinterpret_cast<const double2*>(bl + no * 8 + 2 * q);
+                        double2 acc0 = bias, acc1 = bias;
+#pragma unroll
+                        for (int ni = 0; ni < 8; ++ni) {
+                            if (ni < nti) {
+                                const double2 w = Wl[(no * nti + ni) * 32 + lane];
+                                dmma(acc0.x, acc0.y, a[0][ni].x, w.x);
+                                dmma(acc1.x, acc1.y, a[1][ni].x, w.x);
+                                dmma(acc0.x, acc0.y, a[0][ni].y, w.y);
+                                dmma(acc1.x, acc1.y, a[1][ni].y, w.y);
+                            }
+                        }
+                        o[0][no] = make_double2(act_mma(acc0.x, act), act_mma(acc0.y, act));
+                        o[1][no] = make_double2(act_mma(acc1.x, act), act_mma(acc1.y, act));
+                    } else {
+                        o[0][no] = make_double2(0.0, 0.0);
+                        o[1][no] = make_double2(0.0, 0.0);
+                    }
+                }
+#pragma unroll
+                for (int t = 0; t < 8; ++t) { a[0][t] = o[0][t]; a[1][t] = o[1][t]; }
+            }
+            // outputs (<= 8 wide, tile 0): row = cell, columns 2q, 2q+1
+#pragma unroll
+            for (int mt = 0; mt < 2; ++mt)
+                *reinterpret_cast<double2*>(gw + (half * 16 + mt * 8 + grp) * 8 + 2 * q) = a[mt][0];
+        }
+        __syncwarp();
+        if (ix < g.Nx) {
+            double out[4];
+#pragma unroll
+            for (int n = 0; n < 4; ++n) out[n] = gw[lane * 8 + n];
+            cell_finish<KIND>(prm, c, out, net.n_out, oc, nu_t, txx, txy, tyy);
+        }
+        __syncwarp();
+    }
+}
+#endif  // !CFDNN_DEVSIM
 }  // namespace
 
 // ---------------------------------------------------------------- host side
@@ -230,6 +431,7 @@ NNClosure::NNClosure(int kind, int n_layers, const int* dims, const int* act, co
         CFDNN_CUDA(cudaMemcpy(stds_.p, stds, dims[0] * sizeof(double), cudaMemcpyHostToDevice));
         net_.means = means_.p; net_.stds = stds_.p; net_.n_scale = dims[0];
     }
+    build_fragments(hw, hb);
     CFDNN_CUDA(cudaStreamCreateWithFlags(&st_, cudaStreamNonBlocking));
     CFDNN_CUDA(cudaEventCreate(&ev0_));
     CFDNN_CUDA(cudaEventCreate(&ev1_));
@@ -239,6 +441,55 @@ NNClosure::~NNClosure() {
     if (ev0_) cudaEventDestroy(ev0_);
     if (ev1_) cudaEventDestroy(ev1_);
     if (st_) cudaStreamDestroy(st_);
+}
+
+// Weights in DMMA fragment order (see k_nn_update_mma): layer l holds [nto][nti][32 lanes] double2,
+// lane (grp = lane/4, q = lane%4) of tile pair (no, ni) gets W_l[no*8 + grp][ni*8 + 2q + {0,1}],
+// zero where the index is outside the layer (K and N padded to multiples of 8).
+void NNClosure::build_fragments(const std::vector<double>& hw, const std::vector<double>& hb) {
+    frag_ = NNFrag{};
+    mma_ok_ = false;
+    const int nl = net_.n_layers;
+    size_t nw = 0, nb = 0;
+    for (int l = 0; l < nl; ++l) {
+        frag_.nti[l] = (net_.dims[l] + 7) / 8;
+        frag_.nto[l] = (net_.dims[l + 1] + 7) / 8;
+        frag_.act[l] = net_.act[l];
+        frag_.woff[l] = (int)nw; frag_.boff[l] = (int)nb;
+        nw += (size_t)frag_.nti[l] * frag_.nto[l] * 32;
+        nb += (size_t)frag_.nto[l] * 8;
+    }
+    frag_.n_layers = nl; frag_.w_total = (int)nw; frag_.b_total = (int)nb;
+    frag_.n_in = net_.dims[0]; frag_.n_out = net_.dims[nl];
+    mma_smem_ = nw * sizeof(double2) + ((nb + 1) & ~(size_t)1) * sizeof(double) + 2 * 4 * 32 * 8 * sizeof(double);
+    // tensor-core path: inputs and outputs fit one 8-wide tile, fragments fit shared memory
+    if (net_.dims[0] > 8 || net_.dims[nl] > 8 || mma_smem_ > 200 * 1024) return;
+    std::vector<double2> fw(nw);
+    std::vector<double> fb(nb, 0.0);
+    for (int l = 0; l < nl; ++l) {
+        const int in = net_.dims[l], od = net_.dims[l + 1];
+        const double* W = hw.data() + net_.woff[l];
+        for (int no = 0; no < frag_.nto[l]; ++no)
+            for (int ni = 0; ni < frag_.nti[l]; ++ni)
+                for (int lane = 0; lane < 32; ++lane) {
+                    const int row = no * 8 + (lane >> 2), col = ni * 8 + 2 * (lane & 3);
+                    double2 w;
+                    w.x = (row < od && col < in) ? W[(size_t)row * in + col] : 0.0;
+                    w.y = (row < od && col + 1 < in) ? W[(size_t)row * in + col + 1] : 0.0;
+                    fw[frag_.woff[l] + ((size_t)no * frag_.nti[l] + ni) * 32 + lane] = w;
+                }
+        for (int i = 0; i < od; ++i) fb[frag_.boff[l] + i] = hb[net_.boff[l] + i];
+    }
+    Wf_.alloc(nw, false); bf_.alloc(nb, false);
+    CFDNN_CUDA(cudaMemcpy(Wf_.p, fw.data(), nw * sizeof(double2), cudaMemcpyHostToDevice));
+    CFDNN_CUDA(cudaMemcpy(bf_.p, fb.data(), nb * sizeof(double), cudaMemcpyHostToDevice));
+    frag_.W = Wf_.p; frag_.b = bf_.p;
+#ifndef CFDNN_DEVSIM
+    CFDNN_CUDA(cudaFuncSetAttribute(k_nn_update_mma<CFDNN_TURB_NN_TBNN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mma_smem_));
+    CFDNN_CUDA(cudaFuncSetAttribute(k_nn_update_mma<CFDNN_TURB_NN_MLP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mma_smem_));
+    const char* e = std::getenv("CFDNN_NN_SIMT");
+    mma_ok_ = !(e && std::atoi(e) != 0);
+#endif
 }
 
 void NNClosure::set_params(double nu, double delta, double u_ref, double k_min, double nu_t_max) {
@@ -254,6 +505,29 @@ void NNClosure::update_device(const Geom& g, const double* yc, double y_lo, doub
     if ((size_t)nplanes > kflag_.n) kflag_.alloc(nplanes);
     const dim3 blk(32, 4, 1);
     const dim3 grd((g.Nx + 31) / 32, (g.Ny + 3) / 4, nplanes);
+    if (kind_ == CFDNN_TURB_NN_TBNN && net_.dims[0] != 5) throw std::invalid_argument("TBNN closure expects 5 input features");
+    if (kind_ == CFDNN_TURB_NN_MLP && net_.dims[0] != 6) throw std::invalid_argument("MLP closure expects 6 input features");
+#ifndef CFDNN_DEVSIM
+    if (mma_ok_) {
+        // tensor-core kernel: 4 warps x 32 cells per CTA pass; CTAs stride over row groups so the
+        // weight fragments are staged into shared memory a few times per SM, not once per 128 cells
+        frag_.means = net_.means; frag_.stds = net_.stds;
+        const int xt = (g.Nx + 31) / 32, rows = (g.Ny + MMA_WARPS - 1) / MMA_WARPS;
+        const long long want = 148LL * 8;
+        int gy = (int)std::max(1LL, std::min<long long>(rows, (want + (long long)xt * nplanes - 1) / ((long long)xt * nplanes)));
+        const dim3 mg(xt, gy, nplanes);
+        if (kind_ == CFDNN_TURB_NN_TBNN) {
+            CFDNN_CUDA(cudaMemsetAsync(kflag_.p, 0, nplanes * sizeof(int), st));
+            CFDNN_LAUNCH(k_k_provided, grd, blk, 0, st, g, k, prm_.k_min, plane0, kflag_.p);
+            CFDNN_LAUNCH((k_nn_update_mma<CFDNN_TURB_NN_TBNN>), mg, MMA_WARPS * 32, mma_smem_, st, g, frag_, prm_, yc, y_lo,
+                         y_hi, vel.u, vel.v, k, omega, kflag_.p, plane0, nu_t, txx, txy, tyy);
+        } else {
+            CFDNN_LAUNCH((k_nn_update_mma<CFDNN_TURB_NN_MLP>), mg, MMA_WARPS * 32, mma_smem_, st, g, frag_, prm_, yc, y_lo,
+                         y_hi, vel.u, vel.v, k, omega, kflag_.p, plane0, nu_t, txx, txy, tyy);
+        }
+        return;
+    }
+#endif
     if (kind_ == CFDNN_TURB_NN_TBNN) {
         if (net_.dims[0] != 5) throw std::invalid_argument("TBNN closure expects 5 input features");
         CFDNN_CUDA(cudaMemsetAsync(kflag_.p, 0, nplanes * sizeof(int), st));

@@ -26,6 +26,19 @@ struct NNDev {                       // by-value kernel argument
     int n_scale;
 };
 
+struct NNFrag {                      // by-value kernel argument: weights in DMMA fragment order (nn.cu)
+    int n_layers;
+    int nti[NN_MAX_LAYERS], nto[NN_MAX_LAYERS];   // 8-wide K / N tiles per layer
+    int act[NN_MAX_LAYERS];
+    int woff[NN_MAX_LAYERS];         // double2 offset of layer l: [nto][nti][32 lanes] double2
+    int boff[NN_MAX_LAYERS];         // double offset of the zero-padded bias (nto*8 entries)
+    int w_total, b_total;            // double2 / double counts
+    const double2* W;
+    const double* b;
+    const double *means, *stds;
+    int n_in, n_out;
+};
+
 struct NNParams { double nu, delta, u_ref, k_min, nu_t_max; };
 
 class NNClosure {
@@ -48,6 +61,7 @@ public:
     int kind() const { return kind_; }
     int in_dim() const { return net_.dims[0]; }
     int out_dim() const { return net_.dims[net_.n_layers]; }
+    bool uses_tensor_cores() const { return mma_ok_; }
 
 private:
     int kind_;
@@ -55,6 +69,13 @@ private:
     NNParams prm_{0.001, 1.0, 1.0, 1e-10, 1.0};
     DevBuf<double> W_, b_, means_, stds_;
     DevBuf<int> kflag_;
+    // tensor-core (DMMA) path: pre-permuted weight fragments
+    NNFrag frag_{};
+    DevBuf<double2> Wf_;
+    DevBuf<double> bf_;
+    size_t mma_smem_ = 0;
+    bool mma_ok_ = false;
+    void build_fragments(const std::vector<double>& hw, const std::vector<double>& hb);
     cudaStream_t st_ = nullptr;
     cudaEvent_t ev0_ = nullptr, ev1_ = nullptr;
 };

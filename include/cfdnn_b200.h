@@ -184,6 +184,9 @@ int cfdnn_nn_update(cfdnn_nn* nn, const cfdnn_mesh_desc* mesh, const double* u, 
 /* batched MLP forward (MLP::forward, src/nn_core.cpp:144-204): x[n][in] -> y[n][out] */
 int cfdnn_nn_forward(cfdnn_nn* nn, const double* x, double* y, size_t n);
 int cfdnn_nn_last_timing(const cfdnn_nn* nn, double* ms);
+/* 1 when update() runs the hidden-layer GEMMs on the FP64 tensor cores (mma.sync.m8n8k4.f64), 0 when the
+ * network only fits the scalar kernel (more than 8 inputs/outputs, or fragments larger than shared memory) */
+int cfdnn_nn_uses_tensor_cores(const cfdnn_nn* nn);
 
 #ifdef __cplusplus
 }

@@ -123,3 +123,28 @@ def check_3d_planes(B, Nx=16, Ny=16, Nz=6):
         for n in ("nut", "tau_xx", "tau_xy", "tau_yy"):
             assert R.rel_l2(got[n][kk + 1], refs[kk][n][0]) <= TOL, (kk, n)
     assert not got["nut"][0].any() and not got["nut"][-1].any()      # ghost planes untouched
+
+
+def check_mma_vs_simt(B, Nx=96, Ny=40, Nz=3):
+    preset = "tbnn_channel_caseholdout"
+    sh3 = R.shapes(Nx, Ny, Nz)
+    u3 = np.zeros(sh3["u"]); v3 = np.zeros(sh3["v"]); k3 = np.zeros(sh3["c"]); o3 = np.zeros(sh3["c"])
+    for kk in range(Nz):
+        u, v, k, om = NC.channel_fields(Nx, Ny, seed=20 + kk, k_val=0.01, om_val=10.0)
+        u3[kk + 1], v3[kk + 1], k3[kk + 1], o3[kk + 1] = u[0], v[0], k[0], om[0]
+    res = {}
+    for mode in ("0", "1"):
+        os.environ["CFDNN_NN_SIMT"] = mode
+        try:
+            h = M.create_preset(B, preset)
+        finally:
+            os.environ.pop("CFDNN_NN_SIMT", None)
+        tc = B.lib.cfdnn_nn_uses_tensor_cores(h)
+        assert tc == (1 if mode == "0" else 0)
+        B.check(B.lib.cfdnn_nn_set_params(h, NC.NU, 1.0, 1.0, 1e-10, 1.0))
+        res[mode] = NC.backend_update(B, h, Nx, Ny, u3, v3, k3, o3, Nz=Nz)
+        B.lib.cfdnn_nn_destroy(h)
+    inner = res["1"]["nut"][1:-1, 1:-1, 1:-1]
+    assert inner.max() > 0 and np.mean(inner >= 10 * NC.NU) < 0.5
+    for n in ("nut", "tau_xx", "tau_xy", "tau_yy"):
+        assert R.rel_l2(res["0"][n], res["1"][n]) <= 1e-9, n

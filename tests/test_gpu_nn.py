@@ -28,3 +28,15 @@ def test_mlp_update(gpu, oracle):
 
 def test_tbnn_3d_per_plane(gpu, oracle):
     P.check_3d_planes(gpu, Nx=32, Ny=32, Nz=6)
+
+
+def test_tbnn_update_ragged_tiles(gpu, oracle):
+    """Nx not a multiple of the 32-cell warp tile, Ny not a multiple of the 4-row CTA"""
+    P.check_tbnn_k_provided(gpu, Nx=50, Ny=37)
+    P.check_mlp_closure(gpu, Nx=50, Ny=37)
+
+
+def test_tensor_core_vs_scalar_kernel(gpu):
+    """The FP64 tensor-core (DMMA) kernel against the scalar per-thread kernel of the same library
+    (CFDNN_NN_SIMT=1 selects it at closure creation): same cells, nu_t/tau within 1e-9."""
+    P.check_mma_vs_simt(gpu, Nx=96, Ny=40, Nz=3)
