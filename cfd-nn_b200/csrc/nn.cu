@@ -237,7 +237,7 @@ k_nn_update(Geom g, NNDev net, NNParams prm, const double* __restrict__ yc, doub
 // from the reference's ascending-j loop (and DMMA fuses), which moves results by O(1e-16) —
 // the closure's gate is 1e-6.
 __device__ __forceinline__ void dmma(double& d0, double& d1, double a, double b) {
-    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+    asm("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
                  : "+d"(d0), "+d"(d1) : "d"(a), "d"(b));
 }
 
@@ -351,26 +351,44 @@ k_nn_update_mma(Geom g, NNFrag net, NNParams prm, const double* __restrict__ yc,
                 const double* bl = bsm + net.boff[l];
                 const int nti = net.nti[l], nto = net.nto[l], act = net.act[l];
                 double2 o[2][8];
+                // two N tiles x two M tiles per step: four independent accumulator chains in flight
 #pragma unroll
-                for (int no = 0; no < 8; ++no) {
+                for (int no = 0; no < 8; no += 2) {
                     if (no < nto) {
-                        const double2 bias = *reinterpret_cast<const double2*>(bl + no * 8 + 2 * q);
-                        double2 acc0 = bias, acc1 = bias;
+                        const bool two = no + 1 < nto;                  // warp-uniform
+                        const double2 bias0 = *reinterpret_cast<const double2*>(bl + no * 8 + 2 * q);
+                        const double2 bias1 = two ? *reinterpret_cast<const double2*>(bl + (no + 1) * 8 + 2 * q)
+                                                  : make_double2(0.0, 0.0);
+                        double2 c00 = bias0, c10 = bias0, c01 = bias1, c11 = bias1;   // c[mt][n]
+                        const double2* W0 = Wl + (no * nti) * 32 + lane;
+                        const double2* W1 = Wl + ((two ? no + 1 : no) * nti) * 32 + lane;
 #pragma unroll
                         for (int ni = 0; ni < 8; ++ni) {
                             if (ni < nti) {
-                                const double2 w = Wl[(no * nti + ni) * 32 + lane];
-                                dmma(acc0.x, acc0.y, a[0][ni].x, w.x);
-                                dmma(acc1.x, acc1.y, a[1][ni].x, w.x);
-                                dmma(acc0.x, acc0.y, a[0][ni].y, w.y);
-                                dmma(acc1.x, acc1.y, a[1][ni].y, w.y);
+                                const double2 w0 = W0[ni * 32];
+                                const double2 w1 = W1[ni * 32];
+                                dmma(c00.x, c00.y, a[0][ni].x, w0.x);
+                                dmma(c10.x, c10.y, a[1][ni].x, w0.x);
+                                dmma(c01.x, c01.y, a[0][ni].x, w1.x);
+                                dmma(c11.x, c11.y, a[1][ni].x, w1.x);
+                                dmma(c00.x, c00.y, a[0][ni].y, w0.y);
+                                dmma(c10.x, c10.y, a[1][ni].y, w0.y);
+                                dmma(c01.x, c01.y, a[0][ni].y, w1.y);
+                                dmma(c11.x, c11.y, a[1][ni].y, w1.y);
                             }
                         }
-                        o[0][no] = make_double2(act_mma(acc0.x, act), act_mma(acc0.y, act));
-                        o[1][no] = make_double2(act_mma(acc1.x, act), act_mma(acc1.y, act));
+                        o[0][no] = make_double2(act_mma(c00.x, act), act_mma(c00.y, act));
+                        o[1][no] = make_double2(act_mma(c10.x, act), act_mma(c10.y, act));
+                        if (two) {
+                            o[0][no + 1] = make_double2(act_mma(c01.x, act), act_mma(c01.y, act));
+                            o[1][no + 1] = make_double2(act_mma(c11.x, act), act_mma(c11.y, act));
+                        } else {
+                            o[0][no + 1] = make_double2(0.0, 0.0);
+                            o[1][no + 1] = make_double2(0.0, 0.0);
+                        }
                     } else {
-                        o[0][no] = make_double2(0.0, 0.0);
-                        o[1][no] = make_double2(0.0, 0.0);
+                        o[0][no] = make_double2(0.0, 0.0); o[1][no] = make_double2(0.0, 0.0);
+                        o[0][no + 1] = make_double2(0.0, 0.0); o[1][no + 1] = make_double2(0.0, 0.0);
                     }
                 }
 #pragma unroll
