@@ -23,7 +23,10 @@ Multigrid::Multigrid(const cfdnn_mesh_desc& m) : mesh_(m) {
     if (m.Ng != 1) throw std::invalid_argument("Multigrid: only Nghost == 1 (O2 stencils) is supported");
     ystretched_ = m.y_stretched != 0;
     semi_ = ystretched_;
-    if (ystretched_) throw std::invalid_argument("Multigrid: y-stretched semi-coarsening not built yet");
+    if (ystretched_) {   // stretched y: x/z semi-coarsening with y-line / x-z RBGS smoothing (:181-207)
+        semi_impl_ = std::make_unique<MultigridSemi>(m);
+        return;
+    }
     const int NzG = m.Nz_global > 0 ? m.Nz_global : m.Nz;
 
     int Nx = m.Nx, Ny = m.Ny, Nz = m.Nz, NzGlob = NzG;
@@ -88,7 +91,15 @@ Multigrid::~Multigrid() {
     for (auto& e : evpool_) { if (e.a) cudaEventDestroy(e.a); if (e.b) cudaEventDestroy(e.b); }
 }
 
+void Multigrid::set_comm(Comm* c) {
+    if (semi_impl_ && c && c->nranks > 1)
+        throw std::invalid_argument("Multigrid: z-slab decomposition of the y-stretched solver is not built yet");
+    comm_ = c;
+    apply_bc_codes();
+}
+
 void Multigrid::set_bc(const int bc[6]) {
+    if (semi_impl_) { semi_impl_->set_bc(bc); for (int d = 0; d < 6; ++d) bc_[d] = bc[d]; return; }
     for (int d = 0; d < 6; ++d) {
         if (bc[d] < 0 || bc[d] > 2) throw std::invalid_argument("set_bc: bad PoissonBC value");
         bc_[d] = bc[d];
@@ -413,6 +424,24 @@ void Multigrid::run_vcycle(int nu1, int nu2, int degree) {
 // ---------------------------------------------------------------- solve (:3550-3786)
 int Multigrid::solve_dev(const double* rhs, double* p, const cfdnn_poisson_cfg& cfg, cudaStream_t st) {
     st_ = st;
+    if (semi_impl_) {
+        cur_ev_ = nullptr;
+        if (time_vcycles && evused_ < 4096) {
+            if (evused_ == evpool_.size()) {
+                EvPair e;
+                CFDNN_CUDA(cudaEventCreate(&e.a));
+                CFDNN_CUDA(cudaEventCreate(&e.b));
+                evpool_.push_back(e);
+            }
+            cur_ev_ = &evpool_[evused_++];
+            CFDNN_CUDA(cudaEventRecord(cur_ev_->a, st_));
+        }
+        const int cyc = semi_impl_->solve_dev(rhs, p, cfg, st);
+        if (cur_ev_) { CFDNN_CUDA(cudaEventRecord(cur_ev_->b, st_)); cur_ev_->cycles = cyc; }
+        stats = semi_impl_->stats;
+        vcycle_count = cyc;
+        return cyc;
+    }
     Level& L0 = *levels_[0];
     const int Ng = mesh_.Ng;
     {

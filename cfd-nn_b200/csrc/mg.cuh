@@ -14,6 +14,7 @@
 //   index(i,j,k) = (k+Hz)*Px*Ny + j*Px + i
 #pragma once
 #include "common.cuh"
+#include "mg_semi.cuh"
 #include <vector>
 #include <memory>
 
@@ -51,7 +52,7 @@ public:
     explicit Multigrid(const cfdnn_mesh_desc& m);
     ~Multigrid();
     void set_bc(const int bc[6]);
-    int num_levels() const { return (int)levels_.size(); }
+    int num_levels() const { return semi_impl_ ? semi_impl_->num_levels() : (int)levels_.size(); }
 
     // rhs/p: device pointers, reference ghosted cell layout. Returns V-cycles used.
     int solve_dev(const double* rhs, double* p, const cfdnn_poisson_cfg& cfg, cudaStream_t st);
@@ -65,7 +66,7 @@ public:
     int acc_vcycles = 0;
     bool time_vcycles = true;
 
-    void set_comm(Comm* c) { comm_ = c; apply_bc_codes(); }
+    void set_comm(Comm* c);
     void collect_timing();          // read the V-cycle events of the solves since the last call (syncs)
     cudaStream_t own_stream();
     const cfdnn_mesh_desc& mesh() const { return mesh_; }
@@ -75,6 +76,7 @@ private:
     std::vector<std::unique_ptr<Level>> levels_;
     int bc_[6] = {2, 2, 1, 1, 2, 2};   // reference defaults (header :185-190)
     bool semi_ = false, ystretched_ = false;
+    std::unique_ptr<MultigridSemi> semi_impl_;   // y-stretched meshes: semi-coarsening solver (mg_semi.cuh)
     DevBuf<double> aS_, aN_, aP_;
     DevBuf<double> partial_;        // per-block partials for reductions
     DevBuf<double> scalars_;        // device scalars: [0]=sum/mean [1]=max [2]=sumsq ...

@@ -40,6 +40,7 @@ struct SemiLevel {
     double dx, dz;
     DevBuf<double> u, f, r;
     DevBuf<double> ta, tcp, tden, trden;
+    DevBuf<double> rbd, rbrd;       // RBGS diagonal 2/dx2 + (aS+aN) + 2/dz2 per row and its reciprocal
 };
 
 struct Comm;

@@ -287,10 +287,14 @@ void Solver::build_rhs(double dt) {
     const bool dist = comm_ && comm_->nranks > 1;
     const int NzG = mesh_.Nz_global > 0 ? mesh_.Nz_global : g_.Nz;
     const double count = (double)g_.Nx * g_.Ny * NzG;
-    CFDNN_LAUNCH_COOP(k_final_sum, 1, 1024, 0, st_, partial_.p, nb, scalars_.p + 0, dist ? 0.0 : count);
-    if (dist) {
-        comm_->allreduce_sum(scalars_.p + 0, 1, st_);
-        CFDNN_LAUNCH_COOP(k_final_sum, 1, 32, 0, st_, scalars_.p + 0, 1, scalars_.p + 0, count);
+    if (g_.y_stretched && !dist) {
+        CFDNN_LAUNCH_COOP(k_seq_sum_cells, 1, 256, 0, st_, g_, div_, scalars_.p + 0, count);   // bit-exact mean
+    } else {
+        CFDNN_LAUNCH_COOP(k_final_sum, 1, 1024, 0, st_, partial_.p, nb, scalars_.p + 0, dist ? 0.0 : count);
+        if (dist) {
+            comm_->allreduce_sum(scalars_.p + 0, 1, st_);
+            CFDNN_LAUNCH_COOP(k_final_sum, 1, 32, 0, st_, scalars_.p + 0, 1, scalars_.p + 0, count);
+        }
     }
     CFDNN_LAUNCH(k_build_rhs, gr, kB, 0, st_, g_, div_, scalars_.p + 1, 1.0 / dt, rhs_);
 }

@@ -379,6 +379,32 @@ k_divergence(Geom g, Vel vel, double* __restrict__ div, double* __restrict__ par
     __syncthreads();
     if (wid == 0) { s = lane < nw ? sh[lane] : 0.0; s = warp_sum(s); if (lane == 0) part[bid] = s; }
 }
+// Interior sum of a cell field in the reference's own order (k, j, i ascending, one running double:
+// compute_mean_divergence_3d, src/solver_time_kernels_projection.cpp:31-52); out[0] = sum,
+// out[1] = sum / count.  Used on y-stretched meshes only: their semi-coarsening Poisson solver
+// amplifies a last-bit change of the right-hand side to ~1e-4 (measured on the reference, see
+// DESIGN.md), so the mean must carry the same bits.  One CTA: all threads stage a chunk in shared
+// memory, thread 0 adds it in order.
+static __global__ void __launch_bounds__(256)
+k_seq_sum_cells(Geom g, const double* __restrict__ a, double* __restrict__ out, double count) {
+    constexpr int CH = 4096;
+    __shared__ double buf[CH];
+    const int n = g.Nx * g.Ny * g.Nz;
+    double acc = 0.0;
+    for (int base = 0; base < n; base += CH) {
+        const int m = min(CH, n - base);
+        __syncthreads();
+        for (int t = threadIdx.x; t < m; t += blockDim.x) {
+            const int q = base + t;
+            const int i = q % g.Nx, j = (q / g.Nx) % g.Ny, k = q / (g.Nx * g.Ny);
+            buf[t] = a[CIDX(i + g.Ng, j + g.Ng, k + g.Ng)];
+        }
+        __syncthreads();
+        if (threadIdx.x == 0)
+            for (int t = 0; t < m; ++t) acc += buf[t];
+    }
+    if (threadIdx.x == 0) { out[0] = acc; out[1] = acc / count; }
+}
 // rhs = (div - mean) * dt_inv on interior cells (src/solver_time.cpp:855-864)
 static __global__ void __launch_bounds__(256)
 k_build_rhs(Geom g, const double* __restrict__ div, const double* __restrict__ mean, double dt_inv,

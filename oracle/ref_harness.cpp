@@ -335,6 +335,7 @@ int run_mg() {
     std::cout.rdbuf(old_cout);
 
     if (!out.empty()) write_f64(out + "_p.f64", p.data());
+    if (!out.empty() && mesh.is_y_stretched()) dump_mesh(mesh, out + "_mesh");
     std::ostringstream js;
     js.precision(17);
     js << "{\"mode\":\"mg\",\"cycles\":" << cycles << ",\"residual\":" << mg.residual()
@@ -412,6 +413,12 @@ int main(int argc, char** argv) {
         if (mode == "bench") return run_step(true);
         if (mode == "mg") return run_mg();
         if (mode == "nn") return run_nn();
+        if (mode == "mesh") {                      // dump the reference's mesh arrays (y metrics of stretched meshes)
+            Mesh mesh = make_mesh();
+            dump_mesh(mesh, arg_s("out", "mesh") + "_mesh");
+            std::printf("{\"mode\":\"mesh\",\"stretched\":%d}\n", mesh.is_y_stretched() ? 1 : 0);
+            return 0;
+        }
     } catch (const std::exception& e) {
         std::fprintf(stderr, "ref_harness: exception: %s\n", e.what());
         return 3;

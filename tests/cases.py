@@ -32,6 +32,38 @@ STEP_CASES = [
 ]
 
 
+# y-stretched meshes (tanh, beta = 2) on the channel box 4pi x [-1,1] x 2pi: semi-coarsening MG
+# (y-line Thomas + x-z RBGS + PCG coarse solve, K-cycle-lite) — SURVEY §8 row M10
+CHANNEL_BOX = dict(stretch_beta=2.0, x1=4 * np.pi, y0=-1.0, y1=1.0, z1=2 * np.pi)
+MG_SEMI_CASES = [
+    ("semi_chan_32x16x32_fixed2", (32, 16, 32), "PPNNPP", 2, dict(smooth=1, **CHANNEL_BOX)),
+    ("semi_chan_32x24x16_conv", (32, 24, 16), "PPNNPP", 0, dict(smooth=1, tol_rhs=1e-8, maxv=20, tol_rel=0, tol=0, **CHANNEL_BOX)),
+    ("semi_dirichlet_x_fixed2", (32, 16, 32), "DDNNPP", 2, dict(smooth=1, **CHANNEL_BOX)),
+    ("semi_neumann_all_fixed1", (16, 16, 32), "NNNNNN", 1, dict(smooth=1, **CHANNEL_BOX)),
+    ("semi_random_rhs_fixed1", (32, 16, 16), "PPNNPP", 1, dict(**CHANNEL_BOX)),
+]
+HARNESS_KEYS = ("stretch_beta", "x1", "y0", "y1", "z1", "tol_rhs", "maxv", "tol_rel", "tol", "tol_abs", "check_interval")
+
+
+# stretched-y channel steps (BASELINE config 3 in miniature): stretched divergence / correction
+# metrics in the operators + the semi-coarsening MG of row M10
+STEP_STRETCHED_CASES = [
+    ("chan_stretched_rk3_tgv", (16, 16, 16), "PPWWPP", "rk3", "skew", 6, 2, "tgv", (1.0, 0, 0), dict(**CHANNEL_BOX)),
+    ("chan_stretched_euler_shear", (32, 16, 16), "PPWWPP", "euler", "central", 4, 2, "shear", (1.0, 0, 0), dict(**CHANNEL_BOX)),
+]
+
+
+def mg_inputs_smooth(N):
+    Nx, Ny, Nz = N
+    x = (np.arange(Nx) + 0.5) / Nx; y = (np.arange(Ny) + 0.5) / Ny; z = (np.arange(Nz) + 0.5) / Nz
+    r = (np.sin(2 * np.pi * x)[None, None, :] * np.cos(np.pi * y)[None, :, None] * np.cos(4 * np.pi * z)[:, None, None]
+         + 0.3 * np.cos(6 * np.pi * x)[None, None, :] * np.cos(3 * np.pi * y)[None, :, None])
+    r = r - r.mean()
+    rhs = np.zeros((Nz + 2, Ny + 2, Nx + 2))
+    rhs[1:-1, 1:-1, 1:-1] = r
+    return rhs, np.zeros_like(rhs)
+
+
 def mg_inputs(N, seed=0):
     Nx, Ny, Nz = N
     rng = np.random.default_rng(seed)
@@ -47,21 +79,27 @@ def mg_inputs(N, seed=0):
 
 def run_mg_ref(case, td):
     name, N, bc, fixed, extra = case
-    rhs, p0 = mg_inputs(N)
+    rhs, p0 = mg_inputs_smooth(N) if extra.get("smooth") else mg_inputs(N)
     rhs.tofile(os.path.join(td, "rhs.f64"))
     p0.tofile(os.path.join(td, "p0.f64"))
     meta = R.run_ref("mg", Nx=N[0], Ny=N[1], Nz=N[2], bc=bc, fixed=fixed, rhs=os.path.join(td, "rhs.f64"),
-                     p0=os.path.join(td, "p0.f64"), out=os.path.join(td, "ref"), **extra)
+                     p0=os.path.join(td, "p0.f64"), out=os.path.join(td, "ref"),
+                     **{k: v for k, v in extra.items() if k in HARNESS_KEYS})
     p = np.fromfile(os.path.join(td, "ref_p.f64")).reshape(rhs.shape)
+    if "stretch_beta" in extra:        # the reference's own y-metric arrays (Mesh::init_stretched_y)
+        meta["_mesh"] = R.load_mesh_arrays(os.path.join(td, "ref_mesh"))
     return meta, p
 
 
-def run_mg_backend(B, case):
+def run_mg_backend(B, case, mesh_arrays=None):
     import ctypes as C
     name, N, bc, fixed, extra = case
-    rhs, p0 = mg_inputs(N)
+    rhs, p0 = mg_inputs_smooth(N) if extra.get("smooth") else mg_inputs(N)
     capi = R.capi
-    md = B.mesh(*N)
+    if mesh_arrays is not None:
+        md = B.stretched_mesh(*N, mesh_arrays, Lx=extra["x1"], Lz=extra["z1"], y_lo=extra["y0"], y_hi=extra["y1"])
+    else:
+        md = B.mesh(*N)
     h = C.c_void_p()
     B.check(B.lib.cfdnn_mg_create(C.byref(md), C.byref(h)))
     try:
@@ -101,11 +139,14 @@ def run_step_ref(case, td, dump_at=""):
     u.tofile(pre + "_u.f64"); v.tofile(pre + "_v.f64"); w.tofile(pre + "_w.f64")
     meta = R.run_ref("step", Nx=N[0], Ny=N[1], Nz=N[2], bc=bc, ti=ti, scheme=scheme, fixed=fixed, nsteps=nsteps,
                      dt=0.01, nu=0.01, init="file:" + pre, fx=force[0], fy=force[1], fz=force[2],
-                     out=os.path.join(td, "ref"), dump_at=dump_at, **extra)
+                     out=os.path.join(td, "ref"), dump_at=dump_at,
+                     **{k: v for k, v in extra.items() if k in HARNESS_KEYS})
+    if "stretch_beta" in extra:
+        meta["_mesh"] = R.load_mesh_arrays(os.path.join(td, "ref_mesh"))
     return meta, R.load_state(os.path.join(td, "ref_final"), *N)
 
 
-def make_solver(B, case, **cfg_over):
+def make_solver(B, case, mesh_arrays=None, **cfg_over):
     name, N, bc, ti, scheme, fixed, nsteps, init, force, extra = case
     kw = dict(nu=0.01, dt=0.01, time_integrator=R.TI[ti], convective_scheme=R.SCHEME[scheme], adaptive_dt=0,
               poisson_fixed_cycles=fixed)
@@ -115,15 +156,19 @@ def make_solver(B, case, **cfg_over):
         kw["poisson_max_vcycles"] = int(extra["maxv"])
     kw.update(cfg_over)
     cfg = B.config(**kw)
-    h = B.solver(B.mesh(*N), cfg, bc, tuple(float(f) for f in force))
+    if mesh_arrays is not None:
+        md = B.stretched_mesh(*N, mesh_arrays, Lx=extra["x1"], Lz=extra["z1"], y_lo=extra["y0"], y_hi=extra["y1"])
+    else:
+        md = B.mesh(*N)
+    h = B.solver(md, cfg, bc, tuple(float(f) for f in force))
     u, v, w = step_init(N, init)
     B.upload(h, "u", u); B.upload(h, "v", v); B.upload(h, "w", w)
     return h
 
 
-def run_step_backend(B, case):
+def run_step_backend(B, case, mesh_arrays=None):
     name, N, bc, ti, scheme, fixed, nsteps, init, force, extra = case
-    h = make_solver(B, case)
+    h = make_solver(B, case, mesh_arrays=mesh_arrays)
     try:
         res = [B.step(h) for _ in range(nsteps)]
         return dict(residuals=res, cycles=B.cycles(h)), B.state(h, *N)
@@ -157,3 +202,26 @@ def compare_states(got, ref, tol, label):
             lim = tol if n != "rhs" else max(tol, 1e-9)
             assert err <= lim, f"{label}: {n} rel L2 {err:.3e} > {lim:.1e}"
     return worst
+
+
+def check_mg_semi(B, oracle, case, tol=1e-10):
+    import pytest
+    with tempfile.TemporaryDirectory() as td:
+        meta, pref = run_mg_ref(case, td)
+    st, p = run_mg_backend(B, case, mesh_arrays=meta["_mesh"])
+    assert st["cycles"] == meta["cycles"]
+    assert st["converged"] == meta["converged"] and st["fixed_cycle_mode"] == meta["fixed_mode"]
+    assert oracle.rel_l2(p, pref) <= tol                        # all cells incl. ghosts
+    for k in ("b_inf", "b_l2", "r0", "r0_l2"):
+        assert st[k] == pytest.approx(meta[k], rel=1e-9, abs=1e-300)
+
+
+def check_step_stretched(B, oracle, case, tol=1e-10):
+    import pytest
+    with tempfile.TemporaryDirectory() as td:
+        meta, ref = run_step_ref(case, td)
+    got_meta, got = run_step_backend(B, case, mesh_arrays=meta["_mesh"])
+    if meta["cycles"]:
+        assert got_meta["cycles"] == meta["cycles"]
+    assert got_meta["residuals"] == pytest.approx(meta["residuals"], rel=1e-9)
+    compare_states(got, ref, tol, case[0])

@@ -91,6 +91,11 @@ FIELD_ID = {"u": 0, "v": 1, "w": 2, "p": 3, "pcorr": 4, "div": 5, "rhs": 6, "nut
             "nueff": 10, "tau_xx": 11, "tau_xy": 12, "tau_yy": 13}
 
 
+def load_mesh_arrays(pre):
+    """y-metric arrays of a stretched mesh as dumped by ref_harness (dump_mesh)"""
+    return {k: np.ascontiguousarray(np.fromfile(f"{pre}_{k}.f64")) for k in ("dyv", "dyc", "aS", "aN", "aP", "yc")}
+
+
 class Backend:
     """Thin Python mirror of the reference's RANSSolver / MultigridPoissonSolver call sequence
     over the C ABI (what INTEGRATION.md's C++ shim does)."""
@@ -104,6 +109,18 @@ class Backend:
     def mesh(self, Nx, Ny, Nz, Lx=2 * np.pi, Ly=2 * np.pi, Lz=2 * np.pi, Ng=1, Nz_global=0, k_offset=0):
         return capi.MeshDesc(Nx=Nx, Ny=Ny, Nz=Nz, Ng=Ng, dx=Lx / Nx, dy=Ly / Ny, dz=Lz / max(Nz_global or Nz, 1),
                              y_stretched=0, Nz_global=Nz_global or Nz, k_offset=k_offset)
+
+    def stretched_mesh(self, Nx, Ny, Nz, pre, Lx=2 * np.pi, Lz=2 * np.pi, y_lo=-1.0, y_hi=1.0):
+        """MeshDesc of a tanh-stretched-y mesh from the metric arrays the oracle dumped
+        (`<pre>_dyv.f64` ... written by ref_harness dump_mesh = the reference's Mesh::init_stretched_y)."""
+        arrs = pre if isinstance(pre, dict) else load_mesh_arrays(pre)
+        md = capi.MeshDesc(Nx=Nx, Ny=Ny, Nz=Nz, Ng=1, dx=Lx / Nx, dy=(y_hi - y_lo) / Ny, dz=Lz / max(Nz, 1),
+                           y_stretched=1, Nz_global=Nz, k_offset=0, y_lo=y_lo, y_hi=y_hi)
+        md.dyv, md.dyc = capi.dptr(arrs["dyv"]), capi.dptr(arrs["dyc"])
+        md.yLap_aS, md.yLap_aN, md.yLap_aP = capi.dptr(arrs["aS"]), capi.dptr(arrs["aN"]), capi.dptr(arrs["aP"])
+        md.yc = capi.dptr(arrs["yc"])
+        md._keep = arrs                      # keep the arrays alive as long as the descriptor
+        return md
 
     def config(self, **kw):
         cfg = capi.Config()

@@ -109,3 +109,26 @@ def test_tgv256_properties(gpu, R):
     div = ((u[1:-1, 1:-1, 2:N + 2] - u[1:-1, 1:-1, 1:N + 1]) + (v[1:-1, 2:N + 2, 1:-1] - v[1:-1, 1:N + 1, 1:-1]) +
            (w[2:N + 2, 1:-1, 1:-1] - w[1:N + 1, 1:-1, 1:-1])) / d
     assert np.abs(div).max() < 1e-6
+
+
+# ---- y-stretched meshes: semi-coarsening MG and BASELINE config 3 in miniature
+@pytest.mark.parametrize("case", cases.MG_SEMI_CASES, ids=[c[0] for c in cases.MG_SEMI_CASES])
+def test_mg_semi_coarsening_matches_reference(gpu, oracle, case):
+    cases.check_mg_semi(gpu, oracle, case)
+
+
+def test_mg_semi_64x32x64_converges_like_reference(gpu, oracle):
+    """channel box 64x32x64, tanh beta=2, convergence mode to 1e-8: same cycle count, same solution"""
+    case = ("semi64", (64, 32, 64), "PPNNPP", 0, dict(smooth=1, tol_rhs=1e-8, maxv=20, tol_rel=0, tol=0, **cases.CHANNEL_BOX))
+    cases.check_mg_semi(gpu, oracle, case)
+
+
+@pytest.mark.parametrize("case", cases.STEP_STRETCHED_CASES, ids=[c[0] for c in cases.STEP_STRETCHED_CASES])
+def test_stretched_channel_step_matches_reference(gpu, oracle, case):
+    cases.check_step_stretched(gpu, oracle, case)
+
+
+def test_stretched_channel_48x32x48_rk3_16_cycles(gpu, oracle):
+    """the production recipe of config 3 (poisson_fixed_cycles = 16, RK3, skew) on a 48x32x48 channel"""
+    case = ("chan48", (48, 32, 48), "PPWWPP", "rk3", "skew", 16, 2, "shear", (1.0, 0, 0), dict(**cases.CHANNEL_BOX))
+    cases.check_step_stretched(gpu, oracle, case)

@@ -23,6 +23,13 @@ def test_mg_solve_matches_reference(sim, oracle, case):
         assert st[k] == pytest.approx(meta[k], rel=1e-4, abs=1e-300)
 
 
+@pytest.mark.parametrize("case", cases.MG_SEMI_CASES, ids=[c[0] for c in cases.MG_SEMI_CASES])
+def test_mg_semi_coarsening_matches_reference(sim, oracle, case):
+    """y-stretched mesh: y-line Thomas (lexicographic line Gauss-Seidel reproduced by wavefronts),
+    x-z RBGS, PCG coarse solve, K-cycle-lite — against MultigridPoissonSolver::solve of the oracle"""
+    cases.check_mg_semi(sim, oracle, case)
+
+
 @pytest.mark.parametrize("case", cases.STEP_CASES, ids=[c[0] for c in cases.STEP_CASES])
 def test_step_matches_reference(sim, oracle, case):
     with tempfile.TemporaryDirectory() as td:
@@ -32,6 +39,11 @@ def test_step_matches_reference(sim, oracle, case):
         assert got_meta["cycles"] == meta["cycles"]
     assert got_meta["residuals"] == pytest.approx(meta["residuals"], rel=1e-9)
     cases.compare_states(got, ref, 1e-10, case[0])
+
+
+@pytest.mark.parametrize("case", cases.STEP_STRETCHED_CASES, ids=[c[0] for c in cases.STEP_STRETCHED_CASES])
+def test_stretched_channel_step_matches_reference(sim, oracle, case):
+    cases.check_step_stretched(sim, oracle, case)
 
 
 def test_invalid_periodic_pair_is_invalid_argument(sim, R):
