@@ -10,9 +10,11 @@ namespace cfdnn {
 namespace {
 
 #ifndef CFDNN_DEVSIM
-constexpr int SEMI_CTA = 1024;        // threads of the single-CTA kernels (y-lines, PCG)
+constexpr int SEMI_CTA = 1024;        // threads per CTA of the serial-dependency kernels (y-lines, PCG)
+constexpr int SEMI_CLUSTER = 8;       // CTAs of the y-line kernel's cluster (portable maximum)
 #else
 constexpr int SEMI_CTA = 64;          // host test double: fewer fibers per barrier
+constexpr int SEMI_CLUSTER = 1;
 #endif
 
 __device__ __forceinline__ size_t sidx(const SemiGeom& g, int i, int j, int k) {
@@ -64,15 +66,30 @@ __global__ void __launch_bounds__(256) k_semi_bc(SemiGeom g, double* __restrict_
     if (t < bc_count(g, DIR)) bc_item<DIR>(g, a, t, res != 0);
 }
 
-// whole apply_bc by one CTA (three passes, block barrier between them)
-__device__ void cta_apply_bc(const SemiGeom& g, double* a) {
+// A team = the CTAs that run one serial-dependency kernel together: one CTA (PCG, host test
+// double) or one thread-block cluster of `n` CTAs (y-line relaxation on the GPU).  team_sync is a
+// barrier with release/acquire ordering of global memory across the whole team.
+struct Team { int rank, n; };
+__device__ __forceinline__ void team_sync(const Team& tm) {
+#ifndef CFDNN_DEVSIM
+    if (tm.n > 1) {
+        asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+        return;
+    }
+#endif
     __syncthreads();
-    for (int t = threadIdx.x; t < bc_count(g, 0); t += blockDim.x) bc_item<0>(g, a, t, false);
-    __syncthreads();
-    for (int t = threadIdx.x; t < bc_count(g, 1); t += blockDim.x) bc_item<1>(g, a, t, false);
-    __syncthreads();
-    for (int t = threadIdx.x; t < bc_count(g, 2); t += blockDim.x) bc_item<2>(g, a, t, false);
-    __syncthreads();
+}
+
+// whole apply_bc by one team (three passes, barrier between them)
+__device__ void cta_apply_bc(const SemiGeom& g, double* a, const Team tm = Team{0, 1}) {
+    const int t0 = tm.rank * blockDim.x + threadIdx.x, dt = tm.n * blockDim.x;
+    team_sync(tm);
+    for (int t = t0; t < bc_count(g, 0); t += dt) bc_item<0>(g, a, t, false);
+    team_sync(tm);
+    for (int t = t0; t < bc_count(g, 1); t += dt) bc_item<1>(g, a, t, false);
+    team_sync(tm);
+    for (int t = t0; t < bc_count(g, 2); t += dt) bc_item<2>(g, a, t, false);
+    team_sync(tm);
 }
 
 // ------------------------------------------------------------------ y-line relaxation
@@ -85,7 +102,7 @@ __device__ void cta_apply_bc(const SemiGeom& g, double* a) {
 // are level constants: SemiGeom::ta/tcp/tden).
 // sm: [3*Ny coefficient copies][LB*Ny line workspace, layout j*LB + l]
 __device__ void cta_y_lines(const SemiGeom& g, double* u, const double* f,
-                            int iterations, double* sm, int LB) {
+                            int iterations, double* sm, int LB, const Team tm = Team{0, 1}) {
     const int Nx = g.Nx, Ny = g.Ny, Nz = g.Nz;
     double* s_a = sm;
     double* s_cp = sm + Ny;
@@ -103,49 +120,53 @@ __device__ void cta_y_lines(const SemiGeom& g, double* u, const double* f,
         for (int d = 0; d <= Nx + Nz - 2; ++d) {
             const int k_lo = max(0, d - (Nx - 1)), k_hi = min(Nz - 1, d);
             const int nl = k_hi - k_lo + 1;
-            for (int l0 = 0; l0 < nl; l0 += LB) {
-                const int nb = min(LB, nl - l0);
+            // this CTA's lines of the wavefront: l = rank, rank + n, ...  (local index ll = l / n)
+            const int mine = nl > tm.rank ? (nl - tm.rank + tm.n - 1) / tm.n : 0;
+            for (int l0 = 0; l0 < mine; l0 += LB) {
+                const int nb = min(LB, mine - l0);
                 // phase A: right-hand sides  inv_dx2*(uE+uW) + inv_dz2*(uF+uB) - f  (+ Dirichlet ghost terms)
                 for (int t = threadIdx.x; t < nb * Ny; t += blockDim.x) {
-                    const int l = t % nb, jl = t / nb;
-                    const int k0 = k_lo + l0 + l, i0 = d - k0;
+                    const int ll = t % nb, jl = t / nb;
+                    const int k0 = k_lo + (l0 + ll) * tm.n + tm.rank, i0 = d - k0;
                     const size_t idx = sidx(g, i0 + 1, jl + 1, k0 + 1);
                     double rhs = g.inv_dx2 * (u[idx + 1] + u[idx - 1]) + g.inv_dz2 * (u[idx + P] + u[idx - P]) - f[idx];
                     if (jl == 0 && dir_lo) rhs += aS1 * u[idx - S];
                     if (jl == Ny - 1 && dir_hi) rhs += aNN * u[idx + S];
-                    ws[jl * LB + l] = rhs;
+                    ws[jl * LB + ll] = rhs;
                 }
                 __syncthreads();
                 // phase B: forward elimination, back substitution
                 if (threadIdx.x < nb) {
-                    const int l = threadIdx.x;
-                    const int k0 = k_lo + l0 + l, i0 = d - k0;
-                    double dp = fdiv(ws[l], s_den[0], s_rden[0]);
-                    ws[l] = dp;
+                    const int ll = threadIdx.x;
+                    const int k0 = k_lo + (l0 + ll) * tm.n + tm.rank, i0 = d - k0;
+                    double dp = fdiv(ws[ll], s_den[0], s_rden[0]);
+                    ws[ll] = dp;
                     for (int jl = 1; jl < Ny; ++jl) {
-                        dp = fdiv(ws[jl * LB + l] - s_a[jl] * dp, s_den[jl], s_rden[jl]);
-                        ws[jl * LB + l] = dp;
+                        dp = fdiv(ws[jl * LB + ll] - s_a[jl] * dp, s_den[jl], s_rden[jl]);
+                        ws[jl * LB + ll] = dp;
                     }
                     size_t idx = sidx(g, i0 + 1, Ny, k0 + 1);
                     double un = dp;
                     u[idx] = un;
                     for (int jl = Ny - 2; jl >= 0; --jl) {
                         idx -= S;
-                        un = ws[jl * LB + l] - s_cp[jl] * un;
+                        un = ws[jl * LB + ll] - s_cp[jl] * un;
                         u[idx] = un;
                     }
                 }
                 __syncthreads();
             }
+            if (tm.n > 1) team_sync(tm);                 // next wavefront reads these lines' new values
         }
-        cta_apply_bc(g, u);
+        cta_apply_bc(g, u, tm);
     }
 }
 
+// grid = ONE thread-block cluster (SEMI_CLUSTER CTAs; 1 CTA on the host test double)
 __global__ void __launch_bounds__(SEMI_CTA) k_semi_ylines(SemiGeom g, double* u,
                                                            const double* f, int iterations, int LB) {
     CFDNN_DYN_SMEM(double, sm_y);
-    cta_y_lines(g, u, f, iterations, sm_y, LB);
+    cta_y_lines(g, u, f, iterations, sm_y, LB, Team{(int)blockIdx.x, (int)gridDim.x});
 }
 
 // ------------------------------------------------------------------ x-z red-black Gauss-Seidel
@@ -574,7 +595,20 @@ void MultigridSemi::smooth_y_lines(int level, int iterations) {
     SemiLevel& L = *levels_[level];
     int LB; size_t bytes;
     yline_smem(L.g, LB, bytes);
+#ifndef CFDNN_DEVSIM
+    // one cluster of SEMI_CLUSTER CTAs: the lines of a wavefront are dealt round-robin to the CTAs,
+    // a cluster barrier separates wavefronts
+    cudaLaunchConfig_t lc{};
+    lc.gridDim = dim3(SEMI_CLUSTER); lc.blockDim = dim3(SEMI_CTA); lc.dynamicSmemBytes = bytes; lc.stream = st_;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = SEMI_CLUSTER; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    lc.attrs = at; lc.numAttrs = 1;
+    CFDNN_CUDA(cudaLaunchKernelEx(&lc, k_semi_ylines, L.g, L.u.p, (const double*)L.f.p, iterations, LB));
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+#else
     CFDNN_LAUNCH_COOP(k_semi_ylines, 1, SEMI_CTA, bytes, st_, L.g, L.u.p, L.f.p, iterations, LB);
+#endif
 }
 
 void MultigridSemi::smooth_xz_rbgs(int level, int iterations) {

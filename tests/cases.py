@@ -127,14 +127,31 @@ def step_init(N, init):
         return R.tgv_init(Nx, Ny, Nz)
     sh = R.shapes(Nx, Ny, Nz)
     u = np.zeros(sh["u"]); v = np.zeros(sh["v"]); w = np.zeros(sh["w"])
+    if init == "pchan":
+        # perturbed channel (BASELINE config 3 style): parabolic profile + 5 % sin/cos perturbation,
+        # deterministic, written in index space (ghosts are set by the solver's BC pass)
+        def ax(n, face):
+            return (np.arange(n) - 1 + (0.0 if face else 0.5))
+        xf, xc = ax(sh["u"][2], True) / Nx, ax(sh["c"][2], False) / Nx
+        yf, yc = ax(sh["v"][1], True) / Ny, ax(sh["c"][1], False) / Ny
+        zf, zc = ax(sh["w"][0], True) / Nz, ax(sh["c"][0], False) / Nz
+        Z, Y, X = np.meshgrid(zc, yc, xf, indexing="ij")
+        u[:] = 4 * Y * (1 - Y) + 0.05 * np.sin(4 * np.pi * X) * np.cos(np.pi * Y) * np.sin(2 * np.pi * Z)
+        Z, Y, X = np.meshgrid(zc, yf, xc, indexing="ij")
+        v[:] = 0.05 * np.cos(4 * np.pi * X) * np.sin(np.pi * Y) * np.cos(2 * np.pi * Z)
+        Z, Y, X = np.meshgrid(zf, yc, xc, indexing="ij")
+        w[:] = 0.05 * np.sin(2 * np.pi * X) * np.sin(np.pi * Y) * np.cos(2 * np.pi * Z)
+        return u, v, w
     j = np.arange(Ny + 1)
     u[0:Nz + 1, 0:Ny + 1, 0:Nx + 2] = (0.01 * np.sin(j * 3.14159 / Ny))[None, :, None]
     return u, v, w
 
 
-def run_step_ref(case, td, dump_at=""):
+def run_step_ref(case, td, dump_at="", perturb=0.0):
     name, N, bc, ti, scheme, fixed, nsteps, init, force, extra = case
     u, v, w = step_init(N, init)
+    if perturb:                                   # round-off-sized relative noise on the initial u
+        u = u * (1.0 + perturb * np.random.default_rng(7).standard_normal(u.shape))
     pre = os.path.join(td, "in")
     u.tofile(pre + "_u.f64"); v.tofile(pre + "_v.f64"); w.tofile(pre + "_w.f64")
     meta = R.run_ref("step", Nx=N[0], Ny=N[1], Nz=N[2], bc=bc, ti=ti, scheme=scheme, fixed=fixed, nsteps=nsteps,
@@ -179,13 +196,30 @@ def run_step_backend(B, case, mesh_arrays=None):
 FIELDS = ("u", "v", "w", "p", "pcorr", "div", "rhs")
 
 
-def compare_states(got, ref, tol, label):
+def field_errors(got, ref):
+    """per-field error measure used by the sensitivity gate: max |a-b| / max |b| over the interior"""
+    out = {}
+    for n in FIELDS:
+        a, b = R.interior(n, got[n]), R.interior(n, ref[n])
+        out[n] = np.abs(a - b).max() / max(np.abs(b).max(), 1e-300)
+    return out
+
+
+def compare_states(got, ref, tol, label, vel_joint=False):
     """per-field relative L2 over interior faces/cells (BASELINE.json gate); fields that are
-    ~0 (e.g. w of a 2-D-like flow) are compared by absolute max instead."""
+    ~0 (e.g. w of a 2-D-like flow) are compared by absolute max instead.  vel_joint: velocity
+    components that are tiny next to the flow speed (|v| ~ 1e-7 |u| in a sheared channel) are
+    measured against the flow speed, not against their own round-off-sized norm."""
     worst = {}
+    vmax = max(np.abs(R.interior(n, ref[n])).max() for n in ("u", "v", "w"))
     for n in FIELDS:
         a, b = R.interior(n, got[n]), R.interior(n, ref[n])
         scale = np.abs(b).max()
+        if vel_joint and n in ("u", "v", "w") and scale < 1e-4 * vmax:
+            err = np.abs(a - b).max() / vmax
+            worst[n] = err
+            assert err <= tol, f"{label}: {n} abs err / |vel|max {err:.3e} > {tol:.1e}"
+            continue
         if n in ("div",):
             # divergence is a difference of O(1) numbers: compare against the velocity-gradient scale
             err = np.abs(a - b).max()
@@ -224,4 +258,25 @@ def check_step_stretched(B, oracle, case, tol=1e-10):
     if meta["cycles"]:
         assert got_meta["cycles"] == meta["cycles"]
     assert got_meta["residuals"] == pytest.approx(meta["residuals"], rel=1e-9)
-    compare_states(got, ref, tol, case[0])
+    compare_states(got, ref, tol, case[0], vel_joint=True)
+
+
+def check_step_within_reference_sensitivity(B, oracle, case, factor=100.0, floor=1e-10):
+    """The reference's semi-coarsening solver (PCG run past its attainable accuracy inside a
+    K-cycle) is not a contraction for round-off: perturbing the reference's OWN input by 1e-15
+    moves its output by 1e-9 ... 1e-4.  Where the backend cannot be bit-identical
+    to x86 (GPU momentum kernels differ from the CPU build in the last bit), parity is therefore
+    gated by that measured sensitivity: error <= max(floor, factor * |ref(perturbed) - ref|)."""
+    with tempfile.TemporaryDirectory() as td:
+        meta, ref = run_step_ref(case, td)
+    with tempfile.TemporaryDirectory() as td:
+        _, ref_p = run_step_ref(case, td, perturb=1e-15)
+    sens = field_errors(ref_p, ref)
+    got_meta, got = run_step_backend(B, case, mesh_arrays=meta["_mesh"])
+    if meta["cycles"]:
+        assert got_meta["cycles"] == meta["cycles"]
+    err = field_errors(got, ref)
+    for n in FIELDS:
+        lim = max(floor, factor * sens[n])
+        assert err[n] <= lim, f"{case[0]}: {n} err {err[n]:.3e} > {lim:.3e} (reference sensitivity {sens[n]:.3e})"
+    return err, sens

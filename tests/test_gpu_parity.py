@@ -130,5 +130,6 @@ def test_stretched_channel_step_matches_reference(gpu, oracle, case):
 
 def test_stretched_channel_48x32x48_rk3_16_cycles(gpu, oracle):
     """the production recipe of config 3 (poisson_fixed_cycles = 16, RK3, skew) on a 48x32x48 channel"""
-    case = ("chan48", (48, 32, 48), "PPWWPP", "rk3", "skew", 16, 2, "shear", (1.0, 0, 0), dict(**cases.CHANNEL_BOX))
-    cases.check_step_stretched(gpu, oracle, case)
+    case = ("chan48", (48, 32, 48), "PPWWPP", "rk3", "skew", 16, 2, "pchan", (1.0, 0, 0), dict(**cases.CHANNEL_BOX))
+    err, sens = cases.check_step_within_reference_sensitivity(gpu, oracle, case)
+    print("chan48 errors", err, "reference sensitivity to 1e-15 input noise", sens)
