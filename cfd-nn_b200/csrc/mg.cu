@@ -19,7 +19,10 @@ constexpr int KZ = 8;
 // create_hierarchy (:155-230) + compute_gershgorin_bounds (:232-305)
 Multigrid::Multigrid(const cfdnn_mesh_desc& m) : mesh_(m) {
     require_device();
-    if (m.Nz <= 1) throw std::invalid_argument("Multigrid: 2-D meshes are handled by Multigrid2D");
+    if (m.Nz <= 1) {     // 2-D mesh (reference Mesh::is2D()): 5-point solver, whole V-cycles per launch
+        mg2d_impl_ = std::make_unique<Multigrid2D>(m);
+        return;
+    }
     if (m.Ng != 1) throw std::invalid_argument("Multigrid: only Nghost == 1 (O2 stencils) is supported");
     ystretched_ = m.y_stretched != 0;
     semi_ = ystretched_;
@@ -92,13 +95,14 @@ Multigrid::~Multigrid() {
 }
 
 void Multigrid::set_comm(Comm* c) {
-    if (semi_impl_ && c && c->nranks > 1)
-        throw std::invalid_argument("Multigrid: z-slab decomposition of the y-stretched solver is not built yet");
+    if ((semi_impl_ || mg2d_impl_) && c && c->nranks > 1)
+        throw std::invalid_argument("Multigrid: z-slab decomposition of the y-stretched / 2-D solvers is not built");
     comm_ = c;
     apply_bc_codes();
 }
 
 void Multigrid::set_bc(const int bc[6]) {
+    if (mg2d_impl_) { mg2d_impl_->set_bc(bc); for (int d = 0; d < 4; ++d) bc_[d] = bc[d]; return; }
     if (semi_impl_) { semi_impl_->set_bc(bc); for (int d = 0; d < 6; ++d) bc_[d] = bc[d]; return; }
     for (int d = 0; d < 6; ++d) {
         if (bc[d] < 0 || bc[d] > 2) throw std::invalid_argument("set_bc: bad PoissonBC value");
@@ -424,7 +428,7 @@ void Multigrid::run_vcycle(int nu1, int nu2, int degree) {
 // ---------------------------------------------------------------- solve (:3550-3786)
 int Multigrid::solve_dev(const double* rhs, double* p, const cfdnn_poisson_cfg& cfg, cudaStream_t st) {
     st_ = st;
-    if (semi_impl_) {
+    if (semi_impl_ || mg2d_impl_) {
         cur_ev_ = nullptr;
         if (time_vcycles && evused_ < 4096) {
             if (evused_ == evpool_.size()) {
@@ -436,9 +440,9 @@ int Multigrid::solve_dev(const double* rhs, double* p, const cfdnn_poisson_cfg& 
             cur_ev_ = &evpool_[evused_++];
             CFDNN_CUDA(cudaEventRecord(cur_ev_->a, st_));
         }
-        const int cyc = semi_impl_->solve_dev(rhs, p, cfg, st);
+        const int cyc = mg2d_impl_ ? mg2d_impl_->solve_dev(rhs, p, cfg, st, plane2d_, dup2d_) : semi_impl_->solve_dev(rhs, p, cfg, st);
         if (cur_ev_) { CFDNN_CUDA(cudaEventRecord(cur_ev_->b, st_)); cur_ev_->cycles = cyc; }
-        stats = semi_impl_->stats;
+        stats = mg2d_impl_ ? mg2d_impl_->stats : semi_impl_->stats;
         vcycle_count = cyc;
         return cyc;
     }

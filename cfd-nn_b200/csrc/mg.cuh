@@ -15,6 +15,7 @@
 #pragma once
 #include "common.cuh"
 #include "mg_semi.cuh"
+#include "mg2d.cuh"
 #include <vector>
 #include <memory>
 
@@ -52,7 +53,13 @@ public:
     explicit Multigrid(const cfdnn_mesh_desc& m);
     ~Multigrid();
     void set_bc(const int bc[6]);
-    int num_levels() const { return semi_impl_ ? semi_impl_->num_levels() : (int)levels_.size(); }
+    int num_levels() const {
+        return mg2d_impl_ ? mg2d_impl_->num_levels() : semi_impl_ ? semi_impl_->num_levels() : (int)levels_.size();
+    }
+    // 2-D meshes: which z-plane of the caller's arrays holds the data (0 = the reference's 2-D
+    // convention, the default; 1 = interior plane of the solver's periodic-z embedding, which also
+    // wants the result copied to the two ghost planes)
+    void set_2d_plane(int plane, bool dup) { plane2d_ = plane; dup2d_ = dup; }
 
     // rhs/p: device pointers, reference ghosted cell layout. Returns V-cycles used.
     int solve_dev(const double* rhs, double* p, const cfdnn_poisson_cfg& cfg, cudaStream_t st);
@@ -76,6 +83,9 @@ private:
     std::vector<std::unique_ptr<Level>> levels_;
     int bc_[6] = {2, 2, 1, 1, 2, 2};   // reference defaults (header :185-190)
     bool semi_ = false, ystretched_ = false;
+    std::unique_ptr<Multigrid2D> mg2d_impl_;     // Nz == 1: 2-D solver (mg2d.cuh)
+    int plane2d_ = 0;
+    bool dup2d_ = false;
     std::unique_ptr<MultigridSemi> semi_impl_;   // y-stretched meshes: semi-coarsening solver (mg_semi.cuh)
     DevBuf<double> aS_, aN_, aP_;
     DevBuf<double> partial_;        // per-block partials for reductions

@@ -53,7 +53,39 @@ STEP_STRETCHED_CASES = [
 ]
 
 
+# 2-D meshes (Nz == 1, BASELINE config 1): arrays keep 3 z-planes, the data lives in plane 0
+# (include/fields.hpp:18-19)
+MG_2D_CASES = [
+    ("mg2d_channel_32x64_fixed3", (32, 64, 1), "PPNN", 3, {}),
+    ("mg2d_periodic_32x32_conv", (32, 32, 1), "PPPP", 0, dict(tol_rhs=1e-8, maxv=30, tol_rel=0, tol=0)),
+    ("mg2d_dirichlet_mixed_fixed2", (64, 32, 1), "DNND", 2, {}),
+    ("mg2d_neumann_16x48_conv", (16, 48, 1), "NNNN", 0, dict(tol_rhs=1e-6, maxv=20)),
+    ("mg2d_single_level_8x8", (8, 8, 1), "PPNN", 2, {}),
+    ("mg2d_stretched_semi_32x32_fixed2", (32, 32, 1), "PPNN", 2, dict(smooth=1, **CHANNEL_BOX)),
+    ("mg2d_stretched_semi_64x24_conv", (64, 24, 1), "PPNN", 0, dict(smooth=1, tol_rhs=1e-6, maxv=12, tol_rel=0, tol=0, **CHANNEL_BOX)),
+]
+
+
+def mg_inputs_2d(N, smooth=False, seed=0):
+    Nx, Ny, _ = N
+    if smooth:
+        x = (np.arange(Nx) + 0.5) / Nx; y = (np.arange(Ny) + 0.5) / Ny
+        r = np.sin(2 * np.pi * x)[None, :] * np.cos(np.pi * y)[:, None] + 0.3 * np.cos(6 * np.pi * x)[None, :] * np.cos(3 * np.pi * y)[:, None]
+        p = np.zeros((Ny, Nx))
+    else:
+        rng = np.random.default_rng(seed)
+        r = rng.standard_normal((Ny, Nx))
+        p = 0.1 * rng.standard_normal((Ny, Nx))
+    r = r - r.mean()
+    rhs = np.zeros((3, Ny + 2, Nx + 2)); p0 = np.zeros_like(rhs)
+    rhs[0, 1:-1, 1:-1] = r
+    p0[0, 1:-1, 1:-1] = p
+    return rhs, p0
+
+
 def mg_inputs_smooth(N):
+    if N[2] == 1:
+        return mg_inputs_2d(N, smooth=True)
     Nx, Ny, Nz = N
     x = (np.arange(Nx) + 0.5) / Nx; y = (np.arange(Ny) + 0.5) / Ny; z = (np.arange(Nz) + 0.5) / Nz
     r = (np.sin(2 * np.pi * x)[None, None, :] * np.cos(np.pi * y)[None, :, None] * np.cos(4 * np.pi * z)[:, None, None]
@@ -65,6 +97,8 @@ def mg_inputs_smooth(N):
 
 
 def mg_inputs(N, seed=0):
+    if N[2] == 1:
+        return mg_inputs_2d(N, seed=seed)
     Nx, Ny, Nz = N
     rng = np.random.default_rng(seed)
     shp = (Nz + 2, Ny + 2, Nx + 2)
@@ -103,7 +137,7 @@ def run_mg_backend(B, case, mesh_arrays=None):
     h = C.c_void_p()
     B.check(B.lib.cfdnn_mg_create(C.byref(md), C.byref(h)))
     try:
-        arr = (C.c_int * 6)(*[R.PBC[c] for c in bc])
+        arr = (C.c_int * 6)(*([R.PBC[c] for c in bc] + [2, 2])[:6])
         B.check(B.lib.cfdnn_mg_set_bc(h, arr))
         cfg = capi.PoissonCfg()
         B.lib.cfdnn_poisson_cfg_default(C.byref(cfg))
@@ -280,3 +314,16 @@ def check_step_within_reference_sensitivity(B, oracle, case, factor=100.0, floor
         lim = max(floor, factor * sens[n])
         assert err[n] <= lim, f"{case[0]}: {n} err {err[n]:.3e} > {lim:.3e} (reference sensitivity {sens[n]:.3e})"
     return err, sens
+
+
+def check_mg_2d(B, oracle, case, tol=1e-12):
+    import pytest
+    with tempfile.TemporaryDirectory() as td:
+        meta, pref = run_mg_ref(case, td)
+    st, p = run_mg_backend(B, case, mesh_arrays=meta.get("_mesh"))
+    assert st["cycles"] == meta["cycles"]
+    assert st["converged"] == meta["converged"] and st["fixed_cycle_mode"] == meta["fixed_mode"]
+    assert oracle.rel_l2(p[0], pref[0]) <= tol                  # plane 0, all cells incl. ghosts (:3769-3775)
+    assert not p[1:].any() and not pref[1:].any()               # the other planes are never touched
+    for k in ("b_inf", "b_l2", "r0", "r0_l2"):
+        assert st[k] == pytest.approx(meta[k], rel=1e-9, abs=1e-300)

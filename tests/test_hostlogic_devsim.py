@@ -23,6 +23,12 @@ def test_mg_solve_matches_reference(sim, oracle, case):
         assert st[k] == pytest.approx(meta[k], rel=1e-4, abs=1e-300)
 
 
+@pytest.mark.parametrize("case", cases.MG_2D_CASES, ids=[c[0] for c in cases.MG_2D_CASES])
+def test_mg_2d_matches_reference(sim, oracle, case):
+    """2-D meshes (Nz == 1): 5-point Chebyshev / Jacobi V-cycles, x-only semi-coarsening when y is stretched"""
+    cases.check_mg_2d(sim, oracle, case)
+
+
 @pytest.mark.parametrize("case", cases.MG_SEMI_CASES, ids=[c[0] for c in cases.MG_SEMI_CASES])
 def test_mg_semi_coarsening_matches_reference(sim, oracle, case):
     """y-stretched mesh: y-line Thomas (lexicographic line Gauss-Seidel reproduced by wavefronts),
