@@ -516,9 +516,10 @@ void NNClosure::set_params(double nu, double delta, double u_ref, double k_min, 
 
 void NNClosure::update_device(const Geom& g, const double* yc, double y_lo, double y_hi, const Vel& vel,
                               const double* k, const double* omega, double* nu_t, double* txx, double* txy,
-                              double* tyy, cudaStream_t st) {
+                              double* tyy, cudaStream_t st, int data_plane) {
     const bool is2d = g.Nz == 1;
-    const int plane0 = is2d ? 0 : g.Ng;          // 2-D accessors address plane k = 0 (include/fields.hpp:18-19)
+    // 2-D accessors address plane k = 0 (include/fields.hpp:18-19); the solver keeps 2-D data in plane Ng
+    const int plane0 = data_plane >= 0 ? data_plane : (is2d ? 0 : g.Ng);
     const int nplanes = is2d ? 1 : g.Nz;
     if ((size_t)nplanes > kflag_.n) kflag_.alloc(nplanes);
     const dim3 blk(32, 4, 1);

@@ -54,7 +54,7 @@ public:
     // device-resident twin used by Solver::step.  yc: device array of Ny+2Ng cell-centre y.
     void update_device(const Geom& g, const double* yc, double y_lo, double y_hi, const Vel& vel,
                        const double* k, const double* omega, double* nu_t, double* txx, double* txy,
-                       double* tyy, cudaStream_t st);
+                       double* tyy, cudaStream_t st, int data_plane = -1);
     // MLP::forward on a batch: x[n][in] -> y[n][out]
     void forward_host(const double* x, double* y, size_t n);
     double last_ms = 0.0;

@@ -35,14 +35,18 @@ Solver::Solver(const cfdnn_mesh_desc& m, const cfdnn_config& c) : mesh_(m), cfg_
     require_device();
     if (m.Nx < 1 || m.Ny < 1 || m.Nz < 1) throw std::invalid_argument("Solver: bad mesh size");
     if (m.Ng != 1) throw std::invalid_argument("Solver: only Nghost == 1 (O2 schemes) is supported");
-    if (m.Nz == 1) throw std::invalid_argument("Solver: 2-D meshes (Nz == 1) are not built yet");
     if (c.convective_scheme != CFDNN_CONV_CENTRAL && c.convective_scheme != CFDNN_CONV_SKEW)
         throw std::invalid_argument("Solver: convective_scheme must be central or skew");
     if (c.time_integrator < CFDNN_TI_EULER || c.time_integrator > CFDNN_TI_RK3)
         throw std::invalid_argument("Solver: bad time_integrator");
-    is2d_ = false;
+    // 2-D meshes (reference Mesh::is2D()) run as one periodic z-plane of the 3-D kernels: with w = 0
+    // and identical z-neighbour planes every z term of the 3-D operators is an exact 0.0 added last,
+    // which leaves the 2-D kernels' arithmetic (include/solver_kernels.hpp:341-426, 1282-1374, ...)
+    // bit for bit.  The data plane is k = Ng on the device and k = 0 on the host (fields.hpp:18-19).
+    is2d_ = m.Nz == 1;
+    if (is2d_ && !(mesh_.dz > 0.0)) mesh_.dz = 1.0;
     const int Ng = m.Ng, Nx = m.Nx, Ny = m.Ny, Nz = m.Nz;
-    g_ = make_geom(m);
+    g_ = make_geom(mesh_);
     su_ = (size_t)g_.up * (Nz + 2 * Ng);
     sv_ = (size_t)g_.vp * (Nz + 2 * Ng);
     sw_ = (size_t)g_.wp * (Nz + 1 + 2 * Ng);
@@ -88,6 +92,7 @@ Solver::Solver(const cfdnn_mesh_desc& m, const cfdnn_config& c) : mesh_(m), cfg_
     CFDNN_CUDA(cudaEventCreate(&ev1_));
 
     mg_ = std::make_unique<Multigrid>(m);
+    if (is2d_) mg_->set_2d_plane(Ng, /*dup=*/true);
     dt_ = c.dt;
     set_velocity_bc(vbc_);
 }
@@ -121,8 +126,9 @@ void Solver::set_velocity_bc(const int bc[6]) {
             throw std::invalid_argument(std::string("Periodic BC in ") + axis[a] + " requires both " + axis[a] +
                                         "_lo and " + axis[a] + "_hi to be Periodic");
     for (int d = 0; d < 6; ++d) vbc_[d] = bc[d];
+    if (is2d_) vbc_[4] = vbc_[5] = CFDNN_VBC_PERIODIC;          // the embedding plane is periodic in z
     int pbc[6];
-    for (int d = 0; d < 6; ++d) pbc[d] = bc[d] == CFDNN_VBC_PERIODIC ? CFDNN_PBC_PERIODIC : CFDNN_PBC_NEUMANN;
+    for (int d = 0; d < 6; ++d) pbc[d] = vbc_[d] == CFDNN_VBC_PERIODIC ? CFDNN_PBC_PERIODIC : CFDNN_PBC_NEUMANN;
     mg_->set_bc(pbc);
     update_links();
 }
@@ -168,13 +174,33 @@ size_t Solver::field_size(int field) const { size_t n; field_ptr(field, &n); ret
 void Solver::upload(int field, const double* host, size_t n) {
     size_t want; double* d = field_ptr(field, &want);
     if (n != want) throw std::invalid_argument("upload: size mismatch for field " + std::to_string(field));
-    CFDNN_CUDA(cudaMemcpyAsync(d, host, n * sizeof(double), cudaMemcpyHostToDevice, st_));
+    if (is2d_) {     // host plane 0 holds the data: replicate it into every device plane
+        const size_t pl = plane_elems(field), np = n / pl;
+        for (size_t k = 0; k < np; ++k)
+            CFDNN_CUDA(cudaMemcpyAsync(d + k * pl, host, pl * sizeof(double), cudaMemcpyHostToDevice, st_));
+    } else {
+        CFDNN_CUDA(cudaMemcpyAsync(d, host, n * sizeof(double), cudaMemcpyHostToDevice, st_));
+    }
     CFDNN_CUDA(cudaStreamSynchronize(st_));
+}
+size_t Solver::plane_elems(int field) const {
+    switch (field) {
+        case CFDNN_F_U: return (size_t)g_.up;
+        case CFDNN_F_V: return (size_t)g_.vp;
+        case CFDNN_F_W: return (size_t)g_.wp;
+        default: return (size_t)g_.cp;
+    }
 }
 void Solver::download(int field, double* host, size_t n) {
     size_t want; double* d = field_ptr(field, &want);
     if (n != want) throw std::invalid_argument("download: size mismatch for field " + std::to_string(field));
-    CFDNN_CUDA(cudaMemcpyAsync(host, d, n * sizeof(double), cudaMemcpyDeviceToHost, st_));
+    if (is2d_) {     // device plane Ng -> host plane 0; the reference never touches the other planes (zeros)
+        const size_t pl = plane_elems(field);
+        std::fill(host + pl, host + n, 0.0);
+        CFDNN_CUDA(cudaMemcpyAsync(host, d + (size_t)g_.Ng * pl, pl * sizeof(double), cudaMemcpyDeviceToHost, st_));
+    } else {
+        CFDNN_CUDA(cudaMemcpyAsync(host, d, n * sizeof(double), cudaMemcpyDeviceToHost, st_));
+    }
     CFDNN_CUDA(cudaStreamSynchronize(st_));
     check_launch("download");
 }
@@ -263,6 +289,15 @@ void Solver::momentum(const Vel& in, Vel& out, double dt, bool seam_average) {
     const int Ng = g_.Ng;
     const dim3 gr = grid3(g_.Nx + 1 + 2 * Ng, g_.Ny + 1 + 2 * Ng, g_.Nz + 1 + 2 * Ng);
     const bool alias = out.u == vel_.u;
+    if (is2d_) {
+        // the operators read vel_'s z-neighbour planes: make them copies of the data plane (x/y
+        // ghosts included, stale or not — exactly what the reference's 2-D kernels would read)
+        const size_t up = (size_t)g_.up, vp = (size_t)g_.vp;
+        for (int k = 0; k <= 2; k += 2) {
+            CFDNN_CUDA(cudaMemcpyAsync(vel_.u + k * up, vel_.u + up, up * sizeof(double), cudaMemcpyDeviceToDevice, st_));
+            CFDNN_CUDA(cudaMemcpyAsync(vel_.v + k * vp, vel_.v + vp, vp * sizeof(double), cudaMemcpyDeviceToDevice, st_));
+        }
+    }
     const Vel src_in = in;                       // copies of the pointer triples (in may be vel_ itself)
     const Vel dst = alias ? conv_ : out;
     if (cfg_.convective_scheme == CFDNN_CONV_SKEW)
@@ -276,9 +311,11 @@ void Solver::blend(const Vel& a, const Vel& b, const Vel& c, double a1, double a
     const dim3 gr = grid3(g_.Nx + 1, g_.Ny + 1, g_.Nz + 1);
     CFDNN_LAUNCH(k_blend, gr, kB, 0, st_, g_, a, b, c, a1, a2);
 }
-void Solver::compute_divergence(const Vel& v) {
+void Solver::compute_divergence(const Vel& v, bool uniform_dy) {
     const dim3 gr = grid3(g_.Nx, g_.Ny, g_.Nz);
-    CFDNN_LAUNCH_COOP(k_divergence, gr, kB, 0, st_, g_, v, div_, partial_.p);
+    Geom g = g_;
+    if (uniform_dy) g.y_stretched = 0;
+    CFDNN_LAUNCH_COOP(k_divergence, gr, kB, 0, st_, g, v, div_, partial_.p);
 }
 // mean divergence + rhs (src/solver_time.cpp:812-866; src/solver.cpp:1920-2078)
 void Solver::build_rhs(double dt) {
@@ -367,7 +404,9 @@ void Solver::project_velocity(Vel* which, double dt) {
     const bool need_swap = which != &vel_;
     if (need_swap) std::swap(vel_, *which);
     apply_velocity_bc();
-    compute_divergence(vel_);
+    // the RK path's inline 2-D divergence divides by the UNIFORM dy even on a y-stretched mesh
+    // (src/solver_time.cpp:789-806; the 3-D branch and the Euler path use dyv[j]) — reproduced as is
+    compute_divergence(vel_, /*uniform_dy=*/is2d_);
     build_rhs(dt);
     cfdnn_poisson_cfg pc;
     cfdnn_poisson_cfg_default(&pc);
@@ -457,7 +496,8 @@ void Solver::build_nu_eff() {
 
 void Solver::update_turbulence() {
     if (!nn_) return;
-    nn_->update_device(g_, yc_.p, mesh_.y_lo, mesh_.y_hi, vel_, k_, omega_, nut_, tau_[0], tau_[1], tau_[2], st_);
+    nn_->update_device(g_, yc_.p, mesh_.y_lo, mesh_.y_hi, vel_, k_, omega_, nut_, tau_[0], tau_[1], tau_[2], st_,
+                       /*data_plane=*/g_.Ng);
 }
 
 void Solver::check_nan(int step) {                              // check_for_nan_inf :3195-3350
@@ -554,8 +594,8 @@ double Solver::compute_adaptive_dt() {                          // src/solver.cp
     const double cfl_xz = cfg_.CFL_xz > 0 ? cfg_.CFL_xz : cfg_.CFL_max;
     const double dt_cfl_x = cfl_xz * mesh_.dx / u_abs_max;
     const double dt_cfl_y = cfg_.CFL_max / v_dy_ratio_max;
-    const double dt_cfl_z = cfl_xz * mesh_.dz / w_abs_max;
-    const double dx_min = std::min({mesh_.dx, dy_min_, mesh_.dz});
+    const double dt_cfl_z = is2d_ ? 1e10 : cfl_xz * mesh_.dz / w_abs_max;          // :3688
+    const double dx_min = is2d_ ? std::min(mesh_.dx, dy_min_) : std::min({mesh_.dx, dy_min_, mesh_.dz});
     const double dt_diff = 0.25 * dx_min * dx_min / nu_eff_max;
     double dt_new = cfg_.dt_safety * std::min({dt_cfl_x, dt_cfl_y, dt_cfl_z, dt_diff});
     if (comm_ && comm_->nranks > 1) {

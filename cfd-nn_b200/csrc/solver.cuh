@@ -54,6 +54,7 @@ public:
     void comm_init(Comm* c);
 
     size_t field_size(int field) const;
+    size_t plane_elems(int field) const;
     void upload(int field, const double* host, size_t n);
     void download(int field, double* host, size_t n);
     void initialize();                    // apply_velocity_bc on the uploaded velocity (:1060-1062)
@@ -103,7 +104,7 @@ private:
     void apply_velocity_bc();                                   // solver_operators.cpp:43-491
     void compute_convective_term();                             // :493-867
     void compute_diffusive_term();                              // :869-1070
-    void compute_divergence(const Vel& v);                      // :1072-1245
+    void compute_divergence(const Vel& v, bool uniform_dy = false);                      // :1072-1245
     void correct_velocity();                                    // :1259-1604
     void blend(const Vel& a, const Vel& b, const Vel& c, double a1, double a2);  // c = a1 a + a2 b
     void momentum(const Vel& in, Vel& out, double dt, bool seam_average);   // fused conv + diff + advance

@@ -157,6 +157,8 @@ def run_mg_backend(B, case, mesh_arrays=None):
 def step_init(N, init):
     """Initial velocity exactly as oracle/ref_harness.cpp builds it (so goldens need no oracle run)."""
     Nx, Ny, Nz = N
+    if Nz == 1:
+        return step_init_2d(N, init)
     if init == "tgv":
         return R.tgv_init(Nx, Ny, Nz)
     sh = R.shapes(Nx, Ny, Nz)
@@ -179,6 +181,34 @@ def step_init(N, init):
     j = np.arange(Ny + 1)
     u[0:Nz + 1, 0:Ny + 1, 0:Nx + 2] = (0.01 * np.sin(j * 3.14159 / Ny))[None, :, None]
     return u, v, w
+
+
+def step_init_2d(N, init):
+    """2-D meshes: 3 z-planes (4 for w), data in plane 0 (include/fields.hpp:18-19)"""
+    Nx, Ny, _ = N
+    sh = R.shapes(Nx, Ny, 1)
+    u = np.zeros(sh["u"]); v = np.zeros(sh["v"]); w = np.zeros(sh["w"])
+    xf = (np.arange(Nx + 3) - 1) / Nx; xc = (np.arange(Nx + 2) - 0.5) / Nx
+    yf = (np.arange(Ny + 3) - 1) / Ny; yc = (np.arange(Ny + 2) - 0.5) / Ny
+    if init == "tgv":
+        u[0] = np.cos(2 * np.pi * yc)[:, None] * np.sin(2 * np.pi * xf)[None, :]
+        v[0] = -np.sin(2 * np.pi * yf)[:, None] * np.cos(2 * np.pi * xc)[None, :]
+    elif init == "pchan":
+        u[0] = (4 * yc * (1 - yc))[:, None] + 0.05 * np.cos(np.pi * yc)[:, None] * np.sin(4 * np.pi * xf)[None, :]
+        v[0] = 0.05 * np.sin(np.pi * yf)[:, None] * np.cos(4 * np.pi * xc)[None, :]
+    else:   # "shear": Poiseuille-like profile, zero at the walls
+        u[0] = (0.5 * 4 * yc * (1 - yc))[:, None] * np.ones(Nx + 3)[None, :]
+    return u, v, w
+
+
+# 2-D steps (BASELINE config 1: 2-D channel Nx=32 Ny=64 nu=0.01, Euler; plus RK and periodic variants)
+STEP_2D_CASES = [
+    ("poiseuille2d_32x64_euler", (32, 64, 1), "PPWWPP", "euler", "central", 8, 3, "shear", (1.0, 0, 0), dict(x1=2 * np.pi, y0=-1.0, y1=1.0)),
+    ("tgv2d_32_rk3_skew", (32, 32, 1), "PPPPPP", "rk3", "skew", 6, 2, "tgv", (0, 0, 0), {}),
+    ("chan2d_rk2_conv", (32, 32, 1), "PPWWPP", "rk2", "central", 0, 2, "pchan", (1.0, 0, 0), dict(tol_rhs=1e-8, maxv=30, x1=4 * np.pi, y0=-1.0, y1=1.0)),
+    ("chan2d_euler_skew_conv", (16, 32, 1), "PPWWPP", "euler", "skew", 0, 2, "pchan", (1.0, 0, 0), dict(tol_rhs=1e-6, maxv=20, x1=4 * np.pi, y0=-1.0, y1=1.0)),
+    ("chan2d_stretched_rk3", (32, 32, 1), "PPWWPP", "rk3", "skew", 6, 2, "pchan", (1.0, 0, 0), dict(**CHANNEL_BOX)),
+]
 
 
 def run_step_ref(case, td, dump_at="", perturb=0.0):
@@ -210,7 +240,8 @@ def make_solver(B, case, mesh_arrays=None, **cfg_over):
     if mesh_arrays is not None:
         md = B.stretched_mesh(*N, mesh_arrays, Lx=extra["x1"], Lz=extra["z1"], y_lo=extra["y0"], y_hi=extra["y1"])
     else:
-        md = B.mesh(*N)
+        md = B.mesh(*N, Lx=extra.get("x1", 2 * np.pi), Ly=extra.get("y1", 2 * np.pi) - extra.get("y0", 0.0))
+        md.y_lo, md.y_hi = extra.get("y0", 0.0), extra.get("y1", 2 * np.pi)
     h = B.solver(md, cfg, bc, tuple(float(f) for f in force))
     u, v, w = step_init(N, init)
     B.upload(h, "u", u); B.upload(h, "v", v); B.upload(h, "w", w)
@@ -327,3 +358,91 @@ def check_mg_2d(B, oracle, case, tol=1e-12):
     assert not p[1:].any() and not pref[1:].any()               # the other planes are never touched
     for k in ("b_inf", "b_l2", "r0", "r0_l2"):
         assert st[k] == pytest.approx(meta[k], rel=1e-9, abs=1e-300)
+
+
+def plane0_interior(name, a):
+    """interior faces/cells of the data plane of a 2-D field"""
+    p = a[0]
+    if name == "u":
+        return p[1:-1, 1:p.shape[1] - 1]
+    if name == "v":
+        return p[1:p.shape[0] - 1, 1:-1]
+    return p[1:-1, 1:-1]
+
+
+def check_step_2d(B, oracle, case, tol=1e-10):
+    import pytest
+    with tempfile.TemporaryDirectory() as td:
+        meta, ref = run_step_ref(case, td)
+    got_meta, got = run_step_backend(B, case, mesh_arrays=meta.get("_mesh"))
+    if meta["cycles"]:
+        assert got_meta["cycles"] == meta["cycles"]
+    assert got_meta["residuals"] == pytest.approx(meta["residuals"], rel=1e-9)
+    vmax = max(np.abs(plane0_interior(n, ref[n])).max() for n in ("u", "v"))
+    worst = {}
+    for n in ("u", "v", "p", "pcorr", "div", "rhs"):
+        a, b = plane0_interior(n, got[n]), plane0_interior(n, ref[n])
+        scale = np.abs(b).max()
+        if n in ("u", "v") and scale < 1e-4 * vmax:
+            err = np.abs(a - b).max() / vmax
+        elif n == "div":
+            err = np.abs(a - b).max()
+            assert err <= 1e-9, f"{case[0]}: div abs err {err:.3e}"
+            worst[n] = err
+            continue
+        elif scale < 1e-9:
+            err = np.abs(a - b).max()
+            assert err <= 1e-12, f"{case[0]}: {n} abs err {err:.3e} (field ~ 0)"
+            worst[n] = err
+            continue
+        else:
+            err = oracle.rel_l2(a, b)
+        worst[n] = err
+        lim = tol if n != "rhs" else max(tol, 1e-9)
+        assert err <= lim, f"{case[0]}: {n} rel err {err:.3e} > {lim:.1e}"
+    assert not got["w"].any()                                   # w stays identically zero
+    return worst
+
+
+def check_step_2d_with_tbnn(B, oracle, tol=1e-9, nut_tol=1e-6):
+    """2-D channel steps with the NN-TBNN closure attached (TurbulenceModel::update inside
+    RANSSolver::step, src/solver.cpp:1284-1410): nu_t within 1e-6, fields within `tol` (the closure's
+    glibc-vs-CUDA tanh/exp differences of ~1e-16 enter nu_eff)."""
+    import ctypes as C
+    import nnmodels as M
+    preset = "tbnn_channel_caseholdout"
+    N = (32, 48, 1)
+    case = ("chan2d_tbnn", N, "PPWWPP", "euler", "skew", 8, 3, "pchan", (1.0, 0, 0), dict(x1=4 * np.pi, y0=-1.0, y1=1.0))
+    name, N, bc, ti, scheme, fixed, nsteps, init, force, extra = case
+    nu = 1.0 / 180.0
+    u, v, w = step_init(N, init)
+    with tempfile.TemporaryDirectory() as td:
+        d = M.write_text_dir(preset, os.path.join(td, "m"))
+        pre = os.path.join(td, "in")
+        u.tofile(pre + "_u.f64"); v.tofile(pre + "_v.f64")
+        meta = R.run_ref("step", Nx=N[0], Ny=N[1], Nz=1, bc=bc, ti=ti, scheme=scheme, fixed=fixed, nsteps=nsteps, dt=0.002,
+                         nu=nu, init="file:" + pre, fx=1.0, fy=0, fz=0, out=os.path.join(td, "ref"), model="nn_tbnn",
+                         nn_weights=d, x1=extra["x1"], y0=-1.0, y1=1.0)
+        ref = R.load_state(os.path.join(td, "ref_final"), *N)
+    cfg = B.config(nu=nu, dt=0.002, time_integrator=R.TI[ti], convective_scheme=R.SCHEME[scheme], adaptive_dt=0,
+                   poisson_fixed_cycles=fixed)
+    md = B.mesh(*N, Lx=extra["x1"], Ly=2.0)
+    md.y_lo, md.y_hi = -1.0, 1.0
+    h = B.solver(md, cfg, bc, (1.0, 0.0, 0.0))
+    nn = M.create_preset(B, preset)
+    B.check(B.lib.cfdnn_nn_set_params(nn, nu, 1.0, 1.0, 1e-10, 1.0))
+    B.check(B.lib.cfdnn_solver_set_turbulence_model(h, nn))
+    B.upload(h, "u", u); B.upload(h, "v", v); B.upload(h, "w", w)
+    try:
+        res = [B.step(h) for _ in range(nsteps)]
+        got = B.state(h, *N, names=("u", "v", "w", "p", "pcorr", "div", "rhs", "nut"))
+    finally:
+        B.lib.cfdnn_solver_destroy(h)
+        B.lib.cfdnn_nn_destroy(nn)
+    import pytest
+    assert res == pytest.approx(meta["residuals"], rel=1e-8)
+    nut_ref = plane0_interior("nut", ref["nut"])
+    assert nut_ref.max() > 0                                    # the closure is active
+    assert oracle.rel_l2(plane0_interior("nut", got["nut"]), nut_ref) <= nut_tol
+    for n in ("u", "v", "p"):
+        assert oracle.rel_l2(plane0_interior(n, got[n]), plane0_interior(n, ref[n])) <= tol, n

@@ -133,3 +133,26 @@ def test_stretched_channel_48x32x48_rk3_16_cycles(gpu, oracle):
     case = ("chan48", (48, 32, 48), "PPWWPP", "rk3", "skew", 16, 2, "pchan", (1.0, 0, 0), dict(**cases.CHANNEL_BOX))
     err, sens = cases.check_step_within_reference_sensitivity(gpu, oracle, case)
     print("chan48 errors", err, "reference sensitivity to 1e-15 input noise", sens)
+
+
+# ---- 2-D meshes (Nz == 1; BASELINE config 1): 2-D multigrid + the solver's periodic-z-plane embedding
+@pytest.mark.parametrize("case", cases.MG_2D_CASES, ids=[c[0] for c in cases.MG_2D_CASES])
+def test_mg_2d_matches_reference(gpu, oracle, case):
+    cases.check_mg_2d(gpu, oracle, case)
+
+
+@pytest.mark.parametrize("case", cases.STEP_2D_CASES, ids=[c[0] for c in cases.STEP_2D_CASES])
+def test_2d_step_matches_reference(gpu, oracle, case):
+    cases.check_step_2d(gpu, oracle, case)
+
+
+def test_2d_step_with_tbnn_closure(gpu, oracle):
+    """RANSSolver::step with the NN-TBNN closure attached (DMMA kernel inside the step), 2-D channel"""
+    cases.check_step_2d_with_tbnn(gpu, oracle)
+
+
+def test_poiseuille_2d_config1_100_steps(gpu, oracle):
+    """BASELINE config 1: 2-D laminar Poiseuille channel Nx=32 Ny=64 nu=0.01, Euler; 100 steps <= 1e-8"""
+    case = ("poiseuille2d_100", (32, 64, 1), "PPWWPP", "euler", "central", 8, 100, "shear", (1.0, 0, 0),
+            dict(x1=2 * np.pi, y0=-1.0, y1=1.0))
+    cases.check_step_2d(gpu, oracle, case, tol=1e-8)

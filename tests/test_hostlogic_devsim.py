@@ -52,6 +52,16 @@ def test_stretched_channel_step_matches_reference(sim, oracle, case):
     cases.check_step_stretched(sim, oracle, case)
 
 
+@pytest.mark.parametrize("case", cases.STEP_2D_CASES, ids=[c[0] for c in cases.STEP_2D_CASES])
+def test_2d_step_matches_reference(sim, oracle, case):
+    """2-D meshes (BASELINE config 1 and variants): the solver's periodic-z-plane embedding + the 2-D MG"""
+    cases.check_step_2d(sim, oracle, case)
+
+
+def test_2d_step_with_tbnn_closure(sim, oracle):
+    cases.check_step_2d_with_tbnn(sim, oracle)
+
+
 def test_invalid_periodic_pair_is_invalid_argument(sim, R):
     import ctypes as C
     cfg = sim.config()
