@@ -210,14 +210,35 @@ def main():
         e2e = {"value": cells * args.steps / float(t.item()) / 1e6, "unit": "Mcell-steps/s",
                "h2d_bytes_per_step": nbytes, "d2h_bytes_per_step": nbytes}
 
+    # dominant kernel, timed live with CUDA events on the solver's stream (after the timed steps, same
+    # resident 512^3 level-0 arrays, >> L2): the level-0 temporally blocked smoother
+    sm_ms = C.c_double(0.0)
+    B.check(B.lib.cfdnn_solver_time_smoother(h, 20, C.byref(sm_ms)))
+
     if rank == 0:
         peak, which = peaks()
         vc_avg_ms = vc_ms / max(n_vc, 1)
-        achieved = VCYCLE_BYTES_PER_CELL * N * N * N / (vc_avg_ms * 1e-3) / 1e9 if n_vc else None
-        roof = {"bound": "hbm", "kernel": "multigrid V-cycle (all levels; smoother sweeps dominate)",
+        cells_local = N * N * N
+        vc_achieved = VCYCLE_BYTES_PER_CELL * cells_local / (vc_avg_ms * 1e-3) / 1e9 if n_vc else None
+        # 24 B per cell per sweep (u, f in; u out); one launch = 2 sweeps.  With the two
+        # sweeps fused the compulsory traffic of a launch is 24 B per cell (what ncu's DRAM bytes show).
+        alg = 2 * 24.0 * cells_local
+        achieved = alg / (sm_ms.value * 1e-3) / 1e9 if sm_ms.value > 0 else None
+        traffic = None
+        try:
+            tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))["k_sweep_tb<2,64,26>"]
+            if tj["cells"] == cells_local:
+                traffic = tj["dram_bytes_per_launch"]
+        except Exception:
+            pass
+        roof = {"bound": "hbm", "kernel": "k_sweep_tb<2,64,26>: level-0 smoother, 2 Chebyshev sweeps per launch",
                 "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak if achieved else None,
-                "traffic": None, "peak_source": which, "algorithmic_bytes_per_launch": VCYCLE_BYTES_PER_CELL * N ** 3,
-                "vcycle_ms": vc_avg_ms, "vcycles_timed": n_vc, "vcycle_share_of_step": vc_ms / step_ms}
+                "traffic": traffic, "peak_source": which, "algorithmic_bytes_per_launch": alg,
+                "fused_compulsory_bytes_per_launch": 24.0 * cells_local, "launch_ms": sm_ms.value, "launches_timed": 20,
+                "dram_GBs_at_fused_traffic": (24.0 * cells_local / (sm_ms.value * 1e-3) / 1e9) if sm_ms.value > 0 else None,
+                "vcycle": {"algorithmic_bytes": VCYCLE_BYTES_PER_CELL * cells_local, "ms": vc_avg_ms, "timed": n_vc,
+                           "achieved": vc_achieved, "frac": vc_achieved / peak if vc_achieved else None,
+                           "share_of_step": vc_ms / step_ms}}
         cpu = None
         if not args.no_cpu_baseline and R.have_oracle():
             ns = 4

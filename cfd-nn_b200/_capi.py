@@ -99,6 +99,7 @@ _SIGS = {
     "cfdnn_solver_cycle_log": (C.c_int, [C.c_void_p, c_int_p, C.c_int, c_int_p]),
     "cfdnn_solver_set_turbulence_model": (C.c_int, [C.c_void_p, C.c_void_p]),
     "cfdnn_solver_last_timing": (C.c_int, [C.c_void_p, c_double_p, c_double_p, c_int_p]),
+    "cfdnn_solver_time_smoother": (C.c_int, [C.c_void_p, C.c_int, c_double_p]),
     "cfdnn_comm_unique_id": (C.c_int, [C.c_void_p]),
     "cfdnn_solver_comm_init": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
     "cfdnn_nn_create": (C.c_int, [C.c_int, C.c_int, c_int_p, c_int_p, C.POINTER(c_double_p), C.POINTER(c_double_p),

@@ -163,6 +163,12 @@ int cfdnn_solver_last_timing(const cfdnn_solver* s, double* step_ms, double* vcy
     if (n_vcycles) *n_vcycles = s->impl.last_vcycles;
     return CFDNN_OK;
 }
+int cfdnn_solver_time_smoother(cfdnn_solver* s, int reps, double* ms_per_launch) {
+    return guarded([&] {
+        const double ms = s->impl.mg().time_level0_smoother(reps, s->impl.stream());
+        if (ms_per_launch) *ms_per_launch = ms;
+    });
+}
 int cfdnn_comm_unique_id(void* id128) { return guarded([&] { nccl_unique_id(id128); }); }
 int cfdnn_solver_comm_init(cfdnn_solver* s, int rank, int nranks, const void* id128) {
     return guarded([&] {

@@ -49,6 +49,7 @@ Multigrid::Multigrid(const cfdnn_mesh_desc& m) : mesh_(m) {
         L->g.inv_dx2_2 = 2.0 / dx2;
         L->g.inv_dz2_2 = 2.0 / dz2;
         L->g.nonuniform_y = 0; L->g.joff = 0;
+        { const char* e = std::getenv("CFDNN_MG_FASTDIV"); L->g.fastdiv = (e && std::atoi(e) == 0) ? 0 : 1; }
         L->g.aS = L->g.aN = L->g.aP = nullptr;
         L->size = (size_t)(nz + 2 * L->g.Hz) * L->g.plane;
         L->u.alloc(L->size); L->f.alloc(L->size); L->r.alloc(L->size); L->tmp.alloc(L->size);
@@ -551,6 +552,28 @@ int Multigrid::solve_dev(const double* rhs, double* p, const cfdnn_poisson_cfg& 
     vcycle_count = cycles_used;
     if (cur_ev_) cur_ev_->cycles = cycles_used;
     return cycles_used;
+}
+
+double Multigrid::time_level0_smoother(int reps, cudaStream_t st) {
+    if (levels_.empty() || reps < 1) return 0.0;
+    st_ = st;
+    Level& L = *levels_[0];
+    const double w[2] = {0.6, 0.9};
+    double* a = L.u.p;
+    double* b = L.tmp.p;
+    if (!sweeps_tb(0, a, b, w, 2)) return 0.0;          // warm-up launch, also the eligibility check
+    cudaEvent_t e0, e1;
+    CFDNN_CUDA(cudaEventCreate(&e0));
+    CFDNN_CUDA(cudaEventCreate(&e1));
+    CFDNN_CUDA(cudaEventRecord(e0, st));
+    for (int r = 0; r < reps; ++r) { std::swap(a, b); sweeps_tb(0, a, b, w, 2); }
+    CFDNN_CUDA(cudaEventRecord(e1, st));
+    CFDNN_CUDA(cudaEventSynchronize(e1));
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, e0, e1);
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    check_launch("time_level0_smoother");
+    return (double)ms / reps;
 }
 
 void Multigrid::collect_timing() {

@@ -34,6 +34,10 @@ struct LevelGeom {            // by-value kernel argument
     int joff;
     const double *aS, *aN, *aP;
     double inv_dx2_2, inv_dz2_2;   // 2.0/dx2, 2.0/dz2 (nonuniform diag)
+    int fastdiv;                   // blocked smoother: x * RN(1/d) instead of the correctly rounded x / d —
+                                   // 13 instead of 22 FP64 instructions per cell-sweep, each quotient within
+                                   // 1 ulp of the reference's.  Default on; CFDNN_MG_FASTDIV=0 restores the
+                                   // correctly rounded divisions (last-bit agreement with the x86 build).
 };
 
 struct Level {
@@ -74,6 +78,10 @@ public:
     bool time_vcycles = true;
 
     void set_comm(Comm* c);
+    // Measurement aid (bench.py roofline): `reps` launches of the level-0 temporally blocked smoother
+    // (2 Chebyshev sweeps per launch) on stream st, timed with CUDA events; returns ms per launch
+    // (0 when level 0 is not eligible for the tiled kernel).  The level-0 iterate is scratch afterwards.
+    double time_level0_smoother(int reps, cudaStream_t st);
     void collect_timing();          // read the V-cycle events of the solves since the last call (syncs)
     cudaStream_t own_stream();
     const cfdnn_mesh_desc& mesh() const { return mesh_; }

@@ -64,6 +64,10 @@ __device__ __forceinline__ void st_pair(double* p, double a, double b) {
 __device__ __forceinline__ double jacobi_point(const LevelGeom& g, double uc, double uW, double uE, double uS,
                                                double uN, double ub, double uf, double fv, double omega,
                                                double om1) {
+    if (g.fastdiv) {   // reciprocal multiplies: 1 ulp per quotient off the reference's divisions (mg.cuh)
+        const double uj = ((uE + uW) * g.dx2.r + (uN + uS) * g.dy2.r + (uf + ub) * g.dz2.r - fv) * g.coeff.r;
+        return om1 * uc + omega * uj;
+    }
     const double uj = ((uE + uW) / g.dx2 + (uN + uS) / g.dy2 + (uf + ub) / g.dz2 - fv) / g.coeff;
     return om1 * uc + omega * uj;
 }

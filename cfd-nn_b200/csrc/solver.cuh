@@ -68,6 +68,7 @@ public:
     double last_step_ms = 0.0, last_vcycle_ms = 0.0;
     int last_vcycles = 0;
     Multigrid& mg() { return *mg_; }
+    cudaStream_t stream() const { return st_; }
 
 private:
     cfdnn_mesh_desc mesh_;

@@ -161,6 +161,10 @@ int cfdnn_solver_cycle_log(cfdnn_solver* s, int* cycles, int cap, int* n_out);
 int cfdnn_solver_set_turbulence_model(cfdnn_solver* s, cfdnn_nn* nn);
 /* device timing of the last step()/run(): total ms and ms spent inside V-cycles */
 int cfdnn_solver_last_timing(const cfdnn_solver* s, double* step_ms, double* vcycle_ms, int* n_vcycles);
+/* measurement aid for bench.py's roofline: ms per launch of the level-0 temporally blocked smoother
+ * kernel (2 Chebyshev sweeps per launch), `reps` launches timed with CUDA events on the solver's
+ * stream; 0 when level 0 does not use the tiled kernel.  Leaves the MG scratch iterate modified. */
+int cfdnn_solver_time_smoother(cfdnn_solver* s, int reps, double* ms_per_launch);
 /* z-slab multi-GPU (replaces Decomposition + HaloExchange, src/decomposition.cpp, src/halo_exchange.cpp):
  * nccl_unique_id is the 128-byte ncclUniqueId produced by rank 0 and broadcast by the caller */
 int cfdnn_comm_unique_id(void* id128);
