@@ -92,6 +92,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--workload", default="tgv512", choices=sorted(WORKLOADS))
+    ap.add_argument("--closure", default="none", choices=["none", "tbnn"],
+                    help="tbnn: attach the NN-TBNN closure (tbnn_channel_caseholdout, per-cell 5-64-64-64-4 MLP on the "
+                         "FP64 tensor cores) to the step — the north_star's 'RK3 + MG + NN-TBNN' variant of the workload")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     args = ap.parse_args()
@@ -116,9 +119,17 @@ def main():
     Nzg = N * world                      # weak scaling: every GPU owns an N x N x N slab
     L = 2 * np.pi
     mesh = B.mesh(N, N, N, Lx=L, Ly=L, Lz=L * world, Nz_global=Nzg, k_offset=rank * N)
-    cfg = B.config(nu=0.01, dt=0.01, time_integrator=R.TI["rk3"], convective_scheme=R.SCHEME["skew"],
+    # with the closure nu_t reaches 10 nu: the explicit diffusive limit dx^2 / (6 nu_eff) forces a smaller step
+    nu_, dt_ = (0.01, 0.01) if args.closure == "none" else (1.0 / 180.0, 1e-4)
+    cfg = B.config(nu=nu_, dt=dt_, time_integrator=R.TI["rk3"], convective_scheme=R.SCHEME["skew"],
                    adaptive_dt=0, poisson_fixed_cycles=0, poisson_tol_rhs=MG_TOL_RHS, poisson_max_vcycles=MG_MAXV)
     h = B.solver(mesh, cfg, "PPPPPP")
+    nn = None
+    if args.closure == "tbnn":
+        import nnmodels as M
+        nn = M.create_preset(B, "tbnn_channel_caseholdout")
+        B.check(B.lib.cfdnn_nn_set_params(nn, nu_, 1.0, 1.0, 1e-10, 1.0))
+        B.check(B.lib.cfdnn_solver_set_turbulence_model(h, nn))
     if world > 1:
         idbuf = torch.zeros(128, dtype=torch.uint8)
         if rank == 0:
@@ -198,17 +209,25 @@ def main():
             upload_all(); B.check(B.lib.cfdnn_solver_run(h, 1, C.byref(r))); download_all()
         barrier()
         t0 = time.perf_counter()
+        ph = [0.0, 0.0, 0.0]
         for _ in range(args.steps):
+            ta = time.perf_counter()
             upload_all()
+            tb = time.perf_counter()
             B.check(B.lib.cfdnn_solver_run(h, 1, C.byref(r)))
+            tc = time.perf_counter()
             download_all()
+            td = time.perf_counter()
+            ph[0] += tb - ta; ph[1] += tc - tb; ph[2] += td - tc
         barrier()
         e2e_s = time.perf_counter() - t0
         t = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
         if world > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e = {"value": cells * args.steps / float(t.item()) / 1e6, "unit": "Mcell-steps/s",
-               "h2d_bytes_per_step": nbytes, "d2h_bytes_per_step": nbytes}
+               "h2d_bytes_per_step": nbytes, "d2h_bytes_per_step": nbytes,
+               "ms_per_step": {"h2d": ph[0] / args.steps * 1e3, "step": ph[1] / args.steps * 1e3,
+                               "d2h": ph[2] / args.steps * 1e3}}
 
     # dominant kernel, timed live with CUDA events on the solver's stream (after the timed steps, same
     # resident 512^3 level-0 arrays, >> L2): the level-0 temporally blocked smoother
@@ -252,13 +271,16 @@ def main():
                 "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
                 "data": "synthetic",
                 "config": {"workload": f"{args.workload}: 3D Taylor-Green vortex {N}x{N}x{Nzg}, SSP-RK3, skew-symmetric "
-                                       f"convection, multigrid Poisson to tol_rhs={MG_TOL_RHS} (max {MG_MAXV} V-cycles)",
+                                       f"convection, multigrid Poisson to tol_rhs={MG_TOL_RHS} (max {MG_MAXV} V-cycles)"
+                                       + (f", NN-TBNN closure on every cell (FP64 DMMA), nu={nu_:.5f} dt={dt_}" if nn else ""),
                            "l2": "inputs larger than L2" if N >= 256 else "small grid: fits L2",
                            "vcycles_per_solve": cycles[-3:], "decomposition": f"z-slabs x{world}"},
                 "wall_ms_per_step": wall_ms / args.steps, "gpu_launches": int(launches), "clocks": sampler.result(),
                 "e2e": e2e, "roofline": roof, "cpu_baseline": cpu}
         print(json.dumps(line), flush=True)
     B.lib.cfdnn_solver_destroy(h)
+    if nn:
+        B.lib.cfdnn_nn_destroy(nn)
     if world > 1:
         dist.destroy_process_group()
     return 0

@@ -37,7 +37,7 @@ STEP_CASES = [
 CHANNEL_BOX = dict(stretch_beta=2.0, x1=4 * np.pi, y0=-1.0, y1=1.0, z1=2 * np.pi)
 MG_SEMI_CASES = [
     ("semi_chan_32x16x32_fixed2", (32, 16, 32), "PPNNPP", 2, dict(smooth=1, **CHANNEL_BOX)),
-    ("semi_chan_32x24x16_conv", (32, 24, 16), "PPNNPP", 0, dict(smooth=1, tol_rhs=1e-8, maxv=20, tol_rel=0, tol=0, **CHANNEL_BOX)),
+    ("semi_chan_32x24x16_conv", (32, 24, 16), "PPNNPP", 0, dict(smooth=1, tol_rhs=1e-4, maxv=20, tol_rel=0, tol=0, **CHANNEL_BOX)),
     ("semi_dirichlet_x_fixed2", (32, 16, 32), "DDNNPP", 2, dict(smooth=1, **CHANNEL_BOX)),
     ("semi_neumann_all_fixed1", (16, 16, 32), "NNNNNN", 1, dict(smooth=1, **CHANNEL_BOX)),
     ("semi_random_rhs_fixed1", (32, 16, 16), "PPNNPP", 1, dict(**CHANNEL_BOX)),
@@ -48,7 +48,7 @@ HARNESS_KEYS = ("stretch_beta", "x1", "y0", "y1", "z1", "tol_rhs", "maxv", "tol_
 # stretched-y channel steps (BASELINE config 3 in miniature): stretched divergence / correction
 # metrics in the operators + the semi-coarsening MG of row M10
 STEP_STRETCHED_CASES = [
-    ("chan_stretched_rk3_tgv", (16, 16, 16), "PPWWPP", "rk3", "skew", 6, 2, "tgv", (1.0, 0, 0), dict(**CHANNEL_BOX)),
+    ("chan_stretched_rk3_tgv", (16, 16, 16), "PPWWPP", "rk3", "skew", 6, 1, "tgv", (1.0, 0, 0), dict(**CHANNEL_BOX)),
     ("chan_stretched_euler_shear", (32, 16, 16), "PPWWPP", "euler", "central", 4, 2, "shear", (1.0, 0, 0), dict(**CHANNEL_BOX)),
 ]
 

@@ -9,6 +9,31 @@ import pytest
 import cases
 
 
+@pytest.fixture(autouse=True)
+def _plain_smoother_on_the_test_double(monkeypatch, request):
+    """The temporally blocked smoother runs as ~500 fibers per CTA on the CPU test double (slow); the
+    host-logic tests here use the plain one-sweep kernels (CFDNN_MG_TB=0, same arithmetic) except the
+    tests marked `tiled`, which keep the blocked kernel covered on CPU.  On the GPU every test runs it."""
+    if "tiled" not in request.keywords:
+        monkeypatch.setenv("CFDNN_MG_TB", "0")
+
+
+@pytest.mark.tiled
+def test_blocked_smoother_on_the_test_double(sim, oracle):
+    case = cases.MG_CASES[1]                                   # per32_conv1e8: 32^3, tiled levels 32 and 16
+    with tempfile.TemporaryDirectory() as td:
+        meta, pref = cases.run_mg_ref(case, td)
+    st, p = cases.run_mg_backend(sim, case)
+    assert st["cycles"] == meta["cycles"] and st["converged"] == meta["converged"]
+    assert oracle.rel_l2(p, pref) <= 1e-12
+    step = ("tgv16_rk3_tiled", (16, 16, 16), "PPPPPP", "rk3", "skew", 4, 1, "tgv", (0, 0, 0), {})
+    with tempfile.TemporaryDirectory() as td:
+        meta, ref = cases.run_step_ref(step, td)
+    got_meta, got = cases.run_step_backend(sim, step)
+    assert got_meta["cycles"] == meta["cycles"]
+    cases.compare_states(got, ref, 1e-10, step[0])
+
+
 @pytest.mark.parametrize("case", cases.MG_CASES, ids=[c[0] for c in cases.MG_CASES])
 def test_mg_solve_matches_reference(sim, oracle, case):
     with tempfile.TemporaryDirectory() as td:
