@@ -120,7 +120,9 @@ def main():
     L = 2 * np.pi
     mesh = B.mesh(N, N, N, Lx=L, Ly=L, Lz=L * world, Nz_global=Nzg, k_offset=rank * N)
     # with the closure nu_t reaches 10 nu: the explicit diffusive limit dx^2 / (6 nu_eff) forces a smaller step
-    nu_, dt_ = (0.01, 0.01) if args.closure == "none" else (1.0 / 180.0, 1e-4)
+    # dt keeps the CFL number of BASELINE config 2 (64^3, dt = 0.01): dt = 0.01 * 64 / N.  (dt = 0.01 at
+    # 512^3 is CFL ~ 0.8 and the run diverges within 10 steps.)
+    nu_, dt_ = (0.01, 0.01 * 64.0 / N) if args.closure == "none" else (1.0 / 180.0, 1e-4)
     cfg = B.config(nu=nu_, dt=dt_, time_integrator=R.TI["rk3"], convective_scheme=R.SCHEME["skew"],
                    adaptive_dt=0, poisson_fixed_cycles=0, poisson_tol_rhs=MG_TOL_RHS, poisson_max_vcycles=MG_MAXV)
     h = B.solver(mesh, cfg, "PPPPPP")
@@ -271,8 +273,9 @@ def main():
                 "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
                 "data": "synthetic",
                 "config": {"workload": f"{args.workload}: 3D Taylor-Green vortex {N}x{N}x{Nzg}, SSP-RK3, skew-symmetric "
-                                       f"convection, multigrid Poisson to tol_rhs={MG_TOL_RHS} (max {MG_MAXV} V-cycles)"
-                                       + (f", NN-TBNN closure on every cell (FP64 DMMA), nu={nu_:.5f} dt={dt_}" if nn else ""),
+                                       f"convection, nu={nu_:.5f} dt={dt_:g}, multigrid Poisson to tol_rhs={MG_TOL_RHS} "
+                                       f"(max {MG_MAXV} V-cycles)"
+                                       + (", NN-TBNN closure on every cell (FP64 DMMA)" if nn else ""),
                            "l2": "inputs larger than L2" if N >= 256 else "small grid: fits L2",
                            "vcycles_per_solve": cycles[-3:], "decomposition": f"z-slabs x{world}"},
                 "wall_ms_per_step": wall_ms / args.steps, "gpu_launches": int(launches), "clocks": sampler.result(),
