@@ -247,12 +247,12 @@ def main():
         achieved = alg / (sm_ms.value * 1e-3) / 1e9 if sm_ms.value > 0 else None
         traffic = None
         try:
-            tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))["k_sweep_tb<2,64,26>"]
+            tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))["k_sweep_tbo<64,26>"]
             if tj["cells"] == cells_local:
                 traffic = tj["dram_bytes_per_launch"]
         except Exception:
             pass
-        roof = {"bound": "hbm", "kernel": "k_sweep_tb<2,64,26>: level-0 smoother, 2 Chebyshev sweeps per launch",
+        roof = {"bound": "hbm", "kernel": "k_sweep_tbo<64,26>: level-0 smoother, 2 Chebyshev sweeps per launch",
                 "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak if achieved else None,
                 "traffic": traffic, "peak_source": which, "algorithmic_bytes_per_launch": alg,
                 "fused_compulsory_bytes_per_launch": 24.0 * cells_local, "launch_ms": sm_ms.value, "launches_timed": 20,

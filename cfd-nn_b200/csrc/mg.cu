@@ -1,6 +1,6 @@
 // mg.cu — host orchestration of the multigrid V-cycle (see mg.cuh for the layout).
 #include "mg_kernels.cuh"
-#include "mg_tb_kernels.cuh"
+#include "mg_tbo_kernels.cuh"
 #include "comm.cuh"
 #include <cstdlib>
 #include <cmath>
@@ -158,23 +158,14 @@ void Multigrid::sweep(int level, const double* uin, double* uout, double omega) 
 // ---- temporally blocked sweeps (mg_tb_kernels.cuh)
 namespace {
 // tile shapes: BIG for levels that fill the chip with 64-wide tiles, SMALL for the rest
+constexpr int TBO_MODE = 2;   // k_sweep_tbo variant of the exact-division build
 constexpr int TB_BX_BIG = 64, TB_BY_BIG = 26, TB_BX_SMALL = 32, TB_BY_SMALL = 12;
 
-template <int T, int BX, int BY, bool RES = false>
-void tb_attr() {
-    using S = TbShape<T, BX, BY>;
-    CFDNN_CUDA(cudaFuncSetAttribute(k_sweep_tb<T, BX, BY, RES>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::SMEM));
-}
-template <int T, int BX, int BY, bool RES = false>
-void tb_launch(const LevelGeom& g, const double* in, const double* f, double* out, const double* w,
-               cudaStream_t st) {
-    using S = TbShape<T, BX, BY>;
-    TbOmega<T> om;
-    for (int s = 0; s < T; ++s) om.w[s] = w ? w[s] : 0.0;
+// z chunks (one CTA per SM): pick the chunk count that maximises
+//   (fill of the last wave of 148 SMs) x (useful planes / planes marched incl. the 2T warm-up),
+// with chunks no thinner than 4*T planes.
+dim3 tb_grid(const LevelGeom& g, int T, int BX, int BY, int* ZC_out) {
     const int tx = (g.Nx + BX - 1) / BX, ty = (g.Ny + BY - 1) / BY;
-    // z chunks (one CTA per SM): pick the chunk count that maximises
-    //   (fill of the last wave of 148 SMs) x (useful planes / planes marched incl. the 2T warm-up),
-    // with chunks no thinner than 4*T planes.
     const int nch_max = std::max(1, g.Nz / (4 * T));
     int nch = 1;
     double best = -1.0;
@@ -189,8 +180,51 @@ void tb_launch(const LevelGeom& g, const double* in, const double* f, double* ou
     }
     const int ZC = (g.Nz + nch - 1) / nch;
     nch = (g.Nz + ZC - 1) / ZC;
-    dim3 grid(tx, ty, nch);
+    *ZC_out = ZC;
+    return dim3(tx, ty, nch);
+}
+
+template <int T, int BX, int BY, bool RES = false>
+void tb_attr() {
+    using S = TbShape<T, BX, BY>;
+    CFDNN_CUDA(cudaFuncSetAttribute(k_sweep_tb<T, BX, BY, RES>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::SMEM));
+}
+template <int T, int BX, int BY, bool RES = false>
+void tb_launch(const LevelGeom& g, const double* in, const double* f, double* out, const double* w,
+               cudaStream_t st) {
+    using S = TbShape<T, BX, BY>;
+    TbOmega<T> om;
+    for (int s = 0; s < T; ++s) om.w[s] = w ? w[s] : 0.0;
+    int ZC;
+    dim3 grid = tb_grid(g, T, BX, BY, &ZC);
     CFDNN_LAUNCH_COOP((k_sweep_tb<T, BX, BY, RES>), grid, S::NTHREADS, S::SMEM, st, g, in, f, out, om, ZC);
+}
+// two sweeps on a level without physical faces in reach (mg_tbo_kernels.cuh)
+template <int BX, int BY>
+void tbo_launch(const LevelGeom& g, const double* in, const double* f, double* out, const double* w,
+                cudaStream_t st, int mode) {
+    using S = TbShape<2, BX, BY>;
+    TbOmega<2> om;
+    om.w[0] = w[0]; om.w[1] = w[1];
+    int ZC;
+    dim3 grid = tb_grid(g, 2, BX, BY, &ZC);
+    if (!g.fastdiv) {
+        CFDNN_LAUNCH_COOP((k_sweep_tbo<BX, BY, false, TBO_MODE>), grid, S::NTHREADS, S::SMEM, st, g, in, f, out, om, ZC);
+    } else if (mode == 0) {
+        CFDNN_LAUNCH_COOP((k_sweep_tbo<BX, BY, true, 0>), grid, S::NTHREADS, S::SMEM, st, g, in, f, out, om, ZC);
+    } else if (mode == 1) {
+        CFDNN_LAUNCH_COOP((k_sweep_tbo<BX, BY, true, 1>), grid, S::NTHREADS, S::SMEM, st, g, in, f, out, om, ZC);
+    } else {
+        CFDNN_LAUNCH_COOP((k_sweep_tbo<BX, BY, true, 2>), grid, S::NTHREADS, S::SMEM, st, g, in, f, out, om, ZC);
+    }
+}
+template <int BX, int BY>
+void tbo_attr() {
+    using S = TbShape<2, BX, BY>;
+    CFDNN_CUDA(cudaFuncSetAttribute(k_sweep_tbo<BX, BY, true, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::SMEM));
+    CFDNN_CUDA(cudaFuncSetAttribute(k_sweep_tbo<BX, BY, true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::SMEM));
+    CFDNN_CUDA(cudaFuncSetAttribute(k_sweep_tbo<BX, BY, true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::SMEM));
+    CFDNN_CUDA(cudaFuncSetAttribute(k_sweep_tbo<BX, BY, false, TBO_MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::SMEM));
 }
 }  // namespace
 
@@ -198,7 +232,10 @@ void Multigrid::tb_setup() {
     tb_attr<1, TB_BX_BIG, TB_BY_BIG>(); tb_attr<2, TB_BX_BIG, TB_BY_BIG>();
     tb_attr<1, TB_BX_SMALL, TB_BY_SMALL>(); tb_attr<2, TB_BX_SMALL, TB_BY_SMALL>();
     tb_attr<1, TB_BX_BIG, TB_BY_BIG, true>(); tb_attr<1, TB_BX_SMALL, TB_BY_SMALL, true>();
+    tbo_attr<TB_BX_BIG, TB_BY_BIG>(); tbo_attr<TB_BX_SMALL, TB_BY_SMALL>();
     if (const char* e = std::getenv("CFDNN_MG_TB")) tb_max_ = std::max(0, std::min(2, std::atoi(e)));
+    if (const char* e = std::getenv("CFDNN_MG_TBO")) tbo_ = std::atoi(e) != 0;
+    if (const char* e = std::getenv("CFDNN_MG_TBO_MODE")) tbo_mode_ = std::max(0, std::min(2, std::atoi(e)));
 }
 
 // n (<= 2) sweeps in one pass (w != nullptr), or the tiled residual r = f - L u (w == nullptr, n = 1);
@@ -215,6 +252,15 @@ bool Multigrid::sweeps_tb(int level, const double* in, double* out, const double
     if (!w) {
         if (big) tb_launch<1, TB_BX_BIG, TB_BY_BIG, true>(g, in, L.f.p, out, nullptr, st_);
         else tb_launch<1, TB_BX_SMALL, TB_BY_SMALL, true>(g, in, L.f.p, out, nullptr, st_);
+        return true;
+    }
+    const bool open_xy = g.bc[0] == CFDNN_PBC_PERIODIC && g.bc[1] == CFDNN_PBC_PERIODIC &&
+                         g.bc[2] == CFDNN_PBC_PERIODIC && g.bc[3] == CFDNN_PBC_PERIODIC;
+    const bool open_z = (g.bc[4] == CFDNN_PBC_PERIODIC && g.bc[5] == CFDNN_PBC_PERIODIC) ||
+                        (g.bc[4] == CFDNN_PBC_HALO && g.bc[5] == CFDNN_PBC_HALO);
+    if (tbo_ && n == 2 && open_xy && open_z) {             // no physical face in reach: the lean kernel
+        if (big) tbo_launch<TB_BX_BIG, TB_BY_BIG>(g, in, L.f.p, out, w, st_, tbo_mode_);
+        else tbo_launch<TB_BX_SMALL, TB_BY_SMALL>(g, in, L.f.p, out, w, st_, tbo_mode_);
         return true;
     }
     if (big) {

@@ -15,6 +15,6 @@ PROF="python bench.py --steps 1 --warmup 1 --no-cpu-baseline --no-e2e"
 $PROF > $out/plain_$tag.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --clock-control none -c 12000 --csv --log-file $out/launches512_$tag.csv $PROF > $out/ncu_launches_$tag.log 2>&1
 echo "ncu launches exit $?"
-ncu --set full --clock-control none --import-source on -k regex:k_sweep_tb -s 4 -c 2 -f -o $out/prof_tb512_$tag $PROF > $out/ncu_full_$tag.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:k_sweep_tbo -s 4 -c 2 -f -o $out/prof_tb512_$tag $PROF > $out/ncu_full_$tag.log 2>&1
 echo "ncu full exit $?"
 ls -la $out | tail -12

@@ -446,3 +446,25 @@ def check_step_2d_with_tbnn(B, oracle, tol=1e-9, nut_tol=1e-6):
     assert oracle.rel_l2(plane0_interior("nut", got["nut"]), nut_ref) <= nut_tol
     for n in ("u", "v", "p"):
         assert oracle.rel_l2(plane0_interior(n, got[n]), plane0_interior(n, ref[n])) <= tol, n
+
+
+def check_smoother_variants_bitwise(B, monkeypatch, N=(32, 32, 32), cycles=2):
+    """With exact divisions (CFDNN_MG_FASTDIV=0) the blocked kernels — the lean one for levels without
+    physical faces (k_sweep_tbo) and the general one (k_sweep_tb) — reproduce the one-sweep kernel bit
+    for bit; with reciprocal multiplies (default) the lean kernel's fused multiply-adds stay within
+    1e-13 of it."""
+    case = ("per_variants", N, "PPPPPP", cycles, {})
+    out = {}
+    for tag, env in (("plain", dict(CFDNN_MG_FASTDIV="0", CFDNN_MG_TB="0")),
+                     ("tb", dict(CFDNN_MG_FASTDIV="0", CFDNN_MG_TB="2", CFDNN_MG_TBO="0")),
+                     ("tbo", dict(CFDNN_MG_FASTDIV="0", CFDNN_MG_TB="2", CFDNN_MG_TBO="1")),
+                     ("tbo_fd", dict(CFDNN_MG_FASTDIV="1", CFDNN_MG_TB="2", CFDNN_MG_TBO="1"))):
+        for k in ("CFDNN_MG_FASTDIV", "CFDNN_MG_TB", "CFDNN_MG_TBO"):
+            monkeypatch.delenv(k, raising=False)
+        for k, v in env.items():
+            monkeypatch.setenv(k, v)
+        _, out[tag] = run_mg_backend(B, case)
+    assert np.array_equal(out["plain"], out["tb"])
+    assert np.array_equal(out["plain"], out["tbo"])
+    d = np.linalg.norm(out["tbo_fd"] - out["plain"]) / np.linalg.norm(out["plain"])
+    assert 0 < d <= 1e-13, d

@@ -156,3 +156,8 @@ def test_poiseuille_2d_config1_100_steps(gpu, oracle):
     case = ("poiseuille2d_100", (32, 64, 1), "PPWWPP", "euler", "central", 8, 100, "shear", (1.0, 0, 0),
             dict(x1=2 * np.pi, y0=-1.0, y1=1.0))
     cases.check_step_2d(gpu, oracle, case, tol=1e-8)
+
+
+def test_blocked_smoother_variants_agree(gpu, monkeypatch):
+    """128^3 puts level 0 on the 64x26 tiles and levels 1-2 on the 32x12 tiles of both blocked kernels"""
+    cases.check_smoother_variants_bitwise(gpu, monkeypatch, N=(128, 128, 128), cycles=2)

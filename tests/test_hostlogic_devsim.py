@@ -34,6 +34,11 @@ def test_blocked_smoother_on_the_test_double(sim, oracle):
     cases.compare_states(got, ref, 1e-10, step[0])
 
 
+@pytest.mark.tiled
+def test_blocked_smoother_variants_agree(sim, monkeypatch):
+    cases.check_smoother_variants_bitwise(sim, monkeypatch, N=(16, 16, 16), cycles=1)
+
+
 @pytest.mark.parametrize("case", cases.MG_CASES, ids=[c[0] for c in cases.MG_CASES])
 def test_mg_solve_matches_reference(sim, oracle, case):
     with tempfile.TemporaryDirectory() as td:
