@@ -175,13 +175,17 @@ k_sweep_tbo(LevelGeom g, const double* __restrict__ u, const double* __restrict_
         // ---- level-0 plane zi arrives: publish it
         st_pair(wb + 2 * t, l0[A][0], l0[A][1]);
         st_pair(wb + 2 * NT + 2 * t, l0[A][2], l0[A][3]);
-        // The prefetch is issued AFTER the first consumer of the previous one (the publish above): all
-        // global loads of a warp share one hardware scoreboard, so a wait for the previous prefetch placed
-        // after the new loads would also wait for those — and expose the full DRAM latency every plane.
-        asm volatile("" ::: "memory");
+        // The prefetch must be issued AFTER the wait for the previous one: all global loads of the loop
+        // share one hardware scoreboard, so a wait placed after the new loads also waits for those and
+        // exposes the full DRAM latency every plane.  ptxas hoists independent loads freely, so the
+        // order is pinned by a data dependency: the loads are predicated on a value of the arriving
+        // plane being a number (always true for finite fields; a NaN field stays NaN either way).
+        const bool arrived = !(l0[A][0] != l0[A][0]);
         if (prefetch) {                                    // next iteration's planes
-            load4(u, zoff_u, l0[N]);
-            load4(f, zoff_f, fr[N]);
+            if (arrived) {
+                load4(u, zoff_u, l0[N]);
+                load4(f, zoff_f, fr[N]);
+            }
             advance(zu, zoff_u);
             advance(zf_, zoff_f);
         }
