@@ -1,6 +1,7 @@
 // mg.cu — host orchestration of the multigrid V-cycle (see mg.cuh for the layout).
 #include "mg_kernels.cuh"
 #include "mg_tbo_kernels.cuh"
+#include "mg_rr_kernels.cuh"
 #include "comm.cuh"
 #include <cstdlib>
 #include <cmath>
@@ -159,6 +160,7 @@ void Multigrid::sweep(int level, const double* uin, double* uout, double omega) 
 namespace {
 // tile shapes: BIG for levels that fill the chip with 64-wide tiles, SMALL for the rest
 constexpr int TBO_MODE = 2;   // k_sweep_tbo variant of the exact-division build
+constexpr int RR_CX = 32, RR_CY = 8;   // coarse tile of the fused residual + restriction (mg_rr_kernels.cuh)
 constexpr int TB_BX_BIG = 64, TB_BY_BIG = 26, TB_BX_SMALL = 32, TB_BY_SMALL = 12;
 
 // z chunks (one CTA per SM): pick the chunk count that maximises
@@ -235,6 +237,10 @@ void Multigrid::tb_setup() {
     tbo_attr<TB_BX_BIG, TB_BY_BIG>(); tbo_attr<TB_BX_SMALL, TB_BY_SMALL>();
     if (const char* e = std::getenv("CFDNN_MG_TB")) tb_max_ = std::max(0, std::min(2, std::atoi(e)));
     if (const char* e = std::getenv("CFDNN_MG_TBO")) tbo_ = std::atoi(e) != 0;
+    CFDNN_CUDA(cudaFuncSetAttribute(k_residual_restrict<RR_CX, RR_CY>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    (int)RrShape<RR_CX, RR_CY>::SMEM));
+    if (const char* e = std::getenv("CFDNN_MG_RR")) rr_ = std::atoi(e) != 0;
+    if (const char* e = std::getenv("CFDNN_MG_RR_MIN")) rr_min_ = std::max(8, std::atoi(e));
     if (const char* e = std::getenv("CFDNN_MG_TBO_MODE")) tbo_mode_ = std::max(0, std::min(2, std::atoi(e)));
 }
 
@@ -363,19 +369,41 @@ void Multigrid::mean_free(int level, double* field) {
     CFDNN_LAUNCH(k_sub_scalar, g, kBlk, 0, st_, L.g, field, scalars_.p + 9);
 }
 
-void Multigrid::restrict_to(int fine) {
+// fused = true: r is never formed in HBM — k_residual_restrict evaluates it tile by tile from u and f
+bool Multigrid::rr_eligible(int fine) const {
+    const LevelGeom& g = levels_[fine]->g;
+    if (!rr_ || g.nonuniform_y || ((g.Nx | g.Ny | g.Nz) & 1) || g.Nx < rr_min_ || g.Ny < rr_min_ / 4 || g.Nz < 8)
+        return false;
+    const bool slab = g.bc[4] == CFDNN_PBC_HALO || g.bc[5] == CFDNN_PBC_HALO;
+    return !slab || g.Hz >= 2;       // the residual plane below the slab needs u two planes deep
+}
+
+void Multigrid::restrict_to(int fine, bool fused) {
     Level& F = *levels_[fine];
     Level& C = *levels_[fine + 1];
-    halo(fine, F.r.p);
+    if (fused) halo(fine, F.u.p, std::min(2, F.g.Hz));
+    else halo(fine, F.r.p);
     const int nzc_local = F.g.Nz / 2;
     dim3 g = grid2(C.g.Nx, C.g.Ny, nzc_local, kBlk);
+    int KC = 16;                     // coarse planes per CTA of the fused kernel
+    if (fused) {
+        const int tiles = ((C.g.Nx + RR_CX - 1) / RR_CX) * ((C.g.Ny + RR_CY - 1) / RR_CY);
+        while (KC > 4 && tiles * ((nzc_local + KC - 1) / KC) < 4 * 148) KC /= 2;
+        g = dim3((C.g.Nx + RR_CX - 1) / RR_CX, (C.g.Ny + RR_CY - 1) / RR_CY, (nzc_local + KC - 1) / KC);
+    }
     const int nb = g.x * g.y * g.z;
     int kc_off = 0;
     const bool agglomerate = comm_ && comm_->nranks > 1 && F.g.Nz != F.NzGlobal && C.g.Nz == C.NzGlobal;
     if (agglomerate) kc_off = comm_->rank * nzc_local;
     const bool nullsp = has_nullspace();
-    CFDNN_LAUNCH_COOP(k_restrict, g, kBlk, 0, st_, F.g, C.g, F.r.p, C.f.p, kc_off,
-                 (nullsp && !agglomerate) ? partial_.p : nullptr);
+    double* part = (nullsp && !agglomerate) ? partial_.p : nullptr;
+    if (fused) {
+        using S = RrShape<RR_CX, RR_CY>;
+        CFDNN_LAUNCH_COOP((k_residual_restrict<RR_CX, RR_CY>), g, S::NT, S::SMEM, st_, F.g, C.g, F.u.p, F.f.p, C.f.p,
+                          kc_off, KC, part);
+    } else {
+        CFDNN_LAUNCH_COOP(k_restrict, g, kBlk, 0, st_, F.g, C.g, F.r.p, C.f.p, kc_off, part);
+    }
     if (agglomerate)
         comm_->allgather_planes(C.f.p + (size_t)C.g.Hz * C.g.plane, (size_t)C.g.plane * nzc_local, st_);
     if (nullsp) {   // make_rhs_mean_free(level+1) :3274-3276
@@ -421,8 +449,12 @@ void Multigrid::vcycle(int level, int nu1, int nu2, int degree) {
         return;
     }
     for (int p = 0; p < nu1; ++p) smooth_chebyshev(level, degree);
-    residual(level);
-    restrict_to(level);
+    if (rr_eligible(level)) {
+        restrict_to(level, true);     // residual + restriction in one pass over u and f
+    } else {
+        residual(level);
+        restrict_to(level, false);
+    }
     Level& C = *levels_[level + 1];
     CFDNN_CUDA(cudaMemsetAsync(C.u.p, 0, C.size * sizeof(double), st_));   // :3279-3304
     vcycle(level + 1, nu1, nu2, degree);

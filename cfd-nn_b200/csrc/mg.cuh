@@ -128,7 +128,10 @@ private:
     bool tbo_ = true;               // lean kernel on levels without physical faces in reach (env CFDNN_MG_TBO=0: general kernel)
     void residual(int level);
     void residual_norms(int level, double* d_max, double* d_sumsq);
-    void restrict_to(int fine);
+    void restrict_to(int fine, bool fused);
+    bool rr_eligible(int fine) const;
+    int rr_min_ = 128;              // smallest level width that takes the fused kernel (env CFDNN_MG_RR_MIN, tests)
+    bool rr_ = true;                // fused residual + restriction on big levels (env CFDNN_MG_RR=0: two kernels)
     void prolong_from(int coarse);
     void mean_free(int level, double* field);
     void halo(int level, double* field, int depth = 1);   // slab interface exchange of `depth` planes (no-op single GPU)

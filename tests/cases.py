@@ -468,3 +468,24 @@ def check_smoother_variants_bitwise(B, monkeypatch, N=(32, 32, 32), cycles=2):
     assert np.array_equal(out["plain"], out["tbo"])
     d = np.linalg.norm(out["tbo_fd"] - out["plain"]) / np.linalg.norm(out["plain"])
     assert 0 < d <= 1e-13, d
+
+
+def check_fused_residual_restrict(B, monkeypatch, case, bitwise):
+    """k_residual_restrict (residual + full weighting in one pass, no r in HBM) against the two-kernel
+    path.  The coarse right-hand sides are bitwise equal; with a null space the mean that is removed
+    from them is summed over a different CTA partition, so whole solves agree to round-off, and
+    bitwise when a Dirichlet face removes the null space."""
+    out = {}
+    for tag, env in (("two", dict(CFDNN_MG_RR="0")), ("fused", dict(CFDNN_MG_RR="1", CFDNN_MG_RR_MIN="8"))):
+        for k in ("CFDNN_MG_RR", "CFDNN_MG_RR_MIN"):
+            monkeypatch.delenv(k, raising=False)
+        for k, v in env.items():
+            monkeypatch.setenv(k, v)
+        st, out[tag] = run_mg_backend(B, case)
+        out[tag + "_st"] = st
+    assert out["two_st"]["cycles"] == out["fused_st"]["cycles"]
+    if bitwise:
+        assert np.array_equal(out["two"], out["fused"])
+    else:
+        d = np.linalg.norm(out["fused"] - out["two"]) / np.linalg.norm(out["two"])
+        assert d <= 1e-13, d
