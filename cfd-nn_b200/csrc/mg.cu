@@ -237,7 +237,9 @@ void Multigrid::tb_setup() {
     tbo_attr<TB_BX_BIG, TB_BY_BIG>(); tbo_attr<TB_BX_SMALL, TB_BY_SMALL>();
     if (const char* e = std::getenv("CFDNN_MG_TB")) tb_max_ = std::max(0, std::min(2, std::atoi(e)));
     if (const char* e = std::getenv("CFDNN_MG_TBO")) tbo_ = std::atoi(e) != 0;
-    CFDNN_CUDA(cudaFuncSetAttribute(k_residual_restrict<RR_CX, RR_CY>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    CFDNN_CUDA(cudaFuncSetAttribute(k_residual_restrict<RR_CX, RR_CY, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    (int)RrShape<RR_CX, RR_CY>::SMEM));
+    CFDNN_CUDA(cudaFuncSetAttribute(k_residual_restrict<RR_CX, RR_CY, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                     (int)RrShape<RR_CX, RR_CY>::SMEM));
     if (const char* e = std::getenv("CFDNN_MG_RR")) rr_ = std::atoi(e) != 0;
     if (const char* e = std::getenv("CFDNN_MG_RR_MIN")) rr_min_ = std::max(8, std::atoi(e));
@@ -345,7 +347,7 @@ void Multigrid::residual_norms(int level, double* d_max, double* d_sumsq) {
     const int nb = g.x * g.y * g.z;
     double* pm = partial_.p;
     double* ps = partial_.p + nb;
-    CFDNN_LAUNCH_COOP((k_residual<KZ, false, true>), g, kBlk, 0, st_, L.g, L.u.p, L.f.p, L.r.p, pm, ps);
+    CFDNN_LAUNCH_COOP((k_residual<KZ, false, true>), g, kBlk, 0, st_, L.g, L.u.p, L.f.p, (double*)nullptr, pm, ps);
     CFDNN_LAUNCH_COOP(k_final_max, 1, 1024, 0, st_, pm, nb, d_max);
     CFDNN_LAUNCH_COOP(k_final_sum, 1, 1024, 0, st_, ps, nb, d_sumsq, 0.0);
     if (comm_ && comm_->nranks > 1) {
@@ -399,8 +401,14 @@ void Multigrid::restrict_to(int fine, bool fused) {
     double* part = (nullsp && !agglomerate) ? partial_.p : nullptr;
     if (fused) {
         using S = RrShape<RR_CX, RR_CY>;
-        CFDNN_LAUNCH_COOP((k_residual_restrict<RR_CX, RR_CY>), g, S::NT, S::SMEM, st_, F.g, C.g, F.u.p, F.f.p, C.f.p,
-                          kc_off, KC, part);
+        const bool open_xy = F.g.bc[0] == CFDNN_PBC_PERIODIC && F.g.bc[2] == CFDNN_PBC_PERIODIC &&
+                             F.g.Nx % (2 * RR_CX) == 0 && F.g.Ny % (2 * RR_CY) == 0;   // and no tile overshoot
+        if (open_xy)
+            CFDNN_LAUNCH_COOP((k_residual_restrict<RR_CX, RR_CY, true>), g, S::NT, S::SMEM, st_, F.g, C.g, F.u.p, F.f.p,
+                              C.f.p, kc_off, KC, part);
+        else
+            CFDNN_LAUNCH_COOP((k_residual_restrict<RR_CX, RR_CY, false>), g, S::NT, S::SMEM, st_, F.g, C.g, F.u.p, F.f.p,
+                              C.f.p, kc_off, KC, part);
     } else {
         CFDNN_LAUNCH_COOP(k_restrict, g, kBlk, 0, st_, F.g, C.g, F.r.p, C.f.p, kc_off, part);
     }

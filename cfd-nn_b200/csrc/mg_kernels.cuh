@@ -106,6 +106,7 @@ k_sweep(LevelGeom g, const double* __restrict__ u, const double* __restrict__ f,
 // ------------------------------------------------------------------ residual
 // r = f - ((uE-2u+uW)/dx2 + (uN-2u+uS)/dy2 + (uF-2u+uB)/dz2)   (compute_residual :1807-1816)
 // NORMS: also per-block max|r| and sum r^2 (compute_residual_and_norms :1943-1958).
+// r == nullptr: norms only (the convergence check; nothing reads r before the next residual pass).
 template <int KZ, bool NONUNIF, bool NORMS>
 __global__ void __launch_bounds__(256)
 k_residual(LevelGeom g, const double* __restrict__ u, const double* __restrict__ f,
@@ -149,7 +150,7 @@ k_residual(LevelGeom g, const double* __restrict__ u, const double* __restrict__
                 lap = (uE - two_c + uW) / g.dx2 + (uN - two_c + uS) / g.dy2 + (uf - two_c + ub) / g.dz2;
             }
             const double rv = f[pc + rc + i] - lap;
-            r[pc + rc + i] = rv;
+            if (r) r[pc + rc + i] = rv;
             if (NORMS) {
                 mx = fmax(mx, fabs(rv));
                 sq += rv * rv;

@@ -161,3 +161,12 @@ def test_poiseuille_2d_config1_100_steps(gpu, oracle):
 def test_blocked_smoother_variants_agree(gpu, monkeypatch):
     """128^3 puts level 0 on the 64x26 tiles and levels 1-2 on the 32x12 tiles of both blocked kernels"""
     cases.check_smoother_variants_bitwise(gpu, monkeypatch, N=(128, 128, 128), cycles=2)
+
+
+@pytest.mark.parametrize("N,bc", [((256, 128, 128), "PPPPPP"), ((160, 96, 64), "PPNNPP"), ((128, 64, 48), "DNNDND")],
+                         ids=["periodic", "channel_ragged_tiles", "mixed_dirichlet"])
+def test_fused_residual_restrict_agrees(gpu, monkeypatch, N, bc):
+    """k_residual_restrict vs k_sweep_tb<RES> + k_restrict on levels that take it by default (Nx >= 128)
+    and, forced, on every level down to 8 cells"""
+    case = ("rr_" + bc, N, bc, 2, {})
+    cases.check_fused_residual_restrict(gpu, monkeypatch, case, bitwise="D" in bc)
