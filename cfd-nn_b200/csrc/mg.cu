@@ -62,7 +62,11 @@ Multigrid::Multigrid(const cfdnn_mesh_desc& m) : mesh_(m) {
     // z-slab runs: a coarse level is REPLICATED on every rank (the slabs are all-gathered at the
     // restriction into it, restrict_to) once it is small or its slab would get thinner than 2
     // planes — no halo exchanges below that level, every rank solves it redundantly.
-    constexpr long long REPLICATE_CELLS = 64LL * 64 * 64;
+    // Threshold: a blocked 2-sweep launch on <= 128^3 cells takes ~20 us whether it runs on the whole level
+    // or on a slab of it (latency-bound), while every halo exchange of a slab level costs ~25 us of NCCL
+    // point-to-point latency (measured, profiles/r1/SCALING.md) — so such levels are cheaper replicated.
+    long long REPLICATE_CELLS = 128LL * 128 * 128;
+    if (const char* e = std::getenv("CFDNN_MG_REPLICATE_CELLS")) REPLICATE_CELLS = std::atoll(e);
     bool replicated = (Nz == NzGlob);
     while (Nx > MIN_COARSE && Ny > MIN_COARSE && NzGlob > MIN_COARSE) {
         if ((Nx | Ny | Nz | NzGlob) & 1)

@@ -49,8 +49,13 @@ def _assemble(slabs, name, Nz):
 
 @pytest.mark.parametrize("bc,ti,fixed,nsteps", [("PPPPPP", "rk3", 4, 1), ("PPWWPP", "rk2", 0, 1), ("PPWWWW", "euler", 3, 2)],
                          ids=["tgv_periodic_rk3", "channel_rk2_converge", "duct_z_walls_euler"])
-def test_two_slabs_match_single_domain(R, oracle, sim, bc, ti, fixed, nsteps):
+def test_two_slabs_match_single_domain(R, oracle, sim, bc, ti, fixed, nsteps, monkeypatch):
     sys.path.insert(0, os.path.join(ROOT, "tests"))
+    # small boxes: keep the coarse levels distributed (the default replicates levels of <= 128^3 cells) and
+    # put the fused residual + restriction on them, so the slab paths of both stay covered on CPU
+    monkeypatch.setenv("CFDNN_MG_REPLICATE_CELLS", "600")
+    if ti == "rk3":
+        monkeypatch.setenv("CFDNN_MG_RR_MIN", "8")
     import slab_worker
     N = (16, 16, 32)
     with tempfile.TemporaryDirectory() as td:
