@@ -96,6 +96,7 @@ Multigrid::Multigrid(const cfdnn_mesh_desc& m) : mesh_(m) {
 
 Multigrid::~Multigrid() {
     if (graph_) cudaGraphExecDestroy(graph_);
+    if (comm_st_) { cudaStreamDestroy(comm_st_); cudaEventDestroy(ev_fork_); cudaEventDestroy(ev_join_); }
     if (h_scalars_) cudaFreeHost(h_scalars_);
     for (auto& e : evpool_) { if (e.a) cudaEventDestroy(e.a); if (e.b) cudaEventDestroy(e.b); }
 }
@@ -205,24 +206,40 @@ void tb_launch(const LevelGeom& g, const double* in, const double* f, double* ou
     dim3 grid = tb_grid(g, T, BX, BY, &ZC);
     CFDNN_LAUNCH_COOP((k_sweep_tb<T, BX, BY, RES>), grid, S::NTHREADS, S::SMEM, st, g, in, f, out, om, ZC);
 }
-// two sweeps on a level without physical faces in reach (mg_tbo_kernels.cuh)
+// two sweeps on a level without physical faces in reach (mg_tbo_kernels.cuh).  part = 0: all z chunks;
+// 1: the chunks that read no halo plane (all but the first and the last); 2: the first and the last chunk.
 template <int BX, int BY>
 void tbo_launch(const LevelGeom& g, const double* in, const double* f, double* out, const double* w,
-                cudaStream_t st, int mode) {
+                cudaStream_t st, int mode, int part = 0) {
     using S = TbShape<2, BX, BY>;
     TbOmega<2> om;
     om.w[0] = w[0]; om.w[1] = w[1];
     int ZC;
     dim3 grid = tb_grid(g, 2, BX, BY, &ZC);
+    int zoff = 0, zstep = 1;
+    const int nch = (int)grid.z;
+    if (part == 1) { zoff = 1; grid.z = nch - 2; }
+    else if (part == 2) { zstep = nch - 1; grid.z = 2; }
     if (!g.fastdiv) {
-        CFDNN_LAUNCH_COOP((k_sweep_tbo<BX, BY, false, TBO_MODE>), grid, S::NTHREADS, S::SMEM, st, g, in, f, out, om, ZC);
+        CFDNN_LAUNCH_COOP((k_sweep_tbo<BX, BY, false, TBO_MODE>), grid, S::NTHREADS, S::SMEM, st, g, in, f, out, om, ZC, zoff, zstep);
     } else if (mode == 0) {
-        CFDNN_LAUNCH_COOP((k_sweep_tbo<BX, BY, true, 0>), grid, S::NTHREADS, S::SMEM, st, g, in, f, out, om, ZC);
+        CFDNN_LAUNCH_COOP((k_sweep_tbo<BX, BY, true, 0>), grid, S::NTHREADS, S::SMEM, st, g, in, f, out, om, ZC, zoff, zstep);
     } else if (mode == 1) {
-        CFDNN_LAUNCH_COOP((k_sweep_tbo<BX, BY, true, 1>), grid, S::NTHREADS, S::SMEM, st, g, in, f, out, om, ZC);
+        CFDNN_LAUNCH_COOP((k_sweep_tbo<BX, BY, true, 1>), grid, S::NTHREADS, S::SMEM, st, g, in, f, out, om, ZC, zoff, zstep);
     } else {
-        CFDNN_LAUNCH_COOP((k_sweep_tbo<BX, BY, true, 2>), grid, S::NTHREADS, S::SMEM, st, g, in, f, out, om, ZC);
+        CFDNN_LAUNCH_COOP((k_sweep_tbo<BX, BY, true, 2>), grid, S::NTHREADS, S::SMEM, st, g, in, f, out, om, ZC, zoff, zstep);
     }
+}
+// can the end chunks be split off?  (>= 3 chunks, and the last one at least T planes thick so that the
+// chunk before it reads no halo plane.)  Only launches of a few waves are split: there the exchange
+// (~25 us) is a large share of the pass; a 12-wave level-0 launch at 512^3 loses more to the extra tail
+// of the second launch than the hidden exchange saves (measured, profiles/r1/SCALING.md).
+template <int BX, int BY>
+bool tbo_splittable(const LevelGeom& g) {
+    int ZC;
+    const dim3 gr = tb_grid(g, 2, BX, BY, &ZC);
+    const int nch = (int)gr.z;
+    return nch >= 3 && g.Nz - (nch - 1) * ZC >= 2 && gr.x * gr.y * gr.z <= 4 * 148;
 }
 template <int BX, int BY>
 void tbo_attr() {
@@ -245,6 +262,7 @@ void Multigrid::tb_setup() {
                                     (int)RrShape<RR_CX, RR_CY>::SMEM));
     CFDNN_CUDA(cudaFuncSetAttribute(k_residual_restrict<RR_CX, RR_CY, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                     (int)RrShape<RR_CX, RR_CY>::SMEM));
+    if (const char* e = std::getenv("CFDNN_MG_OVERLAP")) overlap_ = std::atoi(e) != 0;
     if (const char* e = std::getenv("CFDNN_MG_RR")) rr_ = std::atoi(e) != 0;
     if (const char* e = std::getenv("CFDNN_MG_RR_MIN")) rr_min_ = std::max(8, std::atoi(e));
     if (const char* e = std::getenv("CFDNN_MG_TBO_MODE")) tbo_mode_ = std::max(0, std::min(2, std::atoi(e)));
@@ -259,8 +277,36 @@ bool Multigrid::sweeps_tb(int level, const double* in, double* out, const double
     if (g.nonuniform_y || (g.Nx & 1) || g.Nx < 16 || g.Ny < 8 || g.Nz < 4) return false;
     const bool slab = g.bc[4] == CFDNN_PBC_HALO || g.bc[5] == CFDNN_PBC_HALO;
     if (slab && (g.Hz < n || g.Nz < n)) return false;
-    if (slab) halo(level, const_cast<double*>(in), n);     // n-deep halo: one exchange per pass
     const bool big = g.Nx >= 128 && g.Ny >= 56 && g.Nz >= 32;
+    const bool open_xy0 = g.bc[0] == CFDNN_PBC_PERIODIC && g.bc[1] == CFDNN_PBC_PERIODIC &&
+                          g.bc[2] == CFDNN_PBC_PERIODIC && g.bc[3] == CFDNN_PBC_PERIODIC;
+    if (slab && overlap_ && w && tbo_ && n == 2 && open_xy0 && g.bc[4] == CFDNN_PBC_HALO && g.bc[5] == CFDNN_PBC_HALO &&
+        (big ? tbo_splittable<TB_BX_BIG, TB_BY_BIG>(g) : tbo_splittable<TB_BX_SMALL, TB_BY_SMALL>(g))) {
+        // Halo exchange hidden behind the chunks that do not read it: the exchange and the two end chunks
+        // run on the communication stream, the inner chunks on the solver stream, joined by events.
+        if (!comm_st_) {
+            CFDNN_CUDA(cudaStreamCreateWithFlags(&comm_st_, cudaStreamNonBlocking));
+            CFDNN_CUDA(cudaEventCreateWithFlags(&ev_fork_, cudaEventDisableTiming));
+            CFDNN_CUDA(cudaEventCreateWithFlags(&ev_join_, cudaEventDisableTiming));
+        }
+        cudaStream_t main_st = st_;
+        CFDNN_CUDA(cudaEventRecord(ev_fork_, main_st));
+        CFDNN_CUDA(cudaStreamWaitEvent(comm_st_, ev_fork_, 0));
+        st_ = comm_st_;
+        halo(level, const_cast<double*>(in), n);
+        st_ = main_st;
+        if (big) {
+            tbo_launch<TB_BX_BIG, TB_BY_BIG>(g, in, L.f.p, out, w, comm_st_, tbo_mode_, 2);
+            tbo_launch<TB_BX_BIG, TB_BY_BIG>(g, in, L.f.p, out, w, main_st, tbo_mode_, 1);
+        } else {
+            tbo_launch<TB_BX_SMALL, TB_BY_SMALL>(g, in, L.f.p, out, w, comm_st_, tbo_mode_, 2);
+            tbo_launch<TB_BX_SMALL, TB_BY_SMALL>(g, in, L.f.p, out, w, main_st, tbo_mode_, 1);
+        }
+        CFDNN_CUDA(cudaEventRecord(ev_join_, comm_st_));
+        CFDNN_CUDA(cudaStreamWaitEvent(main_st, ev_join_, 0));
+        return true;
+    }
+    if (slab) halo(level, const_cast<double*>(in), n);     // n-deep halo: one exchange per pass
     if (!w) {
         if (big) tb_launch<1, TB_BX_BIG, TB_BY_BIG, true>(g, in, L.f.p, out, nullptr, st_);
         else tb_launch<1, TB_BX_SMALL, TB_BY_SMALL, true>(g, in, L.f.p, out, nullptr, st_);

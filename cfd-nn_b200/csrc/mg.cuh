@@ -130,6 +130,9 @@ private:
     void residual_norms(int level, double* d_max, double* d_sumsq);
     void restrict_to(int fine, bool fused);
     bool rr_eligible(int fine) const;
+    bool overlap_ = true;           // slab levels: halo exchange overlapped with the inner z chunks (env CFDNN_MG_OVERLAP=0: serial)
+    cudaStream_t comm_st_ = nullptr;
+    cudaEvent_t ev_fork_ = nullptr, ev_join_ = nullptr;
     int rr_min_ = 128;              // smallest level width that takes the fused kernel (env CFDNN_MG_RR_MIN, tests)
     bool rr_ = true;                // fused residual + restriction on big levels (env CFDNN_MG_RR=0: two kernels)
     void prolong_from(int coarse);

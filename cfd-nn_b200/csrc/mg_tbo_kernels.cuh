@@ -86,7 +86,7 @@ inline void tbo_wait(unsigned long long*, unsigned) { __syncthreads(); }
 template <int BX, int BY, bool FD, int MODE>
 __global__ void __launch_bounds__(TbShape<2, BX, BY>::NTHREADS, 1)
 k_sweep_tbo(LevelGeom g, const double* __restrict__ u, const double* __restrict__ f, double* __restrict__ out,
-            TbOmega<2> om, int ZC) {
+            TbOmega<2> om, int ZC, int zoff, int zstep) {
     constexpr int T = 2;
     using S = TbShape<T, BX, BY>;
     CFDNN_DYN_SMEM(double, sm);
@@ -100,7 +100,7 @@ k_sweep_tbo(LevelGeom g, const double* __restrict__ u, const double* __restrict_
     const int lx = 4 * q;
     const int gx0 = (int)blockIdx.x * BX - S::HX + lx;
     const int gy = (int)blockIdx.y * BY - T + row;
-    const int z0 = (int)blockIdx.z * ZC;
+    const int z0 = (zoff + (int)blockIdx.z * zstep) * ZC;   // z chunk (zoff, zstep: a launch may cover a subset of chunks)
     const int z1 = min(z0 + ZC, g.Nz);
     const bool perz = g.bc[4] == CFDNN_PBC_PERIODIC;
 

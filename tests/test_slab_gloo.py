@@ -47,9 +47,11 @@ def _assemble(slabs, name, Nz):
     return np.concatenate(parts, axis=0)
 
 
-@pytest.mark.parametrize("bc,ti,fixed,nsteps", [("PPPPPP", "rk3", 4, 1), ("PPWWPP", "rk2", 0, 1), ("PPWWWW", "euler", 3, 2)],
-                         ids=["tgv_periodic_rk3", "channel_rk2_converge", "duct_z_walls_euler"])
-def test_two_slabs_match_single_domain(R, oracle, sim, bc, ti, fixed, nsteps, monkeypatch):
+@pytest.mark.parametrize("bc,ti,fixed,nsteps,N",
+                         [("PPPPPP", "rk3", 4, 1, (16, 16, 32)), ("PPWWPP", "rk2", 0, 1, (16, 16, 32)),
+                          ("PPWWWW", "euler", 3, 2, (16, 16, 32)), ("PPPPPP", "euler", 2, 1, (16, 16, 64))],
+                         ids=["tgv_periodic_rk3", "channel_rk2_converge", "duct_z_walls_euler", "tgv_overlapped_halo"])
+def test_two_slabs_match_single_domain(R, oracle, sim, bc, ti, fixed, nsteps, N, monkeypatch):
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     # small boxes: keep the coarse levels distributed (the default replicates levels of <= 128^3 cells) and
     # put the fused residual + restriction on them, so the slab paths of both stay covered on CPU
@@ -57,7 +59,8 @@ def test_two_slabs_match_single_domain(R, oracle, sim, bc, ti, fixed, nsteps, mo
     if ti == "rk3":
         monkeypatch.setenv("CFDNN_MG_RR_MIN", "8")
     import slab_worker
-    N = (16, 16, 32)
+    # (16, 16, 64): 32 planes per slab = 4 z chunks of the blocked smoother, so the halo exchange is overlapped
+    # with the inner chunks (split launch, Multigrid::sweeps_tb)
     with tempfile.TemporaryDirectory() as td:
         slabs = _run_slabs(2, N, bc, ti, nsteps, fixed, td)
         u, v, w = slab_worker.global_init(*N, bc)
