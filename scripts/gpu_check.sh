@@ -17,4 +17,6 @@ ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum 
 echo "ncu launches exit $?"
 ncu --set full --clock-control none --import-source on -k regex:k_sweep_tbo -s 4 -c 2 -f -o $out/prof_tb512_$tag $PROF > $out/ncu_full_$tag.log 2>&1
 echo "ncu full exit $?"
+ncu --set full --clock-control none --import-source on -k regex:k_residual_restrict -c 1 -f -o $out/prof_rr512_$tag $PROF > $out/ncu_full_rr_$tag.log 2>&1
+echo "ncu full (residual+restrict) exit $?"
 ls -la $out | tail -12
