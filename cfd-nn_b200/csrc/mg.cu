@@ -96,6 +96,7 @@ Multigrid::Multigrid(const cfdnn_mesh_desc& m) : mesh_(m) {
 
 Multigrid::~Multigrid() {
     if (graph_) cudaGraphExecDestroy(graph_);
+    if (sub_graph_) cudaGraphExecDestroy(sub_graph_);
     if (comm_st_) { cudaStreamDestroy(comm_st_); cudaEventDestroy(ev_fork_); cudaEventDestroy(ev_join_); }
     if (h_scalars_) cudaFreeHost(h_scalars_);
     for (auto& e : evpool_) { if (e.a) cudaEventDestroy(e.a); if (e.b) cudaEventDestroy(e.b); }
@@ -134,6 +135,8 @@ void Multigrid::apply_bc_codes() {
 void Multigrid::invalidate_graph() {
     if (graph_) { cudaGraphExecDestroy(graph_); graph_ = nullptr; }
     graph_key_[0] = graph_key_[1] = graph_key_[2] = -1;
+    if (sub_graph_) { cudaGraphExecDestroy(sub_graph_); sub_graph_ = nullptr; }
+    sub_key_[0] = sub_key_[1] = sub_key_[2] = sub_key_[3] = -1;
 }
 
 bool Multigrid::has_nullspace() const {   // :3393-3402
@@ -515,9 +518,53 @@ void Multigrid::vcycle(int level, int nu1, int nu2, int degree) {
     }
     Level& C = *levels_[level + 1];
     CFDNN_CUDA(cudaMemsetAsync(C.u.p, 0, C.size * sizeof(double), st_));   // :3279-3304
-    vcycle(level + 1, nu1, nu2, degree);
+    descend(level + 1, nu1, nu2, degree);
     prolong_from(level + 1);
     for (int p = 0; p < nu2; ++p) smooth_chebyshev(level, degree);
+}
+
+// z-slab runs cannot replay the whole V-cycle as a CUDA graph (NCCL exchanges on the distributed levels),
+// but everything below the first REPLICATED level is communication-free: that sub-V-cycle (~100 launches of
+// a few microseconds each) is captured once and replayed, so the coarse levels do not wait on the host.
+void Multigrid::descend(int level, int nu1, int nu2, int degree) {
+    const bool multi = comm_ && comm_->nranks > 1;
+    const bool first_replicated = multi && use_graph_ && sub_ok_ && level > 0 &&
+                                  levels_[level]->g.Nz == levels_[level]->NzGlobal &&
+                                  levels_[level - 1]->g.Nz != levels_[level - 1]->NzGlobal;
+    if (!first_replicated) { vcycle(level, nu1, nu2, degree); return; }
+    if (!sub_graph_ || sub_key_[0] != nu1 || sub_key_[1] != nu2 || sub_key_[2] != degree || sub_key_[3] != level) {
+        if (sub_graph_) { cudaGraphExecDestroy(sub_graph_); sub_graph_ = nullptr; }
+        std::vector<double*> before;
+        for (auto& L : levels_) before.push_back(L->u.p);
+        cudaGraph_t gr = nullptr;
+        CFDNN_CUDA(cudaStreamBeginCapture(st_, cudaStreamCaptureModeThreadLocal));
+        const unsigned long long l0 = g_launches.load();
+        try {
+            vcycle(level, nu1, nu2, degree);
+        } catch (...) {
+            cudaStreamEndCapture(st_, &gr);
+            if (gr) cudaGraphDestroy(gr);
+            throw;
+        }
+        sub_launches_ = g_launches.load() - l0;
+        g_launches.store(l0);
+        CFDNN_CUDA(cudaStreamEndCapture(st_, &gr));
+        bool same = true;
+        for (size_t l = 0; l < levels_.size(); ++l) same = same && before[l] == levels_[l]->u.p;
+        if (!same) {   // odd sweep count at some level: a replay would address the wrong buffers
+            for (size_t l = 0; l < levels_.size(); ++l)
+                if (before[l] != levels_[l]->u.p) std::swap(levels_[l]->u.p, levels_[l]->tmp.p);
+            cudaGraphDestroy(gr);
+            sub_ok_ = false;
+            vcycle(level, nu1, nu2, degree);
+            return;
+        }
+        CFDNN_CUDA(cudaGraphInstantiate(&sub_graph_, gr, 0));
+        cudaGraphDestroy(gr);
+        sub_key_[0] = nu1; sub_key_[1] = nu2; sub_key_[2] = degree; sub_key_[3] = level;
+    }
+    CFDNN_CUDA(cudaGraphLaunch(sub_graph_, st_));
+    g_launches.fetch_add(sub_launches_, std::memory_order_relaxed);
 }
 
 void Multigrid::run_vcycle(int nu1, int nu2, int degree) {

@@ -118,6 +118,11 @@ private:
     bool has_nullspace() const;
     void vcycle(int level, int nu1, int nu2, int degree);
     void run_vcycle(int nu1, int nu2, int degree);
+    void descend(int level, int nu1, int nu2, int degree);   // vcycle(level), replayed from a graph when communication-free
+    cudaGraphExec_t sub_graph_ = nullptr;                    // sub-V-cycle below the first replicated level (z-slab runs)
+    int sub_key_[4] = {-1, -1, -1, -1};
+    unsigned long long sub_launches_ = 0;
+    bool sub_ok_ = true;
     void smooth_chebyshev(int level, int degree);
     void smooth_jacobi(int level, int iters, double omega);
     void sweep(int level, const double* uin, double* uout, double omega);
