@@ -258,6 +258,10 @@ void Multigrid::tb_setup() {
     tb_attr<1, TB_BX_BIG, TB_BY_BIG>(); tb_attr<2, TB_BX_BIG, TB_BY_BIG>();
     tb_attr<1, TB_BX_SMALL, TB_BY_SMALL>(); tb_attr<2, TB_BX_SMALL, TB_BY_SMALL>();
     tb_attr<1, TB_BX_BIG, TB_BY_BIG, true>(); tb_attr<1, TB_BX_SMALL, TB_BY_SMALL, true>();
+    CFDNN_CUDA(cudaFuncSetAttribute(k_sweep_tb<1, TB_BX_BIG, TB_BY_BIG, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    (int)TbShape<1, TB_BX_BIG, TB_BY_BIG>::SMEM));
+    CFDNN_CUDA(cudaFuncSetAttribute(k_sweep_tb<1, TB_BX_SMALL, TB_BY_SMALL, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    (int)TbShape<1, TB_BX_SMALL, TB_BY_SMALL>::SMEM));
     tbo_attr<TB_BX_BIG, TB_BY_BIG>(); tbo_attr<TB_BX_SMALL, TB_BY_SMALL>();
     if (const char* e = std::getenv("CFDNN_MG_TB")) tb_max_ = std::max(0, std::min(2, std::atoi(e)));
     if (const char* e = std::getenv("CFDNN_MG_TBO")) tbo_ = std::atoi(e) != 0;
@@ -266,6 +270,7 @@ void Multigrid::tb_setup() {
     CFDNN_CUDA(cudaFuncSetAttribute(k_residual_restrict<RR_CX, RR_CY, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                     (int)RrShape<RR_CX, RR_CY>::SMEM));
     if (const char* e = std::getenv("CFDNN_MG_OVERLAP")) overlap_ = std::atoi(e) != 0;
+    if (const char* e = std::getenv("CFDNN_MG_NORMS_TB")) norms_tb_ = std::atoi(e) != 0;
     if (const char* e = std::getenv("CFDNN_MG_RR")) rr_ = std::atoi(e) != 0;
     if (const char* e = std::getenv("CFDNN_MG_RR_MIN")) rr_min_ = std::max(8, std::atoi(e));
     if (const char* e = std::getenv("CFDNN_MG_TBO_MODE")) tbo_mode_ = std::max(0, std::min(2, std::atoi(e)));
@@ -397,9 +402,30 @@ void Multigrid::residual_norms(int level, double* d_max, double* d_sumsq) {
     Level& L = *levels_[level];
     halo(level, L.u.p);
     dim3 g = grid2(L.g.Nx, L.g.Ny, (L.g.Nz + KZ - 1) / KZ, kBlk);
-    const int nb = g.x * g.y * g.z;
+    int nb = g.x * g.y * g.z;
     double* pm = partial_.p;
     double* ps = partial_.p + nb;
+    const LevelGeom& lg = L.g;
+    if (tb_max_ > 0 && norms_tb_ && !lg.nonuniform_y && !(lg.Nx & 1) && lg.Nx >= 16 && lg.Ny >= 8 && lg.Nz >= 4) {
+        // tiled, norms only: u and f are read once (16 B per cell), nothing is written
+        TbOmega<1> om; om.w[0] = 0.0;
+        int ZC;
+        if (lg.Nx >= 128 && lg.Ny >= 56 && lg.Nz >= 32) {
+            using S = TbShape<1, TB_BX_BIG, TB_BY_BIG>;
+            dim3 tg = tb_grid(lg, 1, TB_BX_BIG, TB_BY_BIG, &ZC);
+            nb = tg.x * tg.y * tg.z;
+            ps = partial_.p + nb;
+            CFDNN_LAUNCH_COOP((k_sweep_tb<1, TB_BX_BIG, TB_BY_BIG, true, true>), tg, S::NTHREADS, S::SMEM, st_, lg, L.u.p,
+                              L.f.p, (double*)nullptr, om, ZC, pm, ps);
+        } else {
+            using S = TbShape<1, TB_BX_SMALL, TB_BY_SMALL>;
+            dim3 tg = tb_grid(lg, 1, TB_BX_SMALL, TB_BY_SMALL, &ZC);
+            nb = tg.x * tg.y * tg.z;
+            ps = partial_.p + nb;
+            CFDNN_LAUNCH_COOP((k_sweep_tb<1, TB_BX_SMALL, TB_BY_SMALL, true, true>), tg, S::NTHREADS, S::SMEM, st_, lg, L.u.p,
+                              L.f.p, (double*)nullptr, om, ZC, pm, ps);
+        }
+    } else
     CFDNN_LAUNCH_COOP((k_residual<KZ, false, true>), g, kBlk, 0, st_, L.g, L.u.p, L.f.p, (double*)nullptr, pm, ps);
     CFDNN_LAUNCH_COOP(k_final_max, 1, 1024, 0, st_, pm, nb, d_max);
     CFDNN_LAUNCH_COOP(k_final_sum, 1, 1024, 0, st_, ps, nb, d_sumsq, 0.0);

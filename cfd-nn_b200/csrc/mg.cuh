@@ -135,6 +135,7 @@ private:
     void residual_norms(int level, double* d_max, double* d_sumsq);
     void restrict_to(int fine, bool fused);
     bool rr_eligible(int fine) const;
+    bool norms_tb_ = true;          // convergence-check residual norms with the tiled kernel (env CFDNN_MG_NORMS_TB=0: k_residual)
     bool overlap_ = true;           // slab levels: halo exchange overlapped with the inner z chunks (env CFDNN_MG_OVERLAP=0: serial)
     cudaStream_t comm_st_ = nullptr;
     cudaEvent_t ev_fork_ = nullptr, ev_join_ = nullptr;

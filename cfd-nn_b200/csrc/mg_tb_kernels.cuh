@@ -82,10 +82,13 @@ __device__ __forceinline__ double residual_point(const LevelGeom& g, double uc, 
 
 // RES = true: the LAST stage evaluates the residual of its input level instead of a sweep
 // (T = 1, RES: a tiled residual kernel; `out` is then the r array).
-template <int T, int BX, int BY, bool RES = false>
+// NORMS (with RES): nothing is stored; per-CTA max|r| and sum r^2 go to part_max / part_sq
+// (compute_residual_and_norms :1833-1970 — the convergence check, whose r nobody reads).
+template <int T, int BX, int BY, bool RES = false, bool NORMS = false>
 __global__ void __launch_bounds__(TbShape<T, BX, BY>::NTHREADS, 1)
 k_sweep_tb(LevelGeom g, const double* __restrict__ u, const double* __restrict__ f,
-           double* __restrict__ out, TbOmega<T> om, int ZC) {
+           double* __restrict__ out, TbOmega<T> om, int ZC, double* __restrict__ part_max = nullptr,
+           double* __restrict__ part_sq = nullptr) {
     using S = TbShape<T, BX, BY>;
     static_assert(T >= 1 && T <= 2, "f ring has 3 slots");
     CFDNN_DYN_SMEM(double, sm);
@@ -175,6 +178,7 @@ k_sweep_tb(LevelGeom g, const double* __restrict__ u, const double* __restrict__
     load_plane(u, zi_first, nu_);
     load_plane(f, zi_first - 1, fr[0]);
 
+    double nmx = 0.0, nsq = 0.0;
     int par = 0;
     for (int zb = zi_first; zb <= zi_last; zb += 3) {
 #pragma unroll
@@ -246,16 +250,33 @@ k_sweep_tb(LevelGeom g, const double* __restrict__ u, const double* __restrict__
                 } else {
                     const int zf = zi - T;                 // o = level-T plane zi - T
                     if (zf >= z0 && zf < z1) {
-                        double* base = out + (size_t)(unsigned)(zf + g.Hz) * (size_t)uplane;
+                        if (NORMS) {
 #pragma unroll
-                        for (int h = 0; h < 2; ++h)
-                            if (stok[h]) st_pair(base + off[h], o[2 * h], o[2 * h + 1]);
+                            for (int h = 0; h < 2; ++h)
+                                if (stok[h]) {
+                                    nmx = fmax(nmx, fmax(fabs(o[2 * h]), fabs(o[2 * h + 1])));
+                                    nsq += o[2 * h] * o[2 * h];
+                                    nsq += o[2 * h + 1] * o[2 * h + 1];
+                                }
+                        } else {
+                            double* base = out + (size_t)(unsigned)(zf + g.Hz) * (size_t)uplane;
+#pragma unroll
+                            for (int h = 0; h < 2; ++h)
+                                if (stok[h]) st_pair(base + off[h], o[2 * h], o[2 * h + 1]);
+                        }
                     }
                 }
             }
             __syncthreads();
             par ^= 1;
         }
+    }
+    if (NORMS) {
+        const int bid = ((int)blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+        const double m = block_max(nmx, sm);
+        if (t == 0) part_max[bid] = m;
+        const double q2 = block_sum(nsq, sm);
+        if (t == 0) part_sq[bid] = q2;
     }
 }
 
