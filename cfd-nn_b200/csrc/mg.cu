@@ -435,7 +435,7 @@ void Multigrid::residual_norms(int level, double* d_max, double* d_sumsq) {
     }
 }
 
-void Multigrid::mean_free(int level, double* field) {
+void Multigrid::mean_free(int level, double* field, bool subtract) {
     Level& L = *levels_[level];
     dim3 g = grid2(L.g.Nx, L.g.Ny, L.g.Nz, kBlk);
     const int nb = g.x * g.y * g.z;
@@ -447,7 +447,7 @@ void Multigrid::mean_free(int level, double* field) {
         comm_->allreduce_sum(scalars_.p + 8, 1, st_);
         CFDNN_LAUNCH_COOP(k_final_sum, 1, 32, 0, st_, scalars_.p + 8, 1, scalars_.p + 8, count);
     }
-    CFDNN_LAUNCH(k_sub_scalar, g, kBlk, 0, st_, L.g, field, scalars_.p + 9);
+    if (subtract) CFDNN_LAUNCH(k_sub_scalar, g, kBlk, 0, st_, L.g, field, scalars_.p + 9);
 }
 
 // fused = true: r is never formed in HBM — k_residual_restrict evaluates it tile by tile from u and f
@@ -752,11 +752,12 @@ int Multigrid::solve_dev(const double* rhs, double* p, const cfdnn_poisson_cfg& 
     }
     stats.cycles = cycles_used;
 
-    if (has_nullspace()) mean_free(0, L0.u.p);   // fix_nullspace(0) :3404-3409
+    const bool nullsp = has_nullspace();
+    if (nullsp) mean_free(0, L0.u.p, /*subtract=*/false);   // fix_nullspace(0) :3404-3409: the mean; subtracted in k_copy_out
     halo(0, L0.u.p);
     {
         dim3 g = grid2(L0.g.Nx + 2 * Ng, L0.g.Ny + 2 * Ng, L0.g.Nz + 2 * Ng, kBlk);
-        CFDNN_LAUNCH(k_copy_out, g, kBlk, 0, st_, L0.g, Ng, L0.u.p, p);
+        CFDNN_LAUNCH(k_copy_out, g, kBlk, 0, st_, L0.g, Ng, L0.u.p, p, nullsp ? scalars_.p + 9 : (const double*)nullptr);
     }
     vcycle_count = cycles_used;
     if (cur_ev_) cur_ev_->cycles = cycles_used;

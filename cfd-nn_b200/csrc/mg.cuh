@@ -142,7 +142,7 @@ private:
     int rr_min_ = 128;              // smallest level width that takes the fused kernel (env CFDNN_MG_RR_MIN, tests)
     bool rr_ = true;                // fused residual + restriction on big levels (env CFDNN_MG_RR=0: two kernels)
     void prolong_from(int coarse);
-    void mean_free(int level, double* field);
+    void mean_free(int level, double* field, bool subtract = true);
     void halo(int level, double* field, int depth = 1);   // slab interface exchange of `depth` planes (no-op single GPU)
     void invalidate_graph();
 };

@@ -412,9 +412,13 @@ k_copy_in(LevelGeom g, int Ng, const double* __restrict__ rhs, const double* __r
     f[o] = rhs[src];
     u[o] = p[src];
 }
-// out: p <- u on ALL cells, ghosts from the BCs in x,y,z pass order    (solve :3769-3783)
+// out: p <- u on ALL cells, ghosts from the BCs in x,y,z pass order    (solve :3769-3783).
+// mean != nullptr: p <- u - mean[0], the interior-mean removal of fix_nullspace (:3404-3477) applied on
+// the way out instead of in a separate read-modify-write pass over u (only with a null space, i.e. no
+// Dirichlet face, so every ghost is a copy of an interior value and gets the same subtraction).
 static __global__ void __launch_bounds__(256)
-k_copy_out(LevelGeom g, int Ng, const double* __restrict__ u, double* __restrict__ p) {
+k_copy_out(LevelGeom g, int Ng, const double* __restrict__ u, double* __restrict__ p,
+           const double* __restrict__ mean) {
     const int I = blockIdx.x * blockDim.x + threadIdx.x;   // ghosted indices
     const int J = blockIdx.y * blockDim.y + threadIdx.y;
     const int K = blockIdx.z;
@@ -424,7 +428,9 @@ k_copy_out(LevelGeom g, int Ng, const double* __restrict__ u, double* __restrict
     const int i = bc_map(I - Ng, g.Nx, g.bc[0], g.bc[1], s);
     const int j = bc_map(J - Ng, g.Ny, g.bc[2], g.bc[3], s);
     const int k = bc_map(K - Ng, g.Nz, g.bc[4], g.bc[5], s);
-    p[((size_t)K * sy + J) * sx + I] = s * u[lidx(g, i, j, k)];
+    double v = u[lidx(g, i, j, k)];
+    if (mean) v -= mean[0];
+    p[((size_t)K * sy + J) * sx + I] = s * v;
 }
 
 // ------------------------------------------------------------------ coarsest level
