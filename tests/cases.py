@@ -3,6 +3,7 @@ import os
 import tempfile
 
 import numpy as np
+import pytest
 
 import refharness as R
 
@@ -489,3 +490,19 @@ def check_fused_residual_restrict(B, monkeypatch, case, bitwise):
     else:
         d = np.linalg.norm(out["fused"] - out["two"]) / np.linalg.norm(out["two"])
         assert d <= 1e-13, d
+
+
+def check_tiled_norms(B, monkeypatch, case):
+    """convergence-check norms from the tiled residual kernel (k_sweep_tb<..,RES,NORMS>, no stores) against
+    the plain k_residual<NORMS>: same cycle count, same solution, norms equal to summation round-off"""
+    out = {}
+    for tag, v in (("plain", "0"), ("tiled", "1")):
+        monkeypatch.setenv("CFDNN_MG_NORMS_TB", v)
+        out[tag] = run_mg_backend(B, case)
+    (sa, pa), (sb, pb) = out["plain"], out["tiled"]
+    assert sa["cycles"] == sb["cycles"] and sa["converged"] == sb["converged"]
+    assert np.array_equal(pa, pb)
+    for k in ("r0", "residual"):
+        assert sa[k] == sb[k], k                        # max norms: order-independent
+    for k in ("r0_l2", "residual_l2"):
+        assert sb[k] == pytest.approx(sa[k], rel=1e-12), k

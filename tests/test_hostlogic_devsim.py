@@ -39,6 +39,11 @@ def test_blocked_smoother_variants_agree(sim, monkeypatch):
     cases.check_smoother_variants_bitwise(sim, monkeypatch, N=(16, 16, 16), cycles=1)
 
 
+@pytest.mark.tiled
+def test_tiled_convergence_norms_agree(sim, monkeypatch):
+    cases.check_tiled_norms(sim, monkeypatch, cases.MG_CASES[5])        # mixed BCs, convergence mode, hits max cycles
+
+
 @pytest.mark.parametrize("case", cases.MG_CASES[:7], ids=[c[0] for c in cases.MG_CASES[:7]])
 def test_fused_residual_restrict_agrees(sim, monkeypatch, case):
     cases.check_fused_residual_restrict(sim, monkeypatch, case, bitwise="D" in case[2])
