@@ -99,6 +99,9 @@ _SIGS = {
     "cfdnn_solver_cycle_log": (C.c_int, [C.c_void_p, c_int_p, C.c_int, c_int_p]),
     "cfdnn_solver_set_turbulence_model": (C.c_int, [C.c_void_p, C.c_void_p]),
     "cfdnn_solver_last_timing": (C.c_int, [C.c_void_p, c_double_p, c_double_p, c_int_p]),
+    "cfdnn_solver_device_ptr": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t)]),
+    "cfdnn_solver_set_external_nu_t": (C.c_int, [C.c_void_p, C.c_int]),
+    "cfdnn_solver_phase_timing": (C.c_int, [C.c_void_p, c_double_p]),
     "cfdnn_solver_time_smoother": (C.c_int, [C.c_void_p, C.c_int, c_double_p]),
     "cfdnn_comm_unique_id": (C.c_int, [C.c_void_p]),
     "cfdnn_solver_comm_init": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
@@ -108,6 +111,8 @@ _SIGS = {
     "cfdnn_nn_set_params": (C.c_int, [C.c_void_p, C.c_double, C.c_double, C.c_double, C.c_double, C.c_double]),
     "cfdnn_nn_update": (C.c_int, [C.c_void_p, C.POINTER(MeshDesc), c_double_p, c_double_p, c_double_p, c_double_p,
                                   c_double_p, c_double_p, c_double_p, c_double_p]),
+    "cfdnn_nn_update_dev": (C.c_int, [C.c_void_p, C.POINTER(MeshDesc), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                      C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "cfdnn_nn_forward": (C.c_int, [C.c_void_p, c_double_p, c_double_p, C.c_size_t]),
     "cfdnn_nn_last_timing": (C.c_int, [C.c_void_p, c_double_p]),
     "cfdnn_nn_uses_tensor_cores": (C.c_int, [C.c_void_p]),

@@ -163,6 +163,21 @@ int cfdnn_solver_last_timing(const cfdnn_solver* s, double* step_ms, double* vcy
     if (n_vcycles) *n_vcycles = s->impl.last_vcycles;
     return CFDNN_OK;
 }
+int cfdnn_solver_device_ptr(cfdnn_solver* s, int field, double** dev_out, size_t* n_out) {
+    return guarded([&] {
+        size_t n = 0;
+        double* p = s->impl.view_ptr(field, &n);
+        if (dev_out) *dev_out = p;
+        if (n_out) *n_out = n;
+    });
+}
+int cfdnn_solver_set_external_nu_t(cfdnn_solver* s, int on) {
+    return guarded([&] { s->impl.set_external_nu_t(on != 0); });
+}
+int cfdnn_solver_phase_timing(const cfdnn_solver* s, double ms[CFDNN_PHASE_COUNT]) {
+    for (int q = 0; q < CFDNN_PHASE_COUNT; ++q) ms[q] = s->impl.last_phase_ms[q];
+    return CFDNN_OK;
+}
 int cfdnn_solver_time_smoother(cfdnn_solver* s, int reps, double* ms_per_launch) {
     return guarded([&] {
         const double ms = s->impl.mg().time_level0_smoother(reps, s->impl.stream());
@@ -201,6 +216,11 @@ int cfdnn_nn_set_params(cfdnn_nn* nn, double nu, double delta, double u_ref, dou
 int cfdnn_nn_update(cfdnn_nn* nn, const cfdnn_mesh_desc* mesh, const double* u, const double* v, const double* k,
                     const double* omega, double* nu_t, double* tau_xx, double* tau_xy, double* tau_yy) {
     return guarded([&] { nn->impl.update_host(*mesh, u, v, k, omega, nu_t, tau_xx, tau_xy, tau_yy); });
+}
+int cfdnn_nn_update_dev(cfdnn_nn* nn, const cfdnn_mesh_desc* mesh, const double* u_dev, const double* v_dev,
+                        const double* k_dev, const double* omega_dev, double* nu_t_dev, double* tau_xx_dev,
+                        double* tau_xy_dev, double* tau_yy_dev) {
+    return guarded([&] { nn->impl.update_dev_ptrs(*mesh, u_dev, v_dev, k_dev, omega_dev, nu_t_dev, tau_xx_dev, tau_xy_dev, tau_yy_dev); });
 }
 int cfdnn_nn_forward(cfdnn_nn* nn, const double* x, double* y, size_t n) {
     return guarded([&] { nn->impl.forward_host(x, y, n); });

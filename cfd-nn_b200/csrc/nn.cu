@@ -73,7 +73,20 @@ __device__ __forceinline__ double wall_distance(double y, double y_lo, double y_
 struct CellCtx {
     double T[4][3];
     double k_val, Sxy_, S_mag;
+    double Oxy;              // tau-scaled rotation rate the basis was built from (with T[0] it rebuilds T[1..3])
 };
+
+// TensorBasis::compute (src/features.cpp:192-292) from the normalised strain / rotation components:
+// T1 = S, T2 = [S, Omega], T3 = dev(S^2) (half trace in 2-D), T4 = 0
+__device__ __forceinline__ void tensor_basis(double Sxx, double Sxy, double Syy, double Oxy, CellCtx& c) {
+    c.T[0][0] = Sxx; c.T[0][1] = Sxy; c.T[0][2] = Syy;
+    c.T[1][0] = -2.0 * Sxy * Oxy; c.T[1][1] = (Sxx - Syy) * Oxy; c.T[1][2] = 2.0 * Sxy * Oxy;
+    const double S2xx = Sxx * Sxx + Sxy * Sxy, S2yy = Sxy * Sxy + Syy * Syy, S2xy = Sxy * (Sxx + Syy);
+    const double trS2 = S2xx + S2yy;
+    c.T[2][0] = S2xx - 0.5 * trS2; c.T[2][1] = S2xy; c.T[2][2] = S2yy - 0.5 * trS2;
+    c.T[3][0] = 0.0; c.T[3][1] = 0.0; c.T[3][2] = 0.0;
+    c.Oxy = Oxy;
+}
 
 // Features of one cell (i, j) of plane kk: TBNN 5 invariants (src/features.cpp:121-190) or the 6
 // scalar-nu_t features (:67-119); for TBNN also the tensor basis (:192-292) and k / omega.
@@ -150,12 +163,7 @@ __device__ __forceinline__ void cell_features(const Geom& g, const NNParams& prm
     {
         const double Sxx = dudx * tau, Syy = gdvdy * tau;
         const double Sxy = (0.5 * (gdudy + dvdx)) * tau, Oxy = (0.5 * (gdudy - dvdx)) * tau;
-        c.T[0][0] = Sxx; c.T[0][1] = Sxy; c.T[0][2] = Syy;
-        c.T[1][0] = -2.0 * Sxy * Oxy; c.T[1][1] = (Sxx - Syy) * Oxy; c.T[1][2] = 2.0 * Sxy * Oxy;
-        const double S2xx = Sxx * Sxx + Sxy * Sxy, S2yy = Sxy * Sxy + Syy * Syy, S2xy = Sxy * (Sxx + Syy);
-        const double trS2 = S2xx + S2yy;
-        c.T[2][0] = S2xx - 0.5 * trS2; c.T[2][1] = S2xy; c.T[2][2] = S2yy - 0.5 * trS2;
-        c.T[3][0] = 0.0; c.T[3][1] = 0.0; c.T[3][2] = 0.0;
+        tensor_basis(Sxx, Sxy, Syy, Oxy, c);
     }
 #undef U2
 #undef V2
@@ -409,6 +417,154 @@ k_nn_update_mma(Geom g, NNFrag net, NNParams prm, const double* __restrict__ yc,
         __syncwarp();
     }
 }
+// ---- shape-specialised tensor-core kernel (the product path for the shipped presets).
+// Networks of the form  in(<=8) -> H*8 -> ... -> H*8 -> out(<=8)  with tanh hidden layers and a linear
+// output (5-64-64-64-4 TBNN: H = 8; 6-32-32-1 MLP: H = 4).  Differences to the generic kernel above:
+//   * every tile loop has compile-time bounds and there is no branch inside a layer, so ptxas sees one
+//     straight-line block per layer and interleaves the tanh of one group of N tiles (FP64 FMA pipe)
+//     with the DMMAs of the next group (tensor pipe);
+//   * a warp pushes ONE 8-cell M tile through the network at a time with FOUR N tiles in flight
+//     (four independent accumulator chains, as before) — half the live activations, so the kernel fits
+//     128 registers and 16 warps per SM (4 per scheduler) instead of 8, which is what hides the DMMA
+//     and tanh latencies;
+//   * the per-cell context of the nu_t stage (7 doubles) waits in shared memory, not in registers;
+//   * the single-N-tile output layer splits K over four chains instead of one 16-deep dependent chain.
+constexpr int MMAH_WARPS = 8;
+
+template <int NTI, int NTO, bool TANH>
+__device__ __forceinline__ void mma_layer(const double2* __restrict__ Wl, const double* __restrict__ bl, int lane,
+                                          int q, const double2 (&a)[NTI], double2 (&o)[NTO]) {
+    if constexpr (NTO == 1) {
+        // one N tile: K tiles dealt to four chains, summed pairwise at the end
+        double2 c[4];
+        c[0] = *reinterpret_cast<const double2*>(bl + 2 * q);
+#pragma unroll
+        for (int j = 1; j < 4; ++j) c[j] = make_double2(0.0, 0.0);
+#pragma unroll
+        for (int ni = 0; ni < NTI; ++ni) {
+            const double2 w = Wl[ni * 32 + lane];
+            dmma(c[ni & 3].x, c[ni & 3].y, a[ni].x, w.x);
+            dmma(c[ni & 3].x, c[ni & 3].y, a[ni].y, w.y);
+        }
+        double2 r;
+        r.x = (c[0].x + c[1].x) + (c[2].x + c[3].x);
+        r.y = (c[0].y + c[1].y) + (c[2].y + c[3].y);
+        o[0] = TANH ? make_double2(fast_tanh(r.x), fast_tanh(r.y)) : r;
+    } else {
+        static_assert(NTO % 4 == 0, "N tiles are processed four at a time");
+#pragma unroll
+        for (int ng = 0; ng < NTO; ng += 4) {
+            double2 c[4];
+#pragma unroll
+            for (int n = 0; n < 4; ++n) c[n] = *reinterpret_cast<const double2*>(bl + (ng + n) * 8 + 2 * q);
+#pragma unroll
+            for (int ni = 0; ni < NTI; ++ni) {
+                double2 w[4];
+#pragma unroll
+                for (int n = 0; n < 4; ++n) w[n] = Wl[((ng + n) * NTI + ni) * 32 + lane];
+#pragma unroll
+                for (int n = 0; n < 4; ++n) dmma(c[n].x, c[n].y, a[ni].x, w[n].x);
+#pragma unroll
+                for (int n = 0; n < 4; ++n) dmma(c[n].x, c[n].y, a[ni].y, w[n].y);
+            }
+#pragma unroll
+            for (int n = 0; n < 4; ++n)
+                o[ng + n] = TANH ? make_double2(fast_tanh(c[n].x), fast_tanh(c[n].y)) : c[n];
+        }
+    }
+}
+
+template <int KIND, int H>
+__global__ void __launch_bounds__(MMAH_WARPS * 32, 2)
+k_nn_update_mmah(Geom g, NNFrag net, NNParams prm, const double* __restrict__ yc, double y_lo, double y_hi,
+                 const double* __restrict__ ub, const double* __restrict__ vb, const double* __restrict__ k_in,
+                 const double* __restrict__ omega_in, const int* __restrict__ kflag, int plane0,
+                 double* __restrict__ nu_t, double* __restrict__ txx, double* __restrict__ txy,
+                 double* __restrict__ tyy) {
+    extern __shared__ double2 smem2[];
+    double2* Wsm = smem2;                                               // fragments
+    double* bsm = reinterpret_cast<double*>(Wsm + net.w_total);         // biases
+    double* xsm = bsm + ((net.b_total + 1) & ~1);                       // [warp][32 cells][8]: features in, outputs back
+    double* csm = xsm + MMAH_WARPS * 32 * 8;                            // [warp][8][32 cells]: context of the nu_t stage
+    for (int t = threadIdx.x; t < net.w_total; t += blockDim.x) Wsm[t] = net.W[t];
+    for (int t = threadIdx.x; t < net.b_total; t += blockDim.x) bsm[t] = net.b[t];
+    __syncthreads();
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int grp = lane >> 2, q = lane & 3;
+    double* xw = xsm + warp * 256;
+    double* cw = csm + warp * 256;
+    const int pl = blockIdx.z;
+    const int kk = plane0 + pl;
+    const double* u = ub + (size_t)kk * g.up;
+    const double* v = vb + (size_t)kk * g.vp;
+    const int kprov = KIND == CFDNN_TURB_NN_TBNN ? kflag[pl] : 0;
+    const int ix = blockIdx.x * 32 + lane;
+    const int ixc = min(ix, g.Nx - 1);                                  // clamp: tail lanes recompute the last cell
+    const int nrows = (g.Ny + MMAH_WARPS - 1) / MMAH_WARPS;
+    const int nhid = net.n_layers - 2;                                  // hidden -> hidden layers
+
+    for (int rg = blockIdx.y; rg < nrows; rg += gridDim.y) {
+        const int iy = rg * MMAH_WARPS + warp;
+        if (iy >= g.Ny) continue;                                       // warp-uniform
+        const int i = ixc + g.Ng, j = iy + g.Ng;
+        const size_t oc = (size_t)kk * g.cp + (size_t)j * g.cs + i;
+        {
+            CellCtx c;
+            double feat[8];
+#pragma unroll
+            for (int f = 0; f < 8; ++f) feat[f] = 0.0;
+            cell_features<KIND>(g, prm, yc, y_lo, y_hi, u, v, k_in, omega_in, kprov, i, j, oc, feat, c);
+            if (net.means) {
+#pragma unroll
+                for (int f = 0; f < 8; ++f)
+                    if (f < net.n_in) feat[f] = (feat[f] - net.means[f]) / net.stds[f];
+            }
+#pragma unroll
+            for (int f = 0; f < 8; f += 2)
+                *reinterpret_cast<double2*>(xw + lane * 8 + f) = make_double2(feat[f], feat[f + 1]);
+            // T1 = (Sxx, Sxy, Syy) and Oxy rebuild the whole tensor basis (features.cpp:192-292)
+            cw[0 * 32 + lane] = c.T[0][0]; cw[1 * 32 + lane] = c.T[0][1]; cw[2 * 32 + lane] = c.T[0][2];
+            cw[3 * 32 + lane] = c.Oxy; cw[4 * 32 + lane] = c.k_val; cw[5 * 32 + lane] = c.Sxy_;
+            cw[6 * 32 + lane] = c.S_mag;
+        }
+        __syncwarp();
+
+#pragma unroll 1
+        for (int mt = 0; mt < 4; ++mt) {
+            double* xrow = xw + (mt * 8 + grp) * 8 + 2 * q;             // this lane's column pair of its cell row
+            double2 a[H], o[H];
+            {
+                double2 a0[1];
+                a0[0] = *reinterpret_cast<const double2*>(xrow);
+                mma_layer<1, H, true>(Wsm + net.woff[0], bsm + net.boff[0], lane, q, a0, a);
+            }
+#pragma unroll 1
+            for (int l = 1; l <= nhid; ++l) {
+                mma_layer<H, H, true>(Wsm + net.woff[l], bsm + net.boff[l], lane, q, a, o);
+#pragma unroll
+                for (int t = 0; t < H; ++t) a[t] = o[t];
+            }
+            double2 r[1];
+            mma_layer<H, 1, false>(Wsm + net.woff[nhid + 1], bsm + net.boff[nhid + 1], lane, q, a, r);
+            *reinterpret_cast<double2*>(xrow) = r[0];                   // outputs 2q, 2q+1 of cell mt*8 + grp
+        }
+        __syncwarp();
+        if (ix < g.Nx) {
+            double out[4];
+#pragma unroll
+            for (int n = 0; n < 4; ++n) out[n] = xw[lane * 8 + n];
+            CellCtx c;
+            if (KIND == CFDNN_TURB_NN_TBNN) {
+                const double Sxx = cw[0 * 32 + lane], Sxy = cw[1 * 32 + lane], Syy = cw[2 * 32 + lane];
+                tensor_basis(Sxx, Sxy, Syy, cw[3 * 32 + lane], c);
+            }
+            c.k_val = cw[4 * 32 + lane]; c.Sxy_ = cw[5 * 32 + lane]; c.S_mag = cw[6 * 32 + lane];
+            cell_finish<KIND>(prm, c, out, net.n_out, oc, nu_t, txx, txy, tyy);
+        }
+        __syncwarp();
+    }
+}
 #endif  // !CFDNN_DEVSIM
 }  // namespace
 
@@ -507,6 +663,24 @@ void NNClosure::build_fragments(const std::vector<double>& hw, const std::vector
     CFDNN_CUDA(cudaFuncSetAttribute(k_nn_update_mma<CFDNN_TURB_NN_MLP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mma_smem_));
     const char* e = std::getenv("CFDNN_NN_SIMT");
     mma_ok_ = !(e && std::atoi(e) != 0);
+    // shape-specialised kernel: in(<=8) -> 8H -> ... -> 8H -> out(<=8), tanh hidden layers, linear output
+    mmah_ = 0;
+    if (nl >= 2 && net_.act[nl - 1] == 0) {
+        const int hw = net_.dims[1];
+        bool ok = hw == 64 || hw == 32;
+        for (int l = 1; l < nl; ++l) ok = ok && net_.dims[l] == hw;
+        for (int l = 0; l + 1 < nl; ++l) ok = ok && net_.act[l] == 1;
+        if (ok) mmah_ = hw / 8;
+    }
+    if (const char* g = std::getenv("CFDNN_NN_GENERIC")) if (std::atoi(g) != 0) mmah_ = 0;   // A/B: generic DMMA kernel
+    mmah_smem_ = nw * sizeof(double2) + ((nb + 1) & ~(size_t)1) * sizeof(double) + 2 * MMAH_WARPS * 32 * 8 * sizeof(double);
+    if (mmah_smem_ > 113 * 1024) mmah_ = 0;             // two CTAs per SM
+    if (mmah_) {
+        CFDNN_CUDA(cudaFuncSetAttribute(k_nn_update_mmah<CFDNN_TURB_NN_TBNN, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mmah_smem_));
+        CFDNN_CUDA(cudaFuncSetAttribute(k_nn_update_mmah<CFDNN_TURB_NN_MLP, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mmah_smem_));
+        CFDNN_CUDA(cudaFuncSetAttribute(k_nn_update_mmah<CFDNN_TURB_NN_TBNN, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mmah_smem_));
+        CFDNN_CUDA(cudaFuncSetAttribute(k_nn_update_mmah<CFDNN_TURB_NN_MLP, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mmah_smem_));
+    }
 #endif
 }
 
@@ -535,6 +709,24 @@ void NNClosure::update_device(const Geom& g, const double* yc, double y_lo, doub
         const long long want = 148LL * 8;
         int gy = (int)std::max(1LL, std::min<long long>(rows, (want + (long long)xt * nplanes - 1) / ((long long)xt * nplanes)));
         const dim3 mg(xt, gy, nplanes);
+        if (mmah_) {
+            // 8 warps per CTA, two CTAs per SM; CTAs stride over groups of 8 rows
+            const int rows8 = (g.Ny + MMAH_WARPS - 1) / MMAH_WARPS;
+            const long long want8 = 148LL * 2 * 4;
+            const int gy8 = (int)std::max(1LL, std::min<long long>(rows8, (want8 + (long long)xt * nplanes - 1) / ((long long)xt * nplanes)));
+            const dim3 hg(xt, gy8, nplanes);
+            if (kind_ == CFDNN_TURB_NN_TBNN) {
+                CFDNN_CUDA(cudaMemsetAsync(kflag_.p, 0, nplanes * sizeof(int), st));
+                CFDNN_LAUNCH(k_k_provided, grd, blk, 0, st, g, k, prm_.k_min, plane0, kflag_.p);
+            }
+#define CFDNN_MMAH(KIND, HH)                                                                                       \
+            CFDNN_LAUNCH((k_nn_update_mmah<KIND, HH>), hg, MMAH_WARPS * 32, mmah_smem_, st, g, frag_, prm_, yc, y_lo, \
+                         y_hi, vel.u, vel.v, k, omega, kflag_.p, plane0, nu_t, txx, txy, tyy)
+            if (kind_ == CFDNN_TURB_NN_TBNN) { if (mmah_ == 8) CFDNN_MMAH(CFDNN_TURB_NN_TBNN, 8); else CFDNN_MMAH(CFDNN_TURB_NN_TBNN, 4); }
+            else { if (mmah_ == 8) CFDNN_MMAH(CFDNN_TURB_NN_MLP, 8); else CFDNN_MMAH(CFDNN_TURB_NN_MLP, 4); }
+#undef CFDNN_MMAH
+            return;
+        }
         if (kind_ == CFDNN_TURB_NN_TBNN) {
             CFDNN_CUDA(cudaMemsetAsync(kflag_.p, 0, nplanes * sizeof(int), st));
             CFDNN_LAUNCH(k_k_provided, grd, blk, 0, st, g, k, prm_.k_min, plane0, kflag_.p);
@@ -598,6 +790,39 @@ void NNClosure::update_host(const cfdnn_mesh_desc& m, const double* u, const dou
     }
     CFDNN_CUDA(cudaStreamSynchronize(st_));
     check_launch("nn_update");
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, ev0_, ev1_);
+    last_ms = ms;
+}
+
+void NNClosure::update_dev_ptrs(const cfdnn_mesh_desc& m, const double* u, const double* v, const double* k,
+                                const double* omega, double* nu_t, double* txx, double* txy, double* tyy) {
+    if (m.Ng != 1) throw std::invalid_argument("nn_update_dev: only Nghost == 1 is supported");
+    if (!u || !v || !nu_t) throw std::invalid_argument("nn_update_dev: u, v and nu_t device pointers are required");
+    Geom g = make_geom(m);
+    const int Ng = m.Ng, nzt = m.Nz + 2 * Ng;
+    const size_t sc = (size_t)g.cp * nzt;
+    DevBuf<double> dyc, ddyc, zk, zo;
+    std::vector<double> yc(m.Ny + 2 * Ng);
+    for (int j = 0; j < m.Ny + 2 * Ng; ++j) yc[j] = m.yc ? m.yc[j] : m.y_lo + (j - Ng + 0.5) * m.dy;   // src/mesh.cpp:66-68
+    dyc.alloc(yc.size(), false);
+    CFDNN_CUDA(cudaMemcpyAsync(dyc.p, yc.data(), yc.size() * sizeof(double), cudaMemcpyHostToDevice, st_));
+    if (m.y_stretched) {
+        if (!m.dyc) throw std::invalid_argument("nn_update_dev: stretched mesh needs dyc");
+        ddyc.alloc(m.Ny + 2 * Ng + 1, false);
+        CFDNN_CUDA(cudaMemcpyAsync(ddyc.p, m.dyc, (m.Ny + 2 * Ng + 1) * sizeof(double), cudaMemcpyHostToDevice, st_));
+        g.dyc = ddyc.p;
+    }
+    if (!k) { zk.alloc(sc); k = zk.p; }            // absent k / omega == all zero (estimated by the closure)
+    if (!omega) { zo.alloc(sc); omega = zo.p; }
+    const bool want_tau = txx && txy && tyy && kind_ == CFDNN_TURB_NN_TBNN;
+    Vel vel; vel.u = const_cast<double*>(u); vel.v = const_cast<double*>(v); vel.w = nullptr;
+    CFDNN_CUDA(cudaEventRecord(ev0_, st_));
+    update_device(g, dyc.p, m.y_lo, m.y_hi, vel, k, omega, nu_t, want_tau ? txx : nullptr, want_tau ? txy : nullptr,
+                  want_tau ? tyy : nullptr, st_);
+    CFDNN_CUDA(cudaEventRecord(ev1_, st_));
+    CFDNN_CUDA(cudaStreamSynchronize(st_));
+    check_launch("nn_update_dev");
     float ms = 0.f;
     cudaEventElapsedTime(&ms, ev0_, ev1_);
     last_ms = ms;

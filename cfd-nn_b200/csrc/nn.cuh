@@ -55,6 +55,9 @@ public:
     void update_device(const Geom& g, const double* yc, double y_lo, double y_hi, const Vel& vel,
                        const double* k, const double* omega, double* nu_t, double* txx, double* txy,
                        double* tyy, cudaStream_t st, int data_plane = -1);
+    // TurbulenceModel::update with a device view: every pointer is a device twin in the reference layout
+    void update_dev_ptrs(const cfdnn_mesh_desc& m, const double* u, const double* v, const double* k,
+                         const double* omega, double* nu_t, double* txx, double* txy, double* tyy);
     // MLP::forward on a batch: x[n][in] -> y[n][out]
     void forward_host(const double* x, double* y, size_t n);
     double last_ms = 0.0;
@@ -75,6 +78,8 @@ private:
     DevBuf<double> bf_;
     size_t mma_smem_ = 0;
     bool mma_ok_ = false;
+    int mmah_ = 0;                   // > 0: hidden width / 8 of the shape-specialised kernel (k_nn_update_mmah)
+    size_t mmah_smem_ = 0;
     void build_fragments(const std::vector<double>& hw, const std::vector<double>& hb);
     cudaStream_t st_ = nullptr;
     cudaEvent_t ev0_ = nullptr, ev1_ = nullptr;

@@ -98,6 +98,7 @@ Solver::Solver(const cfdnn_mesh_desc& m, const cfdnn_config& c) : mesh_(m), cfg_
 }
 
 Solver::~Solver() {
+    for (auto& e : phpool_) { if (e.a) cudaEventDestroy(e.a); if (e.b) cudaEventDestroy(e.b); }
     if (h_scalars_) cudaFreeHost(h_scalars_);
     if (ev0_) cudaEventDestroy(ev0_);
     if (ev1_) cudaEventDestroy(ev1_);
@@ -150,6 +151,24 @@ void Solver::update_links() {
     if (seam_scratch_.n != (size_t)g_.wp) seam_scratch_.alloc((size_t)g_.wp);
 }
 
+// ---------------------------------------------------------------- phase timers
+Solver::PhaseEv* Solver::ph_begin(int phase) {
+    if (phused_ >= 16384) return nullptr;
+    if (phused_ == phpool_.size()) {
+        PhaseEv e;
+        CFDNN_CUDA(cudaEventCreate(&e.a));
+        CFDNN_CUDA(cudaEventCreate(&e.b));
+        phpool_.push_back(e);
+    }
+    PhaseEv* e = &phpool_[phused_++];
+    e->phase = phase;
+    CFDNN_CUDA(cudaEventRecord(e->a, st_));
+    return e;
+}
+void Solver::ph_end(PhaseEv* e) {
+    if (e) CFDNN_CUDA(cudaEventRecord(e->b, st_));
+}
+
 // ---------------------------------------------------------------- field transfer
 double* Solver::field_ptr(int field, size_t* n) const {
     switch (field) {
@@ -169,6 +188,23 @@ double* Solver::field_ptr(int field, size_t* n) const {
         case CFDNN_F_TAU_YY: *n = sc_; return tau_[2];
     }
     throw std::invalid_argument("unknown field id");
+}
+double* Solver::view_ptr(int field, size_t* n) const {
+    switch (field) {
+        case CFDNN_F_U_STAR: *n = su_; return star_.u;
+        case CFDNN_F_V_STAR: *n = sv_; return star_.v;
+        case CFDNN_F_W_STAR: *n = sw_; return star_.w;
+        case CFDNN_F_U_OLD: *n = su_; return old_.u;
+        case CFDNN_F_V_OLD: *n = sv_; return old_.v;
+        case CFDNN_F_W_OLD: *n = sw_; return old_.w;
+        case CFDNN_F_CONV_U: *n = su_; return conv_.u;
+        case CFDNN_F_CONV_V: *n = sv_; return conv_.v;
+        case CFDNN_F_CONV_W: *n = sw_; return conv_.w;
+        case CFDNN_F_DIFF_U: *n = su_; return diff_.u;
+        case CFDNN_F_DIFF_V: *n = sv_; return diff_.v;
+        case CFDNN_F_DIFF_W: *n = sw_; return diff_.w;
+    }
+    return field_ptr(field, n);
 }
 size_t Solver::field_size(int field) const { size_t n; field_ptr(field, &n); return n; }
 void Solver::upload(int field, const double* host, size_t n) {
@@ -396,7 +432,9 @@ void Solver::seam_z(const Vel& v, bool average) {
 // euler_substep (src/solver_time.cpp:269-661): operators always read velocity_
 void Solver::euler_substep(const Vel& in, Vel& out, double dt) {
     halo_vel(vel_, /*bc_site=*/false);
+    PhaseEv* e = ph_begin(CFDNN_PHASE_MOMENTUM);
     momentum(in, out, dt, /*seam_average=*/false);
+    ph_end(e);
 }
 
 // project_velocity (src/solver_time.cpp:736-1211); which == &vel_ means "no swap"
@@ -442,7 +480,9 @@ void Solver::ssprk2_step(double dt) {              // :1213-1301
 // Euler path of step() (src/solver.cpp:1505-2507)
 void Solver::euler_step() {
     halo_vel(vel_, /*bc_site=*/false);
+    PhaseEv* pe = ph_begin(CFDNN_PHASE_MOMENTUM);
     momentum(vel_, star_, dt_, /*seam_average=*/true);         // conv + diff + predictor :1505-1722
+    ph_end(pe);
     const bool px = vbc_[0] == CFDNN_VBC_PERIODIC && vbc_[1] == CFDNN_VBC_PERIODIC;
     const bool py = vbc_[2] == CFDNN_VBC_PERIODIC && vbc_[3] == CFDNN_VBC_PERIODIC;
     const bool pz = vbc_[4] == CFDNN_VBC_PERIODIC && vbc_[5] == CFDNN_VBC_PERIODIC;
@@ -490,8 +530,8 @@ void Solver::euler_step() {
 
 void Solver::build_nu_eff() {
     const dim3 gr = grid3(g_.Nx + 2 * g_.Ng, g_.Ny + 2 * g_.Ng, g_.Nz + 2 * g_.Ng);
-    CFDNN_LAUNCH(k_nu_eff, gr, kB, 0, st_, g_, cfg_.nu, nut_, nn_ ? 1 : 0, nueff_);
-    if (nn_) halo_cell(nueff_, /*bc_site=*/false);
+    CFDNN_LAUNCH(k_nu_eff, gr, kB, 0, st_, g_, cfg_.nu, nut_, has_model() ? 1 : 0, nueff_);
+    if (has_model()) halo_cell(nueff_, /*bc_site=*/false);
 }
 
 void Solver::update_turbulence() {
@@ -510,7 +550,7 @@ void Solver::check_nan(int step) {                              // check_for_nan
     CFDNN_LAUNCH(k_nonfinite, blocks, 256, 0, st_, vel_.v, sv_, flag);
     CFDNN_LAUNCH(k_nonfinite, blocks, 256, 0, st_, vel_.w, sw_, flag);
     CFDNN_LAUNCH(k_nonfinite, blocks, 256, 0, st_, p_, sc_, flag);
-    if (nn_) CFDNN_LAUNCH(k_nonfinite, blocks, 256, 0, st_, nut_, sc_, flag);
+    if (has_model()) CFDNN_LAUNCH(k_nonfinite, blocks, 256, 0, st_, nut_, sc_, flag);
     CFDNN_CUDA(cudaMemcpyAsync(h_scalars_ + 16, flag, sizeof(int), cudaMemcpyDeviceToHost, st_));
     CFDNN_CUDA(cudaStreamSynchronize(st_));
     if (*reinterpret_cast<int*>(h_scalars_ + 16) != 0)
@@ -525,9 +565,11 @@ void Solver::step_device(bool want_residual) {
         const dim3 gr = grid3(g_.Nx + 1, g_.Ny + 1, g_.Nz + 1);
         CFDNN_LAUNCH(k_copy2, gr, kB, 0, st_, g_, vel_, old_, rk_);
     }
+    PhaseEv* pe = ph_begin(CFDNN_PHASE_CLOSURE);
     update_turbulence();                                        // :1284-1324
+    ph_end(pe);
     build_nu_eff();                                             // :1326-1410
-    if (cfg_.adaptive_dt && nn_) {                              // diffusion-CFL re-check :1416-1491
+    if (cfg_.adaptive_dt && has_model()) {                      // diffusion-CFL re-check :1416-1491
         const dim3 gr = grid3(g_.Nx, g_.Ny, g_.Nz);
         const int nb = gr.x * gr.y * gr.z;
         CFDNN_LAUNCH_COOP(k_cfl_maxima, gr, kB, 0, st_, g_, vel_, nut_, cfg_.nu, 1, partial_.p, nb);
@@ -565,6 +607,7 @@ double Solver::step() {
 void Solver::run(int nsteps, double* last_residual) {
     if (nsteps <= 0) return;
     mg_->acc_vcycle_ms = 0.0; mg_->acc_vcycles = 0;
+    phused_ = 0;
     CFDNN_CUDA(cudaEventRecord(ev0_, st_));
     for (int s = 0; s < nsteps; ++s) step_device(s == nsteps - 1);
     CFDNN_CUDA(cudaEventRecord(ev1_, st_));
@@ -576,13 +619,18 @@ void Solver::run(int nsteps, double* last_residual) {
     mg_->collect_timing();
     last_vcycle_ms = mg_->acc_vcycle_ms;
     last_vcycles = mg_->acc_vcycles;
+    for (int q = 0; q < CFDNN_PHASE_COUNT; ++q) last_phase_ms[q] = 0.0;
+    for (size_t e = 0; e < phused_; ++e) {
+        float pm = 0.f;
+        if (cudaEventElapsedTime(&pm, phpool_[e].a, phpool_[e].b) == cudaSuccess) last_phase_ms[phpool_[e].phase] += pm;
+    }
     if (last_residual) *last_residual = h_scalars_[3];
 }
 
 double Solver::compute_adaptive_dt() {                          // src/solver.cpp:3369-3729
     const dim3 gr = grid3(g_.Nx, g_.Ny, g_.Nz);
     const int nb = gr.x * gr.y * gr.z;
-    CFDNN_LAUNCH_COOP(k_cfl_maxima, gr, kB, 0, st_, g_, vel_, nut_, cfg_.nu, nn_ ? 1 : 0, partial_.p, nb);
+    CFDNN_LAUNCH_COOP(k_cfl_maxima, gr, kB, 0, st_, g_, vel_, nut_, cfg_.nu, has_model() ? 1 : 0, partial_.p, nb);
     CFDNN_LAUNCH_COOP(k_final_max_rows, 1, 1024, 0, st_, partial_.p, nb, 5, scalars_.p + 4);
     CFDNN_CUDA(cudaMemcpyAsync(h_scalars_ + 4, scalars_.p + 4, 5 * sizeof(double), cudaMemcpyDeviceToHost, st_));
     CFDNN_CUDA(cudaStreamSynchronize(st_));

@@ -51,6 +51,9 @@ public:
     void set_dt(double dt) { dt_ = dt; }
     double dt() const { return dt_; }
     void set_turbulence_model(NNClosure* nn) { nn_ = nn; }
+    void set_external_nu_t(bool on) { ext_nut_ = on; }      // nu_t uploaded by the caller (bridged host model)
+    bool has_model() const { return nn_ != nullptr || ext_nut_; }
+    double* view_ptr(int field, size_t* n) const;           // device twin of a field (cfdnn_solver_device_ptr)
     void comm_init(Comm* c);
 
     size_t field_size(int field) const;
@@ -67,6 +70,7 @@ public:
     std::vector<int> cycle_log;           // V-cycles of every Poisson solve since last read
     double last_step_ms = 0.0, last_vcycle_ms = 0.0;
     int last_vcycles = 0;
+    double last_phase_ms[CFDNN_PHASE_COUNT] = {};   // device ms per phase of the last run() (cfdnn_solver_phase_timing)
     Multigrid& mg() { return *mg_; }
     cudaStream_t stream() const { return st_; }
 
@@ -93,6 +97,7 @@ private:
 
     std::unique_ptr<Multigrid> mg_;
     NNClosure* nn_ = nullptr;
+    bool ext_nut_ = false;
     Comm* comm_ = nullptr;
     cudaStream_t st_ = nullptr;
     cudaEvent_t ev0_ = nullptr, ev1_ = nullptr;
@@ -135,6 +140,12 @@ private:
     void seam_z(const Vel& v, bool average);   // periodic seam of w across the end ranks
     void check_nan(int step);
     double max_change_host();
+    // per-phase device timing of run(): CUDA event pairs recorded around the phase, read after the final sync
+    struct PhaseEv { cudaEvent_t a = nullptr, b = nullptr; int phase = 0; };
+    std::vector<PhaseEv> phpool_;
+    size_t phused_ = 0;
+    PhaseEv* ph_begin(int phase);
+    void ph_end(PhaseEv* e);
 };
 
 }  // namespace cfdnn

@@ -53,7 +53,14 @@ enum {
     CFDNN_F_K = 8, CFDNN_F_OMEGA = 9,                   /* k(), omega()          */
     CFDNN_F_NUEFF = 10,
     CFDNN_F_TAU_XX = 11, CFDNN_F_TAU_XY = 12, CFDNN_F_TAU_YY = 13,
-    CFDNN_F_COUNT = 14
+    CFDNN_F_COUNT = 14,
+    /* device-view only (cfdnn_solver_device_ptr): the work arrays of SolverDeviceView,
+     * include/turbulence_model.hpp:27-78 — not transferable with upload/download */
+    CFDNN_F_U_STAR = 14, CFDNN_F_V_STAR = 15, CFDNN_F_W_STAR = 16,
+    CFDNN_F_U_OLD = 17, CFDNN_F_V_OLD = 18, CFDNN_F_W_OLD = 19,
+    CFDNN_F_CONV_U = 20, CFDNN_F_CONV_V = 21, CFDNN_F_CONV_W = 22,
+    CFDNN_F_DIFF_U = 23, CFDNN_F_DIFF_V = 24, CFDNN_F_DIFF_W = 25,
+    CFDNN_F_VIEW_COUNT = 26
 };
 
 /* Mesh — include/mesh.hpp:16-182 (only what the hot path reads).
@@ -161,6 +168,20 @@ int cfdnn_solver_cycle_log(cfdnn_solver* s, int* cycles, int cap, int* n_out);
 int cfdnn_solver_set_turbulence_model(cfdnn_solver* s, cfdnn_nn* nn);
 /* device timing of the last step()/run(): total ms and ms spent inside V-cycles */
 int cfdnn_solver_last_timing(const cfdnn_solver* s, double* step_ms, double* vcycle_ms, int* n_vcycles);
+/* get_solver_view() / get_device_view() (include/solver.hpp:1118-1122): the DEVICE twin of a solver field
+ * (SolverDeviceView / TurbulenceDeviceView pointers, include/turbulence_model.hpp:27-78,
+ * include/turbulence_device_view.hpp:12-55) and its element count.  On 2-D meshes the data plane is k = Ng.
+ * The RK stages rotate the velocity buffers, so pointers are valid until the next step()/run(). */
+int cfdnn_solver_device_ptr(cfdnn_solver* s, int field, double** dev_out, size_t* n_out);
+/* nu_t supplied by the caller: a reference TurbulenceModel that is NOT one of this backend's closures
+ * (e.g. SST k-omega running on the host) is bridged by download(velocity) -> model.update() ->
+ * upload(CFDNN_F_NUT); with this flag on, step() builds nu_eff = nu + nu_t (src/solver.cpp:1326-1410) and
+ * takes the closure branches of the diffusion-CFL re-check and the NaN guard as if a model were attached */
+int cfdnn_solver_set_external_nu_t(cfdnn_solver* s, int on);
+/* device ms of the last step()/run() spent in the closure update (TurbulenceModel::update inside step(),
+ * src/solver.cpp:1284-1324) and in the fused momentum kernels (convective + diffusive + advance) */
+enum { CFDNN_PHASE_CLOSURE = 0, CFDNN_PHASE_MOMENTUM = 1, CFDNN_PHASE_COUNT = 4 };
+int cfdnn_solver_phase_timing(const cfdnn_solver* s, double ms[CFDNN_PHASE_COUNT]);
 /* measurement aid for bench.py's roofline: ms per launch of the level-0 temporally blocked smoother
  * kernel (2 Chebyshev sweeps per launch), `reps` launches timed with CUDA events on the solver's
  * stream; 0 when level 0 does not use the tiled kernel.  Leaves the MG scratch iterate modified. */
@@ -185,6 +206,11 @@ int cfdnn_nn_set_params(cfdnn_nn* nn, double nu, double delta, double u_ref, dou
 int cfdnn_nn_update(cfdnn_nn* nn, const cfdnn_mesh_desc* mesh, const double* u, const double* v,
                     const double* k, const double* omega, double* nu_t,
                     double* tau_xx, double* tau_xy, double* tau_yy);
+/* TurbulenceModel::update with a device_view (include/turbulence_model.hpp:100-108): the same update on the
+ * DEVICE twins of the fields (pointers from cfdnn_solver_device_ptr or the caller's own allocations) */
+int cfdnn_nn_update_dev(cfdnn_nn* nn, const cfdnn_mesh_desc* mesh, const double* u_dev, const double* v_dev,
+                        const double* k_dev, const double* omega_dev, double* nu_t_dev,
+                        double* tau_xx_dev, double* tau_xy_dev, double* tau_yy_dev);
 /* batched MLP forward (MLP::forward, src/nn_core.cpp:144-204): x[n][in] -> y[n][out] */
 int cfdnn_nn_forward(cfdnn_nn* nn, const double* x, double* y, size_t n);
 int cfdnn_nn_last_timing(const cfdnn_nn* nn, double* ms);

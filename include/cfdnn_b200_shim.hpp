@@ -5,7 +5,8 @@
 // type name: the classes below present the public signatures of
 //   nncfd::MultigridPoissonSolver   (include/poisson_solver_multigrid.hpp:26-102)
 //   nncfd::RANSSolver               (include/solver.hpp:86-311; hot-path subset)
-//   nncfd::TurbulenceNNTBNN / NNMLP (include/turbulence_nn_tbnn.hpp:35-56, turbulence_nn_mlp.hpp)
+//   nncfd::TurbulenceNNTBNN / NNMLP (include/turbulence_nn_tbnn.hpp:35-56, turbulence_nn_mlp.hpp) — derived from
+//                                   nncfd::TurbulenceModel (include/turbulence_model.hpp:81-165)
 // and forward to the C ABI of include/cfdnn_b200.h.  Errors come back as the exception types
 // the reference throws (std::invalid_argument / std::runtime_error).
 //
@@ -24,6 +25,8 @@
 #include "nn_core.hpp"
 #include "poisson_solver.hpp"
 #include "solver.hpp"   // VelocityBC, RANSSolver::PoissonStats
+#include "decomposition.hpp"
+#include "turbulence_model.hpp"
 
 namespace nncfd {
 namespace b200 {
@@ -107,12 +110,18 @@ private:
 };
 
 // ------------------------------------------------------------------ NN closures
-/// Stands in for TurbulenceNNTBNN / TurbulenceNNMLP.  Weights come from the reference's own
-/// nncfd::MLP loader (src/nn_core.cpp:501-611) so the on-disk format stays the reference's.
-class TurbulenceNNB200 {
+/// Stands in for TurbulenceNNTBNN / TurbulenceNNMLP (include/turbulence_nn_tbnn.hpp:35-56,
+/// include/turbulence_nn_mlp.hpp) and IS a nncfd::TurbulenceModel (include/turbulence_model.hpp:81-165): it can be
+/// handed to the reference's own RANSSolver::set_turbulence_model(std::unique_ptr<TurbulenceModel>) or to
+/// RANSSolverB200 below.  Weights come from the reference's own nncfd::MLP loader (src/nn_core.cpp:501-611) so
+/// the on-disk format stays the reference's.
+///   update(..., device_view == nullptr): host fields in, host fields out (copies inside the call);
+///   update(..., device_view != nullptr): the view's pointers are DEVICE twins (RANSSolverB200::get_device_view),
+///                                        nothing crosses PCIe; the host ScalarField arguments are not touched.
+class TurbulenceNNB200 : public TurbulenceModel {
 public:
-    TurbulenceNNB200(int kind /* CFDNN_TURB_NN_MLP | CFDNN_TURB_NN_TBNN */) : kind_(kind) {}
-    ~TurbulenceNNB200() { cfdnn_nn_destroy(h_); }
+    explicit TurbulenceNNB200(int kind /* CFDNN_TURB_NN_MLP | CFDNN_TURB_NN_TBNN */) : kind_(kind) {}
+    ~TurbulenceNNB200() override { cfdnn_nn_destroy(h_); }
     TurbulenceNNB200(const TurbulenceNNB200&) = delete;
     TurbulenceNNB200& operator=(const TurbulenceNNB200&) = delete;
 
@@ -141,19 +150,33 @@ public:
                               mlp.has_scaling() ? mlp.input_stds_ptr() : nullptr, &h_));
         push_params();
     }
-    void set_nu(double nu) { nu_ = nu; push_params(); }
-    void set_delta(double d) { delta_ = d; push_params(); }
-    void set_u_ref(double u) { u_ref_ = u; push_params(); }
-    void set_k_min(double k) { k_min_ = k; push_params(); }
-    void set_nu_t_max(double v) { nu_t_max_ = v; push_params(); }
-    std::string name() const { return kind_ == CFDNN_TURB_NN_TBNN ? "NNTBNN" : "NNMLP"; }
-    bool provides_reynolds_stresses() const { return kind_ == CFDNN_TURB_NN_TBNN; }
-    bool uses_transport_equations() const { return false; }
+    // set_nu / set_delta are non-virtual members of the base (turbulence_model.hpp:153-158): the values are read
+    // from the base at every update()
+    void set_u_ref(double u) { u_ref_ = u; }
+    void set_k_min(double k) { k_min_ = k; }
+    void set_nu_t_max(double v) { nu_t_max_ = v; }
+    std::string name() const override { return kind_ == CFDNN_TURB_NN_TBNN ? "NNTBNN" : "NNMLP"; }
+    bool provides_reynolds_stresses() const override { return kind_ == CFDNN_TURB_NN_TBNN; }
+    bool uses_transport_equations() const override { return false; }
+    void initialize_gpu_buffers(const Mesh&) override {}       // weights are resident from load() on
+    void cleanup_gpu_buffers() override {}
+    bool is_gpu_ready() const override { return h_ != nullptr; }
 
-    /// TurbulenceModel::update (include/turbulence_model.hpp:100-108), host fields
+    /// TurbulenceModel::update (include/turbulence_model.hpp:100-108)
     void update(const Mesh& mesh, const VectorField& velocity, const ScalarField& k, const ScalarField& omega,
-                ScalarField& nu_t, TensorField* tau_ij = nullptr) {
+                ScalarField& nu_t, TensorField* tau_ij = nullptr,
+                const TurbulenceDeviceView* device_view = nullptr) override {
+        if (!h_) throw std::runtime_error("TurbulenceNNB200::update: load() has not been called");
+        push_params();
         const cfdnn_mesh_desc d = mesh_desc(mesh);
+        if (device_view) {
+            if (!device_view->u_face || !device_view->v_face || !device_view->nu_t)
+                throw std::runtime_error("TurbulenceNNB200::update: device view without u/v/nu_t pointers");
+            check(cfdnn_nn_update_dev(h_, &d, device_view->u_face, device_view->v_face, device_view->k,
+                                      device_view->omega, device_view->nu_t, device_view->tau_xx,
+                                      device_view->tau_xy, device_view->tau_yy));
+            return;
+        }
         check(cfdnn_nn_update(h_, &d, velocity.u_data().data(), velocity.v_data().data(), k.data().data(),
                               omega.data().data(), nu_t.data().data(),
                               tau_ij ? tau_ij->xx_data().data() : nullptr,
@@ -161,14 +184,15 @@ public:
                               tau_ij ? tau_ij->yy_data().data() : nullptr));
     }
     cfdnn_nn* handle() const { return h_; }
-
-private:
+    /// parameters pushed to the device closure (called by update(); RANSSolverB200 calls it before every step)
     void push_params() {
         if (h_) check(cfdnn_nn_set_params(h_, nu_, delta_, u_ref_, k_min_, nu_t_max_));
     }
+
+private:
     int kind_;
     cfdnn_nn* h_ = nullptr;
-    double nu_ = 1e-3, delta_ = 1.0, u_ref_ = 1.0, k_min_ = 1e-10, nu_t_max_ = 1.0;
+    double u_ref_ = 1.0, k_min_ = 1e-10, nu_t_max_ = 1.0;
 };
 
 // ------------------------------------------------------------------ RANSSolver (hot-path subset)
@@ -219,8 +243,8 @@ public:
     using PoissonSolveStatus = RANSSolver::PoissonSolveStatus;
 
     RANSSolverB200(const Mesh& mesh, const Config& config)
-        : mesh_(&mesh), velocity_(mesh), pressure_(mesh), pressure_correction_(mesh), div_velocity_(mesh),
-          rhs_poisson_(mesh), nu_t_(mesh), k_(mesh), omega_(mesh), nu_eff_(mesh) {
+        : mesh_(&mesh), config_(config), velocity_(mesh), pressure_(mesh), pressure_correction_(mesh),
+          div_velocity_(mesh), rhs_poisson_(mesh), nu_t_(mesh), k_(mesh), omega_(mesh), nu_eff_(mesh), tau_ij_(mesh) {
         const cfdnn_mesh_desc d = mesh_desc(mesh);
         const cfdnn_config c = solver_cfg(config);
         check(cfdnn_solver_create(&d, &c, &h_));
@@ -236,20 +260,61 @@ public:
         const int v[6] = {vbc_code(bc.x_lo), vbc_code(bc.x_hi), vbc_code(bc.y_lo), vbc_code(bc.y_hi),
                           vbc_code(bc.z_lo), vbc_code(bc.z_hi)};
         check(cfdnn_solver_set_velocity_bc(h_, v));
+        bc_ = bc; have_bc_ = true;
     }
-    void set_body_force(double fx, double fy, double fz = 0.0) { check(cfdnn_solver_set_body_force(h_, fx, fy, fz)); }
-    void set_turbulence_model(std::unique_ptr<TurbulenceNNB200> model) {
+    void set_body_force(double fx, double fy, double fz = 0.0) {
+        fx_ = fx; fy_ = fy; fz_ = fz;
+        check(cfdnn_solver_set_body_force(h_, fx, fy, fz));
+    }
+    /// set_turbulence_model(std::unique_ptr<TurbulenceModel>) (include/solver.hpp:107).  A TurbulenceNNB200 runs
+    /// device-resident inside step().  Any other reference TurbulenceModel (e.g. SST k-omega, which has no B200
+    /// kernels yet) is BRIDGED: every step() downloads the velocity, calls the model's own host update() /
+    /// advance_turbulence() exactly where the reference does (src/solver.cpp:1284-1324), and uploads nu_t — correct,
+    /// but PCIe-bound; it exists so that such a run works at all, not as a fast path.
+    void set_turbulence_model(std::unique_ptr<TurbulenceModel> model) {
         turb_ = std::move(model);
-        if (turb_) {
-            turb_->set_nu(nu_);
-            turb_->set_nu_t_max(nu_t_max_);
-        }
-        check(cfdnn_solver_set_turbulence_model(h_, turb_ ? turb_->handle() : nullptr));
+        native_ = dynamic_cast<TurbulenceNNB200*>(turb_.get());
+        if (turb_) turb_->set_nu(nu_);
+        if (native_) native_->set_nu_t_max(nu_t_max_);
+        check(cfdnn_solver_set_turbulence_model(h_, native_ ? native_->handle() : nullptr));
+        check(cfdnn_solver_set_external_nu_t(h_, turb_ && !native_ ? 1 : 0));
     }
+    /// set_decomposition (include/solver.hpp:93): this rank's mesh is the z-slab [k_global_start, +nz_local) of
+    /// nz_global planes; the NCCL communicator replaces halo_exchange.cpp.  `nccl_id` is the 128-byte
+    /// ncclUniqueId made by rank 0 with cfdnn_comm_unique_id() and broadcast by the caller (MPI_Bcast in an MPI
+    /// build).  Call before initialize(), like the reference.
+    void set_decomposition(Decomposition* decomp, const void* nccl_id = nullptr) {
+        decomp_ = decomp;
+        if (!decomp || !decomp->is_parallel()) return;
+        if (!nccl_id) throw std::invalid_argument("RANSSolverB200::set_decomposition: parallel run needs the ncclUniqueId");
+        cfdnn_mesh_desc d = mesh_desc(*mesh_);
+        d.Nz_global = decomp->nz_global();
+        d.k_offset = decomp->k_global_start();
+        const cfdnn_config c = solver_cfg(config_);
+        cfdnn_solver_destroy(h_); h_ = nullptr;
+        check(cfdnn_solver_create(&d, &c, &h_));
+        if (have_bc_) set_velocity_bc(bc_);
+        check(cfdnn_solver_set_body_force(h_, fx_, fy_, fz_));
+        if (turb_) {
+            check(cfdnn_solver_set_turbulence_model(h_, native_ ? native_->handle() : nullptr));
+            check(cfdnn_solver_set_external_nu_t(h_, !native_ ? 1 : 0));
+        }
+        check(cfdnn_solver_comm_init(h_, decomp->rank(), decomp->nprocs(), nccl_id));
+    }
+    Decomposition* decomposition() const { return decomp_; }
     void initialize(const VectorField& initial_velocity) {
         velocity_ = initial_velocity;
         sync_to_gpu();
         check(cfdnn_solver_initialize(h_));
+        if (turb_) turb_->initialize(*mesh_, velocity_);
+    }
+    /// initialize_uniform (src/solver.cpp:1132-1167; the k / omega seeding of transport models is the model's own
+    /// initialize() here)
+    void initialize_uniform(double u0, double v0) {
+        velocity_.fill(u0, v0);
+        sync_to_gpu();
+        check(cfdnn_solver_initialize(h_));
+        if (turb_) turb_->initialize(*mesh_, velocity_);
     }
     void sync_to_gpu() {
         up(CFDNN_F_U, velocity_.u_data()); up(CFDNN_F_V, velocity_.v_data());
@@ -271,6 +336,8 @@ public:
     /// one time step; returns max|u^{n+1} - u^n| like the reference (:208)
     double step() {
         double r = 0.0;
+        if (native_) native_->push_params();
+        if (turb_ && !native_) bridge_host_model();
         check(cfdnn_solver_step(h_, &r));
         refresh_stats();
         return r;
@@ -278,9 +345,59 @@ public:
     /// n steps without host round trips (app time loops)
     double advance(int nsteps) {
         double r = 0.0;
+        if (turb_ && !native_) {
+            for (int s = 0; s < nsteps; ++s) r = step();
+            return r;
+        }
+        if (native_) native_->push_params();
         check(cfdnn_solver_run(h_, nsteps, &r));
         refresh_stats();
         return r;
+    }
+    /// get_solver_view / get_device_view (include/solver.hpp:1118-1122): DEVICE twins of the solver's arrays in the
+    /// reference layouts.  Valid until the next step() (the RK stages rotate the velocity buffers).  On 2-D meshes the
+    /// pointers address the data plane, as the reference's k = 0 plane does.
+    SolverDeviceView get_solver_view() const {
+        SolverDeviceView v;
+        v.u_face = dev(CFDNN_F_U); v.v_face = dev(CFDNN_F_V);
+        v.u_star_face = dev(CFDNN_F_U_STAR); v.v_star_face = dev(CFDNN_F_V_STAR);
+        v.u_old_face = dev(CFDNN_F_U_OLD); v.v_old_face = dev(CFDNN_F_V_OLD);
+        v.u_stride = velocity_.u_stride(); v.v_stride = velocity_.v_stride();
+        if (!mesh_->is2D()) {
+            v.w_face = dev(CFDNN_F_W); v.w_star_face = dev(CFDNN_F_W_STAR); v.w_old_face = dev(CFDNN_F_W_OLD);
+            v.w_stride = velocity_.w_stride();
+            v.u_plane_stride = velocity_.u_plane_stride(); v.v_plane_stride = velocity_.v_plane_stride();
+            v.w_plane_stride = velocity_.w_plane_stride();
+            v.conv_w = dev(CFDNN_F_CONV_W); v.diff_w = dev(CFDNN_F_DIFF_W);
+        }
+        v.p = dev(CFDNN_F_P); v.p_corr = dev(CFDNN_F_PCORR); v.nu_t = dev(CFDNN_F_NUT); v.nu_eff = dev(CFDNN_F_NUEFF);
+        v.rhs = dev(CFDNN_F_RHS); v.div = dev(CFDNN_F_DIV);
+        v.cell_stride = mesh_->total_Nx();
+        v.cell_plane_stride = mesh_->total_Nx() * mesh_->total_Ny();
+        v.conv_u = dev(CFDNN_F_CONV_U); v.conv_v = dev(CFDNN_F_CONV_V);
+        v.diff_u = dev(CFDNN_F_DIFF_U); v.diff_v = dev(CFDNN_F_DIFF_V);
+        v.Nx = mesh_->Nx; v.Ny = mesh_->Ny; v.Nz = mesh_->Nz; v.Ng = mesh_->Nghost;
+        v.dx = mesh_->dx; v.dy = mesh_->dy; v.dz = mesh_->dz; v.dt = current_dt_;
+        v.y_stretched = mesh_->is_y_stretched();
+        return v;
+    }
+    TurbulenceDeviceView get_device_view() const {
+        TurbulenceDeviceView v;
+        v.u_face = dev(CFDNN_F_U); v.v_face = dev(CFDNN_F_V);
+        v.u_stride = velocity_.u_stride(); v.v_stride = velocity_.v_stride();
+        if (!mesh_->is2D()) {
+            v.w_face = dev(CFDNN_F_W); v.w_stride = velocity_.w_stride();
+            v.u_plane_stride = velocity_.u_plane_stride(); v.v_plane_stride = velocity_.v_plane_stride();
+            v.w_plane_stride = velocity_.w_plane_stride();
+        }
+        v.k = dev(CFDNN_F_K); v.omega = dev(CFDNN_F_OMEGA); v.nu_t = dev(CFDNN_F_NUT);
+        v.cell_stride = mesh_->total_Nx();
+        v.cell_plane_stride = mesh_->total_Nx() * mesh_->total_Ny();
+        v.tau_xx = dev(CFDNN_F_TAU_XX); v.tau_xy = dev(CFDNN_F_TAU_XY); v.tau_yy = dev(CFDNN_F_TAU_YY);
+        v.is_y_stretched = mesh_->is_y_stretched();
+        v.Nx = mesh_->Nx; v.Ny = mesh_->Ny; v.Nz = mesh_->Nz; v.Ng = mesh_->Nghost;
+        v.dx = mesh_->dx; v.dy = mesh_->dy; v.dz = mesh_->dz;
+        return v;
     }
     double compute_adaptive_dt() const {
         double dt = 0.0;
@@ -308,6 +425,26 @@ public:
 private:
     void up(int f, const std::vector<double>& v) { check(cfdnn_solver_upload(h_, f, v.data(), v.size())); }
     void down(int f, std::vector<double>& v) { check(cfdnn_solver_download(h_, f, v.data(), v.size())); }
+    double* dev(int f) const {
+        double* p = nullptr;
+        size_t n = 0;
+        check(cfdnn_solver_device_ptr(h_, f, &p, &n));
+        if (p && mesh_->is2D()) {   // 2-D: the device keeps the data in plane Ng of its 3-plane arrays
+            const size_t planes = (f == CFDNN_F_W || f == CFDNN_F_W_STAR || f == CFDNN_F_W_OLD || f == CFDNN_F_CONV_W ||
+                                   f == CFDNN_F_DIFF_W) ? 4 : 3;
+            p += (n / planes) * (size_t)mesh_->Nghost;
+        }
+        return p;
+    }
+    /// a host-side reference TurbulenceModel inside step(): the reference's call site src/solver.cpp:1284-1324
+    void bridge_host_model() {
+        down(CFDNN_F_U, velocity_.u_data()); down(CFDNN_F_V, velocity_.v_data());
+        if (!mesh_->is2D()) down(CFDNN_F_W, velocity_.w_data());
+        if (turb_->uses_transport_equations())
+            turb_->advance_turbulence(*mesh_, velocity_, current_dt_, k_, omega_, nu_t_, nullptr);
+        turb_->update(*mesh_, velocity_, k_, omega_, nu_t_, turb_->provides_reynolds_stresses() ? &tau_ij_ : nullptr, nullptr);
+        up(CFDNN_F_NUT, nu_t_.data());
+    }
     void refresh_stats() {
         cfdnn_poisson_stats s{};
         check(cfdnn_solver_poisson_stats(h_, &s));
@@ -321,10 +458,17 @@ private:
         cfdnn_solver_get_dt(h_, &current_dt_);
     }
     const Mesh* mesh_;
+    Config config_;
     cfdnn_solver* h_ = nullptr;
-    std::unique_ptr<TurbulenceNNB200> turb_;
+    std::unique_ptr<TurbulenceModel> turb_;
+    TurbulenceNNB200* native_ = nullptr;        // turb_ when it is one of this backend's device closures
+    Decomposition* decomp_ = nullptr;
+    VelocityBC bc_;
+    bool have_bc_ = false;
+    double fx_ = 0.0, fy_ = 0.0, fz_ = 0.0;
     VectorField velocity_;
     ScalarField pressure_, pressure_correction_, div_velocity_, rhs_poisson_, nu_t_, k_, omega_, nu_eff_;
+    TensorField tau_ij_;
     PoissonStats poisson_stats_;
     double current_dt_ = 0.0, nu_ = 0.0, nu_t_max_ = 1.0;
 };

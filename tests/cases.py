@@ -30,6 +30,9 @@ STEP_CASES = [
     ("duct16_rk2_walls_xy", (16, 16, 16), "WWWWPP", "rk2", "central", 4, 2, "shear", (1.0, 0, 0), {}),
     ("box16_euler_walls_all", (16, 16, 16), "WWWWWW", "euler", "skew", 6, 2, "shear", (0.5, 0, 0), {}),
     ("ragged_24x16x32_rk3", (24, 16, 32), "PPWWPP", "rk3", "skew", 4, 1, "shear", (1.0, 0, 0), {}),
+    # inflow / outflow passes of apply_velocity_bc (src/solver_operators.cpp:189-257, w passes :413-441)
+    ("duct16_inflow_outflow_euler", (16, 16, 16), "IOWWPP", "euler", "central", 6, 2, "shear", (0.5, 0, 0), {}),
+    ("duct_24x16x16_inflow_outflow_rk3", (24, 16, 16), "IOWWWW", "rk3", "skew", 6, 2, "shear", (0.5, 0, 0), {}),
 ]
 
 
@@ -506,3 +509,112 @@ def check_tiled_norms(B, monkeypatch, case):
         assert sa[k] == sb[k], k                        # max norms: order-independent
     for k in ("r0_l2", "residual_l2"):
         assert sb[k] == pytest.approx(sa[k], rel=1e-12), k
+
+
+# ---------------------------------------------------------------- reductions of the step
+def check_adaptive_dt(B, oracle, stretched=False, nsteps=3):
+    """compute_adaptive_dt (src/solver.cpp:3369-3729) in the app time loop: dt = compute_adaptive_dt();
+    set_dt(dt); step().  stretched = True exercises max(|v| / dyv[j]) with the reference's 0-based j
+    (:3440,3579,3649) and dx_min over the stretched cell heights."""
+    import ctypes as C
+    if stretched:
+        N, bc, init, force, extra = (16, 16, 16), "PPWWPP", "tgv", (1.0, 0, 0), dict(**CHANNEL_BOX)
+    else:
+        N, bc, init, force, extra = (16, 16, 16), "PPPPPP", "tgv", (0, 0, 0), {}
+    case = ("adt", N, bc, "rk3", "skew", 8, nsteps, init, force, extra)
+    u, v, w = step_init(N, init)
+    with tempfile.TemporaryDirectory() as td:
+        pre = os.path.join(td, "in")
+        u.tofile(pre + "_u.f64"); v.tofile(pre + "_v.f64"); w.tofile(pre + "_w.f64")
+        meta = oracle.run_ref("step", Nx=N[0], Ny=N[1], Nz=N[2], bc=bc, ti="rk3", scheme="skew", fixed=8, nsteps=nsteps,
+                              dt=0.01, nu=0.01, init="file:" + pre, adaptive_dt=1, CFL_max=0.4, fx=force[0],
+                              out=os.path.join(td, "r"), **{k: v_ for k, v_ in extra.items() if k in HARNESS_KEYS})
+        mesh_arrays = oracle.load_mesh_arrays(os.path.join(td, "r_mesh")) if stretched else None
+        ref = R.load_state(os.path.join(td, "r_final"), *N)
+    h = make_solver(B, case, mesh_arrays=mesh_arrays, adaptive_dt=1, CFL_max=0.4)
+    dts = []
+    try:
+        for _ in range(nsteps):
+            dt = C.c_double()
+            B.check(B.lib.cfdnn_solver_compute_adaptive_dt(h, C.byref(dt)))
+            B.check(B.lib.cfdnn_solver_set_dt(h, dt.value))
+            dts.append(dt.value)
+            B.step(h)
+        got = B.state(h, *N)
+    finally:
+        B.lib.cfdnn_solver_destroy(h)
+    assert dts == pytest.approx(meta["dts"], rel=1e-12), (dts, meta["dts"])
+    compare_states(got, ref, 1e-10, "adaptive dt" + (" stretched" if stretched else ""), vel_joint=True)
+    return dts
+
+
+def check_nan_guard(B):
+    """check_for_nan_inf (src/solver.cpp:3195-3350): std::runtime_error -> CFDNN_ERR_RUNTIME"""
+    case = STEP_CASES[0]
+    for bad in (np.nan, np.inf):
+        h = make_solver(B, case, turb_guard_interval=1)
+        sh = R.shapes(16, 16, 16)
+        u = np.zeros(sh["u"]); u[5, 5, 5] = bad
+        B.upload(h, "u", u)
+        with pytest.raises(R.capi.CfdnnError) as e:
+            B.step(h)
+        assert e.value.code == 2 and "NaN/Inf" in str(e.value)
+        B.lib.cfdnn_solver_destroy(h)
+    # guard disabled, or off-interval: no throw (turb_guard_enabled / turb_guard_interval, :3197-3203)
+    h = make_solver(B, case, turb_guard_enabled=0)
+    B.step(h)
+    B.lib.cfdnn_solver_destroy(h)
+
+
+def check_diffusion_cfl_recheck(B, oracle, nsteps=3, tol=1e-9):
+    """Diffusion-CFL re-check inside step() (src/solver.cpp:1416-1491; only with adaptive_dt AND a turbulence
+    model): a 2-D channel whose time step is diffusion-limited, NN-TBNN closure attached.  compute_adaptive_dt sees
+    last step's nu_t (0 before the first step), the closure then raises nu_eff to ~11 nu inside step(), and the
+    re-check must clamp current_dt_ to dt_safety * 0.25 dx_min^2 / nu_eff,max — visible in current_dt() after the
+    step and in every field."""
+    import ctypes as C
+    import nnmodels as M
+    preset = "tbnn_channel_caseholdout"
+    N = (32, 48, 1)
+    bc, ti, scheme, fixed, init = "PPWWPP", "euler", "skew", 8, "pchan"
+    extra = dict(x1=4 * np.pi, y0=-1.0, y1=1.0)
+    nu = 1.0 / 180.0
+    u, v, w = step_init(N, init)
+    with tempfile.TemporaryDirectory() as td:
+        d = M.write_text_dir(preset, os.path.join(td, "m"))
+        pre = os.path.join(td, "in")
+        u.tofile(pre + "_u.f64"); v.tofile(pre + "_v.f64")
+        meta = R.run_ref("step", Nx=N[0], Ny=N[1], Nz=1, bc=bc, ti=ti, scheme=scheme, fixed=fixed, nsteps=nsteps, dt=0.002,
+                         nu=nu, init="file:" + pre, fx=1.0, fy=0, fz=0, out=os.path.join(td, "ref"), model="nn_tbnn",
+                         nn_weights=d, x1=extra["x1"], y0=-1.0, y1=1.0, adaptive_dt=1, CFL_max=0.5)
+        ref = R.load_state(os.path.join(td, "ref_final"), *N)
+    cfg = B.config(nu=nu, dt=0.002, time_integrator=R.TI[ti], convective_scheme=R.SCHEME[scheme], adaptive_dt=1,
+                   CFL_max=0.5, poisson_fixed_cycles=fixed)
+    md = B.mesh(*N, Lx=extra["x1"], Ly=2.0)
+    md.y_lo, md.y_hi = -1.0, 1.0
+    h = B.solver(md, cfg, bc, (1.0, 0.0, 0.0))
+    nn = M.create_preset(B, preset)
+    B.check(B.lib.cfdnn_nn_set_params(nn, nu, 1.0, 1.0, 1e-10, 1.0))
+    B.check(B.lib.cfdnn_solver_set_turbulence_model(h, nn))
+    B.upload(h, "u", u); B.upload(h, "v", v); B.upload(h, "w", w)
+    dts, used, res = [], [], []
+    try:
+        for _ in range(nsteps):
+            dt = C.c_double()
+            B.check(B.lib.cfdnn_solver_compute_adaptive_dt(h, C.byref(dt)))
+            B.check(B.lib.cfdnn_solver_set_dt(h, dt.value))
+            dts.append(dt.value)
+            res.append(B.step(h))
+            B.check(B.lib.cfdnn_solver_get_dt(h, C.byref(dt)))
+            used.append(dt.value)
+        got = B.state(h, *N, names=("u", "v", "w", "p", "nut"))
+    finally:
+        B.lib.cfdnn_solver_destroy(h)
+        B.lib.cfdnn_nn_destroy(nn)
+    assert dts == pytest.approx(meta["dts"], rel=1e-9), (dts, meta["dts"])
+    assert used[0] < 0.5 * dts[0], (used, dts)                  # the re-check really clamped the first step
+    assert res == pytest.approx(meta["residuals"], rel=1e-7)
+    assert R.rel_l2(plane0_interior("nut", got["nut"]), plane0_interior("nut", ref["nut"])) <= 1e-6
+    for n in ("u", "v", "p"):
+        assert R.rel_l2(plane0_interior(n, got[n]), plane0_interior(n, ref[n])) <= tol, n
+    return dts, used

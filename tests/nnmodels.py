@@ -11,11 +11,7 @@ KIND = {"mlp": 1, "tbnn": 2}
 
 
 def load_preset(name):
-    z = np.load(NPZ)
-    n = int(z[f"{name}/n_layers"])
-    W = [np.ascontiguousarray(z[f"{name}/W{l}"], dtype=np.float64) for l in range(n)]
-    b = [np.ascontiguousarray(z[f"{name}/b{l}"], dtype=np.float64) for l in range(n)]
-    return W, b, np.ascontiguousarray(z[f"{name}/means"]), np.ascontiguousarray(z[f"{name}/stds"])
+    return R.backend.load_npz_preset(NPZ, name)
 
 
 def write_text_dir(name, d):
@@ -31,16 +27,7 @@ def write_text_dir(name, d):
 
 
 def create(B, kind, W, b, means=None, stds=None, act=None):
-    n = len(W)
-    dims = [W[0].shape[1]] + [w.shape[0] for w in W]
-    dims_c = (C.c_int * (n + 1))(*dims)
-    act_c = (C.c_int * n)(*act) if act is not None else None
-    Wp = (R.capi.c_double_p * n)(*[R.capi.dptr(w) for w in W])
-    bp = (R.capi.c_double_p * n)(*[R.capi.dptr(x) for x in b])
-    h = C.c_void_p()
-    B.check(B.lib.cfdnn_nn_create(KIND[kind], n, dims_c, act_c, Wp, bp, R.capi.dptr(means) if means is not None else None,
-                                  R.capi.dptr(stds) if stds is not None else None, C.byref(h)))
-    return h
+    return R.backend.nn_create(B, kind, W, b, means, stds, act)
 
 
 def create_preset(B, name):

@@ -4,6 +4,7 @@
 // Built against /root/reference/include + oracle/_ref/libnn_cfd_core.a (tests/shim/build.sh).
 #include "cfdnn_b200_shim.hpp"
 #include "poisson_solver_multigrid.hpp"
+#include "turbulence_nn_tbnn.hpp"
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -17,9 +18,104 @@ static double rel_l2(const std::vector<double>& a, const std::vector<double>& b)
     return den > 0 ? std::sqrt(num / den) : std::sqrt(num);
 }
 
+// ---- closures through the TurbulenceModel plugin interface (include/turbulence_model.hpp:81-165) on a 2-D
+// channel (the reference's closures are 2-D models): (a) reference solver + reference TBNN = the oracle;
+// (b) B200 solver + TurbulenceNNB200 handed over as unique_ptr<TurbulenceModel> (device-resident closure);
+// (c) REFERENCE solver + TurbulenceNNB200 (the plugin used from the reference's own step(), host update());
+// (d) B200 solver + the reference's own TBNN model (bridged host model); (e) update() through get_device_view().
+static int closure_section(const std::string& wdir, std::string& json) {
+    Mesh mesh;
+    mesh.init_uniform(32, 48, 0.0, 4 * M_PI, -1.0, 1.0, 1);
+    Config cfg;
+    cfg.nu = 1.0 / 180.0; cfg.dt = 0.002; cfg.adaptive_dt = false; cfg.verbose = false;
+    cfg.time_integrator = TimeIntegrator::Euler; cfg.convective_scheme = ConvectiveScheme::Skew;
+    cfg.poisson_solver = PoissonSolverType::MG; cfg.poisson_fixed_cycles = 8;
+    cfg.turb_model = TurbulenceModelType::NNTBNN;
+    VelocityBC bc;
+    bc.x_lo = bc.x_hi = VelocityBC::Periodic; bc.y_lo = bc.y_hi = VelocityBC::NoSlip;
+    bc.z_lo = bc.z_hi = VelocityBC::Periodic;
+    VectorField v0(mesh);
+    for (int j = mesh.j_begin(); j < mesh.j_end(); ++j)
+        for (int i = mesh.i_begin(); i <= mesh.i_end(); ++i) {
+            const double y = mesh.y(j);
+            v0.u(i, j) = (1.0 - y * y) + 0.05 * std::cos(0.5 * M_PI * y) * std::sin(2.0 * mesh.xf[i]);
+        }
+    for (int j = mesh.j_begin(); j <= mesh.j_end(); ++j)
+        for (int i = mesh.i_begin(); i < mesh.i_end(); ++i)
+            v0.v(i, j) = 0.05 * std::sin(M_PI * (mesh.yf[j] + 1.0) * 0.5) * std::cos(2.0 * mesh.x(i));
+    const int nsteps = 3;
+    auto make_b200_model = [&] {
+        auto m = std::make_unique<b200::TurbulenceNNB200>(CFDNN_TURB_NN_TBNN);
+        m->load(wdir, wdir);
+        return m;
+    };
+    // (a)
+    RANSSolver ref(mesh, cfg);
+    ref.set_velocity_bc(bc); ref.set_body_force(1.0, 0.0);
+    { auto m = create_turbulence_model(TurbulenceModelType::NNTBNN, wdir, wdir); m->set_nu(cfg.nu); ref.set_turbulence_model(std::move(m)); }
+    ref.initialize(v0);
+    // (b)
+    b200::RANSSolverB200 b(mesh, cfg);
+    b.set_velocity_bc(bc); b.set_body_force(1.0, 0.0);
+    { std::unique_ptr<TurbulenceModel> m = make_b200_model(); b.set_turbulence_model(std::move(m)); }
+    b.initialize(v0);
+    // (c)
+    RANSSolver refp(mesh, cfg);
+    refp.set_velocity_bc(bc); refp.set_body_force(1.0, 0.0);
+    { std::unique_ptr<TurbulenceModel> m = make_b200_model(); m->set_nu(cfg.nu); refp.set_turbulence_model(std::move(m)); }
+    refp.initialize(v0);
+    // (d)
+    b200::RANSSolverB200 bh(mesh, cfg);
+    bh.set_velocity_bc(bc); bh.set_body_force(1.0, 0.0);
+    { auto m = create_turbulence_model(TurbulenceModelType::NNTBNN, wdir, wdir); bh.set_turbulence_model(std::move(m)); }
+    bh.initialize(v0);
+    double r_ref = 0, r_b = 0, r_p = 0, r_h = 0;
+    for (int s = 0; s < nsteps; ++s) { r_ref = ref.step(); r_b = b.step(); r_p = refp.step(); r_h = bh.step(); }
+    b.sync_from_gpu(); bh.sync_from_gpu();
+    const double e_b_u = rel_l2(b.velocity().u_data(), ref.velocity().u_data());
+    const double e_b_nut = rel_l2(b.nu_t().data(), ref.nu_t().data());
+    const double e_p_u = rel_l2(refp.velocity().u_data(), ref.velocity().u_data());
+    const double e_p_nut = rel_l2(refp.nu_t().data(), ref.nu_t().data());
+    const double e_h_u = rel_l2(bh.velocity().u_data(), ref.velocity().u_data());
+    const double e_h_nut = rel_l2(bh.nu_t().data(), ref.nu_t().data());
+    // (e) device view: the closure updates nu_t of solver b in place on the device; must equal a host update()
+    double e_view = 1.0;
+    bool name_ok = false, views_ok = false;
+    {
+        auto m = make_b200_model();
+        m->set_nu(cfg.nu);
+        name_ok = m->name() == "NNTBNN" && m->provides_reynolds_stresses() && !m->uses_transport_equations() &&
+                  m->is_gpu_ready();
+        ScalarField k(mesh), om(mesh), nut_host(mesh), dummy(mesh);
+        m->update(mesh, b.velocity(), k, om, nut_host, nullptr, nullptr);            // host path on the synced velocity
+        const TurbulenceDeviceView view = b.get_device_view();
+        const SolverDeviceView sv = b.get_solver_view();
+        views_ok = view.u_face && view.v_face && view.nu_t && view.Nx == 32 && view.Ny == 48 && sv.is_valid() &&
+                   sv.u_stride == b.velocity().u_stride() && sv.cell_stride == mesh.total_Nx();
+        m->update(mesh, b.velocity(), k, om, dummy, nullptr, &view);                 // device path, in place
+        b.sync_solution_from_gpu();
+        e_view = rel_l2(b.nu_t().data(), nut_host.data());
+    }
+    const bool ok = e_b_u <= 1e-9 && e_b_nut <= 1e-6 && e_p_u <= 1e-9 && e_p_nut <= 1e-6 && e_h_u <= 1e-9 &&
+                    e_h_nut <= 1e-6 && e_view <= 1e-12 && name_ok && views_ok &&
+                    std::fabs(r_ref - r_b) <= 1e-7 * std::fabs(r_ref) && std::fabs(r_ref - r_p) <= 1e-7 * std::fabs(r_ref) &&
+                    std::fabs(r_ref - r_h) <= 1e-7 * std::fabs(r_ref);
+    char buf[1024];
+    std::snprintf(buf, sizeof buf,
+                  "\"closure\": {\"b200_solver_b200_model\": {\"u\": %.3e, \"nu_t\": %.3e}, "
+                  "\"ref_solver_b200_model\": {\"u\": %.3e, \"nu_t\": %.3e}, "
+                  "\"b200_solver_ref_model_bridged\": {\"u\": %.3e, \"nu_t\": %.3e}, \"device_view_vs_host_update\": %.3e, "
+                  "\"interface_ok\": %s, \"views_ok\": %s, \"ok\": %s}",
+                  e_b_u, e_b_nut, e_p_u, e_p_nut, e_h_u, e_h_nut, e_view, name_ok ? "true" : "false",
+                  views_ok ? "true" : "false", ok ? "true" : "false");
+    json = buf;
+    return ok ? 0 : 1;
+}
+
 int main(int argc, char** argv) {
     const int N = argc > 1 ? std::atoi(argv[1]) : 16;
     const int nsteps = argc > 2 ? std::atoi(argv[2]) : 2;
+    const std::string wdir = argc > 3 ? argv[3] : "";
     std::ostringstream sink;                       // the reference is chatty on stdout/stderr
     std::streambuf* oc = std::cout.rdbuf(sink.rdbuf());
     std::streambuf* oe = std::cerr.rdbuf(sink.rdbuf());
@@ -43,6 +139,7 @@ int main(int argc, char** argv) {
                 v0.v(i, j, k) = -std::cos(mesh.x(i)) * std::sin(mesh.yf[j]) * std::cos(mesh.z(k));
 
     int rc = 0;
+    std::string closure_json = "\"closure\": null";
     double r_ref = 0, r_b = 0, eu = 0, ep = 0, emg = 0;
     int cyc_ref = 0, cyc_b = 0, mg_ref = 0, mg_b = 0;
     bool threw_invalid = false;
@@ -86,6 +183,21 @@ int main(int argc, char** argv) {
         VelocityBC bad = bc;
         bad.x_hi = VelocityBC::NoSlip;
         try { b.set_velocity_bc(bad); } catch (const std::invalid_argument&) { threw_invalid = true; }
+        // initialize_uniform (include/solver.hpp:180) and the trivial single-process decomposition (:93)
+        {
+            b200::RANSSolverB200 bu(mesh, cfg);
+            bu.set_velocity_bc(bc);
+            Decomposition single(mesh.Nz);
+            bu.set_decomposition(&single);
+            bu.initialize_uniform(0.3, -0.2);
+            RANSSolver ru(mesh, cfg);
+            ru.set_velocity_bc(bc);
+            ru.initialize_uniform(0.3, -0.2);
+            bu.step(); ru.step();
+            bu.sync_from_gpu();
+            if (rel_l2(bu.velocity().u_data(), ru.velocity().u_data()) > 1e-12 || bu.decomposition() != &single) rc = 1;
+        }
+        if (!wdir.empty() && closure_section(wdir, closure_json) != 0) rc = 1;
     } catch (const std::exception& e) {
         std::cout.rdbuf(oc); std::cerr.rdbuf(oe);
         std::printf("{\"error\": \"%s\"}\n", e.what());
@@ -97,8 +209,8 @@ int main(int argc, char** argv) {
         rc = 1;
     std::printf("{\"N\": %d, \"steps\": %d, \"residual_ref\": %.17g, \"residual_b200\": %.17g, \"u_rel_l2\": %.3e, "
                 "\"p_rel_l2\": %.3e, \"cycles_ref\": %d, \"cycles_b200\": %d, \"mg_cycles_ref\": %d, "
-                "\"mg_cycles_b200\": %d, \"mg_p_rel_l2\": %.3e, \"invalid_argument\": %s, \"ok\": %s}\n",
+                "\"mg_cycles_b200\": %d, \"mg_p_rel_l2\": %.3e, \"invalid_argument\": %s, %s, \"ok\": %s}\n",
                 N, nsteps, r_ref, r_b, eu, ep, cyc_ref, cyc_b, mg_ref, mg_b, emg, threw_invalid ? "true" : "false",
-                rc == 0 ? "true" : "false");
+                closure_json.c_str(), rc == 0 ? "true" : "false");
     return rc;
 }

@@ -45,6 +45,47 @@ def test_tgv64_one_step_1e10(gpu, oracle):
     cases.compare_states(got, ref, 1e-10, "tgv64 1 step")
 
 
+def test_tgv128_one_step_big_tiles_vs_oracle(gpu, oracle):
+    """The kernels that make the headline number against the ORACLE, not against other variants of this
+    library: at 128^3 level 0 runs k_sweep_tbo<64,26> (the 512^3 level-0 smoother) and the fused
+    k_residual_restrict<32,8>, levels 1-2 the 32x12 tiles.  One RK3 step, MG to 1e-8 (default path:
+    reciprocal multiplies + FMA, i.e. not bit-identical by design) within BASELINE's 1e-10."""
+    case = ("tgv128", (128, 128, 128), "PPPPPP", "rk3", "skew", 0, 1, "tgv", (0, 0, 0), dict(tol_rhs=1e-8, maxv=50))
+    with tempfile.TemporaryDirectory() as td:
+        meta, ref = cases.run_step_ref(case, td)
+    got_meta, got = cases.run_step_backend(gpu, case)
+    assert got_meta["cycles"] == meta["cycles"]
+    assert got_meta["residuals"] == pytest.approx(meta["residuals"], rel=1e-9)
+    worst = cases.compare_states(got, ref, 1e-10, "tgv128 1 step")
+    print("tgv128 per-field errors vs oracle", worst)
+
+
+def test_channel_128x64x64_one_step_general_big_tiles_vs_oracle(gpu, oracle):
+    """same for the general blocked kernel k_sweep_tb<2,64,26> (walls in y: the lean kernel does not apply)
+    and the non-periodic variant of the fused residual + restriction"""
+    case = ("chan128", (128, 64, 64), "PPWWPP", "rk3", "skew", 0, 1, "shear", (1.0, 0, 0), dict(tol_rhs=1e-8, maxv=50))
+    with tempfile.TemporaryDirectory() as td:
+        meta, ref = cases.run_step_ref(case, td)
+    got_meta, got = cases.run_step_backend(gpu, case)
+    assert got_meta["cycles"] == meta["cycles"]
+    cases.compare_states(got, ref, 1e-10, "chan128 1 step")
+
+
+def test_mg_256x128x128_solve_vs_oracle(gpu, oracle):
+    """MultigridPoissonSolver::solve on 256 x 128 x 128 (big tiles on levels 0 and 1, fused residual +
+    restriction on both), convergence mode to 1e-8, against the oracle: same cycle count, same solution."""
+    case = ("mg256", (256, 128, 128), "PPPPPP", 0, dict(smooth=1, tol_rhs=1e-8, maxv=30, tol_rel=0, tol=0))
+    with tempfile.TemporaryDirectory() as td:
+        meta, pref = cases.run_mg_ref(case, td)
+    st, p = cases.run_mg_backend(gpu, case)
+    assert st["cycles"] == meta["cycles"] and st["converged"] == meta["converged"]
+    err = oracle.rel_l2(p, pref)
+    print("mg256 rel L2 vs oracle", err, "cycles", st["cycles"])
+    assert err <= 1e-10
+    for k in ("b_inf", "b_l2", "r0", "r0_l2"):
+        assert st[k] == pytest.approx(meta[k], rel=1e-9, abs=1e-300)
+
+
 def test_tgv32_100_steps_1e8(gpu, oracle):
     case = ("tgv32x100", (32, 32, 32), "PPPPPP", "rk3", "skew", 0, 100, "tgv", (0, 0, 0), dict(tol_rhs=1e-8, maxv=50))
     with tempfile.TemporaryDirectory() as td:
@@ -170,3 +211,18 @@ def test_fused_residual_restrict_agrees(gpu, monkeypatch, N, bc):
     and, forced, on every level down to 8 cells"""
     case = ("rr_" + bc, N, bc, 2, {})
     cases.check_fused_residual_restrict(gpu, monkeypatch, case, bitwise="D" in bc)
+
+
+# ---- reductions of the step on the GPU (SURVEY §8 rows R1, R3, R4)
+@pytest.mark.parametrize("stretched", [False, True], ids=["uniform", "stretched_dyv_quirk"])
+def test_adaptive_dt_matches_reference(gpu, oracle, stretched):
+    cases.check_adaptive_dt(gpu, oracle, stretched=stretched)
+
+
+def test_nan_guard_raises_runtime_error(gpu):
+    cases.check_nan_guard(gpu)
+
+
+def test_diffusion_cfl_recheck_with_closure(gpu, oracle):
+    dts, used = cases.check_diffusion_cfl_recheck(gpu, oracle)
+    print("adaptive dts", dts, "dt used by step()", used)

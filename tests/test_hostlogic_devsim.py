@@ -114,33 +114,27 @@ def test_invalid_periodic_pair_is_invalid_argument(sim, R):
     sim.lib.cfdnn_solver_destroy(h)
 
 
-def test_nan_guard_raises_runtime_error(sim, R):
-    case = cases.STEP_CASES[0]
-    h = cases.make_solver(sim, case, turb_guard_interval=1)
-    sh = R.shapes(16, 16, 16)
-    u = np.zeros(sh["u"]); u[5, 5, 5] = np.nan
-    sim.upload(h, "u", u)
-    with pytest.raises(R.capi.CfdnnError) as e:
-        sim.step(h)
-    assert e.value.code == 2 and "NaN/Inf" in str(e.value)    # std::runtime_error (solver.cpp:3195-3350)
-    sim.lib.cfdnn_solver_destroy(h)
+def test_nan_guard_raises_runtime_error(sim):
+    cases.check_nan_guard(sim)
 
 
-def test_adaptive_dt_matches_reference(sim, oracle):
+@pytest.mark.parametrize("stretched", [False, True], ids=["uniform", "stretched_dyv_quirk"])
+def test_adaptive_dt_matches_reference(sim, oracle, stretched):
+    cases.check_adaptive_dt(sim, oracle, stretched=stretched)
+
+
+def test_diffusion_cfl_recheck_with_closure(sim, oracle):
+    cases.check_diffusion_cfl_recheck(sim, oracle)
+
+
+def test_stretched_metrics_match_reference_mesh(oracle):
+    """backend.stretched_y_metrics (the package's restatement of Mesh::init_stretched_y, used by bench.py's
+    config-3 workload) against the oracle's own mesh arrays, bit for bit"""
     import os
-    N = (16, 16, 16)
     with tempfile.TemporaryDirectory() as td:
-        meta = oracle.run_ref("step", Nx=16, Ny=16, Nz=16, bc="PPPPPP", ti="rk3", scheme="skew", fixed=8, nsteps=3,
-                              dt=0.01, nu=0.01, init="tgv", adaptive_dt=1, CFL_max=0.4, out=os.path.join(td, "r"))
-    case = ("a", N, "PPPPPP", "rk3", "skew", 8, 3, "tgv", (0, 0, 0), {})
-    h = cases.make_solver(sim, case, adaptive_dt=1, CFL_max=0.4)
-    import ctypes as C
-    dts = []
-    for _ in range(3):
-        dt = C.c_double()
-        sim.check(sim.lib.cfdnn_solver_compute_adaptive_dt(h, C.byref(dt)))
-        sim.check(sim.lib.cfdnn_solver_set_dt(h, dt.value))
-        dts.append(dt.value)
-        sim.step(h)
-    sim.lib.cfdnn_solver_destroy(h)
-    assert dts == pytest.approx(meta["dts"], rel=1e-12)
+        oracle.run_ref("mesh", Nx=16, Ny=96, Nz=16, stretch_beta=2.0, x1=4 * np.pi, y0=-1.0, y1=1.0, z1=2 * np.pi,
+                       out=os.path.join(td, "m"))
+        ref = oracle.load_mesh_arrays(os.path.join(td, "m_mesh"))
+    got = oracle.backend.stretched_y_metrics(96, -1.0, 1.0, 2.0)
+    for k in ref:
+        assert np.array_equal(ref[k], got[k]), k

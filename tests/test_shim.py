@@ -25,10 +25,25 @@ def _run(exe, *args):
     return r.returncode, json.loads(line)
 
 
-def test_shim_matches_reference_classes_on_test_double(oracle, sim):
+def _weights_dir(td):
+    import nnmodels as M
+    return M.write_text_dir("tbnn_channel_caseholdout", os.path.join(td, "m"))
+
+
+def _check_closure(d):
+    c = d["closure"]
+    assert c and c["ok"], c
+    assert c["interface_ok"] and c["views_ok"]
+    for k in ("b200_solver_b200_model", "ref_solver_b200_model", "b200_solver_ref_model_bridged"):
+        assert c[k]["nu_t"] <= 1e-6 and c[k]["u"] <= 1e-9, (k, c[k])
+    assert c["device_view_vs_host_update"] <= 1e-12
+
+
+def test_shim_matches_reference_classes_on_test_double(oracle, sim, tmp_path):
     _ensure_built()
-    rc, d = _run("shim_parity_sim", 16, 2)
+    rc, d = _run("shim_parity_sim", 16, 2, _weights_dir(str(tmp_path)))
     assert rc == 0 and d["ok"], d
+    _check_closure(d)
     assert d["cycles_ref"] == d["cycles_b200"] and d["mg_cycles_ref"] == d["mg_cycles_b200"]
     assert d["u_rel_l2"] <= 1e-10 and d["p_rel_l2"] <= 1e-10 and d["mg_p_rel_l2"] <= 1e-10
     assert d["invalid_argument"]
@@ -38,6 +53,9 @@ def test_shim_matches_reference_classes_on_test_double(oracle, sim):
 def test_shim_matches_reference_classes_on_gpu(gpu):
     if not os.path.exists(os.path.join(BUILD, "shim_parity_gpu")):
         pytest.fail("tests/shim/_build/shim_parity_gpu missing (built by __graft_entry__.build())")
-    rc, d = _run("shim_parity_gpu", 32, 3)
+    import tempfile
+    with tempfile.TemporaryDirectory() as td:
+        rc, d = _run("shim_parity_gpu", 32, 3, _weights_dir(td))
     assert rc == 0 and d["ok"], d
+    _check_closure(d)
     assert d["u_rel_l2"] <= 1e-10 and d["p_rel_l2"] <= 1e-10 and d["mg_p_rel_l2"] <= 1e-10

@@ -108,3 +108,57 @@ def test_gpu_slabs_match_single_domain(R, oracle, gpu, world):
     got = {n: _assemble(slabs, n, Nz) for n in ("u", "v", "w", "p", "pcorr", "div", "rhs")}
     cases.compare_states(got, ref, 1e-10, f"{world} GPU slabs")
     assert list(slabs[0]["cycles"]) == meta["cycles"]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_gpu_slabs_big_tiles_distributed_levels(R, oracle, gpu, world, monkeypatch):
+    """The multi-GPU paths behind the scaling numbers, on real hardware over NCCL: a periodic 128 x 64 x (64 P)
+    box keeps THREE multigrid levels distributed (CFDNN_MG_REPLICATE_CELLS small), so level 0 runs the 64x26-tile
+    lean smoother with halo z sides, the split launch on the communication stream (overlap on) or the serial
+    exchange (overlap off), slab coarse levels with 2-deep halos, the slab-aware fused residual + restriction
+    (CFDNN_MG_RR_MIN=8) and the agglomerating all-gather.  Checked three ways: P slabs vs the single-GPU run
+    of the same box (<= 1e-12), overlap on vs off (bitwise), and vs the single-domain oracle (<= 1e-10)."""
+    if gpu.lib.cfdnn_device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import slab_worker
+    monkeypatch.setenv("CFDNN_MG_REPLICATE_CELLS", "10000")
+    monkeypatch.setenv("CFDNN_MG_RR_MIN", "8")
+    N = (128, 64, 64 * world)
+    bc, ti, fixed, nsteps = "PPPPPP", "rk3", 0, 1
+    names = ("u", "v", "w", "p", "pcorr", "div", "rhs")
+    got = {}
+    for ov in ("1", "0"):
+        monkeypatch.setenv("CFDNN_MG_OVERLAP", ov)
+        with tempfile.TemporaryDirectory() as td:
+            slabs = _run_slabs(world, N, bc, ti, nsteps, fixed, td, gpu=True)
+            got[ov] = {n: _assemble(slabs, n, N[2] // world) for n in names}
+            got[ov]["cycles"] = list(slabs[0]["cycles"])
+    for n in names:
+        assert np.array_equal(got["1"][n], got["0"][n]), f"overlap on/off differ in {n}"
+    # single-GPU run of the same global box (same library, same environment, no communicator)
+    u, v, w = slab_worker.global_init(*N, bc)
+    cfg = gpu.config(nu=0.01, dt=0.01, time_integrator=R.TI[ti], convective_scheme=R.SCHEME["skew"], adaptive_dt=0,
+                     poisson_fixed_cycles=fixed, poisson_tol_rhs=1e-8, poisson_max_vcycles=50)
+    h = gpu.solver(gpu.mesh(*N), cfg, bc)
+    gpu.upload(h, "u", u); gpu.upload(h, "v", v); gpu.upload(h, "w", w)
+    gpu.check(gpu.lib.cfdnn_solver_initialize(h))
+    gpu.step(h)
+    single = gpu.state(h, *N, names=names)
+    cyc_single = gpu.cycles(h)
+    gpu.lib.cfdnn_solver_destroy(h)
+    assert got["1"]["cycles"] == cyc_single
+    for n in names:
+        a, b = R.interior(n, got["1"][n]), R.interior(n, single[n])
+        scale = max(np.abs(b).max(), 1e-300)
+        assert np.abs(a - b).max() / scale <= (1e-12 if n not in ("div", "rhs") else 1e-9), n
+    with tempfile.TemporaryDirectory() as td:
+        pre = os.path.join(td, "in")
+        u.tofile(pre + "_u.f64"); v.tofile(pre + "_v.f64"); w.tofile(pre + "_w.f64")
+        meta = R.run_ref("step", Nx=N[0], Ny=N[1], Nz=N[2], bc=bc, ti=ti, scheme="skew", fixed=fixed, nsteps=nsteps,
+                         dt=0.01, nu=0.01, init="file:" + pre, call_initialize=1, out=os.path.join(td, "ref"),
+                         tol_rhs=1e-8, maxv=50)
+        ref = R.load_state(os.path.join(td, "ref_final"), *N)
+    assert got["1"]["cycles"] == meta["cycles"]
+    cases.compare_states({n: got["1"][n] for n in names}, ref, 1e-10, f"{world} GPU slabs, big tiles")
