@@ -1,0 +1,280 @@
+// momentum_kernels.cuh — fused momentum update, z-marching tile version (FP64, sm_100a).
+//
+//   out = in + dt * ( -conv(vel) + diff(vel, nu_eff) + f )   on interior faces of u, v, w
+// = compute_convective_term + compute_diffusive_term + the advance loop of euler_substep
+// (reference src/solver_operators.cpp:493-1070, src/solver_time.cpp:269-516; per-face formulas
+// include/solver_kernels.hpp:845-1022 central, :1377-1569 skew-symmetric, :2199-2337 diffusion).
+//
+// The one-thread-per-point kernel it replaces (k_momentum, solver_kernels.cuh) gathered 93 values per
+// cell through the LSU and rebuilt every address with 64-bit multiplies: instruction-bound at 0.26 of
+// the HBM roofline.  Here
+//   * a CTA owns a BX x BY column of cells and marches through a chunk of z planes; a thread owns one
+//     (i, j) column and keeps the planes k-1, k, k+1 of u, v, w, nu_eff of that column in registers
+//     (each value is loaded from HBM once per plane, 4 loads per cell instead of 93);
+//   * the 31 in-plane neighbours the three face stencils need come from one shared-memory tile per
+//     field and plane (ring of 4 z slots, one __syncthreads per plane), addressed with constant offsets
+//     from three per-iteration slot registers;
+//   * the three face updates of a cell share every loaded value (43 distinct inputs in all);
+//   * EXACT = true keeps the reference's expression order and true divisions (correctly rounded fdiv):
+//     bit-identical to the x86 build — required on y-stretched meshes, whose Poisson solver amplifies a
+//     last-bit change.  EXACT = false (uniform meshes): divisions by the constant spacings
+//     become multiplications by their reciprocals and products feed fused multiply-adds — ~225 instead of
+//     ~345 FP64 instructions per cell, every face value within a few ulp of the reference's.
+//
+// Index space: raw array indices (I, J, K) over the ghost-inclusive arrays, like k_momentum: entries that
+// are not interior faces are copied from vel when copy_ghosts is set (RK stages 2-3 write into a scratch
+// buffer that is then swapped with vel, see Solver::momentum).
+#pragma once
+#include "solver.cuh"
+
+namespace cfdnn {
+
+struct MomCoef {                  // spacings as divisor/reciprocal pairs and folded constants
+    Div dx, dy, dz, dx_2, dy_2, dz_2, dx2, dy2, dz2;
+    double h_rdx, h_rdy, h_rdz;           // 0.5 / dx ...      (EXACT = false)
+    double h_r2dx, h_r2dy, h_r2dz;        // 0.5 / (2 dx) ...
+    double dt, fx, fy, fz;
+};
+
+template <bool EXACT>
+__device__ __forceinline__ double mom_fma(double a, double b, double c) {
+    if (EXACT) return a * b + c;          // two roundings, as the x86 build (-fmad=false)
+    return fma(a, b, c);
+}
+
+// One direction of the skew-symmetric form 0.5 * (advective + conservative) for face value q:
+//   adv = a * (q_p - q_m) / (2h),  cons = (a_hi * 0.5 (q + q_p) - a_lo * 0.5 (q + q_m)) / h
+// a: advecting velocity at the face, a_lo / a_hi: advecting velocity at the two neighbouring flux points.
+template <bool EXACT>
+__device__ __forceinline__ double skew_dir(double a, double a_lo, double a_hi, double q, double q_m, double q_p,
+                                           const Div& h, const Div& h2, double h_rh, double h_r2h) {
+    if (EXACT) {
+        const double adv = a * (q_p - q_m) / h2;
+        const double lo = 0.5 * (q + q_m), hi = 0.5 * (q + q_p);
+        const double cons = (a_hi * hi - a_lo * lo) / h;
+        return 0.5 * (adv + cons);
+    } else {
+        const double lo = 0.5 * (q + q_m), hi = 0.5 * (q + q_p);
+        const double fl = fma(a_hi, hi, -(a_lo * lo));
+        return fma(fl, h_rh, (a * (q_p - q_m)) * h_r2h);
+    }
+}
+// own direction of the face: the advecting velocity is q itself, flux = (0.5 (q + q_p))^2
+template <bool EXACT>
+__device__ __forceinline__ double skew_own(double q, double q_m, double q_p, const Div& h, const Div& h2,
+                                           double h_rh, double h_r2h) {
+    if (EXACT) {
+        const double adv = q * (q_p - q_m) / h2;
+        const double lo = 0.5 * (q_m + q), hi = 0.5 * (q + q_p);
+        const double cons = (hi * hi - lo * lo) / h;
+        return 0.5 * (adv + cons);
+    } else {
+        const double lo = 0.5 * (q_m + q), hi = 0.5 * (q + q_p);
+        const double fl = fma(hi, hi, -(lo * lo));
+        return fma(fl, h_rh, (q * (q_p - q_m)) * h_r2h);
+    }
+}
+template <bool EXACT>
+__device__ __forceinline__ double central_dir(double a, double q_m, double q_p, const Div& h2) {
+    if (EXACT) return a * ((q_p - q_m) / h2);
+    return a * ((q_p - q_m) * h2.r);
+}
+// (nu_hi (q_p - q) - nu_lo (q - q_m)) / h^2
+template <bool EXACT>
+__device__ __forceinline__ double diff_dir(double nu_lo, double nu_hi, double q, double q_m, double q_p, const Div& hh) {
+    if (EXACT) return (nu_hi * (q_p - q) - nu_lo * (q - q_m)) / hh;
+    return fma(nu_hi, q_p - q, -(nu_lo * (q - q_m))) * hh.r;
+}
+
+template <int BX, int BY>
+struct MomShape {
+    static constexpr int TX = BX + 2, TY = BY + 2;
+    static constexpr int PL = TX * TY;                    // doubles per tile plane
+    static constexpr int NT = BX * BY;
+    static constexpr int NHALO = PL - NT;
+    static constexpr size_t SMEM = sizeof(double) * 4 /*fields*/ * 4 /*slots*/ * PL;
+    static_assert(NHALO <= NT, "one halo element per thread at most");
+};
+
+// SKEW: skew-symmetric (true) or central (false) convection.  Launch: grid (ceil((ex+1)/BX), ceil((ey+1)/BY), z chunks),
+// block BX*BY threads.  zc = planes per chunk.
+template <bool SKEW, bool EXACT, int BX, int BY>
+__global__ void __launch_bounds__(BX * BY)
+k_momentum_z(Geom g, MomCoef c, Vel vel, const double* __restrict__ nu, Vel in, Vel out, int copy_ghosts, int zc) {
+    using S = MomShape<BX, BY>;
+    CFDNN_DYN_SMEM(double, sm);
+    constexpr int PL = S::PL, TX = S::TX;
+    constexpr int FU = 0, FV = 4 * PL, FW = 8 * PL, FN = 12 * PL;    // field bases (4 slots each)
+    const int Ng = g.Ng;
+    const int ex = g.Nx + 2 * Ng, ey = g.Ny + 2 * Ng, ez = g.Nz + 2 * Ng;   // cell-array extents
+    const int tx = threadIdx.x % BX, ty = threadIdx.x / BX;
+    const int i0 = (int)blockIdx.x * BX, j0 = (int)blockIdx.y * BY;
+    const int i = i0 + tx, j = j0 + ty;
+    const int k0 = (int)blockIdx.z * zc, k1 = min(k0 + zc, ez + 1);   // raw planes [k0, k1), K in [0, ez]
+
+    // ---- per-thread load geometry: own column and (for the first NHALO threads) one halo column
+    // clamped coordinates per field (u has ex+1 columns, v ey+1 rows, w ez+1 planes)
+    const int iu = min(i, ex), ic = min(i, ex - 1);
+    const int jv = min(j, ey), jc = min(j, ey - 1);
+    const unsigned own_u = (unsigned)(jc * g.us + iu), own_v = (unsigned)(jv * g.vs + ic);
+    const unsigned own_w = (unsigned)(jc * g.ws + ic), own_n = (unsigned)(jc * g.cs + ic);
+    const int t_own = (ty + 1) * TX + tx + 1;
+    int t_halo = -1;
+    unsigned hal_u = 0, hal_v = 0, hal_w = 0, hal_n = 0;
+    if ((int)threadIdx.x < S::NHALO) {
+        int h = threadIdx.x, hx, hy;
+        if (h < TX) { hx = h; hy = 0; }
+        else if (h < 2 * TX) { hx = h - TX; hy = S::TY - 1; }
+        else if (h < 2 * TX + BY) { hx = 0; hy = h - 2 * TX + 1; }
+        else { hx = TX - 1; hy = h - 2 * TX - BY + 1; }
+        t_halo = hy * TX + hx;
+        const int hi_ = i0 + hx - 1, hj_ = j0 + hy - 1;
+        const int hiu = min(max(hi_, 0), ex), hic = min(max(hi_, 0), ex - 1);
+        const int hjv = min(max(hj_, 0), ey), hjc = min(max(hj_, 0), ey - 1);
+        hal_u = (unsigned)(hjc * g.us + hiu); hal_v = (unsigned)(hjv * g.vs + hic);
+        hal_w = (unsigned)(hjc * g.ws + hic); hal_n = (unsigned)(hjc * g.cs + hic);
+    }
+    // which entries this column owns, and which of them are interior faces
+    const bool col_u = i <= ex && j < ey, col_v = i < ex && j <= ey, col_w = i < ex && j < ey;
+    const bool ix_c = i >= Ng && i < Ng + g.Nx, iy_c = j >= Ng && j < Ng + g.Ny;
+    const bool ix_f = i >= Ng && i <= Ng + g.Nx, iy_f = j >= Ng && j <= Ng + g.Ny;
+    const bool int_u = ix_f && iy_c, int_v = ix_c && iy_f, int_w = ix_c && iy_c;     // and the k condition, per plane
+
+    // plane loader: K clamped per field; own value -> register + tile, halo value -> tile
+    double pu, pv, pw, pn;                                  // plane K+1 of the own column
+    auto load_plane = [&](int K, int slot) {
+        const int ku = min(max(K, 0), ez - 1), kw = min(max(K, 0), ez);
+        const double* bu = vel.u + (size_t)ku * (size_t)g.up;
+        const double* bv = vel.v + (size_t)ku * (size_t)g.vp;
+        const double* bw = vel.w + (size_t)kw * (size_t)g.wp;
+        const double* bn = nu + (size_t)ku * (size_t)g.cp;
+        pu = bu[own_u]; pv = bv[own_v]; pw = bw[own_w]; pn = bn[own_n];
+        double* t = sm + slot * PL;
+        t[FU + t_own] = pu; t[FV + t_own] = pv; t[FW + t_own] = pw; t[FN + t_own] = pn;
+        if (t_halo >= 0) {
+            t[FU + t_halo] = bu[hal_u]; t[FV + t_halo] = bv[hal_v]; t[FW + t_halo] = bw[hal_w]; t[FN + t_halo] = bn[hal_n];
+        }
+    };
+
+    // ---- prologue: planes k0-1 and k0
+    double um, vm, wm, nm, uc, vc, wc, nc;
+    load_plane(k0 - 1, (k0 - 1) & 3);
+    um = pu; vm = pv; wm = pw; nm = pn;
+    load_plane(k0, k0 & 3);
+    uc = pu; vc = pv; wc = pw; nc = pn;
+
+    for (int K = k0; K < k1; ++K) {
+        load_plane(K + 1, (K + 1) & 3);                     // plane K+1 -> registers (pu..) and tile
+        __syncthreads();
+        const double* tm = sm + ((K - 1) & 3) * PL + t_own;   // tiles of planes K-1, K, K+1 at the own column
+        const double* tc = sm + (K & 3) * PL + t_own;
+        const double* tp = sm + ((K + 1) & 3) * PL + t_own;
+        const bool kz_c = K >= Ng && K < Ng + g.Nz, kz_f = K >= Ng && K <= Ng + g.Nz;
+        const bool kin = K < ez;                            // u, v entries exist on planes < ez; w on planes <= ez
+
+        // in-plane neighbours shared by the three faces (plane K)
+        const double u_w = tc[FU - 1], u_e = tc[FU + 1], u_s = tc[FU - TX], u_n = tc[FU + TX], u_se = tc[FU - TX + 1];
+        const double v_w = tc[FV - 1], v_e = tc[FV + 1], v_s = tc[FV - TX], v_n = tc[FV + TX], v_nw = tc[FV + TX - 1];
+        const double w_w = tc[FW - 1], w_e = tc[FW + 1], w_s = tc[FW - TX], w_n = tc[FW + TX];
+        const double n_w = tc[FN - 1], n_e = tc[FN + 1], n_s = tc[FN - TX], n_n = tc[FN + TX];
+        const double n_sw = tc[FN - TX - 1], n_nw = tc[FN + TX - 1], n_se = tc[FN - TX + 1];
+
+        if (col_u && kin) {
+            const size_t o = (size_t)K * (size_t)g.up + own_u;
+            if (int_u && kz_c) {
+                // u face (i, j, K): x is the own direction
+                const double wp_w = tp[FW - 1];
+                const double vv = 0.25 * (v_w + vc + v_nw + v_n);
+                const double ww = 0.25 * (w_w + wc + wp_w + pw);
+                double conv;
+                if (SKEW) {
+                    const double sx = skew_own<EXACT>(uc, u_w, u_e, c.dx, c.dx_2, c.h_rdx, c.h_r2dx);
+                    const double sy = skew_dir<EXACT>(vv, 0.5 * (v_w + vc), 0.5 * (v_nw + v_n), uc, u_s, u_n, c.dy, c.dy_2, c.h_rdy, c.h_r2dy);
+                    const double sz = skew_dir<EXACT>(ww, 0.5 * (w_w + wc), 0.5 * (wp_w + pw), uc, um, pu, c.dz, c.dz_2, c.h_rdz, c.h_r2dz);
+                    conv = sx + sy + sz;
+                } else {
+                    conv = central_dir<EXACT>(uc, u_w, u_e, c.dx_2) + central_dir<EXACT>(vv, u_s, u_n, c.dy_2) +
+                           central_dir<EXACT>(ww, um, pu, c.dz_2);
+                }
+                const double nl = n_w, nr = nc;             // nu of the two cells adjacent in x
+                const double d2x = diff_dir<EXACT>(nl, nr, uc, u_w, u_e, c.dx2);
+                const double nu_n = 0.25 * (nl + nr + n_nw + n_n);
+                const double nu_s = 0.25 * (nl + nr + n_sw + n_s);
+                const double d2y = diff_dir<EXACT>(nu_s, nu_n, uc, u_s, u_n, c.dy2);
+                const double nu_f = 0.25 * (nl + nr + tp[FN - 1] + pn);
+                const double nu_b = 0.25 * (nl + nr + tm[FN - 1] + nm);
+                const double d2z = diff_dir<EXACT>(nu_b, nu_f, uc, um, pu, c.dz2);
+                const double diff = d2x + d2y + d2z;
+                out.u[o] = mom_fma<EXACT>(c.dt, -conv + diff + c.fx, in.u[o]);
+            } else if (copy_ghosts) {
+                out.u[o] = uc;
+            }
+        }
+        if (col_v && kin) {
+            const size_t o = (size_t)K * (size_t)g.vp + own_v;
+            if (int_v && kz_c) {
+                // v face (i, j, K): y is the own direction
+                const double wp_s = tp[FW - TX];
+                const double uu = 0.25 * (u_s + u_se + uc + u_e);
+                const double ww = 0.25 * (w_s + wc + wp_s + pw);
+                double conv;
+                if (SKEW) {
+                    const double sx = skew_dir<EXACT>(uu, 0.5 * (u_s + uc), 0.5 * (u_se + u_e), vc, v_w, v_e, c.dx, c.dx_2, c.h_rdx, c.h_r2dx);
+                    const double sy = skew_own<EXACT>(vc, v_s, v_n, c.dy, c.dy_2, c.h_rdy, c.h_r2dy);
+                    const double sz = skew_dir<EXACT>(ww, 0.5 * (w_s + wc), 0.5 * (wp_s + pw), vc, vm, pv, c.dz, c.dz_2, c.h_rdz, c.h_r2dz);
+                    conv = sx + sy + sz;
+                } else {
+                    conv = central_dir<EXACT>(uu, v_w, v_e, c.dx_2) + central_dir<EXACT>(vc, v_s, v_n, c.dy_2) +
+                           central_dir<EXACT>(ww, vm, pv, c.dz_2);
+                }
+                const double nb = n_s, nt = nc;             // nu of the two cells adjacent in y
+                const double nu_e = 0.25 * (nb + nt + n_se + n_e);
+                const double nu_w = 0.25 * (nb + nt + n_sw + n_w);
+                const double d2x = diff_dir<EXACT>(nu_w, nu_e, vc, v_w, v_e, c.dx2);
+                const double d2y = diff_dir<EXACT>(nb, nt, vc, v_s, v_n, c.dy2);
+                const double nu_f = 0.25 * (nb + nt + tp[FN - TX] + pn);
+                const double nu_b = 0.25 * (nb + nt + tm[FN - TX] + nm);
+                const double d2z = diff_dir<EXACT>(nu_b, nu_f, vc, vm, pv, c.dz2);
+                const double diff = d2x + d2y + d2z;
+                out.v[o] = mom_fma<EXACT>(c.dt, -conv + diff + c.fy, in.v[o]);
+            } else if (copy_ghosts) {
+                out.v[o] = vc;
+            }
+        }
+        if (col_w) {
+            const size_t o = (size_t)K * (size_t)g.wp + own_w;
+            if (int_w && kz_f) {
+                // w face (i, j, K): z is the own direction; the transverse velocities sit on planes K-1 and K
+                const double um_e = tm[FU + 1], vm_n = tm[FV + TX];
+                const double uu = 0.25 * (um + um_e + uc + u_e);
+                const double vv = 0.25 * (vm + vm_n + vc + v_n);
+                double conv;
+                if (SKEW) {
+                    const double sx = skew_dir<EXACT>(uu, 0.5 * (um + uc), 0.5 * (um_e + u_e), wc, w_w, w_e, c.dx, c.dx_2, c.h_rdx, c.h_r2dx);
+                    const double sy = skew_dir<EXACT>(vv, 0.5 * (vm + vc), 0.5 * (vm_n + v_n), wc, w_s, w_n, c.dy, c.dy_2, c.h_rdy, c.h_r2dy);
+                    const double sz = skew_own<EXACT>(wc, wm, pw, c.dz, c.dz_2, c.h_rdz, c.h_r2dz);
+                    conv = sx + sy + sz;
+                } else {
+                    conv = central_dir<EXACT>(uu, w_w, w_e, c.dx_2) + central_dir<EXACT>(vv, w_s, w_n, c.dy_2) +
+                           central_dir<EXACT>(wc, wm, pw, c.dz_2);
+                }
+                const double nbk = nm, nfr = nc;            // nu of the two cells adjacent in z
+                const double nu_e = 0.25 * (nbk + nfr + tm[FN + 1] + n_e);
+                const double nu_w = 0.25 * (nbk + nfr + tm[FN - 1] + n_w);
+                const double d2x = diff_dir<EXACT>(nu_w, nu_e, wc, w_w, w_e, c.dx2);
+                const double nu_n = 0.25 * (nbk + nfr + tm[FN + TX] + n_n);
+                const double nu_s = 0.25 * (nbk + nfr + tm[FN - TX] + n_s);
+                const double d2y = diff_dir<EXACT>(nu_s, nu_n, wc, w_s, w_n, c.dy2);
+                const double d2z = diff_dir<EXACT>(nbk, nfr, wc, wm, pw, c.dz2);
+                const double diff = d2x + d2y + d2z;
+                out.w[o] = mom_fma<EXACT>(c.dt, -conv + diff + c.fz, in.w[o]);
+            } else if (copy_ghosts) {
+                out.w[o] = wc;
+            }
+        }
+        um = uc; vm = vc; wm = wc; nm = nc;
+        uc = pu; vc = pv; wc = pw; nc = pn;
+    }
+}
+
+}  // namespace cfdnn

@@ -99,8 +99,8 @@ __device__ __forceinline__ void cell_features(const Geom& g, const NNParams& prm
 #define U2(I, J) u[(size_t)(J) * g.us + (I)]
 #define V2(I, J) v[(size_t)(J) * g.vs + (I)]
     // uniform-spacing MAC gradients (features.cpp:132-140, turbulence_nn_tbnn.cpp:838-845)
-    const double inv_2dx = 1.0 / (2.0 * g.dx.d);
-    const double inv_2dy = 1.0 / (2.0 * g.dy.d);
+    const double inv_2dx = g.dx_2.r;     // RN(1 / (2 dx)), the same double the reference's 1.0 / (2.0 * dx) gives
+    const double inv_2dy = g.dy_2.r;
     const double dudx = (U2(i + 1, j) - U2(i - 1, j)) * inv_2dx;
     const double dudy = (U2(i, j + 1) - U2(i, j - 1)) * inv_2dy;
     const double dvdx = (V2(i + 1, j) - V2(i - 1, j)) * inv_2dx;
@@ -290,6 +290,43 @@ __device__ __forceinline__ double act_mma(double s, int act) {
     return s;
 }
 
+// tanh for the shape-specialised kernel.  The FP64 FMA pipe and the DMMA pipe are ONE resource on sm_100a
+// (scripts/fp64_peaks.cu: 37.1 TFLOP/s of DMMA alone, 33.4 of DFMA alone, 32-35 combined in any mix), so every FP64
+// instruction of the activation is taken from the GEMMs.  Same scheme as fast_tanh, t = exp(-2|x|),
+// tanh = (1 - t) / (1 + t), with the work moved off that pipe where possible: the argument reduction is to
+// 1/32 of an octave, exp = 2^m * 2^(j/32) * P4(r) with 2^(j/32) from a 32-entry shared-memory table (stored 16 times
+// so that the lanes of a half-warp read 16 different banks whatever j they need) and a degree-4 polynomial on
+// |r| <= ln2/64; |x| is clamped, the 2^m scaling, the sign and the NaN test are integer operations on the high word;
+// one Newton step on the 20-bit reciprocal seed.  14 FP64 instructions instead of 26; absolute error <= 1e-12.
+constexpr int TANH_TAB_DOUBLES = 32 * 16;
+__device__ __forceinline__ double tanh_tab(double x, const double* __restrict__ tab /* + (lane & 15) */) {
+    const int hx = __double2hiint(x);
+    const int habs = hx & 0x7fffffff;
+    const int hcl = min(habs, 0x40340000);                          // |x| clamped just above 20: tanh = 1 - 8e-18 there
+    const double ax = __hiloint2double(hcl, __double2loint(x));
+    const double y = -2.0 * ax;
+    const double MAGIC = 6755399441055744.0;                        // 1.5 * 2^52
+    double fn = __fma_rn(y, 46.16624130844683, MAGIC);              // 32 / ln2
+    const int n = __double2loint(fn);                               // round(32 y / ln2) in [-1847, 0]
+    fn = fn - MAGIC;
+    const double r = __fma_rn(fn, -0.02166084939249829, y);         // ln2 / 32
+    double p = __fma_rn(r, 4.1666666666666664e-02, 1.6666666666666666e-01);
+    p = __fma_rn(p, r, 0.5);
+    p = __fma_rn(p, r, 1.0);
+    p = __fma_rn(p, r, 1.0);
+    const double T = tab[(n & 31) * 16];
+    const double Ts = __hiloint2double(__double2hiint(T) + ((n >> 5) << 20), __double2loint(T));   // 2^(n/32), exponent >= -58
+    const double t = Ts * p;
+    const double num = 1.0 - t, den = 1.0 + t;                      // den in [1, 2]
+    double rc;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(rc) : "d"(den));
+    const double e = __fma_rn(-den, rc, 1.0);
+    rc = __fma_rn(rc, e, rc);
+    const double q = num * rc;
+    const double qs = __hiloint2double(__double2hiint(q) | (hx & 0x80000000), __double2loint(q));
+    return habs > 0x7ff00000 ? x : qs;                              // NaN in -> NaN out; +-inf -> +-1
+}
+
 constexpr int MMA_WARPS = 4;
 
 template <int KIND>
@@ -433,7 +470,8 @@ constexpr int MMAH_WARPS = 8;
 
 template <int NTI, int NTO, bool TANH>
 __device__ __forceinline__ void mma_layer(const double2* __restrict__ Wl, const double* __restrict__ bl, int lane,
-                                          int q, const double2 (&a)[NTI], double2 (&o)[NTO]) {
+                                          int q, const double* __restrict__ tab, const double2 (&a)[NTI],
+                                          double2 (&o)[NTO]) {
     if constexpr (NTO == 1) {
         // one N tile: K tiles dealt to four chains, summed pairwise at the end
         double2 c[4];
@@ -449,7 +487,7 @@ __device__ __forceinline__ void mma_layer(const double2* __restrict__ Wl, const 
         double2 r;
         r.x = (c[0].x + c[1].x) + (c[2].x + c[3].x);
         r.y = (c[0].y + c[1].y) + (c[2].y + c[3].y);
-        o[0] = TANH ? make_double2(fast_tanh(r.x), fast_tanh(r.y)) : r;
+        o[0] = TANH ? make_double2(tanh_tab(r.x, tab), tanh_tab(r.y, tab)) : r;
     } else {
         static_assert(NTO % 4 == 0, "N tiles are processed four at a time");
 #pragma unroll
@@ -469,7 +507,7 @@ __device__ __forceinline__ void mma_layer(const double2* __restrict__ Wl, const 
             }
 #pragma unroll
             for (int n = 0; n < 4; ++n)
-                o[ng + n] = TANH ? make_double2(fast_tanh(c[n].x), fast_tanh(c[n].y)) : c[n];
+                o[ng + n] = TANH ? make_double2(tanh_tab(c[n].x, tab), tanh_tab(c[n].y, tab)) : c[n];
         }
     }
 }
@@ -486,6 +524,8 @@ k_nn_update_mmah(Geom g, NNFrag net, NNParams prm, const double* __restrict__ yc
     double* bsm = reinterpret_cast<double*>(Wsm + net.w_total);         // biases
     double* xsm = bsm + ((net.b_total + 1) & ~1);                       // [warp][32 cells][8]: features in, outputs back
     double* csm = xsm + MMAH_WARPS * 32 * 8;                            // [warp][8][32 cells]: context of the nu_t stage
+    double* tsm = csm + MMAH_WARPS * 32 * 8;                            // [32 entries][16 copies]: 2^(j/32) for tanh_tab
+    for (int t = threadIdx.x; t < TANH_TAB_DOUBLES; t += blockDim.x) tsm[t] = exp2((double)(t >> 4) * 0.03125);
     for (int t = threadIdx.x; t < net.w_total; t += blockDim.x) Wsm[t] = net.W[t];
     for (int t = threadIdx.x; t < net.b_total; t += blockDim.x) bsm[t] = net.b[t];
     __syncthreads();
@@ -494,6 +534,7 @@ k_nn_update_mmah(Geom g, NNFrag net, NNParams prm, const double* __restrict__ yc
     const int grp = lane >> 2, q = lane & 3;
     double* xw = xsm + warp * 256;
     double* cw = csm + warp * 256;
+    const double* tab = tsm + (lane & 15);
     const int pl = blockIdx.z;
     const int kk = plane0 + pl;
     const double* u = ub + (size_t)kk * g.up;
@@ -537,16 +578,16 @@ k_nn_update_mmah(Geom g, NNFrag net, NNParams prm, const double* __restrict__ yc
             {
                 double2 a0[1];
                 a0[0] = *reinterpret_cast<const double2*>(xrow);
-                mma_layer<1, H, true>(Wsm + net.woff[0], bsm + net.boff[0], lane, q, a0, a);
+                mma_layer<1, H, true>(Wsm + net.woff[0], bsm + net.boff[0], lane, q, tab, a0, a);
             }
 #pragma unroll 1
             for (int l = 1; l <= nhid; ++l) {
-                mma_layer<H, H, true>(Wsm + net.woff[l], bsm + net.boff[l], lane, q, a, o);
+                mma_layer<H, H, true>(Wsm + net.woff[l], bsm + net.boff[l], lane, q, tab, a, o);
 #pragma unroll
                 for (int t = 0; t < H; ++t) a[t] = o[t];
             }
             double2 r[1];
-            mma_layer<H, 1, false>(Wsm + net.woff[nhid + 1], bsm + net.boff[nhid + 1], lane, q, a, r);
+            mma_layer<H, 1, false>(Wsm + net.woff[nhid + 1], bsm + net.boff[nhid + 1], lane, q, tab, a, r);
             *reinterpret_cast<double2*>(xrow) = r[0];                   // outputs 2q, 2q+1 of cell mt*8 + grp
         }
         __syncwarp();
@@ -673,7 +714,8 @@ void NNClosure::build_fragments(const std::vector<double>& hw, const std::vector
         if (ok) mmah_ = hw / 8;
     }
     if (const char* g = std::getenv("CFDNN_NN_GENERIC")) if (std::atoi(g) != 0) mmah_ = 0;   // A/B: generic DMMA kernel
-    mmah_smem_ = nw * sizeof(double2) + ((nb + 1) & ~(size_t)1) * sizeof(double) + 2 * MMAH_WARPS * 32 * 8 * sizeof(double);
+    mmah_smem_ = nw * sizeof(double2) + ((nb + 1) & ~(size_t)1) * sizeof(double) +
+                 (2 * MMAH_WARPS * 32 * 8 + TANH_TAB_DOUBLES) * sizeof(double);
     if (mmah_smem_ > 113 * 1024) mmah_ = 0;             // two CTAs per SM
     if (mmah_) {
         CFDNN_CUDA(cudaFuncSetAttribute(k_nn_update_mmah<CFDNN_TURB_NN_TBNN, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mmah_smem_));

@@ -1,11 +1,13 @@
 // solver.cu — host orchestration of the fractional-step path (see solver.cuh).
 #include "solver_kernels.cuh"
+#include "momentum_kernels.cuh"
 #include "mg_kernels.cuh"
 #include "comm.cuh"
 #include "nn.cuh"
 #include <cmath>
 #include <algorithm>
 #include <cstring>
+#include <cstdlib>
 
 namespace cfdnn {
 
@@ -93,6 +95,15 @@ Solver::Solver(const cfdnn_mesh_desc& m, const cfdnn_config& c) : mesh_(m), cfg_
 
     mg_ = std::make_unique<Multigrid>(m);
     if (is2d_) mg_->set_2d_plane(Ng, /*dup=*/true);
+    if (const char* e = std::getenv("CFDNN_MOMENTUM_Z")) mom_z_ = std::atoi(e) != 0;          // 0: one-thread-per-point kernel
+    if (const char* e = std::getenv("CFDNN_MOMENTUM_EXACT")) mom_exact_ = std::atoi(e) != 0;  // 1: exact divisions everywhere
+    {
+        using S = MomShape<64, 4>;
+        CFDNN_CUDA(cudaFuncSetAttribute(k_momentum_z<true, true, 64, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::SMEM));
+        CFDNN_CUDA(cudaFuncSetAttribute(k_momentum_z<true, false, 64, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::SMEM));
+        CFDNN_CUDA(cudaFuncSetAttribute(k_momentum_z<false, true, 64, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::SMEM));
+        CFDNN_CUDA(cudaFuncSetAttribute(k_momentum_z<false, false, 64, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::SMEM));
+    }
     dt_ = c.dt;
     set_velocity_bc(vbc_);
 }
@@ -336,7 +347,32 @@ void Solver::momentum(const Vel& in, Vel& out, double dt, bool seam_average) {
     }
     const Vel src_in = in;                       // copies of the pointer triples (in may be vel_ itself)
     const Vel dst = alias ? conv_ : out;
-    if (cfg_.convective_scheme == CFDNN_CONV_SKEW)
+    if (mom_z_) {
+        // z-marching tile kernel (momentum_kernels.cuh).  Exact divisions + unfused products wherever the result
+        // must carry the x86 build's bits: y-stretched meshes (their Poisson solver amplifies a last-bit change)
+        // and the 2-D embedding; reciprocal multiplies + FMA on uniform 3-D meshes.
+        constexpr int BX = 64, BY = 4;
+        using S = MomShape<BX, BY>;
+        MomCoef c{};
+        c.dx = g_.dx; c.dy = g_.dy; c.dz = g_.dz; c.dx_2 = g_.dx_2; c.dy_2 = g_.dy_2; c.dz_2 = g_.dz_2;
+        c.dx2 = g_.dx2; c.dy2 = g_.dy2; c.dz2 = g_.dz2;
+        c.h_rdx = 0.5 / g_.dx.d; c.h_rdy = 0.5 / g_.dy.d; c.h_rdz = 0.5 / g_.dz.d;
+        c.h_r2dx = 0.5 / g_.dx_2.d; c.h_r2dy = 0.5 / g_.dy_2.d; c.h_r2dz = 0.5 / g_.dz_2.d;
+        c.dt = dt; c.fx = fx_; c.fy = fy_; c.fz = fz_;
+        const int ex = g_.Nx + 2 * Ng, ey = g_.Ny + 2 * Ng, ez = g_.Nz + 2 * Ng;
+        const int tiles = ((ex + BX) / BX) * ((ey + BY) / BY);
+        int zc = 64;                              // planes per CTA: 2 extra plane loads per chunk
+        while (zc > 8 && (long long)tiles * ((ez + zc) / zc) < 4LL * 148) zc /= 2;
+        const dim3 grid((ex + BX) / BX, (ey + BY) / BY, (ez + zc) / zc);
+        const bool exact = mom_exact_ || g_.y_stretched || is2d_;
+        const bool skew = cfg_.convective_scheme == CFDNN_CONV_SKEW;
+#define CFDNN_MOMZ(SK, EX)                                                                                          \
+        CFDNN_LAUNCH_COOP((k_momentum_z<SK, EX, BX, BY>), grid, BX * BY, S::SMEM, st_, g_, c, vel_, nueff_, src_in, dst, \
+                          alias ? 1 : 0, zc)
+        if (skew) { if (exact) CFDNN_MOMZ(true, true); else CFDNN_MOMZ(true, false); }
+        else { if (exact) CFDNN_MOMZ(false, true); else CFDNN_MOMZ(false, false); }
+#undef CFDNN_MOMZ
+    } else if (cfg_.convective_scheme == CFDNN_CONV_SKEW)
         CFDNN_LAUNCH((k_momentum<true>), gr, kB, 0, st_, g_, vel_, nueff_, src_in, dst, dt, fx_, fy_, fz_, alias ? 1 : 0);
     else
         CFDNN_LAUNCH((k_momentum<false>), gr, kB, 0, st_, g_, vel_, nueff_, src_in, dst, dt, fx_, fy_, fz_, alias ? 1 : 0);

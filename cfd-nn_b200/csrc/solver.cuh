@@ -98,6 +98,8 @@ private:
     std::unique_ptr<Multigrid> mg_;
     NNClosure* nn_ = nullptr;
     bool ext_nut_ = false;
+    bool mom_z_ = true;                    // z-marching momentum kernel (env CFDNN_MOMENTUM_Z=0: one thread per point)
+    bool mom_exact_ = false;               // env CFDNN_MOMENTUM_EXACT=1: exact divisions on uniform 3-D meshes too
     Comm* comm_ = nullptr;
     cudaStream_t st_ = nullptr;
     cudaEvent_t ev0_ = nullptr, ev1_ = nullptr;
