@@ -15,7 +15,8 @@
 //     multiply-adds, 9 FP64 instructions per cell-sweep instead of 13 (22 with exact divisions).
 //     Each partial result is within 1 ulp of the reference's; FD = false keeps the reference's
 //     expression and rounding bit for bit;
-//   * the register prefetch of plane z+1 is issued right AFTER the first use of plane z.  ptxas puts
+//   * the register prefetch of plane z+1 is issued right AFTER the first use of plane z (pinned by an
+//     always-true predicate computed from the arriving data in an opaque asm).  ptxas puts
 //     all global loads of the loop on one hardware scoreboard, and a scoreboard wait covers every
 //     load outstanding on it: with the prefetch at the top of the iteration the wait for plane z
 //     also waited for plane z+1, i.e. the full DRAM latency was exposed once per plane (measured:
@@ -178,9 +179,19 @@ k_sweep_tbo(LevelGeom g, const double* __restrict__ u, const double* __restrict_
         // The prefetch must be issued AFTER the wait for the previous one: all global loads of the loop
         // share one hardware scoreboard, so a wait placed after the new loads also waits for those and
         // exposes the full DRAM latency every plane.  ptxas hoists independent loads freely, so the
-        // order is pinned by a data dependency: the loads are predicated on a value of the arriving
-        // plane being a number (always true for finite fields; a NaN field stays NaN either way).
-        const bool arrived = !(l0[A][0] != l0[A][0]);
+        // order is pinned by a data dependency that never changes what is loaded: the loads are predicated
+        // on (low word of an arriving value | 1) != 0, evaluated in an opaque asm so that ptxas can neither
+        // fold it nor move the loads above the arrival — true for every bit pattern, NaN included.
+        bool arrived;
+        {
+#ifndef CFDNN_DEVSIM
+            unsigned lw = (unsigned)__double2loint(l0[A][0]);
+            asm volatile("or.b32 %0, %0, 1;" : "+r"(lw));
+            arrived = lw != 0u;
+#else
+            arrived = true;
+#endif
+        }
         if (prefetch) {                                    // next iteration's planes
             if (arrived) {
                 load4(u, zoff_u, l0[N]);

@@ -13,7 +13,9 @@
 //     (each value is loaded from HBM once per plane, 4 loads per cell instead of 93);
 //   * the 31 in-plane neighbours the three face stencils need come from one shared-memory tile per
 //     field and plane (ring of 4 z slots, one __syncthreads per plane), addressed with constant offsets
-//     from three per-iteration slot registers;
+//     from three per-iteration slot registers; the global loads of plane k+2 (and of `in` on plane k+1) are
+//     issued before plane k is evaluated and published into the ring afterwards, so HBM latency hides
+//     behind the ~230 FP64 instructions of a cell;
 //   * the three face updates of a cell share every loaded value (43 distinct inputs in all);
 //   * EXACT = true keeps the reference's expression order and true divisions (correctly rounded fdiv):
 //     bit-identical to the x86 build — required on y-stretched meshes, whose Poisson solver amplifies a
@@ -99,7 +101,7 @@ struct MomShape {
 // SKEW: skew-symmetric (true) or central (false) convection.  Launch: grid (ceil((ex+1)/BX), ceil((ey+1)/BY), z chunks),
 // block BX*BY threads.  zc = planes per chunk.
 template <bool SKEW, bool EXACT, int BX, int BY>
-__global__ void __launch_bounds__(BX * BY)
+__global__ void __launch_bounds__(BX * BY, 2)
 k_momentum_z(Geom g, MomCoef c, Vel vel, const double* __restrict__ nu, Vel in, Vel out, int copy_ghosts, int zc) {
     using S = MomShape<BX, BY>;
     CFDNN_DYN_SMEM(double, sm);
@@ -140,32 +142,49 @@ k_momentum_z(Geom g, MomCoef c, Vel vel, const double* __restrict__ nu, Vel in, 
     const bool ix_f = i >= Ng && i <= Ng + g.Nx, iy_f = j >= Ng && j <= Ng + g.Ny;
     const bool int_u = ix_f && iy_c, int_v = ix_c && iy_f, int_w = ix_c && iy_c;     // and the k condition, per plane
 
-    // plane loader: K clamped per field; own value -> register + tile, halo value -> tile
-    double pu, pv, pw, pn;                                  // plane K+1 of the own column
-    auto load_plane = [&](int K, int slot) {
+    // plane loader, split in two so that a plane's global loads are in flight while the previous plane is
+    // evaluated: fetch() issues the loads of plane K (clamped per field) into registers, publish() stores them
+    // into the tile ring one iteration later.
+    double pu, pv, pw, pn;                                  // own column of the plane being fetched
+    double hu = 0.0, hv = 0.0, hw = 0.0, hn = 0.0;          // halo column (first NHALO threads)
+    auto fetch = [&](int K) {
         const int ku = min(max(K, 0), ez - 1), kw = min(max(K, 0), ez);
         const double* bu = vel.u + (size_t)ku * (size_t)g.up;
         const double* bv = vel.v + (size_t)ku * (size_t)g.vp;
         const double* bw = vel.w + (size_t)kw * (size_t)g.wp;
         const double* bn = nu + (size_t)ku * (size_t)g.cp;
         pu = bu[own_u]; pv = bv[own_v]; pw = bw[own_w]; pn = bn[own_n];
+        if (t_halo >= 0) { hu = bu[hal_u]; hv = bv[hal_v]; hw = bw[hal_w]; hn = bn[hal_n]; }
+    };
+    auto publish = [&](int slot) {
         double* t = sm + slot * PL;
         t[FU + t_own] = pu; t[FV + t_own] = pv; t[FW + t_own] = pw; t[FN + t_own] = pn;
-        if (t_halo >= 0) {
-            t[FU + t_halo] = bu[hal_u]; t[FV + t_halo] = bv[hal_v]; t[FW + t_halo] = bw[hal_w]; t[FN + t_halo] = bn[hal_n];
-        }
+        if (t_halo >= 0) { t[FU + t_halo] = hu; t[FV + t_halo] = hv; t[FW + t_halo] = hw; t[FN + t_halo] = hn; }
+    };
+    // `in` values of the faces this column owns on plane K (clamped; unused where the face is not interior)
+    double in_u = 0.0, in_v = 0.0, in_w = 0.0;
+    auto fetch_in = [&](int K, double& a, double& b, double& cc) {
+        const int ku = min(K, ez - 1), kw = min(K, ez);
+        if (int_u) a = in.u[(size_t)ku * (size_t)g.up + own_u];
+        if (int_v) b = in.v[(size_t)ku * (size_t)g.vp + own_v];
+        if (int_w) cc = in.w[(size_t)kw * (size_t)g.wp + own_w];
     };
 
-    // ---- prologue: planes k0-1 and k0
-    double um, vm, wm, nm, uc, vc, wc, nc;
-    load_plane(k0 - 1, (k0 - 1) & 3);
+    // ---- prologue: planes k0-1, k0 and k0+1 into the ring, `in` of plane k0
+    double um, vm, wm, nm, uc, vc, wc, nc, up_, vp_, wp_, np_;
+    fetch(k0 - 1); publish((k0 - 1) & 3);
     um = pu; vm = pv; wm = pw; nm = pn;
-    load_plane(k0, k0 & 3);
+    fetch(k0); publish(k0 & 3);
     uc = pu; vc = pv; wc = pw; nc = pn;
+    fetch(k0 + 1); publish((k0 + 1) & 3);
+    up_ = pu; vp_ = pv; wp_ = pw; np_ = pn;
+    fetch_in(k0, in_u, in_v, in_w);
+    __syncthreads();
 
     for (int K = k0; K < k1; ++K) {
-        load_plane(K + 1, (K + 1) & 3);                     // plane K+1 -> registers (pu..) and tile
-        __syncthreads();
+        fetch(K + 2);                                       // in flight during the evaluation of plane K
+        double niu = 0.0, niv = 0.0, niw = 0.0;
+        fetch_in(K + 1, niu, niv, niw);
         const double* tm = sm + ((K - 1) & 3) * PL + t_own;   // tiles of planes K-1, K, K+1 at the own column
         const double* tc = sm + (K & 3) * PL + t_own;
         const double* tp = sm + ((K + 1) & 3) * PL + t_own;
@@ -185,27 +204,27 @@ k_momentum_z(Geom g, MomCoef c, Vel vel, const double* __restrict__ nu, Vel in, 
                 // u face (i, j, K): x is the own direction
                 const double wp_w = tp[FW - 1];
                 const double vv = 0.25 * (v_w + vc + v_nw + v_n);
-                const double ww = 0.25 * (w_w + wc + wp_w + pw);
+                const double ww = 0.25 * (w_w + wc + wp_w + wp_);
                 double conv;
                 if (SKEW) {
                     const double sx = skew_own<EXACT>(uc, u_w, u_e, c.dx, c.dx_2, c.h_rdx, c.h_r2dx);
                     const double sy = skew_dir<EXACT>(vv, 0.5 * (v_w + vc), 0.5 * (v_nw + v_n), uc, u_s, u_n, c.dy, c.dy_2, c.h_rdy, c.h_r2dy);
-                    const double sz = skew_dir<EXACT>(ww, 0.5 * (w_w + wc), 0.5 * (wp_w + pw), uc, um, pu, c.dz, c.dz_2, c.h_rdz, c.h_r2dz);
+                    const double sz = skew_dir<EXACT>(ww, 0.5 * (w_w + wc), 0.5 * (wp_w + wp_), uc, um, up_, c.dz, c.dz_2, c.h_rdz, c.h_r2dz);
                     conv = sx + sy + sz;
                 } else {
                     conv = central_dir<EXACT>(uc, u_w, u_e, c.dx_2) + central_dir<EXACT>(vv, u_s, u_n, c.dy_2) +
-                           central_dir<EXACT>(ww, um, pu, c.dz_2);
+                           central_dir<EXACT>(ww, um, up_, c.dz_2);
                 }
                 const double nl = n_w, nr = nc;             // nu of the two cells adjacent in x
                 const double d2x = diff_dir<EXACT>(nl, nr, uc, u_w, u_e, c.dx2);
                 const double nu_n = 0.25 * (nl + nr + n_nw + n_n);
                 const double nu_s = 0.25 * (nl + nr + n_sw + n_s);
                 const double d2y = diff_dir<EXACT>(nu_s, nu_n, uc, u_s, u_n, c.dy2);
-                const double nu_f = 0.25 * (nl + nr + tp[FN - 1] + pn);
+                const double nu_f = 0.25 * (nl + nr + tp[FN - 1] + np_);
                 const double nu_b = 0.25 * (nl + nr + tm[FN - 1] + nm);
-                const double d2z = diff_dir<EXACT>(nu_b, nu_f, uc, um, pu, c.dz2);
+                const double d2z = diff_dir<EXACT>(nu_b, nu_f, uc, um, up_, c.dz2);
                 const double diff = d2x + d2y + d2z;
-                out.u[o] = mom_fma<EXACT>(c.dt, -conv + diff + c.fx, in.u[o]);
+                out.u[o] = mom_fma<EXACT>(c.dt, -conv + diff + c.fx, in_u);
             } else if (copy_ghosts) {
                 out.u[o] = uc;
             }
@@ -216,27 +235,27 @@ k_momentum_z(Geom g, MomCoef c, Vel vel, const double* __restrict__ nu, Vel in, 
                 // v face (i, j, K): y is the own direction
                 const double wp_s = tp[FW - TX];
                 const double uu = 0.25 * (u_s + u_se + uc + u_e);
-                const double ww = 0.25 * (w_s + wc + wp_s + pw);
+                const double ww = 0.25 * (w_s + wc + wp_s + wp_);
                 double conv;
                 if (SKEW) {
                     const double sx = skew_dir<EXACT>(uu, 0.5 * (u_s + uc), 0.5 * (u_se + u_e), vc, v_w, v_e, c.dx, c.dx_2, c.h_rdx, c.h_r2dx);
                     const double sy = skew_own<EXACT>(vc, v_s, v_n, c.dy, c.dy_2, c.h_rdy, c.h_r2dy);
-                    const double sz = skew_dir<EXACT>(ww, 0.5 * (w_s + wc), 0.5 * (wp_s + pw), vc, vm, pv, c.dz, c.dz_2, c.h_rdz, c.h_r2dz);
+                    const double sz = skew_dir<EXACT>(ww, 0.5 * (w_s + wc), 0.5 * (wp_s + wp_), vc, vm, vp_, c.dz, c.dz_2, c.h_rdz, c.h_r2dz);
                     conv = sx + sy + sz;
                 } else {
                     conv = central_dir<EXACT>(uu, v_w, v_e, c.dx_2) + central_dir<EXACT>(vc, v_s, v_n, c.dy_2) +
-                           central_dir<EXACT>(ww, vm, pv, c.dz_2);
+                           central_dir<EXACT>(ww, vm, vp_, c.dz_2);
                 }
                 const double nb = n_s, nt = nc;             // nu of the two cells adjacent in y
                 const double nu_e = 0.25 * (nb + nt + n_se + n_e);
                 const double nu_w = 0.25 * (nb + nt + n_sw + n_w);
                 const double d2x = diff_dir<EXACT>(nu_w, nu_e, vc, v_w, v_e, c.dx2);
                 const double d2y = diff_dir<EXACT>(nb, nt, vc, v_s, v_n, c.dy2);
-                const double nu_f = 0.25 * (nb + nt + tp[FN - TX] + pn);
+                const double nu_f = 0.25 * (nb + nt + tp[FN - TX] + np_);
                 const double nu_b = 0.25 * (nb + nt + tm[FN - TX] + nm);
-                const double d2z = diff_dir<EXACT>(nu_b, nu_f, vc, vm, pv, c.dz2);
+                const double d2z = diff_dir<EXACT>(nu_b, nu_f, vc, vm, vp_, c.dz2);
                 const double diff = d2x + d2y + d2z;
-                out.v[o] = mom_fma<EXACT>(c.dt, -conv + diff + c.fy, in.v[o]);
+                out.v[o] = mom_fma<EXACT>(c.dt, -conv + diff + c.fy, in_v);
             } else if (copy_ghosts) {
                 out.v[o] = vc;
             }
@@ -252,11 +271,11 @@ k_momentum_z(Geom g, MomCoef c, Vel vel, const double* __restrict__ nu, Vel in, 
                 if (SKEW) {
                     const double sx = skew_dir<EXACT>(uu, 0.5 * (um + uc), 0.5 * (um_e + u_e), wc, w_w, w_e, c.dx, c.dx_2, c.h_rdx, c.h_r2dx);
                     const double sy = skew_dir<EXACT>(vv, 0.5 * (vm + vc), 0.5 * (vm_n + v_n), wc, w_s, w_n, c.dy, c.dy_2, c.h_rdy, c.h_r2dy);
-                    const double sz = skew_own<EXACT>(wc, wm, pw, c.dz, c.dz_2, c.h_rdz, c.h_r2dz);
+                    const double sz = skew_own<EXACT>(wc, wm, wp_, c.dz, c.dz_2, c.h_rdz, c.h_r2dz);
                     conv = sx + sy + sz;
                 } else {
                     conv = central_dir<EXACT>(uu, w_w, w_e, c.dx_2) + central_dir<EXACT>(vv, w_s, w_n, c.dy_2) +
-                           central_dir<EXACT>(wc, wm, pw, c.dz_2);
+                           central_dir<EXACT>(wc, wm, wp_, c.dz_2);
                 }
                 const double nbk = nm, nfr = nc;            // nu of the two cells adjacent in z
                 const double nu_e = 0.25 * (nbk + nfr + tm[FN + 1] + n_e);
@@ -265,15 +284,19 @@ k_momentum_z(Geom g, MomCoef c, Vel vel, const double* __restrict__ nu, Vel in, 
                 const double nu_n = 0.25 * (nbk + nfr + tm[FN + TX] + n_n);
                 const double nu_s = 0.25 * (nbk + nfr + tm[FN - TX] + n_s);
                 const double d2y = diff_dir<EXACT>(nu_s, nu_n, wc, w_s, w_n, c.dy2);
-                const double d2z = diff_dir<EXACT>(nbk, nfr, wc, wm, pw, c.dz2);
+                const double d2z = diff_dir<EXACT>(nbk, nfr, wc, wm, wp_, c.dz2);
                 const double diff = d2x + d2y + d2z;
-                out.w[o] = mom_fma<EXACT>(c.dt, -conv + diff + c.fz, in.w[o]);
+                out.w[o] = mom_fma<EXACT>(c.dt, -conv + diff + c.fz, in_w);
             } else if (copy_ghosts) {
                 out.w[o] = wc;
             }
         }
+        publish((K + 2) & 3);                               // slot last read as plane K-2: free since the previous barrier
+        __syncthreads();
         um = uc; vm = vc; wm = wc; nm = nc;
-        uc = pu; vc = pv; wc = pw; nc = pn;
+        uc = up_; vc = vp_; wc = wp_; nc = np_;
+        up_ = pu; vp_ = pv; wp_ = pw; np_ = pn;
+        in_u = niu; in_v = niv; in_w = niw;
     }
 }
 

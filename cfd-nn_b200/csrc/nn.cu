@@ -297,32 +297,34 @@ __device__ __forceinline__ double act_mma(double s, int act) {
 // 1/32 of an octave, exp = 2^m * 2^(j/32) * P4(r) with 2^(j/32) from a 32-entry shared-memory table (stored 16 times
 // so that the lanes of a half-warp read 16 different banks whatever j they need) and a degree-4 polynomial on
 // |r| <= ln2/64; |x| is clamped, the 2^m scaling, the sign and the NaN test are integer operations on the high word;
-// one Newton step on the 20-bit reciprocal seed.  14 FP64 instructions instead of 26; absolute error <= 1e-12.
+// one Newton step on the 20-bit reciprocal seed.  12 FP64 instructions instead of 26; absolute error <= 1e-12.
 constexpr int TANH_TAB_DOUBLES = 32 * 16;
 __device__ __forceinline__ double tanh_tab(double x, const double* __restrict__ tab /* + (lane & 15) */) {
     const int hx = __double2hiint(x);
     const int habs = hx & 0x7fffffff;
     const int hcl = min(habs, 0x40340000);                          // |x| clamped just above 20: tanh = 1 - 8e-18 there
     const double ax = __hiloint2double(hcl, __double2loint(x));
-    const double y = -2.0 * ax;
     const double MAGIC = 6755399441055744.0;                        // 1.5 * 2^52
-    double fn = __fma_rn(y, 46.16624130844683, MAGIC);              // 32 / ln2
-    const int n = __double2loint(fn);                               // round(32 y / ln2) in [-1847, 0]
+    double fn = __fma_rn(ax, -92.33248261689366, MAGIC);            // n = round(-2|x| * 32 / ln2) in [-1847, 0]
+    const int n = __double2loint(fn);
     fn = fn - MAGIC;
-    const double r = __fma_rn(fn, -0.02166084939249829, y);         // ln2 / 32
-    double p = __fma_rn(r, 4.1666666666666664e-02, 1.6666666666666666e-01);
-    p = __fma_rn(p, r, 0.5);
-    p = __fma_rn(p, r, 1.0);
-    p = __fma_rn(p, r, 1.0);
+    // -2|x| = n ln2/32 + r, |r| <= ln2/64; the polynomial is written in s = -r/2 = |x| + n ln2/64 so that the
+    // product -2|x| never has to be formed: exp(r) = 1 - 2s + 2s^2 - 4/3 s^3 + 2/3 s^4
+    const double sr = __fma_rn(fn, 0.010830424696249145, ax);       // ln2 / 64
+    double p = __fma_rn(sr, 6.6666666666666663e-01, -1.3333333333333333e+00);
+    p = __fma_rn(p, sr, 2.0);
+    p = __fma_rn(p, sr, -2.0);
+    p = __fma_rn(p, sr, 1.0);
+    // -2 * 2^(n/32): table value with the exponent moved by m + 1 and the sign bit set (integer pipe)
     const double T = tab[(n & 31) * 16];
-    const double Ts = __hiloint2double(__double2hiint(T) + ((n >> 5) << 20), __double2loint(T));   // 2^(n/32), exponent >= -58
-    const double t = Ts * p;
-    const double num = 1.0 - t, den = 1.0 + t;                      // den in [1, 2]
+    const double Tm2 = __hiloint2double((__double2hiint(T) + (((n >> 5) + 1) << 20)) | 0x80000000, __double2loint(T));
+    const double tm2 = Tm2 * p;                                     // -2 t,  t = exp(-2|x|)
+    const double den = __fma_rn(tm2, -0.5, 1.0);                    // 1 + t in [1, 2]
     double rc;
     asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(rc) : "d"(den));
     const double e = __fma_rn(-den, rc, 1.0);
     rc = __fma_rn(rc, e, rc);
-    const double q = num * rc;
+    const double q = __fma_rn(tm2, rc, 1.0);                        // (1 - t) / (1 + t) = 1 - 2t / (1 + t)
     const double qs = __hiloint2double(__double2hiint(q) | (hx & 0x80000000), __double2loint(q));
     return habs > 0x7ff00000 ? x : qs;                              // NaN in -> NaN out; +-inf -> +-1
 }

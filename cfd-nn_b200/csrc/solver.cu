@@ -12,6 +12,7 @@
 namespace cfdnn {
 
 static const dim3 kB(64, 4, 1);
+constexpr int MOM_BX = 32, MOM_BY = 8;      // tile of the z-marching momentum kernel (momentum_kernels.cuh)
 static inline dim3 grid3(int nx, int ny, int nz) {
     return dim3((nx + kB.x - 1) / kB.x, (ny + kB.y - 1) / kB.y, nz);
 }
@@ -98,11 +99,11 @@ Solver::Solver(const cfdnn_mesh_desc& m, const cfdnn_config& c) : mesh_(m), cfg_
     if (const char* e = std::getenv("CFDNN_MOMENTUM_Z")) mom_z_ = std::atoi(e) != 0;          // 0: one-thread-per-point kernel
     if (const char* e = std::getenv("CFDNN_MOMENTUM_EXACT")) mom_exact_ = std::atoi(e) != 0;  // 1: exact divisions everywhere
     {
-        using S = MomShape<64, 4>;
-        CFDNN_CUDA(cudaFuncSetAttribute(k_momentum_z<true, true, 64, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::SMEM));
-        CFDNN_CUDA(cudaFuncSetAttribute(k_momentum_z<true, false, 64, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::SMEM));
-        CFDNN_CUDA(cudaFuncSetAttribute(k_momentum_z<false, true, 64, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::SMEM));
-        CFDNN_CUDA(cudaFuncSetAttribute(k_momentum_z<false, false, 64, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::SMEM));
+        using S = MomShape<MOM_BX, MOM_BY>;
+        CFDNN_CUDA(cudaFuncSetAttribute(k_momentum_z<true, true, MOM_BX, MOM_BY>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::SMEM));
+        CFDNN_CUDA(cudaFuncSetAttribute(k_momentum_z<true, false, MOM_BX, MOM_BY>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::SMEM));
+        CFDNN_CUDA(cudaFuncSetAttribute(k_momentum_z<false, true, MOM_BX, MOM_BY>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::SMEM));
+        CFDNN_CUDA(cudaFuncSetAttribute(k_momentum_z<false, false, MOM_BX, MOM_BY>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::SMEM));
     }
     dt_ = c.dt;
     set_velocity_bc(vbc_);
@@ -146,6 +147,23 @@ void Solver::set_velocity_bc(const int bc[6]) {
 }
 
 void Solver::comm_init(Comm* c) {
+    if (c && c->nranks > 1) {
+        // The slab layout is block distribution with EQUAL slabs (reference Decomposition::nz_for_rank with
+        // Nz_global % nprocs == 0, include/decomposition.hpp:81-92): the coarse-level offsets (rank * Nz / 2),
+        // the in-place all-gather of the agglomerated level and the 2:1 vertex-aligned z coarsening all rely on it.
+        // A remainder (ranks owning Nz_global / P + 1 planes) is rejected here instead of giving wrong coarse
+        // right-hand sides.
+        const int NzG = mesh_.Nz_global, Nz = g_.Nz;
+        if (NzG <= Nz)
+            throw std::invalid_argument("comm_init: mesh.Nz_global must be the global plane count (> local Nz) in a multi-rank run");
+        if ((long long)Nz * c->nranks != NzG)
+            throw std::invalid_argument("comm_init: unequal z-slabs are not supported (need Nz_global == Nz_local * nranks; "
+                                        "Nz_global = " + std::to_string(NzG) + ", Nz_local = " + std::to_string(Nz) +
+                                        ", nranks = " + std::to_string(c->nranks) + ")");
+        if (mesh_.k_offset != c->rank * Nz)
+            throw std::invalid_argument("comm_init: mesh.k_offset must be rank * Nz_local (" + std::to_string(c->rank * Nz) +
+                                        "), got " + std::to_string(mesh_.k_offset));
+    }
     comm_ = c;
     mg_->set_comm(c);
     update_links();
@@ -351,7 +369,7 @@ void Solver::momentum(const Vel& in, Vel& out, double dt, bool seam_average) {
         // z-marching tile kernel (momentum_kernels.cuh).  Exact divisions + unfused products wherever the result
         // must carry the x86 build's bits: y-stretched meshes (their Poisson solver amplifies a last-bit change)
         // and the 2-D embedding; reciprocal multiplies + FMA on uniform 3-D meshes.
-        constexpr int BX = 64, BY = 4;
+        constexpr int BX = MOM_BX, BY = MOM_BY;
         using S = MomShape<BX, BY>;
         MomCoef c{};
         c.dx = g_.dx; c.dy = g_.dy; c.dz = g_.dz; c.dx_2 = g_.dx_2; c.dy_2 = g_.dy_2; c.dz_2 = g_.dz_2;
@@ -477,6 +495,10 @@ void Solver::euler_substep(const Vel& in, Vel& out, double dt) {
 void Solver::project_velocity(Vel* which, double dt) {
     const bool need_swap = which != &vel_;
     if (need_swap) std::swap(vel_, *which);
+    struct SwapBack {                                // an exception mid-projection must not leave the buffers swapped
+        Vel* a; Vel* b; bool on;
+        ~SwapBack() { if (on) std::swap(*a, *b); }
+    } guard{&vel_, which, need_swap};
     apply_velocity_bc();
     // the RK path's inline 2-D divergence divides by the UNIFORM dy even on a y-stretched mesh
     // (src/solver_time.cpp:789-806; the 3-D branch and the Euler path use dyv[j]) — reproduced as is
@@ -490,7 +512,6 @@ void Solver::project_velocity(Vel* which, double dt) {
     poisson_solve(pc);
     copy_correct_velocity();                       // velocity_ -> velocity_star_ (interior) :972-995, then correct
     apply_velocity_bc();
-    if (need_swap) std::swap(vel_, *which);
 }
 
 void Solver::ssprk3_step(double dt) {              // src/solver_time.cpp:1303-1513

@@ -669,4 +669,8 @@ k_nonfinite(const double* __restrict__ a, size_t n, int* __restrict__ flag) {
     if (bad) *flag = 1;
 }
 
+static __global__ void k_flag_to_double(const int* __restrict__ flag, double* __restrict__ out) {
+    out[0] = flag[0] ? 1.0 : 0.0;
+}
+
 }  // namespace cfdnn
