@@ -28,6 +28,7 @@
 // buffer that is then swapped with vel, see Solver::momentum).
 #pragma once
 #include "solver.cuh"
+#include <type_traits>
 
 namespace cfdnn {
 
@@ -142,12 +143,15 @@ k_momentum_z(Geom g, MomCoef c, Vel vel, const double* __restrict__ nu, Vel in, 
     const bool ix_f = i >= Ng && i <= Ng + g.Nx, iy_f = j >= Ng && j <= Ng + g.Ny;
     const bool int_u = ix_f && iy_c, int_v = ix_c && iy_f, int_w = ix_c && iy_c;     // and the k condition, per plane
 
-    // plane loader, split in two so that a plane's global loads are in flight while the previous plane is
-    // evaluated: fetch() issues the loads of plane K (clamped per field) into registers, publish() stores them
-    // into the tile ring one iteration later.
-    double pu, pv, pw, pn;                                  // own column of the plane being fetched
+    // Own-column planes live in register rings of 4 slots (slot = (plane - k0 + 1) & 3, the same numbering as the
+    // shared-memory ring); the z loop is unrolled by 4 so that every slot index is a compile-time constant: no
+    // register moves between iterations (a move of a just-prefetched value would stall on its load) and constant
+    // shared-memory offsets.  fetch() issues the global loads of a plane (clamped per field) into a ring slot and the
+    // halo registers; publish() stores them into the tile ring one evaluation later.
+    double RU[4], RV[4], RW[4], RN[4];
     double hu = 0.0, hv = 0.0, hw = 0.0, hn = 0.0;          // halo column (first NHALO threads)
-    auto fetch = [&](int K) {
+    double INU[2] = {0.0, 0.0}, INV[2] = {0.0, 0.0}, INW[2] = {0.0, 0.0};   // `in` of the own faces, planes K / K+1
+    auto fetch = [&](int K, double& pu, double& pv, double& pw, double& pn) {
         const int ku = min(max(K, 0), ez - 1), kw = min(max(K, 0), ez);
         const double* bu = vel.u + (size_t)ku * (size_t)g.up;
         const double* bv = vel.v + (size_t)ku * (size_t)g.vp;
@@ -156,38 +160,38 @@ k_momentum_z(Geom g, MomCoef c, Vel vel, const double* __restrict__ nu, Vel in, 
         pu = bu[own_u]; pv = bv[own_v]; pw = bw[own_w]; pn = bn[own_n];
         if (t_halo >= 0) { hu = bu[hal_u]; hv = bv[hal_v]; hw = bw[hal_w]; hn = bn[hal_n]; }
     };
-    auto publish = [&](int slot) {
+    auto publish = [&](int slot, double pu, double pv, double pw, double pn) {
         double* t = sm + slot * PL;
         t[FU + t_own] = pu; t[FV + t_own] = pv; t[FW + t_own] = pw; t[FN + t_own] = pn;
         if (t_halo >= 0) { t[FU + t_halo] = hu; t[FV + t_halo] = hv; t[FW + t_halo] = hw; t[FN + t_halo] = hn; }
     };
-    // `in` values of the faces this column owns on plane K (clamped; unused where the face is not interior)
-    double in_u = 0.0, in_v = 0.0, in_w = 0.0;
-    auto fetch_in = [&](int K, double& a, double& b, double& cc) {
+    auto fetch_in = [&](int K, double& a, double& b, double& cc) {       // clamped; unused where the face is not interior
         const int ku = min(K, ez - 1), kw = min(K, ez);
         if (int_u) a = in.u[(size_t)ku * (size_t)g.up + own_u];
         if (int_v) b = in.v[(size_t)ku * (size_t)g.vp + own_v];
         if (int_w) cc = in.w[(size_t)kw * (size_t)g.wp + own_w];
     };
 
-    // ---- prologue: planes k0-1, k0 and k0+1 into the ring, `in` of plane k0
-    double um, vm, wm, nm, uc, vc, wc, nc, up_, vp_, wp_, np_;
-    fetch(k0 - 1); publish((k0 - 1) & 3);
-    um = pu; vm = pv; wm = pw; nm = pn;
-    fetch(k0); publish(k0 & 3);
-    uc = pu; vc = pv; wc = pw; nc = pn;
-    fetch(k0 + 1); publish((k0 + 1) & 3);
-    up_ = pu; vp_ = pv; wp_ = pw; np_ = pn;
-    fetch_in(k0, in_u, in_v, in_w);
+    // ---- prologue: planes k0-1, k0, k0+1 into slots 0, 1, 2; `in` of plane k0
+    fetch(k0 - 1, RU[0], RV[0], RW[0], RN[0]); publish(0, RU[0], RV[0], RW[0], RN[0]);
+    fetch(k0, RU[1], RV[1], RW[1], RN[1]); publish(1, RU[1], RV[1], RW[1], RN[1]);
+    fetch(k0 + 1, RU[2], RV[2], RW[2], RN[2]); publish(2, RU[2], RV[2], RW[2], RN[2]);
+    fetch_in(k0, INU[0], INV[0], INW[0]);
     __syncthreads();
 
-    for (int K = k0; K < k1; ++K) {
-        fetch(K + 2);                                       // in flight during the evaluation of plane K
-        double niu = 0.0, niv = 0.0, niw = 0.0;
-        fetch_in(K + 1, niu, niv, niw);
-        const double* tm = sm + ((K - 1) & 3) * PL + t_own;   // tiles of planes K-1, K, K+1 at the own column
-        const double* tc = sm + (K & 3) * PL + t_own;
-        const double* tp = sm + ((K + 1) & 3) * PL + t_own;
+    auto step = [&](auto AA, const int K) {
+        constexpr int A = decltype(AA)::value;
+        constexpr int SM_ = A, SC = (A + 1) & 3, SP = (A + 2) & 3, SN = (A + 3) & 3;   // planes K-1, K, K+1, K+2
+        constexpr int IC = A & 1, IN_ = (A + 1) & 1;
+        fetch(K + 2, RU[SN], RV[SN], RW[SN], RN[SN]);       // in flight during the evaluation of plane K
+        fetch_in(K + 1, INU[IN_], INV[IN_], INW[IN_]);
+        const double um = RU[SM_], vm = RV[SM_], wm = RW[SM_], nm = RN[SM_];
+        const double uc = RU[SC], vc = RV[SC], wc = RW[SC], nc = RN[SC];
+        const double up_ = RU[SP], vp_ = RV[SP], wp_ = RW[SP], np_ = RN[SP];
+        const double in_u = INU[IC], in_v = INV[IC], in_w = INW[IC];
+        const double* tm = sm + SM_ * PL + t_own;           // tiles of planes K-1, K, K+1 at the own column
+        const double* tc = sm + SC * PL + t_own;
+        const double* tp = sm + SP * PL + t_own;
         const bool kz_c = K >= Ng && K < Ng + g.Nz, kz_f = K >= Ng && K <= Ng + g.Nz;
         const bool kin = K < ez;                            // u, v entries exist on planes < ez; w on planes <= ez
 
@@ -291,12 +295,17 @@ k_momentum_z(Geom g, MomCoef c, Vel vel, const double* __restrict__ nu, Vel in, 
                 out.w[o] = wc;
             }
         }
-        publish((K + 2) & 3);                               // slot last read as plane K-2: free since the previous barrier
+        publish(SN, RU[SN], RV[SN], RW[SN], RN[SN]);       // slot last read as plane K-2: free since the previous barrier
         __syncthreads();
-        um = uc; vm = vc; wm = wc; nm = nc;
-        uc = up_; vc = vp_; wc = wp_; nc = np_;
-        up_ = pu; vp_ = pv; wp_ = pw; np_ = pn;
-        in_u = niu; in_v = niv; in_w = niw;
+    };
+    for (int K = k0; K < k1; K += 4) {
+        step(std::integral_constant<int, 0>{}, K);
+        if (K + 1 >= k1) break;
+        step(std::integral_constant<int, 1>{}, K + 1);
+        if (K + 2 >= k1) break;
+        step(std::integral_constant<int, 2>{}, K + 2);
+        if (K + 3 >= k1) break;
+        step(std::integral_constant<int, 3>{}, K + 3);
     }
 }
 

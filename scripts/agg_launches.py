@@ -6,7 +6,8 @@ import collections
 import csv
 import sys
 
-lines = open(sys.argv[1]).read().splitlines()
+import gzip
+lines = (gzip.open(sys.argv[1], "rt") if sys.argv[1].endswith(".gz") else open(sys.argv[1])).read().splitlines()
 start = next(i for i, l in enumerate(lines) if l.startswith('"ID"'))
 rows = list(csv.DictReader(lines[start:]))
 ids = sorted({int(r["ID"]) for r in rows})
