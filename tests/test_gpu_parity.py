@@ -176,6 +176,15 @@ def test_stretched_channel_48x32x48_rk3_16_cycles(gpu, oracle):
     print("chan48 errors", err, "reference sensitivity to 1e-15 input noise", sens)
 
 
+def test_stretched_channel_96x48x96_rk3_16_cycles(gpu, oracle):
+    """BASELINE config 3 at half resolution (192x96x192 costs the single-threaded oracle ~2 min per step): tanh
+    beta = 2 channel, RK3, skew-symmetric, 16 fixed V-cycles of the semi-coarsening solver.  Gate: the reference's
+    own sensitivity to 1e-15 input noise (BASELINE.md "config 3 gate"), floor 1e-10."""
+    case = ("chan96", (96, 48, 96), "PPWWPP", "rk3", "skew", 16, 1, "pchan", (1.0, 0, 0), dict(**cases.CHANNEL_BOX))
+    err, sens = cases.check_step_within_reference_sensitivity(gpu, oracle, case)
+    print("chan96 errors", err, "reference sensitivity to 1e-15 input noise", sens)
+
+
 # ---- 2-D meshes (Nz == 1; BASELINE config 1): 2-D multigrid + the solver's periodic-z-plane embedding
 @pytest.mark.parametrize("case", cases.MG_2D_CASES, ids=[c[0] for c in cases.MG_2D_CASES])
 def test_mg_2d_matches_reference(gpu, oracle, case):
