@@ -1,6 +1,7 @@
 // mg.cu — host orchestration of the multigrid V-cycle (see mg.cuh for the layout).
 #include "mg_kernels.cuh"
 #include "mg_tbo_kernels.cuh"
+#include "mg_tbq_kernels.cuh"
 #include "mg_rr_kernels.cuh"
 #include "comm.cuh"
 #include <cstdlib>
@@ -223,6 +224,12 @@ void tbo_launch(const LevelGeom& g, const double* in, const double* f, double* o
     const int nch = (int)grid.z;
     if (part == 1) { zoff = 1; grid.z = nch - 2; }
     else if (part == 2) { zstep = nch - 1; grid.z = 2; }
+    if (mode == 3) {      // 2 x 2 patch per thread (mg_tbq_kernels.cuh): the product path
+        using Q = TbqShape<BX, BY>;
+        if (g.fastdiv) CFDNN_LAUNCH_COOP((k_sweep_tbq<BX, BY, true>), grid, Q::NTHREADS, Q::SMEM, st, g, in, f, out, om, ZC, zoff, zstep);
+        else CFDNN_LAUNCH_COOP((k_sweep_tbq<BX, BY, false>), grid, Q::NTHREADS, Q::SMEM, st, g, in, f, out, om, ZC, zoff, zstep);
+        return;
+    }
     if (!g.fastdiv) {
         CFDNN_LAUNCH_COOP((k_sweep_tbo<BX, BY, false, TBO_MODE>), grid, S::NTHREADS, S::SMEM, st, g, in, f, out, om, ZC, zoff, zstep);
     } else if (mode == 0) {
@@ -251,6 +258,9 @@ void tbo_attr() {
     CFDNN_CUDA(cudaFuncSetAttribute(k_sweep_tbo<BX, BY, true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::SMEM));
     CFDNN_CUDA(cudaFuncSetAttribute(k_sweep_tbo<BX, BY, true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::SMEM));
     CFDNN_CUDA(cudaFuncSetAttribute(k_sweep_tbo<BX, BY, false, TBO_MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::SMEM));
+    using Q = TbqShape<BX, BY>;
+    CFDNN_CUDA(cudaFuncSetAttribute(k_sweep_tbq<BX, BY, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Q::SMEM));
+    CFDNN_CUDA(cudaFuncSetAttribute(k_sweep_tbq<BX, BY, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Q::SMEM));
 }
 }  // namespace
 
@@ -273,7 +283,7 @@ void Multigrid::tb_setup() {
     if (const char* e = std::getenv("CFDNN_MG_NORMS_TB")) norms_tb_ = std::atoi(e) != 0;
     if (const char* e = std::getenv("CFDNN_MG_RR")) rr_ = std::atoi(e) != 0;
     if (const char* e = std::getenv("CFDNN_MG_RR_MIN")) rr_min_ = std::max(8, std::atoi(e));
-    if (const char* e = std::getenv("CFDNN_MG_TBO_MODE")) tbo_mode_ = std::max(0, std::min(2, std::atoi(e)));
+    if (const char* e = std::getenv("CFDNN_MG_TBO_MODE")) tbo_mode_ = std::max(0, std::min(3, std::atoi(e)));
 }
 
 // n (<= 2) sweeps in one pass (w != nullptr), or the tiled residual r = f - L u (w == nullptr, n = 1);

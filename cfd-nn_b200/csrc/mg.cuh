@@ -129,7 +129,8 @@ private:
     void tb_setup();
     bool sweeps_tb(int level, const double* in, double* out, const double* w, int n);
     int tb_max_ = 2;                // sweeps fused per pass (env CFDNN_MG_TB: 0 = plain k_sweep only)
-    int tbo_mode_ = 2;              // k_sweep_tbo variant (env CFDNN_MG_TBO_MODE, see mg_tbo_kernels.cuh)
+    int tbo_mode_ = 3;              // lean smoother variant (env CFDNN_MG_TBO_MODE): 3 = k_sweep_tbq (2 x 2 patch per thread,
+                                    // mg_tbq_kernels.cuh), 0-2 = the barrier variants of k_sweep_tbo (mg_tbo_kernels.cuh)
     bool tbo_ = true;               // lean kernel on levels without physical faces in reach (env CFDNN_MG_TBO=0: general kernel)
     void residual(int level);
     void residual_norms(int level, double* d_max, double* d_sumsq);

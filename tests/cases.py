@@ -465,24 +465,29 @@ def check_step_2d_with_tbnn(B, oracle, tol=1e-9, nut_tol=1e-6):
 
 
 def check_smoother_variants_bitwise(B, monkeypatch, N=(32, 32, 32), cycles=2):
-    """With exact divisions (CFDNN_MG_FASTDIV=0) the blocked kernels — the lean one for levels without
-    physical faces (k_sweep_tbo) and the general one (k_sweep_tb) — reproduce the one-sweep kernel bit
-    for bit; with reciprocal multiplies (default) the lean kernel's fused multiply-adds stay within
-    1e-13 of it."""
+    """With exact divisions (CFDNN_MG_FASTDIV=0) the blocked kernels — the lean ones for levels without
+    physical faces (k_sweep_tbq, the product path, and k_sweep_tbo) and the general one (k_sweep_tb) — reproduce
+    the one-sweep kernel bit for bit; with reciprocal multiplies (default) the lean kernels' fused multiply-adds
+    stay within 1e-13 of it and agree with each other bit for bit."""
     case = ("per_variants", N, "PPPPPP", cycles, {})
     out = {}
+    keys = ("CFDNN_MG_FASTDIV", "CFDNN_MG_TB", "CFDNN_MG_TBO", "CFDNN_MG_TBO_MODE")
     for tag, env in (("plain", dict(CFDNN_MG_FASTDIV="0", CFDNN_MG_TB="0")),
                      ("tb", dict(CFDNN_MG_FASTDIV="0", CFDNN_MG_TB="2", CFDNN_MG_TBO="0")),
-                     ("tbo", dict(CFDNN_MG_FASTDIV="0", CFDNN_MG_TB="2", CFDNN_MG_TBO="1")),
-                     ("tbo_fd", dict(CFDNN_MG_FASTDIV="1", CFDNN_MG_TB="2", CFDNN_MG_TBO="1"))):
-        for k in ("CFDNN_MG_FASTDIV", "CFDNN_MG_TB", "CFDNN_MG_TBO"):
+                     ("tbo", dict(CFDNN_MG_FASTDIV="0", CFDNN_MG_TB="2", CFDNN_MG_TBO="1", CFDNN_MG_TBO_MODE="2")),
+                     ("tbq", dict(CFDNN_MG_FASTDIV="0", CFDNN_MG_TB="2", CFDNN_MG_TBO="1", CFDNN_MG_TBO_MODE="3")),
+                     ("tbo_fd", dict(CFDNN_MG_FASTDIV="1", CFDNN_MG_TB="2", CFDNN_MG_TBO="1", CFDNN_MG_TBO_MODE="2")),
+                     ("tbq_fd", dict(CFDNN_MG_FASTDIV="1", CFDNN_MG_TB="2", CFDNN_MG_TBO="1", CFDNN_MG_TBO_MODE="3"))):
+        for k in keys:
             monkeypatch.delenv(k, raising=False)
         for k, v in env.items():
             monkeypatch.setenv(k, v)
         _, out[tag] = run_mg_backend(B, case)
     assert np.array_equal(out["plain"], out["tb"])
     assert np.array_equal(out["plain"], out["tbo"])
-    d = np.linalg.norm(out["tbo_fd"] - out["plain"]) / np.linalg.norm(out["plain"])
+    assert np.array_equal(out["plain"], out["tbq"])          # 2 x 2 patch kernel, exact divisions
+    assert np.array_equal(out["tbo_fd"], out["tbq_fd"])      # ... and with reciprocal multiplies + FMA: same expression
+    d = np.linalg.norm(out["tbq_fd"] - out["plain"]) / np.linalg.norm(out["plain"])
     assert 0 < d <= 1e-13, d
 
 
