@@ -224,7 +224,24 @@ void tbo_launch(const LevelGeom& g, const double* in, const double* f, double* o
     const int nch = (int)grid.z;
     if (part == 1) { zoff = 1; grid.z = nch - 2; }
     else if (part == 2) { zstep = nch - 1; grid.z = 2; }
-    if (mode == 3) {      // 2 x 2 patch per thread (mg_tbq_kernels.cuh): the product path
+#ifndef CFDNN_DEVSIM
+    if (mode == 4 || mode == 5) {      // 2 x 2 patch per thread, level-0 planes through the TMA unit (k_sweep_tbx)
+        using Q = TbqShape<BX, BY>;
+        if (mode == 4) {
+            using X = TbxShape<BX, BY, 4>;
+            if (g.fastdiv) CFDNN_LAUNCH_COOP((k_sweep_tbx<BX, BY, true, 4>), grid, Q::NTHREADS, X::SMEM, st, g, in, f, out, om, ZC, zoff, zstep);
+            else CFDNN_LAUNCH_COOP((k_sweep_tbx<BX, BY, false, 4>), grid, Q::NTHREADS, X::SMEM, st, g, in, f, out, om, ZC, zoff, zstep);
+        } else {
+            using X = TbxShape<BX, BY, 5>;
+            if (g.fastdiv) CFDNN_LAUNCH_COOP((k_sweep_tbx<BX, BY, true, 5>), grid, Q::NTHREADS, X::SMEM, st, g, in, f, out, om, ZC, zoff, zstep);
+            else CFDNN_LAUNCH_COOP((k_sweep_tbx<BX, BY, false, 5>), grid, Q::NTHREADS, X::SMEM, st, g, in, f, out, om, ZC, zoff, zstep);
+        }
+        return;
+    }
+#else
+    if (mode > 3) mode = 3;            // the CPU test double has no TMA: same arithmetic through k_sweep_tbq
+#endif
+    if (mode == 3) {      // 2 x 2 patch per thread (mg_tbq_kernels.cuh)
         using Q = TbqShape<BX, BY>;
         if (g.fastdiv) CFDNN_LAUNCH_COOP((k_sweep_tbq<BX, BY, true>), grid, Q::NTHREADS, Q::SMEM, st, g, in, f, out, om, ZC, zoff, zstep);
         else CFDNN_LAUNCH_COOP((k_sweep_tbq<BX, BY, false>), grid, Q::NTHREADS, Q::SMEM, st, g, in, f, out, om, ZC, zoff, zstep);
@@ -261,6 +278,12 @@ void tbo_attr() {
     using Q = TbqShape<BX, BY>;
     CFDNN_CUDA(cudaFuncSetAttribute(k_sweep_tbq<BX, BY, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Q::SMEM));
     CFDNN_CUDA(cudaFuncSetAttribute(k_sweep_tbq<BX, BY, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Q::SMEM));
+#ifndef CFDNN_DEVSIM
+    CFDNN_CUDA(cudaFuncSetAttribute(k_sweep_tbx<BX, BY, true, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TbxShape<BX, BY, 4>::SMEM));
+    CFDNN_CUDA(cudaFuncSetAttribute(k_sweep_tbx<BX, BY, false, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TbxShape<BX, BY, 4>::SMEM));
+    CFDNN_CUDA(cudaFuncSetAttribute(k_sweep_tbx<BX, BY, true, 5>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TbxShape<BX, BY, 5>::SMEM));
+    CFDNN_CUDA(cudaFuncSetAttribute(k_sweep_tbx<BX, BY, false, 5>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TbxShape<BX, BY, 5>::SMEM));
+#endif
 }
 }  // namespace
 
@@ -283,7 +306,7 @@ void Multigrid::tb_setup() {
     if (const char* e = std::getenv("CFDNN_MG_NORMS_TB")) norms_tb_ = std::atoi(e) != 0;
     if (const char* e = std::getenv("CFDNN_MG_RR")) rr_ = std::atoi(e) != 0;
     if (const char* e = std::getenv("CFDNN_MG_RR_MIN")) rr_min_ = std::max(8, std::atoi(e));
-    if (const char* e = std::getenv("CFDNN_MG_TBO_MODE")) tbo_mode_ = std::max(0, std::min(3, std::atoi(e)));
+    if (const char* e = std::getenv("CFDNN_MG_TBO_MODE")) tbo_mode_ = std::max(0, std::min(5, std::atoi(e)));
 }
 
 // n (<= 2) sweeps in one pass (w != nullptr), or the tiled residual r = f - L u (w == nullptr, n = 1);
