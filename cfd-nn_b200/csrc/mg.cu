@@ -214,7 +214,7 @@ void tb_launch(const LevelGeom& g, const double* in, const double* f, double* ou
 // 1: the chunks that read no halo plane (all but the first and the last); 2: the first and the last chunk.
 template <int BX, int BY>
 void tbo_launch(const LevelGeom& g, const double* in, const double* f, double* out, const double* w,
-                cudaStream_t st, int mode, int part = 0) {
+                cudaStream_t st, int mode, int part = 0, bool wally = false) {
     using S = TbShape<2, BX, BY>;
     TbOmega<2> om;
     om.w[0] = w[0]; om.w[1] = w[1];
@@ -224,29 +224,16 @@ void tbo_launch(const LevelGeom& g, const double* in, const double* f, double* o
     const int nch = (int)grid.z;
     if (part == 1) { zoff = 1; grid.z = nch - 2; }
     else if (part == 2) { zstep = nch - 1; grid.z = 2; }
-#ifndef CFDNN_DEVSIM
-    if (mode == 4 || mode == 5) {      // 2 x 2 patch per thread, level-0 planes through the TMA unit (k_sweep_tbx)
-        using Q = TbqShape<BX, BY>;
-        if (mode == 4) {
-            using X = TbxShape<BX, BY, 4>;
-            if (g.fastdiv) CFDNN_LAUNCH_COOP((k_sweep_tbx<BX, BY, true, 4>), grid, Q::NTHREADS, X::SMEM, st, g, in, f, out, om, ZC, zoff, zstep);
-            else CFDNN_LAUNCH_COOP((k_sweep_tbx<BX, BY, false, 4>), grid, Q::NTHREADS, X::SMEM, st, g, in, f, out, om, ZC, zoff, zstep);
-        } else {
-            using X = TbxShape<BX, BY, 5>;
-            if (g.fastdiv) CFDNN_LAUNCH_COOP((k_sweep_tbx<BX, BY, true, 5>), grid, Q::NTHREADS, X::SMEM, st, g, in, f, out, om, ZC, zoff, zstep);
-            else CFDNN_LAUNCH_COOP((k_sweep_tbx<BX, BY, false, 5>), grid, Q::NTHREADS, X::SMEM, st, g, in, f, out, om, ZC, zoff, zstep);
-        }
-        return;
-    }
-#else
-    if (mode > 3) mode = 3;            // the CPU test double has no TMA: same arithmetic through k_sweep_tbq
-#endif
+    if (wally && mode < 3) mode = 3;   // y walls: only the 2 x 2 patch kernels carry the wall rows
+    using Q = TbqShape<BX, BY>;
+#define CFDNN_TBQ(FD_, WY_) CFDNN_LAUNCH_COOP((k_sweep_tbq<BX, BY, FD_, WY_>), grid, Q::NTHREADS, Q::SMEM, st, g, in, f, out, om, ZC, zoff, zstep)
+    if (mode > 3) mode = 3;
     if (mode == 3) {      // 2 x 2 patch per thread (mg_tbq_kernels.cuh)
-        using Q = TbqShape<BX, BY>;
-        if (g.fastdiv) CFDNN_LAUNCH_COOP((k_sweep_tbq<BX, BY, true>), grid, Q::NTHREADS, Q::SMEM, st, g, in, f, out, om, ZC, zoff, zstep);
-        else CFDNN_LAUNCH_COOP((k_sweep_tbq<BX, BY, false>), grid, Q::NTHREADS, Q::SMEM, st, g, in, f, out, om, ZC, zoff, zstep);
+        if (g.fastdiv) { if (wally) CFDNN_TBQ(true, true); else CFDNN_TBQ(true, false); }
+        else { if (wally) CFDNN_TBQ(false, true); else CFDNN_TBQ(false, false); }
         return;
     }
+#undef CFDNN_TBQ
     if (!g.fastdiv) {
         CFDNN_LAUNCH_COOP((k_sweep_tbo<BX, BY, false, TBO_MODE>), grid, S::NTHREADS, S::SMEM, st, g, in, f, out, om, ZC, zoff, zstep);
     } else if (mode == 0) {
@@ -276,14 +263,10 @@ void tbo_attr() {
     CFDNN_CUDA(cudaFuncSetAttribute(k_sweep_tbo<BX, BY, true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::SMEM));
     CFDNN_CUDA(cudaFuncSetAttribute(k_sweep_tbo<BX, BY, false, TBO_MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::SMEM));
     using Q = TbqShape<BX, BY>;
-    CFDNN_CUDA(cudaFuncSetAttribute(k_sweep_tbq<BX, BY, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Q::SMEM));
-    CFDNN_CUDA(cudaFuncSetAttribute(k_sweep_tbq<BX, BY, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Q::SMEM));
-#ifndef CFDNN_DEVSIM
-    CFDNN_CUDA(cudaFuncSetAttribute(k_sweep_tbx<BX, BY, true, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TbxShape<BX, BY, 4>::SMEM));
-    CFDNN_CUDA(cudaFuncSetAttribute(k_sweep_tbx<BX, BY, false, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TbxShape<BX, BY, 4>::SMEM));
-    CFDNN_CUDA(cudaFuncSetAttribute(k_sweep_tbx<BX, BY, true, 5>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TbxShape<BX, BY, 5>::SMEM));
-    CFDNN_CUDA(cudaFuncSetAttribute(k_sweep_tbx<BX, BY, false, 5>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TbxShape<BX, BY, 5>::SMEM));
-#endif
+    CFDNN_CUDA(cudaFuncSetAttribute(k_sweep_tbq<BX, BY, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Q::SMEM));
+    CFDNN_CUDA(cudaFuncSetAttribute(k_sweep_tbq<BX, BY, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Q::SMEM));
+    CFDNN_CUDA(cudaFuncSetAttribute(k_sweep_tbq<BX, BY, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Q::SMEM));
+    CFDNN_CUDA(cudaFuncSetAttribute(k_sweep_tbq<BX, BY, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Q::SMEM));
 }
 }  // namespace
 
@@ -306,7 +289,7 @@ void Multigrid::tb_setup() {
     if (const char* e = std::getenv("CFDNN_MG_NORMS_TB")) norms_tb_ = std::atoi(e) != 0;
     if (const char* e = std::getenv("CFDNN_MG_RR")) rr_ = std::atoi(e) != 0;
     if (const char* e = std::getenv("CFDNN_MG_RR_MIN")) rr_min_ = std::max(8, std::atoi(e));
-    if (const char* e = std::getenv("CFDNN_MG_TBO_MODE")) tbo_mode_ = std::max(0, std::min(5, std::atoi(e)));
+    if (const char* e = std::getenv("CFDNN_MG_TBO_MODE")) tbo_mode_ = std::max(0, std::min(3, std::atoi(e)));
 }
 
 // n (<= 2) sweeps in one pass (w != nullptr), or the tiled residual r = f - L u (w == nullptr, n = 1);
@@ -360,6 +343,14 @@ bool Multigrid::sweeps_tb(int level, const double* in, double* out, const double
     if (tbo_ && n == 2 && open_xy && open_z) {             // no physical face in reach: the lean kernel
         if (big) tbo_launch<TB_BX_BIG, TB_BY_BIG>(g, in, L.f.p, out, w, st_, tbo_mode_);
         else tbo_launch<TB_BX_SMALL, TB_BY_SMALL>(g, in, L.f.p, out, w, st_, tbo_mode_);
+        return true;
+    }
+    // channel levels: x periodic, z open, walls (Neumann / Dirichlet) on both y faces — the 2 x 2 patch kernels
+    // carry the two wall rows with one select each instead of the general kernel's per-cell boundary path
+    const bool wall_y = g.bc[2] != CFDNN_PBC_PERIODIC && g.bc[3] != CFDNN_PBC_PERIODIC && !(g.Ny & 1);
+    if (tbo_ && tbo_mode_ >= 3 && n == 2 && open_z && wall_y && g.bc[0] == CFDNN_PBC_PERIODIC && g.bc[1] == CFDNN_PBC_PERIODIC) {
+        if (big) tbo_launch<TB_BX_BIG, TB_BY_BIG>(g, in, L.f.p, out, w, st_, tbo_mode_, 0, true);
+        else tbo_launch<TB_BX_SMALL, TB_BY_SMALL>(g, in, L.f.p, out, w, st_, tbo_mode_, 0, true);
         return true;
     }
     if (big) {

@@ -35,6 +35,30 @@ def test_blocked_smoother_on_the_test_double(sim, oracle):
 
 
 @pytest.mark.tiled
+@pytest.mark.parametrize("bc", ["PPNNPP", "PPDNPP", "PPDDPP"])
+def test_blocked_smoother_with_y_walls(sim, oracle, monkeypatch, bc):
+    """channel levels (x periodic, z periodic, Neumann / Dirichlet walls in y) take the 2 x 2 patch kernel with wall
+    rows (k_sweep_tbq<.., WALLY>): exact divisions -> bit-identical to the general blocked kernel and to the one-sweep
+    kernel, and the default path within 1e-12 of the oracle"""
+    case = ("chan_walls_" + bc, (32, 16, 32), bc, 3, {})
+    out = {}
+    for tag, env in (("plain", dict(CFDNN_MG_FASTDIV="0", CFDNN_MG_TB="0")),
+                     ("general", dict(CFDNN_MG_FASTDIV="0", CFDNN_MG_TB="2", CFDNN_MG_TBO="0")),
+                     ("patch", dict(CFDNN_MG_FASTDIV="0", CFDNN_MG_TB="2", CFDNN_MG_TBO="1", CFDNN_MG_TBO_MODE="3")),
+                     ("default", dict(CFDNN_MG_TB="2"))):
+        for k in ("CFDNN_MG_FASTDIV", "CFDNN_MG_TB", "CFDNN_MG_TBO", "CFDNN_MG_TBO_MODE"):
+            monkeypatch.delenv(k, raising=False)
+        for k, v in env.items():
+            monkeypatch.setenv(k, v)
+        _, out[tag] = cases.run_mg_backend(sim, case)
+    assert np.array_equal(out["plain"], out["general"])
+    assert np.array_equal(out["plain"], out["patch"])
+    with tempfile.TemporaryDirectory() as td:
+        meta, pref = cases.run_mg_ref(case, td)
+    assert oracle.rel_l2(out["default"], pref) <= 1e-12
+
+
+@pytest.mark.tiled
 def test_blocked_smoother_variants_agree(sim, monkeypatch):
     cases.check_smoother_variants_bitwise(sim, monkeypatch, N=(16, 16, 16), cycles=1)
 
