@@ -87,7 +87,7 @@ Solver::Solver(const cfdnn_mesh_desc& m, const cfdnn_config& c) : mesh_(m), cfg_
 
     const dim3 gmax = grid3(Nx + 1, Ny + 1, Nz + 1);
     npartial_ = (size_t)gmax.x * gmax.y * gmax.z;
-    partial_.alloc(5 * npartial_ + 16);
+    partial_.alloc(5 * std::max<size_t>(npartial_, 148 * 8) + 16);   // per-block partials (k_cfl_maxima: 5 rows of up to 1184)
     scalars_.alloc(32);
     CFDNN_CUDA(cudaMallocHost(&h_scalars_, 32 * sizeof(double)));
     CFDNN_CUDA(cudaStreamCreateWithFlags(&st_, cudaStreamNonBlocking));
@@ -627,9 +627,8 @@ void Solver::step_device(bool want_residual) {
     ph_end(pe);
     build_nu_eff();                                             // :1326-1410
     if (cfg_.adaptive_dt && has_model()) {                      // diffusion-CFL re-check :1416-1491
-        const dim3 gr = grid3(g_.Nx, g_.Ny, g_.Nz);
-        const int nb = gr.x * gr.y * gr.z;
-        CFDNN_LAUNCH_COOP(k_cfl_maxima, gr, kB, 0, st_, g_, vel_, nut_, cfg_.nu, 1, partial_.p, nb);
+        const int nb = std::min(148 * 8, g_.Ny * g_.Nz);
+        CFDNN_LAUNCH_COOP(k_cfl_maxima, nb, 256, 0, st_, g_, vel_, nut_, cfg_.nu, 1, partial_.p, nb);
         CFDNN_LAUNCH_COOP(k_final_max_rows, 1, 1024, 0, st_, partial_.p, nb, 5, scalars_.p + 4);
         if (comm_ && comm_->nranks > 1) comm_->allreduce_max(scalars_.p + 4, 5, st_);
         CFDNN_CUDA(cudaMemcpyAsync(h_scalars_ + 4, scalars_.p + 4, 5 * sizeof(double), cudaMemcpyDeviceToHost, st_));
@@ -685,9 +684,8 @@ void Solver::run(int nsteps, double* last_residual) {
 }
 
 double Solver::compute_adaptive_dt() {                          // src/solver.cpp:3369-3729
-    const dim3 gr = grid3(g_.Nx, g_.Ny, g_.Nz);
-    const int nb = gr.x * gr.y * gr.z;
-    CFDNN_LAUNCH_COOP(k_cfl_maxima, gr, kB, 0, st_, g_, vel_, nut_, cfg_.nu, has_model() ? 1 : 0, partial_.p, nb);
+    const int nb = std::min(148 * 8, g_.Ny * g_.Nz);
+    CFDNN_LAUNCH_COOP(k_cfl_maxima, nb, 256, 0, st_, g_, vel_, nut_, cfg_.nu, has_model() ? 1 : 0, partial_.p, nb);
     CFDNN_LAUNCH_COOP(k_final_max_rows, 1, 1024, 0, st_, partial_.p, nb, 5, scalars_.p + 4);
     CFDNN_CUDA(cudaMemcpyAsync(h_scalars_ + 4, scalars_.p + 4, 5 * sizeof(double), cudaMemcpyDeviceToHost, st_));
     CFDNN_CUDA(cudaStreamSynchronize(st_));

@@ -619,32 +619,42 @@ k_max_change(Geom g, Vel a, Vel b, double* __restrict__ part) {
 // compute_adaptive_dt maxima (src/solver.cpp:3369-3729): per-block partial maxima of
 // |u| (cell-adjacent faces), |v|, |w|, |v|/dy_local (dyv indexed with the 0-based j — the
 // reference's own quirk, :3440,3579,3649) and nu + nu_t.  part layout: [5][nblocks].
+// A CTA strides over (j, k) rows and its threads over i, so the five block reductions (warp shuffles + one
+// shared-memory exchange) happen once per CTA and a launch of 148 x 8 CTAs leaves 1184 partials per quantity
+// instead of one per 256 cells.  Maxima are order-independent: any partition gives the same bits.
 static __global__ void __launch_bounds__(256)
 k_cfl_maxima(Geom g, Vel vel, const double* __restrict__ nut, double nu, int has_model,
              double* __restrict__ part, int nblocks) {
-    __shared__ double sh[32];
-    const int ix = blockIdx.x * blockDim.x + threadIdx.x;
-    const int iy = blockIdx.y * blockDim.y + threadIdx.y;
-    const int iz = blockIdx.z;
+    __shared__ double sh[5][8];
     double m[5] = {0.0, 0.0, 0.0, 0.0, 0.0};
-    if (ix < g.Nx && iy < g.Ny && iz < g.Nz) {
-        const int i = ix + g.Ng, j = iy + g.Ng, k = iz + g.Ng;
-        m[0] = fmax(fabs(vel.u[UIDX(i, j, k)]), fabs(vel.u[UIDX(i + 1, j, k)]));
-        m[1] = fmax(fabs(vel.v[VIDX(i, j, k)]), fabs(vel.v[VIDX(i, j + 1, k)]));
-        m[2] = fmax(fabs(vel.w[WIDX(i, j, k)]), fabs(vel.w[WIDX(i, j, k + 1)]));
-        m[3] = g.y_stretched ? m[1] / g.dyv[iy] : m[1] / g.dy.d;
-        m[4] = has_model ? nu + nut[CIDX(i, j, k)] : 0.0;
+    const int nrows = g.Ny * g.Nz;
+    for (int row = blockIdx.x; row < nrows; row += gridDim.x) {
+        const int iy = row % g.Ny, iz = row / g.Ny;
+        const int j = iy + g.Ng, k = iz + g.Ng;
+        for (int ix = threadIdx.x; ix < g.Nx; ix += blockDim.x) {
+            const int i = ix + g.Ng;
+            const double mu = fmax(fabs(vel.u[UIDX(i, j, k)]), fabs(vel.u[UIDX(i + 1, j, k)]));
+            const double mv = fmax(fabs(vel.v[VIDX(i, j, k)]), fabs(vel.v[VIDX(i, j + 1, k)]));
+            const double mw = fmax(fabs(vel.w[WIDX(i, j, k)]), fabs(vel.w[WIDX(i, j, k + 1)]));
+            m[0] = fmax(m[0], mu); m[1] = fmax(m[1], mv); m[2] = fmax(m[2], mw);
+            m[3] = fmax(m[3], g.y_stretched ? mv / g.dyv[iy] : mv / g.dy.d);
+            if (has_model) m[4] = fmax(m[4], nu + nut[CIDX(i, j, k)]);
+        }
     }
-    const int tid = threadIdx.y * blockDim.x + threadIdx.x;
-    const int lane = tid & 31, wid = tid >> 5, nw = (blockDim.x * blockDim.y + 31) >> 5;
-    const int bid = (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
 #pragma unroll
     for (int q = 0; q < 5; ++q) {
-        double s = warp_max(m[q]);
-        __syncthreads();
-        if (lane == 0) sh[wid] = s;
-        __syncthreads();
-        if (wid == 0) { s = lane < nw ? sh[lane] : 0.0; s = warp_max(s); if (lane == 0) part[(size_t)q * nblocks + bid] = s; }
+        const double s = warp_max(m[q]);
+        if (lane == 0) sh[q][wid] = s;
+    }
+    __syncthreads();
+    if (wid == 0) {
+#pragma unroll
+        for (int q = 0; q < 5; ++q) {
+            double s = lane < nw ? sh[q][lane] : 0.0;
+            s = warp_max(s);
+            if (lane == 0) part[(size_t)q * nblocks + blockIdx.x] = s;
+        }
     }
 }
 // final max over several partial rows: out[q] = max(init[q], max(part[q][:]))
