@@ -57,7 +57,7 @@ class Config(C.Structure):
                 ("poisson_linf_safety", C.c_double),
                 ("poisson_nu1", C.c_int), ("poisson_nu2", C.c_int), ("poisson_chebyshev_degree", C.c_int),
                 ("turb_guard_enabled", C.c_int), ("turb_guard_interval", C.c_int),
-                ("turb_model", C.c_int), ("nu_t_max", C.c_double)]
+                ("turb_model", C.c_int), ("nu_t_max", C.c_double), ("implicit_y_diffusion", C.c_int)]
 
 
 class CfdnnError(RuntimeError):

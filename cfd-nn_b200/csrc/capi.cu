@@ -69,6 +69,7 @@ void cfdnn_config_default(cfdnn_config* c) {             // include/config.hpp:6
     c->poisson_nu1 = 0; c->poisson_nu2 = 0; c->poisson_chebyshev_degree = 4;
     c->turb_guard_enabled = 1; c->turb_guard_interval = 5;
     c->turb_model = CFDNN_TURB_NONE; c->nu_t_max = 1.0;
+    c->implicit_y_diffusion = 0;
 }
 
 // ---------------------------------------------------------------- multigrid
@@ -172,7 +173,7 @@ int cfdnn_solver_device_ptr(cfdnn_solver* s, int field, double** dev_out, size_t
     });
 }
 int cfdnn_solver_set_external_nu_t(cfdnn_solver* s, int on) {
-    return guarded([&] { s->impl.set_external_nu_t(on != 0); });
+    return guarded([&] { s->impl.set_external_nu_t(on != 0, on == 2); });
 }
 int cfdnn_solver_phase_timing(const cfdnn_solver* s, double ms[CFDNN_PHASE_COUNT]) {
     for (int q = 0; q < CFDNN_PHASE_COUNT; ++q) ms[q] = s->impl.last_phase_ms[q];

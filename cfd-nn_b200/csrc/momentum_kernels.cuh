@@ -30,6 +30,10 @@
 #include "solver.cuh"
 #include <type_traits>
 
+#ifndef CIDX
+#define CIDX(i, j, k) ((size_t)(k) * g.cp + (size_t)(j) * g.cs + (i))
+#endif
+
 namespace cfdnn {
 
 struct MomCoef {                  // spacings as divisor/reciprocal pairs and folded constants
@@ -37,6 +41,7 @@ struct MomCoef {                  // spacings as divisor/reciprocal pairs and fo
     double h_rdx, h_rdy, h_rdz;           // 0.5 / dx ...      (EXACT = false)
     double h_r2dx, h_r2dy, h_r2dz;        // 0.5 / (2 dx) ...
     double dt, fx, fy, fz;
+    int xz_only;                          // implicit y-diffusion: the explicit term carries d2/dx2 + d2/dz2 only (solver_operators.cpp:915)
 };
 
 template <bool EXACT>
@@ -227,7 +232,7 @@ k_momentum_z(Geom g, MomCoef c, Vel vel, const double* __restrict__ nu, Vel in, 
                 const double nu_f = 0.25 * (nl + nr + tp[FN - 1] + np_);
                 const double nu_b = 0.25 * (nl + nr + tm[FN - 1] + nm);
                 const double d2z = diff_dir<EXACT>(nu_b, nu_f, uc, um, up_, c.dz2);
-                const double diff = d2x + d2y + d2z;
+                const double diff = c.xz_only ? d2x + d2z : d2x + d2y + d2z;
                 out.u[o] = mom_fma<EXACT>(c.dt, -conv + diff + c.fx, in_u);
             } else if (copy_ghosts) {
                 out.u[o] = uc;
@@ -258,7 +263,7 @@ k_momentum_z(Geom g, MomCoef c, Vel vel, const double* __restrict__ nu, Vel in, 
                 const double nu_f = 0.25 * (nb + nt + tp[FN - TX] + np_);
                 const double nu_b = 0.25 * (nb + nt + tm[FN - TX] + nm);
                 const double d2z = diff_dir<EXACT>(nu_b, nu_f, vc, vm, vp_, c.dz2);
-                const double diff = d2x + d2y + d2z;
+                const double diff = c.xz_only ? d2x + d2z : d2x + d2y + d2z;
                 out.v[o] = mom_fma<EXACT>(c.dt, -conv + diff + c.fy, in_v);
             } else if (copy_ghosts) {
                 out.v[o] = vc;
@@ -289,7 +294,7 @@ k_momentum_z(Geom g, MomCoef c, Vel vel, const double* __restrict__ nu, Vel in, 
                 const double nu_s = 0.25 * (nbk + nfr + tm[FN - TX] + n_s);
                 const double d2y = diff_dir<EXACT>(nu_s, nu_n, wc, w_s, w_n, c.dy2);
                 const double d2z = diff_dir<EXACT>(nbk, nfr, wc, wm, wp_, c.dz2);
-                const double diff = d2x + d2y + d2z;
+                const double diff = c.xz_only ? d2x + d2z : d2x + d2y + d2z;
                 out.w[o] = mom_fma<EXACT>(c.dt, -conv + diff + c.fz, in_w);
             } else if (copy_ghosts) {
                 out.w[o] = wc;
@@ -306,6 +311,87 @@ k_momentum_z(Geom g, MomCoef c, Vel vel, const double* __restrict__ nu, Vel in, 
         step(std::integral_constant<int, 2>{}, K + 2);
         if (K + 3 >= k1) break;
         step(std::integral_constant<int, 3>{}, K + 3);
+    }
+}
+
+// ------------------------------------------------------------------ implicit y-diffusion
+// (I - dt d/dy(nu_eff d/dy)) q_new = q per y-line, Thomas algorithm: thomas_y_diffusion_{2d,3d}[_stretched]
+// (reference src/solver_time_kernels_implicit.cpp:16-454).  One thread per (i, k) line, consecutive threads on
+// consecutive i so every step of the march is one coalesced access per array; the forward sweep leaves d' in the
+// field itself (q[j] is read once, at step j) and c' in a scratch array of the field's shape, the backward sweep
+// reads them back.  Same operations in the same order as the reference (true divisions, no FMA): bit-identical.
+//   COMP 0: u lines  i in [Ng, Ng+Nx], k cells, Ny unknowns, nu between cells i-1 and i, no-slip ghost = -interior
+//   COMP 1: v lines  i cells, k cells, Ny-1 interior faces (wall faces stay 0), nu between cells j-1 and j
+//   COMP 2: w lines  i cells, k in [Ng, Ng+Nz], Ny unknowns, nu between cells k-1 and k
+template <int COMP, bool STRETCHED>
+__global__ void __launch_bounds__(128)
+k_thomas_y(Geom g, double* __restrict__ q, double* __restrict__ cp, const double* __restrict__ nu, double dt,
+           double dt_inv_dy2, int k_first, int nk) {
+    const int Ng = g.Ng;
+    const int ni = COMP == 0 ? g.Nx + 1 : g.Nx;
+    const int il = blockIdx.x * blockDim.x + threadIdx.x;
+    const int kl = blockIdx.y;
+    if (il >= ni || kl >= nk) return;
+    const int i = il + Ng, k = k_first + kl;
+    const int n = COMP == 1 ? g.Ny - 1 : g.Ny;                 // unknowns per line
+    const int j0 = COMP == 1 ? Ng + 1 : Ng;
+    const size_t qs = COMP == 0 ? g.us : (COMP == 1 ? g.vs : g.ws);
+    const size_t qp = COMP == 0 ? (size_t)g.up : (COMP == 1 ? (size_t)g.vp : (size_t)g.wp);
+    double* ql = q + (size_t)k * qp + i;
+    double* cl = cp + (size_t)k * qp + i;
+    double cprev = 0.0, dprev = 0.0;
+    for (int jj = 0; jj < n; ++jj) {
+        const int j = jj + j0;
+        double nu_avg;
+        if (COMP == 0) nu_avg = 0.5 * (nu[CIDX(i - 1, j, k)] + nu[CIDX(i, j, k)]);
+        else if (COMP == 1) nu_avg = 0.5 * (nu[CIDX(i, j - 1, k)] + nu[CIDX(i, j, k)]);
+        else nu_avg = 0.5 * (nu[CIDX(i, j, k - 1)] + nu[CIDX(i, j, k)]);
+        double a_j, c_j, b_j;
+        if (STRETCHED) {
+            double alpha_lo, alpha_hi;
+            if (COMP == 1) {
+                alpha_lo = dt * nu_avg / (g.dyc[j] * g.dyv[j - 1]);
+                alpha_hi = dt * nu_avg / (g.dyc[j] * g.dyv[j]);
+            } else {
+                alpha_lo = dt * nu_avg / (g.dyv[j] * g.dyc[j]);
+                alpha_hi = dt * nu_avg / (g.dyv[j] * g.dyc[j + 1]);
+            }
+            a_j = jj > 0 ? -alpha_lo : 0.0;
+            c_j = jj < n - 1 ? -alpha_hi : 0.0;
+            b_j = 1.0 + alpha_lo + alpha_hi;
+            if (COMP != 1) {
+                if (jj == 0) b_j += alpha_lo;
+                if (jj == n - 1) b_j += alpha_hi;
+            }
+        } else {
+            const double alpha = dt_inv_dy2 * nu_avg;
+            a_j = jj > 0 ? -alpha : 0.0;
+            c_j = jj < n - 1 ? -alpha : 0.0;
+            b_j = 1.0 + 2.0 * alpha;
+            if (COMP != 1) {
+                if (jj == 0) b_j += alpha;
+                if (jj == n - 1) b_j += alpha;
+            }
+        }
+        const double d_j = ql[(size_t)j * qs];
+        double cj, dj;
+        if (jj == 0) {
+            cj = c_j / b_j;
+            dj = d_j / b_j;
+        } else {
+            const double denom = b_j - a_j * cprev;
+            cj = c_j / denom;
+            dj = (d_j - a_j * dprev) / denom;
+        }
+        cl[(size_t)j * qs] = cj;
+        ql[(size_t)j * qs] = dj;
+        cprev = cj; dprev = dj;
+    }
+    double x = dprev;                                          // q[n-1] = d'[n-1], already in place
+    for (int jj = n - 2; jj >= 0; --jj) {
+        const int j = jj + j0;
+        x = ql[(size_t)j * qs] - cl[(size_t)j * qs] * x;
+        ql[(size_t)j * qs] = x;
     }
 }
 

@@ -365,7 +365,7 @@ void Solver::momentum(const Vel& in, Vel& out, double dt, bool seam_average) {
     }
     const Vel src_in = in;                       // copies of the pointer triples (in may be vel_ itself)
     const Vel dst = alias ? conv_ : out;
-    if (mom_z_) {
+    if (mom_z_ || implicit_y()) {   // (the xz-only explicit term of implicit y-diffusion exists in this kernel only)
         // z-marching tile kernel (momentum_kernels.cuh).  Exact divisions + unfused products wherever the result
         // must carry the x86 build's bits: y-stretched meshes (their Poisson solver amplifies a last-bit change)
         // and the 2-D embedding; reciprocal multiplies + FMA on uniform 3-D meshes.
@@ -377,6 +377,7 @@ void Solver::momentum(const Vel& in, Vel& out, double dt, bool seam_average) {
         c.h_rdx = 0.5 / g_.dx.d; c.h_rdy = 0.5 / g_.dy.d; c.h_rdz = 0.5 / g_.dz.d;
         c.h_r2dx = 0.5 / g_.dx_2.d; c.h_r2dy = 0.5 / g_.dy_2.d; c.h_r2dz = 0.5 / g_.dz_2.d;
         c.dt = dt; c.fx = fx_; c.fy = fy_; c.fz = fz_;
+        c.xz_only = implicit_y() ? 1 : 0;
         const int ex = g_.Nx + 2 * Ng, ey = g_.Ny + 2 * Ng, ez = g_.Nz + 2 * Ng;
         const int tiles = ((ex + BX) / BX) * ((ey + BY) / BY);
         int zc = 64;                              // planes per CTA: 2 extra plane loads per chunk
@@ -489,6 +490,30 @@ void Solver::euler_substep(const Vel& in, Vel& out, double dt) {
     PhaseEv* e = ph_begin(CFDNN_PHASE_MOMENTUM);
     momentum(in, out, dt, /*seam_average=*/false);
     ph_end(e);
+    if (implicit_y()) implicit_y_diffusion_step(out, dt);           // solver_time.cpp:657-660
+}
+
+bool Solver::implicit_y() const {                                    // solver_time.cpp:668-670
+    return cfg_.implicit_y_diffusion && !(vbc_[2] == CFDNN_VBC_PERIODIC && vbc_[3] == CFDNN_VBC_PERIODIC);
+}
+
+// implicit_y_diffusion_step (src/solver_time.cpp:667-735): Thomas solve per y-line of u, v, w (2-D: u, v on the data
+// plane).  c' goes to the diff_ buffers, which the fused momentum kernel leaves unused.
+void Solver::implicit_y_diffusion_step(const Vel& v, double dt) {
+    const int Ng = g_.Ng, Nx = g_.Nx, Nz = g_.Nz;
+    const double dt_inv_dy2 = dt / (mesh_.dy * mesh_.dy);
+    const dim3 blk(128);
+    auto grid = [&](int ni, int nk) { return dim3((ni + 127) / 128, nk); };
+    const int kc = is2d_ ? 1 : Nz;                  // cell planes: the data plane k = Ng of the 2-D embedding only
+    if (g_.y_stretched) {
+        CFDNN_LAUNCH((k_thomas_y<0, true>), grid(Nx + 1, kc), blk, 0, st_, g_, v.u, diff_.u, nueff_, dt, dt_inv_dy2, Ng, kc);
+        if (g_.Ny > 1) CFDNN_LAUNCH((k_thomas_y<1, true>), grid(Nx, kc), blk, 0, st_, g_, v.v, diff_.v, nueff_, dt, dt_inv_dy2, Ng, kc);
+        if (!is2d_) CFDNN_LAUNCH((k_thomas_y<2, true>), grid(Nx, Nz + 1), blk, 0, st_, g_, v.w, diff_.w, nueff_, dt, dt_inv_dy2, Ng, Nz + 1);
+    } else {
+        CFDNN_LAUNCH((k_thomas_y<0, false>), grid(Nx + 1, kc), blk, 0, st_, g_, v.u, diff_.u, nueff_, dt, dt_inv_dy2, Ng, kc);
+        if (g_.Ny > 1) CFDNN_LAUNCH((k_thomas_y<1, false>), grid(Nx, kc), blk, 0, st_, g_, v.v, diff_.v, nueff_, dt, dt_inv_dy2, Ng, kc);
+        if (!is2d_) CFDNN_LAUNCH((k_thomas_y<2, false>), grid(Nx, Nz + 1), blk, 0, st_, g_, v.w, diff_.w, nueff_, dt, dt_inv_dy2, Ng, Nz + 1);
+    }
 }
 
 // project_velocity (src/solver_time.cpp:736-1211); which == &vel_ means "no swap"
@@ -548,6 +573,7 @@ void Solver::euler_step() {
         apply_velocity_bc();
         std::swap(vel_, star_);
     }
+    if (implicit_y()) implicit_y_diffusion_step(star_, dt_);     // :1849-1853
     compute_divergence(star_);
     build_rhs(dt_);
     // iter_ is only advanced by solve_steady*, so a step()-driven run zeroes p' every step
@@ -634,7 +660,9 @@ void Solver::step_device(bool want_residual) {
         CFDNN_CUDA(cudaMemcpyAsync(h_scalars_ + 4, scalars_.p + 4, 5 * sizeof(double), cudaMemcpyDeviceToHost, st_));
         CFDNN_CUDA(cudaStreamSynchronize(st_));
         const double nu_eff_max = std::max(cfg_.nu, h_scalars_[8]);
-        const double dx_min = std::min({mesh_.dx, dy_min_, mesh_.dz});
+        // :1475-1486 (the 2-D branch takes min(dx, dy); implicit y-diffusion without a transport model drops dy)
+        double dx_min = is2d_ ? std::min(mesh_.dx, dy_min_) : std::min({mesh_.dx, dy_min_, mesh_.dz});
+        if (cfg_.implicit_y_diffusion && !ext_transport_) dx_min = is2d_ ? mesh_.dx : std::min(mesh_.dx, mesh_.dz);
         const double dt_diff_limit = 0.25 * dx_min * dx_min / nu_eff_max;
         if (dt_ > dt_diff_limit) dt_ = std::max(cfg_.dt_safety * dt_diff_limit, 1e-15);
     }
@@ -698,8 +726,11 @@ double Solver::compute_adaptive_dt() {                          // src/solver.cp
     const double dt_cfl_x = cfl_xz * mesh_.dx / u_abs_max;
     const double dt_cfl_y = cfg_.CFL_max / v_dy_ratio_max;
     const double dt_cfl_z = is2d_ ? 1e10 : cfl_xz * mesh_.dz / w_abs_max;          // :3688
-    const double dx_min = is2d_ ? std::min(mesh_.dx, dy_min_) : std::min({mesh_.dx, dy_min_, mesh_.dz});
-    const double dt_diff = 0.25 * dx_min * dx_min / nu_eff_max;
+    const double dx_min_full = is2d_ ? std::min(mesh_.dx, dy_min_) : std::min({mesh_.dx, dy_min_, mesh_.dz});
+    const double dx_min = cfg_.implicit_y_diffusion ? (is2d_ ? mesh_.dx : std::min(mesh_.dx, mesh_.dz)) : dx_min_full;   // :3697-3706
+    double dt_diff = 0.25 * dx_min * dx_min / nu_eff_max;
+    if (cfg_.implicit_y_diffusion && ext_transport_)                                       // :3709-3712
+        dt_diff = std::min(dt_diff, 0.25 * dx_min_full * dx_min_full / nu_eff_max);
     double dt_new = cfg_.dt_safety * std::min({dt_cfl_x, dt_cfl_y, dt_cfl_z, dt_diff});
     if (comm_ && comm_->nranks > 1) {
         CFDNN_CUDA(cudaMemcpyAsync(scalars_.p + 10, &dt_new, sizeof(double), cudaMemcpyHostToDevice, st_));

@@ -51,7 +51,7 @@ public:
     void set_dt(double dt) { dt_ = dt; }
     double dt() const { return dt_; }
     void set_turbulence_model(NNClosure* nn) { nn_ = nn; }
-    void set_external_nu_t(bool on) { ext_nut_ = on; }      // nu_t uploaded by the caller (bridged host model)
+    void set_external_nu_t(bool on, bool transport = false) { ext_nut_ = on; ext_transport_ = on && transport; }   // nu_t uploaded by the caller (bridged host model)
     bool has_model() const { return nn_ != nullptr || ext_nut_; }
     double* view_ptr(int field, size_t* n) const;           // device twin of a field (cfdnn_solver_device_ptr)
     void comm_init(Comm* c);
@@ -97,7 +97,7 @@ private:
 
     std::unique_ptr<Multigrid> mg_;
     NNClosure* nn_ = nullptr;
-    bool ext_nut_ = false;
+    bool ext_nut_ = false, ext_transport_ = false;
     bool mom_z_ = true;                    // z-marching momentum kernel (env CFDNN_MOMENTUM_Z=0: one thread per point)
     bool mom_exact_ = false;               // env CFDNN_MOMENTUM_EXACT=1: exact divisions on uniform 3-D meshes too
     Comm* comm_ = nullptr;
@@ -121,6 +121,8 @@ private:
     void build_rhs(double dt);
     int poisson_solve(const cfdnn_poisson_cfg& pc);
     void euler_substep(const Vel& in, Vel& out, double dt);         // solver_time.cpp:269-661
+    void implicit_y_diffusion_step(const Vel& v, double dt);        // solver_time.cpp:667-735 (Thomas solves per y-line)
+    bool implicit_y() const;                                         // config flag and y not periodic
     void project_velocity(Vel* which, double dt);                    // :736-1211
     void ssprk3_step(double dt);                                     // :1303-1513
     void ssprk2_step(double dt);                                     // :1213-1301

@@ -114,6 +114,11 @@ typedef struct cfdnn_config {
     int turb_guard_enabled, turb_guard_interval;
     int turb_model;
     double nu_t_max;
+    /* implicit y-diffusion (include/config.hpp:103): the d2/dy2 part of the momentum diffusion is taken out of the
+     * explicit term (src/solver_operators.cpp:915) and solved per y-line with the Thomas algorithm after every
+     * predictor / RK stage (src/solver_time.cpp:658-735, src/solver_time_kernels_implicit.cpp); no effect when y is
+     * periodic; relaxes the diffusive dt limit to the x/z spacings (src/solver.cpp:1481, 3697-3712) */
+    int implicit_y_diffusion;
 } cfdnn_config;
 
 typedef struct cfdnn_solver cfdnn_solver;   /* stands in for RANSSolver              */
@@ -173,7 +178,9 @@ int cfdnn_solver_last_timing(const cfdnn_solver* s, double* step_ms, double* vcy
  * include/turbulence_device_view.hpp:12-55) and its element count.  On 2-D meshes the data plane is k = Ng.
  * The RK stages rotate the velocity buffers, so pointers are valid until the next step()/run(). */
 int cfdnn_solver_device_ptr(cfdnn_solver* s, int field, double** dev_out, size_t* n_out);
-/* nu_t supplied by the caller: a reference TurbulenceModel that is NOT one of this backend's closures
+/* nu_t supplied by the caller (on = 1; on = 2 when that model also solves transport equations, which keeps the
+ * dy term in the diffusive dt limit under implicit y-diffusion, src/solver.cpp:1481, 3709): a reference
+ * TurbulenceModel that is NOT one of this backend's closures
  * (e.g. SST k-omega running on the host) is bridged by download(velocity) -> model.update() ->
  * upload(CFDNN_F_NUT); with this flag on, step() builds nu_eff = nu + nu_t (src/solver.cpp:1326-1410) and
  * takes the closure branches of the diffusion-CFL re-check and the NaN guard as if a model were attached */

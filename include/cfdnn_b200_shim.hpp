@@ -220,6 +220,7 @@ inline cfdnn_config solver_cfg(const Config& c) {
     o.turb_model = c.turb_model == TurbulenceModelType::NNTBNN ? CFDNN_TURB_NN_TBNN
                  : c.turb_model == TurbulenceModelType::NNMLP ? CFDNN_TURB_NN_MLP : CFDNN_TURB_NONE;
     o.nu_t_max = c.nu_t_max;
+    o.implicit_y_diffusion = c.implicit_y_diffusion ? 1 : 0;
     return o;
 }
 
@@ -277,7 +278,7 @@ public:
         if (turb_) turb_->set_nu(nu_);
         if (native_) native_->set_nu_t_max(nu_t_max_);
         check(cfdnn_solver_set_turbulence_model(h_, native_ ? native_->handle() : nullptr));
-        check(cfdnn_solver_set_external_nu_t(h_, turb_ && !native_ ? 1 : 0));
+        check(cfdnn_solver_set_external_nu_t(h_, turb_ && !native_ ? (turb_->uses_transport_equations() ? 2 : 1) : 0));
     }
     /// set_decomposition (include/solver.hpp:93): this rank's mesh is the z-slab [k_global_start, +nz_local) of
     /// nz_global planes; the NCCL communicator replaces halo_exchange.cpp.  `nccl_id` is the 128-byte
@@ -297,7 +298,7 @@ public:
         check(cfdnn_solver_set_body_force(h_, fx_, fy_, fz_));
         if (turb_) {
             check(cfdnn_solver_set_turbulence_model(h_, native_ ? native_->handle() : nullptr));
-            check(cfdnn_solver_set_external_nu_t(h_, !native_ ? 1 : 0));
+            check(cfdnn_solver_set_external_nu_t(h_, !native_ ? (turb_->uses_transport_equations() ? 2 : 1) : 0));
         }
         check(cfdnn_solver_comm_init(h_, decomp->rank(), decomp->nprocs(), nccl_id));
     }

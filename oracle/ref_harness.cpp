@@ -140,6 +140,7 @@ Config make_config(const Mesh& mesh) {
     c.nn_weights_path = arg_s("nn_weights", "");
     c.nn_scaling_path = arg_s("nn_scaling", c.nn_weights_path);
     c.nu_t_max = arg_d("nu_t_max", c.nu_t_max);
+    c.implicit_y_diffusion = arg_i("implicit_y", 0) != 0;
     return c;
 }
 

@@ -46,7 +46,8 @@ MG_SEMI_CASES = [
     ("semi_neumann_all_fixed1", (16, 16, 32), "NNNNNN", 1, dict(smooth=1, **CHANNEL_BOX)),
     ("semi_random_rhs_fixed1", (32, 16, 16), "PPNNPP", 1, dict(**CHANNEL_BOX)),
 ]
-HARNESS_KEYS = ("stretch_beta", "x1", "y0", "y1", "z1", "tol_rhs", "maxv", "tol_rel", "tol", "tol_abs", "check_interval")
+HARNESS_KEYS = ("stretch_beta", "x1", "y0", "y1", "z1", "tol_rhs", "maxv", "tol_rel", "tol", "tol_abs", "check_interval",
+                "implicit_y")
 
 
 # stretched-y channel steps (BASELINE config 3 in miniature): stretched divergence / correction
@@ -54,6 +55,25 @@ HARNESS_KEYS = ("stretch_beta", "x1", "y0", "y1", "z1", "tol_rhs", "maxv", "tol_
 STEP_STRETCHED_CASES = [
     ("chan_stretched_rk3_tgv", (16, 16, 16), "PPWWPP", "rk3", "skew", 6, 1, "tgv", (1.0, 0, 0), dict(**CHANNEL_BOX)),
     ("chan_stretched_euler_shear", (32, 16, 16), "PPWWPP", "euler", "central", 4, 2, "shear", (1.0, 0, 0), dict(**CHANNEL_BOX)),
+]
+
+
+# implicit y-diffusion (Thomas solve per y-line after every predictor / RK stage, xz-only explicit term;
+# src/solver_time.cpp:657-735, src/solver_time_kernels_implicit.cpp, src/solver_operators.cpp:915)
+CHANNEL_UNIFORM = dict(x1=4 * np.pi, y0=-1.0, y1=1.0, z1=2 * np.pi)
+STEP_IMPLICIT_CASES = [
+    ("chan16_rk3_skew_implicit", (16, 16, 16), "PPWWPP", "rk3", "skew", 8, 2, "pchan", (1.0, 0, 0), dict(implicit_y=1, **CHANNEL_UNIFORM)),
+    ("chan_24x16x16_euler_central_implicit", (24, 16, 16), "PPWWPP", "euler", "central", 6, 2, "pchan", (1.0, 0, 0), dict(implicit_y=1, **CHANNEL_UNIFORM)),
+    ("duct16_rk2_walls_xy_implicit", (16, 16, 16), "WWWWPP", "rk2", "skew", 4, 2, "shear", (1.0, 0, 0), dict(implicit_y=1)),
+    ("tgv16_periodic_y_implicit_is_noop", (16, 16, 16), "PPPPPP", "rk3", "skew", 4, 1, "tgv", (0, 0, 0), dict(implicit_y=1)),
+]
+STEP_IMPLICIT_STRETCHED_CASES = [
+    ("chan_stretched_rk3_implicit", (16, 16, 16), "PPWWPP", "rk3", "skew", 6, 1, "pchan", (1.0, 0, 0), dict(implicit_y=1, **CHANNEL_BOX)),
+    ("chan_stretched_euler_implicit", (32, 16, 16), "PPWWPP", "euler", "central", 4, 2, "shear", (1.0, 0, 0), dict(implicit_y=1, **CHANNEL_BOX)),
+]
+STEP_IMPLICIT_2D_CASES = [
+    ("chan2d_euler_implicit", (32, 32, 1), "PPWWPP", "euler", "skew", 8, 2, "pchan", (1.0, 0, 0), dict(implicit_y=1, x1=4 * np.pi, y0=-1.0, y1=1.0)),
+    ("chan2d_stretched_rk3_implicit", (32, 32, 1), "PPWWPP", "rk3", "skew", 6, 2, "pchan", (1.0, 0, 0), dict(implicit_y=1, **CHANNEL_BOX)),
 ]
 
 
@@ -239,6 +259,8 @@ def make_solver(B, case, mesh_arrays=None, **cfg_over):
         kw["poisson_tol_rhs"] = float(extra["tol_rhs"])
     if "maxv" in extra:
         kw["poisson_max_vcycles"] = int(extra["maxv"])
+    if extra.get("implicit_y"):
+        kw["implicit_y_diffusion"] = 1
     kw.update(cfg_over)
     cfg = B.config(**kw)
     if mesh_arrays is not None:
@@ -529,13 +551,19 @@ def check_tiled_norms(B, monkeypatch, case):
 
 
 # ---------------------------------------------------------------- reductions of the step
-def check_adaptive_dt(B, oracle, stretched=False, nsteps=3):
+def check_adaptive_dt(B, oracle, stretched=False, nsteps=3, implicit=False):
     """compute_adaptive_dt (src/solver.cpp:3369-3729) in the app time loop: dt = compute_adaptive_dt();
     set_dt(dt); step().  stretched = True exercises max(|v| / dyv[j]) with the reference's 0-based j
-    (:3440,3579,3649) and dx_min over the stretched cell heights."""
+    (:3440,3579,3649) and dx_min over the stretched cell heights; implicit = True the relaxed diffusive limit of
+    implicit y-diffusion (dx_min over x and z only, :3697-3706) on a viscous channel where it binds."""
     import ctypes as C
+    nu = 0.01
     if stretched:
         N, bc, init, force, extra = (16, 16, 16), "PPWWPP", "tgv", (1.0, 0, 0), dict(**CHANNEL_BOX)
+        nsteps = min(nsteps, 2)
+    elif implicit:
+        N, bc, init, force, extra = (16, 32, 16), "PPWWPP", "pchan", (1.0, 0, 0), dict(implicit_y=1, **CHANNEL_UNIFORM)
+        nu = 0.5                      # diffusion-limited: 0.25 dy^2 / nu would bind without the implicit treatment
     else:
         N, bc, init, force, extra = (16, 16, 16), "PPPPPP", "tgv", (0, 0, 0), {}
     case = ("adt", N, bc, "rk3", "skew", 8, nsteps, init, force, extra)
@@ -544,11 +572,11 @@ def check_adaptive_dt(B, oracle, stretched=False, nsteps=3):
         pre = os.path.join(td, "in")
         u.tofile(pre + "_u.f64"); v.tofile(pre + "_v.f64"); w.tofile(pre + "_w.f64")
         meta = oracle.run_ref("step", Nx=N[0], Ny=N[1], Nz=N[2], bc=bc, ti="rk3", scheme="skew", fixed=8, nsteps=nsteps,
-                              dt=0.01, nu=0.01, init="file:" + pre, adaptive_dt=1, CFL_max=0.4, fx=force[0],
+                              dt=0.01, nu=nu, init="file:" + pre, adaptive_dt=1, CFL_max=0.4, fx=force[0],
                               out=os.path.join(td, "r"), **{k: v_ for k, v_ in extra.items() if k in HARNESS_KEYS})
         mesh_arrays = oracle.load_mesh_arrays(os.path.join(td, "r_mesh")) if stretched else None
         ref = R.load_state(os.path.join(td, "r_final"), *N)
-    h = make_solver(B, case, mesh_arrays=mesh_arrays, adaptive_dt=1, CFL_max=0.4)
+    h = make_solver(B, case, mesh_arrays=mesh_arrays, adaptive_dt=1, CFL_max=0.4, nu=nu)
     dts = []
     try:
         for _ in range(nsteps):
@@ -561,6 +589,9 @@ def check_adaptive_dt(B, oracle, stretched=False, nsteps=3):
     finally:
         B.lib.cfdnn_solver_destroy(h)
     assert dts == pytest.approx(meta["dts"], rel=1e-12), (dts, meta["dts"])
+    if implicit:                      # the y spacing must not have entered the limit: dt > 0.25 dy^2 / nu
+        dy = (extra["y1"] - extra["y0"]) / N[1]
+        assert min(dts) > 0.25 * dy * dy / nu
     compare_states(got, ref, 1e-10, "adaptive dt" + (" stretched" if stretched else ""), vel_joint=True)
     return dts
 

@@ -228,6 +228,10 @@ def test_adaptive_dt_matches_reference(gpu, oracle, stretched):
     cases.check_adaptive_dt(gpu, oracle, stretched=stretched)
 
 
+def test_adaptive_dt_with_implicit_y_diffusion(gpu, oracle):
+    cases.check_adaptive_dt(gpu, oracle, implicit=True)
+
+
 def test_nan_guard_raises_runtime_error(gpu):
     cases.check_nan_guard(gpu)
 
@@ -235,3 +239,36 @@ def test_nan_guard_raises_runtime_error(gpu):
 def test_diffusion_cfl_recheck_with_closure(gpu, oracle):
     dts, used = cases.check_diffusion_cfl_recheck(gpu, oracle)
     print("adaptive dts", dts, "dt used by step()", used)
+
+
+# ---- implicit y-diffusion: Thomas solve per y-line + xz-only explicit diffusion
+@pytest.mark.parametrize("case", cases.STEP_IMPLICIT_CASES, ids=[c[0] for c in cases.STEP_IMPLICIT_CASES])
+def test_implicit_y_diffusion_step_matches_reference(gpu, oracle, case):
+    with tempfile.TemporaryDirectory() as td:
+        meta, ref = cases.run_step_ref(case, td)
+    got_meta, got = cases.run_step_backend(gpu, case)
+    if meta["cycles"]:
+        assert got_meta["cycles"] == meta["cycles"]
+    assert got_meta["residuals"] == pytest.approx(meta["residuals"], rel=1e-9)
+    cases.compare_states(got, ref, 1e-10, case[0])
+
+
+@pytest.mark.parametrize("case", cases.STEP_IMPLICIT_STRETCHED_CASES, ids=[c[0] for c in cases.STEP_IMPLICIT_STRETCHED_CASES])
+def test_implicit_y_diffusion_stretched_matches_reference(gpu, oracle, case):
+    cases.check_step_stretched(gpu, oracle, case)
+
+
+@pytest.mark.parametrize("case", cases.STEP_IMPLICIT_2D_CASES, ids=[c[0] for c in cases.STEP_IMPLICIT_2D_CASES])
+def test_implicit_y_diffusion_2d_matches_reference(gpu, oracle, case):
+    cases.check_step_2d(gpu, oracle, case)
+
+
+def test_implicit_y_diffusion_channel_128x64x64_vs_oracle(gpu, oracle):
+    """the Thomas lines and the xz-only explicit term at a size where the momentum tiles and the big smoother tiles run"""
+    case = ("chan128_implicit", (128, 64, 64), "PPWWPP", "rk3", "skew", 0, 1, "pchan", (1.0, 0, 0),
+            dict(tol_rhs=1e-8, maxv=50, implicit_y=1, **cases.CHANNEL_UNIFORM))
+    with tempfile.TemporaryDirectory() as td:
+        meta, ref = cases.run_step_ref(case, td)
+    got_meta, got = cases.run_step_backend(gpu, case)
+    assert got_meta["cycles"] == meta["cycles"]
+    cases.compare_states(got, ref, 1e-10, "chan128 implicit-y 1 step")

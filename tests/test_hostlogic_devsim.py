@@ -35,7 +35,7 @@ def test_blocked_smoother_on_the_test_double(sim, oracle):
 
 
 @pytest.mark.tiled
-@pytest.mark.parametrize("bc", ["PPNNPP", "PPDNPP", "PPDDPP"])
+@pytest.mark.parametrize("bc", ["PPNNPP", "PPDNPP"])
 def test_blocked_smoother_with_y_walls(sim, oracle, monkeypatch, bc):
     """channel levels (x periodic, z periodic, Neumann / Dirichlet walls in y) take the 2 x 2 patch kernel with wall
     rows (k_sweep_tbq<.., WALLY>): exact divisions -> bit-identical to the general blocked kernel and to the one-sweep
@@ -147,6 +147,10 @@ def test_adaptive_dt_matches_reference(sim, oracle, stretched):
     cases.check_adaptive_dt(sim, oracle, stretched=stretched)
 
 
+def test_adaptive_dt_with_implicit_y_diffusion(sim, oracle):
+    cases.check_adaptive_dt(sim, oracle, implicit=True)
+
+
 def test_diffusion_cfl_recheck_with_closure(sim, oracle):
     cases.check_diffusion_cfl_recheck(sim, oracle)
 
@@ -162,3 +166,25 @@ def test_stretched_metrics_match_reference_mesh(oracle):
     got = oracle.backend.stretched_y_metrics(96, -1.0, 1.0, 2.0)
     for k in ref:
         assert np.array_equal(ref[k], got[k]), k
+
+
+# ---- implicit y-diffusion
+@pytest.mark.parametrize("case", cases.STEP_IMPLICIT_CASES, ids=[c[0] for c in cases.STEP_IMPLICIT_CASES])
+def test_implicit_y_diffusion_step_matches_reference(sim, oracle, case):
+    with tempfile.TemporaryDirectory() as td:
+        meta, ref = cases.run_step_ref(case, td)
+    got_meta, got = cases.run_step_backend(sim, case)
+    if meta["cycles"]:
+        assert got_meta["cycles"] == meta["cycles"]
+    assert got_meta["residuals"] == pytest.approx(meta["residuals"], rel=1e-9)
+    cases.compare_states(got, ref, 1e-10, case[0])
+
+
+@pytest.mark.parametrize("case", cases.STEP_IMPLICIT_STRETCHED_CASES, ids=[c[0] for c in cases.STEP_IMPLICIT_STRETCHED_CASES])
+def test_implicit_y_diffusion_stretched_matches_reference(sim, oracle, case):
+    cases.check_step_stretched(sim, oracle, case)
+
+
+@pytest.mark.parametrize("case", cases.STEP_IMPLICIT_2D_CASES, ids=[c[0] for c in cases.STEP_IMPLICIT_2D_CASES])
+def test_implicit_y_diffusion_2d_matches_reference(sim, oracle, case):
+    cases.check_step_2d(sim, oracle, case)

@@ -162,3 +162,28 @@ def test_gpu_slabs_big_tiles_distributed_levels(R, oracle, gpu, world, monkeypat
         ref = R.load_state(os.path.join(td, "ref_final"), *N)
     assert got["1"]["cycles"] == meta["cycles"]
     cases.compare_states({n: got["1"][n] for n in names}, ref, 1e-10, f"{world} GPU slabs, big tiles")
+
+
+def test_inconsistent_decomposition_is_rejected(sim):
+    """comm_init validates the slab layout: equal slabs only (the reference's remainder rule,
+    include/decomposition.hpp:81-92, is not supported), consistent Nz_global / k_offset — CFDNN_ERR_INVALID
+    (std::invalid_argument through the shim) instead of silently wrong coarse right-hand sides."""
+    import ctypes as C
+
+    class Callbacks(C.Structure):
+        _fields_ = [("ctx", C.c_void_p), ("sendrecv", C.c_void_p), ("allreduce", C.c_void_p), ("allgather", C.c_void_p)]
+
+    cbs = Callbacks()
+    fn = sim.lib.cfdnn_devsim_solver_comm_init
+    fn.restype = C.c_int
+    fn.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(Callbacks)]
+    cfg = sim.config()
+    for kw, rank, what in ((dict(Nz_global=16, k_offset=0), 0, b"Nz_global"),          # global count not given
+                           (dict(Nz_global=40, k_offset=0), 0, b"unequal z-slabs"),     # 40 planes on 2 ranks of 16
+                           (dict(Nz_global=32, k_offset=0), 1, b"k_offset")):            # rank 1 must start at plane 16
+        h = C.c_void_p()
+        m = sim.mesh(16, 16, 16, **kw)
+        sim.check(sim.lib.cfdnn_solver_create(C.byref(m), C.byref(cfg), C.byref(h)))
+        rc = fn(h, rank, 2, C.byref(cbs))
+        assert rc == 1 and what in sim.lib.cfdnn_last_error(), (rc, sim.lib.cfdnn_last_error())
+        sim.lib.cfdnn_solver_destroy(h)
