@@ -247,6 +247,8 @@ def main():
                          "'RK3 + MG + NN-TBNN' workload; none: closure-free step")
     ap.add_argument("--adaptive-dt", action="store_true",
                     help="call compute_adaptive_dt + set_dt before every step (the CFL reductions in the timed region)")
+    ap.add_argument("--implicit-y", action="store_true",
+                    help="implicit y-diffusion (Thomas solve per y-line after every RK stage; channel workloads)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-parity", action="store_true")
@@ -332,7 +334,7 @@ def main():
         mesh.y_lo, mesh.y_hi = y_lo, y_lo + Ly
     cfg = B.config(nu=nu_, dt=dt_, time_integrator=K.TI["rk3"], convective_scheme=K.SCHEME["skew"],
                    adaptive_dt=1 if args.adaptive_dt else 0, poisson_fixed_cycles=fixed, poisson_tol_rhs=MG_TOL_RHS,
-                   poisson_max_vcycles=MG_MAXV)
+                   poisson_max_vcycles=MG_MAXV, implicit_y_diffusion=1 if args.implicit_y else 0)
     h = B.solver(mesh, cfg, bc, force)
     nn = None
     if args.closure == "tbnn":
@@ -544,6 +546,10 @@ def main():
                             "achieved": gbs(3 * 200.0 * cells_local, T["phases"][1] / args.steps),
                             "frac": frac(gbs(3 * 200.0 * cells_local, T["phases"][1] / args.steps)),
                             "note": "fused conv + diff + advance, 200 B per cell per stage (SURVEY 8(d))"}
+        if args.implicit_y:
+            roof["implicit_y"] = {"ms_per_step": T["phases"][2] / args.steps, "launches_per_step": 9,
+                                  "note": "Thomas solves per y-line of u, v, w after each of the 3 RK stages "
+                                          "(src/solver_time_kernels_implicit.cpp); ~64 B per cell and component"}
         cpu = None
         if not args.no_cpu_baseline and os.path.exists(HARNESS):
             v, ms, sample = cpu_reference(args.workload, args.closure, 3, 1)
@@ -558,7 +564,8 @@ def main():
                                        f"dt={dt_:g}, multigrid Poisson " +
                                        (f"{fixed} fixed V-cycles" if fixed else f"to tol_rhs={MG_TOL_RHS} (max {MG_MAXV} V-cycles)") +
                                        (f", NN-TBNN closure ({PRESET}) on every cell every step (FP64 DMMA)" if nn else ", no closure") +
-                                       (", adaptive dt (compute_adaptive_dt every step)" if args.adaptive_dt else ""),
+                                       (", adaptive dt (compute_adaptive_dt every step)" if args.adaptive_dt else "") +
+                                       (", implicit y-diffusion" if args.implicit_y else ""),
                            "closure": args.closure,
                            "l2": "inputs larger than L2" if cells_local >= 256 ** 3 else "small grid: fits L2",
                            "vcycles_per_solve": cycles[-3:], "decomposition": f"z-slabs x{world}",

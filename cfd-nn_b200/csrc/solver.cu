@@ -505,6 +505,7 @@ void Solver::implicit_y_diffusion_step(const Vel& v, double dt) {
     const dim3 blk(128);
     auto grid = [&](int ni, int nk) { return dim3((ni + 127) / 128, nk); };
     const int kc = is2d_ ? 1 : Nz;                  // cell planes: the data plane k = Ng of the 2-D embedding only
+    PhaseEv* pe = ph_begin(CFDNN_PHASE_IMPLICIT_Y);
     if (g_.y_stretched) {
         CFDNN_LAUNCH((k_thomas_y<0, true>), grid(Nx + 1, kc), blk, 0, st_, g_, v.u, diff_.u, nueff_, dt, dt_inv_dy2, Ng, kc);
         if (g_.Ny > 1) CFDNN_LAUNCH((k_thomas_y<1, true>), grid(Nx, kc), blk, 0, st_, g_, v.v, diff_.v, nueff_, dt, dt_inv_dy2, Ng, kc);
@@ -514,6 +515,7 @@ void Solver::implicit_y_diffusion_step(const Vel& v, double dt) {
         if (g_.Ny > 1) CFDNN_LAUNCH((k_thomas_y<1, false>), grid(Nx, kc), blk, 0, st_, g_, v.v, diff_.v, nueff_, dt, dt_inv_dy2, Ng, kc);
         if (!is2d_) CFDNN_LAUNCH((k_thomas_y<2, false>), grid(Nx, Nz + 1), blk, 0, st_, g_, v.w, diff_.w, nueff_, dt, dt_inv_dy2, Ng, Nz + 1);
     }
+    ph_end(pe);
 }
 
 // project_velocity (src/solver_time.cpp:736-1211); which == &vel_ means "no swap"

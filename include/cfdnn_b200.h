@@ -187,7 +187,7 @@ int cfdnn_solver_device_ptr(cfdnn_solver* s, int field, double** dev_out, size_t
 int cfdnn_solver_set_external_nu_t(cfdnn_solver* s, int on);
 /* device ms of the last step()/run() spent in the closure update (TurbulenceModel::update inside step(),
  * src/solver.cpp:1284-1324) and in the fused momentum kernels (convective + diffusive + advance) */
-enum { CFDNN_PHASE_CLOSURE = 0, CFDNN_PHASE_MOMENTUM = 1, CFDNN_PHASE_COUNT = 4 };
+enum { CFDNN_PHASE_CLOSURE = 0, CFDNN_PHASE_MOMENTUM = 1, CFDNN_PHASE_IMPLICIT_Y = 2, CFDNN_PHASE_COUNT = 4 };
 int cfdnn_solver_phase_timing(const cfdnn_solver* s, double ms[CFDNN_PHASE_COUNT]);
 /* measurement aid for bench.py's roofline: ms per launch of the level-0 temporally blocked smoother
  * kernel (2 Chebyshev sweeps per launch), `reps` launches timed with CUDA events on the solver's
