@@ -23,7 +23,7 @@ class MeshDesc(C.Structure):
                 ("dyv", c_double_p), ("dyc", c_double_p),
                 ("yLap_aS", c_double_p), ("yLap_aN", c_double_p), ("yLap_aP", c_double_p),
                 ("yc", c_double_p), ("y_lo", C.c_double), ("y_hi", C.c_double),
-                ("Nz_global", C.c_int), ("k_offset", C.c_int)]
+                ("Nz_global", C.c_int), ("k_offset", C.c_int), ("yf", c_double_p)]
 
 
 class PoissonCfg(C.Structure):
@@ -113,6 +113,8 @@ _SIGS = {
                                   c_double_p, c_double_p, c_double_p, c_double_p]),
     "cfdnn_nn_update_dev": (C.c_int, [C.c_void_p, C.POINTER(MeshDesc), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                       C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "cfdnn_les_update": (C.c_int, [C.POINTER(MeshDesc), C.c_int, C.c_double, c_double_p, c_double_p, c_double_p, c_double_p]),
+    "cfdnn_solver_set_les_model": (C.c_int, [C.c_void_p, C.c_int, C.c_double]),
     "cfdnn_nn_forward": (C.c_int, [C.c_void_p, c_double_p, c_double_p, C.c_size_t]),
     "cfdnn_nn_last_timing": (C.c_int, [C.c_void_p, c_double_p]),
     "cfdnn_nn_uses_tensor_cores": (C.c_int, [C.c_void_p]),

@@ -70,6 +70,8 @@ class Backend:
         md.dyv, md.dyc = capi.dptr(arrs["dyv"]), capi.dptr(arrs["dyc"])
         md.yLap_aS, md.yLap_aN, md.yLap_aP = capi.dptr(arrs["aS"]), capi.dptr(arrs["aN"]), capi.dptr(arrs["aP"])
         md.yc = capi.dptr(arrs["yc"])
+        if "yf" in arrs:
+            md.yf = capi.dptr(arrs["yf"])
         md._keep = arrs                      # keep the arrays alive as long as the descriptor
         return md
 
@@ -123,8 +125,10 @@ class Backend:
 
 
 def _load_mesh_arrays(pre):
-    """y-metric arrays of a stretched mesh (dyv, dyc, aS, aN, aP, yc) from `<pre>_<name>.f64` files"""
-    return {k: np.ascontiguousarray(np.fromfile(f"{pre}_{k}.f64")) for k in ("dyv", "dyc", "aS", "aN", "aP", "yc")}
+    """y-metric arrays of a stretched mesh (dyv, dyc, aS, aN, aP, yc, yf) from `<pre>_<name>.f64` files"""
+    import os
+    return {k: np.ascontiguousarray(np.fromfile(f"{pre}_{k}.f64")) for k in ("dyv", "dyc", "aS", "aN", "aP", "yc", "yf")
+            if os.path.exists(f"{pre}_{k}.f64")}
 
 
 def tgv_init(Nx, Ny, Nz, L=2 * np.pi, V0=1.0, Ng=1):
@@ -191,6 +195,7 @@ def stretched_y_metrics(Ny, y_lo, y_hi, beta, Ng=1):
 
 # ---------------------------------------------------------------- NN closures (cfdnn_nn handles)
 NN_KIND = {"mlp": 1, "tbnn": 2}
+LES_MODEL = {"smagorinsky": 1, "wale": 2, "vreman": 3, "sigma": 4}
 
 
 def load_npz_preset(path, name):

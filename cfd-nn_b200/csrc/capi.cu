@@ -4,6 +4,7 @@
 #ifndef CFDNN_MG_ONLY
 #include "solver.cuh"
 #include "nn.cuh"
+#include "les.cuh"
 #endif
 #include <mutex>
 #include <cstring>
@@ -222,6 +223,16 @@ int cfdnn_nn_update_dev(cfdnn_nn* nn, const cfdnn_mesh_desc* mesh, const double*
                         const double* k_dev, const double* omega_dev, double* nu_t_dev, double* tau_xx_dev,
                         double* tau_xy_dev, double* tau_yy_dev) {
     return guarded([&] { nn->impl.update_dev_ptrs(*mesh, u_dev, v_dev, k_dev, omega_dev, nu_t_dev, tau_xx_dev, tau_xy_dev, tau_yy_dev); });
+}
+int cfdnn_les_update(const cfdnn_mesh_desc* mesh, int model, double constant, const double* u, const double* v,
+                     const double* w, double* nu_t) {
+    return guarded([&] {
+        if (!mesh) throw std::invalid_argument("cfdnn_les_update: null mesh");
+        les_update_host(*mesh, model, constant, u, v, w, nu_t);
+    });
+}
+int cfdnn_solver_set_les_model(cfdnn_solver* s, int model, double constant) {
+    return guarded([&] { s->impl.set_les_model(model, constant); });
 }
 int cfdnn_nn_forward(cfdnn_nn* nn, const double* x, double* y, size_t n) {
     return guarded([&] { nn->impl.forward_host(x, y, n); });

@@ -41,7 +41,6 @@ struct MomCoef {                  // spacings as divisor/reciprocal pairs and fo
     double h_rdx, h_rdy, h_rdz;           // 0.5 / dx ...      (EXACT = false)
     double h_r2dx, h_r2dy, h_r2dz;        // 0.5 / (2 dx) ...
     double dt, fx, fy, fz;
-    int xz_only;                          // implicit y-diffusion: the explicit term carries d2/dx2 + d2/dz2 only (solver_operators.cpp:915)
 };
 
 template <bool EXACT>
@@ -106,7 +105,8 @@ struct MomShape {
 
 // SKEW: skew-symmetric (true) or central (false) convection.  Launch: grid (ceil((ex+1)/BX), ceil((ey+1)/BY), z chunks),
 // block BX*BY threads.  zc = planes per chunk.
-template <bool SKEW, bool EXACT, int BX, int BY>
+// XZ: implicit y-diffusion — the explicit term carries d2/dx2 + d2/dz2 only (src/solver_operators.cpp:915)
+template <bool SKEW, bool EXACT, bool XZ, int BX, int BY>
 __global__ void __launch_bounds__(BX * BY, 2)
 k_momentum_z(Geom g, MomCoef c, Vel vel, const double* __restrict__ nu, Vel in, Vel out, int copy_ghosts, int zc) {
     using S = MomShape<BX, BY>;
@@ -232,7 +232,7 @@ k_momentum_z(Geom g, MomCoef c, Vel vel, const double* __restrict__ nu, Vel in, 
                 const double nu_f = 0.25 * (nl + nr + tp[FN - 1] + np_);
                 const double nu_b = 0.25 * (nl + nr + tm[FN - 1] + nm);
                 const double d2z = diff_dir<EXACT>(nu_b, nu_f, uc, um, up_, c.dz2);
-                const double diff = c.xz_only ? d2x + d2z : d2x + d2y + d2z;
+                const double diff = XZ ? d2x + d2z : d2x + d2y + d2z;
                 out.u[o] = mom_fma<EXACT>(c.dt, -conv + diff + c.fx, in_u);
             } else if (copy_ghosts) {
                 out.u[o] = uc;
@@ -263,7 +263,7 @@ k_momentum_z(Geom g, MomCoef c, Vel vel, const double* __restrict__ nu, Vel in, 
                 const double nu_f = 0.25 * (nb + nt + tp[FN - TX] + np_);
                 const double nu_b = 0.25 * (nb + nt + tm[FN - TX] + nm);
                 const double d2z = diff_dir<EXACT>(nu_b, nu_f, vc, vm, vp_, c.dz2);
-                const double diff = c.xz_only ? d2x + d2z : d2x + d2y + d2z;
+                const double diff = XZ ? d2x + d2z : d2x + d2y + d2z;
                 out.v[o] = mom_fma<EXACT>(c.dt, -conv + diff + c.fy, in_v);
             } else if (copy_ghosts) {
                 out.v[o] = vc;
@@ -294,7 +294,7 @@ k_momentum_z(Geom g, MomCoef c, Vel vel, const double* __restrict__ nu, Vel in, 
                 const double nu_s = 0.25 * (nbk + nfr + tm[FN - TX] + n_s);
                 const double d2y = diff_dir<EXACT>(nu_s, nu_n, wc, w_s, w_n, c.dy2);
                 const double d2z = diff_dir<EXACT>(nbk, nfr, wc, wm, wp_, c.dz2);
-                const double diff = c.xz_only ? d2x + d2z : d2x + d2y + d2z;
+                const double diff = XZ ? d2x + d2z : d2x + d2y + d2z;
                 out.w[o] = mom_fma<EXACT>(c.dt, -conv + diff + c.fz, in_w);
             } else if (copy_ghosts) {
                 out.w[o] = wc;

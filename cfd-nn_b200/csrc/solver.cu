@@ -4,6 +4,7 @@
 #include "mg_kernels.cuh"
 #include "comm.cuh"
 #include "nn.cuh"
+#include "les.cuh"
 #include <cmath>
 #include <algorithm>
 #include <cstring>
@@ -77,7 +78,9 @@ Solver::Solver(const cfdnn_mesh_desc& m, const cfdnn_config& c) : mesh_(m), cfg_
         yc_.alloc(yc.size(), false);
         CFDNN_CUDA(cudaMemcpy(yc_.p, yc.data(), yc.size() * sizeof(double), cudaMemcpyHostToDevice));
     }
-    mesh_.dyv = mesh_.dyc = mesh_.yLap_aS = mesh_.yLap_aN = mesh_.yLap_aP = mesh_.yc = nullptr;  // host pointers not kept
+    if (m.yc) h_yc_.assign(m.yc, m.yc + (Ny + 2 * Ng));
+    if (m.yf) h_yf_.assign(m.yf, m.yf + (Ny + 2 * Ng + 1));
+    mesh_.dyv = mesh_.dyc = mesh_.yLap_aS = mesh_.yLap_aN = mesh_.yLap_aP = mesh_.yc = mesh_.yf = nullptr;  // host pointers not kept
 
     vel_ = alloc_vel(); star_ = alloc_vel(); old_ = alloc_vel(); rk_ = alloc_vel();
     conv_ = alloc_vel(); diff_ = alloc_vel();
@@ -100,10 +103,10 @@ Solver::Solver(const cfdnn_mesh_desc& m, const cfdnn_config& c) : mesh_(m), cfg_
     if (const char* e = std::getenv("CFDNN_MOMENTUM_EXACT")) mom_exact_ = std::atoi(e) != 0;  // 1: exact divisions everywhere
     {
         using S = MomShape<MOM_BX, MOM_BY>;
-        CFDNN_CUDA(cudaFuncSetAttribute(k_momentum_z<true, true, MOM_BX, MOM_BY>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::SMEM));
-        CFDNN_CUDA(cudaFuncSetAttribute(k_momentum_z<true, false, MOM_BX, MOM_BY>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::SMEM));
-        CFDNN_CUDA(cudaFuncSetAttribute(k_momentum_z<false, true, MOM_BX, MOM_BY>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::SMEM));
-        CFDNN_CUDA(cudaFuncSetAttribute(k_momentum_z<false, false, MOM_BX, MOM_BY>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::SMEM));
+#define CFDNN_MOMZ_ATTR(SK, EX, XZ_) CFDNN_CUDA(cudaFuncSetAttribute(k_momentum_z<SK, EX, XZ_, MOM_BX, MOM_BY>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::SMEM))
+        CFDNN_MOMZ_ATTR(true, true, false); CFDNN_MOMZ_ATTR(true, false, false); CFDNN_MOMZ_ATTR(false, true, false); CFDNN_MOMZ_ATTR(false, false, false);
+        CFDNN_MOMZ_ATTR(true, true, true); CFDNN_MOMZ_ATTR(true, false, true); CFDNN_MOMZ_ATTR(false, true, true); CFDNN_MOMZ_ATTR(false, false, true);
+#undef CFDNN_MOMZ_ATTR
     }
     dt_ = c.dt;
     set_velocity_bc(vbc_);
@@ -377,7 +380,6 @@ void Solver::momentum(const Vel& in, Vel& out, double dt, bool seam_average) {
         c.h_rdx = 0.5 / g_.dx.d; c.h_rdy = 0.5 / g_.dy.d; c.h_rdz = 0.5 / g_.dz.d;
         c.h_r2dx = 0.5 / g_.dx_2.d; c.h_r2dy = 0.5 / g_.dy_2.d; c.h_r2dz = 0.5 / g_.dz_2.d;
         c.dt = dt; c.fx = fx_; c.fy = fy_; c.fz = fz_;
-        c.xz_only = implicit_y() ? 1 : 0;
         const int ex = g_.Nx + 2 * Ng, ey = g_.Ny + 2 * Ng, ez = g_.Nz + 2 * Ng;
         const int tiles = ((ex + BX) / BX) * ((ey + BY) / BY);
         int zc = 64;                              // planes per CTA: 2 extra plane loads per chunk
@@ -385,11 +387,17 @@ void Solver::momentum(const Vel& in, Vel& out, double dt, bool seam_average) {
         const dim3 grid((ex + BX) / BX, (ey + BY) / BY, (ez + zc) / zc);
         const bool exact = mom_exact_ || g_.y_stretched || is2d_;
         const bool skew = cfg_.convective_scheme == CFDNN_CONV_SKEW;
-#define CFDNN_MOMZ(SK, EX)                                                                                          \
-        CFDNN_LAUNCH_COOP((k_momentum_z<SK, EX, BX, BY>), grid, BX * BY, S::SMEM, st_, g_, c, vel_, nueff_, src_in, dst, \
+#define CFDNN_MOMZ(SK, EX, XZ_)                                                                                      \
+        CFDNN_LAUNCH_COOP((k_momentum_z<SK, EX, XZ_, BX, BY>), grid, BX * BY, S::SMEM, st_, g_, c, vel_, nueff_, src_in, dst, \
                           alias ? 1 : 0, zc)
-        if (skew) { if (exact) CFDNN_MOMZ(true, true); else CFDNN_MOMZ(true, false); }
-        else { if (exact) CFDNN_MOMZ(false, true); else CFDNN_MOMZ(false, false); }
+        const bool xz = implicit_y();
+        if (skew) {
+            if (exact) { if (xz) CFDNN_MOMZ(true, true, true); else CFDNN_MOMZ(true, true, false); }
+            else { if (xz) CFDNN_MOMZ(true, false, true); else CFDNN_MOMZ(true, false, false); }
+        } else {
+            if (exact) { if (xz) CFDNN_MOMZ(false, true, true); else CFDNN_MOMZ(false, true, false); }
+            else { if (xz) CFDNN_MOMZ(false, false, true); else CFDNN_MOMZ(false, false, false); }
+        }
 #undef CFDNN_MOMZ
     } else if (cfg_.convective_scheme == CFDNN_CONV_SKEW)
         CFDNN_LAUNCH((k_momentum<true>), gr, kB, 0, st_, g_, vel_, nueff_, src_in, dst, dt, fx_, fy_, fz_, alias ? 1 : 0);
@@ -619,7 +627,25 @@ void Solver::build_nu_eff() {
     if (has_model()) halo_cell(nueff_, /*bc_site=*/false);
 }
 
+void Solver::set_les_model(int model, double constant) {
+    if (model == CFDNN_LES_NONE) { les_model_ = 0; return; }
+    (void)les_default_constant(model);               // validates the id
+    if (!les_met_) {
+        les_mesh_ = mesh_;
+        les_mesh_.yc = h_yc_.empty() ? nullptr : h_yc_.data();
+        les_mesh_.yf = h_yf_.empty() ? nullptr : h_yf_.data();
+        if (is2d_) les_mesh_.Nz = 1;
+        les_met_ = std::make_unique<LesMetrics>(les_mesh_);
+    }
+    les_model_ = model;
+    les_c_ = constant;
+}
+
 void Solver::update_turbulence() {
+    if (les_model_) {                                // LESModel::update: nu_t = nu_sgs (src/turbulence_les.cpp:292-335)
+        les_update_device(g_, les_mesh_, *les_met_, les_model_, les_c_, vel_, nut_, g_.Ng, is2d_ ? 1 : g_.Nz, is2d_, st_);
+        return;
+    }
     if (!nn_) return;
     nn_->update_device(g_, yc_.p, mesh_.y_lo, mesh_.y_hi, vel_, k_, omega_, nut_, tau_[0], tau_[1], tau_[2], st_,
                        /*data_plane=*/g_.Ng);

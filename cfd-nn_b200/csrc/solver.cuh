@@ -21,6 +21,7 @@ namespace cfdnn {
 
 struct Comm;
 class NNClosure;
+struct LesMetrics;
 
 struct Geom {                 // by-value kernel argument
     int Nx, Ny, Nz, Ng;
@@ -52,7 +53,8 @@ public:
     double dt() const { return dt_; }
     void set_turbulence_model(NNClosure* nn) { nn_ = nn; }
     void set_external_nu_t(bool on, bool transport = false) { ext_nut_ = on; ext_transport_ = on && transport; }   // nu_t uploaded by the caller (bridged host model)
-    bool has_model() const { return nn_ != nullptr || ext_nut_; }
+    void set_les_model(int model, double constant);          // static LES SGS closure evaluated at the top of step()
+    bool has_model() const { return nn_ != nullptr || ext_nut_ || les_model_ != 0; }
     double* view_ptr(int field, size_t* n) const;           // device twin of a field (cfdnn_solver_device_ptr)
     void comm_init(Comm* c);
 
@@ -98,6 +100,11 @@ private:
     std::unique_ptr<Multigrid> mg_;
     NNClosure* nn_ = nullptr;
     bool ext_nut_ = false, ext_transport_ = false;
+    int les_model_ = 0;                    // CFDNN_LES_*
+    double les_c_ = 0.0;
+    std::unique_ptr<LesMetrics> les_met_;
+    cfdnn_mesh_desc les_mesh_{};           // mesh descriptor with the y arrays the LES closure needs (host copies below)
+    std::vector<double> h_yc_, h_yf_;
     bool mom_z_ = true;                    // z-marching momentum kernel (env CFDNN_MOMENTUM_Z=0: one thread per point)
     bool mom_exact_ = false;               // env CFDNN_MOMENTUM_EXACT=1: exact divisions on uniform 3-D meshes too
     Comm* comm_ = nullptr;

@@ -39,6 +39,8 @@ enum { CFDNN_TI_EULER = 0, CFDNN_TI_RK2 = 1, CFDNN_TI_RK3 = 2 };
 enum { CFDNN_CONV_CENTRAL = 0, CFDNN_CONV_SKEW = 2 };  /* Upwind(1)/Upwind2(3): out of scope */
 /* closure kinds — TurbulenceModelType::{None,NNMLP,NNTBNN} */
 enum { CFDNN_TURB_NONE = 0, CFDNN_TURB_NN_MLP = 1, CFDNN_TURB_NN_TBNN = 2 };
+/* static LES subgrid-scale models — TurbulenceModelType::{Smagorinsky, WALE, Vreman, Sigma}, include/turbulence_les.hpp */
+enum { CFDNN_LES_NONE = 0, CFDNN_LES_SMAGORINSKY = 1, CFDNN_LES_WALE = 2, CFDNN_LES_VREMAN = 3, CFDNN_LES_SIGMA = 4 };
 /* PoissonSolveStatus — include/solver.hpp:130-140 */
 enum { CFDNN_PSTAT_CONVERGED = 0, CFDNN_PSTAT_HIT_MAX = 1, CFDNN_PSTAT_FIXED = 2 };
 
@@ -80,6 +82,7 @@ typedef struct cfdnn_mesh_desc {
     /* z-slab decomposition (replaces include/decomposition.hpp): this rank owns global
      * planes [k_offset, k_offset+Nz) of Nz_global; single rank: k_offset=0, Nz_global=Nz */
     int Nz_global, k_offset;
+    const double* yf;       /* face y, Ny+2Ng+1 (Mesh::yf); needed by the LES closures on y-stretched meshes, else NULL */
 } cfdnn_mesh_desc;
 
 /* PoissonConfig — include/poisson_solver.hpp:16-53 (same defaults via cfdnn_poisson_cfg_default) */
@@ -218,6 +221,14 @@ int cfdnn_nn_update(cfdnn_nn* nn, const cfdnn_mesh_desc* mesh, const double* u, 
 int cfdnn_nn_update_dev(cfdnn_nn* nn, const cfdnn_mesh_desc* mesh, const double* u_dev, const double* v_dev,
                         const double* k_dev, const double* omega_dev, double* nu_t_dev,
                         double* tau_xx_dev, double* tau_xy_dev, double* tau_yy_dev);
+/* ---- static LES SGS closures (include/turbulence_les.hpp:24-115, src/turbulence_les.cpp, src/velocity_gradient.cpp) ----
+ * LESModel::update(mesh, velocity, k, omega, nu_t, ...) on host arrays: nu_t = nu_sgs on every interior cell
+ * (2-D mesh: plane 0).  constant <= 0 selects the reference default (Cs 0.17, Cw 0.325, Cv 0.07, C_sigma 1.35). */
+int cfdnn_les_update(const cfdnn_mesh_desc* mesh, int model, double constant, const double* u, const double* v,
+                     const double* w, double* nu_t);
+/* set_turbulence_model(std::make_unique<SmagorinskyModel|WALEModel|VremanModel|SigmaModel>(constant)): the model is
+ * evaluated device-resident at the top of every step() (src/solver.cpp:1284-1324); CFDNN_LES_NONE detaches it */
+int cfdnn_solver_set_les_model(cfdnn_solver* s, int model, double constant);
 /* batched MLP forward (MLP::forward, src/nn_core.cpp:144-204): x[n][in] -> y[n][out] */
 int cfdnn_nn_forward(cfdnn_nn* nn, const double* x, double* y, size_t n);
 int cfdnn_nn_last_timing(const cfdnn_nn* nn, double* ms);

@@ -48,6 +48,7 @@ inline cfdnn_mesh_desc mesh_desc(const Mesh& m) {
         d.yLap_aS = m.yLap_aS.data(); d.yLap_aN = m.yLap_aN.data(); d.yLap_aP = m.yLap_aP.data();
     }
     d.yc = m.yc.data();
+    d.yf = m.yf.data();
     d.y_lo = m.y_min; d.y_hi = m.y_max;
     d.Nz_global = m.Nz; d.k_offset = 0;
     return d;
@@ -268,17 +269,23 @@ public:
         check(cfdnn_solver_set_body_force(h_, fx, fy, fz));
     }
     /// set_turbulence_model(std::unique_ptr<TurbulenceModel>) (include/solver.hpp:107).  A TurbulenceNNB200 runs
-    /// device-resident inside step().  Any other reference TurbulenceModel (e.g. SST k-omega, which has no B200
-    /// kernels yet) is BRIDGED: every step() downloads the velocity, calls the model's own host update() /
+    /// device-resident inside step(); so do the reference's own static LES models (SmagorinskyModel, WALEModel,
+    /// VremanModel, SigmaModel with their default constants: recognised by name(), evaluated by k_les_sgs).  Any other
+    /// reference TurbulenceModel (e.g. SST k-omega, which has no B200 kernels yet) is BRIDGED: every step() downloads the velocity, calls the model's own host update() /
     /// advance_turbulence() exactly where the reference does (src/solver.cpp:1284-1324), and uploads nu_t — correct,
     /// but PCIe-bound; it exists so that such a run works at all, not as a fast path.
     void set_turbulence_model(std::unique_ptr<TurbulenceModel> model) {
         turb_ = std::move(model);
         native_ = dynamic_cast<TurbulenceNNB200*>(turb_.get());
+        les_ = CFDNN_LES_NONE;
+        if (turb_ && !native_) {       // the reference's own static LES models run as device kernels (default constants)
+            const std::string n = turb_->name();
+            les_ = n == "Smagorinsky" ? CFDNN_LES_SMAGORINSKY : n == "WALE" ? CFDNN_LES_WALE
+                 : n == "Vreman" ? CFDNN_LES_VREMAN : n == "Sigma" ? CFDNN_LES_SIGMA : CFDNN_LES_NONE;
+        }
         if (turb_) turb_->set_nu(nu_);
         if (native_) native_->set_nu_t_max(nu_t_max_);
-        check(cfdnn_solver_set_turbulence_model(h_, native_ ? native_->handle() : nullptr));
-        check(cfdnn_solver_set_external_nu_t(h_, turb_ && !native_ ? (turb_->uses_transport_equations() ? 2 : 1) : 0));
+        attach_model();
     }
     /// set_decomposition (include/solver.hpp:93): this rank's mesh is the z-slab [k_global_start, +nz_local) of
     /// nz_global planes; the NCCL communicator replaces halo_exchange.cpp.  `nccl_id` is the 128-byte
@@ -296,10 +303,7 @@ public:
         check(cfdnn_solver_create(&d, &c, &h_));
         if (have_bc_) set_velocity_bc(bc_);
         check(cfdnn_solver_set_body_force(h_, fx_, fy_, fz_));
-        if (turb_) {
-            check(cfdnn_solver_set_turbulence_model(h_, native_ ? native_->handle() : nullptr));
-            check(cfdnn_solver_set_external_nu_t(h_, !native_ ? (turb_->uses_transport_equations() ? 2 : 1) : 0));
-        }
+        if (turb_) attach_model();
         check(cfdnn_solver_comm_init(h_, decomp->rank(), decomp->nprocs(), nccl_id));
     }
     Decomposition* decomposition() const { return decomp_; }
@@ -338,7 +342,7 @@ public:
     double step() {
         double r = 0.0;
         if (native_) native_->push_params();
-        if (turb_ && !native_) bridge_host_model();
+        if (bridged()) bridge_host_model();
         check(cfdnn_solver_step(h_, &r));
         refresh_stats();
         return r;
@@ -346,7 +350,7 @@ public:
     /// n steps without host round trips (app time loops)
     double advance(int nsteps) {
         double r = 0.0;
-        if (turb_ && !native_) {
+        if (bridged()) {
             for (int s = 0; s < nsteps; ++s) r = step();
             return r;
         }
@@ -426,6 +430,12 @@ public:
 private:
     void up(int f, const std::vector<double>& v) { check(cfdnn_solver_upload(h_, f, v.data(), v.size())); }
     void down(int f, std::vector<double>& v) { check(cfdnn_solver_download(h_, f, v.data(), v.size())); }
+    bool bridged() const { return turb_ && !native_ && les_ == CFDNN_LES_NONE; }
+    void attach_model() {
+        check(cfdnn_solver_set_turbulence_model(h_, native_ ? native_->handle() : nullptr));
+        check(cfdnn_solver_set_les_model(h_, les_, 0.0));
+        check(cfdnn_solver_set_external_nu_t(h_, bridged() ? (turb_->uses_transport_equations() ? 2 : 1) : 0));
+    }
     double* dev(int f) const {
         double* p = nullptr;
         size_t n = 0;
@@ -463,6 +473,7 @@ private:
     cfdnn_solver* h_ = nullptr;
     std::unique_ptr<TurbulenceModel> turb_;
     TurbulenceNNB200* native_ = nullptr;        // turb_ when it is one of this backend's device closures
+    int les_ = CFDNN_LES_NONE;                  // turb_ is one of the reference's static LES models: device kernel
     Decomposition* decomp_ = nullptr;
     VelocityBC bc_;
     bool have_bc_ = false;

@@ -136,6 +136,10 @@ Config make_config(const Mesh& mesh) {
     const std::string model = arg_s("model", "none");
     if (model == "nn_tbnn") c.turb_model = TurbulenceModelType::NNTBNN;
     else if (model == "nn_mlp") c.turb_model = TurbulenceModelType::NNMLP;
+    else if (model == "smagorinsky") c.turb_model = TurbulenceModelType::Smagorinsky;
+    else if (model == "wale") c.turb_model = TurbulenceModelType::WALE;
+    else if (model == "vreman") c.turb_model = TurbulenceModelType::Vreman;
+    else if (model == "sigma") c.turb_model = TurbulenceModelType::Sigma;
     else c.turb_model = TurbulenceModelType::None;
     c.nn_weights_path = arg_s("nn_weights", "");
     c.nn_scaling_path = arg_s("nn_scaling", c.nn_weights_path);
@@ -399,6 +403,31 @@ int run_nn() {
     return 0;
 }
 
+// LESModel::update (CPU path: GradientComputer + compute_nu_sgs_cell) on a given velocity; 2-D or 3-D mesh
+// (reference src/turbulence_les.cpp:292-335, src/velocity_gradient.cpp:20-119)
+int run_les() {
+    Mesh mesh = make_mesh();
+    const std::string out = arg_s("out", "");
+    const std::string model = arg_s("model", "smagorinsky");
+    TurbulenceModelType type = model == "wale" ? TurbulenceModelType::WALE
+                             : model == "vreman" ? TurbulenceModelType::Vreman
+                             : model == "sigma" ? TurbulenceModelType::Sigma : TurbulenceModelType::Smagorinsky;
+    auto tm = create_turbulence_model(type, "", "", 0.1, 0.1);
+    VectorField vel(mesh);
+    const std::string pre = arg_s("in", "");
+    read_f64(pre + "_u.f64", vel.u_data());
+    read_f64(pre + "_v.f64", vel.v_data());
+    if (!mesh.is2D()) read_f64(pre + "_w.f64", vel.w_data());
+    ScalarField k(mesh), omega(mesh), nu_t(mesh);
+    tm->update(mesh, vel, k, omega, nu_t, nullptr, nullptr);
+    if (!out.empty()) {
+        write_f64(out + "_nut.f64", nu_t.data());
+        dump_mesh(mesh, out + "_mesh");
+    }
+    std::cout << "{\"mode\":\"les\",\"model\":\"" << tm->name() << "\"}" << std::endl;
+    return 0;
+}
+
 } // namespace
 
 int main(int argc, char** argv) {
@@ -414,6 +443,7 @@ int main(int argc, char** argv) {
         if (mode == "bench") return run_step(true);
         if (mode == "mg") return run_mg();
         if (mode == "nn") return run_nn();
+        if (mode == "les") return run_les();
         if (mode == "mesh") {                      // dump the reference's mesh arrays (y metrics of stretched meshes)
             Mesh mesh = make_mesh();
             dump_mesh(mesh, arg_s("out", "mesh") + "_mesh");

@@ -666,3 +666,91 @@ def check_diffusion_cfl_recheck(B, oracle, nsteps=3, tol=1e-9):
     for n in ("u", "v", "p"):
         assert R.rel_l2(plane0_interior(n, got[n]), plane0_interior(n, ref[n])) <= tol, n
     return dts, used
+
+
+# ---------------------------------------------------------------- static LES SGS closures
+LES_MODELS = ("smagorinsky", "wale", "vreman", "sigma")
+
+
+def les_velocity(N, seed=5):
+    """smooth 3-component field with every gradient component non-zero (2-D: u, v in plane 0)"""
+    Nx, Ny, Nz = N
+    u, v, w = step_init(N, "tgv")
+    rng = np.random.default_rng(seed)
+    sh = R.shapes(Nx, Ny, Nz)
+    if Nz == 1:
+        x = np.arange(sh["u"][2]) / Nx; y = np.arange(sh["u"][1]) / Ny
+        u[0] += 0.3 * np.sin(2 * np.pi * y)[:, None] * np.cos(4 * np.pi * x)[None, :] + 0.01 * rng.standard_normal(sh["u"][1:])
+        v[0] += 0.2 * np.cos(2 * np.pi * np.arange(sh["v"][1]) / Ny)[:, None] * np.sin(2 * np.pi * np.arange(sh["v"][2]) / Nx)[None, :]
+        return u, v, w
+    zf = np.arange(sh["w"][0]) / Nz; yc = np.arange(sh["w"][1]) / Ny; xc = np.arange(sh["w"][2]) / Nx
+    w[:] = 0.4 * np.sin(2 * np.pi * zf)[:, None, None] * np.cos(2 * np.pi * yc)[None, :, None] * np.sin(4 * np.pi * xc)[None, None, :]
+    u += 0.2 * np.sin(4 * np.pi * np.arange(sh["u"][0]) / Nz)[:, None, None] + 0.01 * rng.standard_normal(sh["u"])
+    v += 0.1 * np.cos(2 * np.pi * np.arange(sh["v"][0]) / Nz)[:, None, None] * np.sin(2 * np.pi * np.arange(sh["v"][2]) / Nx)[None, None, :]
+    return u, v, w
+
+
+def check_les_update(B, oracle, model, N=(24, 16, 12), stretched=False, tol=1e-6):
+    """LESModel::update (CPU path: GradientComputer + nu_sgs per cell) vs cfdnn_les_update; gate = BASELINE's closure
+    gate (nu_t within 1e-6 relative); in practice the only differences are the last bits of cbrt / acos / cos"""
+    import ctypes as C
+    Nx, Ny, Nz = N
+    u, v, w = les_velocity(N)
+    box = dict(**CHANNEL_BOX) if stretched else dict(x1=4 * np.pi, y0=-1.0, y1=1.0, z1=2 * np.pi)
+    with tempfile.TemporaryDirectory() as td:
+        pre = os.path.join(td, "in")
+        u.tofile(pre + "_u.f64"); v.tofile(pre + "_v.f64"); w.tofile(pre + "_w.f64")
+        kw = {k_: v_ for k_, v_ in box.items() if k_ in HARNESS_KEYS}
+        kw["in"] = pre
+        oracle.run_ref("les", Nx=Nx, Ny=Ny, Nz=Nz, model=model, out=os.path.join(td, "o"), **kw)
+        sh = R.shapes(Nx, Ny, Nz)["c"]
+        ref = np.fromfile(os.path.join(td, "o_nut.f64")).reshape(sh)
+        arrs = oracle.load_mesh_arrays(os.path.join(td, "o_mesh")) if stretched else None
+    if stretched:
+        md = B.stretched_mesh(Nx, Ny, Nz, arrs, Lx=box["x1"], Lz=box["z1"], y_lo=box["y0"], y_hi=box["y1"])
+    else:
+        md = B.mesh(Nx, Ny, Nz, Lx=box["x1"], Ly=box["y1"] - box["y0"], Lz=box["z1"])
+        md.y_lo, md.y_hi = box["y0"], box["y1"]
+    got = np.zeros(sh)
+    B.check(B.lib.cfdnn_les_update(C.byref(md), R.backend.LES_MODEL[model], 0.0, R.capi.dptr(u), R.capi.dptr(v),
+                                   R.capi.dptr(w), R.capi.dptr(got)))
+    a = got[0, 1:-1, 1:-1] if Nz == 1 else got[1:-1, 1:-1, 1:-1]
+    b = ref[0, 1:-1, 1:-1] if Nz == 1 else ref[1:-1, 1:-1, 1:-1]
+    assert b.max() > 0
+    err = R.rel_l2(a, b)
+    assert err <= tol, (model, err)
+    mask = np.ones_like(got, dtype=bool)
+    if Nz == 1:
+        mask[0, 1:-1, 1:-1] = False
+    else:
+        mask[1:-1, 1:-1, 1:-1] = False
+    assert not got[mask].any()                       # only interior cells are written, like the reference
+    return err
+
+
+def check_step_with_les(B, oracle, model="smagorinsky", tol=1e-9):
+    """RANSSolver::step with an LES SGS model attached (nu_t = nu_sgs at the top of every step, variable-viscosity
+    diffusion): 3-D channel, RK3"""
+    N = (16, 16, 16)
+    case = ("chan_les_" + model, N, "PPWWPP", "rk3", "skew", 8, 2, "pchan", (1.0, 0, 0), dict(**CHANNEL_UNIFORM))
+    name, N, bc, ti, scheme, fixed, nsteps, init, force, extra = case
+    u, v, w = step_init(N, init)
+    with tempfile.TemporaryDirectory() as td:
+        pre = os.path.join(td, "in")
+        u.tofile(pre + "_u.f64"); v.tofile(pre + "_v.f64"); w.tofile(pre + "_w.f64")
+        meta = R.run_ref("step", Nx=N[0], Ny=N[1], Nz=N[2], bc=bc, ti=ti, scheme=scheme, fixed=fixed, nsteps=nsteps,
+                         dt=0.01, nu=0.01, init="file:" + pre, fx=1.0, out=os.path.join(td, "ref"), model=model,
+                         **{k_: v_ for k_, v_ in extra.items() if k_ in HARNESS_KEYS})
+        ref = R.load_state(os.path.join(td, "ref_final"), *N)
+    h = make_solver(B, case)
+    B.check(B.lib.cfdnn_solver_set_les_model(h, R.backend.LES_MODEL[model], 0.0))
+    try:
+        res = [B.step(h) for _ in range(nsteps)]
+        got = B.state(h, *N)
+    finally:
+        B.lib.cfdnn_solver_destroy(h)
+    assert res == pytest.approx(meta["residuals"], rel=1e-8)
+    nut_ref = R.interior("nut", ref["nut"])
+    assert nut_ref.max() > 0
+    assert R.rel_l2(R.interior("nut", got["nut"]), nut_ref) <= 1e-6
+    compare_states(got, ref, tol, case[0])

@@ -62,6 +62,6 @@ def load_state(prefix, Nx, Ny, Nz, Ng=1):
 
 def load_mesh_arrays(pre):
     """y-metric arrays of a stretched mesh as dumped by ref_harness (dump_mesh)"""
-    return {k: np.ascontiguousarray(np.fromfile(f"{pre}_{k}.f64")) for k in ("dyv", "dyc", "aS", "aN", "aP", "yc")}
+    return {k: np.ascontiguousarray(np.fromfile(f"{pre}_{k}.f64")) for k in ("dyv", "dyc", "aS", "aN", "aP", "yc", "yf")}
 
 

@@ -5,6 +5,7 @@
 #include "cfdnn_b200_shim.hpp"
 #include "poisson_solver_multigrid.hpp"
 #include "turbulence_nn_tbnn.hpp"
+#include "turbulence_les.hpp"
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -140,7 +141,7 @@ int main(int argc, char** argv) {
 
     int rc = 0;
     std::string closure_json = "\"closure\": null";
-    double r_ref = 0, r_b = 0, eu = 0, ep = 0, emg = 0;
+    double r_ref = 0, r_b = 0, eu = 0, ep = 0, emg = 0, les_u = 1, les_nut = 1;
     int cyc_ref = 0, cyc_b = 0, mg_ref = 0, mg_b = 0;
     bool threw_invalid = false;
     try {
@@ -197,6 +198,24 @@ int main(int argc, char** argv) {
             bu.sync_from_gpu();
             if (rel_l2(bu.velocity().u_data(), ru.velocity().u_data()) > 1e-12 || bu.decomposition() != &single) rc = 1;
         }
+        // the reference's own LES model object handed to both solvers: device kernel under the B200 solver
+        {
+            Config lc = cfg;
+            lc.poisson_fixed_cycles = 4;
+            RANSSolver rl(mesh, lc);
+            rl.set_velocity_bc(bc);
+            rl.set_turbulence_model(std::make_unique<WALEModel>());
+            rl.initialize(v0);
+            b200::RANSSolverB200 bl(mesh, lc);
+            bl.set_velocity_bc(bc);
+            bl.set_turbulence_model(std::make_unique<WALEModel>());
+            bl.initialize(v0);
+            rl.step(); bl.step(); rl.step(); bl.step();
+            bl.sync_from_gpu();
+            les_u = rel_l2(bl.velocity().u_data(), rl.velocity().u_data());
+            les_nut = rel_l2(bl.nu_t().data(), rl.nu_t().data());
+            if (!(les_u <= 1e-10 && les_nut <= 1e-6)) rc = 1;
+        }
         if (!wdir.empty() && closure_section(wdir, closure_json) != 0) rc = 1;
     } catch (const std::exception& e) {
         std::cout.rdbuf(oc); std::cerr.rdbuf(oe);
@@ -209,8 +228,8 @@ int main(int argc, char** argv) {
         rc = 1;
     std::printf("{\"N\": %d, \"steps\": %d, \"residual_ref\": %.17g, \"residual_b200\": %.17g, \"u_rel_l2\": %.3e, "
                 "\"p_rel_l2\": %.3e, \"cycles_ref\": %d, \"cycles_b200\": %d, \"mg_cycles_ref\": %d, "
-                "\"mg_cycles_b200\": %d, \"mg_p_rel_l2\": %.3e, \"invalid_argument\": %s, %s, \"ok\": %s}\n",
+                "\"mg_cycles_b200\": %d, \"mg_p_rel_l2\": %.3e, \"invalid_argument\": %s, \"les_wale\": {\"u\": %.3e, \"nu_t\": %.3e}, %s, \"ok\": %s}\n",
                 N, nsteps, r_ref, r_b, eu, ep, cyc_ref, cyc_b, mg_ref, mg_b, emg, threw_invalid ? "true" : "false",
-                closure_json.c_str(), rc == 0 ? "true" : "false");
+                les_u, les_nut, closure_json.c_str(), rc == 0 ? "true" : "false");
     return rc;
 }

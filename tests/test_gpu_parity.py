@@ -272,3 +272,19 @@ def test_implicit_y_diffusion_channel_128x64x64_vs_oracle(gpu, oracle):
     got_meta, got = cases.run_step_backend(gpu, case)
     assert got_meta["cycles"] == meta["cycles"]
     cases.compare_states(got, ref, 1e-10, "chan128 implicit-y 1 step")
+
+
+# ---- static LES SGS closures
+@pytest.mark.parametrize("model", cases.LES_MODELS)
+def test_les_sgs_update_matches_reference(oracle, gpu, model):
+    cases.check_les_update(gpu, oracle, model, N=(24, 16, 12))
+
+
+@pytest.mark.parametrize("model", ["smagorinsky", "sigma"])
+def test_les_sgs_update_stretched_and_2d(oracle, gpu, model):
+    cases.check_les_update(gpu, oracle, model, N=(16, 24, 8), stretched=True)
+    cases.check_les_update(gpu, oracle, model, N=(32, 24, 1))
+
+
+def test_step_with_smagorinsky_matches_reference(gpu, oracle):
+    cases.check_step_with_les(gpu, oracle, "smagorinsky")

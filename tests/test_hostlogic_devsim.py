@@ -188,3 +188,19 @@ def test_implicit_y_diffusion_stretched_matches_reference(sim, oracle, case):
 @pytest.mark.parametrize("case", cases.STEP_IMPLICIT_2D_CASES, ids=[c[0] for c in cases.STEP_IMPLICIT_2D_CASES])
 def test_implicit_y_diffusion_2d_matches_reference(sim, oracle, case):
     cases.check_step_2d(sim, oracle, case)
+
+
+# ---- static LES SGS closures
+@pytest.mark.parametrize("model", cases.LES_MODELS)
+def test_les_sgs_update_matches_reference(oracle, sim, model):
+    cases.check_les_update(sim, oracle, model, N=(24, 16, 12))
+
+
+@pytest.mark.parametrize("model", ["smagorinsky", "sigma"])
+def test_les_sgs_update_stretched_and_2d(oracle, sim, model):
+    cases.check_les_update(sim, oracle, model, N=(16, 24, 8), stretched=True)
+    cases.check_les_update(sim, oracle, model, N=(32, 24, 1))
+
+
+def test_step_with_smagorinsky_matches_reference(sim, oracle):
+    cases.check_step_with_les(sim, oracle, "smagorinsky")
