@@ -176,6 +176,8 @@ def cpu_reference(workload, closure, steps, warmup):
         what = f"{N}^3 channel sub-grid" + (" (tanh-stretched y, 16 fixed cycles)" if "beta" in w else "")
     plane_ms = 0.0
     with tempfile.TemporaryDirectory() as td:
+        if closure not in ("none", "tbnn"):          # static LES SGS model: the reference's own 3-D LESModel::update
+            kw.update(model=closure)
         if closure == "tbnn":
             pkg = load_package()
             W, b, means, stds = pkg.backend.load_npz_preset(PRESETS_NPZ, PRESET)
@@ -242,7 +244,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--workload", default="tgv512", choices=sorted(WORKLOADS))
-    ap.add_argument("--closure", default=None, choices=["none", "tbnn"],
+    ap.add_argument("--closure", default=None, choices=["none", "tbnn", "smagorinsky", "wale", "vreman", "sigma"],
                     help="tbnn (default for tgv*): the NN-TBNN closure is attached to the step — the north star's "
                          "'RK3 + MG + NN-TBNN' workload; none: closure-free step")
     ap.add_argument("--adaptive-dt", action="store_true",
@@ -342,6 +344,8 @@ def main():
         nn = K.nn_create(B, "tbnn", W, b, means, stds)
         B.check(B.lib.cfdnn_nn_set_params(nn, nu_, 1.0, 1.0, 1e-10, 1.0))
         B.check(B.lib.cfdnn_solver_set_turbulence_model(h, nn))
+    elif args.closure in K.LES_MODEL:       # static LES SGS closure, default constant (reference turbulence_les.hpp)
+        B.check(B.lib.cfdnn_solver_set_les_model(h, K.LES_MODEL[args.closure], -1.0))
     if world > 1:
         comm_init(h)
 
@@ -546,6 +550,12 @@ def main():
                             "achieved": gbs(3 * 200.0 * cells_local, T["phases"][1] / args.steps),
                             "frac": frac(gbs(3 * 200.0 * cells_local, T["phases"][1] / args.steps)),
                             "note": "fused conv + diff + advance, 200 B per cell per stage (SURVEY 8(d))"}
+        if args.closure in K.LES_MODEL:
+            les_ms = T["phases"][0] / args.steps
+            roof["les"] = {"bound": "hbm", "kernel": f"k_les_sgs<{args.closure}> (velocity-gradient tensor + nu_sgs, one pass)",
+                           "ms_per_step": les_ms, "share_of_step": T["phases"][0] / T["step_ms"],
+                           "achieved": gbs(32.0 * cells_local, les_ms), "frac": frac(gbs(32.0 * cells_local, les_ms)),
+                           "note": "compulsory 32 B per cell: u, v, w read once, nu_t written"}
         if args.implicit_y:
             roof["implicit_y"] = {"ms_per_step": T["phases"][2] / args.steps, "launches_per_step": 9,
                                   "note": "Thomas solves per y-line of u, v, w after each of the 3 RK stages "
@@ -563,7 +573,8 @@ def main():
                 "config": {"workload": f"{args.workload}: {desc}, SSP-RK3, skew-symmetric convection, nu={nu_:.6f} "
                                        f"dt={dt_:g}, multigrid Poisson " +
                                        (f"{fixed} fixed V-cycles" if fixed else f"to tol_rhs={MG_TOL_RHS} (max {MG_MAXV} V-cycles)") +
-                                       (f", NN-TBNN closure ({PRESET}) on every cell every step (FP64 DMMA)" if nn else ", no closure") +
+                                       (f", NN-TBNN closure ({PRESET}) on every cell every step (FP64 DMMA)" if nn else
+                                        f", static LES SGS closure ({args.closure})" if args.closure in K.LES_MODEL else ", no closure") +
                                        (", adaptive dt (compute_adaptive_dt every step)" if args.adaptive_dt else "") +
                                        (", implicit y-diffusion" if args.implicit_y else ""),
                            "closure": args.closure,
