@@ -717,8 +717,18 @@ def check_les_update(B, oracle, model, N=(24, 16, 12), stretched=False, tol=1e-6
     a = got[0, 1:-1, 1:-1] if Nz == 1 else got[1:-1, 1:-1, 1:-1]
     b = ref[0, 1:-1, 1:-1] if Nz == 1 else ref[1:-1, 1:-1, 1:-1]
     assert b.max() > 0
-    err = R.rel_l2(a, b)
-    assert err <= tol, (model, err)
+    if model == "sigma" and Nz == 1:
+        # In a 2-D field the smallest singular value of the gradient tensor is 0, so the Sigma model's nu_t is 0
+        # analytically: what the reference returns is sqrt(round-off of the trigonometric eigenvalue formula), i.e. it
+        # depends on the last bit of acos/cos.  The comparison is therefore on the scale of a resolved nu_sgs
+        # ((C delta)^2 |grad u|), not of the noise itself.
+        g = max(np.abs(np.diff(u[0], axis=1)).max() / md.dx, np.abs(np.diff(u[0], axis=0)).max() / md.dy)
+        scale = (1.35 ** 2) * md.dx * md.dy * g
+        err = float(np.abs(a - b).max() / scale)
+        assert max(a.max(), b.max()) / scale < 1e-5 and err <= tol, (model, err, a.max() / scale, b.max() / scale)
+    else:
+        err = R.rel_l2(a, b)
+        assert err <= tol, (model, err)
     mask = np.ones_like(got, dtype=bool)
     if Nz == 1:
         mask[0, 1:-1, 1:-1] = False
