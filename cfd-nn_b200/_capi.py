@@ -113,6 +113,8 @@ _SIGS = {
                                   c_double_p, c_double_p, c_double_p, c_double_p]),
     "cfdnn_nn_update_dev": (C.c_int, [C.c_void_p, C.POINTER(MeshDesc), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                       C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "cfdnn_adaptive_dt_noalloc": (C.c_int, [C.POINTER(MeshDesc), C.POINTER(Config), C.c_void_p, C.c_void_p, C.c_void_p,
+                                            C.c_void_p, C.c_void_p, C.POINTER(C.c_double)]),
     "cfdnn_les_update": (C.c_int, [C.POINTER(MeshDesc), C.c_int, C.c_double, c_double_p, c_double_p, c_double_p, c_double_p]),
     "cfdnn_solver_set_les_model": (C.c_int, [C.c_void_p, C.c_int, C.c_double]),
     "cfdnn_nn_forward": (C.c_int, [C.c_void_p, c_double_p, c_double_p, C.c_size_t]),

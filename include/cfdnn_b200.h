@@ -170,6 +170,21 @@ int cfdnn_solver_step(cfdnn_solver* s, double* residual_out);           /* doubl
 int cfdnn_solver_run(cfdnn_solver* s, int nsteps, double* last_residual_out);
 int cfdnn_solver_compute_adaptive_dt(cfdnn_solver* s, double* dt_out);  /* compute_adaptive_dt :214 */
 int cfdnn_solver_poisson_stats(const cfdnn_solver* s, cfdnn_poisson_stats* out); /* poisson_stats() */
+/* NO COUNTERPART IN THE REFERENCE — added for callers that cannot call
+ * cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).  compute_adaptive_dt on caller-owned
+ * DEVICE fields (the solver's ghosted u, v, w layouts, e.g. from cfdnn_solver_device_ptr; nu_t_dev = NULL when no
+ * closure is attached) that allocates nothing: the kernels' scratch (per-block partial maxima, the five final maxima,
+ * the device copy of dyv) lives in one file-scope static __device__ array of CFDNN_NOALLOC_SCRATCH_BYTES that every
+ * GPU which loads the library holds until exit.  Limits: Ny <= CFDNN_NOALLOC_MAX_NY (else CFDNN_ERR_INVALID), Nghost 1,
+ * single domain.  `stream` is a cudaStream_t or NULL; the call synchronises that stream before it returns.  All calls
+ * share the array and it keeps the previous call's contents (each call rewrites what it reads): calls that overlap on
+ * the GPU — other streams, other host threads — race and must be serialised by the caller.  Same value as
+ * cfdnn_solver_compute_adaptive_dt on the same fields (bridged transport models excepted, see that entry). */
+#define CFDNN_NOALLOC_MAX_NY 4096
+#define CFDNN_NOALLOC_SCRATCH_BYTES 80224
+int cfdnn_adaptive_dt_noalloc(const cfdnn_mesh_desc* mesh, const cfdnn_config* cfg, const double* u_dev,
+                              const double* v_dev, const double* w_dev, const double* nu_t_dev, void* stream,
+                              double* dt_out);
 /* V-cycles of every Poisson solve since the last call (oracle: POISSON_STATS lines) */
 int cfdnn_solver_cycle_log(cfdnn_solver* s, int* cycles, int cap, int* n_out);
 /* set_turbulence_model(unique_ptr<TurbulenceModel>) :98 — solver borrows the closure */
