@@ -251,6 +251,9 @@ def main():
                     help="call compute_adaptive_dt + set_dt before every step (the CFL reductions in the timed region)")
     ap.add_argument("--implicit-y", action="store_true",
                     help="implicit y-diffusion (Thomas solve per y-line after every RK stage; channel workloads)")
+    ap.add_argument("--poisson", default="mg", choices=["mg", "fft"],
+                    help="Poisson back end of the projection: mg (default, the north-star path) or fft (FFTPoissonSolver: "
+                         "periodic x/z + walls y, i.e. the chan* workloads, single GPU)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-parity", action="store_true")
@@ -336,7 +339,8 @@ def main():
         mesh.y_lo, mesh.y_hi = y_lo, y_lo + Ly
     cfg = B.config(nu=nu_, dt=dt_, time_integrator=K.TI["rk3"], convective_scheme=K.SCHEME["skew"],
                    adaptive_dt=1 if args.adaptive_dt else 0, poisson_fixed_cycles=fixed, poisson_tol_rhs=MG_TOL_RHS,
-                   poisson_max_vcycles=MG_MAXV, implicit_y_diffusion=1 if args.implicit_y else 0)
+                   poisson_max_vcycles=MG_MAXV, implicit_y_diffusion=1 if args.implicit_y else 0,
+                   poisson_solver=1 if args.poisson == "fft" else 0)
     h = B.solver(mesh, cfg, bc, force)
     nn = None
     if args.closure == "tbnn":
@@ -556,6 +560,16 @@ def main():
                            "ms_per_step": les_ms, "share_of_step": T["phases"][0] / T["step_ms"],
                            "achieved": gbs(32.0 * cells_local, les_ms), "frac": frac(gbs(32.0 * cells_local, les_ms)),
                            "note": "compulsory 32 B per cell: u, v, w read once, nu_t written"}
+        if len(T["phases"]) > 3:
+            cells_b = 100.0 * cells_local
+            pms = T["phases"][3] / args.steps
+            roof["poisson"] = {"solver": args.poisson, "ms_per_step": pms, "solves_per_step": 3,
+                               "share_of_step": T["phases"][3] / T["step_ms"]}
+            if args.poisson == "fft":
+                roof["poisson"].update({"kernels": "k_fft_x_fwd, k_fft_z, k_fft_thomas, k_fft_z<inv>, k_fft_x_inv",
+                                        "achieved": gbs(3 * cells_b, pms), "frac": frac(gbs(3 * cells_b, pms)),
+                                        "note": "direct solve: 2-D FFT over x/z (shared-memory Stockham) + Thomas in y; "
+                                                "100 B per cell per solve (DESIGN 3.5)"})
         if args.implicit_y:
             roof["implicit_y"] = {"ms_per_step": T["phases"][2] / args.steps, "launches_per_step": 9,
                                   "note": "Thomas solves per y-line of u, v, w after each of the 3 RK stages "
@@ -571,8 +585,10 @@ def main():
                 "higher_is_better": True, "scaling": scaling_of(args.workload), "vs_baseline": None, "dtype": "f64",
                 "data": "synthetic",
                 "config": {"workload": f"{args.workload}: {desc}, SSP-RK3, skew-symmetric convection, nu={nu_:.6f} "
-                                       f"dt={dt_:g}, multigrid Poisson " +
-                                       (f"{fixed} fixed V-cycles" if fixed else f"to tol_rhs={MG_TOL_RHS} (max {MG_MAXV} V-cycles)") +
+                                       f"dt={dt_:g}, " +
+                                       ("FFT Poisson solver (direct: FFT in x/z + tridiagonal systems in y)" if args.poisson == "fft" else
+                                        "multigrid Poisson " + (f"{fixed} fixed V-cycles" if fixed else
+                                                                f"to tol_rhs={MG_TOL_RHS} (max {MG_MAXV} V-cycles)")) +
                                        (f", NN-TBNN closure ({PRESET}) on every cell every step (FP64 DMMA)" if nn else
                                         f", static LES SGS closure ({args.closure})" if args.closure in K.LES_MODEL else ", no closure") +
                                        (", adaptive dt (compute_adaptive_dt every step)" if args.adaptive_dt else "") +

@@ -57,7 +57,8 @@ class Config(C.Structure):
                 ("poisson_linf_safety", C.c_double),
                 ("poisson_nu1", C.c_int), ("poisson_nu2", C.c_int), ("poisson_chebyshev_degree", C.c_int),
                 ("turb_guard_enabled", C.c_int), ("turb_guard_interval", C.c_int),
-                ("turb_model", C.c_int), ("nu_t_max", C.c_double), ("implicit_y_diffusion", C.c_int)]
+                ("turb_model", C.c_int), ("nu_t_max", C.c_double), ("implicit_y_diffusion", C.c_int),
+                ("poisson_solver", C.c_int)]
 
 
 class CfdnnError(RuntimeError):
@@ -115,6 +116,12 @@ _SIGS = {
                                       C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "cfdnn_adaptive_dt_noalloc": (C.c_int, [C.POINTER(MeshDesc), C.POINTER(Config), C.c_void_p, C.c_void_p, C.c_void_p,
                                             C.c_void_p, C.c_void_p, C.POINTER(C.c_double)]),
+    "cfdnn_fft_create": (C.c_int, [C.POINTER(MeshDesc), C.POINTER(C.c_void_p)]),
+    "cfdnn_fft_destroy": (None, [C.c_void_p]),
+    "cfdnn_fft_set_bc": (C.c_int, [C.c_void_p, C.POINTER(C.c_int)]),
+    "cfdnn_fft_is_suitable": (C.c_int, [C.POINTER(C.c_int), C.c_int, C.c_int]),
+    "cfdnn_fft_solve_dev": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_int)]),
+    "cfdnn_fft_solve": (C.c_int, [C.c_void_p, c_double_p, c_double_p, C.POINTER(C.c_int)]),
     "cfdnn_les_update": (C.c_int, [C.POINTER(MeshDesc), C.c_int, C.c_double, c_double_p, c_double_p, c_double_p, c_double_p]),
     "cfdnn_solver_set_les_model": (C.c_int, [C.c_void_p, C.c_int, C.c_double]),
     "cfdnn_nn_forward": (C.c_int, [C.c_void_p, c_double_p, c_double_p, C.c_size_t]),

@@ -1,5 +1,6 @@
 // capi.cu — the C ABI of libcfdnn_b200.so (declared in include/cfdnn_b200.h).
 #include "mg.cuh"
+#include "fft.cuh"
 #include "comm.cuh"
 #ifndef CFDNN_MG_ONLY
 #include "solver.cuh"
@@ -28,6 +29,7 @@ void require_device() {
 using namespace cfdnn;
 
 struct cfdnn_mg { Multigrid impl; explicit cfdnn_mg(const cfdnn_mesh_desc& m) : impl(m) {} };
+struct cfdnn_fft { FftPoisson impl; explicit cfdnn_fft(const cfdnn_mesh_desc& m) : impl(m) {} };
 #ifndef CFDNN_MG_ONLY
 struct cfdnn_nn {
     NNClosure impl;
@@ -71,6 +73,7 @@ void cfdnn_config_default(cfdnn_config* c) {             // include/config.hpp:6
     c->turb_guard_enabled = 1; c->turb_guard_interval = 5;
     c->turb_model = CFDNN_TURB_NONE; c->nu_t_max = 1.0;
     c->implicit_y_diffusion = 0;
+    c->poisson_solver = CFDNN_POISSON_MG;
 }
 
 // ---------------------------------------------------------------- multigrid
@@ -81,6 +84,31 @@ int cfdnn_mg_create(const cfdnn_mesh_desc* mesh, cfdnn_mg** out) {
     });
 }
 void cfdnn_mg_destroy(cfdnn_mg* mg) { delete mg; }
+
+int cfdnn_fft_create(const cfdnn_mesh_desc* mesh, cfdnn_fft** out) {
+    return guarded([&] {
+        if (!mesh || !out) throw std::invalid_argument("cfdnn_fft_create: null argument");
+        *out = new cfdnn_fft(*mesh);
+    });
+}
+void cfdnn_fft_destroy(cfdnn_fft* f) { delete f; }
+int cfdnn_fft_set_bc(cfdnn_fft* f, const int bc[6]) { return guarded([&] { f->impl.set_bc(bc); }); }
+int cfdnn_fft_is_suitable(const int bc[6], int uniform_x, int uniform_z) {       // poisson_solver_fft.cpp:284-292
+    return bc[0] == CFDNN_PBC_PERIODIC && bc[1] == CFDNN_PBC_PERIODIC && bc[4] == CFDNN_PBC_PERIODIC &&
+           bc[5] == CFDNN_PBC_PERIODIC && uniform_x && uniform_z;
+}
+int cfdnn_fft_solve_dev(cfdnn_fft* f, const double* rhs_dev, double* p_dev, void* stream, int* iterations) {
+    return guarded([&] {
+        const int it = f->impl.solve_dev(rhs_dev, p_dev, static_cast<cudaStream_t>(stream));
+        if (iterations) *iterations = it;
+    });
+}
+int cfdnn_fft_solve(cfdnn_fft* f, const double* rhs, double* p, int* iterations) {
+    return guarded([&] {
+        const int it = f->impl.solve_host(rhs, p);
+        if (iterations) *iterations = it;
+    });
+}
 int cfdnn_mg_set_bc(cfdnn_mg* mg, const int bc[6]) { return guarded([&] { mg->impl.set_bc(bc); }); }
 int cfdnn_mg_num_levels(const cfdnn_mg* mg) { return mg->impl.num_levels(); }
 int cfdnn_mg_solve(cfdnn_mg* mg, const double* rhs, double* p, const cfdnn_poisson_cfg* cfg,

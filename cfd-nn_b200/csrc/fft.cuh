@@ -1,0 +1,43 @@
+// fft.cuh — FFT-hybrid Poisson solver for channels (periodic x/z, Neumann walls in y): 2-D FFT over (x, z) with
+// hand-written shared-memory Stockham kernels + one tridiagonal (Thomas) system in y per Fourier mode.
+// Stands in for FFTPoissonSolver (reference include/poisson_solver_fft.hpp:18-50, src/poisson_solver_fft.cpp);
+// see fft.cu.  Single GPU (no z-slab variant).
+#pragma once
+#include <vector>
+#include "common.cuh"
+
+namespace cfdnn {
+
+class FftPoisson {
+public:
+    explicit FftPoisson(const cfdnn_mesh_desc& m);
+    // x and z must be periodic, y Neumann on both walls (include/poisson_solver_fft.hpp:27-30 allows Dirichlet in y
+    // as well; not supported here)
+    void set_bc(const int bc[6]);
+    // rhs, p: device arrays in the solver's ghosted cell layout; returns 1 like the reference's direct solve
+    int solve_dev(const double* rhs, double* p, cudaStream_t st);
+    // host arrays, same layout (test/FFI convenience: FFTPoissonSolver has only solve_device)
+    int solve_host(const double* rhs, double* p);
+    static bool size_supported(int n);          // n = 2^a 3^b 5^c, 2 <= n <= 1024
+    size_t field_elems() const { return (size_t)cp_ * (Nz_ + 2 * Ng_); }
+
+private:
+    void setup_tables(const cfdnn_mesh_desc& m);
+    int Nx_, Ny_, Nz_, Ng_;
+    int Nxh_, Pxh_;                 // kept x modes Nx/2+1 and their padded pitch (complex elements)
+    int cs_, cp_;                   // row and plane pitch of the ghosted cell layout
+    int Lx_, Lz_;                   // lines per CTA of the x and z transforms
+    int nrx_, nrz_;
+    int radx_[12], radz_[12];       // radix sequences
+    double total_volume_;
+    bool bc_set_ = false;
+    DevBuf<double2> spec_;          // [Nz][Ny][Pxh] half spectrum
+    DevBuf<double> cprime_;         // [Nz][Ny][Pxh] Thomas c' (depends on the mesh only)
+    DevBuf<double2> twx_, twz_;     // exp(-2 pi i n / N)
+    DevBuf<double> lamx_, lamz_;    // Laplacian symbols
+    DevBuf<double> lo_, up_, base_, dyv_;   // tridiagonal rows, volume weights
+    DevBuf<double> partial_;        // reduction scratch + mean
+    bool cprime_ready_ = false;
+};
+
+}  // namespace cfdnn

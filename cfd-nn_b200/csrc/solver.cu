@@ -99,6 +99,12 @@ Solver::Solver(const cfdnn_mesh_desc& m, const cfdnn_config& c) : mesh_(m), cfg_
 
     mg_ = std::make_unique<Multigrid>(m);
     if (is2d_) mg_->set_2d_plane(Ng, /*dup=*/true);
+    if (c.poisson_solver == CFDNN_POISSON_FFT) {                 // selection: src/solver.cpp:432-447
+        if (is2d_) throw std::invalid_argument("Solver: poisson_solver = FFT needs a 3-D mesh (the 2-D variant FFT2D is not built)");
+        fft_ = std::make_unique<FftPoisson>(m);
+    } else if (c.poisson_solver != CFDNN_POISSON_MG) {
+        throw std::invalid_argument("Solver: poisson_solver must be CFDNN_POISSON_MG or CFDNN_POISSON_FFT");
+    }
     if (const char* e = std::getenv("CFDNN_MOMENTUM_Z")) mom_z_ = std::atoi(e) != 0;          // 0: one-thread-per-point kernel
     if (const char* e = std::getenv("CFDNN_MOMENTUM_EXACT")) mom_exact_ = std::atoi(e) != 0;  // 1: exact divisions everywhere
     {
@@ -146,10 +152,20 @@ void Solver::set_velocity_bc(const int bc[6]) {
     int pbc[6];
     for (int d = 0; d < 6; ++d) pbc[d] = vbc_[d] == CFDNN_VBC_PERIODIC ? CFDNN_PBC_PERIODIC : CFDNN_PBC_NEUMANN;
     mg_->set_bc(pbc);
+    // FFT was requested: it stays selected while x and z are periodic and y is walled, otherwise the multigrid takes
+    // over, as the reference does when the BCs change under a selected FFT solver (src/solver.cpp:727-739)
+    fft_active_ = false;
+    if (fft_) {
+        const bool ok = pbc[0] == CFDNN_PBC_PERIODIC && pbc[1] == CFDNN_PBC_PERIODIC && pbc[4] == CFDNN_PBC_PERIODIC &&
+                        pbc[5] == CFDNN_PBC_PERIODIC && pbc[2] == CFDNN_PBC_NEUMANN && pbc[3] == CFDNN_PBC_NEUMANN;
+        if (ok) { fft_->set_bc(pbc); fft_active_ = true; }
+    }
     update_links();
 }
 
 void Solver::comm_init(Comm* c) {
+    if (c && c->nranks > 1 && fft_)
+        throw std::invalid_argument("comm_init: poisson_solver = FFT is single-GPU (the reference's FFT_MPI variant is not built)");
     if (c && c->nranks > 1) {
         // The slab layout is block distribution with EQUAL slabs (reference Decomposition::nz_for_rank with
         // Nz_global % nprocs == 0, include/decomposition.hpp:81-92): the coarse-level offsets (rank * Nz / 2),
@@ -447,7 +463,16 @@ void Solver::copy_correct_velocity() {
 }
 
 int Solver::poisson_solve(const cfdnn_poisson_cfg& pc) {
+    if (fft_active_) {                               // dispatch on the selected solver, src/solver_time.cpp:875-884
+        PhaseEv* pe = ph_begin(CFDNN_PHASE_POISSON);
+        const int it = fft_->solve_dev(rhs_, pcorr_, st_);
+        ph_end(pe);
+        cycle_log.push_back(it);
+        return it;
+    }
+    PhaseEv* pe = ph_begin(CFDNN_PHASE_POISSON);
     const int cyc = mg_->solve_dev(rhs_, pcorr_, pc, st_);
+    ph_end(pe);
     cycle_log.push_back(cyc);
     return cyc;
 }

@@ -14,6 +14,7 @@
 #pragma once
 #include "common.cuh"
 #include "mg.cuh"
+#include "fft.cuh"
 #include <vector>
 #include <memory>
 
@@ -98,6 +99,8 @@ private:
     size_t npartial_ = 0;
 
     std::unique_ptr<Multigrid> mg_;
+    std::unique_ptr<FftPoisson> fft_;        // cfg.poisson_solver == CFDNN_POISSON_FFT (periodic x/z, walls y)
+    bool fft_active_ = false;                // the current velocity BCs allow it (else the multigrid takes over)
     NNClosure* nn_ = nullptr;
     bool ext_nut_ = false, ext_transport_ = false;
     int les_model_ = 0;                    // CFDNN_LES_*

@@ -122,11 +122,17 @@ typedef struct cfdnn_config {
      * predictor / RK stage (src/solver_time.cpp:658-735, src/solver_time_kernels_implicit.cpp); no effect when y is
      * periodic; relaxes the diffusive dt limit to the x/z spacings (src/solver.cpp:1481, 3697-3712) */
     int implicit_y_diffusion;
+    /* Poisson back end of the projection (Config::poisson_solver, include/config.hpp:47-56, 151): CFDNN_POISSON_MG
+     * (default; also what Auto means here — the reference's CPU build, the parity oracle, always takes MG) or
+     * CFDNN_POISSON_FFT = FFTPoissonSolver (periodic x/z, walls y, uniform or stretched y; single GPU) */
+    int poisson_solver;
 } cfdnn_config;
+enum { CFDNN_POISSON_MG = 0, CFDNN_POISSON_FFT = 1 };
 
 typedef struct cfdnn_solver cfdnn_solver;   /* stands in for RANSSolver              */
 typedef struct cfdnn_mg cfdnn_mg;           /* stands in for MultigridPoissonSolver  */
 typedef struct cfdnn_nn cfdnn_nn;           /* stands in for TurbulenceNNTBNN / NNMLP */
+typedef struct cfdnn_fft cfdnn_fft;         /* stands in for FFTPoissonSolver        */
 
 const char* cfdnn_last_error(void);
 int cfdnn_version(void);
@@ -152,6 +158,19 @@ int cfdnn_mg_solve_dev(cfdnn_mg* mg, const double* rhs_dev, double* p_dev,
                        const cfdnn_poisson_cfg* cfg, cfdnn_poisson_stats* stats);
 /* device timing of the last solve's V-cycles (CUDA events), for bench.py's roofline object */
 int cfdnn_mg_last_timing(const cfdnn_mg* mg, double* vcycle_ms_total, int* n_vcycles);
+
+/* ---- FFTPoissonSolver (include/poisson_solver_fft.hpp:18-50; src/poisson_solver_fft.cpp, GPU builds only) ----
+ * 2-D FFT over the periodic x/z directions + one tridiagonal system in y per mode; Nx, Nz = 2^a 3^b 5^c <= 1024 */
+int cfdnn_fft_create(const cfdnn_mesh_desc* mesh, cfdnn_fft** out);    /* ctor :20            */
+void cfdnn_fft_destroy(cfdnn_fft* f);                                   /* dtor :21            */
+/* set_bc :27-30 — x, z periodic (else CFDNN_ERR_RUNTIME like the reference's runtime_error), y Neumann */
+int cfdnn_fft_set_bc(cfdnn_fft* f, const int bc[6]);
+/* is_suitable :38-41 */
+int cfdnn_fft_is_suitable(const int bc[6], int uniform_x, int uniform_z);
+/* solve_device(double* rhs, double* p) :46 — device arrays in the ghosted cell layout, on `stream` (a cudaStream_t or
+ * NULL); *iterations = 1 (direct solve).  cfdnn_fft_solve: the same with host arrays, copies inside. */
+int cfdnn_fft_solve_dev(cfdnn_fft* f, const double* rhs_dev, double* p_dev, void* stream, int* iterations);
+int cfdnn_fft_solve(cfdnn_fft* f, const double* rhs, double* p, int* iterations);
 
 /* ---- RANSSolver (include/solver.hpp:86-311) ---- */
 int cfdnn_solver_create(const cfdnn_mesh_desc* mesh, const cfdnn_config* cfg, cfdnn_solver** out); /* ctor :88 */
@@ -205,7 +224,8 @@ int cfdnn_solver_device_ptr(cfdnn_solver* s, int field, double** dev_out, size_t
 int cfdnn_solver_set_external_nu_t(cfdnn_solver* s, int on);
 /* device ms of the last step()/run() spent in the closure update (TurbulenceModel::update inside step(),
  * src/solver.cpp:1284-1324) and in the fused momentum kernels (convective + diffusive + advance) */
-enum { CFDNN_PHASE_CLOSURE = 0, CFDNN_PHASE_MOMENTUM = 1, CFDNN_PHASE_IMPLICIT_Y = 2, CFDNN_PHASE_COUNT = 4 };
+enum { CFDNN_PHASE_CLOSURE = 0, CFDNN_PHASE_MOMENTUM = 1, CFDNN_PHASE_IMPLICIT_Y = 2, CFDNN_PHASE_POISSON = 3,
+       CFDNN_PHASE_COUNT = 4 };   /* POISSON: the Poisson solves (multigrid or FFT), copies in and out included */
 int cfdnn_solver_phase_timing(const cfdnn_solver* s, double ms[CFDNN_PHASE_COUNT]);
 /* measurement aid for bench.py's roofline: ms per launch of the level-0 temporally blocked smoother
  * kernel (2 Chebyshev sweeps per launch), `reps` launches timed with CUDA events on the solver's

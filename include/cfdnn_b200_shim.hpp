@@ -222,6 +222,9 @@ inline cfdnn_config solver_cfg(const Config& c) {
                  : c.turb_model == TurbulenceModelType::NNMLP ? CFDNN_TURB_NN_MLP : CFDNN_TURB_NONE;
     o.nu_t_max = c.nu_t_max;
     o.implicit_y_diffusion = c.implicit_y_diffusion ? 1 : 0;
+    // Config::poisson_solver (include/config.hpp:151): an explicit FFT request maps to this backend's FFT solver; Auto
+    // stays on the multigrid (what the reference's CPU build, the parity oracle, selects)
+    o.poisson_solver = c.poisson_solver == PoissonSolverType::FFT ? CFDNN_POISSON_FFT : CFDNN_POISSON_MG;
     return o;
 }
 

@@ -764,3 +764,118 @@ def check_step_with_les(B, oracle, model="smagorinsky", tol=1e-9):
     assert nut_ref.max() > 0
     assert R.rel_l2(R.interior("nut", got["nut"]), nut_ref) <= 1e-6
     compare_states(got, ref, tol, case[0])
+
+
+# ---------------------------------------------------------------- FFT Poisson
+# (name, N, stretched).  Sizes cover radix 4 / 2 / 3 / 5 stages, odd row counts (the last x line carries one row),
+# tiles with padding columns, and lines long enough for 4 and 2 lines per CTA.
+FFT_CASES = [
+    ("fft_32x16x32", (32, 16, 32), False),
+    ("fft_ragged_24x13x20", (24, 13, 20), False),
+    ("fft_radix35_30x8x45", (30, 8, 45), False),
+    ("fft_stretched_32x24x16", (32, 24, 16), True),
+    ("fft_long_lines_512x6x8", (512, 6, 8), False),
+    ("fft_long_z_8x5x1024", (8, 5, 1024), False),
+]
+
+
+def _fft_oracle():
+    import sys
+    sys.path.insert(0, os.path.join(os.path.dirname(__file__), "..", "oracle"))
+    import fft_poisson
+    return fft_poisson
+
+
+def check_fft_solve(B, case, tol=1e-11):
+    """cfdnn_fft_solve (FFTPoissonSolver::solve_device) vs oracle/fft_poisson.py — the numpy restatement that
+    tests/test_fft_oracle.py pins to the reference's multigrid; interior AND ghost cells, two solves in a row on the
+    same handle (the second one takes the tabulated c')."""
+    import ctypes as C
+    F = _fft_oracle()
+    name, N, stretched = case
+    Nx, Ny, Nz = N
+    box = dict(**CHANNEL_UNIFORM)
+    dx, dz, dy = box["x1"] / Nx, box["z1"] / Nz, (box["y1"] - box["y0"]) / Ny
+    if stretched:
+        arrs = R.backend.stretched_y_metrics(Ny, box["y0"], box["y1"], 2.0)
+        md = B.stretched_mesh(Nx, Ny, Nz, arrs, Lx=box["x1"], Lz=box["z1"], y_lo=box["y0"], y_hi=box["y1"])
+        kw = dict(dyv=arrs["dyv"][1:-1], aS=arrs["aS"][1:-1], aN=arrs["aN"][1:-1])
+    else:
+        md = B.mesh(Nx, Ny, Nz, Lx=box["x1"], Ly=box["y1"] - box["y0"], Lz=box["z1"])
+        kw = dict(dy=dy)
+    h = C.c_void_p()
+    B.check(B.lib.cfdnn_fft_create(C.byref(md), C.byref(h)))
+    try:
+        B.check(B.lib.cfdnn_fft_set_bc(h, (C.c_int * 6)(*[R.PBC[c] for c in "PPNNPP"])))
+        errs = []
+        for seed in (0, 1):
+            rhs, _ = mg_inputs(N, seed=seed)
+            rhs[1:-1, 1:-1, 1:-1] += 0.37                       # a non-zero mean: the solver must remove it
+            ref = F.with_ghosts(F.solve(rhs[1:-1, 1:-1, 1:-1], dx, dz, **kw))
+            got = np.full_like(rhs, np.nan)
+            it = C.c_int()
+            B.check(B.lib.cfdnn_fft_solve(h, R.capi.dptr(rhs), R.capi.dptr(got), C.byref(it)))
+            assert it.value == 1
+            gi, ri = got[1:-1], ref[1:-1]                       # interior planes with their x and y ghosts
+            assert np.isfinite(gi).all()
+            err = np.abs(gi - ri).max() / np.abs(ri).max()
+            assert err <= tol, (name, seed, err)
+            assert np.array_equal(got[0], got[Nz]) and np.array_equal(got[Nz + 1], got[1])
+            errs.append(err)
+        return errs
+    finally:
+        B.lib.cfdnn_fft_destroy(h)
+
+
+def check_fft_rejections(B):
+    import ctypes as C
+    md = B.mesh(14, 8, 16)                                      # 14 = 2 * 7
+    h = C.c_void_p()
+    with pytest.raises(R.capi.CfdnnError) as e:
+        B.check(B.lib.cfdnn_fft_create(C.byref(md), C.byref(h)))
+    assert e.value.code == 1 and "2^a 3^b 5^c" in str(e.value)
+    md = B.mesh(16, 8, 16)
+    B.check(B.lib.cfdnn_fft_create(C.byref(md), C.byref(h)))
+    try:
+        with pytest.raises(R.capi.CfdnnError) as e:             # reference: std::runtime_error
+            B.check(B.lib.cfdnn_fft_set_bc(h, (C.c_int * 6)(*[R.PBC[c] for c in "NNNNPP"])))
+        assert e.value.code == 2 and "periodic BC in x" in str(e.value)
+        rhs = np.zeros((18, 10, 18))
+        with pytest.raises(R.capi.CfdnnError):                  # set_bc has not succeeded yet
+            B.check(B.lib.cfdnn_fft_solve(h, R.capi.dptr(rhs), R.capi.dptr(rhs.copy()), None))
+    finally:
+        B.lib.cfdnn_fft_destroy(h)
+    assert B.lib.cfdnn_fft_is_suitable((C.c_int * 6)(*[R.PBC[c] for c in "PPNNPP"]), 1, 1) == 1
+    assert B.lib.cfdnn_fft_is_suitable((C.c_int * 6)(*[R.PBC[c] for c in "PPNNNN"]), 1, 1) == 0
+
+
+def check_step_with_fft(B, oracle, stretched=False, N=(16, 16, 16), nsteps=2):
+    """RANSSolver::step with poisson_solver = FFT against the reference's step with its multigrid converged to
+    round-off (the reference's CPU build has no FFT solver; both invert the same discrete Laplacian, so velocity and
+    pressure gradient agree to the multigrid's tolerance; p itself up to the gauge constant)."""
+    extra = dict(**(CHANNEL_BOX if stretched else CHANNEL_UNIFORM))
+    case = ("chan_fft", N, "PPWWPP", "rk3", "skew", 0, nsteps, "pchan", (1.0, 0, 0), extra)
+    u, v, w = step_init(N, "pchan")
+    with tempfile.TemporaryDirectory() as td:
+        pre = os.path.join(td, "in")
+        u.tofile(pre + "_u.f64"); v.tofile(pre + "_v.f64"); w.tofile(pre + "_w.f64")
+        R.run_ref("step", Nx=N[0], Ny=N[1], Nz=N[2], bc="PPWWPP", ti="rk3", scheme="skew", fixed=0, nsteps=nsteps,
+                  dt=0.01, nu=0.01, init="file:" + pre, fx=1.0, out=os.path.join(td, "ref"), tol_rhs=1e-13, maxv=200,
+                  **{k_: v_ for k_, v_ in extra.items() if k_ in HARNESS_KEYS})
+        ref = R.load_state(os.path.join(td, "ref_final"), *N)
+        arrs = R.load_mesh_arrays(os.path.join(td, "ref_mesh")) if stretched else None
+    h = make_solver(B, case, mesh_arrays=arrs, poisson_solver=1)
+    try:
+        for _ in range(nsteps):
+            B.step(h)
+        assert B.cycles(h) == [1] * (3 * nsteps)                 # direct solve: "1 iteration" per projection
+        got = B.state(h, *N)
+    finally:
+        B.lib.cfdnn_solver_destroy(h)
+    for n in ("u", "v", "w"):
+        a, b = R.interior(n, got[n]), R.interior(n, ref[n])
+        scale = np.abs(R.interior("u", ref["u"])).max()
+        assert np.abs(a - b).max() <= 1e-9 * scale, (n, np.abs(a - b).max(), scale)
+    a, b = R.interior("p", got["p"]), R.interior("p", ref["p"])
+    a = a - a.mean(); b = b - b.mean()
+    assert np.abs(a - b).max() <= 1e-8 * max(np.abs(b).max(), 1e-300), np.abs(a - b).max()

@@ -288,3 +288,22 @@ def test_les_sgs_update_stretched_and_2d(oracle, gpu, model):
 
 def test_step_with_smagorinsky_matches_reference(gpu, oracle):
     cases.check_step_with_les(gpu, oracle, "smagorinsky")
+
+
+# ---- FFT Poisson solver
+@pytest.mark.parametrize("case", cases.FFT_CASES, ids=[c[0] for c in cases.FFT_CASES])
+def test_fft_poisson_matches_restatement(gpu, case):
+    cases.check_fft_solve(gpu, case)
+
+
+def test_fft_poisson_128x64x128(gpu):
+    cases.check_fft_solve(gpu, ("fft_128x64x128", (128, 64, 128), False))
+
+
+def test_fft_poisson_rejections(gpu):
+    cases.check_fft_rejections(gpu)
+
+
+@pytest.mark.parametrize("stretched", [False, True], ids=["uniform", "stretched"])
+def test_step_with_fft_poisson_matches_converged_reference(gpu, oracle, stretched):
+    cases.check_step_with_fft(gpu, oracle, stretched=stretched)

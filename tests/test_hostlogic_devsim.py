@@ -204,3 +204,17 @@ def test_les_sgs_update_stretched_and_2d(oracle, sim, model):
 
 def test_step_with_smagorinsky_matches_reference(sim, oracle):
     cases.check_step_with_les(sim, oracle, "smagorinsky")
+
+
+# ---- FFT Poisson solver: host logic + kernel arithmetic on the test double
+@pytest.mark.parametrize("case", cases.FFT_CASES[:4], ids=[c[0] for c in cases.FFT_CASES[:4]])
+def test_fft_poisson_matches_restatement(sim, case):
+    cases.check_fft_solve(sim, case)
+
+
+def test_fft_poisson_rejections(sim):
+    cases.check_fft_rejections(sim)
+
+
+def test_step_with_fft_poisson_matches_converged_reference(oracle, sim):
+    cases.check_step_with_fft(sim, oracle)
