@@ -17,6 +17,7 @@
 #include "fft.cuh"
 #include <cmath>
 #include <cstring>
+#include <cstdlib>
 
 namespace cfdnn {
 namespace {
@@ -45,14 +46,49 @@ template <int R>
 __device__ __forceinline__ void fft_stage(const double2* __restrict__ A, double2* __restrict__ B, int N, int Ns, int L, int logL,
                                           const double2* __restrict__ tw) {
     const int M = N / R, tstep = N / (Ns * R);
+    const int logNs = (Ns & (Ns - 1)) == 0 ? 31 - __clz(Ns) : -1;     // 4s and 2s come first: almost always a shift
     for (int t = threadIdx.x; t < M * L; t += blockDim.x) {
         const int l = t & (L - 1), j = t >> logL;
-        const int k = j % Ns, d0 = (j / Ns) * Ns * R + k;
+        const int k = logNs >= 0 ? (j & (Ns - 1)) : j % Ns;
+        const int d0 = (j - k) * R + k;                                 // (j / Ns) Ns R + k
         double2 v[R];
 #pragma unroll
-        for (int r = 0; r < R; ++r) {
-            v[r] = A[sw(j + r * M, l, L)];
-            if (r > 0 && k > 0) v[r] = cmul(v[r], tw[r * k * tstep]);
+        for (int r = 0; r < R; ++r) v[r] = A[sw(j + r * M, l, L)];
+        if constexpr (R == 8) {
+            if (k > 0) {                    // w^r, r = 1..7, from three table entries (w, w^2, w^4)
+                const double2 w1 = tw[k * tstep], w2 = tw[2 * k * tstep], w4 = tw[4 * k * tstep];
+                const double2 w3 = cmul(w1, w2), w5 = cmul(w4, w1), w6 = cmul(w4, w2);
+                v[1] = cmul(v[1], w1); v[2] = cmul(v[2], w2); v[3] = cmul(v[3], w3); v[4] = cmul(v[4], w4);
+                v[5] = cmul(v[5], w5); v[6] = cmul(v[6], w6); v[7] = cmul(v[7], cmul(w4, w3));
+            }
+            // decimation in frequency: X[2m] = DFT4(v[q] + v[q+4])[m], X[2m+1] = DFT4((v[q] - v[q+4]) W8^q)[m]
+            const double h = 0.70710678118654752440;
+            const double2 a0 = cadd(v[0], v[4]), a1 = cadd(v[1], v[5]), a2 = cadd(v[2], v[6]), a3 = cadd(v[3], v[7]);
+            const double2 b0 = csub(v[0], v[4]), e1 = csub(v[1], v[5]), e2 = csub(v[2], v[6]), e3 = csub(v[3], v[7]);
+            const double2 b1 = c2(h * (e1.x + e1.y), h * (e1.y - e1.x));      // e1 (1 - i) / sqrt 2
+            const double2 b2 = c2(e2.y, -e2.x);                                // -i e2
+            const double2 b3 = c2(h * (e3.y - e3.x), -h * (e3.x + e3.y));     // e3 (-1 - i) / sqrt 2
+            {
+                const double2 t0 = cadd(a0, a2), t1 = csub(a0, a2), t2 = cadd(a1, a3), e = csub(a1, a3);
+                const double2 t3 = c2(e.y, -e.x);
+                B[sw(d0, l, L)] = cadd(t0, t2);
+                B[sw(d0 + 2 * Ns, l, L)] = cadd(t1, t3);
+                B[sw(d0 + 4 * Ns, l, L)] = csub(t0, t2);
+                B[sw(d0 + 6 * Ns, l, L)] = csub(t1, t3);
+            }
+            {
+                const double2 t0 = cadd(b0, b2), t1 = csub(b0, b2), t2 = cadd(b1, b3), e = csub(b1, b3);
+                const double2 t3 = c2(e.y, -e.x);
+                B[sw(d0 + Ns, l, L)] = cadd(t0, t2);
+                B[sw(d0 + 3 * Ns, l, L)] = cadd(t1, t3);
+                B[sw(d0 + 5 * Ns, l, L)] = csub(t0, t2);
+                B[sw(d0 + 7 * Ns, l, L)] = csub(t1, t3);
+            }
+            continue;
+        }
+        if (k > 0) {
+#pragma unroll
+            for (int r = 1; r < R; ++r) v[r] = cmul(v[r], tw[r * k * tstep]);
         }
         if (R == 2) {
             B[sw(d0, l, L)] = cadd(v[0], v[1]);
@@ -83,7 +119,8 @@ __device__ double2* fft_lines(double2* A, double2* B, int N, int L, int logL, co
     int Ns = 1;
     for (int s = 0; s < rad.n; ++s) {
         const int R = rad.r[s];
-        if (R == 4) fft_stage<4>(A, B, N, Ns, L, logL, tw);
+        if (R == 8) fft_stage<8>(A, B, N, Ns, L, logL, tw);
+        else if (R == 4) fft_stage<4>(A, B, N, Ns, L, logL, tw);
         else if (R == 2) fft_stage<2>(A, B, N, Ns, L, logL, tw);
         else if (R == 3) fft_stage<3>(A, B, N, Ns, L, logL, tw);
         else fft_stage<5>(A, B, N, Ns, L, logL, tw);
@@ -94,71 +131,42 @@ __device__ double2* fft_lines(double2* A, double2* B, int N, int L, int logL, co
     return A;
 }
 
-// ---------------------------------------------------------------- volume-weighted sum of the right-hand side
-// sum f dyv over the interior (kernel_pack_and_partial_sum, src/poisson_solver_fft.cpp:53-89): a CTA strides over
-// (k, j) rows, per-block partials, fixed-order final pass (bitwise-reproducible)
-__global__ void __launch_bounds__(256)
-k_fft_wsum(const double* __restrict__ rhs, const double* __restrict__ dyv, int Nx, int Ny, int Nz, int Ng, int cs, int cp,
-           double* __restrict__ partial) {
-    __shared__ double red[256];
-    double acc = 0.0;
-    const int rows = Ny * Nz;
-    for (int row = blockIdx.x; row < rows; row += gridDim.x) {
-        const int k = row / Ny, j = row - k * Ny;
-        const double* src = rhs + (size_t)(k + Ng) * cp + (size_t)(j + Ng) * cs + Ng;
-        double a = 0.0;
-        for (int i = threadIdx.x; i < Nx; i += blockDim.x) a += src[i];
-        acc += a * dyv[j];
-    }
-    red[threadIdx.x] = acc;
-    __syncthreads();
-    for (int s = 128; s > 0; s >>= 1) {
-        if ((int)threadIdx.x < s) red[threadIdx.x] += red[threadIdx.x + s];
-        __syncthreads();
-    }
-    if (threadIdx.x == 0) partial[1 + blockIdx.x] = red[0];
-}
-__global__ void k_fft_mean(double* __restrict__ partial, int n, double inv_volume) {       // :91-110, :930-938
-    double s = 0.0;
-    for (int i = 0; i < n; ++i) s += partial[1 + i];
-    partial[0] = s * inv_volume;
-}
-
 // ---------------------------------------------------------------- x transforms (rows of the ghosted cell layout)
 // forward: line l of the CTA carries rows 2l (real part) and 2l+1 (imaginary part); row = k Ny + j
 __global__ void __launch_bounds__(FFT_THREADS)
-k_fft_x_fwd(const double* __restrict__ rhs, const double* __restrict__ mean_p, double2* __restrict__ spec, int Nx, int Ny,
+k_fft_x_fwd(const double* __restrict__ rhs, double2* __restrict__ spec, int Nx, int Ny,
             int Nz, int Ng, int cs, int cp, int Pxh, int L, int logL, Radices rad, const double2* __restrict__ tw) {
     CFDNN_DYN_SMEM(double2, sm);
     double2* A = sm;
     double2* B = sm + (size_t)Nx * L;
     const int rows = Ny * Nz;
-    const double mean = mean_p[0];
     const int line0 = blockIdx.x * L;
-    for (int t = threadIdx.x; t < Nx * L; t += blockDim.x) {
-        const int l = t / Nx, n = t - l * Nx;
-        const int ra = 2 * (line0 + l), rb = ra + 1;
-        double a = 0.0, b = 0.0;
-        if (ra < rows) {
-            const int k = ra / Ny, j = ra - k * Ny;
-            a = rhs[(size_t)(k + Ng) * cp + (size_t)(j + Ng) * cs + Ng + n] - mean;
+    __shared__ long long ro[16];                    // offset of the first interior cell of rows 2l, 2l+1 (-1: no such row)
+    if ((int)threadIdx.x < 2 * L) {
+        const int row = 2 * line0 + threadIdx.x;
+        const int k = row / Ny, j = row - k * Ny;
+        ro[threadIdx.x] = row < rows ? (long long)(k + Ng) * cp + (long long)(j + Ng) * cs + Ng : -1;
+    }
+    __syncthreads();
+    for (int l = 0; l < L; ++l) {
+        const long long oa = ro[2 * l], ob = ro[2 * l + 1];
+        for (int n = threadIdx.x; n < Nx; n += blockDim.x) {
+            const double a = oa >= 0 ? rhs[oa + n] : 0.0;
+            const double b = ob >= 0 ? rhs[ob + n] : 0.0;
+            A[sw(n, l, L)] = c2(a, b);
         }
-        if (rb < rows) {
-            const int k = rb / Ny, j = rb - k * Ny;
-            b = rhs[(size_t)(k + Ng) * cp + (size_t)(j + Ng) * cs + Ng + n] - mean;
-        }
-        A[sw(n, l, L)] = c2(a, b);
     }
     __syncthreads();
     const double2* Z = fft_lines(A, B, Nx, L, logL, rad, tw);
     const int Nxh = Nx / 2 + 1;
-    for (int t = threadIdx.x; t < Nxh * L; t += blockDim.x) {
-        const int l = t / Nxh, kx = t - l * Nxh;
+    for (int l = 0; l < L; ++l) {
         const int ra = 2 * (line0 + l), rb = ra + 1;
-        const double2 z = Z[sw(kx, l, L)], zc = cconj(Z[sw(kx == 0 ? 0 : Nx - kx, l, L)]);
-        const double2 s = cadd(z, zc), d = csub(z, zc);
-        if (ra < rows) spec[(size_t)ra * Pxh + kx] = c2(0.5 * s.x, 0.5 * s.y);
-        if (rb < rows) spec[(size_t)rb * Pxh + kx] = c2(0.5 * d.y, -0.5 * d.x);      // (z - conj z') / (2 i)
+        for (int kx = threadIdx.x; kx < Nxh; kx += blockDim.x) {
+            const double2 z = Z[sw(kx, l, L)], zc = cconj(Z[sw(kx == 0 ? 0 : Nx - kx, l, L)]);
+            const double2 s = cadd(z, zc), d = csub(z, zc);
+            if (ra < rows) spec[(size_t)ra * Pxh + kx] = c2(0.5 * s.x, 0.5 * s.y);
+            if (rb < rows) spec[(size_t)rb * Pxh + kx] = c2(0.5 * d.y, -0.5 * d.x);  // (z - conj z') / (2 i)
+        }
     }
 }
 
@@ -172,32 +180,33 @@ k_fft_x_inv(const double2* __restrict__ spec, double* __restrict__ p, int Nx, in
     double2* B = sm + (size_t)Nx * L;
     const int rows = Ny * Nz;
     const int line0 = blockIdx.x * L;
-    for (int t = threadIdx.x; t < Nx * L; t += blockDim.x) {
-        const int l = t / Nx, n = t - l * Nx;
+    __shared__ long long ro[16];                    // offset of column 0 (x ghost) of rows 2l, 2l+1 (-1: no such row)
+    if ((int)threadIdx.x < 2 * L) {
+        const int row = 2 * line0 + threadIdx.x;
+        const int k = row / Ny, j = row - k * Ny;
+        ro[threadIdx.x] = row < rows ? (long long)(k + Ng) * cp + (long long)(j + Ng) * cs : -1;
+    }
+    for (int l = 0; l < L; ++l) {
         const int ra = 2 * (line0 + l), rb = ra + 1;
-        const bool upper = n > Nx / 2;
-        const int kx = upper ? Nx - n : n;
-        double2 a = c2(0.0, 0.0), b = c2(0.0, 0.0);
-        if (ra < rows) a = spec[(size_t)ra * Pxh + kx];
-        if (rb < rows) b = spec[(size_t)rb * Pxh + kx];
-        if (upper) { a = cconj(a); b = cconj(b); }
-        const double2 z = c2(a.x - b.y, a.y + b.x);                    // a + i b
-        A[sw(n, l, L)] = cconj(z);
+        for (int n = threadIdx.x; n < Nx; n += blockDim.x) {
+            const bool upper = n > Nx / 2;
+            const int kx = upper ? Nx - n : n;
+            double2 a = c2(0.0, 0.0), b = c2(0.0, 0.0);
+            if (ra < rows) a = spec[(size_t)ra * Pxh + kx];
+            if (rb < rows) b = spec[(size_t)rb * Pxh + kx];
+            if (upper) { a = cconj(a); b = cconj(b); }
+            A[sw(n, l, L)] = c2(a.x - b.y, -(a.y + b.x));              // conj(a + i b)
+        }
     }
     __syncthreads();
     const double2* Z = fft_lines(A, B, Nx, L, logL, rad, tw);
-    for (int t = threadIdx.x; t < (Nx + 2) * L; t += blockDim.x) {
-        const int l = t / (Nx + 2), i = t - l * (Nx + 2);              // i: ghosted column 0 .. Nx+1 (Ng = 1)
-        const int n = (i + Nx - 1) % Nx;
-        const int ra = 2 * (line0 + l), rb = ra + 1;
-        const double2 z = Z[sw(n, l, L)];
-        if (ra < rows) {
-            const int k = ra / Ny, j = ra - k * Ny;
-            p[(size_t)(k + Ng) * cp + (size_t)(j + Ng) * cs + i] = z.x * norm;
-        }
-        if (rb < rows) {
-            const int k = rb / Ny, j = rb - k * Ny;
-            p[(size_t)(k + Ng) * cp + (size_t)(j + Ng) * cs + i] = -z.y * norm;
+    for (int l = 0; l < L; ++l) {
+        const long long oa = ro[2 * l], ob = ro[2 * l + 1];
+        for (int i = threadIdx.x; i < Nx + 2; i += blockDim.x) {        // ghosted column 0 .. Nx+1 (Ng = 1)
+            const int n = i == 0 ? Nx - 1 : (i == Nx + 1 ? 0 : i - 1);
+            const double2 z = Z[sw(n, l, L)];
+            if (oa >= 0) p[oa + i] = z.x * norm;
+            if (ob >= 0) p[ob + i] = -z.y * norm;
         }
     }
 }
@@ -229,47 +238,98 @@ k_fft_z(double2* __restrict__ spec, int Ny, int Nz, int Pxh, int L, int logL, Ra
 
 // ---------------------------------------------------------------- tridiagonal systems in y, one thread per mode
 // Thomas algorithm with the reference's rows (:606-641 for the matrix, :1027-1075 for the recurrences): diagonal
-// -(aS + aN) - (lambda_x + lambda_z); the (0, 0) mode is pinned to 0 at j = 0.  d' overwrites the spectrum, c' is
-// written when BUILD (mesh-only data, tabulated at the first solve) and read by the back substitution.
-template <bool BUILD>
+// -(aS + aN) - (lambda_x + lambda_z); the (0, 0) mode is pinned to 0 at j = 0.  The factorisation depends on the mesh
+// only: c'[j] = upper / den[j] and 1 / den[j], den[j] = diag[j] - lower[j] c'[j-1], are tabulated once per solver.
 __global__ void __launch_bounds__(128)
-k_fft_thomas(double2* __restrict__ spec, double* __restrict__ cprime, const double* __restrict__ lamx,
-             const double* __restrict__ lamz, const double* __restrict__ lo, const double* __restrict__ up,
-             const double* __restrict__ dbase, int Ny, int Nxh, int Pxh) {
+k_fft_thomas_setup(double* __restrict__ cprime, double* __restrict__ invden, const double* __restrict__ lamx,
+                   const double* __restrict__ lamz, const double* __restrict__ lo, const double* __restrict__ up,
+                   const double* __restrict__ dbase, int Ny, int Nxh, int Pxh) {
     const int kx = blockIdx.x * blockDim.x + threadIdx.x, kz = blockIdx.y;
     if (kx >= Nxh) return;
     const double shift = lamx[kx] + lamz[kz];
     const bool zero_mode = kx == 0 && kz == 0;
     size_t idx = (size_t)kz * Ny * Pxh + kx;
     double c = 0.0;
-    double2 d = c2(0.0, 0.0);
     for (int j = 0; j < Ny; ++j, idx += Pxh) {
         double diag = dbase[j] - shift;
         const double lower = j > 0 ? lo[j] : 0.0;
         double upper = j < Ny - 1 ? up[j] : 0.0;
-        double2 r = spec[idx];
-        if (zero_mode && j == 0) { diag = 1.0; upper = 0.0; r = c2(0.0, 0.0); }
-        if (BUILD) {
-            const double den = diag - lower * c;
-            c = upper / den;
-            d = c2((r.x - lower * d.x) / den, (r.y - lower * d.y) / den);
-            cprime[idx] = c;
-        } else {                        // c'[j] comes from the table: one division per row less
-            const double cn = cprime[idx];
-            const double den = diag - lower * c;
-            d = c2((r.x - lower * d.x) / den, (r.y - lower * d.y) / den);
-            c = cn;
-        }
-        spec[idx] = d;
+        if (zero_mode && j == 0) { diag = 1.0; upper = 0.0; }
+        const double den = diag - lower * c;
+        c = upper / den;
+        cprime[idx] = c;
+        invden[idx] = 1.0 / den;
     }
-    idx -= Pxh;
-    double2 x = d;
-    for (int j = Ny - 2; j >= 0; --j) {
-        idx -= Pxh;
-        const double2 dj = spec[idx];
-        const double cj = cprime[idx];
-        x = c2(dj.x - cj * x.x, dj.y - cj * x.y);
-        spec[idx] = x;
+}
+
+// Forward elimination d'[j] = (r[j] - lower[j] d'[j-1]) / den[j] and back substitution x[j] = d'[j] - c'[j] x[j+1],
+// in place on the spectrum.  Rows are taken U at a time: the U loads of a chunk do not depend on the recurrence and
+// are all in flight before the first dependent operation (one thread per mode gives too few warps to hide a
+// load per row otherwise).
+template <int U>
+__global__ void __launch_bounds__(128)
+k_fft_thomas(double2* __restrict__ spec, const double* __restrict__ cprime, const double* __restrict__ invden,
+             const double* __restrict__ lo, const double* __restrict__ dyv, double inv_Ly, int Ny, int Nxh, int Pxh) {
+    const int kx = blockIdx.x * blockDim.x + threadIdx.x, kz = blockIdx.y;
+    if (kx >= Nxh) return;
+    const bool zero_mode = kx == 0 && kz == 0;
+    const size_t base = (size_t)kz * Ny * Pxh + kx;
+    // Mean removal (solvability, kernel_pack_and_partial_sum + kernel_subtract_mean :53-130): subtracting the
+    // volume-weighted mean m = sum f dyv / (Nx Nz Ly) from every cell changes nothing but the (0, 0) coefficient of each
+    // row, F00[j] -= m Nx Nz, and sum_j dyv[j] F00[j] IS sum f dyv: the thread of the zero mode does it on its column.
+    double mean_hat = 0.0;
+    if (zero_mode) {
+        double s = 0.0;
+        for (int j = 0; j < Ny; ++j) s += spec[base + (size_t)j * Pxh].x * dyv[j];
+        mean_hat = s * inv_Ly;
+    }
+    double2 d = c2(0.0, 0.0);
+    for (int j0 = 0; j0 < Ny; j0 += U) {
+        double2 r[U];
+        double iv[U], lw[U];
+#pragma unroll
+        for (int q = 0; q < U; ++q) {
+            const int j = j0 + q;
+            if (j < Ny) {
+                r[q] = spec[base + (size_t)j * Pxh];
+                iv[q] = invden[base + (size_t)j * Pxh];
+                lw[q] = j > 0 ? lo[j] : 0.0;
+            }
+        }
+        if (zero_mode) {
+#pragma unroll
+            for (int q = 0; q < U; ++q) r[q].x -= mean_hat;
+            if (j0 == 0) r[0] = c2(0.0, 0.0);
+        }
+#pragma unroll
+        for (int q = 0; q < U; ++q) {
+            const int j = j0 + q;
+            if (j < Ny) {
+                d = c2((r[q].x - lw[q] * d.x) * iv[q], (r[q].y - lw[q] * d.y) * iv[q]);
+                spec[base + (size_t)j * Pxh] = d;
+            }
+        }
+    }
+    double2 x = d;                                   // row Ny - 1
+    for (int j0 = Ny - 2; j0 >= 0; j0 -= U) {
+        double2 dj[U];
+        double cj[U];
+#pragma unroll
+        for (int q = 0; q < U; ++q) {
+            const int j = j0 - q;
+            if (j >= 0) {
+                dj[q] = spec[base + (size_t)j * Pxh];
+                cj[q] = cprime[base + (size_t)j * Pxh];
+            }
+        }
+#pragma unroll
+        for (int q = 0; q < U; ++q) {
+            const int j = j0 - q;
+            if (j >= 0) {
+                x = c2(dj[q].x - cj[q] * x.x, dj[q].y - cj[q] * x.y);
+                spec[base + (size_t)j * Pxh] = x;
+            }
+        }
     }
 }
 
@@ -285,9 +345,11 @@ __global__ void k_fft_ghost_y(double* __restrict__ p, int Nxt, int Ny, int Nz, i
 
 int ilog2(int v) { int l = 0; while ((1 << l) < v) ++l; return l; }
 
-Radices factorize(int n) {              // 4s first, then one 2, then 3s and 5s
+Radices factorize(int n) {              // 8s first, then 4s, one 2, then 3s and 5s (power-of-two strides as long as possible)
     Radices r; r.n = 0;
     for (int q = 0; q < FFT_MAX_RAD; ++q) r.r[q] = 0;
+    const bool r8 = std::getenv("CFDNN_FFT_RADIX8") == nullptr || std::atoi(std::getenv("CFDNN_FFT_RADIX8")) != 0;
+    while (r8 && n % 8 == 0) { r.r[r.n++] = 8; n /= 8; }
     while (n % 4 == 0) { r.r[r.n++] = 4; n /= 4; }
     while (n % 2 == 0) { r.r[r.n++] = 2; n /= 2; }
     while (n % 3 == 0) { r.r[r.n++] = 3; n /= 3; }
@@ -341,6 +403,14 @@ FftPoisson::FftPoisson(const cfdnn_mesh_desc& m) : Nx_(m.Nx), Ny_(m.Ny), Nz_(m.N
     cp_ = cs_ * (Ny_ + 2 * Ng_);
     Lx_ = lines_per_cta(Nx_);
     Lz_ = lines_per_cta(Nz_);
+    auto tune = [](const char* name, int& L, int n) {       // measurement aid: lines per CTA (a power of two <= 8)
+        if (const char* e = std::getenv(name)) {
+            const int v = std::atoi(e);
+            if ((v == 1 || v == 2 || v == 4 || v == 8) && (size_t)2 * n * v * sizeof(double2) <= 65536) L = v;
+        }
+    };
+    tune("CFDNN_FFT_LX", Lx_, Nx_);
+    tune("CFDNN_FFT_LZ", Lz_, Nz_);
     Radices rx = factorize(Nx_), rz = factorize(Nz_);
     nrx_ = rx.n; nrz_ = rz.n;
     std::memcpy(radx_, rx.r, sizeof(radx_));
@@ -349,7 +419,14 @@ FftPoisson::FftPoisson(const cfdnn_mesh_desc& m) : Nx_(m.Nx), Ny_(m.Ny), Nz_(m.N
     const size_t ns = (size_t)Nz_ * Ny_ * Pxh_;
     spec_.alloc(ns, true);
     cprime_.alloc(ns, true);
-    partial_.alloc(1 + 1184, true);
+    invden_.alloc(ns, true);
+    {
+        const dim3 gt((Nxh_ + 127) / 128, Nz_);
+        CFDNN_LAUNCH(k_fft_thomas_setup, gt, 128, 0, nullptr, cprime_.p, invden_.p, lamx_.p, lamz_.p, lo_.p, up_.p, base_.p, Ny_,
+                     Nxh_, Pxh_);
+        CFDNN_CUDA(cudaDeviceSynchronize());
+        check_launch("fft thomas setup");
+    }
     CFDNN_CUDA(cudaFuncSetAttribute(k_fft_x_fwd, cudaFuncAttributeMaxDynamicSharedMemorySize, 65536));
     CFDNN_CUDA(cudaFuncSetAttribute(k_fft_x_inv, cudaFuncAttributeMaxDynamicSharedMemorySize, 65536));
     CFDNN_CUDA(cudaFuncSetAttribute(k_fft_z<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 65536));
@@ -383,7 +460,7 @@ void FftPoisson::setup_tables(const cfdnn_mesh_desc& m) {
         w[j] = m.y_stretched ? m.dyv[j + Ng_] : m.dy;
         Ly += w[j];
     }
-    total_volume_ = (double)Nx_ * Nz_ * Ly;
+    inv_Ly_ = 1.0 / Ly;
     upload(lo_, lo); upload(up_, up); upload(base_, base); upload(dyv_, w);
 }
 
@@ -405,28 +482,18 @@ int FftPoisson::solve_dev(const double* rhs, double* p, cudaStream_t st) {      
     std::memcpy(rx.r, radx_, sizeof(rx.r));
     std::memcpy(rz.r, radz_, sizeof(rz.r));
     const int rows = Ny_ * Nz_;
-    // 1. volume-weighted mean of the right-hand side
-    const int nb = rows < 1184 ? rows : 1184;
-    CFDNN_LAUNCH_COOP(k_fft_wsum, nb, 256, 0, st, rhs, dyv_.p, Nx_, Ny_, Nz_, Ng_, cs_, cp_, partial_.p);
-    CFDNN_LAUNCH(k_fft_mean, 1, 1, 0, st, partial_.p, nb, 1.0 / total_volume_);
-    // 2. forward transforms
+    // 1. forward transforms
     const int xlines = (rows + 1) / 2;
     const size_t smx = (size_t)2 * Nx_ * Lx_ * sizeof(double2), smz = (size_t)2 * Nz_ * Lz_ * sizeof(double2);
-    CFDNN_LAUNCH_COOP(k_fft_x_fwd, (xlines + Lx_ - 1) / Lx_, FFT_THREADS, smx, st, rhs, partial_.p, spec_.p, Nx_, Ny_, Nz_, Ng_,
+    CFDNN_LAUNCH_COOP(k_fft_x_fwd, (xlines + Lx_ - 1) / Lx_, FFT_THREADS, smx, st, rhs, spec_.p, Nx_, Ny_, Nz_, Ng_,
                       cs_, cp_, Pxh_, Lx_, ilog2(Lx_), rx, twx_.p);
     const dim3 gz(Pxh_ / Lz_, Ny_);
     CFDNN_LAUNCH_COOP((k_fft_z<false>), gz, FFT_THREADS, smz, st, spec_.p, Ny_, Nz_, Pxh_, Lz_, ilog2(Lz_), rz, twz_.p);
-    // 3. tridiagonal solves
+    // 2. tridiagonal solves (with the mean removal on the zero mode)
     const dim3 gt((Nxh_ + 127) / 128, Nz_);
-    if (!cprime_ready_) {
-        CFDNN_LAUNCH((k_fft_thomas<true>), gt, 128, 0, st, spec_.p, cprime_.p, lamx_.p, lamz_.p, lo_.p, up_.p, base_.p, Ny_,
-                     Nxh_, Pxh_);
-        cprime_ready_ = true;
-    } else {
-        CFDNN_LAUNCH((k_fft_thomas<false>), gt, 128, 0, st, spec_.p, cprime_.p, lamx_.p, lamz_.p, lo_.p, up_.p, base_.p, Ny_,
-                     Nxh_, Pxh_);
-    }
-    // 4. inverse transforms, normalisation, ghosts (x in the kernel, then y rows, then the periodic z planes)
+    CFDNN_LAUNCH((k_fft_thomas<8>), gt, 128, 0, st, spec_.p, cprime_.p, invden_.p, lo_.p, dyv_.p, inv_Ly_, Ny_,
+                 Nxh_, Pxh_);
+    // 3. inverse transforms, normalisation, ghosts (x in the kernel, then y rows, then the periodic z planes)
     CFDNN_LAUNCH_COOP((k_fft_z<true>), gz, FFT_THREADS, smz, st, spec_.p, Ny_, Nz_, Pxh_, Lz_, ilog2(Lz_), rz, twz_.p);
     CFDNN_LAUNCH_COOP(k_fft_x_inv, (xlines + Lx_ - 1) / Lx_, FFT_THREADS, smx, st, spec_.p, p, Nx_, Ny_, Nz_, Ng_, cs_, cp_, Pxh_,
                       Lx_, ilog2(Lx_), rx, twx_.p, 1.0 / ((double)Nx_ * (double)Nz_));

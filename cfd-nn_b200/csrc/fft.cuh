@@ -29,15 +29,13 @@ private:
     int Lx_, Lz_;                   // lines per CTA of the x and z transforms
     int nrx_, nrz_;
     int radx_[12], radz_[12];       // radix sequences
-    double total_volume_;
+    double inv_Ly_;                 // 1 / sum dyv
     bool bc_set_ = false;
     DevBuf<double2> spec_;          // [Nz][Ny][Pxh] half spectrum
-    DevBuf<double> cprime_;         // [Nz][Ny][Pxh] Thomas c' (depends on the mesh only)
+    DevBuf<double> cprime_, invden_;   // [Nz][Ny][Pxh] Thomas c' and 1 / den (depend on the mesh only)
     DevBuf<double2> twx_, twz_;     // exp(-2 pi i n / N)
     DevBuf<double> lamx_, lamz_;    // Laplacian symbols
     DevBuf<double> lo_, up_, base_, dyv_;   // tridiagonal rows, volume weights
-    DevBuf<double> partial_;        // reduction scratch + mean
-    bool cprime_ready_ = false;
 };
 
 }  // namespace cfdnn

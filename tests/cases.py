@@ -872,10 +872,22 @@ def check_step_with_fft(B, oracle, stretched=False, N=(16, 16, 16), nsteps=2):
         got = B.state(h, *N)
     finally:
         B.lib.cfdnn_solver_destroy(h)
+    # The reference's semi-coarsening multigrid (stretched y) stalls near 1e-7 relative on this case however many
+    # cycles it gets (200 and 1000 cycles give the same fields), so the stretched comparison is at that level; the
+    # direct solve itself is checked by the property below: the projected velocity is discretely divergence-free.
+    vtol, ptol = (2e-6, 2e-5) if stretched else (1e-9, 1e-8)
+    scale = np.abs(R.interior("u", ref["u"])).max()
     for n in ("u", "v", "w"):
         a, b = R.interior(n, got[n]), R.interior(n, ref[n])
-        scale = np.abs(R.interior("u", ref["u"])).max()
-        assert np.abs(a - b).max() <= 1e-9 * scale, (n, np.abs(a - b).max(), scale)
+        assert np.abs(a - b).max() <= vtol * scale, (n, np.abs(a - b).max(), scale)
     a, b = R.interior("p", got["p"]), R.interior("p", ref["p"])
     a = a - a.mean(); b = b - b.mean()
-    assert np.abs(a - b).max() <= 1e-8 * max(np.abs(b).max(), 1e-300), np.abs(a - b).max()
+    assert np.abs(a - b).max() <= ptol * max(np.abs(b).max(), 1e-300), np.abs(a - b).max()
+    Nx, Ny, Nz = N
+    dx, dz = extra["x1"] / Nx, extra["z1"] / Nz
+    dyv = arrs["dyv"][1:-1] if stretched else np.full(Ny, (extra["y1"] - extra["y0"]) / Ny)
+    U, V, W = got["u"], got["v"], got["w"]
+    div = ((U[1:-1, 1:-1, 2:Nx + 2] - U[1:-1, 1:-1, 1:Nx + 1]) / dx +
+           (V[1:-1, 2:Ny + 2, 1:-1] - V[1:-1, 1:Ny + 1, 1:-1]) / dyv[None, :, None] +
+           (W[2:Nz + 2, 1:-1, 1:-1] - W[1:Nz + 1, 1:-1, 1:-1]) / dz)
+    assert np.abs(div).max() <= 1e-11 * scale / min(dx, dz, dyv.min()), np.abs(div).max()

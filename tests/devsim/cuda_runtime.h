@@ -141,6 +141,7 @@ inline cudaError_t cudaStreamDestroy(cudaStream_t s) { std::free(s); return cuda
 inline cudaError_t cudaStreamSynchronize(cudaStream_t) { return cudaSuccess; }
 inline cudaError_t cudaStreamWaitEvent(cudaStream_t, cudaEvent_t, unsigned = 0) { return cudaSuccess; }
 inline cudaError_t cudaDeviceSynchronize() { return cudaSuccess; }
+inline int __clz(int x) { return x ? __builtin_clz((unsigned)x) : 32; }
 inline cudaError_t cudaEventCreate(cudaEvent_t* e) { *e = new devsim_event(); return cudaSuccess; }
 inline cudaError_t cudaEventCreateWithFlags(cudaEvent_t* e, unsigned) { return cudaEventCreate(e); }
 inline cudaError_t cudaEventDestroy(cudaEvent_t e) { delete e; return cudaSuccess; }
