@@ -148,12 +148,18 @@ k_fft_x_fwd(const double* __restrict__ rhs, double2* __restrict__ spec, int Nx, 
         ro[threadIdx.x] = row < rows ? (long long)(k + Ng) * cp + (long long)(j + Ng) * cs + Ng : -1;
     }
     __syncthreads();
-    for (int l = 0; l < L; ++l) {
-        const long long oa = ro[2 * l], ob = ro[2 * l + 1];
+    for (int l0 = 0; l0 < L; l0 += 4) {             // 8 loads in flight per thread before the first shared-memory store
         for (int n = threadIdx.x; n < Nx; n += blockDim.x) {
-            const double a = oa >= 0 ? rhs[oa + n] : 0.0;
-            const double b = ob >= 0 ? rhs[ob + n] : 0.0;
-            A[sw(n, l, L)] = c2(a, b);
+            double a[4], b[4];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const long long oa = l0 + q < L ? ro[2 * (l0 + q)] : -1, ob = l0 + q < L ? ro[2 * (l0 + q) + 1] : -1;
+                a[q] = oa >= 0 ? rhs[oa + n] : 0.0;
+                b[q] = ob >= 0 ? rhs[ob + n] : 0.0;
+            }
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+                if (l0 + q < L) A[sw(n, l0 + q, L)] = c2(a[q], b[q]);
         }
     }
     __syncthreads();
@@ -186,16 +192,23 @@ k_fft_x_inv(const double2* __restrict__ spec, double* __restrict__ p, int Nx, in
         const int k = row / Ny, j = row - k * Ny;
         ro[threadIdx.x] = row < rows ? (long long)(k + Ng) * cp + (long long)(j + Ng) * cs : -1;
     }
-    for (int l = 0; l < L; ++l) {
-        const int ra = 2 * (line0 + l), rb = ra + 1;
+    for (int l0 = 0; l0 < L; l0 += 4) {             // 8 loads in flight per thread before the first shared-memory store
         for (int n = threadIdx.x; n < Nx; n += blockDim.x) {
             const bool upper = n > Nx / 2;
             const int kx = upper ? Nx - n : n;
-            double2 a = c2(0.0, 0.0), b = c2(0.0, 0.0);
-            if (ra < rows) a = spec[(size_t)ra * Pxh + kx];
-            if (rb < rows) b = spec[(size_t)rb * Pxh + kx];
-            if (upper) { a = cconj(a); b = cconj(b); }
-            A[sw(n, l, L)] = c2(a.x - b.y, -(a.y + b.x));              // conj(a + i b)
+            double2 a[4], b[4];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const int ra = 2 * (line0 + l0 + q), rb = ra + 1;
+                a[q] = (l0 + q < L && ra < rows) ? spec[(size_t)ra * Pxh + kx] : c2(0.0, 0.0);
+                b[q] = (l0 + q < L && rb < rows) ? spec[(size_t)rb * Pxh + kx] : c2(0.0, 0.0);
+            }
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                if (l0 + q >= L) continue;
+                if (upper) { a[q] = cconj(a[q]); b[q] = cconj(b[q]); }
+                A[sw(n, l0 + q, L)] = c2(a[q].x - b[q].y, -(a[q].y + b[q].x));      // conj(a + i b)
+            }
         }
     }
     __syncthreads();
@@ -222,10 +235,18 @@ k_fft_z(double2* __restrict__ spec, int Ny, int Nz, int Pxh, int L, int logL, Ra
     const int j = blockIdx.y, kx0 = blockIdx.x * L;
     const size_t zs = (size_t)Ny * Pxh;
     double2* base = spec + (size_t)j * Pxh + kx0;
-    for (int t = threadIdx.x; t < Nz * L; t += blockDim.x) {
-        const int l = t & (L - 1), n = t >> logL;
-        const double2 v = base[(size_t)n * zs + l];
-        A[sw(n, l, L)] = INV ? cconj(v) : v;
+    for (int t0 = threadIdx.x; t0 < Nz * L; t0 += 8 * blockDim.x) {      // 8 loads in flight per thread
+        double2 v[8];
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+            const int t = t0 + q * blockDim.x;
+            if (t < Nz * L) v[q] = base[(size_t)(t >> logL) * zs + (t & (L - 1))];
+        }
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+            const int t = t0 + q * blockDim.x;
+            if (t < Nz * L) A[sw(t >> logL, t & (L - 1), L)] = INV ? cconj(v[q]) : v[q];
+        }
     }
     __syncthreads();
     const double2* Z = fft_lines(A, B, Nz, L, logL, rad, tw);
