@@ -1,5 +1,6 @@
 // comm.cu — NCCL-backed slab communicator (see comm.cuh).
 #include "comm.cuh"
+#include <vector>
 #include <dlfcn.h>
 #include <cstring>
 #include <mutex>
@@ -80,6 +81,18 @@ struct NcclComm final : Comm {
     void allgather_planes(double* base, size_t count, cudaStream_t st) override {
         NCCL_OK(nccl().AllGather(base + (size_t)rank * count, base, count, ncclFloat64, comm, st));
     }
+    void alltoall(const double* send, double* recv, size_t count, cudaStream_t st) override {
+        Nccl& n = nccl();
+        CFDNN_CUDA(cudaMemcpyAsync(recv + (size_t)rank * count, send + (size_t)rank * count, count * sizeof(double),
+                                   cudaMemcpyDeviceToDevice, st));
+        NCCL_OK(n.GroupStart());
+        for (int d = 1; d < nranks; ++d) {           // pair (rank + d, rank - d): every rank posts the same pattern
+            const int to = (rank + d) % nranks, from = (rank + nranks - d) % nranks;
+            NCCL_OK(n.Send(send + (size_t)to * count, count, ncclFloat64, to, comm, st));
+            NCCL_OK(n.Recv(recv + (size_t)from * count, count, ncclFloat64, from, comm, st));
+        }
+        NCCL_OK(n.GroupEnd());
+    }
 };
 }  // namespace
 
@@ -125,6 +138,15 @@ struct CallbackComm final : Comm {
     void allreduce_max(double* d, int n, cudaStream_t) override { cb.allreduce(cb.ctx, d, n, 1); }
     void allreduce_min(double* d, int n, cudaStream_t) override { cb.allreduce(cb.ctx, d, n, 2); }
     void allgather_planes(double* base, size_t count, cudaStream_t) override { cb.allgather(cb.ctx, base, count); }
+    void alltoall(const double* send, double* recv, size_t count, cudaStream_t) override {
+        // test transport: everybody gathers everybody's send buffer and keeps its own blocks
+        const size_t per = count * (size_t)nranks;
+        std::vector<double> all(per * (size_t)nranks);
+        std::memcpy(all.data() + per * (size_t)rank, send, per * sizeof(double));
+        cb.allgather(cb.ctx, all.data(), per);
+        for (int s = 0; s < nranks; ++s)
+            std::memcpy(recv + (size_t)s * count, all.data() + per * (size_t)s + count * (size_t)rank, count * sizeof(double));
+    }
 };
 }  // namespace
 Comm* make_callback_comm(int rank, int nranks, const cfdnn_comm_callbacks_t& cb) {

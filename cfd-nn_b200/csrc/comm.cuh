@@ -37,6 +37,9 @@ struct Comm {
     virtual void allreduce_min(double* d, int n, cudaStream_t st) = 0;
     // in place: rank r's `count` doubles already sit at base + r*count
     virtual void allgather_planes(double* base, size_t count, cudaStream_t st) = 0;
+    // block q of `send` (count doubles at send + q*count) goes to rank q, which stores it as block `rank` of its
+    // `recv`; send and recv must not overlap (the FFT Poisson solver's transposes)
+    virtual void alltoall(const double* send, double* recv, size_t count, cudaStream_t st) = 0;
 };
 
 // NCCL transport (product).  id128 = ncclUniqueId bytes made by cfdnn_comm_unique_id on rank 0.

@@ -132,6 +132,13 @@ __device__ double2* fft_lines(double2* A, double2* B, int N, int L, int logL, co
 }
 
 // ---------------------------------------------------------------- x transforms (rows of the ghosted cell layout)
+// The half spectrum of the local rows is stored in blocks of Pq columns, S[q][row][c] with kx = q Pq + c: block q is what
+// rank q receives in the all-to-all (one rank: a single block, i.e. the plain [row][kx] array).  Offset of (row 0, kx):
+__device__ __forceinline__ size_t sblock(int kx, int Pq, int rows) {
+    const int q = kx < Pq ? 0 : kx / Pq;
+    return (size_t)q * rows * Pq + (size_t)(kx - q * Pq);
+}
+
 // forward: line l of the CTA carries rows 2l (real part) and 2l+1 (imaginary part); row = k Ny + j
 __global__ void __launch_bounds__(FFT_THREADS)
 k_fft_x_fwd(const double* __restrict__ rhs, double2* __restrict__ spec, int Nx, int Ny,
@@ -170,8 +177,9 @@ k_fft_x_fwd(const double* __restrict__ rhs, double2* __restrict__ spec, int Nx, 
         for (int kx = threadIdx.x; kx < Nxh; kx += blockDim.x) {
             const double2 z = Z[sw(kx, l, L)], zc = cconj(Z[sw(kx == 0 ? 0 : Nx - kx, l, L)]);
             const double2 s = cadd(z, zc), d = csub(z, zc);
-            if (ra < rows) spec[(size_t)ra * Pxh + kx] = c2(0.5 * s.x, 0.5 * s.y);
-            if (rb < rows) spec[(size_t)rb * Pxh + kx] = c2(0.5 * d.y, -0.5 * d.x);  // (z - conj z') / (2 i)
+            const size_t o = sblock(kx, Pxh, rows);
+            if (ra < rows) spec[o + (size_t)ra * Pxh] = c2(0.5 * s.x, 0.5 * s.y);
+            if (rb < rows) spec[o + (size_t)rb * Pxh] = c2(0.5 * d.y, -0.5 * d.x);  // (z - conj z') / (2 i)
         }
     }
 }
@@ -197,11 +205,12 @@ k_fft_x_inv(const double2* __restrict__ spec, double* __restrict__ p, int Nx, in
             const bool upper = n > Nx / 2;
             const int kx = upper ? Nx - n : n;
             double2 a[4], b[4];
+            const size_t o = sblock(kx, Pxh, rows);
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
                 const int ra = 2 * (line0 + l0 + q), rb = ra + 1;
-                a[q] = (l0 + q < L && ra < rows) ? spec[(size_t)ra * Pxh + kx] : c2(0.0, 0.0);
-                b[q] = (l0 + q < L && rb < rows) ? spec[(size_t)rb * Pxh + kx] : c2(0.0, 0.0);
+                a[q] = (l0 + q < L && ra < rows) ? spec[o + (size_t)ra * Pxh] : c2(0.0, 0.0);
+                b[q] = (l0 + q < L && rb < rows) ? spec[o + (size_t)rb * Pxh] : c2(0.0, 0.0);
             }
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
@@ -264,12 +273,13 @@ k_fft_z(double2* __restrict__ spec, int Ny, int Nz, int Pxh, int L, int logL, Ra
 __global__ void __launch_bounds__(128)
 k_fft_thomas_setup(double* __restrict__ cprime, double* __restrict__ invden, const double* __restrict__ lamx,
                    const double* __restrict__ lamz, const double* __restrict__ lo, const double* __restrict__ up,
-                   const double* __restrict__ dbase, int Ny, int Nxh, int Pxh) {
-    const int kx = blockIdx.x * blockDim.x + threadIdx.x, kz = blockIdx.y;
-    if (kx >= Nxh) return;
+                   const double* __restrict__ dbase, int Ny, int Nxh, int Pxh, int kx0) {
+    const int c_ = blockIdx.x * blockDim.x + threadIdx.x, kz = blockIdx.y;      // column of this rank, kx = kx0 + column
+    const int kx = kx0 + c_;
+    if (c_ >= Pxh || kx >= Nxh) return;
     const double shift = lamx[kx] + lamz[kz];
     const bool zero_mode = kx == 0 && kz == 0;
-    size_t idx = (size_t)kz * Ny * Pxh + kx;
+    size_t idx = (size_t)kz * Ny * Pxh + c_;
     double c = 0.0;
     for (int j = 0; j < Ny; ++j, idx += Pxh) {
         double diag = dbase[j] - shift;
@@ -290,11 +300,13 @@ k_fft_thomas_setup(double* __restrict__ cprime, double* __restrict__ invden, con
 template <int U>
 __global__ void __launch_bounds__(128)
 k_fft_thomas(double2* __restrict__ spec, const double* __restrict__ cprime, const double* __restrict__ invden,
-             const double* __restrict__ lo, const double* __restrict__ dyv, double inv_Ly, int Ny, int Nxh, int Pxh) {
-    const int kx = blockIdx.x * blockDim.x + threadIdx.x, kz = blockIdx.y;
-    if (kx >= Nxh) return;
+             const double* __restrict__ lo, const double* __restrict__ dyv, double inv_Ly, int Ny, int Nxh, int Pxh,
+             int kx0) {
+    const int c_ = blockIdx.x * blockDim.x + threadIdx.x, kz = blockIdx.y;      // column of this rank, kx = kx0 + column
+    const int kx = kx0 + c_;
+    if (c_ >= Pxh || kx >= Nxh) return;
     const bool zero_mode = kx == 0 && kz == 0;
-    const size_t base = (size_t)kz * Ny * Pxh + kx;
+    const size_t base = (size_t)kz * Ny * Pxh + c_;
     // Mean removal (solvability, kernel_pack_and_partial_sum + kernel_subtract_mean :53-130): subtracting the
     // volume-weighted mean m = sum f dyv / (Nx Nz Ly) from every cell changes nothing but the (0, 0) coefficient of each
     // row, F00[j] -= m Nx Nz, and sum_j dyv[j] F00[j] IS sum f dyv: the thread of the zero mode does it on its column.
@@ -411,19 +423,18 @@ bool FftPoisson::size_supported(int n) {
 FftPoisson::FftPoisson(const cfdnn_mesh_desc& m) : Nx_(m.Nx), Ny_(m.Ny), Nz_(m.Nz), Ng_(m.Ng) {
     require_device();
     if (m.Ng != 1) throw std::invalid_argument("FFT Poisson: only Nghost == 1 is supported");
-    if (m.Nz_global > 0 && m.Nz_global != m.Nz)
-        throw std::invalid_argument("FFT Poisson: single-GPU only (no z-slab decomposition)");
     if (Ny_ < 2) throw std::invalid_argument("FFT Poisson: Ny >= 2 required");
-    if (!size_supported(Nx_) || !size_supported(Nz_))
+    Nzg_ = m.Nz_global > 0 ? m.Nz_global : m.Nz;
+    if (Nzg_ % Nz_ != 0) throw std::invalid_argument("FFT Poisson: Nz_global must be a multiple of the local Nz (equal z-slabs)");
+    if (!size_supported(Nx_) || !size_supported(Nzg_))
         throw std::invalid_argument("FFT Poisson: Nx and Nz must be 2^a 3^b 5^c in [2, 1024]");
     if (m.y_stretched && (!m.yLap_aS || !m.yLap_aN || !m.dyv))
         throw std::invalid_argument("FFT Poisson: y-stretched mesh needs yLap_aS, yLap_aN and dyv");
     Nxh_ = Nx_ / 2 + 1;
-    Pxh_ = (Nxh_ + 7) / 8 * 8;
     cs_ = Nx_ + 2 * Ng_;
     cp_ = cs_ * (Ny_ + 2 * Ng_);
     Lx_ = lines_per_cta(Nx_);
-    Lz_ = lines_per_cta(Nz_);
+    Lz_ = lines_per_cta(Nzg_);
     auto tune = [](const char* name, int& L, int n) {       // measurement aid: lines per CTA (a power of two <= 8)
         if (const char* e = std::getenv(name)) {
             const int v = std::atoi(e);
@@ -431,36 +442,56 @@ FftPoisson::FftPoisson(const cfdnn_mesh_desc& m) : Nx_(m.Nx), Ny_(m.Ny), Nz_(m.N
         }
     };
     tune("CFDNN_FFT_LX", Lx_, Nx_);
-    tune("CFDNN_FFT_LZ", Lz_, Nz_);
-    Radices rx = factorize(Nx_), rz = factorize(Nz_);
+    tune("CFDNN_FFT_LZ", Lz_, Nzg_);
+    Radices rx = factorize(Nx_), rz = factorize(Nzg_);
     nrx_ = rx.n; nrz_ = rz.n;
     std::memcpy(radx_, rx.r, sizeof(radx_));
     std::memcpy(radz_, rz.r, sizeof(radz_));
     setup_tables(m);
-    const size_t ns = (size_t)Nz_ * Ny_ * Pxh_;
-    spec_.alloc(ns, true);
-    cprime_.alloc(ns, true);
-    invden_.alloc(ns, true);
-    {
-        const dim3 gt((Nxh_ + 127) / 128, Nz_);
-        CFDNN_LAUNCH(k_fft_thomas_setup, gt, 128, 0, nullptr, cprime_.p, invden_.p, lamx_.p, lamz_.p, lo_.p, up_.p, base_.p, Ny_,
-                     Nxh_, Pxh_);
-        CFDNN_CUDA(cudaDeviceSynchronize());
-        check_launch("fft thomas setup");
-    }
     CFDNN_CUDA(cudaFuncSetAttribute(k_fft_x_fwd, cudaFuncAttributeMaxDynamicSharedMemorySize, 65536));
     CFDNN_CUDA(cudaFuncSetAttribute(k_fft_x_inv, cudaFuncAttributeMaxDynamicSharedMemorySize, 65536));
     CFDNN_CUDA(cudaFuncSetAttribute(k_fft_z<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 65536));
     CFDNN_CUDA(cudaFuncSetAttribute(k_fft_z<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 65536));
+    if (Nzg_ == Nz_) plan(nullptr);                 // single domain; a slab waits for set_comm
+}
+
+// Decomposition of the spectrum.  The x transform runs on this rank's z-slab and leaves S[q][k_local][j][c] — the kx
+// range of rank q (c < Pq columns, kx = q Pq + c) as one contiguous block; an all-to-all turns the blocks into
+// T[kz][j][c], ALL z for this rank's kx columns (source ranks arrive in global z order), on which the z transform and
+// the tridiagonal systems are local; the way back is the same in reverse.  One rank: S and T are the same array.
+void FftPoisson::set_comm(Comm* c) {
+    const int P = c ? c->nranks : 1;
+    if ((long long)Nz_ * P != Nzg_)
+        throw std::invalid_argument("FFT Poisson: need Nz_global == Nz_local * nranks (Nz_global = " + std::to_string(Nzg_) +
+                                    ", Nz_local = " + std::to_string(Nz_) + ", nranks = " + std::to_string(P) + ")");
+    plan(P > 1 ? c : nullptr);
+}
+
+void FftPoisson::plan(Comm* c) {
+    comm_ = c;
+    P_ = c ? c->nranks : 1;
+    rank_ = c ? c->rank : 0;
+    Pq_ = ((Nxh_ + P_ - 1) / P_ + 7) / 8 * 8;
+    const size_t ns = (size_t)Nzg_ * Ny_ * Pq_;     // = P * Nz_local * Ny * Pq
+    spec_.alloc(ns, true);
+    if (P_ > 1) spec2_.alloc(ns, true); else spec2_.release();
+    cprime_.alloc(ns, true);
+    invden_.alloc(ns, true);
+    const dim3 gt((Pq_ + 127) / 128, Nzg_);
+    CFDNN_LAUNCH(k_fft_thomas_setup, gt, 128, 0, nullptr, cprime_.p, invden_.p, lamx_.p, lamz_.p, lo_.p, up_.p, base_.p, Ny_,
+                 Nxh_, Pq_, rank_ * Pq_);
+    CFDNN_CUDA(cudaDeviceSynchronize());
+    check_launch("fft thomas setup");
+    planned_ = true;
 }
 
 void FftPoisson::setup_tables(const cfdnn_mesh_desc& m) {
     fill_twiddles(twx_, Nx_);
-    fill_twiddles(twz_, Nz_);
+    fill_twiddles(twz_, Nzg_);
     // compute_eigenvalues, second-order branch (src/poisson_solver_fft.cpp:494-504)
-    std::vector<double> lx(Nxh_), lz(Nz_);
+    std::vector<double> lx(Nxh_), lz(Nzg_);
     for (int k = 0; k < Nxh_; ++k) lx[k] = (2.0 - 2.0 * std::cos(2.0 * M_PI * k / Nx_)) / (m.dx * m.dx);
-    for (int k = 0; k < Nz_; ++k) lz[k] = (2.0 - 2.0 * std::cos(2.0 * M_PI * k / Nz_)) / (m.dz * m.dz);
+    for (int k = 0; k < Nzg_; ++k) lz[k] = (2.0 - 2.0 * std::cos(2.0 * M_PI * k / Nzg_)) / (m.dz * m.dz);
     upload(lamx_, lx);
     upload(lamz_, lz);
     // compute_tridiagonal_coeffs (:509-547) with Neumann walls, volume weights (:420-435)
@@ -497,31 +528,41 @@ void FftPoisson::set_bc(const int bc[6]) {      // set_bc :253-265 (runtime_erro
 
 int FftPoisson::solve_dev(const double* rhs, double* p, cudaStream_t st) {          // solve_device :960-1098
     if (!bc_set_) throw Error(CFDNN_ERR_RUNTIME, "FFTPoissonSolver: set_bc has not been called");
+    if (!planned_) throw Error(CFDNN_ERR_RUNTIME, "FFT Poisson: this mesh is a z-slab of a larger box; comm_init first");
     if (!rhs || !p) throw std::invalid_argument("FFT Poisson: null field pointer");
     Radices rx, rz;
     rx.n = nrx_; rz.n = nrz_;
     std::memcpy(rx.r, radx_, sizeof(rx.r));
     std::memcpy(rz.r, radz_, sizeof(rz.r));
     const int rows = Ny_ * Nz_;
+    double2* S = spec_.p;                            // [q][k_local][j][c]
+    double2* T = P_ > 1 ? spec2_.p : spec_.p;        // [kz][j][c]
+    const size_t blk = (size_t)rows * Pq_ * 2;       // doubles per all-to-all block
     // 1. forward transforms
     const int xlines = (rows + 1) / 2;
-    const size_t smx = (size_t)2 * Nx_ * Lx_ * sizeof(double2), smz = (size_t)2 * Nz_ * Lz_ * sizeof(double2);
-    CFDNN_LAUNCH_COOP(k_fft_x_fwd, (xlines + Lx_ - 1) / Lx_, FFT_THREADS, smx, st, rhs, spec_.p, Nx_, Ny_, Nz_, Ng_,
-                      cs_, cp_, Pxh_, Lx_, ilog2(Lx_), rx, twx_.p);
-    const dim3 gz(Pxh_ / Lz_, Ny_);
-    CFDNN_LAUNCH_COOP((k_fft_z<false>), gz, FFT_THREADS, smz, st, spec_.p, Ny_, Nz_, Pxh_, Lz_, ilog2(Lz_), rz, twz_.p);
+    const size_t smx = (size_t)2 * Nx_ * Lx_ * sizeof(double2), smz = (size_t)2 * Nzg_ * Lz_ * sizeof(double2);
+    CFDNN_LAUNCH_COOP(k_fft_x_fwd, (xlines + Lx_ - 1) / Lx_, FFT_THREADS, smx, st, rhs, S, Nx_, Ny_, Nz_, Ng_, cs_, cp_, Pq_,
+                      Lx_, ilog2(Lx_), rx, twx_.p);
+    if (P_ > 1) comm_->alltoall(reinterpret_cast<const double*>(S), reinterpret_cast<double*>(T), blk, st);
+    const dim3 gz(Pq_ / Lz_, Ny_);
+    CFDNN_LAUNCH_COOP((k_fft_z<false>), gz, FFT_THREADS, smz, st, T, Ny_, Nzg_, Pq_, Lz_, ilog2(Lz_), rz, twz_.p);
     // 2. tridiagonal solves (with the mean removal on the zero mode)
-    const dim3 gt((Nxh_ + 127) / 128, Nz_);
-    CFDNN_LAUNCH((k_fft_thomas<8>), gt, 128, 0, st, spec_.p, cprime_.p, invden_.p, lo_.p, dyv_.p, inv_Ly_, Ny_,
-                 Nxh_, Pxh_);
+    const dim3 gt((Pq_ + 127) / 128, Nzg_);
+    CFDNN_LAUNCH((k_fft_thomas<8>), gt, 128, 0, st, T, cprime_.p, invden_.p, lo_.p, dyv_.p, inv_Ly_, Ny_, Nxh_, Pq_,
+                 rank_ * Pq_);
     // 3. inverse transforms, normalisation, ghosts (x in the kernel, then y rows, then the periodic z planes)
-    CFDNN_LAUNCH_COOP((k_fft_z<true>), gz, FFT_THREADS, smz, st, spec_.p, Ny_, Nz_, Pxh_, Lz_, ilog2(Lz_), rz, twz_.p);
-    CFDNN_LAUNCH_COOP(k_fft_x_inv, (xlines + Lx_ - 1) / Lx_, FFT_THREADS, smx, st, spec_.p, p, Nx_, Ny_, Nz_, Ng_, cs_, cp_, Pxh_,
-                      Lx_, ilog2(Lx_), rx, twx_.p, 1.0 / ((double)Nx_ * (double)Nz_));
+    CFDNN_LAUNCH_COOP((k_fft_z<true>), gz, FFT_THREADS, smz, st, T, Ny_, Nzg_, Pq_, Lz_, ilog2(Lz_), rz, twz_.p);
+    if (P_ > 1) comm_->alltoall(reinterpret_cast<const double*>(T), reinterpret_cast<double*>(S), blk, st);
+    CFDNN_LAUNCH_COOP(k_fft_x_inv, (xlines + Lx_ - 1) / Lx_, FFT_THREADS, smx, st, S, p, Nx_, Ny_, Nz_, Ng_, cs_, cp_, Pq_,
+                      Lx_, ilog2(Lx_), rx, twx_.p, 1.0 / ((double)Nx_ * (double)Nzg_));
     CFDNN_LAUNCH(k_fft_ghost_y, dim3((cs_ + 127) / 128, Nz_), 128, 0, st, p, cs_, Ny_, Nz_, Ng_, cs_, cp_);
-    CFDNN_CUDA(cudaMemcpyAsync(p, p + (size_t)Nz_ * cp_, (size_t)cp_ * sizeof(double), cudaMemcpyDeviceToDevice, st));
-    CFDNN_CUDA(cudaMemcpyAsync(p + (size_t)(Nz_ + 1) * cp_, p + (size_t)cp_, (size_t)cp_ * sizeof(double),
-                               cudaMemcpyDeviceToDevice, st));
+    if (P_ > 1) {
+        comm_->exchange_planes(p, (size_t)cp_, Nz_, Ng_, true, true, st);       // periodic ring of slabs
+    } else {
+        CFDNN_CUDA(cudaMemcpyAsync(p, p + (size_t)Nz_ * cp_, (size_t)cp_ * sizeof(double), cudaMemcpyDeviceToDevice, st));
+        CFDNN_CUDA(cudaMemcpyAsync(p + (size_t)(Nz_ + 1) * cp_, p + (size_t)cp_, (size_t)cp_ * sizeof(double),
+                                   cudaMemcpyDeviceToDevice, st));
+    }
     return 1;
 }
 

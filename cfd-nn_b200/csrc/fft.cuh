@@ -5,6 +5,7 @@
 #pragma once
 #include <vector>
 #include "common.cuh"
+#include "comm.cuh"
 
 namespace cfdnn {
 
@@ -14,6 +15,9 @@ public:
     // x and z must be periodic, y Neumann on both walls (include/poisson_solver_fft.hpp:27-30 allows Dirichlet in y
     // as well; not supported here)
     void set_bc(const int bc[6]);
+    // z-slab decomposition (the reference's FFT_MPI variant, src/poisson_solver_fft_mpi.cpp): c->nranks equal slabs;
+    // the spectrum is redistributed by two all-to-alls per solve.  nullptr / one rank: single domain.
+    void set_comm(Comm* c);
     // rhs, p: device arrays in the solver's ghosted cell layout; returns 1 like the reference's direct solve
     int solve_dev(const double* rhs, double* p, cudaStream_t st);
     // host arrays, same layout (test/FFI convenience: FFTPoissonSolver has only solve_device)
@@ -23,15 +27,20 @@ public:
 
 private:
     void setup_tables(const cfdnn_mesh_desc& m);
-    int Nx_, Ny_, Nz_, Ng_;
-    int Nxh_, Pxh_;                 // kept x modes Nx/2+1 and their padded pitch (complex elements)
+    void plan(Comm* c);
+    int Nx_, Ny_, Nz_, Ng_;         // Nz_: planes of this rank
+    int Nzg_;                       // planes of the whole box
+    int Nxh_, Pq_ = 0;              // kept x modes Nx/2+1; columns per rank (padded, complex elements)
+    int P_ = 1, rank_ = 0;
+    Comm* comm_ = nullptr;
+    bool planned_ = false;
     int cs_, cp_;                   // row and plane pitch of the ghosted cell layout
     int Lx_, Lz_;                   // lines per CTA of the x and z transforms
     int nrx_, nrz_;
     int radx_[12], radz_[12];       // radix sequences
     double inv_Ly_;                 // 1 / sum dyv
     bool bc_set_ = false;
-    DevBuf<double2> spec_;          // [Nz][Ny][Pxh] half spectrum
+    DevBuf<double2> spec_, spec2_;  // S[q][k_local][j][c] and (P > 1) T[kz][j][c]
     DevBuf<double> cprime_, invden_;   // [Nz][Ny][Pxh] Thomas c' and 1 / den (depend on the mesh only)
     DevBuf<double2> twx_, twz_;     // exp(-2 pi i n / N)
     DevBuf<double> lamx_, lamz_;    // Laplacian symbols

@@ -164,8 +164,6 @@ void Solver::set_velocity_bc(const int bc[6]) {
 }
 
 void Solver::comm_init(Comm* c) {
-    if (c && c->nranks > 1 && fft_)
-        throw std::invalid_argument("comm_init: poisson_solver = FFT is single-GPU (the reference's FFT_MPI variant is not built)");
     if (c && c->nranks > 1) {
         // The slab layout is block distribution with EQUAL slabs (reference Decomposition::nz_for_rank with
         // Nz_global % nprocs == 0, include/decomposition.hpp:81-92): the coarse-level offsets (rank * Nz / 2),
@@ -185,6 +183,7 @@ void Solver::comm_init(Comm* c) {
     }
     comm_ = c;
     mg_->set_comm(c);
+    if (fft_) fft_->set_comm(c);                     // the reference's FFT_MPI role: slabs + all-to-all transposes
     update_links();
 }
 bool Solver::multi() const { return comm_ && comm_->nranks > 1; }

@@ -91,7 +91,8 @@ def main():
     L = 2 * np.pi
     mesh = B.mesh(Nx, Ny, Nz, Lz=L, Nz_global=NzG, k_offset=k0)
     cfg = B.config(nu=0.01, dt=0.01, time_integrator=R.TI[ti], convective_scheme=R.SCHEME["skew"], adaptive_dt=0,
-                   poisson_fixed_cycles=fixed, poisson_tol_rhs=1e-8, poisson_max_vcycles=50)
+                   poisson_fixed_cycles=fixed, poisson_tol_rhs=1e-8, poisson_max_vcycles=50,
+                   poisson_solver=1 if os.environ.get("SLAB_POISSON") == "fft" else 0)
     h = B.solver(mesh, cfg, bc, (0.5, 0.0, 0.0) if "W" in bc else (0.0, 0.0, 0.0))
     if on_gpu:
         raw = (C.c_char * 128)()

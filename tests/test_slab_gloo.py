@@ -187,3 +187,49 @@ def test_inconsistent_decomposition_is_rejected(sim):
         rc = fn(h, rank, 2, C.byref(cbs))
         assert rc == 1 and what in sim.lib.cfdnn_last_error(), (rc, sim.lib.cfdnn_last_error())
         sim.lib.cfdnn_solver_destroy(h)
+
+
+# ---- FFT Poisson on z-slabs (the reference's FFT_MPI role): local x transform, all-to-all, z transform + Thomas on
+# this rank's kx columns, all-to-all back
+def _single_domain_fft(B, R, slab_worker, N, bc, ti, nsteps):
+    u, v, w = slab_worker.global_init(*N, bc)
+    cfg = B.config(nu=0.01, dt=0.01, time_integrator=R.TI[ti], convective_scheme=R.SCHEME["skew"], adaptive_dt=0,
+                   poisson_fixed_cycles=0, poisson_tol_rhs=1e-8, poisson_max_vcycles=50, poisson_solver=1)
+    h = B.solver(B.mesh(*N), cfg, bc, (0.5, 0.0, 0.0))
+    B.upload(h, "u", u); B.upload(h, "v", v); B.upload(h, "w", w)
+    B.check(B.lib.cfdnn_solver_initialize(h))
+    for _ in range(nsteps):
+        B.step(h)
+    st = B.state(h, *N, names=("u", "v", "w", "p", "pcorr", "div", "rhs"))
+    cyc = B.cycles(h)
+    B.lib.cfdnn_solver_destroy(h)
+    return st, cyc
+
+
+def _check_fft_slabs(B, R, world, N, ti, nsteps, monkeypatch, on_gpu):
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import slab_worker
+    bc = "PPWWPP"
+    monkeypatch.setenv("SLAB_POISSON", "fft")
+    with tempfile.TemporaryDirectory() as td:
+        slabs = _run_slabs(world, N, bc, ti, nsteps, 0, td, gpu=on_gpu)
+    names = ("u", "v", "w", "p", "pcorr", "div", "rhs")
+    got = {n: _assemble(slabs, n, N[2] // world) for n in names}
+    single, cyc = _single_domain_fft(B, R, slab_worker, N, bc, ti, nsteps)
+    assert list(slabs[0]["cycles"]) == cyc and all(c == 1 for c in cyc)
+    for n in names:
+        a, b = R.interior(n, got[n]), R.interior(n, single[n])
+        scale = max(np.abs(b).max(), 1e-300) if n not in ("div", "rhs", "pcorr") else max(np.abs(R.interior("p", single["p"])).max(), np.abs(b).max())
+        assert np.abs(a - b).max() / scale <= 1e-12, (n, np.abs(a - b).max(), scale)
+
+
+def test_two_slabs_fft_poisson_match_single_domain(R, sim, monkeypatch):
+    _check_fft_slabs(sim, R, 2, (24, 12, 16), "rk3", 2, monkeypatch, on_gpu=False)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_gpu_slabs_fft_poisson(R, gpu, world, monkeypatch):
+    if gpu.lib.cfdnn_device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    _check_fft_slabs(gpu, R, world, (128, 48, 32 * world), "rk3", 1, monkeypatch, on_gpu=True)
