@@ -61,6 +61,11 @@ class Config(C.Structure):
                 ("poisson_solver", C.c_int)]
 
 
+class TripDesc(C.Structure):
+    _fields_ = [("amplitude", C.c_double), ("duration", C.c_double), ("ramp_off_start", C.c_double), ("w_scale", C.c_double),
+                ("env_x", c_double_p), ("g_y", c_double_p), ("Fz_v", c_double_p), ("Fz_w", c_double_p)]
+
+
 class CfdnnError(RuntimeError):
     def __init__(self, code, msg):
         super().__init__(f"cfdnn error {code}: {msg}")
@@ -122,6 +127,10 @@ _SIGS = {
     "cfdnn_fft_is_suitable": (C.c_int, [C.POINTER(C.c_int), C.c_int, C.c_int]),
     "cfdnn_fft_solve_dev": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_int)]),
     "cfdnn_fft_solve": (C.c_int, [C.c_void_p, c_double_p, c_double_p, C.POINTER(C.c_int)]),
+    "cfdnn_solver_set_trip_forcing": (C.c_int, [C.c_void_p, C.POINTER(TripDesc)]),
+    "cfdnn_solver_get_time": (C.c_int, [C.c_void_p, C.POINTER(C.c_double)]),
+    "cfdnn_solver_set_time": (C.c_int, [C.c_void_p, C.c_double]),
+    "cfdnn_solver_apply_velocity_filter": (C.c_int, [C.c_void_p, C.c_double]),
     "cfdnn_les_update": (C.c_int, [C.POINTER(MeshDesc), C.c_int, C.c_double, c_double_p, c_double_p, c_double_p, c_double_p]),
     "cfdnn_solver_set_les_model": (C.c_int, [C.c_void_p, C.c_int, C.c_double]),
     "cfdnn_nn_forward": (C.c_int, [C.c_void_p, c_double_p, c_double_p, C.c_size_t]),

@@ -43,7 +43,7 @@ def rel_l2(a, b):
 
 
 FIELD_ID = {"u": 0, "v": 1, "w": 2, "p": 3, "pcorr": 4, "div": 5, "rhs": 6, "nut": 7, "k": 8, "omega": 9,
-            "nueff": 10, "tau_xx": 11, "tau_xy": 12, "tau_yy": 13}
+            "nueff": 10, "tau_xx": 11, "tau_xy": 12, "tau_yy": 13, "u_star": 14, "v_star": 15, "w_star": 16}
 
 
 
@@ -220,3 +220,87 @@ def nn_create(B, kind, W, b, means=None, stds=None, act=None):
     B.check(B.lib.cfdnn_nn_create(NN_KIND[kind], n, dims_c, act_c, Wp, bp, capi.dptr(means) if means is not None else None,
                                   capi.dptr(stds) if stds is not None else None, C.byref(h)))
     return h
+
+
+def trip_tables(Nx, Ny, Nz, x_lo, Lx, yf, z_lo, Lz, fx, y_lo, y_hi, amplitude=3.0, n_modes=8, x_start=-1.0, x_end=-1.0,
+                Ng=1, k_offset=0, Nz_global=None):
+    """The tables of the reference's trip-region forcing, RANSSolver::initialize_trip_forcing (src/solver.cpp:818-923),
+    for cfdnn_solver_set_trip_forcing: x envelope on cell centres, g(y) = y (1 - y^2) on the y faces `yf` (Ny+2Ng+1
+    values), spanwise mode sums on cell centres / z faces with the phases of std::srand(12345); std::rand() (the C
+    library's generator, called through ctypes so the sequence is the reference's).  Returns (amplitude * u_tau^2, dict)."""
+    import ctypes
+    import ctypes.util
+    import math
+    libc = ctypes.CDLL(ctypes.util.find_library("c"))
+    libc.srand(12345)
+    RAND_MAX = 2147483647
+    phases = [2.0 * math.pi * float(libc.rand()) / RAND_MAX for _ in range(n_modes)]
+    delta = 0.5 * (y_hi - y_lo)
+    u_tau = math.sqrt(delta * abs(fx))
+    x0 = x_lo + 0.1 * Lx if x_start < 0 else x_start
+    x1 = x_lo + 0.2 * Lx if x_end < 0 else x_end
+    width = x1 - x0
+    dx = Lx / Nx
+    env = np.zeros(Nx + 2 * Ng)
+    for i in range(Nx + 2 * Ng):
+        x = x_lo + (i - Ng + 0.5) * dx
+        if x0 <= x <= x1:
+            xi = (x - x0) / width
+            env[i] = 0.5 * (1.0 - math.cos(2.0 * math.pi * xi))
+    yf = np.asarray(yf, dtype=np.float64)
+    g_y = yf * (1.0 - yf * yf)
+    out = {"env_x": env, "g_y": np.ascontiguousarray(g_y)}
+    if Nz > 1:
+        NzG = Nz_global or Nz
+        dz = Lz / NzG
+        wsum = 0.0
+        for m in range(n_modes):
+            wsum += 1.0 / (m + 1)
+        fzv = np.zeros(Nz + 2 * Ng)
+        fzw = np.zeros(Nz + 2 * Ng + 1)
+        for k in range(Nz + 2 * Ng):
+            z = z_lo + (k + k_offset - Ng + 0.5) * dz
+            s = 0.0
+            for m in range(n_modes):
+                kz = 2.0 * math.pi * (m + 1) / Lz
+                s += ((1.0 / (m + 1)) / wsum) * math.sin(kz * z + phases[m])
+            fzv[k] = s
+        for k in range(Nz + 2 * Ng + 1):
+            z = z_lo + (k + k_offset - Ng) * dz
+            s = 0.0
+            for m in range(n_modes):
+                kz = 2.0 * math.pi * (m + 1) / Lz
+                s += ((1.0 / (m + 1)) / wsum) * math.cos(kz * z + phases[m])
+            fzw[k] = s
+        out["Fz_v"], out["Fz_w"] = fzv, fzw
+    return amplitude * u_tau * u_tau, out
+
+
+def set_trip(B, h, A, tabs, duration=2.0, ramp_off_start=1.5, w_scale=1.0, force_w=True):
+    d = capi.TripDesc(amplitude=A, duration=duration, ramp_off_start=ramp_off_start, w_scale=w_scale)
+    d.env_x, d.g_y = capi.dptr(tabs["env_x"]), capi.dptr(tabs["g_y"])
+    if "Fz_v" in tabs:
+        d.Fz_v = capi.dptr(tabs["Fz_v"])
+        if force_w:
+            d.Fz_w = capi.dptr(tabs["Fz_w"])
+    B.check(B.lib.cfdnn_solver_set_trip_forcing(h, C.byref(d)))
+
+
+def velocity_filter_reference(u, v, w, strength):
+    """apply_velocity_filter (src/solver.cpp:4065-4162) with every second difference taken from the unfiltered field
+    (ghost-inclusive 3-D arrays, Ng = 1); returns filtered copies."""
+    alpha = strength * 0.25
+    alpha_y = alpha * 0.5
+    out = []
+    for q, comp in ((u, 0), (v, 1), (w, 2)):
+        r = q.copy()
+        c = q[1:-1, 1:-1, 1:-1]
+        Lx = q[1:-1, 1:-1, :-2] - 2.0 * c + q[1:-1, 1:-1, 2:]
+        Lz = q[:-2, 1:-1, 1:-1] - 2.0 * c + q[2:, 1:-1, 1:-1]
+        Ly = q[1:-1, :-2, 1:-1] - 2.0 * c + q[1:-1, 2:, 1:-1]
+        Ly = Ly.copy()
+        Ly[:, 0, :] = 0.0            # j = Ng: first cell row (u, w) / lower wall face (v)
+        Ly[:, -1, :] = 0.0           # last cell row (u, w) / upper wall face (v)
+        r[1:-1, 1:-1, 1:-1] = c + (alpha * (Lx + Lz) + alpha_y * Ly)
+        out.append(r)
+    return out

@@ -262,6 +262,14 @@ int cfdnn_les_update(const cfdnn_mesh_desc* mesh, int model, double constant, co
 int cfdnn_solver_set_les_model(cfdnn_solver* s, int model, double constant) {
     return guarded([&] { s->impl.set_les_model(model, constant); });
 }
+int cfdnn_solver_set_trip_forcing(cfdnn_solver* s, const cfdnn_trip_desc* desc) {
+    return guarded([&] { s->impl.set_trip_forcing(desc); });
+}
+int cfdnn_solver_get_time(const cfdnn_solver* s, double* t) { *t = s->impl.time(); return CFDNN_OK; }
+int cfdnn_solver_set_time(cfdnn_solver* s, double t) { s->impl.set_time(t); return CFDNN_OK; }
+int cfdnn_solver_apply_velocity_filter(cfdnn_solver* s, double strength) {
+    return guarded([&] { s->impl.apply_velocity_filter(strength); });
+}
 int cfdnn_nn_forward(cfdnn_nn* nn, const double* x, double* y, size_t n) {
     return guarded([&] { nn->impl.forward_host(x, y, n); });
 }

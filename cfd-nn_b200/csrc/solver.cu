@@ -268,14 +268,14 @@ void Solver::upload(int field, const double* host, size_t n) {
 }
 size_t Solver::plane_elems(int field) const {
     switch (field) {
-        case CFDNN_F_U: return (size_t)g_.up;
-        case CFDNN_F_V: return (size_t)g_.vp;
-        case CFDNN_F_W: return (size_t)g_.wp;
+        case CFDNN_F_U: case CFDNN_F_U_STAR: case CFDNN_F_U_OLD: case CFDNN_F_CONV_U: case CFDNN_F_DIFF_U: return (size_t)g_.up;
+        case CFDNN_F_V: case CFDNN_F_V_STAR: case CFDNN_F_V_OLD: case CFDNN_F_CONV_V: case CFDNN_F_DIFF_V: return (size_t)g_.vp;
+        case CFDNN_F_W: case CFDNN_F_W_STAR: case CFDNN_F_W_OLD: case CFDNN_F_CONV_W: case CFDNN_F_DIFF_W: return (size_t)g_.wp;
         default: return (size_t)g_.cp;
     }
 }
-void Solver::download(int field, double* host, size_t n) {
-    size_t want; double* d = field_ptr(field, &want);
+void Solver::download(int field, double* host, size_t n) {          // the work fields of the device view can be read too
+    size_t want; double* d = view_ptr(field, &want);
     if (n != want) throw std::invalid_argument("download: size mismatch for field " + std::to_string(field));
     if (is2d_) {     // device plane Ng -> host plane 0; the reference never touches the other planes (zeros)
         const size_t pl = plane_elems(field);
@@ -599,6 +599,7 @@ void Solver::euler_step() {
     PhaseEv* pe = ph_begin(CFDNN_PHASE_MOMENTUM);
     momentum(vel_, star_, dt_, /*seam_average=*/true);         // conv + diff + predictor :1505-1722
     ph_end(pe);
+    trip_force(star_, dt_);                                      // :1724-1810
     const bool px = vbc_[0] == CFDNN_VBC_PERIODIC && vbc_[1] == CFDNN_VBC_PERIODIC;
     const bool py = vbc_[2] == CFDNN_VBC_PERIODIC && vbc_[3] == CFDNN_VBC_PERIODIC;
     const bool pz = vbc_[4] == CFDNN_VBC_PERIODIC && vbc_[5] == CFDNN_VBC_PERIODIC;
@@ -649,6 +650,59 @@ void Solver::build_nu_eff() {
     const dim3 gr = grid3(g_.Nx + 2 * g_.Ng, g_.Ny + 2 * g_.Ng, g_.Nz + 2 * g_.Ng);
     CFDNN_LAUNCH(k_nu_eff, gr, kB, 0, st_, g_, cfg_.nu, nut_, has_model() ? 1 : 0, nueff_);
     if (has_model()) halo_cell(nueff_, /*bc_site=*/false);
+}
+
+// ---------------------------------------------------------------- trip forcing, velocity filter
+void Solver::set_trip_forcing(const cfdnn_trip_desc* d) {
+    if (!d) { trip_on_ = false; return; }
+    if (!d->env_x || !d->g_y) throw std::invalid_argument("set_trip_forcing: env_x and g_y are required");
+    if (!is2d_ && !d->Fz_v) throw std::invalid_argument("set_trip_forcing: a 3-D mesh needs Fz_v");
+    const int Ng = g_.Ng;
+    auto up = [](DevBuf<double>& b, const double* h, size_t n) {
+        b.alloc(n, false);
+        CFDNN_CUDA(cudaMemcpy(b.p, h, n * sizeof(double), cudaMemcpyHostToDevice));
+    };
+    up(trip_env_x_, d->env_x, g_.Nx + 2 * Ng);
+    up(trip_g_y_, d->g_y, g_.Ny + 2 * Ng + 1);
+    if (!is2d_) up(trip_fz_v_, d->Fz_v, g_.Nz + 2 * Ng);
+    trip_w_ = !is2d_ && d->Fz_w != nullptr;                     // force_w = config.trip_force_w && is_3d :1730
+    if (trip_w_) up(trip_fz_w_, d->Fz_w, g_.Nz + 2 * Ng + 1);
+    trip_A_ = d->amplitude; trip_duration_ = d->duration; trip_ramp_start_ = d->ramp_off_start; trip_w_scale_ = d->w_scale;
+    trip_on_ = true;
+}
+
+void Solver::trip_force(Vel& star, double dt) {
+    if (!trip_on_ || !(time_ < trip_duration_)) return;         // is_trip_active(), include/solver.hpp:721
+    double ramp = 1.0;                                          // get_trip_time_ramp :939-950
+    if (time_ > trip_ramp_start_) {
+        const double frac = (time_ - trip_ramp_start_) / (trip_duration_ - trip_ramp_start_);
+        ramp = 0.5 * (1.0 + std::cos(M_PI * frac));
+    }
+    const double A = trip_A_ * ramp;
+    const int nk = is2d_ ? 1 : g_.Nz;
+    const dim3 blk(64, 4, 1);
+    CFDNN_LAUNCH(k_trip_v, dim3((g_.Nx + 63) / 64, (g_.Ny + 1 + 3) / 4, nk), blk, 0, st_, g_, star.v, trip_env_x_.p, trip_g_y_.p,
+                 is2d_ ? nullptr : trip_fz_v_.p, A, dt, g_.Ng, nk);
+    if (trip_w_)
+        CFDNN_LAUNCH(k_trip_w, dim3((g_.Nx + 63) / 64, (g_.Ny + 3) / 4, g_.Nz + 1), blk, 0, st_, g_, star.w, trip_env_x_.p,
+                     trip_g_y_.p, trip_fz_w_.p, A * trip_w_scale_, dt);
+}
+
+void Solver::apply_velocity_filter(double strength) {           // src/solver.cpp:4065-4162
+    if (strength <= 0.0) return;
+    if (is2d_) return;                                           // the reference filters 3-D meshes only (:4090)
+    if (multi()) throw std::invalid_argument("apply_velocity_filter: single-GPU only");
+    const double alpha = strength * 0.25, alpha_y = alpha * 0.5;
+    CFDNN_CUDA(cudaMemcpyAsync(conv_.u, vel_.u, su_ * sizeof(double), cudaMemcpyDeviceToDevice, st_));
+    CFDNN_CUDA(cudaMemcpyAsync(conv_.v, vel_.v, sv_ * sizeof(double), cudaMemcpyDeviceToDevice, st_));
+    CFDNN_CUDA(cudaMemcpyAsync(conv_.w, vel_.w, sw_ * sizeof(double), cudaMemcpyDeviceToDevice, st_));
+    const dim3 blk(64, 4, 1);
+    auto grid = [&](int nx, int ny, int nz) { return dim3((nx + 63) / 64, (ny + 3) / 4, nz); };
+    CFDNN_LAUNCH((k_velocity_filter<0>), grid(g_.Nx + 1, g_.Ny, g_.Nz), blk, 0, st_, g_, vel_.u, conv_.u, alpha, alpha_y);
+    CFDNN_LAUNCH((k_velocity_filter<1>), grid(g_.Nx, g_.Ny + 1, g_.Nz), blk, 0, st_, g_, vel_.v, conv_.v, alpha, alpha_y);
+    CFDNN_LAUNCH((k_velocity_filter<2>), grid(g_.Nx, g_.Ny, g_.Nz + 1), blk, 0, st_, g_, vel_.w, conv_.w, alpha, alpha_y);
+    CFDNN_CUDA(cudaStreamSynchronize(st_));
+    check_launch("apply_velocity_filter");
 }
 
 void Solver::set_les_model(int model, double constant) {

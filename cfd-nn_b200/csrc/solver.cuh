@@ -54,6 +54,10 @@ public:
     double dt() const { return dt_; }
     void set_turbulence_model(NNClosure* nn) { nn_ = nn; }
     void set_external_nu_t(bool on, bool transport = false) { ext_nut_ = on; ext_transport_ = on && transport; }   // nu_t uploaded by the caller (bridged host model)
+    void set_trip_forcing(const cfdnn_trip_desc* d);         // trip-region forcing in the Euler predictor
+    void apply_velocity_filter(double strength);             // explicit Laplacian filter between steps
+    double time() const { return time_; }
+    void set_time(double t) { time_ = t; }
     void set_les_model(int model, double constant);          // static LES SGS closure evaluated at the top of step()
     bool has_model() const { return nn_ != nullptr || ext_nut_ || les_model_ != 0; }
     double* view_ptr(int field, size_t* n) const;           // device twin of a field (cfdnn_solver_device_ptr)
@@ -99,6 +103,11 @@ private:
     size_t npartial_ = 0;
 
     std::unique_ptr<Multigrid> mg_;
+    // trip forcing (src/solver.cpp:818-950): device copies of the caller's tables
+    bool trip_on_ = false, trip_w_ = false;
+    double trip_A_ = 0, trip_duration_ = 0, trip_ramp_start_ = 0, trip_w_scale_ = 1;
+    DevBuf<double> trip_env_x_, trip_g_y_, trip_fz_v_, trip_fz_w_;
+    void trip_force(Vel& star, double dt);
     std::unique_ptr<FftPoisson> fft_;        // cfg.poisson_solver == CFDNN_POISSON_FFT (periodic x/z, walls y)
     bool fft_active_ = false;                // the current velocity BCs allow it (else the multigrid takes over)
     NNClosure* nn_ = nullptr;

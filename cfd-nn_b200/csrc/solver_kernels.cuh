@@ -668,6 +668,49 @@ static __global__ void k_final_max_rows(const double* __restrict__ part, int n, 
         __syncthreads();
     }
 }
+// Trip-region forcing on the provisional velocity (Euler predictor, src/solver.cpp:1724-1810): v* += dt A env_x[i] g_y[j]
+// Fz_v[k] on the v faces, w* += dt A_w env_x[i] (g_y[j] + g_y[j+1]) / 2 Fz_w[k] on the w faces; the tables come from the
+// caller (initialize_trip_forcing :818-923).  fz == nullptr: 2-D, Fz = 1.  plane0: first z plane, nk planes.
+static __global__ void k_trip_v(Geom g, double* __restrict__ v, const double* __restrict__ env_x, const double* __restrict__ g_y,
+                                const double* __restrict__ fz, double A, double dt, int plane0, int nk) {
+    const int ix = blockIdx.x * blockDim.x + threadIdx.x, iy = blockIdx.y * blockDim.y + threadIdx.y, iz = blockIdx.z;
+    if (ix >= g.Nx || iy > g.Ny || iz >= nk) return;
+    const int i = ix + g.Ng, j = iy + g.Ng, k = plane0 + iz;
+    const double Fz = fz ? fz[k] : 1.0;
+    const double f_trip = A * env_x[i] * g_y[j] * Fz;
+    v[VIDX(i, j, k)] += dt * f_trip;
+}
+static __global__ void k_trip_w(Geom g, double* __restrict__ w, const double* __restrict__ env_x, const double* __restrict__ g_y,
+                                const double* __restrict__ fz, double A_w, double dt) {
+    const int ix = blockIdx.x * blockDim.x + threadIdx.x, iy = blockIdx.y * blockDim.y + threadIdx.y, iz = blockIdx.z;
+    if (ix >= g.Nx || iy >= g.Ny || iz > g.Nz) return;
+    const int i = ix + g.Ng, j = iy + g.Ng, k = iz + g.Ng;
+    const double gy = 0.5 * (g_y[j] + g_y[j + 1]);              // j > 0 and j < size - 1 always hold for interior rows
+    const double f_trip = A_w * env_x[i] * gy * fz[k];
+    w[WIDX(i, j, k)] += dt * f_trip;
+}
+
+// Explicit Laplacian velocity filter (apply_velocity_filter, src/solver.cpp:4065-4162): q += alpha (Lx + Lz) + alpha_y Ly
+// with second differences of the UNFILTERED field `old` (a copy of q made by the caller); the y term is dropped on the
+// wall-adjacent rows (u, w: first and last cell row; v: the two wall faces).  COMP 0/1/2 = u/v/w.
+template <int COMP>
+static __global__ void k_velocity_filter(Geom g, double* __restrict__ q, const double* __restrict__ old, double alpha,
+                                         double alpha_y) {
+    const int ix = blockIdx.x * blockDim.x + threadIdx.x, iy = blockIdx.y * blockDim.y + threadIdx.y, iz = blockIdx.z;
+    const int nx = g.Nx + (COMP == 0), ny = g.Ny + (COMP == 1), nz = g.Nz + (COMP == 2);
+    if (ix >= nx || iy >= ny || iz >= nz) return;
+    const int i = ix + g.Ng, j = iy + g.Ng, k = iz + g.Ng;
+    const size_t sj = COMP == 0 ? g.us : COMP == 1 ? g.vs : g.ws;
+    const size_t sk = COMP == 0 ? g.up : COMP == 1 ? g.vp : g.wp;
+    const size_t c = (size_t)k * sk + (size_t)j * sj + i;
+    const double Lx = old[c - 1] - 2.0 * old[c] + old[c + 1];
+    const double Lz = old[c - sk] - 2.0 * old[c] + old[c + sk];
+    double Ly = 0.0;
+    const bool inner = COMP == 1 ? (j > g.Ng && j < g.Ny + g.Ng) : (j > g.Ng && j < g.Ny + g.Ng - 1);
+    if (inner) Ly = old[c - sj] - 2.0 * old[c] + old[c + sj];
+    q[c] = old[c] + (alpha * (Lx + Lz) + alpha_y * Ly);
+}
+
 // non-finite flag over a flat array: x - x != 0 catches NaN and Inf (check_for_nan_inf :3195-3350)
 static __global__ void __launch_bounds__(256)
 k_nonfinite(const double* __restrict__ a, size_t n, int* __restrict__ flag) {

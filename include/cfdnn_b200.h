@@ -180,7 +180,7 @@ int cfdnn_solver_set_body_force(cfdnn_solver* s, double fx, double fy, double fz
 int cfdnn_solver_set_dt(cfdnn_solver* s, double dt);                    /* set_dt             */
 int cfdnn_solver_get_dt(const cfdnn_solver* s, double* dt);             /* current_dt         */
 int cfdnn_solver_upload(cfdnn_solver* s, int field, const double* host, size_t n);   /* sync_to_gpu   */
-int cfdnn_solver_download(cfdnn_solver* s, int field, double* host, size_t n);       /* sync_from_gpu */
+int cfdnn_solver_download(cfdnn_solver* s, int field, double* host, size_t n);       /* sync_from_gpu; also the CFDNN_F_*_STAR / OLD / CONV / DIFF work fields */
 size_t cfdnn_solver_field_size(const cfdnn_solver* s, int field);
 /* initialize(const VectorField&) :1060-1062 — apply_velocity_bc on the uploaded velocity */
 int cfdnn_solver_initialize(cfdnn_solver* s);
@@ -222,6 +222,28 @@ int cfdnn_solver_device_ptr(cfdnn_solver* s, int field, double** dev_out, size_t
  * upload(CFDNN_F_NUT); with this flag on, step() builds nu_eff = nu + nu_t (src/solver.cpp:1326-1410) and
  * takes the closure branches of the diffusion-CFL re-check and the NaN guard as if a model were attached */
 int cfdnn_solver_set_external_nu_t(cfdnn_solver* s, int on);
+/* Trip-region forcing (Config::trip_*, include/config.hpp:202-210): a localized body force on v* (and w*) in the Euler
+ * predictor while time < duration (src/solver.cpp:1724-1810, get_trip_time_ramp :939-950).  The tables are the ones
+ * initialize_trip_forcing (:818-923) builds — x envelope on cell centres (Nx+2Ng), g(y) = y (1 - y^2) on the y faces
+ * (Ny+2Ng+1), the spanwise mode sums on cell centres (Nz+2Ng) and z faces (Nz+2Ng+1) with std::srand(12345) phases — and
+ * are computed by the caller (the C++ shim does it with the reference's expressions; a z-slab passes its own planes).
+ * amplitude = trip_amplitude * u_tau^2.  Fz_v = NULL on 2-D meshes; Fz_w = NULL: no w forcing.  desc = NULL: off.
+ * As in the reference the RK integrators do not apply it. */
+typedef struct cfdnn_trip_desc {
+    double amplitude, duration, ramp_off_start, w_scale;
+    const double* env_x;
+    const double* g_y;
+    const double* Fz_v;
+    const double* Fz_w;
+} cfdnn_trip_desc;
+int cfdnn_solver_set_trip_forcing(cfdnn_solver* s, const cfdnn_trip_desc* desc);
+int cfdnn_solver_get_time(const cfdnn_solver* s, double* t);             /* current_time()            */
+int cfdnn_solver_set_time(cfdnn_solver* s, double t);                    /* restart / tests           */
+/* apply_velocity_filter(strength) (include/solver.hpp:260, src/solver.cpp:4065-4162): explicit Laplacian filter of u, v, w
+ * between steps (3-D meshes; strength <= 0: no-op).  The reference has this kernel in its GPU build only and updates
+ * the field in place while neighbouring threads read it; here every second difference is taken from the unfiltered
+ * field (the order-independent reading of the same formula). */
+int cfdnn_solver_apply_velocity_filter(cfdnn_solver* s, double strength);
 /* device ms of the last step()/run() spent in the closure update (TurbulenceModel::update inside step(),
  * src/solver.cpp:1284-1324) and in the fused momentum kernels (convective + diffusive + advance) */
 enum { CFDNN_PHASE_CLOSURE = 0, CFDNN_PHASE_MOMENTUM = 1, CFDNN_PHASE_IMPLICIT_Y = 2, CFDNN_PHASE_POISSON = 3,

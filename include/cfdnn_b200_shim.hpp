@@ -13,6 +13,8 @@
 // Nothing here computes: there is no CPU path.  See INTEGRATION.md for the build line.
 #pragma once
 #include <memory>
+#include <cstdlib>
+#include <cmath>
 #include <stdexcept>
 #include <string>
 #include <utility>
@@ -315,7 +317,63 @@ public:
         sync_to_gpu();
         check(cfdnn_solver_initialize(h_));
         if (turb_) turb_->initialize(*mesh_, velocity_);
+        initialize_trip_forcing();
     }
+    /// initialize_trip_forcing (src/solver.cpp:818-923): the envelope / profile / spanwise-mode tables, built here with the
+    /// reference's expressions (std::srand(12345) phases) from its Mesh and Config and handed to the backend, which adds
+    /// the force to v* and w* in the Euler predictor while current_time() < trip_duration (:1724-1810).
+    void initialize_trip_forcing() {
+        if (!config_.trip_enabled) { check(cfdnn_solver_set_trip_forcing(h_, nullptr)); return; }
+        const Mesh& m = *mesh_;
+        const double delta = 0.5 * (m.y_max - m.y_min);
+        const double u_tau = std::sqrt(delta * std::abs(fx_));
+        const double Lx = m.x_max - m.x_min, Lz = m.z_max - m.z_min;
+        const double x0 = config_.trip_x_start < 0 ? m.x_min + 0.1 * Lx : config_.trip_x_start;
+        const double x1 = config_.trip_x_end < 0 ? m.x_min + 0.2 * Lx : config_.trip_x_end;
+        const double width = x1 - x0;
+        const int nm = config_.trip_n_modes_z;
+        std::srand(12345);
+        std::vector<double> ph(nm);
+        for (int q = 0; q < nm; ++q) ph[q] = 2.0 * M_PI * static_cast<double>(std::rand()) / RAND_MAX;
+        std::vector<double> env(m.total_Nx(), 0.0), gy(m.total_Ny() + 1, 0.0), fzv, fzw;
+        for (int i = 0; i < m.total_Nx(); ++i) {
+            const double x = m.xc[i];
+            if (x >= x0 && x <= x1) env[i] = 0.5 * (1.0 - std::cos(2.0 * M_PI * ((x - x0) / width)));
+        }
+        for (int j = 0; j < static_cast<int>(gy.size()) && j < static_cast<int>(m.yf.size()); ++j)
+            gy[j] = m.yf[j] * (1.0 - m.yf[j] * m.yf[j]);
+        const bool is3d = !m.is2D();
+        if (is3d) {
+            double wsum = 0.0;
+            for (int q = 0; q < nm; ++q) wsum += 1.0 / (q + 1);
+            fzv.assign(m.total_Nz(), 0.0);
+            fzw.assign(m.total_Nz() + 1, 0.0);
+            for (int k = 0; k < m.total_Nz(); ++k) {
+                double sum = 0.0;
+                for (int q = 0; q < nm; ++q)
+                    sum += ((1.0 / (q + 1)) / wsum) * std::sin(2.0 * M_PI * (q + 1) / Lz * m.zc[k] + ph[q]);
+                fzv[k] = sum;
+            }
+            for (int k = 0; k < static_cast<int>(fzw.size()) && k < static_cast<int>(m.zf.size()); ++k) {
+                double sum = 0.0;
+                for (int q = 0; q < nm; ++q)
+                    sum += ((1.0 / (q + 1)) / wsum) * std::cos(2.0 * M_PI * (q + 1) / Lz * m.zf[k] + ph[q]);
+                fzw[k] = sum;
+            }
+        }
+        cfdnn_trip_desc d{};
+        d.amplitude = config_.trip_amplitude * u_tau * u_tau;
+        d.duration = config_.trip_duration;
+        d.ramp_off_start = config_.trip_ramp_off_start;
+        d.w_scale = config_.trip_w_scale;
+        d.env_x = env.data(); d.g_y = gy.data();
+        d.Fz_v = is3d ? fzv.data() : nullptr;
+        d.Fz_w = (is3d && config_.trip_force_w) ? fzw.data() : nullptr;
+        check(cfdnn_solver_set_trip_forcing(h_, &d));
+    }
+    /// apply_velocity_filter (include/solver.hpp:260, src/solver.cpp:4065-4162): explicit Laplacian filter between steps
+    void apply_velocity_filter(double strength) { check(cfdnn_solver_apply_velocity_filter(h_, strength)); }
+    double current_time() const { double t = 0.0; cfdnn_solver_get_time(h_, &t); return t; }
     /// initialize_uniform (src/solver.cpp:1132-1167; the k / omega seeding of transport models is the model's own
     /// initialize() here)
     void initialize_uniform(double u0, double v0) {

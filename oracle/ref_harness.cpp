@@ -145,6 +145,15 @@ Config make_config(const Mesh& mesh) {
     c.nn_scaling_path = arg_s("nn_scaling", c.nn_weights_path);
     c.nu_t_max = arg_d("nu_t_max", c.nu_t_max);
     c.implicit_y_diffusion = arg_i("implicit_y", 0) != 0;
+    c.trip_enabled = arg_i("trip", 0) != 0;                 // trip-region forcing (Euler path; needs call_initialize=1)
+    c.trip_amplitude = arg_d("trip_amp", c.trip_amplitude);
+    c.trip_duration = arg_d("trip_duration", c.trip_duration);
+    c.trip_ramp_off_start = arg_d("trip_ramp", c.trip_ramp_off_start);
+    c.trip_n_modes_z = arg_i("trip_modes", c.trip_n_modes_z);
+    c.trip_force_w = arg_i("trip_force_w", c.trip_force_w ? 1 : 0) != 0;
+    c.trip_w_scale = arg_d("trip_w_scale", c.trip_w_scale);
+    c.trip_x_start = arg_d("trip_x0", c.trip_x_start);
+    c.trip_x_end = arg_d("trip_x1", c.trip_x_end);
     return c;
 }
 

@@ -891,3 +891,96 @@ def check_step_with_fft(B, oracle, stretched=False, N=(16, 16, 16), nsteps=2):
            (V[1:-1, 2:Ny + 2, 1:-1] - V[1:-1, 1:Ny + 1, 1:-1]) / dyv[None, :, None] +
            (W[2:Nz + 2, 1:-1, 1:-1] - W[1:Nz + 1, 1:-1, 1:-1]) / dz)
     assert np.abs(div).max() <= 1e-11 * scale / min(dx, dz, dyv.min()), np.abs(div).max()
+
+
+# ---------------------------------------------------------------- trip forcing + velocity filter
+def check_trip_forcing(B, N=(16, 16, 16), stretched=False, force_w=True):
+    """Trip-region forcing in the Euler predictor (src/solver.cpp:818-950, 1724-1810).  The reference applies it through
+    pointers that only its GPU build sets (src/solver.cpp:906-911), so its CPU build — the oracle — cannot run it; the
+    check is on the definition instead: the provisional velocity of a step with the forcing minus the one without is
+    exactly dt A(t) env_x[i] g_y[j] Fz[k] (tables restated from initialize_trip_forcing, phases from the C library's
+    srand(12345) / rand()), through the three regimes of the time ramp (full, cosine ramp-off, off), u* untouched."""
+    import ctypes as C
+    K = R.backend
+    extra = dict(**(CHANNEL_BOX if stretched else CHANNEL_UNIFORM))
+    case = ("chan_trip", N, "PPWWPP", "euler", "skew", 4, 1, "pchan", (1.0, 0, 0), extra)
+    Nx, Ny, Nz = N
+    y0, y1 = extra["y0"], extra["y1"]
+    arrs = K.stretched_y_metrics(Ny, y0, y1, 2.0) if stretched else None
+    yf = arrs["yf"] if stretched else y0 + (np.arange(Ny + 3) - 1) * ((y1 - y0) / Ny)
+    A, tabs = K.trip_tables(Nx, Ny, Nz, 0.0, extra["x1"], yf, 0.0, extra["z1"], 1.0, y0, y1, amplitude=3.0, n_modes=5)
+    dur, ramp0, wsc, dt = 0.035, 0.015, 1.5, 0.01
+    sh = R.shapes(*N)
+
+    def stars(trip, t0):
+        h = make_solver(B, case, mesh_arrays=arrs)
+        try:
+            if trip:
+                K.set_trip(B, h, A, tabs, duration=dur, ramp_off_start=ramp0, w_scale=wsc, force_w=force_w)
+            B.check(B.lib.cfdnn_solver_initialize(h))
+            B.check(B.lib.cfdnn_solver_set_time(h, t0))
+            B.step(h)
+            t = C.c_double()
+            B.lib.cfdnn_solver_get_time(h, C.byref(t))
+            assert abs(t.value - (t0 + dt)) < 1e-15
+            return {n: B.download(h, n + "_star", sh[n]) for n in ("u", "v", "w")}
+        finally:
+            B.lib.cfdnn_solver_destroy(h)
+
+    for t0 in (0.0, 0.02, 0.03, 0.035, 0.05):
+        on, off = stars(True, t0), stars(False, t0)
+        if t0 >= dur:
+            r = 0.0
+        elif t0 <= ramp0:
+            r = 1.0
+        else:
+            r = 0.5 * (1.0 + np.cos(np.pi * (t0 - ramp0) / (dur - ramp0)))
+        assert np.array_equal(on["u"], off["u"])
+        fz_v = tabs["Fz_v"][1:Nz + 1] if Nz > 1 else np.ones(1)
+        fv = (A * r) * tabs["env_x"][None, None, 1:Nx + 1] * tabs["g_y"][None, 1:Ny + 2, None] * fz_v[:, None, None]
+        dv = (on["v"] - off["v"])[(slice(0, 1) if Nz == 1 else slice(1, Nz + 1)), 1:Ny + 2, 1:Nx + 1]
+        # interior faces only: the wall faces are overwritten by the BC pass after the forcing (g_y vanishes there anyway)
+        scale = max(np.abs(fv).max() * dt, 1e-300)
+        if r == 0.0:
+            assert np.array_equal(on["v"], off["v"]) and np.array_equal(on["w"], off["w"])
+            continue
+        assert np.abs(dv[:, 1:-1] - dt * fv[:, 1:-1]).max() <= 1e-13 * max(scale, np.abs(off["v"]).max()), t0
+        assert np.abs(dv).max() > 1e-4 * dt
+        if Nz > 1 and force_w:
+            gy = 0.5 * (tabs["g_y"][1:Ny + 1] + tabs["g_y"][2:Ny + 2])
+            fw = (A * r * wsc) * tabs["env_x"][None, None, 1:Nx + 1] * gy[None, :, None] * tabs["Fz_w"][1:Nz + 2, None, None]
+            dw = (on["w"] - off["w"])[1:Nz + 2, 1:Ny + 1, 1:Nx + 1]
+            # the periodic seam averages faces k = Ng and Ng + Nz BEFORE the forcing (:1707-1722); both get their own term
+            assert np.abs(dw - dt * fw).max() <= 1e-13 * max(np.abs(fw).max() * dt, np.abs(off["w"]).max()), t0
+        else:
+            assert np.array_equal(on["w"], off["w"])
+
+
+def check_velocity_filter(B, N=(20, 12, 16), strength=0.3):
+    """apply_velocity_filter (src/solver.cpp:4065-4162) vs its numpy restatement (backend.velocity_filter_reference):
+    same expression order, no FMA contraction => bitwise; fields outside the filtered faces are untouched."""
+    K = R.backend
+    rng = np.random.default_rng(11)
+    sh = R.shapes(*N)
+    u, v, w = (rng.standard_normal(sh[n]) for n in ("u", "v", "w"))
+    case = ("filter", N, "PPWWPP", "rk3", "skew", 2, 1, "tgv", (0, 0, 0), dict(**CHANNEL_UNIFORM))
+    h = make_solver(B, case)
+    try:
+        B.upload(h, "u", u); B.upload(h, "v", v); B.upload(h, "w", w)
+        B.check(B.lib.cfdnn_solver_apply_velocity_filter(h, 0.0))              # strength <= 0: no-op
+        assert np.array_equal(B.download(h, "u", sh["u"]), u)
+        B.check(B.lib.cfdnn_solver_apply_velocity_filter(h, strength))
+        got = [B.download(h, n, sh[n]) for n in ("u", "v", "w")]
+    finally:
+        B.lib.cfdnn_solver_destroy(h)
+    Nx, Ny, Nz = N
+    ref = K.velocity_filter_reference(u, v, w, strength)
+    # filtered sets: u faces (Nx+1) x Ny x Nz, v faces Nx x (Ny+1) x Nz, w faces Nx x Ny x (Nz+1)
+    sel = {0: (slice(1, Nz + 1), slice(1, Ny + 1), slice(1, Nx + 2)), 1: (slice(1, Nz + 1), slice(1, Ny + 2), slice(1, Nx + 1)),
+           2: (slice(1, Nz + 2), slice(1, Ny + 1), slice(1, Nx + 1))}
+    for c, (g, r, q) in enumerate(zip(got, ref, (u, v, w))):
+        assert np.array_equal(g[sel[c]], r[sel[c]]), c
+        mask = np.ones(g.shape, dtype=bool)
+        mask[sel[c]] = False
+        assert np.array_equal(g[mask], q[mask]), c
+        assert np.abs(g[sel[c]] - q[sel[c]]).max() > 1e-3

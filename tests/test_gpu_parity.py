@@ -307,3 +307,13 @@ def test_fft_poisson_rejections(gpu):
 @pytest.mark.parametrize("stretched", [False, True], ids=["uniform", "stretched"])
 def test_step_with_fft_poisson_matches_converged_reference(gpu, oracle, stretched):
     cases.check_step_with_fft(gpu, oracle, stretched=stretched)
+
+
+# ---- trip forcing + velocity filter
+@pytest.mark.parametrize("kind", ["uniform", "stretched", "2d"])
+def test_trip_forcing_adds_the_reference_term(gpu, kind):
+    cases.check_trip_forcing(gpu, N=(32, 16, 1) if kind == "2d" else (32, 24, 16), stretched=kind == "stretched")
+
+
+def test_velocity_filter_matches_restatement(gpu):
+    cases.check_velocity_filter(gpu, N=(40, 24, 32))

@@ -218,3 +218,14 @@ def test_fft_poisson_rejections(sim):
 
 def test_step_with_fft_poisson_matches_converged_reference(oracle, sim):
     cases.check_step_with_fft(sim, oracle)
+
+
+# ---- trip forcing + velocity filter
+@pytest.mark.parametrize("kind", ["uniform", "stretched", "no_w", "2d"])
+def test_trip_forcing_adds_the_reference_term(sim, kind):
+    cases.check_trip_forcing(sim, N=(16, 16, 1) if kind == "2d" else (16, 12, 8), stretched=kind == "stretched",
+                             force_w=kind != "no_w")
+
+
+def test_velocity_filter_matches_restatement(sim):
+    cases.check_velocity_filter(sim)
