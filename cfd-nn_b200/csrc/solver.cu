@@ -5,6 +5,7 @@
 #include "comm.cuh"
 #include "nn.cuh"
 #include "les.cuh"
+#include "sst.cuh"
 #include <cmath>
 #include <algorithm>
 #include <cstring>
@@ -61,6 +62,7 @@ Solver::Solver(const cfdnn_mesh_desc& m, const cfdnn_config& c) : mesh_(m), cfg_
         if (!m.dyv || !m.dyc) throw std::invalid_argument("Solver: stretched mesh needs dyv/dyc");
         const int nv = Ny + 2 * Ng, nc = Ny + 2 * Ng + 1;
         h_dyv_.assign(m.dyv, m.dyv + nv);
+        h_dyc_.assign(m.dyc, m.dyc + nc);
         std::vector<double> r(nv), rc(nc);
         for (int j = 0; j < nv; ++j) r[j] = 1.0 / m.dyv[j];
         for (int j = 0; j < nc; ++j) rc[j] = 1.0 / m.dyc[j];
@@ -719,7 +721,24 @@ void Solver::set_les_model(int model, double constant) {
     les_c_ = constant;
 }
 
+void Solver::set_sst_model(bool on) {
+    if (!on) { sst_.reset(); return; }
+    if (!is2d_)
+        throw std::invalid_argument("set_sst_model: the reference's SST k-omega transport is two-dimensional (k, omega, nu_t "
+                                    "indexed (i, j)); on a 3-D mesh bridge the host model instead");
+    cfdnn_mesh_desc m = mesh_;
+    m.yc = h_yc_.empty() ? nullptr : h_yc_.data();
+    m.dyc = h_dyc_.empty() ? nullptr : h_dyc_.data();
+    sst_ = std::make_unique<SstModel>(m, cfg_.nu);
+}
+
 void Solver::update_turbulence() {
+    if (sst_) {
+        // transport first, with the previous step's nu_t, then the closure (src/solver.cpp:1255-1306)
+        sst_->advance(g_, vel_, k_, omega_, nut_, dt_, g_.Ng, st_);
+        sst_->closure(g_, vel_, k_, omega_, nut_, g_.Ng, st_);
+        return;
+    }
     if (les_model_) {                                // LESModel::update: nu_t = nu_sgs (src/turbulence_les.cpp:292-335)
         les_update_device(g_, les_mesh_, *les_met_, les_model_, les_c_, vel_, nut_, g_.Ng, is2d_ ? 1 : g_.Nz, is2d_, st_);
         return;
@@ -768,7 +787,7 @@ void Solver::step_device(bool want_residual) {
         const double nu_eff_max = std::max(cfg_.nu, h_scalars_[8]);
         // :1475-1486 (the 2-D branch takes min(dx, dy); implicit y-diffusion without a transport model drops dy)
         double dx_min = is2d_ ? std::min(mesh_.dx, dy_min_) : std::min({mesh_.dx, dy_min_, mesh_.dz});
-        if (cfg_.implicit_y_diffusion && !ext_transport_) dx_min = is2d_ ? mesh_.dx : std::min(mesh_.dx, mesh_.dz);
+        if (cfg_.implicit_y_diffusion && !transport_model()) dx_min = is2d_ ? mesh_.dx : std::min(mesh_.dx, mesh_.dz);
         const double dt_diff_limit = 0.25 * dx_min * dx_min / nu_eff_max;
         if (dt_ > dt_diff_limit) dt_ = std::max(cfg_.dt_safety * dt_diff_limit, 1e-15);
     }
@@ -835,7 +854,7 @@ double Solver::compute_adaptive_dt() {                          // src/solver.cp
     const double dx_min_full = is2d_ ? std::min(mesh_.dx, dy_min_) : std::min({mesh_.dx, dy_min_, mesh_.dz});
     const double dx_min = cfg_.implicit_y_diffusion ? (is2d_ ? mesh_.dx : std::min(mesh_.dx, mesh_.dz)) : dx_min_full;   // :3697-3706
     double dt_diff = 0.25 * dx_min * dx_min / nu_eff_max;
-    if (cfg_.implicit_y_diffusion && ext_transport_)                                       // :3709-3712
+    if (cfg_.implicit_y_diffusion && transport_model())                                    // :3709-3712
         dt_diff = std::min(dt_diff, 0.25 * dx_min_full * dx_min_full / nu_eff_max);
     double dt_new = cfg_.dt_safety * std::min({dt_cfl_x, dt_cfl_y, dt_cfl_z, dt_diff});
     if (comm_ && comm_->nranks > 1) {

@@ -54,12 +54,14 @@ public:
     double dt() const { return dt_; }
     void set_turbulence_model(NNClosure* nn) { nn_ = nn; }
     void set_external_nu_t(bool on, bool transport = false) { ext_nut_ = on; ext_transport_ = on && transport; }   // nu_t uploaded by the caller (bridged host model)
+    void set_sst_model(bool on);                             // native SST k-omega transport + closure (2-D meshes)
     void set_trip_forcing(const cfdnn_trip_desc* d);         // trip-region forcing in the Euler predictor
     void apply_velocity_filter(double strength);             // explicit Laplacian filter between steps
     double time() const { return time_; }
     void set_time(double t) { time_ = t; }
     void set_les_model(int model, double constant);          // static LES SGS closure evaluated at the top of step()
-    bool has_model() const { return nn_ != nullptr || ext_nut_ || les_model_ != 0; }
+    bool has_model() const { return nn_ != nullptr || ext_nut_ || les_model_ != 0 || sst_ != nullptr; }
+    bool transport_model() const { return ext_transport_ || sst_ != nullptr; }   // uses_transport_equations()
     double* view_ptr(int field, size_t* n) const;           // device twin of a field (cfdnn_solver_device_ptr)
     void comm_init(Comm* c);
 
@@ -97,12 +99,13 @@ private:
            *nueff_ = nullptr, *k_ = nullptr, *omega_ = nullptr, *tau_[3] = {nullptr, nullptr, nullptr};
     DevBuf<double> dyv_, dyc_, rdyv_, rdyc_, yc_;
     double dy_min_ = 0.0;
-    std::vector<double> h_dyv_;
+    std::vector<double> h_dyv_, h_dyc_;
     DevBuf<double> partial_, scalars_;
     double* h_scalars_ = nullptr;          // pinned
     size_t npartial_ = 0;
 
     std::unique_ptr<Multigrid> mg_;
+    std::unique_ptr<class SstModel> sst_;
     // trip forcing (src/solver.cpp:818-950): device copies of the caller's tables
     bool trip_on_ = false, trip_w_ = false;
     double trip_A_ = 0, trip_duration_ = 0, trip_ramp_start_ = 0, trip_w_scale_ = 1;

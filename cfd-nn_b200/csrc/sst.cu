@@ -1,0 +1,226 @@
+// sst.cu — SST k-omega transport and closure for 2-D meshes, device-resident inside step().
+//
+// Reference: SSTKOmegaTransport (src/turbulence_transport.cpp:315-958, constants include/turbulence_transport.hpp:32-58)
+// with its default SSTClosure (:234-313).  Parity is defined against the reference's CPU path, which advances k and
+// omega IN PLACE, one sweep over the cells in (j, i) order (:818-860): a cell sees the new values of its west and south
+// neighbours and the old values of its east and north ones.  That order is a data dependence, not an accident of the
+// loop, so the GPU version keeps it: cells on an anti-diagonal i + j = d depend only on diagonal d - 1, and one CTA
+// walks the diagonals with a barrier between them (k_sst_sweep).  A 2-D RANS grid has 10^4 .. 10^5 cells; the sweep is
+// latency-bound by construction (Nx + Ny - 1 barriers) and costs tens of microseconds.  The reference's own GPU path
+// runs the same cell function as a Jacobi update (every neighbour old) and therefore differs from its CPU path.
+//
+// The model is 2-D in the reference (fields indexed (i, j) only); 3-D meshes are not supported here.
+#include "sst.cuh"
+#include <cmath>
+#include <vector>
+
+namespace cfdnn {
+namespace {
+
+struct SstGrid {                    // grid constants of the sweep, computed on the host like the reference does (:772-781)
+    double dx, dy, dx2, dy2, inv_2dx, inv_2dy;
+};
+
+__device__ __forceinline__ double hi_of(double a, double b) { return (a > b) ? a : b; }     // (a > b) ? a : b
+__device__ __forceinline__ double lo_of(double a, double b) { return (a < b) ? a : b; }     // (a < b) ? a : b
+
+// The values a cell update reads: k and omega at the cell and its four neighbours (raw, ghosts included), the
+// previous nu_t, the wall distance, the MAC velocity differences and the cell-centred velocity.
+struct SstCellIn {
+    double kC, kE, kW, kN, kS;
+    double oC, oE, oW, oN, oS;
+    double nut, ywall;
+    double dudx, dudy, dvdx, dvdy, uc, vc;
+};
+
+// One point-implicit SST update (sst_transport_cell_kernel, src/turbulence_transport.cpp:56-190): F1 blending from the
+// cross-diffusion term, limited production, first-order upwind advection, central diffusion with nu + sigma nu_t,
+// destruction treated implicitly, clipping.  Expression order is the reference's (parity to the last bits on the
+// CPU test double; tanh / sqrt are the only library calls).
+__device__ __forceinline__ void sst_cell_update(const SstParams& p, const SstGrid& g, double dt, const SstCellIn& c,
+                                                double& k_out, double& omega_out) {
+    const double kc = hi_of(c.kC, p.k_min);
+    const double oc = hi_of(c.oC, p.omega_min);
+    const double y = hi_of(c.ywall, 1e-10);
+    const double nut = hi_of(c.nut, 0.0);
+
+    const double Sxy = 0.5 * (c.dudy + c.dvdx);
+    const double S2 = 2.0 * (c.dudx * c.dudx + c.dvdy * c.dvdy + 2.0 * Sxy * Sxy);
+
+    const double dkdx = (c.kE - c.kW) * g.inv_2dx, dkdy = (c.kN - c.kS) * g.inv_2dy;
+    const double dodx = (c.oE - c.oW) * g.inv_2dx, dody = (c.oN - c.oS) * g.inv_2dy;
+    const double grad_dot = dkdx * dodx + dkdy * dody;
+
+    const double CDkw = hi_of(2.0 * p.sigma_omega2 / oc * grad_dot, p.CD_omega_min);
+    const double a_visc = 500.0 * p.nu / (y * y * oc);
+    const double a_turb = sqrt(kc) / (p.beta_star * oc * y);
+    const double a_cd = 4.0 * p.sigma_omega2 * kc / (CDkw * y * y);
+    const double arg1 = lo_of(hi_of(a_turb, a_visc), a_cd);
+    const double F1 = tanh(arg1 * arg1 * arg1 * arg1);
+    const double G1 = 1.0 - F1;
+
+    const double beta = F1 * p.beta1 + G1 * p.beta2;
+    const double alpha = F1 * p.alpha1 + G1 * p.alpha2;
+    const double nu_k = p.nu + (F1 * p.sigma_k1 + G1 * p.sigma_k2) * nut;
+    const double nu_o = p.nu + (F1 * p.sigma_omega1 + G1 * p.sigma_omega2) * nut;
+
+    const double Pk = lo_of(2.0 * nut * S2, 10.0 * p.beta_star * kc * oc);
+
+    double adv_k, adv_o;
+    if (c.uc >= 0) { adv_k = c.uc * (kc - c.kW) / g.dx; adv_o = c.uc * (oc - c.oW) / g.dx; }
+    else           { adv_k = c.uc * (c.kE - kc) / g.dx; adv_o = c.uc * (c.oE - oc) / g.dx; }
+    if (c.vc >= 0) { adv_k += c.vc * (kc - c.kS) / g.dy; adv_o += c.vc * (oc - c.oS) / g.dy; }
+    else           { adv_k += c.vc * (c.kN - kc) / g.dy; adv_o += c.vc * (c.oN - oc) / g.dy; }
+
+    const double lap_k = (c.kE - 2.0 * kc + c.kW) / g.dx2 + (c.kN - 2.0 * kc + c.kS) / g.dy2;
+    const double lap_o = (c.oE - 2.0 * oc + c.oW) / g.dx2 + (c.oN - 2.0 * oc + c.oS) / g.dy2;
+    const double dif_k = nu_k * lap_k, dif_o = nu_o * lap_o;
+
+    const double CD = hi_of(2.0 * G1 * p.sigma_omega2 / oc * grad_dot, 0.0);
+
+    const double src_k = Pk + dif_k - adv_k;
+    const double src_o = alpha * (oc / kc) * Pk + dif_o - adv_o + CD;
+    double kn = (kc + dt * src_k) / (1.0 + dt * (p.beta_star * oc));
+    double on = (oc + dt * src_o) / (1.0 + dt * (beta * oc));
+    kn = lo_of(hi_of(kn, p.k_min), p.k_max);
+    on = lo_of(hi_of(on, p.omega_min), p.omega_max);
+    k_out = kn;
+    omega_out = on;
+}
+
+// The in-place sweep as a wavefront: ONE CTA, diagonals d = ix + iy in increasing order, a barrier after each.
+// k and omega are read and written through plain pointers (no read-only path: a neighbour written on the previous
+// diagonal must be seen).  u, v, nu_t, wall are read-only.
+__global__ void __launch_bounds__(1024)
+k_sst_sweep(Geom g, SstParams p, SstGrid sg, double dt, const double* __restrict__ u, const double* __restrict__ v,
+            double* k, double* omega, const double* __restrict__ nu_t, const double* __restrict__ wall) {
+    const int Nx = g.Nx, Ny = g.Ny, Ng = g.Ng;
+    const int cs = g.cs, us = g.us, vs = g.vs;
+    for (int d = 0; d < Nx + Ny - 1; ++d) {
+        const int iy_lo = d - (Nx - 1) > 0 ? d - (Nx - 1) : 0, iy_hi = d < Ny - 1 ? d : Ny - 1;
+        for (int iy = iy_lo + (int)threadIdx.x; iy <= iy_hi; iy += blockDim.x) {
+            const int i = d - iy + Ng, j = iy + Ng;
+            const int o = j * cs + i;
+            SstCellIn c;
+            c.kC = k[o]; c.kE = k[o + 1]; c.kW = k[o - 1]; c.kN = k[o + cs]; c.kS = k[o - cs];
+            c.oC = omega[o]; c.oE = omega[o + 1]; c.oW = omega[o - 1]; c.oN = omega[o + cs]; c.oS = omega[o - cs];
+            c.nut = nu_t[o];
+            c.ywall = wall[j];
+            const int ou = j * us + i, ov = j * vs + i;
+            c.dudx = (u[ou + 1] - u[ou - 1]) * sg.inv_2dx;
+            c.dudy = (u[ou + us] - u[ou - us]) * sg.inv_2dy;
+            c.dvdx = (v[ov + 1] - v[ov - 1]) * sg.inv_2dx;
+            c.dvdy = (v[ov + vs] - v[ov - vs]) * sg.inv_2dy;
+            c.uc = 0.5 * (u[ou] + u[ou + 1]);
+            c.vc = 0.5 * (v[ov] + v[ov + vs]);
+            double kn, on;
+            sst_cell_update(p, sg, dt, c, kn, on);
+            k[o] = kn;
+            omega[o] = on;
+        }
+        __syncthreads();
+    }
+}
+
+// Wall BCs after the sweep (apply_wall_bc_k :547-567: ghost = -first/last interior row, every column, ghost columns
+// included; apply_wall_bc_omega :569-603: ghost = 2 omega_wall - interior, interior columns only)
+__global__ void k_sst_wall_bc(Geom g, SstParams p, double* __restrict__ k, double* __restrict__ omega,
+                              const double* __restrict__ wall) {
+    const int I = blockIdx.x * blockDim.x + threadIdx.x;
+    const int Ng = g.Ng, cs = g.cs, jb = Ng, jt = g.Ny + Ng - 1;
+    if (I >= g.Nx + 2 * Ng) return;
+    k[(jb - 1) * cs + I] = -k[jb * cs + I];
+    k[(jt + 1) * cs + I] = -k[jt * cs + I];
+    if (I < Ng || I >= g.Nx + Ng) return;
+    {
+        const double y1 = hi_of(wall[jb], 1e-10);                       // std::max(wall_distance, 1e-10)
+        double ow = 10.0 * 6.0 * p.nu / (p.beta1 * y1 * y1);
+        ow = (p.omega_max < ow) ? p.omega_max : ow;                     // std::min(omega_wall, omega_max)
+        omega[(jb - 1) * cs + I] = 2.0 * ow - omega[jb * cs + I];
+    }
+    {
+        const double y1 = hi_of(wall[jt], 1e-10);
+        double ow = 10.0 * 6.0 * p.nu / (p.beta1 * y1 * y1);
+        ow = (p.omega_max < ow) ? p.omega_max : ow;
+        omega[(jt + 1) * cs + I] = 2.0 * ow - omega[jt * cs + I];
+    }
+}
+
+// SSTClosure::compute_nu_t (:259-313): nu_t = a1 k / max(a1 omega, |S| F2), F2 = tanh(max(2 sqrt k / (beta* omega y),
+// 500 nu / (y^2 omega))^2), gradients from the MAC faces (compute_gradients_from_mac, src/gpu_kernels.cpp:17-130;
+// stretched meshes divide by dyc[j] + dyc[j+1]), clipped to [0, 1000 nu]
+__global__ void k_sst_closure(Geom g, SstParams p, double inv_2dx, double inv_2dy, const double* __restrict__ dyc,
+                              const double* __restrict__ u, const double* __restrict__ v, const double* __restrict__ k,
+                              const double* __restrict__ omega, const double* __restrict__ wall, double* __restrict__ nu_t) {
+    const int ix = blockIdx.x * blockDim.x + threadIdx.x, iy = blockIdx.y * blockDim.y + threadIdx.y;
+    if (ix >= g.Nx || iy >= g.Ny) return;
+    const int i = ix + g.Ng, j = iy + g.Ng;
+    const int o = j * g.cs + i, ou = j * g.us + i, ov = j * g.vs + i;
+    const double wy = dyc ? 1.0 / (dyc[j] + dyc[j + 1]) : inv_2dy;
+    const double dudx = (u[ou + 1] - u[ou - 1]) * inv_2dx;
+    const double dudy = (u[ou + g.us] - u[ou - g.us]) * wy;
+    const double dvdx = (v[ov + 1] - v[ov - 1]) * inv_2dx;
+    const double dvdy = (v[ov + g.vs] - v[ov - g.vs]) * wy;
+    const double kl = (p.k_min < k[o]) ? k[o] : p.k_min;                // std::max(k_min, k)
+    const double ol = (p.omega_min < omega[o]) ? omega[o] : p.omega_min;
+    const double Sxy = 0.5 * (dudy + dvdx);
+    const double Smag = sqrt(2.0 * (dudx * dudx + dvdy * dvdy + 2.0 * Sxy * Sxy));
+    // compute_F2 (:244-257) clamps its arguments once more
+    const double ks = (p.k_min < kl) ? kl : p.k_min;
+    const double os = (p.omega_min < ol) ? ol : p.omega_min;
+    const double ys = (1e-10 < wall[j]) ? wall[j] : 1e-10;
+    const double t1 = 2.0 * sqrt(ks) / (p.beta_star * os * ys);
+    const double t2 = 500.0 * p.nu / (ys * ys * os);
+    const double arg2 = (t1 < t2) ? t2 : t1;
+    const double F2 = tanh(arg2 * arg2);
+    const double den_a = p.a1 * ol, den_b = Smag * F2;
+    const double den = (den_a < den_b) ? den_b : den_a;
+    const double mag = (fabs(den) < 1e-10) ? 1e-10 : fabs(den);        // numerics::safe_divide with K_FLOOR
+    double r = p.a1 * kl / ((den < 0.0) ? -mag : mag);
+    const double cap = 1000.0 * p.nu;
+    r = (r < 0.0) ? 0.0 : ((cap < r) ? cap : r);                        // std::clamp
+    nu_t[o] = r;
+}
+}  // namespace
+
+SstModel::SstModel(const cfdnn_mesh_desc& m, double nu) : dx_(m.dx), dy_(m.dy) {
+    require_device();
+    if (m.Nz > 1)
+        throw std::invalid_argument("SST k-omega: the reference model is two-dimensional (fields indexed (i, j)); 3-D meshes "
+                                    "are not supported");
+    if (m.Ng != 1) throw std::invalid_argument("SST k-omega: only Nghost == 1 is supported");
+    prm.nu = nu;
+    const int n = m.Ny + 2 * m.Ng;
+    std::vector<double> w(n);
+    for (int j = 0; j < n; ++j) {
+        const double y = m.yc ? m.yc[j] : m.y_lo + (j - m.Ng + 0.5) * m.dy;                          // src/mesh.cpp:66-68
+        const double lo = std::abs(y - m.y_lo), hi = std::abs(y - m.y_hi);
+        w[j] = std::min(lo, hi);
+    }
+    wall_.alloc(n, false);
+    CFDNN_CUDA(cudaMemcpy(wall_.p, w.data(), n * sizeof(double), cudaMemcpyHostToDevice));
+    if (m.y_stretched && m.dyc) {
+        dyc_.alloc(n + 1, false);
+        CFDNN_CUDA(cudaMemcpy(dyc_.p, m.dyc, (n + 1) * sizeof(double), cudaMemcpyHostToDevice));
+    }
+}
+
+void SstModel::advance(const Geom& g, const Vel& vel, double* k, double* omega, const double* nu_t, double dt, int plane,
+                       cudaStream_t st) {
+    SstGrid sg;
+    sg.dx = dx_; sg.dy = dy_; sg.dx2 = dx_ * dx_; sg.dy2 = dy_ * dy_;
+    sg.inv_2dx = 1.0 / (2.0 * dx_); sg.inv_2dy = 1.0 / (2.0 * dy_);
+    const size_t oc = (size_t)plane * g.cp, ou = (size_t)plane * g.up, ov = (size_t)plane * g.vp;
+    CFDNN_LAUNCH_COOP(k_sst_sweep, 1, 1024, 0, st, g, prm, sg, dt, vel.u + ou, vel.v + ov, k + oc, omega + oc, nu_t + oc, wall_.p);
+    CFDNN_LAUNCH(k_sst_wall_bc, (g.Nx + 2 * g.Ng + 127) / 128, 128, 0, st, g, prm, k + oc, omega + oc, wall_.p);
+}
+
+void SstModel::closure(const Geom& g, const Vel& vel, const double* k, const double* omega, double* nu_t, int plane,
+                       cudaStream_t st) {
+    const size_t oc = (size_t)plane * g.cp, ou = (size_t)plane * g.up, ov = (size_t)plane * g.vp;
+    const dim3 blk(64, 4);
+    CFDNN_LAUNCH(k_sst_closure, dim3((g.Nx + 63) / 64, (g.Ny + 3) / 4), blk, 0, st, g, prm, 1.0 / (2.0 * dx_), 1.0 / (2.0 * dy_),
+                 dyc_.p, vel.u + ou, vel.v + ov, k + oc, omega + oc, wall_.p, nu_t + oc);
+}
+
+}  // namespace cfdnn

@@ -1,0 +1,34 @@
+// sst.cuh — SST k-omega transport + SST eddy-viscosity closure on 2-D meshes; see sst.cu.
+#pragma once
+#include "common.cuh"
+#include "solver.cuh"
+
+namespace cfdnn {
+
+struct SstParams {                  // SSTConstants, include/turbulence_transport.hpp:32-58 (defaults), + nu
+    double nu;
+    double sigma_k1 = 0.85, sigma_omega1 = 0.5, beta1 = 0.075, alpha1 = 5.0 / 9.0;
+    double sigma_k2 = 1.0, sigma_omega2 = 0.856, beta2 = 0.0828, alpha2 = 0.44;
+    double beta_star = 0.09, a1 = 0.31;
+    double CD_omega_min = 1e-10;
+    double k_min = 1e-10, omega_min = 1e-10, k_max = 100.0, omega_max = 1e8;
+};
+
+class SstModel {
+public:
+    SstModel(const cfdnn_mesh_desc& m, double nu);
+    // SSTKOmegaTransport::advance_turbulence (CPU path, src/turbulence_transport.cpp:768-865): one in-place sweep over
+    // the cells in (j, i) order + wall BCs of k and omega.  Fields are planes of the solver's cell layout.
+    void advance(const Geom& g, const Vel& vel, double* k, double* omega, const double* nu_t, double dt, int plane,
+                 cudaStream_t st);
+    // SSTKOmegaTransport::update -> SSTClosure::compute_nu_t (:259-313)
+    void closure(const Geom& g, const Vel& vel, const double* k, const double* omega, double* nu_t, int plane, cudaStream_t st);
+    SstParams prm;
+
+private:
+    double dx_, dy_;
+    DevBuf<double> wall_;           // wall distance per row, Ny + 2 Ng (Mesh::wall_distance, src/mesh.cpp:6-12)
+    DevBuf<double> dyc_;            // centre spacings of a stretched mesh (closure gradients), else empty
+};
+
+}  // namespace cfdnn

@@ -222,6 +222,13 @@ int cfdnn_solver_device_ptr(cfdnn_solver* s, int field, double** dev_out, size_t
  * upload(CFDNN_F_NUT); with this flag on, step() builds nu_eff = nu + nu_t (src/solver.cpp:1326-1410) and
  * takes the closure branches of the diffusion-CFL re-check and the NaN guard as if a model were attached */
 int cfdnn_solver_set_external_nu_t(cfdnn_solver* s, int on);
+/* SST k-omega transport + SST closure (SSTKOmegaTransport, include/turbulence_transport.hpp:32-58,
+ * src/turbulence_transport.cpp:56-190, 259-313, 547-603, 768-865) evaluated device-resident at the top of every step():
+ * advance_turbulence (one in-place sweep in the reference CPU path's (j, i) order, as a wavefront) with the previous
+ * nu_t, then the closure.  Default SSTConstants.  k and omega are the solver's CFDNN_F_K / CFDNN_F_OMEGA fields — seed
+ * them with cfdnn_solver_upload the way RANSSolver::initialize does (src/solver.cpp:1064-1103).  2-D meshes only, like
+ * the reference model (CFDNN_ERR_INVALID on a 3-D mesh); replaces the NN / LES closure slot.  on = 0 detaches it. */
+int cfdnn_solver_set_sst_model(cfdnn_solver* s, int on);
 /* Trip-region forcing (Config::trip_*, include/config.hpp:202-210): a localized body force on v* (and w*) in the Euler
  * predictor while time < duration (src/solver.cpp:1724-1810, get_trip_time_ramp :939-950).  The tables are the ones
  * initialize_trip_forcing (:818-923) builds — x envelope on cell centres (Nx+2Ng), g(y) = y (1 - y^2) on the y faces

@@ -12,6 +12,7 @@
 //
 // Nothing here computes: there is no CPU path.  See INTEGRATION.md for the build line.
 #pragma once
+#include <algorithm>
 #include <memory>
 #include <cstdlib>
 #include <cmath>
@@ -22,6 +23,7 @@
 
 #include "cfdnn_b200.h"
 #include "config.hpp"
+#include "numerics.hpp"
 #include "fields.hpp"
 #include "mesh.hpp"
 #include "nn_core.hpp"
@@ -288,6 +290,8 @@ public:
             les_ = n == "Smagorinsky" ? CFDNN_LES_SMAGORINSKY : n == "WALE" ? CFDNN_LES_WALE
                  : n == "Vreman" ? CFDNN_LES_VREMAN : n == "Sigma" ? CFDNN_LES_SIGMA : CFDNN_LES_NONE;
         }
+        // the reference's SSTKOmegaTransport (default SST closure) on a 2-D mesh: native wavefront sweep + closure
+        sst_ = turb_ && !native_ && mesh_->is2D() && turb_->name() == "SSTKOmega";
         if (turb_) turb_->set_nu(nu_);
         if (native_) native_->set_nu_t_max(nu_t_max_);
         attach_model();
@@ -316,8 +320,36 @@ public:
         velocity_ = initial_velocity;
         sync_to_gpu();
         check(cfdnn_solver_initialize(h_));
+        if (turb_ && turb_->uses_transport_equations()) {        // k / omega seeding, src/solver.cpp:1064-1103
+            down(CFDNN_F_U, velocity_.u_data()); down(CFDNN_F_V, velocity_.v_data());    // with the BCs applied
+            double u_max = 0.0;
+            for (int j = mesh_->j_begin(); j < mesh_->j_end(); ++j)
+                for (int i = mesh_->i_begin(); i < mesh_->i_end(); ++i) {
+                    const double uc = 0.5 * (velocity_.u(i, j) + velocity_.u(i + 1, j));
+                    const double vc = 0.5 * (velocity_.v(i, j) + velocity_.v(i, j + 1));
+                    u_max = std::max(u_max, std::sqrt(uc * uc + vc * vc));
+                }
+            seed_k_omega(std::max(u_max, 0.01), /*guard_wall=*/true);
+        }
         if (turb_) turb_->initialize(*mesh_, velocity_);
         initialize_trip_forcing();
+    }
+    /// the uniform k, omega of RANSSolver::initialize / initialize_uniform with the near-wall omega rows
+    void seed_k_omega(double u_ref, bool guard_wall) {
+        const double Ti = 0.05;
+        double k_init = 1.5 * (u_ref * Ti) * (u_ref * Ti);
+        k_init = std::max(k_init, 1e-7);
+        double omega_init = k_init / (numerics::C_MU * config_.nu * 100.0);
+        omega_init = std::max(omega_init, 1e-6);
+        k_.fill(k_init);
+        omega_.fill(omega_init);
+        for (int i = mesh_->i_begin(); i < mesh_->i_end(); ++i) {
+            const int jb = mesh_->j_begin(), jt = mesh_->j_end() - 1;
+            const double yb = mesh_->wall_distance(i, jb), yt = mesh_->wall_distance(i, jt);
+            if (!guard_wall || yb > 1e-10) omega_(i, jb) = 10.0 * 6.0 * config_.nu / (0.075 * yb * yb);
+            if (!guard_wall || yt > 1e-10) omega_(i, jt) = 10.0 * 6.0 * config_.nu / (0.075 * yt * yt);
+        }
+        up(CFDNN_F_K, k_.data()); up(CFDNN_F_OMEGA, omega_.data());
     }
     /// initialize_trip_forcing (src/solver.cpp:818-923): the envelope / profile / spanwise-mode tables, built here with the
     /// reference's expressions (std::srand(12345) phases) from its Mesh and Config and handed to the backend, which adds
@@ -380,6 +412,8 @@ public:
         velocity_.fill(u0, v0);
         sync_to_gpu();
         check(cfdnn_solver_initialize(h_));
+        if (turb_ && turb_->uses_transport_equations())          // src/solver.cpp:1136-1160
+            seed_k_omega(std::max(std::abs(u0), 0.01), /*guard_wall=*/false);
         if (turb_) turb_->initialize(*mesh_, velocity_);
     }
     void sync_to_gpu() {
@@ -491,10 +525,11 @@ public:
 private:
     void up(int f, const std::vector<double>& v) { check(cfdnn_solver_upload(h_, f, v.data(), v.size())); }
     void down(int f, std::vector<double>& v) { check(cfdnn_solver_download(h_, f, v.data(), v.size())); }
-    bool bridged() const { return turb_ && !native_ && les_ == CFDNN_LES_NONE; }
+    bool bridged() const { return turb_ && !native_ && les_ == CFDNN_LES_NONE && !sst_; }
     void attach_model() {
         check(cfdnn_solver_set_turbulence_model(h_, native_ ? native_->handle() : nullptr));
         check(cfdnn_solver_set_les_model(h_, les_, 0.0));
+        check(cfdnn_solver_set_sst_model(h_, sst_ ? 1 : 0));
         check(cfdnn_solver_set_external_nu_t(h_, bridged() ? (turb_->uses_transport_equations() ? 2 : 1) : 0));
     }
     double* dev(int f) const {
@@ -535,6 +570,7 @@ private:
     std::unique_ptr<TurbulenceModel> turb_;
     TurbulenceNNB200* native_ = nullptr;        // turb_ when it is one of this backend's device closures
     int les_ = CFDNN_LES_NONE;                  // turb_ is one of the reference's static LES models: device kernel
+    bool sst_ = false;                          // turb_ is the reference's SST k-omega on a 2-D mesh: device kernels
     Decomposition* decomp_ = nullptr;
     VelocityBC bc_;
     bool have_bc_ = false;

@@ -136,6 +136,7 @@ Config make_config(const Mesh& mesh) {
     const std::string model = arg_s("model", "none");
     if (model == "nn_tbnn") c.turb_model = TurbulenceModelType::NNTBNN;
     else if (model == "nn_mlp") c.turb_model = TurbulenceModelType::NNMLP;
+    else if (model == "sst") c.turb_model = TurbulenceModelType::SSTKOmega;
     else if (model == "smagorinsky") c.turb_model = TurbulenceModelType::Smagorinsky;
     else if (model == "wale") c.turb_model = TurbulenceModelType::WALE;
     else if (model == "vreman") c.turb_model = TurbulenceModelType::Vreman;
@@ -210,6 +211,8 @@ void dump_state(const Mesh& mesh, const RANSSolver& s, const std::string& pre) {
     write_f64(pre + "_div.f64", s.div_velocity().data());
     write_f64(pre + "_rhs.f64", s.rhs_poisson().data());
     write_f64(pre + "_nut.f64", s.nu_t().data());
+    write_f64(pre + "_k.f64", s.k().data());
+    write_f64(pre + "_omega.f64", s.omega().data());
 }
 
 // parse "[Poisson] solve #n vcycles=k" lines the reference prints with POISSON_STATS set

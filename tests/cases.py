@@ -984,3 +984,63 @@ def check_velocity_filter(B, N=(20, 12, 16), strength=0.3):
         mask[sel[c]] = False
         assert np.array_equal(g[mask], q[mask]), c
         assert np.abs(g[sel[c]] - q[sel[c]]).max() > 1e-3
+
+
+# ---------------------------------------------------------------- SST k-omega
+def check_step_with_sst(B, oracle, stretched=False, ti="rk3", N=(32, 24, 1), nsteps=3, tol=1e-10, turb_tol=1e-10):
+    """2-D channel steps with the reference's SSTKOmegaTransport attached (advance_turbulence + SST closure at the top
+    of every step, src/solver.cpp:1255-1306) against the native wavefront sweep.  k and omega start from the
+    reference's own seeding in initialize() (read back from its `_init` dump); compared: k, omega (ghost rows
+    included: the wall BCs), nu_t and the flow fields."""
+    extra = dict(**CHANNEL_BOX) if stretched else dict(x1=4 * np.pi, y0=-1.0, y1=1.0)
+    case = ("chan2d_sst", N, "PPWWPP", ti, "skew", 8, nsteps, "pchan", (1.0, 0, 0), extra)
+    nu = 1.0 / 180.0
+    u, v, w = step_init(N, "pchan")
+    with tempfile.TemporaryDirectory() as td:
+        pre = os.path.join(td, "in")
+        u.tofile(pre + "_u.f64"); v.tofile(pre + "_v.f64")
+        kw = {k_: v_ for k_, v_ in extra.items() if k_ in HARNESS_KEYS and k_ != "z1"}
+        meta = R.run_ref("step", Nx=N[0], Ny=N[1], Nz=1, bc="PPWWPP", ti=ti, scheme="skew", fixed=8, nsteps=nsteps, dt=0.002,
+                         nu=nu, init="file:" + pre, fx=1.0, call_initialize=1, model="sst", out=os.path.join(td, "ref"), **kw)
+        ref0 = R.load_state(os.path.join(td, "ref_init"), *N)
+        ref = R.load_state(os.path.join(td, "ref_final"), *N)
+        arrs = R.load_mesh_arrays(os.path.join(td, "ref_mesh")) if stretched else None
+    assert ref0["k"].max() > 0 and ref0["omega"].max() > 0
+    h = make_solver(B, case, mesh_arrays=arrs, nu=nu, dt=0.002)
+    try:
+        B.upload(h, "k", ref0["k"]); B.upload(h, "omega", ref0["omega"])
+        B.check(B.lib.cfdnn_solver_set_sst_model(h, 1))
+        B.check(B.lib.cfdnn_solver_initialize(h))
+        res = [B.step(h) for _ in range(nsteps)]
+        got = B.state(h, *N)
+        sh = R.shapes(*N)["c"]
+        got["k"], got["omega"] = B.download(h, "k", sh), B.download(h, "omega", sh)
+    finally:
+        B.lib.cfdnn_solver_destroy(h)
+    assert res == pytest.approx(meta["residuals"], rel=1e-8)
+    Nx, Ny = N[0], N[1]
+    for n in ("k", "omega"):
+        a, b = got[n][0], ref[n][0]
+        # interior + the wall ghost rows the model writes (k: every column, omega: interior columns)
+        cols = slice(0, Nx + 2) if n == "k" else slice(1, Nx + 1)
+        assert not np.array_equal(b[1:Ny + 1, 1:Nx + 1], ref0[n][0][1:Ny + 1, 1:Nx + 1])          # the transport really ran
+        err = np.abs(a[:, cols] - b[:, cols]).max() / np.abs(b[:, cols]).max()
+        assert err <= turb_tol, (n, err)
+    nut_ref = plane0_interior("nut", ref["nut"])
+    assert nut_ref.max() > 10 * nu * 1e-3
+    assert np.abs(plane0_interior("nut", got["nut"]) - nut_ref).max() / nut_ref.max() <= turb_tol
+    for n in ("u", "v", "p"):
+        a, b = plane0_interior(n, got[n]), plane0_interior(n, ref[n])
+        scale = np.abs(plane0_interior("u", ref["u"])).max() if n != "p" else max(np.abs(b).max(), 1e-300)
+        assert np.abs(a - b).max() / scale <= tol, (n, np.abs(a - b).max() / scale)
+
+
+def check_sst_rejects_3d(B):
+    case = ("sst3d", (16, 16, 16), "PPWWPP", "rk3", "skew", 4, 1, "pchan", (1.0, 0, 0), dict(**CHANNEL_UNIFORM))
+    h = make_solver(B, case)
+    try:
+        with pytest.raises(R.capi.CfdnnError) as e:
+            B.check(B.lib.cfdnn_solver_set_sst_model(h, 1))
+        assert e.value.code == 1 and "two-dimensional" in str(e.value)
+    finally:
+        B.lib.cfdnn_solver_destroy(h)

@@ -53,7 +53,7 @@ def load_state(prefix, Nx, Ny, Nz, Ng=1):
     sh = shapes(Nx, Ny, Nz, Ng)
     out = {}
     for name, key in [("u", "u"), ("v", "v"), ("w", "w"), ("p", "c"), ("pcorr", "c"), ("div", "c"),
-                      ("rhs", "c"), ("nut", "c")]:
+                      ("rhs", "c"), ("nut", "c"), ("k", "c"), ("omega", "c")]:
         path = f"{prefix}_{name}.f64"
         if os.path.exists(path):
             out[name] = np.fromfile(path).reshape(sh[key])

@@ -6,6 +6,8 @@
 #include "poisson_solver_multigrid.hpp"
 #include "turbulence_nn_tbnn.hpp"
 #include "turbulence_les.hpp"
+#include "turbulence_transport.hpp"
+#include <algorithm>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -17,6 +19,11 @@ static double rel_l2(const std::vector<double>& a, const std::vector<double>& b)
     double num = 0, den = 0;
     for (size_t i = 0; i < a.size(); ++i) { const double d = a[i] - b[i]; num += d * d; den += b[i] * b[i]; }
     return den > 0 ? std::sqrt(num / den) : std::sqrt(num);
+}
+
+// the data plane of a 2-D field only (host plane 0; the reference's fill() also writes the two unused planes)
+static double rel_l2_plane0(const std::vector<double>& a, const std::vector<double>& b, size_t n) {
+    return rel_l2(std::vector<double>(a.begin(), a.begin() + n), std::vector<double>(b.begin(), b.begin() + n));
 }
 
 // ---- closures through the TurbulenceModel plugin interface (include/turbulence_model.hpp:81-165) on a 2-D
@@ -141,7 +148,7 @@ int main(int argc, char** argv) {
 
     int rc = 0;
     std::string closure_json = "\"closure\": null";
-    double r_ref = 0, r_b = 0, eu = 0, ep = 0, emg = 0, les_u = 1, les_nut = 1;
+    double r_ref = 0, r_b = 0, eu = 0, ep = 0, emg = 0, les_u = 1, les_nut = 1, sst_u = 1, sst_k = 1, sst_nut = 1;
     int cyc_ref = 0, cyc_b = 0, mg_ref = 0, mg_b = 0;
     bool threw_invalid = false;
     try {
@@ -216,6 +223,39 @@ int main(int argc, char** argv) {
             les_nut = rel_l2(bl.nu_t().data(), rl.nu_t().data());
             if (!(les_u <= 1e-10 && les_nut <= 1e-6)) rc = 1;
         }
+        // the reference's SST k-omega transport model on a 2-D channel: native wavefront sweep under the B200 solver
+        {
+            Mesh m2;
+            m2.init_uniform(32, 24, 0.0, 4 * M_PI, -1.0, 1.0);
+            Config sc = cfg;
+            sc.Nx = 32; sc.Ny = 24; sc.Nz = 1;
+            sc.nu = 1.0 / 180.0; sc.dt = 0.002;
+            sc.poisson_fixed_cycles = 6;
+            VelocityBC b2;
+            b2.x_lo = b2.x_hi = VelocityBC::Periodic;
+            b2.y_lo = b2.y_hi = VelocityBC::NoSlip;
+            VectorField w0(m2);
+            for (int j = m2.j_begin(); j < m2.j_end(); ++j)
+                for (int i = m2.i_begin(); i <= m2.i_end(); ++i)
+                    w0.u(i, j) = (1.0 - m2.y(j) * m2.y(j)) * (1.0 + 0.05 * std::sin(m2.xf[i]));
+            RANSSolver rs(m2, sc);
+            rs.set_velocity_bc(b2);
+            rs.set_body_force(1.0, 0.0);
+            rs.set_turbulence_model(std::make_unique<SSTKOmegaTransport>());
+            rs.initialize(w0);
+            b200::RANSSolverB200 bs(m2, sc);
+            bs.set_velocity_bc(b2);
+            bs.set_body_force(1.0, 0.0);
+            bs.set_turbulence_model(std::make_unique<SSTKOmegaTransport>());
+            bs.initialize(w0);
+            for (int s = 0; s < 3; ++s) { rs.step(); bs.step(); }
+            bs.sync_from_gpu();
+            sst_u = rel_l2(bs.velocity().u_data(), rs.velocity().u_data());
+            const size_t pl = (size_t)m2.total_Nx() * m2.total_Ny();
+            sst_k = std::max(rel_l2_plane0(bs.k().data(), rs.k().data(), pl), rel_l2_plane0(bs.omega().data(), rs.omega().data(), pl));
+            sst_nut = rel_l2(bs.nu_t().data(), rs.nu_t().data());
+            if (!(sst_u <= 1e-10 && sst_k <= 1e-10 && sst_nut <= 1e-9)) rc = 1;
+        }
         if (!wdir.empty() && closure_section(wdir, closure_json) != 0) rc = 1;
     } catch (const std::exception& e) {
         std::cout.rdbuf(oc); std::cerr.rdbuf(oe);
@@ -228,8 +268,8 @@ int main(int argc, char** argv) {
         rc = 1;
     std::printf("{\"N\": %d, \"steps\": %d, \"residual_ref\": %.17g, \"residual_b200\": %.17g, \"u_rel_l2\": %.3e, "
                 "\"p_rel_l2\": %.3e, \"cycles_ref\": %d, \"cycles_b200\": %d, \"mg_cycles_ref\": %d, "
-                "\"mg_cycles_b200\": %d, \"mg_p_rel_l2\": %.3e, \"invalid_argument\": %s, \"les_wale\": {\"u\": %.3e, \"nu_t\": %.3e}, %s, \"ok\": %s}\n",
+                "\"mg_cycles_b200\": %d, \"mg_p_rel_l2\": %.3e, \"invalid_argument\": %s, \"les_wale\": {\"u\": %.3e, \"nu_t\": %.3e}, \"sst\": {\"u\": %.3e, \"k\": %.3e, \"nu_t\": %.3e}, %s, \"ok\": %s}\n",
                 N, nsteps, r_ref, r_b, eu, ep, cyc_ref, cyc_b, mg_ref, mg_b, emg, threw_invalid ? "true" : "false",
-                les_u, les_nut, closure_json.c_str(), rc == 0 ? "true" : "false");
+                les_u, les_nut, sst_u, sst_k, sst_nut, closure_json.c_str(), rc == 0 ? "true" : "false");
     return rc;
 }

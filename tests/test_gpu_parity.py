@@ -317,3 +317,18 @@ def test_trip_forcing_adds_the_reference_term(gpu, kind):
 
 def test_velocity_filter_matches_restatement(gpu):
     cases.check_velocity_filter(gpu, N=(40, 24, 32))
+
+
+# ---- SST k-omega transport + closure on 2-D meshes
+@pytest.mark.parametrize("kind,ti", [("uniform", "rk3"), ("uniform", "euler"), ("stretched", "rk3")])
+def test_step_with_sst_k_omega_matches_reference(gpu, oracle, kind, ti):
+    cases.check_step_with_sst(gpu, oracle, stretched=kind == "stretched", ti=ti)
+
+
+def test_step_with_sst_k_omega_192x96(gpu, oracle):
+    """the x-y plane of BASELINE config 3 (192 x 96, tanh beta = 2), 5 steps"""
+    cases.check_step_with_sst(gpu, oracle, stretched=True, ti="rk3", N=(192, 96, 1), nsteps=5, tol=1e-9, turb_tol=1e-9)
+
+
+def test_sst_rejects_3d_meshes(gpu):
+    cases.check_sst_rejects_3d(gpu)

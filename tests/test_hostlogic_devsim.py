@@ -229,3 +229,13 @@ def test_trip_forcing_adds_the_reference_term(sim, kind):
 
 def test_velocity_filter_matches_restatement(sim):
     cases.check_velocity_filter(sim)
+
+
+# ---- SST k-omega transport + closure on 2-D meshes
+@pytest.mark.parametrize("kind,ti", [("uniform", "rk3"), ("uniform", "euler"), ("stretched", "rk3")])
+def test_step_with_sst_k_omega_matches_reference(sim, oracle, kind, ti):
+    cases.check_step_with_sst(sim, oracle, stretched=kind == "stretched", ti=ti)
+
+
+def test_sst_rejects_3d_meshes(sim):
+    cases.check_sst_rejects_3d(sim)

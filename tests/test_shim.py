@@ -33,6 +33,7 @@ def _weights_dir(td):
 
 def _check_closure(d):
     assert d["les_wale"]["u"] <= 1e-10 and d["les_wale"]["nu_t"] <= 1e-6, d["les_wale"]
+    assert d["sst"]["u"] <= 1e-10 and d["sst"]["k"] <= 1e-10 and d["sst"]["nu_t"] <= 1e-9, d["sst"]     # native SST k-omega
     c = d["closure"]
     assert c and c["ok"], c
     assert c["interface_ok"] and c["views_ok"]
