@@ -721,15 +721,15 @@ void Solver::set_les_model(int model, double constant) {
     les_c_ = constant;
 }
 
-void Solver::set_sst_model(bool on) {
-    if (!on) { sst_.reset(); return; }
+void Solver::set_sst_model(int kind) {
+    if (kind == CFDNN_RANS_NONE) { sst_.reset(); return; }
     if (!is2d_)
         throw std::invalid_argument("set_sst_model: the reference's SST k-omega transport is two-dimensional (k, omega, nu_t "
                                     "indexed (i, j)); on a 3-D mesh bridge the host model instead");
     cfdnn_mesh_desc m = mesh_;
     m.yc = h_yc_.empty() ? nullptr : h_yc_.data();
     m.dyc = h_dyc_.empty() ? nullptr : h_dyc_.data();
-    sst_ = std::make_unique<SstModel>(m, cfg_.nu);
+    sst_ = std::make_unique<SstModel>(m, cfg_.nu, kind);
 }
 
 void Solver::update_turbulence() {

@@ -88,12 +88,45 @@ __device__ __forceinline__ void sst_cell_update(const SstParams& p, const SstGri
     omega_out = on;
 }
 
+// Standard k-omega (Wilcox 1988), KOmegaTransport::advance_turbulence host path (src/turbulence_transport.cpp:1062-1118):
+// no blending, no cross-diffusion, the advecting velocity is the FACE value u(i, j), v(i, j) (not the cell average), the
+// strain comes from compute_gradients_from_mac (stretched-aware), every k / omega entering a difference is raw.
+struct KwParams { double nu, sigma_k, sigma_omega, beta, beta_star, alpha, k_min, k_max, omega_min, omega_max; };
+
+__device__ __forceinline__ void kw_cell_update(const KwParams& p, const SstGrid& g, double dt, const SstCellIn& c,
+                                               double& k_out, double& omega_out) {
+    const double k_old = (p.k_min < c.kC) ? c.kC : p.k_min;            // std::max(k_min, k)
+    const double o_old = (p.omega_min < c.oC) ? c.oC : p.omega_min;
+    const double nut = (0.0 < c.nut) ? c.nut : 0.0;                     // std::max(0.0, nu_t)
+    const double Sxy = 0.5 * (c.dudy + c.dvdx);
+    const double S2 = 2.0 * (c.dudx * c.dudx + c.dvdy * c.dvdy + 2.0 * Sxy * Sxy);
+    const double Pk = 2.0 * nut * S2;
+    const double nu_k = p.nu + p.sigma_k * nut, nu_o = p.nu + p.sigma_omega * nut;
+    const double dkdx = (c.uc >= 0) ? (c.kC - c.kW) / g.dx : (c.kE - c.kC) / g.dx;
+    const double dkdy = (c.vc >= 0) ? (c.kC - c.kS) / g.dy : (c.kN - c.kC) / g.dy;
+    const double dodx = (c.uc >= 0) ? (c.oC - c.oW) / g.dx : (c.oE - c.oC) / g.dx;
+    const double dody = (c.vc >= 0) ? (c.oC - c.oS) / g.dy : (c.oN - c.oC) / g.dy;
+    const double adv_k = c.uc * dkdx + c.vc * dkdy, adv_o = c.uc * dodx + c.vc * dody;
+    const double dif_k = nu_k * ((c.kE - 2.0 * c.kC + c.kW) / g.dx2 + (c.kN - 2.0 * c.kC + c.kS) / g.dy2);
+    const double dif_o = nu_o * ((c.oE - 2.0 * c.oC + c.oW) / g.dx2 + (c.oN - 2.0 * c.oC + c.oS) / g.dy2);
+    const double src_k = Pk + dif_k - adv_k;
+    const double src_o = p.alpha * (o_old / k_old) * Pk + dif_o - adv_o;
+    const double kn = (k_old + dt * src_k) / (1.0 + dt * (p.beta_star * o_old));
+    const double on = (o_old + dt * src_o) / (1.0 + dt * (p.beta * o_old));
+    const double kl = (kn < p.k_min) ? p.k_min : kn, ol = (on < p.omega_min) ? p.omega_min : on;   // std::max(new, min)
+    k_out = (p.k_max < kl) ? p.k_max : kl;                               // std::min(., max)
+    omega_out = (p.omega_max < ol) ? p.omega_max : ol;
+}
+
 // The in-place sweep as a wavefront: ONE CTA, diagonals d = ix + iy in increasing order, a barrier after each.
 // k and omega are read and written through plain pointers (no read-only path: a neighbour written on the previous
 // diagonal must be seen).  u, v, nu_t, wall are read-only.
+// SST = true: SSTKOmegaTransport; false: KOmegaTransport (dyc != nullptr: stretched-aware y differences of the strain).
+template <bool SST>
 __global__ void __launch_bounds__(1024)
-k_sst_sweep(Geom g, SstParams p, SstGrid sg, double dt, const double* __restrict__ u, const double* __restrict__ v,
-            double* k, double* omega, const double* __restrict__ nu_t, const double* __restrict__ wall) {
+k_sst_sweep(Geom g, SstParams p, KwParams kw, SstGrid sg, double dt, const double* __restrict__ u, const double* __restrict__ v,
+            double* k, double* omega, const double* __restrict__ nu_t, const double* __restrict__ wall,
+            const double* __restrict__ dyc) {
     const int Nx = g.Nx, Ny = g.Ny, Ng = g.Ng;
     const int cs = g.cs, us = g.us, vs = g.vs;
     for (int d = 0; d < Nx + Ny - 1; ++d) {
@@ -107,14 +140,16 @@ k_sst_sweep(Geom g, SstParams p, SstGrid sg, double dt, const double* __restrict
             c.nut = nu_t[o];
             c.ywall = wall[j];
             const int ou = j * us + i, ov = j * vs + i;
+            const double wy = (!SST && dyc) ? 1.0 / (dyc[j] + dyc[j + 1]) : sg.inv_2dy;
             c.dudx = (u[ou + 1] - u[ou - 1]) * sg.inv_2dx;
-            c.dudy = (u[ou + us] - u[ou - us]) * sg.inv_2dy;
+            c.dudy = (u[ou + us] - u[ou - us]) * wy;
             c.dvdx = (v[ov + 1] - v[ov - 1]) * sg.inv_2dx;
-            c.dvdy = (v[ov + vs] - v[ov - vs]) * sg.inv_2dy;
-            c.uc = 0.5 * (u[ou] + u[ou + 1]);
-            c.vc = 0.5 * (v[ov] + v[ov + vs]);
+            c.dvdy = (v[ov + vs] - v[ov - vs]) * wy;
+            c.uc = SST ? 0.5 * (u[ou] + u[ou + 1]) : u[ou];
+            c.vc = SST ? 0.5 * (v[ov] + v[ov + vs]) : v[ov];
             double kn, on;
-            sst_cell_update(p, sg, dt, c, kn, on);
+            if (SST) sst_cell_update(p, sg, dt, c, kn, on);
+            else kw_cell_update(kw, sg, dt, c, kn, on);
             k[o] = kn;
             omega[o] = on;
         }
@@ -181,9 +216,24 @@ __global__ void k_sst_closure(Geom g, SstParams p, double inv_2dx, double inv_2d
     r = (r < 0.0) ? 0.0 : ((cap < r) ? cap : r);                        // std::clamp
     nu_t[o] = r;
 }
+// BoussinesqClosure::compute_nu_t (:202-228): nu_t = k / omega with the numerics:: floors, |.| capped at 1000 nu
+__global__ void k_kw_closure(Geom g, double nu, const double* __restrict__ k, const double* __restrict__ omega,
+                             double* __restrict__ nu_t) {
+    const int ix = blockIdx.x * blockDim.x + threadIdx.x, iy = blockIdx.y * blockDim.y + threadIdx.y;
+    if (ix >= g.Nx || iy >= g.Ny) return;
+    const int o = (iy + g.Ng) * g.cs + ix + g.Ng;
+    const double kl = (1e-10 < k[o]) ? k[o] : 1e-10;                    // std::max(K_FLOOR, k)
+    const double ol = (1e-10 < omega[o]) ? omega[o] : 1e-10;            // std::max(OMEGA_FLOOR, omega)
+    const double mag = (fabs(ol) < 1e-10) ? 1e-10 : fabs(ol);          // bounded_ratio -> safe_divide(k, omega, OMEGA_FLOOR)
+    const double r = kl / ((ol < 0.0) ? -mag : mag);
+    const double cap = 1000.0 * nu;
+    nu_t[o] = (r < -cap) ? -cap : ((cap < r) ? cap : r);                // std::clamp(ratio, -ceiling, ceiling)
+}
 }  // namespace
 
-SstModel::SstModel(const cfdnn_mesh_desc& m, double nu) : dx_(m.dx), dy_(m.dy) {
+SstModel::SstModel(const cfdnn_mesh_desc& m, double nu, int kind) : kind_(kind), dx_(m.dx), dy_(m.dy) {
+    if (kind != CFDNN_RANS_SST && kind != CFDNN_RANS_KOMEGA)
+        throw std::invalid_argument("transport model: kind must be CFDNN_RANS_SST or CFDNN_RANS_KOMEGA");
     require_device();
     if (m.Nz > 1)
         throw std::invalid_argument("SST k-omega: the reference model is two-dimensional (fields indexed (i, j)); 3-D meshes "
@@ -211,14 +261,27 @@ void SstModel::advance(const Geom& g, const Vel& vel, double* k, double* omega, 
     sg.dx = dx_; sg.dy = dy_; sg.dx2 = dx_ * dx_; sg.dy2 = dy_ * dy_;
     sg.inv_2dx = 1.0 / (2.0 * dx_); sg.inv_2dy = 1.0 / (2.0 * dy_);
     const size_t oc = (size_t)plane * g.cp, ou = (size_t)plane * g.up, ov = (size_t)plane * g.vp;
-    CFDNN_LAUNCH_COOP(k_sst_sweep, 1, 1024, 0, st, g, prm, sg, dt, vel.u + ou, vel.v + ov, k + oc, omega + oc, nu_t + oc, wall_.p);
-    CFDNN_LAUNCH(k_sst_wall_bc, (g.Nx + 2 * g.Ng + 127) / 128, 128, 0, st, g, prm, k + oc, omega + oc, wall_.p);
+    KwParams kw;                                    // KOmegaConstants, include/turbulence_transport.hpp:61-72
+    kw.nu = prm.nu; kw.sigma_k = 0.5; kw.sigma_omega = 0.5; kw.beta = 0.075; kw.beta_star = 0.09; kw.alpha = 5.0 / 9.0;
+    kw.k_min = 1e-10; kw.k_max = 100.0; kw.omega_min = 1e-10; kw.omega_max = 1e8;
+    if (kind_ == CFDNN_RANS_SST) {
+        CFDNN_LAUNCH_COOP((k_sst_sweep<true>), 1, 1024, 0, st, g, prm, kw, sg, dt, vel.u + ou, vel.v + ov, k + oc, omega + oc,
+                          nu_t + oc, wall_.p, dyc_.p);
+        CFDNN_LAUNCH(k_sst_wall_bc, (g.Nx + 2 * g.Ng + 127) / 128, 128, 0, st, g, prm, k + oc, omega + oc, wall_.p);
+    } else {                                        // the standard model applies no wall BCs after its sweep
+        CFDNN_LAUNCH_COOP((k_sst_sweep<false>), 1, 1024, 0, st, g, prm, kw, sg, dt, vel.u + ou, vel.v + ov, k + oc, omega + oc,
+                          nu_t + oc, wall_.p, dyc_.p);
+    }
 }
 
 void SstModel::closure(const Geom& g, const Vel& vel, const double* k, const double* omega, double* nu_t, int plane,
                        cudaStream_t st) {
     const size_t oc = (size_t)plane * g.cp, ou = (size_t)plane * g.up, ov = (size_t)plane * g.vp;
     const dim3 blk(64, 4);
+    if (kind_ == CFDNN_RANS_KOMEGA) {
+        CFDNN_LAUNCH(k_kw_closure, dim3((g.Nx + 63) / 64, (g.Ny + 3) / 4), blk, 0, st, g, prm.nu, k + oc, omega + oc, nu_t + oc);
+        return;
+    }
     CFDNN_LAUNCH(k_sst_closure, dim3((g.Nx + 63) / 64, (g.Ny + 3) / 4), blk, 0, st, g, prm, 1.0 / (2.0 * dx_), 1.0 / (2.0 * dy_),
                  dyc_.p, vel.u + ou, vel.v + ov, k + oc, omega + oc, wall_.p, nu_t + oc);
 }

@@ -1,4 +1,5 @@
-// sst.cuh — SST k-omega transport + SST eddy-viscosity closure on 2-D meshes; see sst.cu.
+// sst.cuh — SST k-omega (+ SST closure) and standard k-omega (+ Boussinesq closure) transport models on 2-D meshes
+// (SURVEY §8(f)2); see sst.cu.
 #pragma once
 #include "common.cuh"
 #include "solver.cuh"
@@ -16,7 +17,7 @@ struct SstParams {                  // SSTConstants, include/turbulence_transpor
 
 class SstModel {
 public:
-    SstModel(const cfdnn_mesh_desc& m, double nu);
+    SstModel(const cfdnn_mesh_desc& m, double nu, int kind);      // kind: CFDNN_RANS_SST / CFDNN_RANS_KOMEGA
     // SSTKOmegaTransport::advance_turbulence (CPU path, src/turbulence_transport.cpp:768-865): one in-place sweep over
     // the cells in (j, i) order + wall BCs of k and omega.  Fields are planes of the solver's cell layout.
     void advance(const Geom& g, const Vel& vel, double* k, double* omega, const double* nu_t, double dt, int plane,
@@ -26,6 +27,7 @@ public:
     SstParams prm;
 
 private:
+    int kind_;
     double dx_, dy_;
     DevBuf<double> wall_;           // wall distance per row, Ny + 2 Ng (Mesh::wall_distance, src/mesh.cpp:6-12)
     DevBuf<double> dyc_;            // centre spacings of a stretched mesh (closure gradients), else empty

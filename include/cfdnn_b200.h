@@ -227,8 +227,11 @@ int cfdnn_solver_set_external_nu_t(cfdnn_solver* s, int on);
  * advance_turbulence (one in-place sweep in the reference CPU path's (j, i) order, as a wavefront) with the previous
  * nu_t, then the closure.  Default SSTConstants.  k and omega are the solver's CFDNN_F_K / CFDNN_F_OMEGA fields — seed
  * them with cfdnn_solver_upload the way RANSSolver::initialize does (src/solver.cpp:1064-1103).  2-D meshes only, like
- * the reference model (CFDNN_ERR_INVALID on a 3-D mesh); replaces the NN / LES closure slot.  on = 0 detaches it. */
-int cfdnn_solver_set_sst_model(cfdnn_solver* s, int on);
+ * the reference model (CFDNN_ERR_INVALID on a 3-D mesh); replaces the NN / LES closure slot.  kind = CFDNN_RANS_SST, or
+ * CFDNN_RANS_KOMEGA for the standard Wilcox model KOmegaTransport with its Boussinesq closure (:202-228, 1012-1118;
+ * no wall BC pass, face velocities advect), or CFDNN_RANS_NONE to detach. */
+enum { CFDNN_RANS_NONE = 0, CFDNN_RANS_SST = 1, CFDNN_RANS_KOMEGA = 2 };
+int cfdnn_solver_set_sst_model(cfdnn_solver* s, int kind);
 /* Trip-region forcing (Config::trip_*, include/config.hpp:202-210): a localized body force on v* (and w*) in the Euler
  * predictor while time < duration (src/solver.cpp:1724-1810, get_trip_time_ramp :939-950).  The tables are the ones
  * initialize_trip_forcing (:818-923) builds — x envelope on cell centres (Nx+2Ng), g(y) = y (1 - y^2) on the y faces

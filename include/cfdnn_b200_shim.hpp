@@ -287,11 +287,16 @@ public:
         les_ = CFDNN_LES_NONE;
         if (turb_ && !native_) {       // the reference's own static LES models run as device kernels (default constants)
             const std::string n = turb_->name();
-            les_ = n == "Smagorinsky" ? CFDNN_LES_SMAGORINSKY : n == "WALE" ? CFDNN_LES_WALE
+            // DynamicSmagorinsky: the reference's CPU path (the parity target) evaluates it as static Smagorinsky with
+            // Cs = 0.17 — the Germano procedure exists in its GPU build only (src/turbulence_les_dynamic.cpp:56-67)
+            les_ = (n == "Smagorinsky" || n == "DynamicSmagorinsky") ? CFDNN_LES_SMAGORINSKY : n == "WALE" ? CFDNN_LES_WALE
                  : n == "Vreman" ? CFDNN_LES_VREMAN : n == "Sigma" ? CFDNN_LES_SIGMA : CFDNN_LES_NONE;
         }
         // the reference's SSTKOmegaTransport (default SST closure) on a 2-D mesh: native wavefront sweep + closure
-        sst_ = turb_ && !native_ && mesh_->is2D() && turb_->name() == "SSTKOmega";
+        // ... and its standard KOmegaTransport (default Boussinesq closure)
+        sst_ = CFDNN_RANS_NONE;
+        if (turb_ && !native_ && mesh_->is2D())
+            sst_ = turb_->name() == "SSTKOmega" ? CFDNN_RANS_SST : turb_->name() == "KOmega" ? CFDNN_RANS_KOMEGA : CFDNN_RANS_NONE;
         if (turb_) turb_->set_nu(nu_);
         if (native_) native_->set_nu_t_max(nu_t_max_);
         attach_model();
@@ -529,7 +534,7 @@ private:
     void attach_model() {
         check(cfdnn_solver_set_turbulence_model(h_, native_ ? native_->handle() : nullptr));
         check(cfdnn_solver_set_les_model(h_, les_, 0.0));
-        check(cfdnn_solver_set_sst_model(h_, sst_ ? 1 : 0));
+        check(cfdnn_solver_set_sst_model(h_, sst_));
         check(cfdnn_solver_set_external_nu_t(h_, bridged() ? (turb_->uses_transport_equations() ? 2 : 1) : 0));
     }
     double* dev(int f) const {
@@ -570,7 +575,7 @@ private:
     std::unique_ptr<TurbulenceModel> turb_;
     TurbulenceNNB200* native_ = nullptr;        // turb_ when it is one of this backend's device closures
     int les_ = CFDNN_LES_NONE;                  // turb_ is one of the reference's static LES models: device kernel
-    bool sst_ = false;                          // turb_ is the reference's SST k-omega on a 2-D mesh: device kernels
+    int sst_ = CFDNN_RANS_NONE;                 // turb_ is the reference's SST / standard k-omega on a 2-D mesh: device kernels
     Decomposition* decomp_ = nullptr;
     VelocityBC bc_;
     bool have_bc_ = false;

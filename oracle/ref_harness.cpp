@@ -137,6 +137,7 @@ Config make_config(const Mesh& mesh) {
     if (model == "nn_tbnn") c.turb_model = TurbulenceModelType::NNTBNN;
     else if (model == "nn_mlp") c.turb_model = TurbulenceModelType::NNMLP;
     else if (model == "sst") c.turb_model = TurbulenceModelType::SSTKOmega;
+    else if (model == "komega") c.turb_model = TurbulenceModelType::KOmega;
     else if (model == "smagorinsky") c.turb_model = TurbulenceModelType::Smagorinsky;
     else if (model == "wale") c.turb_model = TurbulenceModelType::WALE;
     else if (model == "vreman") c.turb_model = TurbulenceModelType::Vreman;

@@ -987,7 +987,7 @@ def check_velocity_filter(B, N=(20, 12, 16), strength=0.3):
 
 
 # ---------------------------------------------------------------- SST k-omega
-def check_step_with_sst(B, oracle, stretched=False, ti="rk3", N=(32, 24, 1), nsteps=3, tol=1e-10, turb_tol=1e-10):
+def check_step_with_sst(B, oracle, stretched=False, ti="rk3", N=(32, 24, 1), nsteps=3, tol=1e-10, turb_tol=1e-10, model="sst"):
     """2-D channel steps with the reference's SSTKOmegaTransport attached (advance_turbulence + SST closure at the top
     of every step, src/solver.cpp:1255-1306) against the native wavefront sweep.  k and omega start from the
     reference's own seeding in initialize() (read back from its `_init` dump); compared: k, omega (ghost rows
@@ -1001,7 +1001,7 @@ def check_step_with_sst(B, oracle, stretched=False, ti="rk3", N=(32, 24, 1), nst
         u.tofile(pre + "_u.f64"); v.tofile(pre + "_v.f64")
         kw = {k_: v_ for k_, v_ in extra.items() if k_ in HARNESS_KEYS and k_ != "z1"}
         meta = R.run_ref("step", Nx=N[0], Ny=N[1], Nz=1, bc="PPWWPP", ti=ti, scheme="skew", fixed=8, nsteps=nsteps, dt=0.002,
-                         nu=nu, init="file:" + pre, fx=1.0, call_initialize=1, model="sst", out=os.path.join(td, "ref"), **kw)
+                         nu=nu, init="file:" + pre, fx=1.0, call_initialize=1, model=model, out=os.path.join(td, "ref"), **kw)
         ref0 = R.load_state(os.path.join(td, "ref_init"), *N)
         ref = R.load_state(os.path.join(td, "ref_final"), *N)
         arrs = R.load_mesh_arrays(os.path.join(td, "ref_mesh")) if stretched else None
@@ -1009,7 +1009,7 @@ def check_step_with_sst(B, oracle, stretched=False, ti="rk3", N=(32, 24, 1), nst
     h = make_solver(B, case, mesh_arrays=arrs, nu=nu, dt=0.002)
     try:
         B.upload(h, "k", ref0["k"]); B.upload(h, "omega", ref0["omega"])
-        B.check(B.lib.cfdnn_solver_set_sst_model(h, 1))
+        B.check(B.lib.cfdnn_solver_set_sst_model(h, {"sst": 1, "komega": 2}[model]))
         B.check(B.lib.cfdnn_solver_initialize(h))
         res = [B.step(h) for _ in range(nsteps)]
         got = B.state(h, *N)
@@ -1027,7 +1027,7 @@ def check_step_with_sst(B, oracle, stretched=False, ti="rk3", N=(32, 24, 1), nst
         err = np.abs(a[:, cols] - b[:, cols]).max() / np.abs(b[:, cols]).max()
         assert err <= turb_tol, (n, err)
     nut_ref = plane0_interior("nut", ref["nut"])
-    assert nut_ref.max() > 10 * nu * 1e-3
+    assert nut_ref.max() > nu * 1e-2
     assert np.abs(plane0_interior("nut", got["nut"]) - nut_ref).max() / nut_ref.max() <= turb_tol
     for n in ("u", "v", "p"):
         a, b = plane0_interior(n, got[n]), plane0_interior(n, ref[n])

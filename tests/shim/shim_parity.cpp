@@ -222,6 +222,19 @@ int main(int argc, char** argv) {
             les_u = rel_l2(bl.velocity().u_data(), rl.velocity().u_data());
             les_nut = rel_l2(bl.nu_t().data(), rl.nu_t().data());
             if (!(les_u <= 1e-10 && les_nut <= 1e-6)) rc = 1;
+            // DynamicSmagorinskyModel: the reference's CPU path evaluates it as static Smagorinsky (Cs = 0.17); same kernel here
+            RANSSolver rd(mesh, lc);
+            rd.set_velocity_bc(bc);
+            rd.set_turbulence_model(std::make_unique<DynamicSmagorinskyModel>());
+            rd.initialize(v0);
+            b200::RANSSolverB200 bd(mesh, lc);
+            bd.set_velocity_bc(bc);
+            bd.set_turbulence_model(std::make_unique<DynamicSmagorinskyModel>());
+            bd.initialize(v0);
+            rd.step(); bd.step();
+            bd.sync_from_gpu();
+            if (!(rel_l2(bd.velocity().u_data(), rd.velocity().u_data()) <= 1e-10 &&
+                  rel_l2(bd.nu_t().data(), rd.nu_t().data()) <= 1e-6)) rc = 1;
         }
         // the reference's SST k-omega transport model on a 2-D channel: native wavefront sweep under the B200 solver
         {
@@ -255,6 +268,22 @@ int main(int argc, char** argv) {
             sst_k = std::max(rel_l2_plane0(bs.k().data(), rs.k().data(), pl), rel_l2_plane0(bs.omega().data(), rs.omega().data(), pl));
             sst_nut = rel_l2(bs.nu_t().data(), rs.nu_t().data());
             if (!(sst_u <= 1e-10 && sst_k <= 1e-10 && sst_nut <= 1e-9)) rc = 1;
+            // the standard k-omega model, same route
+            RANSSolver rk(m2, sc);
+            rk.set_velocity_bc(b2);
+            rk.set_body_force(1.0, 0.0);
+            rk.set_turbulence_model(std::make_unique<KOmegaTransport>());
+            rk.initialize(w0);
+            b200::RANSSolverB200 bk(m2, sc);
+            bk.set_velocity_bc(b2);
+            bk.set_body_force(1.0, 0.0);
+            bk.set_turbulence_model(std::make_unique<KOmegaTransport>());
+            bk.initialize(w0);
+            for (int s = 0; s < 2; ++s) { rk.step(); bk.step(); }
+            bk.sync_from_gpu();
+            if (!(rel_l2(bk.velocity().u_data(), rk.velocity().u_data()) <= 1e-10 &&
+                  rel_l2_plane0(bk.k().data(), rk.k().data(), pl) <= 1e-10 &&
+                  rel_l2(bk.nu_t().data(), rk.nu_t().data()) <= 1e-9)) rc = 1;
         }
         if (!wdir.empty() && closure_section(wdir, closure_json) != 0) rc = 1;
     } catch (const std::exception& e) {

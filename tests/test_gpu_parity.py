@@ -330,5 +330,10 @@ def test_step_with_sst_k_omega_192x96(gpu, oracle):
     cases.check_step_with_sst(gpu, oracle, stretched=True, ti="rk3", N=(192, 96, 1), nsteps=5, tol=1e-9, turb_tol=1e-9)
 
 
+@pytest.mark.parametrize("kind", ["uniform", "stretched"])
+def test_step_with_standard_k_omega_matches_reference(gpu, oracle, kind):
+    cases.check_step_with_sst(gpu, oracle, stretched=kind == "stretched", ti="rk3", model="komega")
+
+
 def test_sst_rejects_3d_meshes(gpu):
     cases.check_sst_rejects_3d(gpu)

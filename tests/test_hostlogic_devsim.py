@@ -237,5 +237,10 @@ def test_step_with_sst_k_omega_matches_reference(sim, oracle, kind, ti):
     cases.check_step_with_sst(sim, oracle, stretched=kind == "stretched", ti=ti)
 
 
+@pytest.mark.parametrize("kind", ["uniform", "stretched"])
+def test_step_with_standard_k_omega_matches_reference(sim, oracle, kind):
+    cases.check_step_with_sst(sim, oracle, stretched=kind == "stretched", ti="rk3", model="komega")
+
+
 def test_sst_rejects_3d_meshes(sim):
     cases.check_sst_rejects_3d(sim)
