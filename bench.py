@@ -352,6 +352,7 @@ def main():
         B.check(B.lib.cfdnn_solver_set_les_model(h, K.LES_MODEL[args.closure], -1.0))
     if world > 1:
         comm_init(h)
+    fft_p2p = bool(B.lib.cfdnn_solver_fft_peer_to_peer(h))
 
     # synthetic input, this rank's slab of the global box (pinned host arrays)
     sh = K.shapes(Nx, Ny, Nzl)
@@ -566,6 +567,9 @@ def main():
             roof["poisson"] = {"solver": args.poisson, "ms_per_step": pms, "solves_per_step": 3,
                                "share_of_step": T["phases"][3] / T["step_ms"]}
             if args.poisson == "fft":
+                if world > 1:
+                    roof["poisson"]["transposes"] = ("peer-to-peer stores over NVLink (CUDA IPC), fused into the transform kernels"
+                                                     if fft_p2p else "NCCL all-to-all")
                 roof["poisson"].update({"kernels": "k_fft_x_fwd, k_fft_z, k_fft_thomas, k_fft_z<inv>, k_fft_x_inv",
                                         "achieved": gbs(3 * cells_b, pms), "frac": frac(gbs(3 * cells_b, pms)),
                                         "note": "direct solve: 2-D FFT over x/z (shared-memory Stockham) + Thomas in y; "

@@ -81,6 +81,7 @@ struct NcclComm final : Comm {
     void allgather_planes(double* base, size_t count, cudaStream_t st) override {
         NCCL_OK(nccl().AllGather(base + (size_t)rank * count, base, count, ncclFloat64, comm, st));
     }
+    bool device_transport() const override { return true; }
     void alltoall(const double* send, double* recv, size_t count, cudaStream_t st) override {
         Nccl& n = nccl();
         CFDNN_CUDA(cudaMemcpyAsync(recv + (size_t)rank * count, send + (size_t)rank * count, count * sizeof(double),

@@ -40,6 +40,9 @@ struct Comm {
     // block q of `send` (count doubles at send + q*count) goes to rank q, which stores it as block `rank` of its
     // `recv`; send and recv must not overlap (the FFT Poisson solver's transposes)
     virtual void alltoall(const double* send, double* recv, size_t count, cudaStream_t st) = 0;
+    // true when the ranks are GPUs of one node driven by NCCL (device buffers, CUDA IPC possible); false for the host
+    // callback transport of the CPU test double
+    virtual bool device_transport() const { return false; }
 };
 
 // NCCL transport (product).  id128 = ncclUniqueId bytes made by cfdnn_comm_unique_id on rank 0.

@@ -18,6 +18,7 @@
 #include <cmath>
 #include <cstring>
 #include <cstdlib>
+#include <cstdio>
 
 namespace cfdnn {
 namespace {
@@ -27,6 +28,14 @@ constexpr int FFT_MAX_RAD = 12;
 
 struct Radices {
     int n, r[FFT_MAX_RAD];
+};
+
+// Where the blocks of the decomposed spectrum live, as seen by the kernel that WRITES them: b[q] = base of the block
+// that belongs to rank q.  One rank / NCCL transposes: offsets into this rank's own array.  Peer-to-peer transposes: the
+// IPC-mapped arrays of the other GPUs, so the store of the transform IS the all-to-all (NVLink writes, no pack, no pass).
+constexpr int FFT_MAX_RANKS = 16;
+struct BlockPtrs {
+    double2* b[FFT_MAX_RANKS];
 };
 
 __device__ __forceinline__ double2 c2(double x, double y) { double2 r; r.x = x; r.y = y; return r; }
@@ -141,7 +150,7 @@ __device__ __forceinline__ size_t sblock(int kx, int Pq, int rows) {
 
 // forward: line l of the CTA carries rows 2l (real part) and 2l+1 (imaginary part); row = k Ny + j
 __global__ void __launch_bounds__(FFT_THREADS)
-k_fft_x_fwd(const double* __restrict__ rhs, double2* __restrict__ spec, int Nx, int Ny,
+k_fft_x_fwd(const double* __restrict__ rhs, BlockPtrs dst, int Nx, int Ny,
             int Nz, int Ng, int cs, int cp, int Pxh, int L, int logL, Radices rad, const double2* __restrict__ tw) {
     CFDNN_DYN_SMEM(double2, sm);
     double2* A = sm;
@@ -177,9 +186,10 @@ k_fft_x_fwd(const double* __restrict__ rhs, double2* __restrict__ spec, int Nx, 
         for (int kx = threadIdx.x; kx < Nxh; kx += blockDim.x) {
             const double2 z = Z[sw(kx, l, L)], zc = cconj(Z[sw(kx == 0 ? 0 : Nx - kx, l, L)]);
             const double2 s = cadd(z, zc), d = csub(z, zc);
-            const size_t o = sblock(kx, Pxh, rows);
-            if (ra < rows) spec[o + (size_t)ra * Pxh] = c2(0.5 * s.x, 0.5 * s.y);
-            if (rb < rows) spec[o + (size_t)rb * Pxh] = c2(0.5 * d.y, -0.5 * d.x);  // (z - conj z') / (2 i)
+            const int q = kx < Pxh ? 0 : kx / Pxh;                       // owner of this kx column
+            double2* const blk = dst.b[q] + (kx - q * Pxh);
+            if (ra < rows) blk[(size_t)ra * Pxh] = c2(0.5 * s.x, 0.5 * s.y);
+            if (rb < rows) blk[(size_t)rb * Pxh] = c2(0.5 * d.y, -0.5 * d.x);        // (z - conj z') / (2 i)
         }
     }
 }
@@ -237,7 +247,8 @@ k_fft_x_inv(const double2* __restrict__ spec, double* __restrict__ p, int Nx, in
 // a CTA owns row j and a tile of L consecutive kx: every global access is a run of L complex numbers
 template <bool INV>
 __global__ void __launch_bounds__(FFT_THREADS)
-k_fft_z(double2* __restrict__ spec, int Ny, int Nz, int Pxh, int L, int logL, Radices rad, const double2* __restrict__ tw) {
+k_fft_z(double2* __restrict__ spec, BlockPtrs out, int Nzl, int Ny, int Nz, int Pxh, int L, int logL, Radices rad,
+        const double2* __restrict__ tw) {
     CFDNN_DYN_SMEM(double2, sm);
     double2* A = sm;
     double2* B = sm + (size_t)Nz * L;
@@ -262,7 +273,12 @@ k_fft_z(double2* __restrict__ spec, int Ny, int Nz, int Pxh, int L, int logL, Ra
     for (int t = threadIdx.x; t < Nz * L; t += blockDim.x) {
         const int l = t & (L - 1), n = t >> logL;
         const double2 v = Z[sw(n, l, L)];
-        base[(size_t)n * zs + l] = INV ? cconj(v) : v;
+        if (INV) {                                  // plane n belongs to the slab of rank n / Nzl: its block of S
+            const int s = n / Nzl;
+            out.b[s][((size_t)(n - s * Nzl) * Ny + j) * Pxh + kx0 + l] = cconj(v);
+        } else {
+            base[(size_t)n * zs + l] = v;
+        }
     }
 }
 
@@ -467,7 +483,74 @@ void FftPoisson::set_comm(Comm* c) {
     plan(P > 1 ? c : nullptr);
 }
 
+// Peer-to-peer transposes: every rank maps the S and T arrays of the others through CUDA IPC (one process per GPU), so the
+// transform kernels store straight into the owner's array over NVLink.  All ranks must succeed, else everybody stays on
+// the NCCL all-to-all.  CFDNN_FFT_P2P=0 turns it off.
+void FftPoisson::release_peer_access() {
+#ifndef CFDNN_DEVSIM
+    for (void* p : peer_opened_) cudaIpcCloseMemHandle(p);
+#endif
+    peer_opened_.clear();
+    p2p_ = false;
+}
+
+void FftPoisson::setup_peer_access() {
+    release_peer_access();
+#ifndef CFDNN_DEVSIM
+    if (P_ <= 1 || P_ > FFT_MAX_RANKS || !comm_->device_transport()) return;
+    if (const char* e = std::getenv("CFDNN_FFT_P2P")) if (std::atoi(e) == 0) return;
+    const bool dbg = std::getenv("CFDNN_FFT_P2P_DEBUG") != nullptr;
+    auto note = [&](const char* what, cudaError_t e) {
+        if (dbg) std::fprintf(stderr, "[cfdnn fft p2p] rank %d: %s: %s\n", rank_, what, cudaGetErrorString(e));
+    };
+    constexpr int HD = 2 * (int)(sizeof(cudaIpcMemHandle_t) / sizeof(double));        // doubles per rank: two handles
+    static_assert(sizeof(cudaIpcMemHandle_t) % sizeof(double) == 0, "IPC handle size");
+    std::vector<double> host((size_t)HD * P_, 0.0);
+    cudaIpcMemHandle_t hs, ht;
+    cudaError_t e1 = cudaIpcGetMemHandle(&hs, spec_.p), e2 = cudaIpcGetMemHandle(&ht, spec2_.p);
+    note("cudaIpcGetMemHandle(S)", e1); note("cudaIpcGetMemHandle(T)", e2);
+    bool ok = e1 == cudaSuccess && e2 == cudaSuccess;
+    if (ok) {
+        std::memcpy(host.data() + (size_t)HD * rank_, &hs, sizeof(hs));
+        std::memcpy(host.data() + (size_t)HD * rank_ + HD / 2, &ht, sizeof(ht));
+    }
+    (void)cudaGetLastError();
+    DevBuf<double> dev;
+    dev.alloc((size_t)HD * P_ + 1, true);
+    CFDNN_CUDA(cudaMemcpy(dev.p + (size_t)HD * rank_, host.data() + (size_t)HD * rank_, HD * sizeof(double), cudaMemcpyHostToDevice));
+    comm_->allgather_planes(dev.p, HD, nullptr);
+    CFDNN_CUDA(cudaMemcpy(host.data(), dev.p, host.size() * sizeof(double), cudaMemcpyDeviceToHost));
+    peer_S_.assign(P_, nullptr);
+    peer_T_.assign(P_, nullptr);
+    for (int q = 0; q < P_ && ok; ++q) {
+        if (q == rank_) { peer_S_[q] = spec_.p; peer_T_[q] = spec2_.p; continue; }
+        cudaIpcMemHandle_t a, b;
+        std::memcpy(&a, host.data() + (size_t)HD * q, sizeof(a));
+        std::memcpy(&b, host.data() + (size_t)HD * q + HD / 2, sizeof(b));
+        void *ps = nullptr, *pt = nullptr;
+        cudaError_t eo = cudaIpcOpenMemHandle(&ps, a, cudaIpcMemLazyEnablePeerAccess);
+        note("cudaIpcOpenMemHandle(S)", eo);
+        if (eo != cudaSuccess) { ok = false; break; }
+        peer_opened_.push_back(ps);
+        eo = cudaIpcOpenMemHandle(&pt, b, cudaIpcMemLazyEnablePeerAccess);
+        note("cudaIpcOpenMemHandle(T)", eo);
+        if (eo != cudaSuccess) { ok = false; break; }
+        peer_opened_.push_back(pt);
+        peer_S_[q] = static_cast<double2*>(ps);
+        peer_T_[q] = static_cast<double2*>(pt);
+    }
+    (void)cudaGetLastError();
+    const double flag = ok ? 1.0 : 0.0;                          // everybody or nobody
+    CFDNN_CUDA(cudaMemcpy(dev.p + (size_t)HD * P_, &flag, sizeof(double), cudaMemcpyHostToDevice));
+    comm_->allreduce_min(dev.p + (size_t)HD * P_, 1, nullptr);
+    double all = 0.0;
+    CFDNN_CUDA(cudaMemcpy(&all, dev.p + (size_t)HD * P_, sizeof(double), cudaMemcpyDeviceToHost));
+    if (all > 0.5) p2p_ = true; else release_peer_access();
+#endif
+}
+
 void FftPoisson::plan(Comm* c) {
+    release_peer_access();
     comm_ = c;
     P_ = c ? c->nranks : 1;
     rank_ = c ? c->rank : 0;
@@ -475,8 +558,10 @@ void FftPoisson::plan(Comm* c) {
     const size_t ns = (size_t)Nzg_ * Ny_ * Pq_;     // = P * Nz_local * Ny * Pq
     spec_.alloc(ns, true);
     if (P_ > 1) spec2_.alloc(ns, true); else spec2_.release();
+    sync_.alloc(8, true);
     cprime_.alloc(ns, true);
     invden_.alloc(ns, true);
+    setup_peer_access();
     const dim3 gt((Pq_ + 127) / 128, Nzg_);
     CFDNN_LAUNCH(k_fft_thomas_setup, gt, 128, 0, nullptr, cprime_.p, invden_.p, lamx_.p, lamz_.p, lo_.p, up_.p, base_.p, Ny_,
                  Nxh_, Pq_, rank_ * Pq_);
@@ -538,21 +623,30 @@ int FftPoisson::solve_dev(const double* rhs, double* p, cudaStream_t st) {      
     double2* S = spec_.p;                            // [q][k_local][j][c]
     double2* T = P_ > 1 ? spec2_.p : spec_.p;        // [kz][j][c]
     const size_t blk = (size_t)rows * Pq_ * 2;       // doubles per all-to-all block
+    const size_t bel = (size_t)rows * Pq_;           // complex elements per block
+    BlockPtrs to_T{}, to_S{};                        // where x_fwd / the inverse z transform store block q
+    for (int q = 0; q < P_; ++q) {
+        to_T.b[q] = p2p_ ? peer_T_[q] + bel * rank_ : S + bel * q;      // p2p: straight into the owner's T
+        to_S.b[q] = p2p_ ? peer_S_[q] + bel * rank_ : T + bel * q;      // p2p: straight into the owner's S
+    }
+    auto barrier = [&] { comm_->allreduce_sum(sync_.p, 1, st); };      // stream-ordered: every rank's stores have landed
     // 1. forward transforms
     const int xlines = (rows + 1) / 2;
     const size_t smx = (size_t)2 * Nx_ * Lx_ * sizeof(double2), smz = (size_t)2 * Nzg_ * Lz_ * sizeof(double2);
-    CFDNN_LAUNCH_COOP(k_fft_x_fwd, (xlines + Lx_ - 1) / Lx_, FFT_THREADS, smx, st, rhs, S, Nx_, Ny_, Nz_, Ng_, cs_, cp_, Pq_,
+    CFDNN_LAUNCH_COOP(k_fft_x_fwd, (xlines + Lx_ - 1) / Lx_, FFT_THREADS, smx, st, rhs, to_T, Nx_, Ny_, Nz_, Ng_, cs_, cp_, Pq_,
                       Lx_, ilog2(Lx_), rx, twx_.p);
-    if (P_ > 1) comm_->alltoall(reinterpret_cast<const double*>(S), reinterpret_cast<double*>(T), blk, st);
+    if (p2p_) barrier();
+    else if (P_ > 1) comm_->alltoall(reinterpret_cast<const double*>(S), reinterpret_cast<double*>(T), blk, st);
     const dim3 gz(Pq_ / Lz_, Ny_);
-    CFDNN_LAUNCH_COOP((k_fft_z<false>), gz, FFT_THREADS, smz, st, T, Ny_, Nzg_, Pq_, Lz_, ilog2(Lz_), rz, twz_.p);
+    CFDNN_LAUNCH_COOP((k_fft_z<false>), gz, FFT_THREADS, smz, st, T, to_S, Nz_, Ny_, Nzg_, Pq_, Lz_, ilog2(Lz_), rz, twz_.p);
     // 2. tridiagonal solves (with the mean removal on the zero mode)
     const dim3 gt((Pq_ + 127) / 128, Nzg_);
     CFDNN_LAUNCH((k_fft_thomas<8>), gt, 128, 0, st, T, cprime_.p, invden_.p, lo_.p, dyv_.p, inv_Ly_, Ny_, Nxh_, Pq_,
                  rank_ * Pq_);
     // 3. inverse transforms, normalisation, ghosts (x in the kernel, then y rows, then the periodic z planes)
-    CFDNN_LAUNCH_COOP((k_fft_z<true>), gz, FFT_THREADS, smz, st, T, Ny_, Nzg_, Pq_, Lz_, ilog2(Lz_), rz, twz_.p);
-    if (P_ > 1) comm_->alltoall(reinterpret_cast<const double*>(T), reinterpret_cast<double*>(S), blk, st);
+    CFDNN_LAUNCH_COOP((k_fft_z<true>), gz, FFT_THREADS, smz, st, T, to_S, Nz_, Ny_, Nzg_, Pq_, Lz_, ilog2(Lz_), rz, twz_.p);
+    if (p2p_) barrier();
+    else if (P_ > 1) comm_->alltoall(reinterpret_cast<const double*>(T), reinterpret_cast<double*>(S), blk, st);
     CFDNN_LAUNCH_COOP(k_fft_x_inv, (xlines + Lx_ - 1) / Lx_, FFT_THREADS, smx, st, S, p, Nx_, Ny_, Nz_, Ng_, cs_, cp_, Pq_,
                       Lx_, ilog2(Lx_), rx, twx_.p, 1.0 / ((double)Nx_ * (double)Nzg_));
     CFDNN_LAUNCH(k_fft_ghost_y, dim3((cs_ + 127) / 128, Nz_), 128, 0, st, p, cs_, Ny_, Nz_, Ng_, cs_, cp_);

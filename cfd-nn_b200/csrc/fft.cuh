@@ -12,6 +12,8 @@ namespace cfdnn {
 class FftPoisson {
 public:
     explicit FftPoisson(const cfdnn_mesh_desc& m);
+    ~FftPoisson() { release_peer_access(); }
+    bool peer_to_peer() const { return p2p_; }   // transposes by direct stores into the other GPUs' arrays
     // x and z must be periodic, y Neumann on both walls (include/poisson_solver_fft.hpp:27-30 allows Dirichlet in y
     // as well; not supported here)
     void set_bc(const int bc[6]);
@@ -28,6 +30,12 @@ public:
 private:
     void setup_tables(const cfdnn_mesh_desc& m);
     void plan(Comm* c);
+    void setup_peer_access();
+    void release_peer_access();
+    bool p2p_ = false;
+    std::vector<double2*> peer_S_, peer_T_;     // S / T of every rank as mapped here (own entry: the local array)
+    std::vector<void*> peer_opened_;            // IPC mappings to close
+    DevBuf<double> sync_;                       // operand of the barrier all-reduce
     int Nx_, Ny_, Nz_, Ng_;         // Nz_: planes of this rank
     int Nzg_;                       // planes of the whole box
     int Nxh_, Pq_ = 0;              // kept x modes Nx/2+1; columns per rank (padded, complex elements)

@@ -54,6 +54,7 @@ public:
     double dt() const { return dt_; }
     void set_turbulence_model(NNClosure* nn) { nn_ = nn; }
     void set_external_nu_t(bool on, bool transport = false) { ext_nut_ = on; ext_transport_ = on && transport; }   // nu_t uploaded by the caller (bridged host model)
+    bool fft_peer_to_peer() const { return fft_ && fft_active_ && fft_->peer_to_peer(); }
     void set_sst_model(int kind);                            // native SST / standard k-omega transport + closure (2-D meshes)
     void set_trip_forcing(const cfdnn_trip_desc* d);         // trip-region forcing in the Euler predictor
     void apply_velocity_filter(double strength);             // explicit Laplacian filter between steps

@@ -206,6 +206,9 @@ int cfdnn_adaptive_dt_noalloc(const cfdnn_mesh_desc* mesh, const cfdnn_config* c
                               double* dt_out);
 /* V-cycles of every Poisson solve since the last call (oracle: POISSON_STATS lines) */
 int cfdnn_solver_cycle_log(cfdnn_solver* s, int* cycles, int cap, int* n_out);
+/* 1 when the FFT Poisson solver of a multi-GPU run does its transposes by peer-to-peer stores (CUDA IPC over NVLink: the
+ * transform kernels write straight into the owning GPU's array), 0 when it uses NCCL all-to-alls or is not in use */
+int cfdnn_solver_fft_peer_to_peer(const cfdnn_solver* s);
 /* set_turbulence_model(unique_ptr<TurbulenceModel>) :98 — solver borrows the closure */
 int cfdnn_solver_set_turbulence_model(cfdnn_solver* s, cfdnn_nn* nn);
 /* device timing of the last step()/run(): total ms and ms spent inside V-cycles */

@@ -113,9 +113,10 @@ def main():
     dts = []
     dt = C.c_double()
     B.check(B.lib.cfdnn_solver_compute_adaptive_dt(h, C.byref(dt)))
+    fft_p2p = int(B.lib.cfdnn_solver_fft_peer_to_peer(h))
     st = B.state(h, Nx, Ny, Nz, names=("u", "v", "w", "p", "pcorr", "div", "rhs"))
     np.savez(os.path.join(outdir, f"slab{rank}.npz"), residuals=np.array(res), cycles=np.array(B.cycles(h)),
-             adaptive_dt=dt.value, stats=np.array([stats["sendrecv"], stats["allreduce"], stats["allgather"]]), **st)
+             adaptive_dt=dt.value, fft_p2p=fft_p2p, stats=np.array([stats["sendrecv"], stats["allreduce"], stats["allgather"]]), **st)
     B.lib.cfdnn_solver_destroy(h)
     dist.barrier()
     dist.destroy_process_group()

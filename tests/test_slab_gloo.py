@@ -206,13 +206,17 @@ def _single_domain_fft(B, R, slab_worker, N, bc, ti, nsteps):
     return st, cyc
 
 
-def _check_fft_slabs(B, R, world, N, ti, nsteps, monkeypatch, on_gpu):
+def _check_fft_slabs(B, R, world, N, ti, nsteps, monkeypatch, on_gpu, p2p=None):
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import slab_worker
     bc = "PPWWPP"
     monkeypatch.setenv("SLAB_POISSON", "fft")
+    if p2p is not None:
+        monkeypatch.setenv("CFDNN_FFT_P2P", "1" if p2p else "0")
     with tempfile.TemporaryDirectory() as td:
         slabs = _run_slabs(world, N, bc, ti, nsteps, 0, td, gpu=on_gpu)
+    if p2p is not None:                             # the transposes really took the requested route on every rank
+        assert [int(s_["fft_p2p"]) for s_ in slabs] == [1 if p2p else 0] * world
     names = ("u", "v", "w", "p", "pcorr", "div", "rhs")
     got = {n: _assemble(slabs, n, N[2] // world) for n in names}
     single, cyc = _single_domain_fft(B, R, slab_worker, N, bc, ti, nsteps)
@@ -232,4 +236,6 @@ def test_two_slabs_fft_poisson_match_single_domain(R, sim, monkeypatch):
 def test_gpu_slabs_fft_poisson(R, gpu, world, monkeypatch):
     if gpu.lib.cfdnn_device_count() < world:
         pytest.skip(f"needs {world} GPUs")
-    _check_fft_slabs(gpu, R, world, (128, 48, 32 * world), "rk3", 1, monkeypatch, on_gpu=True)
+    # peer-to-peer transposes (the transform kernels store into the other GPUs' arrays through CUDA IPC) and NCCL all-to-alls
+    _check_fft_slabs(gpu, R, world, (128, 48, 32 * world), "rk3", 1, monkeypatch, on_gpu=True, p2p=True)
+    _check_fft_slabs(gpu, R, world, (128, 48, 32 * world), "rk3", 2, monkeypatch, on_gpu=True, p2p=False)
