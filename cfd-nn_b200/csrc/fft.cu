@@ -498,7 +498,12 @@ void FftPoisson::setup_peer_access() {
     release_peer_access();
 #ifndef CFDNN_DEVSIM
     if (P_ <= 1 || P_ > FFT_MAX_RANKS || !comm_->device_transport()) return;
-    if (const char* e = std::getenv("CFDNN_FFT_P2P")) if (std::atoi(e) == 0) return;
+    // Default route, from the measurements in DESIGN 6: the direct stores win on 2 GPUs (config 5 Poisson 44.0 -> 38.4 ms
+    // per step) and lose on 8 (13.7 -> 15.9 ms): there the inverse z transform scatters 32-byte runs to eight GPUs.
+    // CFDNN_FFT_P2P=1 / 0 forces the route.
+    bool want = P_ == 2;
+    if (const char* e = std::getenv("CFDNN_FFT_P2P")) want = std::atoi(e) != 0;
+    if (!want) return;
     const bool dbg = std::getenv("CFDNN_FFT_P2P_DEBUG") != nullptr;
     auto note = [&](const char* what, cudaError_t e) {
         if (dbg) std::fprintf(stderr, "[cfdnn fft p2p] rank %d: %s: %s\n", rank_, what, cudaGetErrorString(e));
