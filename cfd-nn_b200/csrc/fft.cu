@@ -7,13 +7,16 @@
 //   * no pack/unpack passes: the x transform reads the solver's ghosted rows and the inverse x transform writes
 //     them (x ghosts included);
 //   * the half spectrum is taken along x (the contiguous index), two real rows ride one complex transform;
-//   * hand-written Stockham autosort FFTs in shared memory (radix 2/3/4/5, conflict-free swizzled [n][line] tiles):
+//   * hand-written Stockham autosort FFTs in shared memory (radix 8/4/2/3/5, conflict-free swizzled [n][line] tiles):
 //     x lines are contiguous rows, z lines are gathered as tiles of L consecutive kx so every global access is a
 //     run of L complex numbers;
-//   * the Thomas solve runs on the [kz][j][kx] spectrum in place, one thread per mode, coalesced in kx; c' depends
-//     on the mesh only and is tabulated once.
-// Algorithmic traffic per real cell: x fwd 8+8, z fwd 8+8, Thomas 8+8 (+8+4+8: second read, c', write), z inv 8+8,
-// x inv 8+8 = 100 B — 6.7 GB at 512x256x512, against ~20 V-cycles of ~1 GB each for the multigrid.
+//   * the Thomas solve runs on the [kz][j][kx] spectrum in place, one thread per mode, coalesced in kx; its
+//     factorisation (c', 1/den) depends on the mesh only and is tabulated once; the mean removal is folded into the
+//     zero mode;
+//   * on z-slabs the spectrum is kept in per-rank blocks and the two transposes per solve are either NCCL all-to-alls or
+//     direct stores of the transform kernels into the other GPUs' arrays (CUDA IPC), see setup_peer_access().
+// Algorithmic traffic per real cell: x fwd 8+8, z fwd 8+8, Thomas 36, z inv 8+8, x inv 8+8 = 100 B — 6.7 GB at
+// 512x256x512 (1.89 ms per solve measured), against ~20 V-cycles of ~1 GB each for the multigrid.
 #include "fft.cuh"
 #include <cmath>
 #include <cstring>
