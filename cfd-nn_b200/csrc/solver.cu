@@ -722,6 +722,7 @@ void Solver::set_les_model(int model, double constant) {
 }
 
 void Solver::set_sst_model(int kind) {
+    sst_kind_ = kind;
     if (kind == CFDNN_RANS_NONE) { sst_.reset(); return; }
     if (!is2d_)
         throw std::invalid_argument("set_sst_model: the reference's SST k-omega transport is two-dimensional (k, omega, nu_t "
@@ -729,7 +730,13 @@ void Solver::set_sst_model(int kind) {
     cfdnn_mesh_desc m = mesh_;
     m.yc = h_yc_.empty() ? nullptr : h_yc_.data();
     m.dyc = h_dyc_.empty() ? nullptr : h_dyc_.data();
+    m.dyv = h_dyv_.empty() ? nullptr : h_dyv_.data();
     sst_ = std::make_unique<SstModel>(m, cfg_.nu, kind);
+}
+
+void Solver::set_mixing_length_params(double kappa, double A_plus, double delta) {
+    if (!sst_) throw std::invalid_argument("set_mixing_length_params: attach CFDNN_RANS_MIXING_LENGTH first");
+    sst_->ml_kappa = kappa; sst_->ml_A_plus = A_plus; sst_->ml_delta = delta;
 }
 
 void Solver::update_turbulence() {

@@ -55,6 +55,7 @@ public:
     void set_turbulence_model(NNClosure* nn) { nn_ = nn; }
     void set_external_nu_t(bool on, bool transport = false) { ext_nut_ = on; ext_transport_ = on && transport; }   // nu_t uploaded by the caller (bridged host model)
     bool fft_peer_to_peer() const { return fft_ && fft_active_ && fft_->peer_to_peer(); }
+    void set_mixing_length_params(double kappa, double A_plus, double delta);
     void set_sst_model(int kind);                            // native SST / standard k-omega transport + closure (2-D meshes)
     void set_trip_forcing(const cfdnn_trip_desc* d);         // trip-region forcing in the Euler predictor
     void apply_velocity_filter(double strength);             // explicit Laplacian filter between steps
@@ -62,7 +63,9 @@ public:
     void set_time(double t) { time_ = t; }
     void set_les_model(int model, double constant);          // static LES SGS closure evaluated at the top of step()
     bool has_model() const { return nn_ != nullptr || ext_nut_ || les_model_ != 0 || sst_ != nullptr; }
-    bool transport_model() const { return ext_transport_ || sst_ != nullptr; }   // uses_transport_equations()
+    bool transport_model() const {               // uses_transport_equations(): SST / standard k-omega, not the algebraic models
+        return ext_transport_ || (sst_ != nullptr && (sst_kind_ == CFDNN_RANS_SST || sst_kind_ == CFDNN_RANS_KOMEGA));
+    }
     double* view_ptr(int field, size_t* n) const;           // device twin of a field (cfdnn_solver_device_ptr)
     void comm_init(Comm* c);
 
@@ -107,6 +110,7 @@ private:
 
     std::unique_ptr<Multigrid> mg_;
     std::unique_ptr<class SstModel> sst_;
+    int sst_kind_ = CFDNN_RANS_NONE;
     // trip forcing (src/solver.cpp:818-950): device copies of the caller's tables
     bool trip_on_ = false, trip_w_ = false;
     double trip_A_ = 0, trip_duration_ = 0, trip_ramp_start_ = 0, trip_w_scale_ = 1;

@@ -229,11 +229,75 @@ __global__ void k_kw_closure(Geom g, double nu, const double* __restrict__ k, co
     const double cap = 1000.0 * nu;
     nu_t[o] = (r < -cap) ? -cap : ((cap < r) ? cap : r);                // std::clamp(ratio, -ceiling, ceiling)
 }
+// ---- the two algebraic 2-D RANS baselines (src/turbulence_baseline.cpp): both scale with a friction velocity taken from
+// the mean |du/dy| of the first interior row, summed over i in order like the reference's loop (one thread: Nx values).
+// ML = true : MixingLengthModel (:330-352) — one-sided difference u(i, j+1) - u(i, j) over the local centre spacing
+// ML = false: AlgebraicKOmegaModel (:433-447) — the MAC central difference dudy(i, j) of compute_gradients_from_mac
+template <bool ML>
+__global__ void k_rans_utau(Geom g, double nu, double inv_2dy, double dy_local, const double* __restrict__ dyc,
+                            const double* __restrict__ u, double* __restrict__ out) {
+    if (blockIdx.x != 0 || threadIdx.x != 0) return;
+    const int j = g.Ng;
+    double acc = 0.0;
+    for (int ix = 0; ix < g.Nx; ++ix) {
+        const int ou = j * g.us + ix + g.Ng;
+        if (ML) acc += fabs((u[ou + g.us] - u[ou]) / dy_local);
+        else acc += fabs((u[ou + g.us] - u[ou - g.us]) * (dyc ? 1.0 / (dyc[j] + dyc[j + 1]) : inv_2dy));
+    }
+    acc /= g.Nx;
+    const double ut = sqrt(nu * acc);
+    out[0] = (ut < 1e-10) ? 1e-10 : ut;                                 // std::max(u_tau, 1e-10)
+}
+
+// MixingLengthModel: l = kappa y (1 - exp(-y+ / A+)) capped at delta / 2, nu_t = l^2 |S| capped at 1000 nu, under-relaxed
+// with the previous nu_t (mixing_length_cell_kernel :36-76)
+__global__ void k_mixing_length(Geom g, double nu, double kappa, double A_plus, double delta, double inv_2dx, double inv_2dy,
+                                const double* __restrict__ dyc, const double* __restrict__ u, const double* __restrict__ v,
+                                const double* __restrict__ wall, const double* __restrict__ utau, double* __restrict__ nu_t) {
+    const int ix = blockIdx.x * blockDim.x + threadIdx.x, iy = blockIdx.y * blockDim.y + threadIdx.y;
+    if (ix >= g.Nx || iy >= g.Ny) return;
+    const int i = ix + g.Ng, j = iy + g.Ng;
+    const int o = j * g.cs + i, ou = j * g.us + i, ov = j * g.vs + i;
+    const double wy = dyc ? 1.0 / (dyc[j] + dyc[j + 1]) : inv_2dy;
+    const double dudx = (u[ou + 1] - u[ou - 1]) * inv_2dx, dudy = (u[ou + g.us] - u[ou - g.us]) * wy;
+    const double dvdx = (v[ov + 1] - v[ov - 1]) * inv_2dx, dvdy = (v[ov + g.vs] - v[ov - g.vs]) * wy;
+    const double Sxy = 0.5 * (dudy + dvdx);
+    const double Smag = sqrt(2.0 * (dudx * dudx + dvdy * dvdy + 2.0 * Sxy * Sxy));
+    const double yw = wall[j];
+    const double y_plus = yw * utau[0] / nu;
+    const double damping = 1.0 - exp(-y_plus / A_plus);
+    double l_mix = kappa * yw * damping;
+    if (l_mix > 0.5 * delta) l_mix = 0.5 * delta;
+    double nut_new = l_mix * l_mix * Smag;
+    const double cap = 1000.0 * nu;
+    if (nut_new > cap) nut_new = cap;
+    nu_t[o] = 0.5 * nut_new + 0.5 * nu_t[o];
+}
+
+// AlgebraicKOmegaModel (:449-470): k and omega estimated from u_tau and the wall distance, nu_t = k / omega
+__global__ void k_algebraic_komega(Geom g, double nu, double C_mu, const double* __restrict__ wall,
+                                   const double* __restrict__ utau, double* __restrict__ nu_t) {
+    const int ix = blockIdx.x * blockDim.x + threadIdx.x, iy = blockIdx.y * blockDim.y + threadIdx.y;
+    if (ix >= g.Nx || iy >= g.Ny) return;
+    const int j = iy + g.Ng, o = j * g.cs + ix + g.Ng;
+    const double ut = utau[0], yw = wall[j];
+    const double y_plus = yw * ut / nu;
+    const double f_mu = 1.0 - exp(-y_plus / 26.0);                                      // numerics::A_PLUS
+    const double k_est = (ut * ut / sqrt(C_mu)) * f_mu * f_mu;
+    const double yf = (yw < 1e-10) ? 1e-10 : yw;                                        // std::max(y_wall, Y_WALL_FLOOR)
+    double o_est = ut / (0.41 * yf * f_mu + 1e-10);                                     // numerics::KAPPA
+    if (y_plus < 5.0) o_est = 6.0 * nu / (0.075 * yw * yw + 1e-20);
+    const double od = (o_est < 1e-10) ? 1e-10 : o_est;
+    const double r = k_est / od;
+    const double r0 = (0.0 < r) ? r : 0.0;                                              // std::max(0.0, .)
+    const double cap = 1000.0 * nu;
+    nu_t[o] = (cap < r0) ? cap : r0;                                                    // std::min(., 1000 nu)
+}
 }  // namespace
 
 SstModel::SstModel(const cfdnn_mesh_desc& m, double nu, int kind) : kind_(kind), dx_(m.dx), dy_(m.dy) {
-    if (kind != CFDNN_RANS_SST && kind != CFDNN_RANS_KOMEGA)
-        throw std::invalid_argument("transport model: kind must be CFDNN_RANS_SST or CFDNN_RANS_KOMEGA");
+    if (kind < CFDNN_RANS_SST || kind > CFDNN_RANS_ALGEBRAIC_KOMEGA)
+        throw std::invalid_argument("2-D RANS model: kind must be CFDNN_RANS_SST, _KOMEGA, _MIXING_LENGTH or _ALGEBRAIC_KOMEGA");
     require_device();
     if (m.Nz > 1)
         throw std::invalid_argument("SST k-omega: the reference model is two-dimensional (fields indexed (i, j)); 3-D meshes "
@@ -249,6 +313,9 @@ SstModel::SstModel(const cfdnn_mesh_desc& m, double nu, int kind) : kind_(kind),
     }
     wall_.alloc(n, false);
     CFDNN_CUDA(cudaMemcpy(wall_.p, w.data(), n * sizeof(double), cudaMemcpyHostToDevice));
+    dy_wall_ = m.dy;                                 // centre spacing at the lower wall row, src/turbulence_baseline.cpp:337-341
+    if (m.y_stretched && m.dyv) dy_wall_ = 0.5 * (m.dyv[m.Ng] + m.dyv[m.Ng + 1]);
+    utau_.alloc(1, true);
     if (m.y_stretched && m.dyc) {
         dyc_.alloc(n + 1, false);
         CFDNN_CUDA(cudaMemcpy(dyc_.p, m.dyc, (n + 1) * sizeof(double), cudaMemcpyHostToDevice));
@@ -261,6 +328,7 @@ void SstModel::advance(const Geom& g, const Vel& vel, double* k, double* omega, 
     sg.dx = dx_; sg.dy = dy_; sg.dx2 = dx_ * dx_; sg.dy2 = dy_ * dy_;
     sg.inv_2dx = 1.0 / (2.0 * dx_); sg.inv_2dy = 1.0 / (2.0 * dy_);
     const size_t oc = (size_t)plane * g.cp, ou = (size_t)plane * g.up, ov = (size_t)plane * g.vp;
+    if (kind_ == CFDNN_RANS_MIXING_LENGTH || kind_ == CFDNN_RANS_ALGEBRAIC_KOMEGA) return;      // algebraic: no transport
     KwParams kw;                                    // KOmegaConstants, include/turbulence_transport.hpp:61-72
     kw.nu = prm.nu; kw.sigma_k = 0.5; kw.sigma_omega = 0.5; kw.beta = 0.075; kw.beta_star = 0.09; kw.alpha = 5.0 / 9.0;
     kw.k_min = 1e-10; kw.k_max = 100.0; kw.omega_min = 1e-10; kw.omega_max = 1e8;
@@ -278,6 +346,18 @@ void SstModel::closure(const Geom& g, const Vel& vel, const double* k, const dou
                        cudaStream_t st) {
     const size_t oc = (size_t)plane * g.cp, ou = (size_t)plane * g.up, ov = (size_t)plane * g.vp;
     const dim3 blk(64, 4);
+    if (kind_ == CFDNN_RANS_MIXING_LENGTH) {
+        CFDNN_LAUNCH((k_rans_utau<true>), 1, 32, 0, st, g, prm.nu, 1.0 / (2.0 * dy_), dy_wall_, dyc_.p, vel.u + ou, utau_.p);
+        CFDNN_LAUNCH(k_mixing_length, dim3((g.Nx + 63) / 64, (g.Ny + 3) / 4), blk, 0, st, g, prm.nu, ml_kappa, ml_A_plus, ml_delta,
+                     1.0 / (2.0 * dx_), 1.0 / (2.0 * dy_), dyc_.p, vel.u + ou, vel.v + ov, wall_.p, utau_.p, nu_t + oc);
+        return;
+    }
+    if (kind_ == CFDNN_RANS_ALGEBRAIC_KOMEGA) {
+        CFDNN_LAUNCH((k_rans_utau<false>), 1, 32, 0, st, g, prm.nu, 1.0 / (2.0 * dy_), dy_wall_, dyc_.p, vel.u + ou, utau_.p);
+        CFDNN_LAUNCH(k_algebraic_komega, dim3((g.Nx + 63) / 64, (g.Ny + 3) / 4), blk, 0, st, g, prm.nu, 0.09, wall_.p, utau_.p,
+                     nu_t + oc);
+        return;
+    }
     if (kind_ == CFDNN_RANS_KOMEGA) {
         CFDNN_LAUNCH(k_kw_closure, dim3((g.Nx + 63) / 64, (g.Ny + 3) / 4), blk, 0, st, g, prm.nu, k + oc, omega + oc, nu_t + oc);
         return;

@@ -17,7 +17,7 @@ struct SstParams {                  // SSTConstants, include/turbulence_transpor
 
 class SstModel {
 public:
-    SstModel(const cfdnn_mesh_desc& m, double nu, int kind);      // kind: CFDNN_RANS_SST / CFDNN_RANS_KOMEGA
+    SstModel(const cfdnn_mesh_desc& m, double nu, int kind);      // kind: CFDNN_RANS_SST ... CFDNN_RANS_ALGEBRAIC_KOMEGA
     // SSTKOmegaTransport::advance_turbulence (CPU path, src/turbulence_transport.cpp:768-865): one in-place sweep over
     // the cells in (j, i) order + wall BCs of k and omega.  Fields are planes of the solver's cell layout.
     void advance(const Geom& g, const Vel& vel, double* k, double* omega, const double* nu_t, double dt, int plane,
@@ -25,10 +25,12 @@ public:
     // SSTKOmegaTransport::update -> SSTClosure::compute_nu_t (:259-313)
     void closure(const Geom& g, const Vel& vel, const double* k, const double* omega, double* nu_t, int plane, cudaStream_t st);
     SstParams prm;
+    double ml_kappa = 0.41, ml_A_plus = 26.0, ml_delta = 1.0;     // MixingLengthModel, include/turbulence_baseline.hpp:43-45
 
 private:
     int kind_;
-    double dx_, dy_;
+    double dx_, dy_, dy_wall_;
+    DevBuf<double> utau_;           // friction velocity of the algebraic models (device scalar)
     DevBuf<double> wall_;           // wall distance per row, Ny + 2 Ng (Mesh::wall_distance, src/mesh.cpp:6-12)
     DevBuf<double> dyc_;            // centre spacings of a stretched mesh (closure gradients), else empty
 };

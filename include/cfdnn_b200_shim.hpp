@@ -293,10 +293,12 @@ public:
                  : n == "Vreman" ? CFDNN_LES_VREMAN : n == "Sigma" ? CFDNN_LES_SIGMA : CFDNN_LES_NONE;
         }
         // the reference's SSTKOmegaTransport (default SST closure) on a 2-D mesh: native wavefront sweep + closure
-        // ... and its standard KOmegaTransport (default Boussinesq closure)
+        // ... its standard KOmegaTransport (default Boussinesq closure) and the two algebraic baselines
         sst_ = CFDNN_RANS_NONE;
         if (turb_ && !native_ && mesh_->is2D())
-            sst_ = turb_->name() == "SSTKOmega" ? CFDNN_RANS_SST : turb_->name() == "KOmega" ? CFDNN_RANS_KOMEGA : CFDNN_RANS_NONE;
+            sst_ = turb_->name() == "SSTKOmega" ? CFDNN_RANS_SST : turb_->name() == "KOmega" ? CFDNN_RANS_KOMEGA
+                 : turb_->name() == "MixingLength" ? CFDNN_RANS_MIXING_LENGTH       // kappa, A+ at their defaults (no getters)
+                 : turb_->name() == "AlgebraicKOmega" ? CFDNN_RANS_ALGEBRAIC_KOMEGA : CFDNN_RANS_NONE;
         if (turb_) turb_->set_nu(nu_);
         if (native_) native_->set_nu_t_max(nu_t_max_);
         attach_model();
@@ -535,6 +537,7 @@ private:
         check(cfdnn_solver_set_turbulence_model(h_, native_ ? native_->handle() : nullptr));
         check(cfdnn_solver_set_les_model(h_, les_, 0.0));
         check(cfdnn_solver_set_sst_model(h_, sst_));
+        if (sst_ == CFDNN_RANS_MIXING_LENGTH) check(cfdnn_solver_set_mixing_length_params(h_, 0.41, 26.0, turb_->delta()));
         check(cfdnn_solver_set_external_nu_t(h_, bridged() ? (turb_->uses_transport_equations() ? 2 : 1) : 0));
     }
     double* dev(int f) const {

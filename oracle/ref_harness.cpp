@@ -15,6 +15,7 @@
 //
 // usage: ref_harness key=value ...   (see parse below)
 
+#include "turbulence_baseline.hpp"
 #include "solver.hpp"
 #include "config.hpp"
 #include "mesh.hpp"
@@ -138,6 +139,7 @@ Config make_config(const Mesh& mesh) {
     else if (model == "nn_mlp") c.turb_model = TurbulenceModelType::NNMLP;
     else if (model == "sst") c.turb_model = TurbulenceModelType::SSTKOmega;
     else if (model == "komega") c.turb_model = TurbulenceModelType::KOmega;
+    else if (model == "baseline") c.turb_model = TurbulenceModelType::Baseline;
     else if (model == "smagorinsky") c.turb_model = TurbulenceModelType::Smagorinsky;
     else if (model == "wale") c.turb_model = TurbulenceModelType::WALE;
     else if (model == "vreman") c.turb_model = TurbulenceModelType::Vreman;
@@ -259,6 +261,12 @@ int run_step(bool bench) {
             model->set_nu(cfg.nu);
             solver.set_turbulence_model(std::move(model));
         }
+    }
+
+    if (arg_s("model", "none") == "algebraic_komega") {      // not reachable through the reference's factory
+        auto model = std::make_unique<AlgebraicKOmegaModel>();
+        model->set_nu(cfg.nu);
+        solver.set_turbulence_model(std::move(model));
     }
 
     init_velocity(mesh, solver);

@@ -1044,3 +1044,37 @@ def check_sst_rejects_3d(B):
         assert e.value.code == 1 and "two-dimensional" in str(e.value)
     finally:
         B.lib.cfdnn_solver_destroy(h)
+
+
+def check_step_with_algebraic_rans(B, oracle, model="baseline", stretched=False, ti="rk3", N=(32, 24, 1), nsteps=3, tol=1e-10):
+    """2-D channel steps with one of the reference's algebraic baselines attached (src/turbulence_baseline.cpp):
+    `baseline` = MixingLengthModel (nu_t under-relaxed with its previous value, so several steps matter),
+    `algebraic_komega` = AlgebraicKOmegaModel.  nu_t and the flow fields against the oracle."""
+    extra = dict(**CHANNEL_BOX) if stretched else dict(x1=4 * np.pi, y0=-1.0, y1=1.0)
+    case = ("chan2d_" + model, N, "PPWWPP", ti, "skew", 8, nsteps, "pchan", (1.0, 0, 0), extra)
+    nu = 1.0 / 180.0
+    u, v, w = step_init(N, "pchan")
+    with tempfile.TemporaryDirectory() as td:
+        pre = os.path.join(td, "in")
+        u.tofile(pre + "_u.f64"); v.tofile(pre + "_v.f64")
+        kw = {k_: v_ for k_, v_ in extra.items() if k_ in HARNESS_KEYS and k_ != "z1"}
+        meta = R.run_ref("step", Nx=N[0], Ny=N[1], Nz=1, bc="PPWWPP", ti=ti, scheme="skew", fixed=8, nsteps=nsteps, dt=0.002,
+                         nu=nu, init="file:" + pre, fx=1.0, call_initialize=1, model=model, out=os.path.join(td, "ref"), **kw)
+        ref = R.load_state(os.path.join(td, "ref_final"), *N)
+        arrs = R.load_mesh_arrays(os.path.join(td, "ref_mesh")) if stretched else None
+    h = make_solver(B, case, mesh_arrays=arrs, nu=nu, dt=0.002)
+    try:
+        B.check(B.lib.cfdnn_solver_set_sst_model(h, {"baseline": 3, "algebraic_komega": 4}[model]))
+        B.check(B.lib.cfdnn_solver_initialize(h))
+        res = [B.step(h) for _ in range(nsteps)]
+        got = B.state(h, *N)
+    finally:
+        B.lib.cfdnn_solver_destroy(h)
+    assert res == pytest.approx(meta["residuals"], rel=1e-8)
+    nut_ref = plane0_interior("nut", ref["nut"])
+    assert nut_ref.max() > 1e-3 * nu
+    assert np.abs(plane0_interior("nut", got["nut"]) - nut_ref).max() / nut_ref.max() <= tol
+    for n in ("u", "v", "p"):
+        a, b = plane0_interior(n, got[n]), plane0_interior(n, ref[n])
+        scale = np.abs(plane0_interior("u", ref["u"])).max() if n != "p" else max(np.abs(b).max(), 1e-300)
+        assert np.abs(a - b).max() / scale <= tol, (n, np.abs(a - b).max() / scale)

@@ -7,6 +7,7 @@
 #include "turbulence_nn_tbnn.hpp"
 #include "turbulence_les.hpp"
 #include "turbulence_transport.hpp"
+#include "turbulence_baseline.hpp"
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
@@ -268,6 +269,23 @@ int main(int argc, char** argv) {
             sst_k = std::max(rel_l2_plane0(bs.k().data(), rs.k().data(), pl), rel_l2_plane0(bs.omega().data(), rs.omega().data(), pl));
             sst_nut = rel_l2(bs.nu_t().data(), rs.nu_t().data());
             if (!(sst_u <= 1e-10 && sst_k <= 1e-10 && sst_nut <= 1e-9)) rc = 1;
+            // the mixing-length baseline (turb_model = baseline), same route
+            {
+                RANSSolver rm(m2, sc);
+                rm.set_velocity_bc(b2);
+                rm.set_body_force(1.0, 0.0);
+                rm.set_turbulence_model(std::make_unique<MixingLengthModel>());
+                rm.initialize(w0);
+                b200::RANSSolverB200 bm(m2, sc);
+                bm.set_velocity_bc(b2);
+                bm.set_body_force(1.0, 0.0);
+                bm.set_turbulence_model(std::make_unique<MixingLengthModel>());
+                bm.initialize(w0);
+                for (int s = 0; s < 3; ++s) { rm.step(); bm.step(); }
+                bm.sync_from_gpu();
+                if (!(rel_l2(bm.velocity().u_data(), rm.velocity().u_data()) <= 1e-10 &&
+                      rel_l2(bm.nu_t().data(), rm.nu_t().data()) <= 1e-9)) rc = 1;
+            }
             // the standard k-omega model, same route
             RANSSolver rk(m2, sc);
             rk.set_velocity_bc(b2);

@@ -335,5 +335,11 @@ def test_step_with_standard_k_omega_matches_reference(gpu, oracle, kind):
     cases.check_step_with_sst(gpu, oracle, stretched=kind == "stretched", ti="rk3", model="komega")
 
 
+@pytest.mark.parametrize("model,kind", [("baseline", "uniform"), ("baseline", "stretched"), ("algebraic_komega", "uniform"),
+                                        ("algebraic_komega", "stretched")])
+def test_step_with_algebraic_rans_baselines(gpu, oracle, model, kind):
+    cases.check_step_with_algebraic_rans(gpu, oracle, model=model, stretched=kind == "stretched")
+
+
 def test_sst_rejects_3d_meshes(gpu):
     cases.check_sst_rejects_3d(gpu)

@@ -242,5 +242,11 @@ def test_step_with_standard_k_omega_matches_reference(sim, oracle, kind):
     cases.check_step_with_sst(sim, oracle, stretched=kind == "stretched", ti="rk3", model="komega")
 
 
+@pytest.mark.parametrize("model,kind", [("baseline", "uniform"), ("baseline", "stretched"), ("algebraic_komega", "uniform"),
+                                        ("algebraic_komega", "stretched")])
+def test_step_with_algebraic_rans_baselines(sim, oracle, model, kind):
+    cases.check_step_with_algebraic_rans(sim, oracle, model=model, stretched=kind == "stretched")
+
+
 def test_sst_rejects_3d_meshes(sim):
     cases.check_sst_rejects_3d(sim)
