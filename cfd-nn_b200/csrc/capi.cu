@@ -267,6 +267,9 @@ int cfdnn_solver_set_sst_model(cfdnn_solver* s, int kind) { return guarded([&] {
 int cfdnn_solver_set_mixing_length_params(cfdnn_solver* s, double kappa, double A_plus, double delta) {
     return guarded([&] { s->impl.set_mixing_length_params(kappa, A_plus, delta); });
 }
+int cfdnn_solver_set_gep_params(cfdnn_solver* s, int variant, double model_nu) {
+    return guarded([&] { s->impl.set_gep_params(variant, model_nu); });
+}
 int cfdnn_solver_set_trip_forcing(cfdnn_solver* s, const cfdnn_trip_desc* desc) {
     return guarded([&] { s->impl.set_trip_forcing(desc); });
 }

@@ -739,6 +739,13 @@ void Solver::set_mixing_length_params(double kappa, double A_plus, double delta)
     sst_->ml_kappa = kappa; sst_->ml_A_plus = A_plus; sst_->ml_delta = delta;
 }
 
+void Solver::set_gep_params(int variant, double model_nu) {
+    if (!sst_) throw std::invalid_argument("set_gep_params: attach CFDNN_RANS_GEP first");
+    if (variant < 0 || variant > 2) throw std::invalid_argument("set_gep_params: variant must be 0, 1 or 2");
+    sst_->gep_variant = variant;
+    sst_->gep_nu = model_nu > 0.0 ? model_nu : 0.001;
+}
+
 void Solver::update_turbulence() {
     if (sst_) {
         // transport first, with the previous step's nu_t, then the closure (src/solver.cpp:1255-1306)

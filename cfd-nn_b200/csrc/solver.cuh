@@ -56,6 +56,7 @@ public:
     void set_external_nu_t(bool on, bool transport = false) { ext_nut_ = on; ext_transport_ = on && transport; }   // nu_t uploaded by the caller (bridged host model)
     bool fft_peer_to_peer() const { return fft_ && fft_active_ && fft_->peer_to_peer(); }
     void set_mixing_length_params(double kappa, double A_plus, double delta);
+    void set_gep_params(int variant, double model_nu);
     void set_sst_model(int kind);                            // native SST / standard k-omega transport + closure (2-D meshes)
     void set_trip_forcing(const cfdnn_trip_desc* d);         // trip-region forcing in the Euler predictor
     void apply_velocity_filter(double strength);             // explicit Laplacian filter between steps

@@ -293,11 +293,45 @@ __global__ void k_algebraic_komega(Geom g, double nu, double C_mu, const double*
     const double cap = 1000.0 * nu;
     nu_t[o] = (cap < r0) ? cap : r0;                                                    // std::min(., 1000 nu)
 }
+// TurbulenceGEP (src/turbulence_gep.cpp:21-83, gep_cell_kernel): an algebraic mixing-length form whose damping is one of
+// three gene-expression correction functions (variant 0 channel, 1 periodic hill, else plain van Driest squared);
+// y+ is approximated with |S| y / nu
+__global__ void k_gep_closure(Geom g, double nu, int variant, double inv_2dx, double inv_2dy, const double* __restrict__ dyc,
+                              const double* __restrict__ u, const double* __restrict__ v, const double* __restrict__ wall,
+                              double* __restrict__ nu_t) {
+    const int ix = blockIdx.x * blockDim.x + threadIdx.x, iy = blockIdx.y * blockDim.y + threadIdx.y;
+    if (ix >= g.Nx || iy >= g.Ny) return;
+    const int i = ix + g.Ng, j = iy + g.Ng;
+    const int o = j * g.cs + i, ou = j * g.us + i, ov = j * g.vs + i;
+    const double wy = dyc ? 1.0 / (dyc[j] + dyc[j + 1]) : inv_2dy;
+    const double dudx = (u[ou + 1] - u[ou - 1]) * inv_2dx, dudy = (u[ou + g.us] - u[ou - g.us]) * wy;
+    const double dvdx = (v[ov + 1] - v[ov - 1]) * inv_2dx, dvdy = (v[ov + g.vs] - v[ov - g.vs]) * wy;
+    const double Sxy = 0.5 * (dudy + dvdx), Oxy = 0.5 * (dudy - dvdx);
+    const double Smag = sqrt(2.0 * (dudx * dudx + dvdy * dvdy + 2.0 * Sxy * Sxy));
+    const double Omag = sqrt(2.0 * Oxy * Oxy);
+    const double yw = hi_of(wall[j], 1e-10);
+    const double y_plus = Smag * yw / (nu + 1e-20);
+    double f_damp = 1.0 - exp(-y_plus / 26.0);
+    f_damp = f_damp * f_damp;
+    double f = f_damp;
+    if (variant == 0) {
+        const double ratio = (Smag > 1e-10) ? Omag / Smag : 1.0;
+        f = f_damp * (1.0 / (1.0 + 0.1 * ratio * ratio));
+    } else if (variant == 1) {
+        const double ratio = (Smag > 1e-10) ? Omag / Smag : 1.0;
+        const double f_sep = 1.0 / (1.0 + 0.2 * ratio * ratio);
+        f = tanh(y_plus / 50.0) * f_sep;
+    }
+    const double l = 0.41 * yw * f;
+    double r = l * l * Smag;
+    r = hi_of(r, 0.0);
+    nu_t[o] = lo_of(r, 1000.0 * nu);
+}
 }  // namespace
 
 SstModel::SstModel(const cfdnn_mesh_desc& m, double nu, int kind) : kind_(kind), dx_(m.dx), dy_(m.dy) {
-    if (kind < CFDNN_RANS_SST || kind > CFDNN_RANS_ALGEBRAIC_KOMEGA)
-        throw std::invalid_argument("2-D RANS model: kind must be CFDNN_RANS_SST, _KOMEGA, _MIXING_LENGTH or _ALGEBRAIC_KOMEGA");
+    if (kind < CFDNN_RANS_SST || kind > CFDNN_RANS_GEP)
+        throw std::invalid_argument("2-D RANS model: kind must be CFDNN_RANS_SST, _KOMEGA, _MIXING_LENGTH, _ALGEBRAIC_KOMEGA or _GEP");
     require_device();
     if (m.Nz > 1)
         throw std::invalid_argument("SST k-omega: the reference model is two-dimensional (fields indexed (i, j)); 3-D meshes "
@@ -328,7 +362,7 @@ void SstModel::advance(const Geom& g, const Vel& vel, double* k, double* omega, 
     sg.dx = dx_; sg.dy = dy_; sg.dx2 = dx_ * dx_; sg.dy2 = dy_ * dy_;
     sg.inv_2dx = 1.0 / (2.0 * dx_); sg.inv_2dy = 1.0 / (2.0 * dy_);
     const size_t oc = (size_t)plane * g.cp, ou = (size_t)plane * g.up, ov = (size_t)plane * g.vp;
-    if (kind_ == CFDNN_RANS_MIXING_LENGTH || kind_ == CFDNN_RANS_ALGEBRAIC_KOMEGA) return;      // algebraic: no transport
+    if (kind_ != CFDNN_RANS_SST && kind_ != CFDNN_RANS_KOMEGA) return;                          // algebraic: no transport
     KwParams kw;                                    // KOmegaConstants, include/turbulence_transport.hpp:61-72
     kw.nu = prm.nu; kw.sigma_k = 0.5; kw.sigma_omega = 0.5; kw.beta = 0.075; kw.beta_star = 0.09; kw.alpha = 5.0 / 9.0;
     kw.k_min = 1e-10; kw.k_max = 100.0; kw.omega_min = 1e-10; kw.omega_max = 1e8;
@@ -350,6 +384,11 @@ void SstModel::closure(const Geom& g, const Vel& vel, const double* k, const dou
         CFDNN_LAUNCH((k_rans_utau<true>), 1, 32, 0, st, g, prm.nu, 1.0 / (2.0 * dy_), dy_wall_, dyc_.p, vel.u + ou, utau_.p);
         CFDNN_LAUNCH(k_mixing_length, dim3((g.Nx + 63) / 64, (g.Ny + 3) / 4), blk, 0, st, g, prm.nu, ml_kappa, ml_A_plus, ml_delta,
                      1.0 / (2.0 * dx_), 1.0 / (2.0 * dy_), dyc_.p, vel.u + ou, vel.v + ov, wall_.p, utau_.p, nu_t + oc);
+        return;
+    }
+    if (kind_ == CFDNN_RANS_GEP) {
+        CFDNN_LAUNCH(k_gep_closure, dim3((g.Nx + 63) / 64, (g.Ny + 3) / 4), blk, 0, st, g, gep_nu, gep_variant, 1.0 / (2.0 * dx_),
+                     1.0 / (2.0 * dy_), dyc_.p, vel.u + ou, vel.v + ov, wall_.p, nu_t + oc);
         return;
     }
     if (kind_ == CFDNN_RANS_ALGEBRAIC_KOMEGA) {

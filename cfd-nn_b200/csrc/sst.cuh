@@ -25,6 +25,8 @@ public:
     // SSTKOmegaTransport::update -> SSTClosure::compute_nu_t (:259-313)
     void closure(const Geom& g, const Vel& vel, const double* k, const double* omega, double* nu_t, int plane, cudaStream_t st);
     SstParams prm;
+    double gep_nu = 0.001;                                         // TurbulenceGEP's own nu_ (see cfdnn_solver_set_gep_params)
+    int gep_variant = 2;                                           // TurbulenceGEP::Variant (0 channel, 1 periodic hill, 2 simple = default)
     double ml_kappa = 0.41, ml_A_plus = 26.0, ml_delta = 1.0;     // MixingLengthModel, include/turbulence_baseline.hpp:43-45
 
 private:

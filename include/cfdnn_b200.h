@@ -234,13 +234,20 @@ int cfdnn_solver_set_external_nu_t(cfdnn_solver* s, int on);
  * CFDNN_RANS_KOMEGA for the standard Wilcox model KOmegaTransport with its Boussinesq closure (:202-228, 1012-1118;
  * no wall BC pass, face velocities advect), or CFDNN_RANS_NONE to detach. */
 enum { CFDNN_RANS_NONE = 0, CFDNN_RANS_SST = 1, CFDNN_RANS_KOMEGA = 2, CFDNN_RANS_MIXING_LENGTH = 3,
-       CFDNN_RANS_ALGEBRAIC_KOMEGA = 4 };
+       CFDNN_RANS_ALGEBRAIC_KOMEGA = 4, CFDNN_RANS_GEP = 5 };
 int cfdnn_solver_set_sst_model(cfdnn_solver* s, int kind);
 /* The algebraic 2-D baselines of src/turbulence_baseline.cpp through the same slot: CFDNN_RANS_MIXING_LENGTH =
  * MixingLengthModel (van Driest mixing length, nu_t under-relaxed with its previous value; `turb_model = baseline`,
  * :36-76, 330-402) and CFDNN_RANS_ALGEBRAIC_KOMEGA = AlgebraicKOmegaModel (:408-483).  Mixing-length constants
  * (set_kappa / set_A_plus / set_delta, include/turbulence_baseline.hpp:38-45; defaults 0.41, 26, 1): */
 int cfdnn_solver_set_mixing_length_params(cfdnn_solver* s, double kappa, double A_plus, double delta);
+/* CFDNN_RANS_GEP = TurbulenceGEP (Weatheritt-Sandberg algebraic model, src/turbulence_gep.cpp:21-83); variant as
+ * TurbulenceGEP::Variant (include/turbulence_gep.hpp:53-60: 0 WS2016_Channel, 1 WS2016_PeriodicHill, 2 Simple = default).
+ * model_nu: the viscosity inside the model.  TurbulenceGEP keeps its OWN nu_ = 0.001 and a non-virtual set_nu
+ * (include/turbulence_gep.hpp:48, 63), so the set_nu the solver / factory issue through a TurbulenceModel pointer never
+ * reaches it: a reference run evaluates the model with nu = 0.001 whatever Config::nu is.  model_nu <= 0 selects that
+ * effective value (parity with a reference run); pass the physical nu for a model whose concrete set_nu was called. */
+int cfdnn_solver_set_gep_params(cfdnn_solver* s, int variant, double model_nu);
 /* Trip-region forcing (Config::trip_*, include/config.hpp:202-210): a localized body force on v* (and w*) in the Euler
  * predictor while time < duration (src/solver.cpp:1724-1810, get_trip_time_ramp :939-950).  The tables are the ones
  * initialize_trip_forcing (:818-923) builds — x envelope on cell centres (Nx+2Ng), g(y) = y (1 - y^2) on the y faces

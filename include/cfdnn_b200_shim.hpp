@@ -299,6 +299,8 @@ public:
             sst_ = turb_->name() == "SSTKOmega" ? CFDNN_RANS_SST : turb_->name() == "KOmega" ? CFDNN_RANS_KOMEGA
                  : turb_->name() == "MixingLength" ? CFDNN_RANS_MIXING_LENGTH       // kappa, A+ at their defaults (no getters)
                  : turb_->name() == "AlgebraicKOmega" ? CFDNN_RANS_ALGEBRAIC_KOMEGA : CFDNN_RANS_NONE;
+        // TurbulenceGEP keeps its variant and its own nu private (no getters): it stays a bridged host model; the device
+        // kernel is available through cfdnn_solver_set_sst_model(CFDNN_RANS_GEP) + cfdnn_solver_set_gep_params
         if (turb_) turb_->set_nu(nu_);
         if (native_) native_->set_nu_t_max(nu_t_max_);
         attach_model();

@@ -15,6 +15,7 @@
 //
 // usage: ref_harness key=value ...   (see parse below)
 
+#include "turbulence_gep.hpp"
 #include "turbulence_baseline.hpp"
 #include "solver.hpp"
 #include "config.hpp"
@@ -140,6 +141,7 @@ Config make_config(const Mesh& mesh) {
     else if (model == "sst") c.turb_model = TurbulenceModelType::SSTKOmega;
     else if (model == "komega") c.turb_model = TurbulenceModelType::KOmega;
     else if (model == "baseline") c.turb_model = TurbulenceModelType::Baseline;
+    else if (model == "gep") c.turb_model = TurbulenceModelType::GEP;
     else if (model == "smagorinsky") c.turb_model = TurbulenceModelType::Smagorinsky;
     else if (model == "wale") c.turb_model = TurbulenceModelType::WALE;
     else if (model == "vreman") c.turb_model = TurbulenceModelType::Vreman;
@@ -258,6 +260,8 @@ int run_step(bool bench) {
         auto model = create_turbulence_model(cfg.turb_model, cfg.nn_weights_path, cfg.nn_scaling_path,
                                              cfg.pope_C1, cfg.pope_C2);
         if (model) {
+            if (auto* gp = dynamic_cast<TurbulenceGEP*>(model.get()))
+                gp->set_variant(static_cast<TurbulenceGEP::Variant>(arg_i("gep_variant", 2)));
             model->set_nu(cfg.nu);
             solver.set_turbulence_model(std::move(model));
         }

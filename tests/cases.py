@@ -1046,7 +1046,8 @@ def check_sst_rejects_3d(B):
         B.lib.cfdnn_solver_destroy(h)
 
 
-def check_step_with_algebraic_rans(B, oracle, model="baseline", stretched=False, ti="rk3", N=(32, 24, 1), nsteps=3, tol=1e-10):
+def check_step_with_algebraic_rans(B, oracle, model="baseline", stretched=False, ti="rk3", N=(32, 24, 1), nsteps=3, tol=1e-10,
+                                   gep_variant=2):
     """2-D channel steps with one of the reference's algebraic baselines attached (src/turbulence_baseline.cpp):
     `baseline` = MixingLengthModel (nu_t under-relaxed with its previous value, so several steps matter),
     `algebraic_komega` = AlgebraicKOmegaModel.  nu_t and the flow fields against the oracle."""
@@ -1059,12 +1060,15 @@ def check_step_with_algebraic_rans(B, oracle, model="baseline", stretched=False,
         u.tofile(pre + "_u.f64"); v.tofile(pre + "_v.f64")
         kw = {k_: v_ for k_, v_ in extra.items() if k_ in HARNESS_KEYS and k_ != "z1"}
         meta = R.run_ref("step", Nx=N[0], Ny=N[1], Nz=1, bc="PPWWPP", ti=ti, scheme="skew", fixed=8, nsteps=nsteps, dt=0.002,
-                         nu=nu, init="file:" + pre, fx=1.0, call_initialize=1, model=model, out=os.path.join(td, "ref"), **kw)
+                         nu=nu, init="file:" + pre, fx=1.0, call_initialize=1, model=model, gep_variant=gep_variant,
+                         out=os.path.join(td, "ref"), **kw)
         ref = R.load_state(os.path.join(td, "ref_final"), *N)
         arrs = R.load_mesh_arrays(os.path.join(td, "ref_mesh")) if stretched else None
     h = make_solver(B, case, mesh_arrays=arrs, nu=nu, dt=0.002)
     try:
-        B.check(B.lib.cfdnn_solver_set_sst_model(h, {"baseline": 3, "algebraic_komega": 4}[model]))
+        B.check(B.lib.cfdnn_solver_set_sst_model(h, {"baseline": 3, "algebraic_komega": 4, "gep": 5}[model]))
+        if model == "gep":
+            B.check(B.lib.cfdnn_solver_set_gep_params(h, gep_variant, -1.0))      # the reference run's effective model nu
         B.check(B.lib.cfdnn_solver_initialize(h))
         res = [B.step(h) for _ in range(nsteps)]
         got = B.state(h, *N)

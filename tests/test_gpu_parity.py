@@ -341,5 +341,10 @@ def test_step_with_algebraic_rans_baselines(gpu, oracle, model, kind):
     cases.check_step_with_algebraic_rans(gpu, oracle, model=model, stretched=kind == "stretched")
 
 
+@pytest.mark.parametrize("variant,kind", [(0, "uniform"), (1, "stretched"), (2, "uniform")])
+def test_step_with_gep_closure(gpu, oracle, variant, kind):
+    cases.check_step_with_algebraic_rans(gpu, oracle, model="gep", stretched=kind == "stretched", gep_variant=variant)
+
+
 def test_sst_rejects_3d_meshes(gpu):
     cases.check_sst_rejects_3d(gpu)

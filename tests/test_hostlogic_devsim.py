@@ -248,5 +248,10 @@ def test_step_with_algebraic_rans_baselines(sim, oracle, model, kind):
     cases.check_step_with_algebraic_rans(sim, oracle, model=model, stretched=kind == "stretched")
 
 
+@pytest.mark.parametrize("variant,kind", [(0, "uniform"), (1, "stretched"), (2, "uniform")])
+def test_step_with_gep_closure(sim, oracle, variant, kind):
+    cases.check_step_with_algebraic_rans(sim, oracle, model="gep", stretched=kind == "stretched", gep_variant=variant)
+
+
 def test_sst_rejects_3d_meshes(sim):
     cases.check_sst_rejects_3d(sim)
