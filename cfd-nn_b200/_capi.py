@@ -131,6 +131,7 @@ _SIGS = {
     "cfdnn_solver_set_sst_model": (C.c_int, [C.c_void_p, C.c_int]),
     "cfdnn_solver_set_mixing_length_params": (C.c_int, [C.c_void_p, C.c_double, C.c_double, C.c_double]),
     "cfdnn_solver_set_gep_params": (C.c_int, [C.c_void_p, C.c_int, C.c_double]),
+    "cfdnn_solver_set_pope_constants": (C.c_int, [C.c_void_p, C.c_double, C.c_double]),
     "cfdnn_solver_set_trip_forcing": (C.c_int, [C.c_void_p, C.POINTER(TripDesc)]),
     "cfdnn_solver_get_time": (C.c_int, [C.c_void_p, C.POINTER(C.c_double)]),
     "cfdnn_solver_set_time": (C.c_int, [C.c_void_p, C.c_double]),

@@ -270,6 +270,9 @@ int cfdnn_solver_set_mixing_length_params(cfdnn_solver* s, double kappa, double 
 int cfdnn_solver_set_gep_params(cfdnn_solver* s, int variant, double model_nu) {
     return guarded([&] { s->impl.set_gep_params(variant, model_nu); });
 }
+int cfdnn_solver_set_pope_constants(cfdnn_solver* s, double C1, double C2) {
+    return guarded([&] { s->impl.set_pope_constants(C1, C2); });
+}
 int cfdnn_solver_set_trip_forcing(cfdnn_solver* s, const cfdnn_trip_desc* desc) {
     return guarded([&] { s->impl.set_trip_forcing(desc); });
 }

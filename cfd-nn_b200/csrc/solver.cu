@@ -746,11 +746,16 @@ void Solver::set_gep_params(int variant, double model_nu) {
     sst_->gep_nu = model_nu > 0.0 ? model_nu : 0.001;
 }
 
+void Solver::set_pope_constants(double C1, double C2) {
+    if (!sst_) throw std::invalid_argument("set_pope_constants: attach CFDNN_RANS_EARSM_POPE first");
+    sst_->pope_C1 = C1; sst_->pope_C2 = C2;
+}
+
 void Solver::update_turbulence() {
     if (sst_) {
         // transport first, with the previous step's nu_t, then the closure (src/solver.cpp:1255-1306)
         sst_->advance(g_, vel_, k_, omega_, nut_, dt_, g_.Ng, st_);
-        sst_->closure(g_, vel_, k_, omega_, nut_, g_.Ng, st_);
+        sst_->closure(g_, vel_, k_, omega_, nut_, tau_[0], tau_[1], tau_[2], g_.Ng, st_);
         return;
     }
     if (les_model_) {                                // LESModel::update: nu_t = nu_sgs (src/turbulence_les.cpp:292-335)

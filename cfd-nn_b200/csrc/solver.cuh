@@ -57,6 +57,7 @@ public:
     bool fft_peer_to_peer() const { return fft_ && fft_active_ && fft_->peer_to_peer(); }
     void set_mixing_length_params(double kappa, double A_plus, double delta);
     void set_gep_params(int variant, double model_nu);
+    void set_pope_constants(double C1, double C2);
     void set_sst_model(int kind);                            // native SST / standard k-omega transport + closure (2-D meshes)
     void set_trip_forcing(const cfdnn_trip_desc* d);         // trip-region forcing in the Euler predictor
     void apply_velocity_filter(double strength);             // explicit Laplacian filter between steps
@@ -65,7 +66,8 @@ public:
     void set_les_model(int model, double constant);          // static LES SGS closure evaluated at the top of step()
     bool has_model() const { return nn_ != nullptr || ext_nut_ || les_model_ != 0 || sst_ != nullptr; }
     bool transport_model() const {               // uses_transport_equations(): SST / standard k-omega, not the algebraic models
-        return ext_transport_ || (sst_ != nullptr && (sst_kind_ == CFDNN_RANS_SST || sst_kind_ == CFDNN_RANS_KOMEGA));
+        return ext_transport_ || (sst_ != nullptr && (sst_kind_ == CFDNN_RANS_SST || sst_kind_ == CFDNN_RANS_KOMEGA ||
+                                                      sst_kind_ >= CFDNN_RANS_EARSM_WJ));
     }
     double* view_ptr(int field, size_t* n) const;           // device twin of a field (cfdnn_solver_device_ptr)
     void comm_init(Comm* c);

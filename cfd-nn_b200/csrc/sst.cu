@@ -327,11 +327,137 @@ __global__ void k_gep_closure(Geom g, double nu, int variant, double inv_2dx, do
     r = hi_of(r, 0.0);
     nu_t[o] = lo_of(r, 1000.0 * nu);
 }
+// ---- explicit algebraic Reynolds-stress closures on the SST transport (SSTWithEARSM, src/turbulence_earsm.cpp:205-346,
+// 349-529): b_ij = sum_n G_n(eta, zeta) T^n_ij on the TBNN tensor basis (TensorBasis::compute, src/features.cpp:192-292,
+// built from the stretched-aware MAC gradients and the RAW k, omega like FeatureComputer::compute_tbnn_features :361-396),
+// the nonlinear terms faded in with the turbulence Reynolds number, nu_t recovered from b_xy.
+// VARIANT 0: Wallin-Johansson 2000, 1: Gatski-Speziale 1993, 2: Pope 1975 quadratic.
+struct EarsmParams {
+    double nu, k_min, omega_min, Re_t_center, Re_t_width;     // EARSMClosure thresholds (include/turbulence_earsm.hpp:84-92)
+    double pope_C1, pope_C2;                                  // PopeQuadraticEARSM (:255)
+};
+
+__device__ __forceinline__ double clampd(double v, double lo, double hi) {       // std::max(lo, std::min(v, hi))
+    const double m = (hi < v) ? hi : v;
+    return (lo < m) ? m : lo;
+}
+__device__ __forceinline__ bool finite_d(double x) { return x - x == 0.0; }
+
+template <int VARIANT>
+__device__ __forceinline__ void earsm_G(const EarsmParams& p, double eta, double zeta, double G[4]) {
+    if (VARIANT == 0) {                                        // WallinJohanssonEARSM::compute_G / solve_for_N (:349-449)
+        const double C2 = 0.36, C3 = 1.25, C4 = 0.4, C5 = 1.88;                      // WJConstants (:51-66)
+        const double A1 = 4.0 / 5.0 - C2 / 2.0, A2 = 2.0 - C4 / 2.0, A3 = 2.0 - C3 / 2.0, A4 = 2.0 * C5 - 1.0;
+        const double II_S = eta * eta, II_O = -zeta * zeta;
+        double den = 1.0 + A3 * II_S + A4 * fabs(II_O);
+        const double dm = (fabs(den) < 0.1) ? 0.1 : fabs(den);
+        den = dm * (den >= 0 ? 1.0 : -1.0);
+        const double N = clampd(-A1 / den, -10.0, 10.0);
+        double d2 = A1 + N;
+        if (fabs(d2) < 0.01) d2 = 0.01 * (d2 >= 0 ? 1.0 : -1.0);
+        G[0] = -N / d2;
+        G[1] = (fabs(II_O) > 1e-10) ? A2 * N * N / (d2 * d2) : 0.0;
+        G[2] = (II_S > 1e-10) ? A3 * N / d2 : 0.0;
+        G[3] = 0.0;
+        for (int n = 0; n < 4; ++n) G[n] = clampd(G[n], -10.0, 10.0);
+    } else if (VARIANT == 1) {                                 // GatskiSpezialeEARSM::compute_G (:452-494)
+        const double C_mu0 = 0.09, C1 = 1.8, C2 = 0.6, eta_max = 10.0;               // GSConstants (:69-79)
+        const double reg = 1.0 + (eta * eta) / (eta_max * eta_max);
+        const double Ce = C_mu0 / reg;
+        double rot = 1.0;
+        if (eta > 1e-10) { const double ratio = zeta / eta; rot = 1.0 / (1.0 + 0.1 * ratio * ratio); }
+        G[0] = -Ce * rot; G[1] = C1 * Ce * Ce; G[2] = C2 * Ce; G[3] = 0.0;
+        for (int n = 0; n < 4; ++n) G[n] = clampd(G[n], -5.0, 5.0);
+    } else {                                                   // PopeQuadraticEARSM::compute_G (:497-528)
+        const double es = (finite_d(eta) && eta < 100.0) ? eta : 100.0;
+        const double Ce = 0.09 / (1.0 + 0.01 * es * es);
+        G[0] = -Ce; G[1] = p.pope_C2 * es; G[2] = p.pope_C1 * es; G[3] = 0.0;
+    }
+}
+
+template <int VARIANT>
+__global__ void k_earsm_closure(Geom g, EarsmParams p, double inv_2dx, double inv_2dy, const double* __restrict__ dyc,
+                                const double* __restrict__ u, const double* __restrict__ v, const double* __restrict__ k,
+                                const double* __restrict__ omega, double* __restrict__ nu_t, double* __restrict__ txx,
+                                double* __restrict__ txy, double* __restrict__ tyy) {
+    const int ix = blockIdx.x * blockDim.x + threadIdx.x, iy = blockIdx.y * blockDim.y + threadIdx.y;
+    if (ix >= g.Nx || iy >= g.Ny) return;
+    const int i = ix + g.Ng, j = iy + g.Ng;
+    const int o = j * g.cs + i, ou = j * g.us + i, ov = j * g.vs + i;
+    const double dux = u[ou + 1] - u[ou - 1], duy = u[ou + g.us] - u[ou - g.us];
+    const double dvx = v[ov + 1] - v[ov - 1], dvy = v[ov + g.vs] - v[ov - g.vs];
+    // tensor basis: stretched-aware gradients, raw k / omega (TensorBasis::compute)
+    double T[3][3];
+    {
+        const double wy = dyc ? 1.0 / (dyc[j] + dyc[j + 1]) : inv_2dy;
+        const double dudx = dux * inv_2dx, dudy = duy * wy, dvdx = dvx * inv_2dx, dvdy = dvy * wy;
+        const double kv = k[o], eps = 0.09 * kv * omega[o];
+        const double tau = ((kv < 1e-10) ? 1e-10 : kv) / ((eps < 1e-20) ? 1e-20 : eps);
+        const double Sxx = dudx * tau, Syy = dvdy * tau, Sxy = (0.5 * (dudy + dvdx)) * tau, Oxy = (0.5 * (dudy - dvdx)) * tau;
+        T[0][0] = Sxx; T[0][1] = Sxy; T[0][2] = Syy;
+        T[1][0] = -2.0 * Sxy * Oxy; T[1][1] = (Sxx - Syy) * Oxy; T[1][2] = 2.0 * Sxy * Oxy;
+        const double S2xx = Sxx * Sxx + Sxy * Sxy, S2yy = Sxy * Sxy + Syy * Syy, S2xy = Sxy * (Sxx + Syy);
+        const double trS2 = S2xx + S2yy;
+        T[2][0] = S2xx - 0.5 * trS2; T[2][1] = S2xy; T[2][2] = S2yy - 0.5 * trS2;
+    }
+    const double kl = (p.k_min < k[o]) ? k[o] : p.k_min;                 // std::max(k_min, k)
+    const double ol = (p.omega_min < omega[o]) ? omega[o] : p.omega_min;
+    double Re_t;
+    {                                                                    // safe_divide(k, nu omega, OMEGA_FLOOR nu)
+        const double den = p.nu * ol, fl = 1e-10 * p.nu;
+        const double mag = (fabs(den) < fl) ? fl : fabs(den);
+        Re_t = kl / ((den < 0.0) ? -mag : mag);
+    }
+    const double alpha = 0.5 * (1.0 + tanh((Re_t - p.Re_t_center) / p.Re_t_width));
+    double tau;
+    {                                                                    // safe_divide(k, eps, K_FLOOR)
+        const double eps = 0.09 * kl * ol;
+        const double mag = (fabs(eps) < 1e-10) ? 1e-10 : fabs(eps);
+        tau = kl / ((eps < 0.0) ? -mag : mag);
+    }
+    // uniform-spacing gradients for the invariants (:252-258)
+    const double dudx = dux * inv_2dx, dudy = duy * inv_2dy, dvdx = dvx * inv_2dx, dvdy = dvy * inv_2dy;
+    const double Sxy = 0.5 * (dudy + dvdx), Oxy = 0.5 * (dudy - dvdx);
+    const double S_mag = sqrt(dudx * dudx + dvdy * dvdy + 2.0 * Sxy * Sxy);
+    const double O_mag = sqrt(2.0 * Oxy * Oxy);
+    double eta = tau * S_mag, zeta = tau * O_mag;
+    if (!finite_d(eta)) eta = 100.0;
+    if (!finite_d(zeta)) zeta = 100.0;
+    double G[4];
+    earsm_G<VARIANT>(p, eta, zeta, G);
+    for (int n = 0; n < 4; ++n) if (!finite_d(G[n])) G[n] = 0.0;
+    G[1] *= alpha; G[2] *= alpha; G[3] *= alpha;
+    double b_xx = 0.0, b_xy = 0.0, b_yy = 0.0;
+    for (int n = 0; n < 3; ++n) { b_xx += G[n] * T[n][0]; b_xy += G[n] * T[n][1]; b_yy += G[n] * T[n][2]; }
+    b_xx += G[3] * 0.0; b_xy += G[3] * 0.0; b_yy += G[3] * 0.0;          // T4 = 0 in 2-D (keeps a NaN G[3] visible)
+    if (!finite_d(b_xx)) b_xx = 0.0;
+    if (!finite_d(b_xy)) b_xy = 0.0;
+    if (!finite_d(b_yy)) b_yy = 0.0;
+    if (txx) {                                                           // anisotropy_to_reynolds_stress :310-326
+        const double ks = (kl < 0.0) ? 0.0 : kl;
+        txx[o] = 2.0 * ks * (b_xx + 1.0 / 3.0);
+        txy[o] = 2.0 * ks * b_xy;
+        tyy[o] = 2.0 * ks * (b_yy + 1.0 / 3.0);
+    }
+    double r = 0.0;
+    if (fabs(Sxy) > 1e-10) {
+        const double mag = (fabs(Sxy) < 1e-10) ? 1e-10 : fabs(Sxy);
+        r = fabs((-b_xy * kl) / ((Sxy < 0.0) ? -mag : mag));
+    } else if (S_mag > 1e-10) {
+        const double b_mag = sqrt(b_xx * b_xx + 2.0 * b_xy * b_xy + b_yy * b_yy);
+        r = (kl * b_mag) / ((S_mag < 1e-10) ? 1e-10 : S_mag);
+    }
+    r = (0.0 < r) ? r : 0.0;
+    const double cap = 100.0 * p.nu;
+    r = (cap < r) ? cap : r;
+    if (!finite_d(r)) r = 0.0;
+    nu_t[o] = r;
+}
 }  // namespace
 
 SstModel::SstModel(const cfdnn_mesh_desc& m, double nu, int kind) : kind_(kind), dx_(m.dx), dy_(m.dy) {
-    if (kind < CFDNN_RANS_SST || kind > CFDNN_RANS_GEP)
-        throw std::invalid_argument("2-D RANS model: kind must be CFDNN_RANS_SST, _KOMEGA, _MIXING_LENGTH, _ALGEBRAIC_KOMEGA or _GEP");
+    if (kind < CFDNN_RANS_SST || kind > CFDNN_RANS_EARSM_POPE)
+        throw std::invalid_argument("2-D RANS model: kind must be one of CFDNN_RANS_SST ... CFDNN_RANS_EARSM_POPE");
     require_device();
     if (m.Nz > 1)
         throw std::invalid_argument("SST k-omega: the reference model is two-dimensional (fields indexed (i, j)); 3-D meshes "
@@ -362,11 +488,12 @@ void SstModel::advance(const Geom& g, const Vel& vel, double* k, double* omega, 
     sg.dx = dx_; sg.dy = dy_; sg.dx2 = dx_ * dx_; sg.dy2 = dy_ * dy_;
     sg.inv_2dx = 1.0 / (2.0 * dx_); sg.inv_2dy = 1.0 / (2.0 * dy_);
     const size_t oc = (size_t)plane * g.cp, ou = (size_t)plane * g.up, ov = (size_t)plane * g.vp;
-    if (kind_ != CFDNN_RANS_SST && kind_ != CFDNN_RANS_KOMEGA) return;                          // algebraic: no transport
+    const bool earsm = kind_ >= CFDNN_RANS_EARSM_WJ && kind_ <= CFDNN_RANS_EARSM_POPE;         // SSTWithEARSM: SST transport
+    if (kind_ != CFDNN_RANS_SST && kind_ != CFDNN_RANS_KOMEGA && !earsm) return;                // algebraic: no transport
     KwParams kw;                                    // KOmegaConstants, include/turbulence_transport.hpp:61-72
     kw.nu = prm.nu; kw.sigma_k = 0.5; kw.sigma_omega = 0.5; kw.beta = 0.075; kw.beta_star = 0.09; kw.alpha = 5.0 / 9.0;
     kw.k_min = 1e-10; kw.k_max = 100.0; kw.omega_min = 1e-10; kw.omega_max = 1e8;
-    if (kind_ == CFDNN_RANS_SST) {
+    if (kind_ == CFDNN_RANS_SST || earsm) {
         CFDNN_LAUNCH_COOP((k_sst_sweep<true>), 1, 1024, 0, st, g, prm, kw, sg, dt, vel.u + ou, vel.v + ov, k + oc, omega + oc,
                           nu_t + oc, wall_.p, dyc_.p);
         CFDNN_LAUNCH(k_sst_wall_bc, (g.Nx + 2 * g.Ng + 127) / 128, 128, 0, st, g, prm, k + oc, omega + oc, wall_.p);
@@ -376,10 +503,24 @@ void SstModel::advance(const Geom& g, const Vel& vel, double* k, double* omega, 
     }
 }
 
-void SstModel::closure(const Geom& g, const Vel& vel, const double* k, const double* omega, double* nu_t, int plane,
-                       cudaStream_t st) {
+void SstModel::closure(const Geom& g, const Vel& vel, const double* k, const double* omega, double* nu_t, double* txx,
+                       double* txy, double* tyy, int plane, cudaStream_t st) {
     const size_t oc = (size_t)plane * g.cp, ou = (size_t)plane * g.up, ov = (size_t)plane * g.vp;
     const dim3 blk(64, 4);
+    if (kind_ >= CFDNN_RANS_EARSM_WJ && kind_ <= CFDNN_RANS_EARSM_POPE) {
+        EarsmParams ep;
+        ep.nu = prm.nu; ep.k_min = 1e-10; ep.omega_min = 1e-10; ep.Re_t_center = 10.0; ep.Re_t_width = 5.0;
+        ep.pope_C1 = pope_C1; ep.pope_C2 = pope_C2;
+        const dim3 grd((g.Nx + 63) / 64, (g.Ny + 3) / 4);
+#define CFDNN_EARSM(V) CFDNN_LAUNCH((k_earsm_closure<V>), grd, blk, 0, st, g, ep, 1.0 / (2.0 * dx_), 1.0 / (2.0 * dy_), dyc_.p, \
+                                    vel.u + ou, vel.v + ov, k + oc, omega + oc, nu_t + oc, txx ? txx + oc : nullptr,             \
+                                    txy ? txy + oc : nullptr, tyy ? tyy + oc : nullptr)
+        if (kind_ == CFDNN_RANS_EARSM_WJ) CFDNN_EARSM(0);
+        else if (kind_ == CFDNN_RANS_EARSM_GS) CFDNN_EARSM(1);
+        else CFDNN_EARSM(2);
+#undef CFDNN_EARSM
+        return;
+    }
     if (kind_ == CFDNN_RANS_MIXING_LENGTH) {
         CFDNN_LAUNCH((k_rans_utau<true>), 1, 32, 0, st, g, prm.nu, 1.0 / (2.0 * dy_), dy_wall_, dyc_.p, vel.u + ou, utau_.p);
         CFDNN_LAUNCH(k_mixing_length, dim3((g.Nx + 63) / 64, (g.Ny + 3) / 4), blk, 0, st, g, prm.nu, ml_kappa, ml_A_plus, ml_delta,

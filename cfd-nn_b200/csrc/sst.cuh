@@ -23,8 +23,11 @@ public:
     void advance(const Geom& g, const Vel& vel, double* k, double* omega, const double* nu_t, double dt, int plane,
                  cudaStream_t st);
     // SSTKOmegaTransport::update -> SSTClosure::compute_nu_t (:259-313)
-    void closure(const Geom& g, const Vel& vel, const double* k, const double* omega, double* nu_t, int plane, cudaStream_t st);
+    // (the EARSM kinds also write the Reynolds stresses when txx / txy / tyy are given)
+    void closure(const Geom& g, const Vel& vel, const double* k, const double* omega, double* nu_t, double* txx, double* txy,
+                 double* tyy, int plane, cudaStream_t st);
     SstParams prm;
+    double pope_C1 = 0.1, pope_C2 = 0.1;                           // PopeQuadraticEARSM defaults (include/turbulence_earsm.hpp:255)
     double gep_nu = 0.001;                                         // TurbulenceGEP's own nu_ (see cfdnn_solver_set_gep_params)
     int gep_variant = 2;                                           // TurbulenceGEP::Variant (0 channel, 1 periodic hill, 2 simple = default)
     double ml_kappa = 0.41, ml_A_plus = 26.0, ml_delta = 1.0;     // MixingLengthModel, include/turbulence_baseline.hpp:43-45

@@ -234,7 +234,11 @@ int cfdnn_solver_set_external_nu_t(cfdnn_solver* s, int on);
  * CFDNN_RANS_KOMEGA for the standard Wilcox model KOmegaTransport with its Boussinesq closure (:202-228, 1012-1118;
  * no wall BC pass, face velocities advect), or CFDNN_RANS_NONE to detach. */
 enum { CFDNN_RANS_NONE = 0, CFDNN_RANS_SST = 1, CFDNN_RANS_KOMEGA = 2, CFDNN_RANS_MIXING_LENGTH = 3,
-       CFDNN_RANS_ALGEBRAIC_KOMEGA = 4, CFDNN_RANS_GEP = 5 };
+       CFDNN_RANS_ALGEBRAIC_KOMEGA = 4, CFDNN_RANS_GEP = 5,
+       /* SSTWithEARSM (src/turbulence_earsm.cpp:205-346, 349-690): SST transport + an explicit algebraic Reynolds-stress
+        * closure on the TBNN tensor basis — Wallin-Johansson 2000, Gatski-Speziale 1993, Pope 1975 quadratic
+        * (turb_model = earsm_wj / earsm_gs / earsm_pope); nu_t and tau_ij (CFDNN_F_TAU_*) are written */
+       CFDNN_RANS_EARSM_WJ = 6, CFDNN_RANS_EARSM_GS = 7, CFDNN_RANS_EARSM_POPE = 8 };
 int cfdnn_solver_set_sst_model(cfdnn_solver* s, int kind);
 /* The algebraic 2-D baselines of src/turbulence_baseline.cpp through the same slot: CFDNN_RANS_MIXING_LENGTH =
  * MixingLengthModel (van Driest mixing length, nu_t under-relaxed with its previous value; `turb_model = baseline`,
@@ -248,6 +252,8 @@ int cfdnn_solver_set_mixing_length_params(cfdnn_solver* s, double kappa, double 
  * reaches it: a reference run evaluates the model with nu = 0.001 whatever Config::nu is.  model_nu <= 0 selects that
  * effective value (parity with a reference run); pass the physical nu for a model whose concrete set_nu was called. */
 int cfdnn_solver_set_gep_params(cfdnn_solver* s, int variant, double model_nu);
+/* SSTWithEARSM::set_pope_constants (Config::pope_C1 / pope_C2, include/config.hpp:122-123; defaults 0.1, 0.1) */
+int cfdnn_solver_set_pope_constants(cfdnn_solver* s, double C1, double C2);
 /* Trip-region forcing (Config::trip_*, include/config.hpp:202-210): a localized body force on v* (and w*) in the Euler
  * predictor while time < duration (src/solver.cpp:1724-1810, get_trip_time_ramp :939-950).  The tables are the ones
  * initialize_trip_forcing (:818-923) builds — x envelope on cell centres (Nx+2Ng), g(y) = y (1 - y^2) on the y faces

@@ -298,7 +298,9 @@ public:
         if (turb_ && !native_ && mesh_->is2D())
             sst_ = turb_->name() == "SSTKOmega" ? CFDNN_RANS_SST : turb_->name() == "KOmega" ? CFDNN_RANS_KOMEGA
                  : turb_->name() == "MixingLength" ? CFDNN_RANS_MIXING_LENGTH       // kappa, A+ at their defaults (no getters)
-                 : turb_->name() == "AlgebraicKOmega" ? CFDNN_RANS_ALGEBRAIC_KOMEGA : CFDNN_RANS_NONE;
+                 : turb_->name() == "AlgebraicKOmega" ? CFDNN_RANS_ALGEBRAIC_KOMEGA
+                 : turb_->name() == "SST+WJ-EARSM" ? CFDNN_RANS_EARSM_WJ : turb_->name() == "SST+GS-EARSM" ? CFDNN_RANS_EARSM_GS
+                 : turb_->name() == "SST+Pope-Quadratic" ? CFDNN_RANS_EARSM_POPE : CFDNN_RANS_NONE;
         // TurbulenceGEP keeps its variant and its own nu private (no getters): it stays a bridged host model; the device
         // kernel is available through cfdnn_solver_set_sst_model(CFDNN_RANS_GEP) + cfdnn_solver_set_gep_params
         if (turb_) turb_->set_nu(nu_);
@@ -540,6 +542,8 @@ private:
         check(cfdnn_solver_set_les_model(h_, les_, 0.0));
         check(cfdnn_solver_set_sst_model(h_, sst_));
         if (sst_ == CFDNN_RANS_MIXING_LENGTH) check(cfdnn_solver_set_mixing_length_params(h_, 0.41, 26.0, turb_->delta()));
+        // the Pope constants as the reference's factory sets them (create_turbulence_model, src/turbulence_baseline.cpp:542)
+        if (sst_ == CFDNN_RANS_EARSM_POPE) check(cfdnn_solver_set_pope_constants(h_, config_.pope_C1, config_.pope_C2));
         check(cfdnn_solver_set_external_nu_t(h_, bridged() ? (turb_->uses_transport_equations() ? 2 : 1) : 0));
     }
     double* dev(int f) const {

@@ -142,6 +142,9 @@ Config make_config(const Mesh& mesh) {
     else if (model == "komega") c.turb_model = TurbulenceModelType::KOmega;
     else if (model == "baseline") c.turb_model = TurbulenceModelType::Baseline;
     else if (model == "gep") c.turb_model = TurbulenceModelType::GEP;
+    else if (model == "earsm_wj") c.turb_model = TurbulenceModelType::EARSM_WJ;
+    else if (model == "earsm_gs") c.turb_model = TurbulenceModelType::EARSM_GS;
+    else if (model == "earsm_pope") c.turb_model = TurbulenceModelType::EARSM_Pope;
     else if (model == "smagorinsky") c.turb_model = TurbulenceModelType::Smagorinsky;
     else if (model == "wale") c.turb_model = TurbulenceModelType::WALE;
     else if (model == "vreman") c.turb_model = TurbulenceModelType::Vreman;

@@ -1009,7 +1009,7 @@ def check_step_with_sst(B, oracle, stretched=False, ti="rk3", N=(32, 24, 1), nst
     h = make_solver(B, case, mesh_arrays=arrs, nu=nu, dt=0.002)
     try:
         B.upload(h, "k", ref0["k"]); B.upload(h, "omega", ref0["omega"])
-        B.check(B.lib.cfdnn_solver_set_sst_model(h, {"sst": 1, "komega": 2}[model]))
+        B.check(B.lib.cfdnn_solver_set_sst_model(h, {"sst": 1, "komega": 2, "earsm_wj": 6, "earsm_gs": 7, "earsm_pope": 8}[model]))
         B.check(B.lib.cfdnn_solver_initialize(h))
         res = [B.step(h) for _ in range(nsteps)]
         got = B.state(h, *N)

@@ -8,6 +8,7 @@
 #include "turbulence_les.hpp"
 #include "turbulence_transport.hpp"
 #include "turbulence_baseline.hpp"
+#include "turbulence_earsm.hpp"
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
@@ -285,6 +286,23 @@ int main(int argc, char** argv) {
                 bm.sync_from_gpu();
                 if (!(rel_l2(bm.velocity().u_data(), rm.velocity().u_data()) <= 1e-10 &&
                       rel_l2(bm.nu_t().data(), rm.nu_t().data()) <= 1e-9)) rc = 1;
+            }
+            // SST + Wallin-Johansson EARSM, same route (the reference's SSTWithEARSM object)
+            {
+                RANSSolver re(m2, sc);
+                re.set_velocity_bc(b2);
+                re.set_body_force(1.0, 0.0);
+                re.set_turbulence_model(std::make_unique<SSTWithEARSM>(EARSMType::WallinJohansson2000));
+                re.initialize(w0);
+                b200::RANSSolverB200 be(m2, sc);
+                be.set_velocity_bc(b2);
+                be.set_body_force(1.0, 0.0);
+                be.set_turbulence_model(std::make_unique<SSTWithEARSM>(EARSMType::WallinJohansson2000));
+                be.initialize(w0);
+                for (int s = 0; s < 2; ++s) { re.step(); be.step(); }
+                be.sync_from_gpu();
+                if (!(rel_l2(be.velocity().u_data(), re.velocity().u_data()) <= 1e-10 &&
+                      rel_l2(be.nu_t().data(), re.nu_t().data()) <= 1e-9)) rc = 1;
             }
             // the standard k-omega model, same route
             RANSSolver rk(m2, sc);

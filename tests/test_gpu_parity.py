@@ -346,5 +346,11 @@ def test_step_with_gep_closure(gpu, oracle, variant, kind):
     cases.check_step_with_algebraic_rans(gpu, oracle, model="gep", stretched=kind == "stretched", gep_variant=variant)
 
 
+@pytest.mark.parametrize("model,kind", [("earsm_wj", "uniform"), ("earsm_gs", "stretched"), ("earsm_pope", "uniform"),
+                                        ("earsm_wj", "stretched")])
+def test_step_with_sst_earsm_closures(gpu, oracle, model, kind):
+    cases.check_step_with_sst(gpu, oracle, stretched=kind == "stretched", ti="rk3", model=model)
+
+
 def test_sst_rejects_3d_meshes(gpu):
     cases.check_sst_rejects_3d(gpu)

@@ -255,3 +255,8 @@ def test_step_with_gep_closure(sim, oracle, variant, kind):
 
 def test_sst_rejects_3d_meshes(sim):
     cases.check_sst_rejects_3d(sim)
+
+
+@pytest.mark.parametrize("model,kind", [("earsm_wj", "uniform"), ("earsm_gs", "stretched"), ("earsm_pope", "uniform")])
+def test_step_with_sst_earsm_closures(sim, oracle, model, kind):
+    cases.check_step_with_sst(sim, oracle, stretched=kind == "stretched", ti="rk3", model=model)
