@@ -99,7 +99,13 @@ Solver::Solver(const cfdnn_mesh_desc& m, const cfdnn_config& c) : mesh_(m), cfg_
     CFDNN_CUDA(cudaEventCreate(&ev0_));
     CFDNN_CUDA(cudaEventCreate(&ev1_));
 
-    mg_ = std::make_unique<Multigrid>(m);
+    {
+        // A y-stretched slab with the FFT solver requested: the semi-coarsening multigrid has no slab variant and is never
+        // called there (comm_init / set_velocity_bc enforce it); it is built on the local box so the handle stays complete.
+        cfdnn_mesh_desc mm = m;
+        if (c.poisson_solver == CFDNN_POISSON_FFT && m.y_stretched && m.Nz_global > m.Nz) { mm.Nz_global = m.Nz; mm.k_offset = 0; }
+        mg_ = std::make_unique<Multigrid>(mm);
+    }
     if (is2d_) mg_->set_2d_plane(Ng, /*dup=*/true);
     if (c.poisson_solver == CFDNN_POISSON_FFT) {                 // selection: src/solver.cpp:432-447
         if (is2d_) throw std::invalid_argument("Solver: poisson_solver = FFT needs a 3-D mesh (the 2-D variant FFT2D is not built)");
@@ -162,6 +168,9 @@ void Solver::set_velocity_bc(const int bc[6]) {
                         pbc[5] == CFDNN_PBC_PERIODIC && pbc[2] == CFDNN_PBC_NEUMANN && pbc[3] == CFDNN_PBC_NEUMANN;
         if (ok) { fft_->set_bc(pbc); fft_active_ = true; }
     }
+    if (multi() && g_.y_stretched && !fft_active_)
+        throw std::invalid_argument("set_velocity_bc: on z-slabs a y-stretched mesh needs the FFT Poisson solver (periodic x/z, "
+                                    "walls y); the semi-coarsening multigrid has no slab variant");
     update_links();
 }
 
@@ -184,7 +193,10 @@ void Solver::comm_init(Comm* c) {
                                         "), got " + std::to_string(mesh_.k_offset));
     }
     comm_ = c;
-    mg_->set_comm(c);
+    // the semi-coarsening (y-stretched) multigrid has no slab variant; with the FFT solver selected and active it is never
+    // called, so a stretched channel can still be decomposed
+    const bool mg_unused = c && c->nranks > 1 && g_.y_stretched && fft_ && fft_active_;
+    if (!mg_unused) mg_->set_comm(c);
     if (fft_) fft_->set_comm(c);                     // the reference's FFT_MPI role: slabs + all-to-all transposes
     update_links();
 }
@@ -440,7 +452,10 @@ void Solver::build_rhs(double dt) {
     const bool dist = comm_ && comm_->nranks > 1;
     const int NzG = mesh_.Nz_global > 0 ? mesh_.Nz_global : g_.Nz;
     const double count = (double)g_.Nx * g_.Ny * NzG;
-    if (g_.y_stretched && !dist) {
+    // Stretched meshes under the multigrid: the reference's loop-order sum, bit for bit (the semi-coarsening solver
+    // amplifies a last-bit change of the right-hand side).  The FFT solver is direct and removes the mean itself, so the
+    // serial sum (25 ms at 192x96x192, 3 per step) is not paid there.
+    if (g_.y_stretched && !dist && !fft_active_) {
         CFDNN_LAUNCH_COOP(k_seq_sum_cells, 1, 256, 0, st_, g_, div_, scalars_.p + 0, count);   // bit-exact mean
     } else {
         CFDNN_LAUNCH_COOP(k_final_sum, 1, 1024, 0, st_, partial_.p, nb, scalars_.p + 0, dist ? 0.0 : count);

@@ -89,7 +89,12 @@ def main():
     Nz = NzG // world
     k0 = rank * Nz
     L = 2 * np.pi
-    mesh = B.mesh(Nx, Ny, Nz, Lz=L, Nz_global=NzG, k_offset=k0)
+    if os.environ.get("SLAB_STRETCH"):          # tanh-stretched y (y in [-1, 1], beta = 2): FFT Poisson only on slabs
+        arrs = R.backend.stretched_y_metrics(Ny, -1.0, 1.0, 2.0)
+        mesh = B.stretched_mesh(Nx, Ny, Nz, arrs, Lx=L, Lz=L, y_lo=-1.0, y_hi=1.0)
+        mesh.dz, mesh.Nz_global, mesh.k_offset = L / NzG, NzG, k0
+    else:
+        mesh = B.mesh(Nx, Ny, Nz, Lz=L, Nz_global=NzG, k_offset=k0)
     cfg = B.config(nu=0.01, dt=0.01, time_integrator=R.TI[ti], convective_scheme=R.SCHEME["skew"], adaptive_dt=0,
                    poisson_fixed_cycles=fixed, poisson_tol_rhs=1e-8, poisson_max_vcycles=50,
                    poisson_solver=1 if os.environ.get("SLAB_POISSON") == "fft" else 0)

@@ -191,11 +191,16 @@ def test_inconsistent_decomposition_is_rejected(sim):
 
 # ---- FFT Poisson on z-slabs (the reference's FFT_MPI role): local x transform, all-to-all, z transform + Thomas on
 # this rank's kx columns, all-to-all back
-def _single_domain_fft(B, R, slab_worker, N, bc, ti, nsteps):
+def _single_domain_fft(B, R, slab_worker, N, bc, ti, nsteps, stretched=False):
     u, v, w = slab_worker.global_init(*N, bc)
     cfg = B.config(nu=0.01, dt=0.01, time_integrator=R.TI[ti], convective_scheme=R.SCHEME["skew"], adaptive_dt=0,
                    poisson_fixed_cycles=0, poisson_tol_rhs=1e-8, poisson_max_vcycles=50, poisson_solver=1)
-    h = B.solver(B.mesh(*N), cfg, bc, (0.5, 0.0, 0.0))
+    if stretched:
+        L = 2 * np.pi
+        md = B.stretched_mesh(*N, R.backend.stretched_y_metrics(N[1], -1.0, 1.0, 2.0), Lx=L, Lz=L, y_lo=-1.0, y_hi=1.0)
+    else:
+        md = B.mesh(*N)
+    h = B.solver(md, cfg, bc, (0.5, 0.0, 0.0))
     B.upload(h, "u", u); B.upload(h, "v", v); B.upload(h, "w", w)
     B.check(B.lib.cfdnn_solver_initialize(h))
     for _ in range(nsteps):
@@ -206,11 +211,13 @@ def _single_domain_fft(B, R, slab_worker, N, bc, ti, nsteps):
     return st, cyc
 
 
-def _check_fft_slabs(B, R, world, N, ti, nsteps, monkeypatch, on_gpu, p2p=None):
+def _check_fft_slabs(B, R, world, N, ti, nsteps, monkeypatch, on_gpu, p2p=None, stretched=False):
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import slab_worker
     bc = "PPWWPP"
     monkeypatch.setenv("SLAB_POISSON", "fft")
+    if stretched:
+        monkeypatch.setenv("SLAB_STRETCH", "1")
     if p2p is not None:
         monkeypatch.setenv("CFDNN_FFT_P2P", "1" if p2p else "0")
     with tempfile.TemporaryDirectory() as td:
@@ -219,7 +226,7 @@ def _check_fft_slabs(B, R, world, N, ti, nsteps, monkeypatch, on_gpu, p2p=None):
         assert [int(s_["fft_p2p"]) for s_ in slabs] == [1 if p2p else 0] * world
     names = ("u", "v", "w", "p", "pcorr", "div", "rhs")
     got = {n: _assemble(slabs, n, N[2] // world) for n in names}
-    single, cyc = _single_domain_fft(B, R, slab_worker, N, bc, ti, nsteps)
+    single, cyc = _single_domain_fft(B, R, slab_worker, N, bc, ti, nsteps, stretched)
     assert list(slabs[0]["cycles"]) == cyc and all(c == 1 for c in cyc)
     for n in names:
         a, b = R.interior(n, got[n]), R.interior(n, single[n])
@@ -231,6 +238,11 @@ def test_two_slabs_fft_poisson_match_single_domain(R, sim, monkeypatch):
     _check_fft_slabs(sim, R, 2, (24, 12, 16), "rk3", 2, monkeypatch, on_gpu=False)
 
 
+def test_two_slabs_fft_poisson_stretched_y(R, sim, monkeypatch):
+    """a y-stretched channel on z-slabs: possible with the FFT solver only (the semi-coarsening multigrid has no slab variant)"""
+    _check_fft_slabs(sim, R, 2, (16, 16, 16), "rk3", 1, monkeypatch, on_gpu=False, stretched=True)
+
+
 @pytest.mark.gpu
 @pytest.mark.parametrize("world", [2, 4, 8])
 def test_gpu_slabs_fft_poisson(R, gpu, world, monkeypatch):
@@ -239,3 +251,5 @@ def test_gpu_slabs_fft_poisson(R, gpu, world, monkeypatch):
     # peer-to-peer transposes (the transform kernels store into the other GPUs' arrays through CUDA IPC) and NCCL all-to-alls
     _check_fft_slabs(gpu, R, world, (128, 48, 32 * world), "rk3", 1, monkeypatch, on_gpu=True, p2p=True)
     _check_fft_slabs(gpu, R, world, (128, 48, 32 * world), "rk3", 2, monkeypatch, on_gpu=True, p2p=False)
+    monkeypatch.delenv("CFDNN_FFT_P2P")
+    _check_fft_slabs(gpu, R, world, (64, 48, 16 * world), "rk3", 1, monkeypatch, on_gpu=True, stretched=True)
