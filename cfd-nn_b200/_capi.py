@@ -129,6 +129,7 @@ _SIGS = {
     "cfdnn_fft_solve": (C.c_int, [C.c_void_p, c_double_p, c_double_p, C.POINTER(C.c_int)]),
     "cfdnn_solver_fft_peer_to_peer": (C.c_int, [C.c_void_p]),
     "cfdnn_solver_set_sst_model": (C.c_int, [C.c_void_p, C.c_int]),
+    "cfdnn_solver_set_rans_model": (C.c_int, [C.c_void_p, C.c_int]),
     "cfdnn_solver_set_mixing_length_params": (C.c_int, [C.c_void_p, C.c_double, C.c_double, C.c_double]),
     "cfdnn_solver_set_gep_params": (C.c_int, [C.c_void_p, C.c_int, C.c_double]),
     "cfdnn_solver_set_pope_constants": (C.c_int, [C.c_void_p, C.c_double, C.c_double]),

@@ -264,6 +264,7 @@ int cfdnn_solver_set_les_model(cfdnn_solver* s, int model, double constant) {
 }
 int cfdnn_solver_fft_peer_to_peer(const cfdnn_solver* s) { return s->impl.fft_peer_to_peer() ? 1 : 0; }
 int cfdnn_solver_set_sst_model(cfdnn_solver* s, int kind) { return guarded([&] { s->impl.set_sst_model(kind); }); }
+int cfdnn_solver_set_rans_model(cfdnn_solver* s, int kind) { return cfdnn_solver_set_sst_model(s, kind); }
 int cfdnn_solver_set_mixing_length_params(cfdnn_solver* s, double kappa, double A_plus, double delta) {
     return guarded([&] { s->impl.set_mixing_length_params(kappa, A_plus, delta); });
 }

@@ -1,4 +1,6 @@
-// sst.cu — SST k-omega transport and closure for 2-D meshes, device-resident inside step().
+// sst.cu — the reference's 2-D RANS closures, device-resident inside step(): SST k-omega transport + SST closure (the
+// file's namesake), standard k-omega + Boussinesq, SST + EARSM (Wallin-Johansson / Gatski-Speziale / Pope), and the
+// algebraic models (mixing length, algebraic k-omega, GEP).  Selected with cfdnn_solver_set_rans_model(CFDNN_RANS_*).
 //
 // Reference: SSTKOmegaTransport (src/turbulence_transport.cpp:315-958, constants include/turbulence_transport.hpp:32-58)
 // with its default SSTClosure (:234-313).  Parity is defined against the reference's CPU path, which advances k and

@@ -240,6 +240,8 @@ enum { CFDNN_RANS_NONE = 0, CFDNN_RANS_SST = 1, CFDNN_RANS_KOMEGA = 2, CFDNN_RAN
         * (turb_model = earsm_wj / earsm_gs / earsm_pope); nu_t and tau_ij (CFDNN_F_TAU_*) are written */
        CFDNN_RANS_EARSM_WJ = 6, CFDNN_RANS_EARSM_GS = 7, CFDNN_RANS_EARSM_POPE = 8 };
 int cfdnn_solver_set_sst_model(cfdnn_solver* s, int kind);
+/* the same entry under the name of what it has become: every 2-D RANS closure of the reference (CFDNN_RANS_*) */
+int cfdnn_solver_set_rans_model(cfdnn_solver* s, int kind);
 /* The algebraic 2-D baselines of src/turbulence_baseline.cpp through the same slot: CFDNN_RANS_MIXING_LENGTH =
  * MixingLengthModel (van Driest mixing length, nu_t under-relaxed with its previous value; `turb_model = baseline`,
  * :36-76, 330-402) and CFDNN_RANS_ALGEBRAIC_KOMEGA = AlgebraicKOmegaModel (:408-483).  Mixing-length constants
