@@ -562,6 +562,8 @@ void FftPoisson::plan(Comm* c) {
     comm_ = c;
     P_ = c ? c->nranks : 1;
     rank_ = c ? c->rank : 0;
+    if (P_ > FFT_MAX_RANKS)
+        throw std::invalid_argument("FFT Poisson: at most " + std::to_string(FFT_MAX_RANKS) + " z-slabs (block pointer table)");
     Pq_ = ((Nxh_ + P_ - 1) / P_ + 7) / 8 * 8;
     const size_t ns = (size_t)Nzg_ * Ny_ * Pq_;     // = P * Nz_local * Ny * Pq
     spec_.alloc(ns, true);
