@@ -221,7 +221,7 @@ def test_step_with_fft_poisson_matches_converged_reference(oracle, sim):
 
 
 # ---- trip forcing + velocity filter
-@pytest.mark.parametrize("kind", ["stretched", "no_w", "2d"])
+@pytest.mark.parametrize("kind", ["uniform", "no_w", "2d"])
 def test_trip_forcing_adds_the_reference_term(sim, kind):
     cases.check_trip_forcing(sim, N=(16, 16, 1) if kind == "2d" else (16, 12, 8), stretched=kind == "stretched",
                              force_w=kind != "no_w")
@@ -237,17 +237,17 @@ def test_step_with_sst_k_omega_matches_reference(sim, oracle, kind, ti):
     cases.check_step_with_sst(sim, oracle, stretched=kind == "stretched", ti=ti)
 
 
-@pytest.mark.parametrize("kind", ["stretched"])
+@pytest.mark.parametrize("kind", ["uniform"])          # stretched (x-only semi-coarsening, slow on the test double): GPU
 def test_step_with_standard_k_omega_matches_reference(sim, oracle, kind):
     cases.check_step_with_sst(sim, oracle, stretched=kind == "stretched", ti="rk3", model="komega")
 
 
-@pytest.mark.parametrize("model,kind", [("baseline", "stretched"), ("algebraic_komega", "uniform")])
+@pytest.mark.parametrize("model,kind", [("baseline", "uniform"), ("algebraic_komega", "uniform")])
 def test_step_with_algebraic_rans_baselines(sim, oracle, model, kind):
     cases.check_step_with_algebraic_rans(sim, oracle, model=model, stretched=kind == "stretched")
 
 
-@pytest.mark.parametrize("variant,kind", [(0, "uniform"), (1, "stretched")])
+@pytest.mark.parametrize("variant,kind", [(0, "uniform"), (1, "uniform")])
 def test_step_with_gep_closure(sim, oracle, variant, kind):
     cases.check_step_with_algebraic_rans(sim, oracle, model="gep", stretched=kind == "stretched", gep_variant=variant)
 
@@ -256,6 +256,6 @@ def test_sst_rejects_3d_meshes(sim):
     cases.check_sst_rejects_3d(sim)
 
 
-@pytest.mark.parametrize("model,kind", [("earsm_wj", "uniform"), ("earsm_gs", "stretched"), ("earsm_pope", "uniform")])
+@pytest.mark.parametrize("model,kind", [("earsm_wj", "uniform"), ("earsm_gs", "uniform"), ("earsm_pope", "uniform")])
 def test_step_with_sst_earsm_closures(sim, oracle, model, kind):
     cases.check_step_with_sst(sim, oracle, stretched=kind == "stretched", ti="rk3", model=model)
