@@ -260,6 +260,9 @@ def main():
     ap.add_argument("--no-second", action="store_true", help="skip the closure-free second measurement")
     args = ap.parse_args()
     wl = WORKLOADS[args.workload]
+    if args.poisson == "fft" and wl["kind"] != "chan":
+        raise SystemExit("--poisson fft needs a channel workload (periodic x/z, walls y): the solver falls back to the multigrid "
+                         "on a fully periodic box, which is not what this flag is for")
     if args.closure is None:
         args.closure = "tbnn" if wl["kind"] == "tgv" else "none"
     if args.impl == "reference":
