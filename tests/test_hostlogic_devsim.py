@@ -20,7 +20,7 @@ def _plain_smoother_on_the_test_double(monkeypatch, request):
 
 @pytest.mark.tiled
 def test_blocked_smoother_on_the_test_double(sim, oracle):
-    case = ("per32_conv1e5", (32, 32, 32), "PPPPPP", 0, dict(tol_rhs=1e-5, maxv=50, tol_rel=0, tol=0))   # tiled levels 32 and 16
+    case = cases.MG_CASES[1]                                   # per32_conv1e8: 32^3, tiled levels 32 and 16
     with tempfile.TemporaryDirectory() as td:
         meta, pref = cases.run_mg_ref(case, td)
     st, p = cases.run_mg_backend(sim, case)
@@ -144,11 +144,11 @@ def test_nan_guard_raises_runtime_error(sim):
 
 @pytest.mark.parametrize("stretched", [False, True], ids=["uniform", "stretched_dyv_quirk"])
 def test_adaptive_dt_matches_reference(sim, oracle, stretched):
-    cases.check_adaptive_dt(sim, oracle, stretched=stretched, nsteps=1 if stretched else 2)     # 3 steps on the GPU
+    cases.check_adaptive_dt(sim, oracle, stretched=stretched)
 
 
 def test_adaptive_dt_with_implicit_y_diffusion(sim, oracle):
-    cases.check_adaptive_dt(sim, oracle, implicit=True, nsteps=1)                               # 3 steps on the GPU
+    cases.check_adaptive_dt(sim, oracle, implicit=True)
 
 
 def test_diffusion_cfl_recheck_with_closure(sim, oracle):
@@ -221,7 +221,7 @@ def test_step_with_fft_poisson_matches_converged_reference(oracle, sim):
 
 
 # ---- trip forcing + velocity filter
-@pytest.mark.parametrize("kind", ["uniform", "no_w", "2d"])
+@pytest.mark.parametrize("kind", ["uniform", "stretched", "no_w", "2d"])
 def test_trip_forcing_adds_the_reference_term(sim, kind):
     cases.check_trip_forcing(sim, N=(16, 16, 1) if kind == "2d" else (16, 12, 8), stretched=kind == "stretched",
                              force_w=kind != "no_w")
@@ -232,22 +232,23 @@ def test_velocity_filter_matches_restatement(sim):
 
 
 # ---- SST k-omega transport + closure on 2-D meshes
-@pytest.mark.parametrize("kind,ti", [("uniform", "euler"), ("stretched", "rk3")])        # all three on the GPU
+@pytest.mark.parametrize("kind,ti", [("uniform", "rk3"), ("uniform", "euler"), ("stretched", "rk3")])
 def test_step_with_sst_k_omega_matches_reference(sim, oracle, kind, ti):
     cases.check_step_with_sst(sim, oracle, stretched=kind == "stretched", ti=ti)
 
 
-@pytest.mark.parametrize("kind", ["uniform"])          # stretched (x-only semi-coarsening, slow on the test double): GPU
+@pytest.mark.parametrize("kind", ["uniform", "stretched"])
 def test_step_with_standard_k_omega_matches_reference(sim, oracle, kind):
     cases.check_step_with_sst(sim, oracle, stretched=kind == "stretched", ti="rk3", model="komega")
 
 
-@pytest.mark.parametrize("model,kind", [("baseline", "uniform"), ("algebraic_komega", "uniform")])
+@pytest.mark.parametrize("model,kind", [("baseline", "uniform"), ("baseline", "stretched"), ("algebraic_komega", "uniform"),
+                                        ("algebraic_komega", "stretched")])
 def test_step_with_algebraic_rans_baselines(sim, oracle, model, kind):
     cases.check_step_with_algebraic_rans(sim, oracle, model=model, stretched=kind == "stretched")
 
 
-@pytest.mark.parametrize("variant,kind", [(0, "uniform"), (1, "uniform")])
+@pytest.mark.parametrize("variant,kind", [(0, "uniform"), (1, "stretched"), (2, "uniform")])
 def test_step_with_gep_closure(sim, oracle, variant, kind):
     cases.check_step_with_algebraic_rans(sim, oracle, model="gep", stretched=kind == "stretched", gep_variant=variant)
 
@@ -256,6 +257,7 @@ def test_sst_rejects_3d_meshes(sim):
     cases.check_sst_rejects_3d(sim)
 
 
-@pytest.mark.parametrize("model,kind", [("earsm_wj", "uniform"), ("earsm_gs", "uniform"), ("earsm_pope", "uniform")])
+@pytest.mark.parametrize("model,kind", [("earsm_wj", "uniform"), ("earsm_gs", "stretched"), ("earsm_pope", "uniform"),
+                                        ("earsm_wj", "stretched")])
 def test_step_with_sst_earsm_closures(sim, oracle, model, kind):
     cases.check_step_with_sst(sim, oracle, stretched=kind == "stretched", ti="rk3", model=model)

@@ -48,7 +48,7 @@ def _assemble(slabs, name, Nz):
 
 
 @pytest.mark.parametrize("bc,ti,fixed,nsteps,N",
-                         [("PPPPPP", "rk3", 4, 1, (16, 16, 32)), ("PPWWPP", "rk2", 0, 1, (16, 8, 32)),
+                         [("PPPPPP", "rk3", 4, 1, (16, 16, 32)), ("PPWWPP", "rk2", 0, 1, (16, 16, 32)),
                           ("PPWWWW", "euler", 3, 2, (16, 16, 32)), ("PPPPPP", "euler", 2, 1, (16, 16, 64))],
                          ids=["tgv_periodic_rk3", "channel_rk2_converge", "duct_z_walls_euler", "tgv_overlapped_halo"])
 def test_two_slabs_match_single_domain(R, oracle, sim, bc, ti, fixed, nsteps, N, monkeypatch):
