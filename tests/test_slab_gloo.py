@@ -238,6 +238,13 @@ def test_two_slabs_fft_poisson_match_single_domain(R, sim, monkeypatch):
     _check_fft_slabs(sim, R, 2, (24, 12, 16), "rk3", 2, monkeypatch, on_gpu=False)
 
 
+@pytest.mark.parametrize("world,N", [(4, (12, 6, 16)), (3, (10, 5, 12))], ids=["4_ranks", "3_ranks"])
+def test_more_slabs_fft_poisson_ragged_columns(R, sim, monkeypatch, world, N):
+    """more ranks than kx column blocks fill evenly: Nxh = 7 (6) columns over 4 (3) ranks of 8 padded columns each, so the
+    last ranks own no mode at all; z-slabs of 4 planes"""
+    _check_fft_slabs(sim, R, world, N, "rk3", 1, monkeypatch, on_gpu=False)
+
+
 def test_two_slabs_fft_poisson_stretched_y(R, sim, monkeypatch):
     """a y-stretched channel on z-slabs: possible with the FFT solver only (the semi-coarsening multigrid has no slab variant)"""
     _check_fft_slabs(sim, R, 2, (16, 16, 16), "rk3", 1, monkeypatch, on_gpu=False, stretched=True)
