@@ -52,6 +52,15 @@ def _assemble(slabs, name, Nz):
                           ("PPWWWW", "euler", 3, 2, (16, 16, 32)), ("PPPPPP", "euler", 2, 1, (16, 16, 64))],
                          ids=["tgv_periodic_rk3", "channel_rk2_converge", "duct_z_walls_euler", "tgv_overlapped_halo"])
 def test_two_slabs_match_single_domain(R, oracle, sim, bc, ti, fixed, nsteps, N, monkeypatch):
+    _check_mg_slabs(R, 2, bc, ti, fixed, nsteps, N, monkeypatch)
+
+
+def test_four_slabs_match_single_domain(R, oracle, sim, monkeypatch):
+    """four ranks: interior ranks have two slab interfaces, the end ranks wrap around periodically"""
+    _check_mg_slabs(R, 4, "PPPPPP", "rk3", 3, 1, (16, 16, 64), monkeypatch)
+
+
+def _check_mg_slabs(R, world, bc, ti, fixed, nsteps, N, monkeypatch):
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     # small boxes: keep the coarse levels distributed (the default replicates levels of <= 128^3 cells) and
     # put the fused residual + restriction on them, so the slab paths of both stay covered on CPU
@@ -62,7 +71,7 @@ def test_two_slabs_match_single_domain(R, oracle, sim, bc, ti, fixed, nsteps, N,
     # (16, 16, 64): 32 planes per slab = 4 z chunks of the blocked smoother, so the halo exchange is overlapped
     # with the inner chunks (split launch, Multigrid::sweeps_tb)
     with tempfile.TemporaryDirectory() as td:
-        slabs = _run_slabs(2, N, bc, ti, nsteps, fixed, td)
+        slabs = _run_slabs(world, N, bc, ti, nsteps, fixed, td)
         u, v, w = slab_worker.global_init(*N, bc)
         pre = os.path.join(td, "in")
         u.tofile(pre + "_u.f64"); v.tofile(pre + "_v.f64"); w.tofile(pre + "_w.f64")
@@ -72,12 +81,12 @@ def test_two_slabs_match_single_domain(R, oracle, sim, bc, ti, fixed, nsteps, N,
                          dt=0.01, nu=0.01, init="file:" + pre, call_initialize=1, fx=force[0], fy=force[1], fz=force[2],
                          out=os.path.join(td, "ref"), **extra)
         ref = R.load_state(os.path.join(td, "ref_final"), *N)
-    Nz = N[2] // 2
+    Nz = N[2] // world
     got = {n: _assemble(slabs, n, Nz) for n in ("u", "v", "w", "p", "pcorr", "div", "rhs")}
     for n in got:
         assert got[n].shape == ref[n].shape, (n, got[n].shape, ref[n].shape)
-    cases.compare_states(got, ref, 1e-10, f"2 slabs {bc} {ti}")
-    assert list(slabs[0]["cycles"]) == list(slabs[1]["cycles"])
+    cases.compare_states(got, ref, 1e-10, f"{world} slabs {bc} {ti}")
+    assert all(list(s_["cycles"]) == list(slabs[0]["cycles"]) for s_ in slabs)
     if meta["cycles"]:
         assert list(slabs[0]["cycles"]) == meta["cycles"]
     assert slabs[0]["residuals"] == pytest.approx(meta["residuals"], rel=1e-9)
